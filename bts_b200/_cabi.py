@@ -1,0 +1,84 @@
+"""ctypes binding of libbts_b200.so (include/bts_b200.h). No fallback: a missing library is an error."""
+import ctypes
+import os
+import re
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libbts_b200.so")
+HEADER_PATH = os.path.join(_HERE, "..", "include", "bts_b200.h")
+
+_c_float_p = ctypes.c_void_p  # raw device pointers travel as integers
+
+_SIGNATURES = {
+    "bts_abi_version": (ctypes.c_int, []),
+    "bts_last_error": (ctypes.c_char_p, []),
+    "bts_force_path": (None, [ctypes.c_int]),
+    "bts_reduc_path": (ctypes.c_int, [ctypes.POINTER(ctypes.c_int), ctypes.c_int, ctypes.c_int]),
+    "bts_lpg_fwd": (ctypes.c_int, [_c_float_p, _c_float_p, _c_float_p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                   ctypes.c_int, ctypes.c_float, ctypes.c_void_p]),
+    "bts_lpg_bwd": (ctypes.c_int, [_c_float_p, _c_float_p, _c_float_p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                   ctypes.c_int, ctypes.c_float, ctypes.c_void_p]),
+    "bts_workspace_bytes": (ctypes.c_size_t, [ctypes.POINTER(ctypes.c_int), ctypes.c_int, ctypes.c_int,
+                                              ctypes.c_int, ctypes.c_int, ctypes.c_int]),
+    "bts_reduc_fwd": (ctypes.c_int, [_c_float_p, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_int),
+                                     ctypes.c_int, ctypes.c_int, ctypes.c_float, ctypes.c_int, ctypes.c_int,
+                                     ctypes.c_int, _c_float_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]),
+    "bts_reduc_bwd": (ctypes.c_int, [_c_float_p, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_int),
+                                     ctypes.c_int, ctypes.c_int, ctypes.c_float, ctypes.c_int, ctypes.c_int,
+                                     ctypes.c_int, _c_float_p, _c_float_p, ctypes.POINTER(ctypes.c_void_p),
+                                     ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]),
+    "bts_reduc_lpg_fwd": (ctypes.c_int, [_c_float_p, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_int),
+                                         ctypes.c_int, ctypes.c_float, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                         ctypes.c_int, ctypes.c_float, _c_float_p, _c_float_p, _c_float_p,
+                                         ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]),
+    "bts_reduc_lpg_bwd": (ctypes.c_int, [_c_float_p, _c_float_p, ctypes.POINTER(ctypes.c_void_p),
+                                         ctypes.POINTER(ctypes.c_int), ctypes.c_int, ctypes.c_float, ctypes.c_int,
+                                         ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_float, _c_float_p,
+                                         ctypes.POINTER(ctypes.c_void_p), ctypes.c_void_p, ctypes.c_size_t,
+                                         ctypes.c_void_p]),
+}
+
+_lib = None
+
+
+class BtsLibraryError(RuntimeError):
+    pass
+
+
+def declared_symbols(header=HEADER_PATH):
+    """Names of every BTS_API function the public header declares."""
+    with open(header) as f:
+        return re.findall(r"BTS_API\s+[\w\s\*]+?\b(bts_\w+)\s*\(", f.read())
+
+
+def lib():
+    """The loaded C-ABI library. Raises loudly when it has not been built (no CPU / torch fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise BtsLibraryError(
+                "libbts_b200.so is missing (%s). Build it with `python -m bts_b200.build` "
+                "(or __graft_entry__.build()). bts_b200 has no CPU or PyTorch fallback." % LIB_PATH)
+        l = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(l, name)
+            fn.restype = res
+            fn.argtypes = args
+        if l.bts_abi_version() != 1:
+            raise BtsLibraryError("libbts_b200.so ABI version %d, expected 1" % l.bts_abi_version())
+        _lib = l
+    return _lib
+
+
+def check(code, what):
+    if code != 0:
+        msg = lib().bts_last_error().decode("utf-8", "replace")
+        raise RuntimeError("%s failed (code %d): %s" % (what, code, msg))
+
+
+def int_array(values):
+    return (ctypes.c_int * len(values))(*values)
+
+
+def ptr_array(ptrs):
+    return (ctypes.c_void_p * len(ptrs))(*ptrs)

@@ -1,0 +1,189 @@
+// cabi.cu -- extern "C" entry points of libbts_b200.so (declared in include/bts_b200.h).
+// Argument validation, path selection and error plumbing only; kernels live in the other files.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "common.cuh"
+
+namespace bts {
+
+static thread_local char g_err[512] = "";
+static thread_local int g_force_path = -1;
+
+int set_error(int code, const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+int check_launch(const char *what)
+{
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return set_error((int)e, "%s: launch failed: %s", what, cudaGetErrorString(e));
+    return BTS_OK;
+}
+
+// kernels / launchers implemented elsewhere
+int launch_lpg_fwd(const float *, float *, float *, int, int, int, int, float, cudaStream_t);
+int launch_lpg_bwd(const float *, const float *, float *, int, int, int, int, float, cudaStream_t);
+int launch_chain_generic_fwd(const ChainParams &, const float *, float *, int, int, cudaStream_t);
+int launch_chain_generic_bwd(const ChainParams &, const float *, const float *, float *, int, int, cudaStream_t);
+
+static int fill_chain(ChainParams &cp, const float *const *W, float *const *gW, const int *dims,
+                      int n_layers, int is_final, float max_depth)
+{
+    if (dims == nullptr || W == nullptr) return set_error(BTS_ERR_BAD_ARG, "dims / W is NULL");
+    if (n_layers < 1 || n_layers > BTS_MAX_LAYERS)
+        return set_error(BTS_ERR_BAD_ARG, "n_layers=%d outside [1,%d]", n_layers, BTS_MAX_LAYERS);
+    memset(&cp, 0, sizeof(cp));
+    for (int l = 0; l <= n_layers; ++l) {
+        if (dims[l] < 1 || dims[l] > BTS_MAX_CHANNELS)
+            return set_error(BTS_ERR_BAD_ARG, "dims[%d]=%d outside [1,%d]", l, dims[l], BTS_MAX_CHANNELS);
+        cp.dims[l] = dims[l];
+    }
+    const int last = dims[n_layers];
+    if (is_final ? last != 1 : last != 3)
+        return set_error(BTS_ERR_BAD_ARG, "last layer must have %d outputs, got %d", is_final ? 1 : 3, last);
+    int n_null = 0;
+    for (int l = 0; l < n_layers; ++l) {
+        if (W[l] == nullptr) return set_error(BTS_ERR_BAD_ARG, "W[%d] is NULL", l);
+        cp.W[l] = W[l];
+        cp.gW[l] = gW ? gW[l] : nullptr;
+        if (gW && gW[l] == nullptr) ++n_null;
+    }
+    if (gW && n_null != 0 && n_null != n_layers)
+        return set_error(BTS_ERR_BAD_ARG, "grad_W entries must be all NULL or all non-NULL");
+    cp.n_layers = n_layers;
+    cp.is_final = is_final ? 1 : 0;
+    cp.max_depth = max_depth;
+    return BTS_OK;
+}
+
+static int check_shape(int B, int h, int w)
+{
+    if (B < 0 || h < 0 || w < 0) return set_error(BTS_ERR_BAD_ARG, "negative size B=%d h=%d w=%d", B, h, w);
+    if ((long long)B * h * w > (1ll << 31) - 1) return set_error(BTS_ERR_UNSUPPORTED, "more than 2^31 low-res pixels");
+    return BTS_OK;
+}
+
+}  // namespace bts
+
+using namespace bts;
+
+extern "C" {
+
+int bts_abi_version(void) { return BTS_ABI_VERSION; }
+const char *bts_last_error(void) { return g_err; }
+void bts_force_path(int path) { g_force_path = path; }
+
+int bts_reduc_path(const int *dims, int n_layers, int is_final)
+{
+    (void)dims; (void)n_layers; (void)is_final;
+    return BTS_PATH_GENERIC;
+}
+
+int bts_lpg_fwd(const float *plane_eq, float *depth, float *abs_min, int B, int h, int w, int r,
+                float eps, void *stream)
+{
+    if (int e = check_shape(B, h, w)) return e;
+    if (r < 1) return set_error(BTS_ERR_BAD_ARG, "upratio r=%d must be >= 1", r);
+    if ((long long)B * h * w == 0) return BTS_OK;                     // empty input: nothing to do
+    if (!plane_eq || !depth) return set_error(BTS_ERR_BAD_ARG, "plane_eq / depth is NULL");
+    if ((long long)B * h * r * w * r > (1ll << 40)) return set_error(BTS_ERR_UNSUPPORTED, "output too large");
+    return launch_lpg_fwd(plane_eq, depth, abs_min, B, h, w, r, eps, (cudaStream_t)stream);
+}
+
+int bts_lpg_bwd(const float *grad_depth, const float *plane_eq, float *grad_plane_eq, int B, int h,
+                int w, int r, float eps, void *stream)
+{
+    if (int e = check_shape(B, h, w)) return e;
+    if (r < 1) return set_error(BTS_ERR_BAD_ARG, "upratio r=%d must be >= 1", r);
+    if ((long long)B * h * w == 0) return BTS_OK;
+    if (!grad_depth || !plane_eq || !grad_plane_eq)
+        return set_error(BTS_ERR_BAD_ARG, "grad_depth / plane_eq / grad_plane_eq is NULL");
+    return launch_lpg_bwd(grad_depth, plane_eq, grad_plane_eq, B, h, w, r, eps, (cudaStream_t)stream);
+}
+
+size_t bts_workspace_bytes(const int *dims, int n_layers, int B, int h, int w, int r)
+{
+    (void)dims; (void)n_layers;
+    if (B <= 0 || h <= 0 || w <= 0) return 0;
+    // fused generic path: plane_eq (fwd) / grad_plane_eq + plane_eq (bwd) staging when r > 0
+    return r > 0 ? (size_t)2 * 4 * sizeof(float) * (size_t)B * h * w : 0;
+}
+
+int bts_reduc_fwd(const float *x, const float *const *W, const int *dims, int n_layers, int is_final,
+                  float max_depth, int B, int h, int w, float *out, void *ws, size_t ws_bytes, void *stream)
+{
+    (void)ws; (void)ws_bytes;
+    ChainParams cp;
+    if (int e = fill_chain(cp, W, nullptr, dims, n_layers, is_final, max_depth)) return e;
+    if (int e = check_shape(B, h, w)) return e;
+    if ((long long)B * h * w == 0) return BTS_OK;
+    if (!x || !out) return set_error(BTS_ERR_BAD_ARG, "x / out is NULL");
+    return launch_chain_generic_fwd(cp, x, out, B, h * w, (cudaStream_t)stream);
+}
+
+int bts_reduc_bwd(const float *x, const float *const *W, const int *dims, int n_layers, int is_final,
+                  float max_depth, int B, int h, int w, const float *grad_out, float *grad_x,
+                  float *const *grad_W, void *ws, size_t ws_bytes, void *stream)
+{
+    (void)ws; (void)ws_bytes;
+    ChainParams cp;
+    if (int e = fill_chain(cp, W, grad_W, dims, n_layers, is_final, max_depth)) return e;
+    if (int e = check_shape(B, h, w)) return e;
+    if ((long long)B * h * w == 0) return BTS_OK;
+    if (!x || !grad_out) return set_error(BTS_ERR_BAD_ARG, "x / grad_out is NULL");
+    return launch_chain_generic_bwd(cp, x, grad_out, grad_x, B, h * w, (cudaStream_t)stream);
+}
+
+int bts_reduc_lpg_fwd(const float *x, const float *const *W, const int *dims, int n_layers,
+                      float max_depth, int B, int h, int w, int r, float eps, float *plane_eq_out,
+                      float *depth, float *abs_min, void *ws, size_t ws_bytes, void *stream)
+{
+    ChainParams cp;
+    if (int e = fill_chain(cp, W, nullptr, dims, n_layers, 0, max_depth)) return e;
+    if (int e = check_shape(B, h, w)) return e;
+    if (r < 1) return set_error(BTS_ERR_BAD_ARG, "upratio r=%d must be >= 1", r);
+    if ((long long)B * h * w == 0) return BTS_OK;
+    if (!x || !depth) return set_error(BTS_ERR_BAD_ARG, "x / depth is NULL");
+    float *pe = plane_eq_out;
+    if (pe == nullptr) {
+        const size_t need = (size_t)4 * sizeof(float) * (size_t)B * h * w;
+        if (ws == nullptr || ws_bytes < need)
+            return set_error(BTS_ERR_WORKSPACE, "workspace %zu B < %zu B", ws_bytes, need);
+        pe = static_cast<float *>(ws);
+    }
+    if (int e = launch_chain_generic_fwd(cp, x, pe, B, h * w, (cudaStream_t)stream)) return e;
+    return launch_lpg_fwd(pe, depth, abs_min, B, h, w, r, eps, (cudaStream_t)stream);
+}
+
+int bts_reduc_lpg_bwd(const float *grad_depth, const float *x, const float *const *W, const int *dims,
+                      int n_layers, float max_depth, int B, int h, int w, int r, float eps,
+                      float *grad_x, float *const *grad_W, void *ws, size_t ws_bytes, void *stream)
+{
+    ChainParams cp;
+    if (int e = fill_chain(cp, W, grad_W, dims, n_layers, 0, max_depth)) return e;
+    if (int e = check_shape(B, h, w)) return e;
+    if (r < 1) return set_error(BTS_ERR_BAD_ARG, "upratio r=%d must be >= 1", r);
+    if ((long long)B * h * w == 0) return BTS_OK;
+    if (!x || !grad_depth) return set_error(BTS_ERR_BAD_ARG, "x / grad_depth is NULL");
+    const size_t one = (size_t)4 * sizeof(float) * (size_t)B * h * w;
+    if (ws == nullptr || ws_bytes < 2 * one)
+        return set_error(BTS_ERR_WORKSPACE, "workspace %zu B < %zu B", ws_bytes, 2 * one);
+    float *pe = static_cast<float *>(ws);
+    float *gpe = pe + (size_t)4 * B * h * w;
+    cudaStream_t s = (cudaStream_t)stream;
+    // generic route: recompute plane_eq, reduce grad_depth over each r x r block, then the chain.
+    ChainParams cf = cp;
+    for (int l = 0; l < BTS_MAX_LAYERS; ++l) cf.gW[l] = nullptr;
+    if (int e = launch_chain_generic_fwd(cf, x, pe, B, h * w, s)) return e;
+    if (int e = launch_lpg_bwd(grad_depth, pe, gpe, B, h, w, r, eps, s)) return e;
+    return launch_chain_generic_bwd(cp, x, gpe, grad_x, B, h * w, s);
+}
+
+}  // extern "C"

@@ -1,0 +1,193 @@
+"""torch.autograd.Function wrappers over the C ABI (include/bts_b200.h).
+
+PyTorch is plumbing here: it owns device memory, the current stream and the autograd graph. All
+arithmetic happens in libbts_b200.so. Tensors must be CUDA fp32; anything else raises (no fallback).
+"""
+import torch
+
+from . import _cabi
+
+EPS = 1e-3  # pytorch/bts.py:168
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _require_cuda_f32(t, name):
+    if not isinstance(t, torch.Tensor):
+        raise TypeError("%s must be a torch.Tensor" % name)
+    if not t.is_cuda:
+        raise RuntimeError("%s is on %s: bts_b200 runs on CUDA (sm_100a) only and has no CPU fallback" % (name, t.device))
+    if t.dtype != torch.float32:
+        raise RuntimeError("%s has dtype %s: the fp32 path expects torch.float32" % (name, t.dtype))
+    return t.contiguous()
+
+
+def _weights2d(weights):
+    ws = []
+    for i, w in enumerate(weights):
+        w = _require_cuda_f32(w, "weight[%d]" % i)
+        if w.dim() == 4:
+            if w.shape[2] != 1 or w.shape[3] != 1:
+                raise RuntimeError("weight[%d] must be a 1x1 convolution kernel, got %s" % (i, tuple(w.shape)))
+        elif w.dim() != 2:
+            raise RuntimeError("weight[%d] must be [out,in,1,1] or [out,in]" % i)
+        ws.append(w)
+    return ws
+
+
+def _dims(x, ws):
+    dims = [x.shape[1]] + [w.shape[0] for w in ws]
+    for l, w in enumerate(ws):
+        if w.shape[1] != dims[l]:
+            raise RuntimeError("weight[%d] expects %d input channels, chain provides %d" % (l, w.shape[1], dims[l]))
+    return dims
+
+
+def _workspace(dims, B, h, w, r, device):
+    n = _cabi.lib().bts_workspace_bytes(_cabi.int_array(dims), len(dims) - 1, B, h, w, r)
+    if n == 0:
+        return None, 0, 0
+    ws = torch.empty((n + 3) // 4, dtype=torch.float32, device=device)
+    return ws, ws.data_ptr(), n
+
+
+class _LPG(torch.autograd.Function):
+    """local_planar_guidance.forward (pytorch/bts.py:149-173) and its autograd backward."""
+
+    @staticmethod
+    def forward(ctx, plane_eq, upratio):
+        plane_eq = _require_cuda_f32(plane_eq, "plane_eq")
+        if plane_eq.dim() != 4 or plane_eq.shape[1] != 4:
+            raise RuntimeError("plane_eq must be [B,4,h,w], got %s" % (tuple(plane_eq.shape),))
+        B, _, h, w = plane_eq.shape
+        r = int(upratio)
+        depth = torch.empty((B, h * r, w * r), dtype=torch.float32, device=plane_eq.device)
+        abs_min = torch.full((), float("inf"), dtype=torch.float32, device=plane_eq.device)
+        with torch.cuda.device(plane_eq.device):
+            _cabi.check(_cabi.lib().bts_lpg_fwd(plane_eq.data_ptr(), depth.data_ptr(), abs_min.data_ptr(),
+                                                B, h, w, r, EPS, _stream()), "bts_lpg_fwd")
+        ctx.save_for_backward(plane_eq)
+        ctx.r = r
+        ctx.mark_non_differentiable(abs_min)
+        return depth, abs_min
+
+    @staticmethod
+    def backward(ctx, grad_depth, _grad_abs_min):
+        (plane_eq,) = ctx.saved_tensors
+        grad_depth = _require_cuda_f32(grad_depth, "grad_depth")
+        B, _, h, w = plane_eq.shape
+        gpe = torch.empty_like(plane_eq)
+        with torch.cuda.device(plane_eq.device):
+            _cabi.check(_cabi.lib().bts_lpg_bwd(grad_depth.data_ptr(), plane_eq.data_ptr(), gpe.data_ptr(),
+                                                B, h, w, ctx.r, EPS, _stream()), "bts_lpg_bwd")
+        return gpe, None
+
+
+class _Reduc(torch.autograd.Function):
+    """reduction_1x1.forward (pytorch/bts.py:124-136) and its autograd backward (chain recomputed)."""
+
+    @staticmethod
+    def forward(ctx, x, max_depth, is_final, *weights):
+        x = _require_cuda_f32(x, "net")
+        if x.dim() != 4:
+            raise RuntimeError("net must be [B,C,h,w], got %s" % (tuple(x.shape),))
+        ws = _weights2d(weights)
+        dims = _dims(x, ws)
+        B, _, h, w = x.shape
+        out = torch.empty((B, 1 if is_final else 4, h, w), dtype=torch.float32, device=x.device)
+        wsb, wsp, wsn = _workspace(dims, B, h, w, 0, x.device)
+        with torch.cuda.device(x.device):
+            _cabi.check(_cabi.lib().bts_reduc_fwd(x.data_ptr(), _cabi.ptr_array([t.data_ptr() for t in ws]),
+                                                  _cabi.int_array(dims), len(ws), int(bool(is_final)),
+                                                  float(max_depth), B, h, w, out.data_ptr(), wsp, wsn, _stream()),
+                        "bts_reduc_fwd")
+        ctx.save_for_backward(x, *ws)
+        ctx.cfg = (float(max_depth), bool(is_final), dims, [tuple(t.shape) for t in weights])
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        x, *ws = ctx.saved_tensors
+        max_depth, is_final, dims, shapes = ctx.cfg
+        grad_out = _require_cuda_f32(grad_out, "grad_out")
+        B, _, h, w = x.shape
+        need_x = ctx.needs_input_grad[0]
+        need_w = any(ctx.needs_input_grad[3:])
+        gx = torch.empty_like(x) if need_x else None
+        gws = [torch.zeros_like(t) for t in ws] if need_w else None
+        wsb, wsp, wsn = _workspace(dims, B, h, w, 0, x.device)
+        with torch.cuda.device(x.device):
+            _cabi.check(_cabi.lib().bts_reduc_bwd(
+                x.data_ptr(), _cabi.ptr_array([t.data_ptr() for t in ws]), _cabi.int_array(dims), len(ws),
+                int(is_final), max_depth, B, h, w, grad_out.data_ptr(), gx.data_ptr() if need_x else None,
+                _cabi.ptr_array([t.data_ptr() for t in gws]) if need_w else None, wsp, wsn, _stream()),
+                "bts_reduc_bwd")
+        gw_out = [g.view(s) for g, s in zip(gws, shapes)] if need_w else [None] * len(ws)
+        return (gx, None, None, *gw_out)
+
+
+class _ReducLPG(torch.autograd.Function):
+    """Fused decoder stage reducNxN -> normalise/cat -> lpgNxN (pytorch/bts.py:249-254)."""
+
+    @staticmethod
+    def forward(ctx, x, max_depth, upratio, want_plane_eq, *weights):
+        x = _require_cuda_f32(x, "net")
+        if x.dim() != 4:
+            raise RuntimeError("net must be [B,C,h,w], got %s" % (tuple(x.shape),))
+        ws = _weights2d(weights)
+        dims = _dims(x, ws)
+        B, _, h, w = x.shape
+        r = int(upratio)
+        depth = torch.empty((B, h * r, w * r), dtype=torch.float32, device=x.device)
+        abs_min = torch.full((), float("inf"), dtype=torch.float32, device=x.device)
+        plane_eq = torch.empty((B, 4, h, w), dtype=torch.float32, device=x.device) if want_plane_eq else None
+        wsb, wsp, wsn = _workspace(dims, B, h, w, r, x.device)
+        with torch.cuda.device(x.device):
+            _cabi.check(_cabi.lib().bts_reduc_lpg_fwd(
+                x.data_ptr(), _cabi.ptr_array([t.data_ptr() for t in ws]), _cabi.int_array(dims), len(ws),
+                float(max_depth), B, h, w, r, EPS, plane_eq.data_ptr() if want_plane_eq else None,
+                depth.data_ptr(), abs_min.data_ptr(), wsp, wsn, _stream()), "bts_reduc_lpg_fwd")
+        ctx.save_for_backward(x, *ws)
+        ctx.cfg = (float(max_depth), r, dims, [tuple(t.shape) for t in weights])
+        ctx.mark_non_differentiable(abs_min)
+        if want_plane_eq:
+            ctx.mark_non_differentiable(plane_eq)
+            return depth, abs_min, plane_eq
+        return depth, abs_min
+
+    @staticmethod
+    def backward(ctx, grad_depth, *_ignored):
+        x, *ws = ctx.saved_tensors
+        max_depth, r, dims, shapes = ctx.cfg
+        grad_depth = _require_cuda_f32(grad_depth, "grad_depth")
+        B, _, h, w = x.shape
+        need_x = ctx.needs_input_grad[0]
+        need_w = any(ctx.needs_input_grad[4:])
+        gx = torch.empty_like(x) if need_x else None
+        gws = [torch.zeros_like(t) for t in ws] if need_w else None
+        wsb, wsp, wsn = _workspace(dims, B, h, w, r, x.device)
+        with torch.cuda.device(x.device):
+            _cabi.check(_cabi.lib().bts_reduc_lpg_bwd(
+                grad_depth.data_ptr(), x.data_ptr(), _cabi.ptr_array([t.data_ptr() for t in ws]),
+                _cabi.int_array(dims), len(ws), max_depth, B, h, w, r, EPS, gx.data_ptr() if need_x else None,
+                _cabi.ptr_array([t.data_ptr() for t in gws]) if need_w else None, wsp, wsn, _stream()),
+                "bts_reduc_lpg_bwd")
+        gw_out = [g.view(s) for g, s in zip(gws, shapes)] if need_w else [None] * len(ws)
+        return (gx, None, None, None, *gw_out)
+
+
+def lpg(plane_eq, upratio):
+    """-> (depth [B,h*r,w*r], abs_min 0-dim). Drop-in math of local_planar_guidance.forward."""
+    return _LPG.apply(plane_eq, upratio)
+
+
+def reduc(x, weights, max_depth, is_final=False):
+    """-> [B,4,h,w] plane parameters, or [B,1,h,w] sigmoid head. Drop-in math of reduction_1x1.forward."""
+    return _Reduc.apply(x, max_depth, is_final, *weights)
+
+
+def reduc_lpg(x, weights, max_depth, upratio, return_plane_eq=False):
+    """Fused stage -> (depth, abs_min[, plane_eq])."""
+    return _ReducLPG.apply(x, max_depth, upratio, return_plane_eq, *weights)

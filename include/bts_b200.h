@@ -1,0 +1,129 @@
+/*
+ * bts_b200.h -- C ABI of the B200-native BTS LPG decoder hot path (libbts_b200.so).
+ *
+ * The reference (minghanz/bts, pytorch/bts.py) implements this path as two nn.Modules on top of
+ * ATen; its only native prior art is the TF custom op in tensorflow/custom_layer/. Each entry point
+ * below names the reference code it replaces. The host side (bts_b200/modules.py) keeps the
+ * reference's nn.Module constructor / forward signatures and calls these through ctypes.
+ *
+ * Conventions
+ *  - All tensors are fp32, NCHW-contiguous DEVICE pointers owned by the caller. The library
+ *    allocates nothing, frees nothing and keeps no pointer after return.
+ *  - `stream` is a cudaStream_t passed as void*. Every call only enqueues work on it: no
+ *    cudaDeviceSynchronize / cudaStreamSynchronize anywhere (unlike the TF op's d.synchronize(),
+ *    tensorflow/custom_layer/local_planar_guidance.cu:91,170). Calls run on the caller's current
+ *    device; there is no global mutable state, so one thread per device (nn.DataParallel,
+ *    pytorch/bts_test.py:91) is safe.
+ *  - Return value: 0 on success, otherwise a BTS_ERR_* or cudaError_t code; bts_last_error()
+ *    returns a thread-local message. Nothing is printed, nothing exits.
+ *  - The chain of 1x1 convolutions is DATA: `dims[0..n_layers]` are the channel counts
+ *    (e.g. {128,128,64,32,16,8,3}), `W[l]` is layer l's weight, PyTorch layout [dims[l+1]][dims[l]]
+ *    (= nn.Conv2d.weight [out,in,1,1]). `W` and `grad_W` are HOST arrays of DEVICE pointers.
+ *  - `abs_min` points at ONE device float that the caller pre-sets to +inf; kernels lower it with
+ *    an atomic min of |den| (pre-clamp, pytorch/bts.py:167). NaN denominators yield NaN, as
+ *    torch.min would.
+ */
+#ifndef BTS_B200_H
+#define BTS_B200_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define BTS_API __attribute__((visibility("default")))
+#else
+#define BTS_API
+#endif
+
+#define BTS_ABI_VERSION 1
+#define BTS_MAX_LAYERS 8      /* reduction_1x1 builds at most log2(num_out) layers */
+#define BTS_MAX_CHANNELS 512  /* per layer */
+
+enum {
+    BTS_OK = 0,
+    BTS_ERR_BAD_ARG = -1,      /* null pointer, non-positive size, bad dims, misaligned pointer */
+    BTS_ERR_UNSUPPORTED = -2,  /* valid request this build cannot serve (e.g. chain too wide)   */
+    BTS_ERR_WORKSPACE = -3     /* workspace smaller than bts_workspace_bytes() reports          */
+};
+
+/* Which implementation serves a chain call (returned by bts_reduc_path; for tests and profiles). */
+enum {
+    BTS_PATH_GENERIC = 0,      /* any dims: one thread per low-res pixel                          */
+    BTS_PATH_SIMT_REG = 1,     /* narrow chains (<= 32 input channels): register-resident SIMT    */
+    BTS_PATH_TCGEN05 = 2       /* wide chains: 3xTF32 tcgen05 MMAs for the >= 64-channel layers   */
+};
+
+BTS_API int bts_abi_version(void);
+BTS_API const char *bts_last_error(void);
+
+/* Debug / test hook: force a path for subsequent calls from this thread (-1 = automatic). */
+BTS_API void bts_force_path(int path);
+BTS_API int bts_reduc_path(const int *dims, int n_layers, int is_final);
+
+/*
+ * local_planar_guidance.forward(plane_eq, focal)            pytorch/bts.py:149-173
+ * (TF prior art: LocalPlanarGuidanceKernel<GPU>, tensorflow/custom_layer/local_planar_guidance.cu:33-93)
+ *   plane_eq [B,4,h,w] -> depth [B,h*r,w*r];  depth = n4 / clamp(n1*u + n2*v + n3, +-eps)
+ * `focal` is not a parameter: the reference accepts and ignores it (bts.py:149 vs 150-173).
+ * The arithmetic order is the reference's, so depth is bit-identical to the reference's fp32 result.
+ */
+BTS_API int bts_lpg_fwd(const float *plane_eq, float *depth, float *abs_min,
+                int B, int h, int w, int r, float eps, void *stream);
+
+/*
+ * autograd backward of the above                            (implicit in the reference)
+ * (TF prior art: LocalPlanarGuidanceGradKernel<GPU>, local_planar_guidance.cu:95-172 -- which
+ *  omits the n4 factor; this follows PyTorch autograd)
+ *   grad_depth [B,h*r,w*r], plane_eq [B,4,h,w] -> grad_plane_eq [B,4,h,w]  (fully overwritten)
+ */
+BTS_API int bts_lpg_bwd(const float *grad_depth, const float *plane_eq, float *grad_plane_eq,
+                int B, int h, int w, int r, float eps, void *stream);
+
+/* Scratch the chain entry points need for this problem (0 is a valid answer). */
+BTS_API size_t bts_workspace_bytes(const int *dims, int n_layers, int B, int h, int w, int r);
+
+/*
+ * reduction_1x1.forward(net)                                pytorch/bts.py:124-136
+ *   x [B,dims[0],h,w] -> out [B,4,h,w] = (sin t cos p, sin t sin p, cos t, dist)   (is_final == 0)
+ *                        out [B,1,h,w] = sigmoid(chain(x))                          (is_final != 0)
+ */
+BTS_API int bts_reduc_fwd(const float *x, const float *const *W, const int *dims, int n_layers, int is_final,
+                  float max_depth, int B, int h, int w, float *out,
+                  void *ws, size_t ws_bytes, void *stream);
+
+/*
+ * autograd backward of reduction_1x1.forward. The chain is recomputed from x; nothing is saved.
+ *   grad_out shaped like out -> grad_x shaped like x (overwritten; may be NULL to skip),
+ *   grad_W[l] shaped like W[l] (ACCUMULATED: caller zero-initialises; entries may be NULL only
+ *   if all are NULL).
+ */
+BTS_API int bts_reduc_bwd(const float *x, const float *const *W, const int *dims, int n_layers, int is_final,
+                  float max_depth, int B, int h, int w, const float *grad_out,
+                  float *grad_x, float *const *grad_W,
+                  void *ws, size_t ws_bytes, void *stream);
+
+/*
+ * Fused decoder stage  reducNxN -> normalise/cat -> lpgNxN   pytorch/bts.py:249-254 (and 263-268,
+ * 277-282): one pass from features to full-resolution depth.
+ *   x [B,dims[0],h,w] -> depth [B,h*r,w*r];  plane_eq_out [B,4,h,w] optional (NULL to skip).
+ * The normalisation (bts.py:251) is the identity on (sin t cos p, sin t sin p, cos t) up to
+ * rounding and is not re-applied.
+ */
+BTS_API int bts_reduc_lpg_fwd(const float *x, const float *const *W, const int *dims, int n_layers,
+                      float max_depth, int B, int h, int w, int r, float eps,
+                      float *plane_eq_out, float *depth, float *abs_min,
+                      void *ws, size_t ws_bytes, void *stream);
+
+/* Backward of the fused stage: grad_depth [B,h*r,w*r] -> grad_x, grad_W (as bts_reduc_bwd). */
+BTS_API int bts_reduc_lpg_bwd(const float *grad_depth, const float *x, const float *const *W, const int *dims,
+                      int n_layers, float max_depth, int B, int h, int w, int r, float eps,
+                      float *grad_x, float *const *grad_W,
+                      void *ws, size_t ws_bytes, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BTS_B200_H */
