@@ -1,0 +1,444 @@
+#!/usr/bin/env python
+"""bench.py -- LPG decoder Mpixels/s, forward + backward, on N B200s (BASELINE.json's metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload nyu_b8]
+
+A step = one forward + backward pass of the four hot-path stages of the BTS decoder
+(reduc8x8+lpg8x8, reduc4x4+lpg4x4, reduc2x2+lpg2x2, reduc1x1 head; pytorch/bts.py:249-286) over one
+batch of synthetic decoder features. Unit of work = one full-resolution pixel of one image
+(SURVEY.md 8(d)). Workload at N=1: BASELINE.json configs[1] (NYU 480x640, batch 8, max_depth 10);
+each extra GPU gets its own batch of 8 (weak scaling, batch sharding, no data-path collective).
+
+Prints ONE JSON line (rank 0). See DESIGN.md "Measurement" for every field.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# name, H, W, per-GPU batch, max_depth, focal (train_test_inputs/*.txt col 3)
+WORKLOADS = {
+    "nyu_b8": dict(H=480, W=640, B=8, max_depth=10.0, focal=518.8579,
+                   desc="BTS DenseNet161 NYU Depth V2 480x640 batch 8 (BASELINE.json configs[1]), LPG3+head stages"),
+    "kitti_b16": dict(H=352, W=1216, B=16, max_depth=80.0, focal=721.5377,
+                      desc="BTS ResNeXt101 KITTI Eigen 352x1216 batch 16 (configs[2]), LPG3+head stages"),
+    "kitti_train_b4": dict(H=352, W=704, B=4, max_depth=80.0, focal=721.5377,
+                           desc="BTS DenseNet161 KITTI 352x704 batch 4/GPU (configs[3]), LPG3+head stages"),
+    "nyu_train_b4": dict(H=416, W=544, B=4, max_depth=10.0, focal=518.8579,
+                         desc="NYU 416x544 batch 4 (configs[0]), LPG3+head stages"),
+}
+# decoder instances at bts_size=512 (pytorch/bts.py:198-217): name, C_in, num_out, upratio, is_final
+STAGES = [("reduc8x8+lpg8x8", 128, 128, 8, False), ("reduc4x4+lpg4x4", 128, 64, 4, False),
+          ("reduc2x2+lpg2x2", 64, 32, 2, False), ("reduc1x1_head", 32, 16, 1, True)]
+# algorithmic bytes per FULL-RES pixel, fp32
+ALGO_BYTES = {"reduc8x8+lpg8x8": (12.25, 20.0), "reduc4x4+lpg4x4": (37.0, 68.0),
+              "reduc2x2+lpg2x2": (72.0, 132.0), "reduc1x1_head": (132.0, 260.0)}
+HBM_FALLBACK_GBS = 6650.0   # B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="nyu_b8", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the CPU port timing (profiling runs)")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer end-to-end leg (profiling runs)")
+    ap.add_argument("--kernel-only", action="store_true", help="only the timed device loop (for ncu)")
+    return ap.parse_args()
+
+
+def hbm_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return HBM_FALLBACK_GBS, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU baseline: the torch port of the reference modules (oracle/torch_port.py) on the host cores
+# ------------------------------------------------------------------------------------------------
+def make_cpu_inputs(wl, B, seed=0):
+    import torch
+    from oracle import torch_port as tp
+    gen = torch.Generator().manual_seed(seed)
+    H, W = wl["H"], wl["W"]
+    items = []
+    for name, cin, nout, r, final in STAGES:
+        dims = tp.chain_dims(cin, nout, final)
+        ws = [w.requires_grad_(True) for w in tp.xavier_weights(dims, final, gen)]
+        x = torch.randn(B, cin, H // r, W // r, generator=gen).requires_grad_(True)
+        g = torch.randn((B, 1, H, W) if final else (B, H, W), generator=gen)
+        items.append((name, r, final, ws, x, g))
+    return items
+
+
+def cpu_step(wl, items):
+    """One fwd+bwd pass of the four stages with the reference's own operator sequence."""
+    from oracle import torch_port as tp
+    for name, r, final, ws, x, g in items:
+        for t in ws + [x]:
+            t.grad = None
+        if final:
+            out = tp.chain_forward(x, ws, wl["max_depth"], True)
+        else:
+            out, _ = tp.stage_forward(x, ws, wl["max_depth"], r)
+        out.backward(g)
+
+
+def time_cpu(wl, B, steps, warmup):
+    import torch
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    items = make_cpu_inputs(wl, B)
+    for _ in range(warmup):
+        cpu_step(wl, items)
+    ts = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        cpu_step(wl, items)
+        ts.append(time.perf_counter() - t0)
+    med = statistics.median(ts)
+    px = B * wl["H"] * wl["W"]
+    return dict(value=px / med / 1e6, unit="Mpixels/s", cores=cores, kind="port",
+                sample="batch %d of %dx%d, all four stages fwd+bwd, median of %d steps (%.3f s/step), "
+                       "oracle/torch_port.py (reference ATen op sequence) with %d torch threads"
+                       % (B, wl["H"], wl["W"], steps, med, cores)), med, ts
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks during the timed region (B200_PROFILING.md recipe), sampled with NVML on a side thread
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+               0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz, self._stop, self._t = [], set(), None, threading.Event(), None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            # NVML indexes physical devices; honour CUDA_VISIBLE_DEVICES when it lists integers
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            if vis and all(v.strip().isdigit() for v in vis.split(",")):
+                index = int(vis.split(",")[index])
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                fn = getattr(self.nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or self.nv.nvmlDeviceGetCurrentClocksThrottleReasons
+                bits = fn(self.h)
+                for b, n in self.REASONS.items():
+                    if bits & b and n != "gpu_idle":
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            self._stop.wait(0.02)
+
+    def __enter__(self):
+        if self.nv:
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self._t:
+            self._t.join()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["nvml unavailable"]}
+        return {"sm_mhz": statistics.median(self.samples), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------------
+def build_stages(wl, device, seed):
+    """Modules with the reference constructor signatures + synthetic features resident in HBM."""
+    import torch
+    import bts_b200
+    torch.manual_seed(seed)
+    H, W, B = wl["H"], wl["W"], wl["B"]
+    stages = []
+    for name, cin, nout, r, final in STAGES:
+        red = bts_b200.reduction_1x1(cin, nout, wl["max_depth"], is_final=final).to(device)
+        for m in red.modules():                                   # weights_init_xavier, bts.py:34-38
+            if isinstance(m, torch.nn.Conv2d):
+                torch.nn.init.xavier_uniform_(m.weight)
+        lpg = None if final else bts_b200.local_planar_guidance(r)
+        x = torch.randn(B, cin, H // r, W // r, device=device, requires_grad=True)
+        g = torch.randn((B, 1, H, W) if final else (B, H, W), device=device)
+        stages.append(dict(name=name, r=r, final=final, red=red, lpg=lpg, x=x, g=g))
+    return stages
+
+
+def stage_forward(st):
+    import bts_b200
+    if st["final"]:
+        return st["red"](st["x"])
+    return bts_b200.fused_stage(st["red"], st["lpg"], st["x"])
+
+
+def gpu_step(stages):
+    """fwd + bwd of the four stages through the public module API (autograd drives the backward)."""
+    outs = []
+    for st in stages:
+        st["x"].grad = None
+        for p in st["red"].parameters():
+            p.grad = None
+        out = stage_forward(st)
+        out.backward(st["g"])
+        outs.append(out)
+    return outs
+
+
+def time_calls(stages, wl, iters=10):
+    """Per-call device times (CUDA events on the launching stream): each stage's forward and backward."""
+    import torch
+    res = {}
+    px = wl["B"] * wl["H"] * wl["W"]
+    for st in stages:
+        fwd, bwd = [], []
+        for it in range(iters + 2):
+            st["x"].grad = None
+            for p in st["red"].parameters():
+                p.grad = None
+            e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+            e[0].record()
+            out = stage_forward(st)
+            e[1].record()
+            out.backward(st["g"])
+            e[2].record()
+            torch.cuda.synchronize()
+            if it >= 2:
+                fwd.append(e[0].elapsed_time(e[1]))
+                bwd.append(e[1].elapsed_time(e[2]))
+        fb, bb = ALGO_BYTES[st["name"]]
+        res[st["name"]] = dict(fwd_ms=statistics.median(fwd), bwd_ms=statistics.median(bwd),
+                               fwd_gbs=fb * px / statistics.median(fwd) / 1e6,
+                               bwd_gbs=bb * px / statistics.median(bwd) / 1e6)
+    return res
+
+
+def e2e_leg(stages, wl, steps, warmup, device):
+    """Same step through the public module API with HOST buffers: every step copies the features and
+    upstream gradients from pinned host memory, and reads every result (depth maps / head output,
+    grad_x, grad_W, abs_min) back to pinned host memory, inside the timed region."""
+    import torch
+    host_in, host_out = [], []
+    for st in stages:
+        hx = st["x"].detach().cpu().pin_memory()
+        hg = st["g"].cpu().pin_memory()
+        host_in.append((hx, hg))
+    h2d = sum(hx.numel() * 4 + hg.numel() * 4 for hx, hg in host_in)
+    dev_in = [(torch.empty_like(st["x"]).requires_grad_(True), torch.empty_like(st["g"])) for st in stages]
+    outs_host = None
+    d2h = 0
+
+    def step():
+        nonlocal outs_host, d2h
+        results = []
+        for st, (hx, hg), (dx, dg) in zip(stages, host_in, dev_in):
+            with torch.no_grad():
+                dx.copy_(hx, non_blocking=True)
+                dg.copy_(hg, non_blocking=True)
+            dx.grad = None
+            for p in st["red"].parameters():
+                p.grad = None
+            saved = st["x"]
+            st["x"] = dx
+            out = stage_forward(st)
+            out.backward(dg)
+            st["x"] = saved
+            res = [out.detach(), dx.grad] + [p.grad for p in st["red"].parameters()]
+            if st["lpg"] is not None:
+                res.append(st["lpg"].abs_min)
+            results.append(res)
+        if outs_host is None:
+            outs_host = [[torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in res] for res in results]
+            d2h = sum(t.numel() * 4 for res in results for t in res)
+        for res, hres in zip(results, outs_host):
+            for t, ht in zip(res, hres):
+                ht.copy_(t, non_blocking=True)
+
+    for _ in range(max(1, warmup)):
+        step()
+    torch.cuda.synchronize()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    return dt, h2d, d2h
+
+
+_DIST = {"on": False}
+
+
+def barrier():
+    if _DIST["on"]:
+        import torch.distributed as dist
+        dist.barrier()
+
+
+def max_over_ranks(value, device):
+    if not _DIST["on"]:
+        return value
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([value], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def run_reference_arm(args, wl, rank):
+    """--impl reference: the reference's own CPU implementation of the path (torch port of
+    pytorch/bts.py:97-173 -- the reference tree itself does not travel to the GPU box) on the host
+    cores, each step a bounded sample (batch 1) of the workload. Rank 0 only."""
+    if rank != 0:
+        return
+    B = 1
+    cb, med, ts = time_cpu(wl, B, args.steps, args.warmup)
+    line = {
+        "impl": "reference", "metric": "LPG decoder Mpixels/s fwd+bwd", "value": cb["value"], "unit": "Mpixels/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": med * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl["desc"], "sample": "batch 1 per step", "H": wl["H"], "W": wl["W"]},
+        "cpu_baseline": cb,
+        "e2e": {"value": cb["value"], "unit": "Mpixels/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    wl = WORKLOADS[args.workload]
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.gpus > 1 and world == 1 and "RANK" not in os.environ:
+        # convenience: `python bench.py --gpus N` re-launches itself one process per GPU
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
+               "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29531"),
+               os.path.abspath(__file__)] + sys.argv[1:]
+        sys.exit(subprocess.call(cmd))
+
+    if args.impl == "reference":
+        run_reference_arm(args, wl, rank)
+        return
+
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: bts_b200 has no CPU fallback "
+                         "(use --impl reference for the CPU arm)")
+    from bts_b200 import _cabi
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=device)
+        _DIST["on"] = True
+    lib = _cabi.lib()
+
+    stages = build_stages(wl, device, seed=rank)
+    px_per_rank = wl["B"] * wl["H"] * wl["W"]
+    in_bytes = sum(st["x"].numel() * 4 + st["g"].numel() * 4 for st in stages)
+
+    for _ in range(max(3, args.warmup)):
+        gpu_step(stages)
+    torch.cuda.synchronize()
+    barrier()
+    launches0 = lib.bts_launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local_rank) as clocks:
+        torch.cuda.synchronize()
+        ev0.record()
+        for _ in range(args.steps):
+            gpu_step(stages)
+        ev1.record()
+        torch.cuda.synchronize()
+    barrier()
+    launches = lib.bts_launch_count() - launches0
+    ms_total = max_over_ranks(ev0.elapsed_time(ev1), device)
+    ms_step = ms_total / args.steps
+    value = world * px_per_rank / (ms_step * 1e-3) / 1e6
+
+    if args.kernel_only:
+        if rank == 0:
+            print(json.dumps({"metric": "LPG decoder Mpixels/s fwd+bwd", "value": value, "ms_per_step": ms_step,
+                              "gpu_launches": int(launches)}), flush=True)
+        return
+
+    # per-call device times -> roofline of the dominant call (the one that moves the most bytes)
+    calls = time_calls(stages, wl)
+    peak, peak_src = hbm_peak()
+    dom = max(((n, d, k) for n, d in calls.items() for k in ("fwd", "bwd")),
+              key=lambda t: ALGO_BYTES[t[0]][0 if t[2] == "fwd" else 1])
+    dn, dd, dk = dom
+    algo_b = ALGO_BYTES[dn][0 if dk == "fwd" else 1] * px_per_rank
+    achieved = dd[dk + "_gbs"]
+    step_bytes = sum(sum(ALGO_BYTES[n]) for n in calls) * px_per_rank
+    roofline = {"bound": "hbm", "kernel": "%s %s" % (dn, dk), "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": algo_b, "launch_ms": dd[dk + "_ms"],
+                "whole_step": {"algorithmic_bytes": step_bytes, "achieved": step_bytes / (ms_step * 1e-3) / 1e9,
+                               "frac": step_bytes / (ms_step * 1e-3) / 1e9 / peak},
+                "per_call": calls}
+
+    e2e = None
+    if not args.no_e2e:
+        e_steps = max(2, min(args.steps, 10))
+        dt, h2d, d2h = e2e_leg(stages, wl, e_steps, 2, device)
+        dt = max_over_ranks(dt, device)
+        e2e = {"value": world * px_per_rank * e_steps / dt / 1e6, "unit": "Mpixels/s",
+               "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": e_steps,
+               "ms_per_step": dt / e_steps * 1e3,
+               "what": "module API with pinned HOST buffers: H2D of features + upstream grads, D2H of every "
+                       "output (depths, grad_x, grad_W, abs_min) inside the timed region"}
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu_baseline, _, _ = time_cpu(wl, 1, 8, 2)
+
+    if rank == 0:
+        line = {
+            "metric": "LPG decoder Mpixels/s fwd+bwd", "value": value, "unit": "Mpixels/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl["desc"], "per_gpu_batch": wl["B"], "H": wl["H"], "W": wl["W"],
+                       "max_depth": wl["max_depth"], "stages": [s[0] for s in STAGES], "parallelism": "batch-sharded x%d" % world,
+                       "l2": "inputs %.0f MB per step > 126 MB L2 (no flush needed)" % (in_bytes / 1e6),
+                       "api": "bts_b200.reduction_1x1 / fused_stage via libbts_b200.so C ABI"},
+            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches),
+            "clocks": clocks.summary(),
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

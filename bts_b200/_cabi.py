@@ -13,6 +13,7 @@ _SIGNATURES = {
     "bts_abi_version": (ctypes.c_int, []),
     "bts_last_error": (ctypes.c_char_p, []),
     "bts_force_path": (None, [ctypes.c_int]),
+    "bts_launch_count": (ctypes.c_ulonglong, []),
     "bts_reduc_path": (ctypes.c_int, [ctypes.POINTER(ctypes.c_int), ctypes.c_int, ctypes.c_int]),
     "bts_lpg_fwd": (ctypes.c_int, [_c_float_p, _c_float_p, _c_float_p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                    ctypes.c_int, ctypes.c_float, ctypes.c_void_p]),

@@ -20,8 +20,11 @@ int set_error(int code, const char *fmt, ...)
     return code;
 }
 
+static unsigned long long g_launches = 0;
+
 int check_launch(const char *what)
 {
+    __atomic_add_fetch(&g_launches, 1ull, __ATOMIC_RELAXED);
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error((int)e, "%s: launch failed: %s", what, cudaGetErrorString(e));
     return BTS_OK;
@@ -79,6 +82,7 @@ extern "C" {
 int bts_abi_version(void) { return BTS_ABI_VERSION; }
 const char *bts_last_error(void) { return g_err; }
 void bts_force_path(int path) { g_force_path = path; }
+unsigned long long bts_launch_count(void) { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
 
 int bts_reduc_path(const int *dims, int n_layers, int is_final)
 {

@@ -63,6 +63,10 @@ BTS_API const char *bts_last_error(void);
 BTS_API void bts_force_path(int path);
 BTS_API int bts_reduc_path(const int *dims, int n_layers, int is_final);
 
+/* Number of kernels this library has launched in the calling process (all threads). Lets a
+ * benchmark state, not guess, how many of OUR kernels ran inside a timed region. */
+BTS_API unsigned long long bts_launch_count(void);
+
 /*
  * local_planar_guidance.forward(plane_eq, focal)            pytorch/bts.py:149-173
  * (TF prior art: LocalPlanarGuidanceKernel<GPU>, tensorflow/custom_layer/local_planar_guidance.cu:33-93)

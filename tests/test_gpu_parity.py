@@ -1,0 +1,279 @@
+"""GPU (-m gpu): the CUDA path, called through the C ABI, against the golden vectors of the
+unmodified reference, against the oracle on fresh seeded inputs, and against size-independent
+properties at BASELINE.json's full sizes.
+
+Tolerances (north_star: 1e-5 relative in fp32):
+  depth ............ element-wise rtol 1e-5 (+ atol 1e-6*max_depth)
+  plane_eq, grads .. max|a-b| <= 1e-5 * max|b|  and  L2-relative <= 1e-5   (they cross zero)
+  standalone LPG forward: BIT-IDENTICAL (same IEEE operation order as the reference).
+"""
+import numpy as np
+import pytest
+import torch
+
+from conftest import golden_cases, max_rel_to_peak, l2_rel
+from oracle import c_oracle as co
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-5
+CHAIN = golden_cases("chain")
+LPG = golden_cases("lpg")
+
+
+def dev(a, requires_grad=False):
+    t = torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    return t.requires_grad_(True) if requires_grad else t
+
+
+def close_peak(a, b, tol=RTOL):
+    a = a.detach().cpu().numpy() if isinstance(a, torch.Tensor) else a
+    assert max_rel_to_peak(a, b) <= tol, ("max-rel-to-peak", max_rel_to_peak(a, b))
+    assert l2_rel(a, b) <= tol, ("l2-rel", l2_rel(a, b))
+
+
+def close_depth(a, b, max_depth):
+    a = a.detach().cpu().numpy()
+    assert np.allclose(a, b, rtol=RTOL, atol=1e-6 * max_depth), float(np.abs(a - b).max())
+
+
+@pytest.mark.parametrize("g", LPG, ids=lambda g: g.name)
+def test_lpg_module_vs_golden(g):
+    import bts_b200
+    r = g.meta["upratio"]
+    pe = dev(g["plane_eq"], True)
+    m = bts_b200.local_planar_guidance(r)
+    depth = m(pe, torch.full((pe.shape[0],), 518.8579, dtype=torch.float64).cuda())
+    assert np.array_equal(depth.detach().cpu().numpy(), g["f32_depth"], equal_nan=True)   # bit-exact
+    assert np.array_equal(m.abs_min.cpu().numpy(), g["f32_abs_min"], equal_nan=True)
+    depth.backward(dev(g["grad_out"]))
+    got, ref = pe.grad.cpu().numpy(), g["f64_grad_plane_eq"].astype(np.float64)
+    assert np.array_equal(np.isnan(got), np.isnan(ref)) and np.array_equal(np.isinf(got), np.isinf(ref))
+    fin = np.isfinite(ref)
+    close_peak(got[fin], ref[fin])
+
+
+@pytest.mark.parametrize("g", CHAIN, ids=lambda g: g.name)
+def test_strict_dropin_vs_golden(g):
+    """reduction_1x1 -> (reference's own Python glue, bts.py:250-253) -> local_planar_guidance."""
+    import bts_b200
+    import torch.nn.functional as F
+    m = g.meta
+    red = bts_b200.reduction_1x1(m["num_in"], m["num_out"], m["max_depth"], m["is_final"]).cuda()
+    with torch.no_grad():
+        for p, w in zip(red.chain_weights(), g.weights):
+            p.copy_(dev(w).view_as(p))
+    x = dev(g["x"], True)
+    out = red(x)
+    close_peak(out, g["f64_out"])
+    if m["is_final"]:
+        final = out
+    else:
+        lpg = bts_b200.local_planar_guidance(m["upratio"])
+        n = F.normalize(out[:, :3, :, :], 2, 1)
+        pe = torch.cat([n, out[:, 3, :, :].unsqueeze(1)], 1)
+        final = lpg(pe, None)
+        close_depth(final, g["f32_depth"], m["max_depth"])
+        assert abs(float(lpg.abs_min) - float(g["f32_abs_min"])) <= 1e-5
+    final.backward(dev(g["grad_out"]))
+    close_peak(x.grad, g["f64_grad_x"])
+    for i, p in enumerate(red.chain_weights()):
+        close_peak(p.grad.view(p.shape[0], p.shape[1]), g["f64_grad_w%d" % i])
+
+
+@pytest.mark.parametrize("g", [c for c in CHAIN if not c.meta["is_final"]], ids=lambda g: g.name)
+def test_fused_stage_vs_golden(g):
+    import bts_b200
+    m = g.meta
+    red = bts_b200.reduction_1x1(m["num_in"], m["num_out"], m["max_depth"]).cuda()
+    with torch.no_grad():
+        for p, w in zip(red.chain_weights(), g.weights):
+            p.copy_(dev(w).view_as(p))
+    lpg = bts_b200.local_planar_guidance(m["upratio"])
+    x = dev(g["x"], True)
+    depth, pe = bts_b200.fused_stage(red, lpg, x, return_plane_eq=True)
+    close_depth(depth, g["f32_depth"], m["max_depth"])
+    close_peak(pe, g["f64_plane_eq"])
+    assert abs(float(lpg.abs_min) - float(g["f32_abs_min"])) <= 1e-5
+    depth.backward(dev(g["grad_out"]))
+    close_peak(x.grad, g["f64_grad_x"])
+    for i, p in enumerate(red.chain_weights()):
+        close_peak(p.grad.view(p.shape[0], p.shape[1]), g["f64_grad_w%d" % i])
+
+
+SEEDED = [  # (num_in, num_out, is_final, r, B, h, w, max_depth): sizes the C oracle finishes in seconds
+    (128, 128, False, 8, 2, 15, 20, 10.0),
+    (128, 64, False, 4, 2, 30, 40, 10.0),
+    (64, 32, False, 2, 2, 44, 76, 80.0),
+    (32, 16, True, 1, 2, 88, 152, 80.0),
+    (64, 64, False, 8, 1, 11, 13, 10.0),
+    (48, 24, False, 4, 1, 9, 7, 10.0),       # widths no fast path covers: generic kernel
+    (16, 16, True, 1, 3, 33, 31, 10.0),
+]
+
+
+@pytest.mark.parametrize("cfg", SEEDED, ids=lambda c: "x".join(map(str, c[:7])))
+def test_fused_vs_c_oracle_seeded(cfg):
+    import bts_b200
+    from oracle import torch_port as tp
+    num_in, num_out, is_final, r, B, h, w, md = cfg
+    gen = torch.Generator().manual_seed(1234 + num_in + r)
+    dims = tp.chain_dims(num_in, num_out, is_final)
+    ws = [t[:, :, 0, 0].numpy() for t in tp.xavier_weights(dims, is_final, gen)]
+    x = torch.randn(B, num_in, h, w, generator=gen).numpy()
+    red = bts_b200.reduction_1x1(num_in, num_out, md, is_final).cuda()
+    with torch.no_grad():
+        for p, wt in zip(red.chain_weights(), ws):
+            p.copy_(dev(wt).view_as(p))
+    xd = dev(x, True)
+    if is_final:
+        g = torch.randn(B, 1, h, w, generator=gen).numpy()
+        out = red(xd)
+        close_peak(out, co.reduc_fwd(x, ws, md, True, np.float64))
+        out.backward(dev(g))
+        gx, gw = co.reduc_bwd(x, ws, md, True, g, np.float64)
+    else:
+        g = torch.randn(B, h * r, w * r, generator=gen).numpy()
+        lpg = bts_b200.local_planar_guidance(r)
+        depth = bts_b200.fused_stage(red, lpg, xd)
+        ref = co.fused_fwd(x, ws, md, r, np.float64)
+        close_depth(depth, ref["depth"], md)
+        assert abs(float(lpg.abs_min) - float(ref["abs_min"])) <= 1e-5
+        depth.backward(dev(g))
+        gx, gw = co.fused_bwd(x, ws, md, r, g, np.float64)
+    close_peak(xd.grad, gx)
+    for p, gr in zip(red.chain_weights(), gw):
+        close_peak(p.grad.view(p.shape[0], p.shape[1]), gr)
+
+
+@pytest.mark.parametrize("r,B,h,w", [(8, 8, 60, 80), (4, 8, 120, 160), (2, 8, 240, 320), (8, 16, 44, 152),
+                                     (3, 1, 5, 7), (8, 1, 3, 5), (2, 2, 7, 9), (1, 2, 6, 10), (1, 1, 5, 4)])
+def test_lpg_full_size_vs_c_oracle(r, B, h, w):
+    """BASELINE.json config shapes (NYU 480x640 b8, KITTI 352x1216 b16) and ragged / odd-ratio shapes
+    that take the scalar kernels. Adversarial planes: the clamp fires."""
+    from bts_b200 import functional as Fn
+    rng = np.random.default_rng(r * 1000 + w)
+    theta = rng.uniform(0.9, 1.0, (B, h, w)) * np.pi / 3
+    phi = rng.uniform(0, 2 * np.pi, (B, h, w))
+    pe = np.stack([np.sin(theta) * np.cos(phi), np.sin(theta) * np.sin(phi), np.cos(theta),
+                   rng.uniform(0.1, 80, (B, h, w))], 1).astype(np.float32)
+    g = rng.standard_normal((B, h * r, w * r)).astype(np.float32)
+    ped = dev(pe, True)
+    depth, amin = Fn.lpg(ped, r)
+    ref_d, ref_a = co.lpg_fwd(pe, r, np.float32)
+    assert np.array_equal(depth.detach().cpu().numpy(), ref_d)
+    assert float(amin) == float(ref_a)
+    depth.backward(dev(g))
+    close_peak(ped.grad, co.lpg_bwd(g, pe, r, np.float64))
+
+
+def test_lpg_properties_full_size():
+    """Size-independent properties at the largest config (KITTI 352x1216, batch 16)."""
+    from bts_b200 import functional as Fn
+    B, h, w, r = 16, 44, 152, 8
+    gen = torch.Generator(device="cuda").manual_seed(7)
+    theta = torch.rand(B, h, w, generator=gen, device="cuda") * (np.pi / 3) * 0.8
+    phi = torch.rand(B, h, w, generator=gen, device="cuda") * 2 * np.pi
+    n4 = torch.rand(B, h, w, generator=gen, device="cuda") * 80 + 0.1
+    pe = torch.stack([theta.sin() * phi.cos(), theta.sin() * phi.sin(), theta.cos(), n4], 1).contiguous()
+    d1, a1 = Fn.lpg(pe, r)
+    # (1) linear in n4:  lpg(n, 2*n4) == 2*lpg(n, n4) exactly (power-of-two scaling commutes with rounding)
+    pe2 = pe.clone(); pe2[:, 3] *= 2
+    d2, a2 = Fn.lpg(pe2, r)
+    assert torch.equal(d2, 2 * d1) and torch.equal(a1, a2)
+    # (2) a fronto-parallel plane (n1=n2=0) yields constant depth n4/n3 over each r x r block
+    pe3 = pe.clone(); pe3[:, 0] = 0; pe3[:, 1] = 0
+    d3, a3 = Fn.lpg(pe3, r)
+    blk = (pe3[:, 3] / pe3[:, 2]).repeat_interleave(r, 1).repeat_interleave(r, 2)
+    assert torch.equal(d3, blk) and float(a3) == float(pe3[:, 2].abs().min())
+    # (3) the mean of 1/depth over a block is n3/n4 (the sub-pixel offsets are symmetric)
+    inv = (1.0 / d1.double()).view(B, h, r, w, r).mean(dim=(2, 4))
+    assert torch.allclose(inv, (pe[:, 2] / pe[:, 3]).double(), rtol=1e-5, atol=1e-7)
+    # (4) deterministic
+    d1b, _ = Fn.lpg(pe, r)
+    assert torch.equal(d1, d1b)
+
+
+def test_abs_min_nan_and_empty():
+    from bts_b200 import functional as Fn
+    pe = torch.rand(1, 4, 4, 4, device="cuda") + 0.5
+    pe[0, 2, 1, 1] = float("nan")
+    _, amin = Fn.lpg(pe, 2)
+    assert torch.isnan(amin)                      # torch.min propagates NaN (bts.py:167)
+    depth, amin = Fn.lpg(torch.empty(0, 4, 4, 4, device="cuda"), 8)
+    assert tuple(depth.shape) == (0, 32, 32) and float(amin) == float("inf")
+
+
+def test_chain_linearity_of_backward_full_size():
+    """NYU config-2 head shape [8,32,480,640]: backward is linear in the upstream gradient, and
+    grad_W of a batch equals the sum of per-sample grad_W (batch sharding needs no collective)."""
+    import bts_b200
+    torch.manual_seed(3)
+    red = bts_b200.reduction_1x1(32, 16, 10.0, True).cuda()
+    for p in red.parameters():
+        torch.nn.init.xavier_uniform_(p)
+    x = torch.randn(8, 32, 480, 640, device="cuda")
+    g = torch.randn(8, 1, 480, 640, device="cuda")
+
+    def run(xx, gg):
+        xx = xx.clone().requires_grad_(True)
+        red.zero_grad()
+        out = red(xx)
+        out.backward(gg)
+        return out.detach(), xx.grad, [p.grad.clone() for p in red.parameters()]
+
+    out, gx, gw = run(x, g)
+    assert out.min() > 0 and out.max() < 1
+    _, gx2, gw2 = run(x, 2 * g)
+    assert torch.equal(gx2, 2 * gx)
+    for a, b in zip(gw2, gw):
+        assert torch.allclose(a, 2 * b, rtol=1e-4, atol=1e-6 * float(b.abs().max()))
+    acc = [torch.zeros_like(p) for p in gw]
+    for s in range(0, 8, 4):
+        _, gxs, gws = run(x[s:s + 4], g[s:s + 4])
+        assert torch.equal(gxs, gx[s:s + 4])
+        for a, b in zip(acc, gws):
+            a += b
+    for a, b in zip(acc, gw):
+        assert torch.allclose(a, b, rtol=1e-4, atol=1e-5 * float(b.abs().max()))
+
+
+def test_noncontiguous_and_state_dict_roundtrip():
+    import bts_b200
+    red = bts_b200.reduction_1x1(64, 32, 10.0).cuda()
+    sd = {k: v.clone() for k, v in red.state_dict().items()}
+    red2 = bts_b200.reduction_1x1(64, 32, 10.0).cuda()
+    red2.load_state_dict(sd)
+    x = torch.randn(2, 6, 10, 64, device="cuda").permute(0, 3, 1, 2)      # channels-last strides
+    assert not x.is_contiguous()
+    assert torch.equal(red(x), red2(x.contiguous()))
+
+
+def test_ddp_wraps_the_modules():
+    """DDP(find_unused_parameters=True) as bts_main.py:314 -- weight grads must reach the reducer hooks."""
+    import os
+    import torch.distributed as dist
+    import bts_b200
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29577")
+    created = False
+    if not dist.is_initialized():
+        dist.init_process_group("nccl", rank=0, world_size=1)
+        created = True
+    try:
+        class Stage(torch.nn.Module):
+            def __init__(self):
+                super().__init__()
+                self.reduc = bts_b200.reduction_1x1(64, 32, 10.0)
+                self.lpg = bts_b200.local_planar_guidance(2)
+
+            def forward(self, x):
+                return bts_b200.fused_stage(self.reduc, self.lpg, x)
+
+        m = torch.nn.parallel.DistributedDataParallel(Stage().cuda(), device_ids=[0], find_unused_parameters=True)
+        out = m(torch.randn(2, 64, 8, 8, device="cuda"))
+        out.mean().backward()
+        assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in m.parameters())
+    finally:
+        if created:
+            dist.destroy_process_group()
