@@ -4,7 +4,7 @@
 #include <cstdio>
 #include <cstring>
 
-#include "common.cuh"
+#include "chain_tc.cuh"
 
 namespace bts {
 
@@ -35,6 +35,44 @@ int launch_lpg_fwd(const float *, float *, float *, int, int, int, int, float, c
 int launch_lpg_bwd(const float *, const float *, float *, int, int, int, int, float, cudaStream_t);
 int launch_chain_generic_fwd(const ChainParams &, const float *, float *, int, int, cudaStream_t);
 int launch_chain_generic_bwd(const ChainParams &, const float *, const float *, float *, int, int, cudaStream_t);
+int launch_chain_tc_fwd(const ChainParams &, const TcArgs &, int r, float *wpack, int sms, cudaStream_t);
+int launch_chain_tc_bwd(const ChainParams &, const TcArgs &, int mode, int r, void *ws, int sms, cudaStream_t);
+bool tc_supported(const ChainParams &);
+size_t tc_pack_bytes();
+size_t tc_bwd_workspace_bytes(const ChainParams &, long long npx, int sms);
+
+static int sm_count()
+{
+    int dev = 0, n = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    return n;
+}
+
+static bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// tensor-core path usable for this call? (chain covered, not forced off, workspace + alignment ok)
+static bool use_tc(const ChainParams &cp, const void *ws, size_t ws_bytes, const void *depth)
+{
+    if (g_force_path == BTS_PATH_GENERIC) return false;
+    if (!tc_supported(cp)) return false;
+    if (ws == nullptr || ws_bytes < tc_pack_bytes() || !aligned16(ws)) return false;
+    return depth == nullptr || aligned16(depth);
+}
+
+static bool use_tc_bwd(const ChainParams &cp, const void *ws, size_t ws_bytes, long long npx, const void *grad16)
+{
+    if (!use_tc(cp, ws, ws_bytes, grad16)) return false;
+    return ws_bytes >= 2 * tc_pack_bytes() + tc_bwd_workspace_bytes(cp, npx, sm_count());
+}
+
+static TcArgs make_tc_args(const float *x, int B, int h, int w, float max_depth, float eps)
+{
+    TcArgs a;
+    memset(&a, 0, sizeof(a));
+    a.x = x; a.B = B; a.h = h; a.w = w; a.hw = h * w; a.npx = (long long)B * h * w;
+    a.max_depth = max_depth; a.eps = eps;
+    return a;
+}
 
 static int fill_chain(ChainParams &cp, const float *const *W, float *const *gW, const int *dims,
                       int n_layers, int is_final, float max_depth)
@@ -86,8 +124,11 @@ unsigned long long bts_launch_count(void) { return __atomic_load_n(&g_launches, 
 
 int bts_reduc_path(const int *dims, int n_layers, int is_final)
 {
-    (void)dims; (void)n_layers; (void)is_final;
-    return BTS_PATH_GENERIC;
+    ChainParams cp;
+    const float *fake[BTS_MAX_LAYERS];
+    for (int l = 0; l < BTS_MAX_LAYERS; ++l) fake[l] = reinterpret_cast<const float *>(16);
+    if (fill_chain(cp, fake, nullptr, dims, n_layers, is_final, 1.f)) return -1;
+    return (g_force_path != BTS_PATH_GENERIC && tc_supported(cp)) ? BTS_PATH_TCGEN05 : BTS_PATH_GENERIC;
 }
 
 int bts_lpg_fwd(const float *plane_eq, float *depth, float *abs_min, int B, int h, int w, int r,
@@ -114,21 +155,35 @@ int bts_lpg_bwd(const float *grad_depth, const float *plane_eq, float *grad_plan
 
 size_t bts_workspace_bytes(const int *dims, int n_layers, int B, int h, int w, int r)
 {
-    (void)dims; (void)n_layers;
     if (B <= 0 || h <= 0 || w <= 0) return 0;
-    // fused generic path: plane_eq (fwd) / grad_plane_eq + plane_eq (bwd) staging when r > 0
-    return r > 0 ? (size_t)2 * 4 * sizeof(float) * (size_t)B * h * w : 0;
+    // layout: [packed weights | packed transposed weights | backward spill rows + wgrad partials]
+    // (tensor-core path) or [.. | plane_eq, grad_plane_eq staging] (generic fused route, r > 0)
+    const size_t npx = (size_t)B * h * w;
+    size_t tail = r > 0 ? (size_t)2 * 4 * sizeof(float) * npx : 0;
+    ChainParams cp;
+    const float *fake[BTS_MAX_LAYERS];
+    for (int l = 0; l < BTS_MAX_LAYERS; ++l) fake[l] = reinterpret_cast<const float *>(16);
+    const int last = (dims && n_layers >= 1 && n_layers <= BTS_MAX_LAYERS) ? dims[n_layers] : 0;
+    if (last && fill_chain(cp, fake, nullptr, dims, n_layers, last == 1, 1.f) == BTS_OK && tc_supported(cp)) {
+        const size_t t = tc_bwd_workspace_bytes(cp, (long long)npx, sm_count());
+        if (t > tail) tail = t;
+    }
+    return 2 * tc_pack_bytes() + tail;
 }
 
 int bts_reduc_fwd(const float *x, const float *const *W, const int *dims, int n_layers, int is_final,
                   float max_depth, int B, int h, int w, float *out, void *ws, size_t ws_bytes, void *stream)
 {
-    (void)ws; (void)ws_bytes;
     ChainParams cp;
     if (int e = fill_chain(cp, W, nullptr, dims, n_layers, is_final, max_depth)) return e;
     if (int e = check_shape(B, h, w)) return e;
     if ((long long)B * h * w == 0) return BTS_OK;
     if (!x || !out) return set_error(BTS_ERR_BAD_ARG, "x / out is NULL");
+    if (use_tc(cp, ws, ws_bytes, nullptr)) {
+        TcArgs a = make_tc_args(x, B, h, w, max_depth, 0.f);
+        a.out = out;
+        return launch_chain_tc_fwd(cp, a, 0, static_cast<float *>(ws), sm_count(), (cudaStream_t)stream);
+    }
     return launch_chain_generic_fwd(cp, x, out, B, h * w, (cudaStream_t)stream);
 }
 
@@ -136,12 +191,16 @@ int bts_reduc_bwd(const float *x, const float *const *W, const int *dims, int n_
                   float max_depth, int B, int h, int w, const float *grad_out, float *grad_x,
                   float *const *grad_W, void *ws, size_t ws_bytes, void *stream)
 {
-    (void)ws; (void)ws_bytes;
     ChainParams cp;
     if (int e = fill_chain(cp, W, grad_W, dims, n_layers, is_final, max_depth)) return e;
     if (int e = check_shape(B, h, w)) return e;
     if ((long long)B * h * w == 0) return BTS_OK;
     if (!x || !grad_out) return set_error(BTS_ERR_BAD_ARG, "x / grad_out is NULL");
+    if (use_tc_bwd(cp, ws, ws_bytes, (long long)B * h * w, nullptr)) {
+        TcArgs a = make_tc_args(x, B, h, w, max_depth, 0.f);
+        a.grad = grad_out; a.grad_x = grad_x;
+        return launch_chain_tc_bwd(cp, a, is_final ? 0 : 1, 0, ws, sm_count(), (cudaStream_t)stream);
+    }
     return launch_chain_generic_bwd(cp, x, grad_out, grad_x, B, h * w, (cudaStream_t)stream);
 }
 
@@ -155,12 +214,17 @@ int bts_reduc_lpg_fwd(const float *x, const float *const *W, const int *dims, in
     if (r < 1) return set_error(BTS_ERR_BAD_ARG, "upratio r=%d must be >= 1", r);
     if ((long long)B * h * w == 0) return BTS_OK;
     if (!x || !depth) return set_error(BTS_ERR_BAD_ARG, "x / depth is NULL");
+    if ((r == 1 || r == 2 || r == 4 || r == 8) && use_tc(cp, ws, ws_bytes, depth)) {
+        TcArgs a = make_tc_args(x, B, h, w, max_depth, eps);
+        a.out = plane_eq_out; a.depth = depth; a.abs_min = abs_min;
+        return launch_chain_tc_fwd(cp, a, r, static_cast<float *>(ws), sm_count(), (cudaStream_t)stream);
+    }
     float *pe = plane_eq_out;
     if (pe == nullptr) {
-        const size_t need = (size_t)4 * sizeof(float) * (size_t)B * h * w;
+        const size_t need = tc_pack_bytes() + (size_t)4 * sizeof(float) * (size_t)B * h * w;
         if (ws == nullptr || ws_bytes < need)
             return set_error(BTS_ERR_WORKSPACE, "workspace %zu B < %zu B", ws_bytes, need);
-        pe = static_cast<float *>(ws);
+        pe = reinterpret_cast<float *>(static_cast<char *>(ws) + tc_pack_bytes());
     }
     if (int e = launch_chain_generic_fwd(cp, x, pe, B, h * w, (cudaStream_t)stream)) return e;
     return launch_lpg_fwd(pe, depth, abs_min, B, h, w, r, eps, (cudaStream_t)stream);
@@ -176,10 +240,15 @@ int bts_reduc_lpg_bwd(const float *grad_depth, const float *x, const float *cons
     if (r < 1) return set_error(BTS_ERR_BAD_ARG, "upratio r=%d must be >= 1", r);
     if ((long long)B * h * w == 0) return BTS_OK;
     if (!x || !grad_depth) return set_error(BTS_ERR_BAD_ARG, "x / grad_depth is NULL");
+    if ((r == 1 || r == 2 || r == 4 || r == 8) && use_tc_bwd(cp, ws, ws_bytes, (long long)B * h * w, grad_depth)) {
+        TcArgs a = make_tc_args(x, B, h, w, max_depth, eps);
+        a.grad = grad_depth; a.grad_x = grad_x;
+        return launch_chain_tc_bwd(cp, a, 2, r, ws, sm_count(), (cudaStream_t)stream);
+    }
     const size_t one = (size_t)4 * sizeof(float) * (size_t)B * h * w;
-    if (ws == nullptr || ws_bytes < 2 * one)
-        return set_error(BTS_ERR_WORKSPACE, "workspace %zu B < %zu B", ws_bytes, 2 * one);
-    float *pe = static_cast<float *>(ws);
+    if (ws == nullptr || ws_bytes < 2 * tc_pack_bytes() + 2 * one)
+        return set_error(BTS_ERR_WORKSPACE, "workspace %zu B < %zu B", ws_bytes, 2 * tc_pack_bytes() + 2 * one);
+    float *pe = reinterpret_cast<float *>(static_cast<char *>(ws) + 2 * tc_pack_bytes());
     float *gpe = pe + (size_t)4 * B * h * w;
     cudaStream_t s = (cudaStream_t)stream;
     // generic route: recompute plane_eq, reduce grad_depth over each r x r block, then the chain.

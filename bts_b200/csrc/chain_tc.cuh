@@ -1,0 +1,287 @@
+// chain_tc.cuh -- shared pieces of the tensor-core chain kernels (chain_tc_fwd.cu, chain_tc_bwd.cu).
+//
+// A reduction_1x1 chain  D0 -> D1 -> ... -> 16 -> 8 -> (3 | 1)  is split in two parts:
+//   * "wide" layers (every layer whose output width is >= 16) run on the 5th-gen tensor cores as
+//     3xTF32 tcgen05.mma: M = 128 low-res pixels (one per TMEM lane / per thread of a warpgroup),
+//     N = output channels, K = input channels. Activations live in TMEM (A operand, hi and lo
+//     halves), weights in shared memory (B operand, K-major, no swizzle, hi and lo halves).
+//   * the narrow tail 16 -> 8 -> (3|1), the ELUs, the plane parameterisation and the LPG expansion
+//     run as SIMT code, one thread per low-res pixel, on registers.
+// 3xTF32: x = hi + lo with hi = the fp32 word as the tensor core truncates it; D = lo*Whi + hi*Wlo
+// + hi*Whi accumulated in fp32 (error ~5e-7 of peak, measured by tests/cuda/probe_umma.cu).
+#pragma once
+#include "common.cuh"
+#include "tc.cuh"
+
+namespace bts {
+
+constexpr int kTile = 128;              // low-res pixels per tile = TMEM lanes = threads per warpgroup
+constexpr int kTailIn = 16;             // width at which the SIMT tail takes over
+constexpr int kTailMid = 8;
+
+// Widths of the tensor-core part: D0 -> D1 [-> D2 [-> D3 [-> D4]]], the last one being 16.
+template <int NW_, int D0_, int D1_, int D2_ = 0, int D3_ = 0, int D4_ = 0>
+struct TcCfg {
+    static constexpr int NW = NW_;
+    __host__ __device__ static constexpr int dim(int l)
+    {
+        return l == 0 ? D0_ : l == 1 ? D1_ : l == 2 ? D2_ : l == 3 ? D3_ : D4_;
+    }
+    __host__ __device__ static constexpr int K(int l) { return dim(l); }
+    __host__ __device__ static constexpr int N(int l) { return dim(l + 1); }
+    __host__ __device__ static constexpr int kmax()
+    {
+        int m = 0;
+        for (int l = 0; l < NW; ++l) m = K(l) > m ? K(l) : m;
+        return m;
+    }
+    __host__ __device__ static constexpr int nmax()
+    {
+        int m = 0;
+        for (int l = 0; l < NW; ++l) m = N(l) > m ? N(l) : m;
+        return m;
+    }
+    // packed weight image (floats): per wide layer [hi image | lo image], then the raw tail weights
+    __host__ __device__ static constexpr int w_off(int l)
+    {
+        int o = 0;
+        for (int j = 0; j < l; ++j) o += 2 * N(j) * K(j);
+        return o;
+    }
+    __host__ __device__ static constexpr int tail_off() { return w_off(NW); }
+    __host__ __device__ static constexpr int pack_floats(int last) { return tail_off() + kTailMid * kTailIn + last * kTailMid; }
+    static_assert(NW_ >= 1 && NW_ <= 4, "1..4 tensor-core layers");
+};
+
+// canonical K-major, no-swizzle operand: element (row, k) of an [rows][K] fp32 matrix
+__host__ __device__ constexpr uint32_t kmajor_off_floats(int row, int k, int K)
+{
+    return (uint32_t)((row % 8) * 4 + (row / 8) * (K / 4) * 32 + (k / 4) * 32 + (k % 4));
+}
+
+// ELU with the hardware exponential (ex2.approx): absolute error <= 2e-7 on the negative branch.
+__device__ __forceinline__ float elu_fast(float t)
+{
+    float e;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(t * 1.4426950408889634f));
+    return t > 0.f ? t : e - 1.f;
+}
+
+// Parameters shared by the forward and backward tensor-core kernels.
+struct TcArgs {
+    const float *x;          // [B][D0][hw]
+    const float *wpack;      // packed weight image built by tc_pack_weights_kernel
+    float *out;              // forward: plane_eq [B][4][hw] (may be null) or head output [B][1][hw]
+    float *depth;            // forward fused: [B][h*r][w*r] (null when not fused)
+    float *abs_min;
+    const float *grad;       // backward: grad_depth (fused) / grad_out
+    float *grad_x;
+    float *gw[BTS_MAX_LAYERS];
+    int B, h, w, hw;
+    long long npx;           // B*hw
+    float max_depth, eps;
+};
+
+using namespace tc;
+
+// ---- one wide layer: 3 x (K/8) MMAs issued by a single thread, then commit -> mbarrier
+template <class CFG, int L>
+__device__ __forceinline__ void tc_issue_layer(uint32_t wg_base, const float *sw, uint64_t *bar)
+{
+    constexpr int K = CFG::K(L), N = CFG::N(L), KMAX = CFG::kmax();
+    constexpr uint32_t LBO = 128, SBO = (K / 4) * 128;
+    constexpr uint32_t idesc = idesc_tf32(kTile, N, 0, 0);
+    const uint32_t whi = smem_u32(sw + CFG::w_off(L));
+    const uint32_t wlo = whi + N * K * 4;
+    const uint32_t d = wg_base + 2 * KMAX;
+#pragma unroll
+    for (int k0 = 0; k0 < K; k0 += 8)   // lo(a) * hi(W)
+        mma_tf32_ts(d, wg_base + KMAX + k0, smem_desc(whi + (k0 / 4) * LBO, LBO, SBO), idesc, k0 > 0);
+#pragma unroll
+    for (int k0 = 0; k0 < K; k0 += 8)   // hi(a) * lo(W)
+        mma_tf32_ts(d, wg_base + k0, smem_desc(wlo + (k0 / 4) * LBO, LBO, SBO), idesc, 1);
+#pragma unroll
+    for (int k0 = 0; k0 < K; k0 += 8)   // hi(a) * hi(W)
+        mma_tf32_ts(d, wg_base + k0, smem_desc(whi + (k0 / 4) * LBO, LBO, SBO), idesc, 1);
+    mma_commit(bar);
+}
+
+// ---- hand a finished A operand to the tensor core and wait for the layer's accumulator
+template <class CFG, int L>
+__device__ __forceinline__ void tc_run_layer(uint32_t wg_base, const float *sw, uint64_t *bar, uint32_t &phase,
+                                             int wg, int t)
+{
+    wait_st();
+    fence_before_sync();
+    named_bar_sync(1 + wg, kTile);
+    if (t == 0) {
+        fence_after_sync();
+        tc_issue_layer<CFG, L>(wg_base, sw, bar);
+    }
+    mbar_wait(bar, phase);
+    phase ^= 1;
+    fence_after_sync();
+}
+
+// ---- epilogue of a wide layer that feeds another wide layer: D -> ELU -> (hi, lo) -> A
+template <class CFG, int L>
+__device__ __forceinline__ void tc_epilogue_to_a(uint32_t lane_addr)
+{
+    constexpr int N = CFG::N(L), KMAX = CFG::kmax();
+#pragma unroll
+    for (int n0 = 0; n0 < N; n0 += 16) {
+        uint32_t r[16], lo[16];
+        tmem_ld<16>(lane_addr + 2 * KMAX + n0, r);
+        wait_ld();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const float v = elu_fast(__uint_as_float(r[j]));
+            r[j] = __float_as_uint(v);
+            lo[j] = __float_as_uint(tf32_lo(v));
+        }
+        tmem_st<16>(lane_addr + n0, r);
+        tmem_st<16>(lane_addr + KMAX + n0, lo);
+    }
+}
+
+// ---- LPG expansion of this thread's plane (n1..n4) into depth; returns the abs_min key
+template <int R>
+__device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, float n3, float n4,
+                                          long long gp, bool valid, int lane)
+{
+    int key = 0x7f800000;
+    if constexpr (R == 8) {
+        // two 512 B stores per output row and warp: lane L writes columns (L&1)*4..+3 of pixel 16*half + L/2
+        const long long gp0 = gp - lane;
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            const int src = half * 16 + (lane >> 1);
+            const float m1 = __shfl_sync(0xffffffffu, n1, src), m2 = __shfl_sync(0xffffffffu, n2, src);
+            const float m3 = __shfl_sync(0xffffffffu, n3, src), m4 = __shfl_sync(0xffffffffu, n4, src);
+            const long long gs = gp0 + src;
+            if (gs < a.npx) {
+                const int b = (int)(gs / a.hw);
+                const int rem = (int)(gs - (long long)b * a.hw);
+                const int i = rem / a.w, j = rem - i * a.w;
+                const int q0 = (lane & 1) * 4;
+                const int Wd = a.w * 8;
+                float *out = a.depth + ((size_t)b * a.h + i) * 8 * (size_t)Wd + (size_t)j * 8 + q0;
+                float n1u[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) n1u[k] = __fmul_rn(m1, lpg_offset(q0 + k, 8));
+#pragma unroll
+                for (int p = 0; p < 8; ++p) {
+                    const float n2v = __fmul_rn(m2, lpg_offset(p, 8));
+                    float4 o;
+                    float *op = reinterpret_cast<float *>(&o);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        float den = lpg_den(n1u[k], n2v, m3);
+                        key = min(key, absmin_key(den));
+                        op[k] = __fdiv_rn(m4, lpg_clamp(den, a.eps));
+                    }
+                    *reinterpret_cast<float4 *>(out + (size_t)p * Wd) = o;
+                }
+            }
+        }
+    } else if (valid) {
+        const int b = (int)(gp / a.hw);
+        const int rem = (int)(gp - (long long)b * a.hw);
+        const int i = rem / a.w, j = rem - i * a.w;
+        const int Wd = a.w * R;
+        float *out = a.depth + ((size_t)b * a.h + i) * R * (size_t)Wd + (size_t)j * R;
+        float n1u[R];
+#pragma unroll
+        for (int k = 0; k < R; ++k) n1u[k] = __fmul_rn(n1, lpg_offset(k, R));
+#pragma unroll
+        for (int p = 0; p < R; ++p) {
+            const float n2v = __fmul_rn(n2, lpg_offset(p, R));
+            float o[R];
+#pragma unroll
+            for (int k = 0; k < R; ++k) {
+                float den = lpg_den(n1u[k], n2v, n3);
+                key = min(key, absmin_key(den));
+                o[k] = __fdiv_rn(n4, lpg_clamp(den, a.eps));
+            }
+            float *row = out + (size_t)p * Wd;
+            if constexpr (R == 4) *reinterpret_cast<float4 *>(row) = make_float4(o[0], o[1], o[2], o[3]);
+            else if constexpr (R == 2) *reinterpret_cast<float2 *>(row) = make_float2(o[0], o[1]);
+            else {
+#pragma unroll
+                for (int k = 0; k < R; ++k) row[k] = o[k];
+            }
+        }
+    }
+    return key;
+}
+
+// ---- the 16 -> 8 -> (3|1) tail on registers; weights broadcast from shared memory
+template <int LAST>
+__device__ __forceinline__ void tail_forward(const float *tw, const float (&a16)[kTailIn], float (&a8)[kTailMid],
+                                             float (&z)[LAST])
+{
+#pragma unroll
+    for (int o = 0; o < kTailMid; ++o) {
+        float s = 0.f;
+#pragma unroll
+        for (int c = 0; c < kTailIn; c += 4) {
+            const float4 w4 = *reinterpret_cast<const float4 *>(tw + o * kTailIn + c);
+            s = fmaf(w4.x, a16[c], s); s = fmaf(w4.y, a16[c + 1], s);
+            s = fmaf(w4.z, a16[c + 2], s); s = fmaf(w4.w, a16[c + 3], s);
+        }
+        a8[o] = elu_fast(s);
+    }
+    const float *w5 = tw + kTailMid * kTailIn;
+#pragma unroll
+    for (int o = 0; o < LAST; ++o) {
+        float s = 0.f;
+#pragma unroll
+        for (int c = 0; c < kTailMid; c += 4) {
+            const float4 w4 = *reinterpret_cast<const float4 *>(w5 + o * kTailMid + c);
+            s = fmaf(w4.x, a8[c], s); s = fmaf(w4.y, a8[c + 1], s);
+            s = fmaf(w4.z, a8[c + 2], s); s = fmaf(w4.w, a8[c + 3], s);
+        }
+        z[o] = s;
+    }
+}
+
+// ---- weight packing: fp32 [N][K] -> canonical K-major (hi | lo) images + raw tail weights
+template <class CFG>
+__global__ void tc_pack_weights_kernel(ChainParams cp, float *wpack, int last)
+{
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+#pragma unroll
+    for (int l = 0; l < CFG::NW; ++l) {
+        const int K = CFG::K(l), N = CFG::N(l);
+        float *hi = wpack + CFG::w_off(l), *lo = hi + N * K;
+        for (int e = tid; e < N * K; e += nth) {
+            const int n = e / K, k = e - n * K;
+            const float v = __ldg(cp.W[l] + e);
+            const uint32_t off = kmajor_off_floats(n, k, K);
+            hi[off] = v;
+            lo[off] = tc::tf32_lo(v);
+        }
+    }
+    float *tw = wpack + CFG::tail_off();
+    for (int e = tid; e < kTailMid * kTailIn; e += nth) tw[e] = __ldg(cp.W[CFG::NW] + e);
+    for (int e = tid; e < last * kTailMid; e += nth) tw[kTailMid * kTailIn + e] = __ldg(cp.W[CFG::NW + 1] + e);
+}
+
+// chain signatures served by the tensor-core path (bts_size = 512 and 256 decoders)
+using Cfg128_128 = TcCfg<4, 128, 128, 64, 32, 16>;
+using Cfg128_64 = TcCfg<3, 128, 64, 32, 16>;
+using Cfg64_64 = TcCfg<3, 64, 64, 32, 16>;
+using Cfg64_32 = TcCfg<2, 64, 32, 16>;
+using Cfg32_32 = TcCfg<2, 32, 32, 16>;
+using Cfg32_16 = TcCfg<1, 32, 16>;
+
+template <class CFG>
+static bool cfg_matches(const ChainParams &cp)
+{
+    if (cp.n_layers != CFG::NW + 2) return false;
+    for (int l = 0; l <= CFG::NW; ++l)
+        if (cp.dims[l] != CFG::dim(l)) return false;
+    return cp.dims[CFG::NW + 1] == kTailMid;
+}
+
+}  // namespace bts

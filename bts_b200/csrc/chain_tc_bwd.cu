@@ -1,0 +1,768 @@
+// chain_tc_bwd.cu -- backward of a BTS decoder stage on sm_100a tensor cores.
+//
+// Autograd backward of reduction_1x1 (+ LPG) (pytorch/bts.py:124-173), with
+// the chain recomputed from x instead of saved. Four launches:
+//   K1 bwd1   : recompute the chain (3xTF32 tcgen05, as the forward), evaluate the upstream gradient
+//               (sigmoid head / plane parameterisation / LPG block reduction), back-propagate through
+//               the SIMT tail; activations a_l and deltas of the tail go to an L2-sized workspace
+//   K2 dgrad  : delta_l = (delta_{l+1} W_l) * ELU'(a_l) through the wide layers (3xTF32 tcgen05, the
+//               weights as a transposed K-major image), ending in grad_x
+//   K3 wgrad  : dW_l = sum_px delta_{l+1} (x) a_l as tcgen05 SS-mode MMAs with the pixel axis as K;
+//               per-CTA partial sums (deterministic, no atomics)
+//   K4 reduce : grad_W += sum of partials
+// Workspace rows are [channel][pixel] fp32 matrices padded to a multiple of 128 pixels.
+#include <cstring>
+
+#include "chain_tc.cuh"
+
+namespace bts {
+
+struct BwdArgs {
+    TcArgs a;              // x, wpack (forward images + tail weights), grad, grad_x, sizes
+    const float *wpack_t;  // transposed images for dgrad
+    float *act;            // [RA][npx_pad]   a_1 .. a_NW (=a16), a8
+    float *del;            // [RD][npx_pad]   delta_1 .. delta_NW (=d16), d8, dz
+    long long npx_pad;
+};
+
+template <class CFG>
+struct BwdRows {
+    // first workspace row of a_l / delta_l for l = 1..NW; the tail rows follow
+    __host__ __device__ static constexpr int row(int l)
+    {
+        int r = 0;
+        for (int j = 1; j < l; ++j) r += CFG::dim(j);
+        return r;
+    }
+    __host__ __device__ static constexpr int row8() { return row(CFG::NW + 1); }
+    __host__ __device__ static constexpr int rowz() { return row8() + kTailMid; }
+};
+
+// D -> ELU -> spill a_{L+1} -> (hi, lo) -> A
+template <class CFG, int L>
+__device__ __forceinline__ void tc_epilogue_to_a_spill(uint32_t lane_addr, float *act_gp, long long npx_pad)
+{
+    constexpr int N = CFG::N(L), KMAX = CFG::kmax();
+    float *dst = act_gp + (size_t)BwdRows<CFG>::row(L + 1) * npx_pad;
+#pragma unroll
+    for (int n0 = 0; n0 < N; n0 += 16) {
+        uint32_t r[16], lo[16];
+        tmem_ld<16>(lane_addr + 2 * KMAX + n0, r);
+        wait_ld();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const float v = elu_fast(__uint_as_float(r[j]));
+            dst[(size_t)(n0 + j) * npx_pad] = v;
+            r[j] = __float_as_uint(v);
+            lo[j] = __float_as_uint(tf32_lo(v));
+        }
+        tmem_st<16>(lane_addr + n0, r);
+        tmem_st<16>(lane_addr + KMAX + n0, lo);
+    }
+}
+
+// upstream gradient of one low-res pixel in fused mode: reduce grad_depth over its R x R block
+template <int R>
+__device__ __forceinline__ void lpg_block_grad(const TcArgs &a, const PlaneFwd &pl, long long gp, float g[4])
+{
+    const int b = (int)(gp / a.hw);
+    const int rem = (int)(gp - (long long)b * a.hw);
+    const int i = rem / a.w, j = rem - i * a.w;
+    const int Wd = a.w * R;
+    const float *gp0 = a.grad + ((size_t)b * a.h + i) * R * (size_t)Wd + (size_t)j * R;
+    LpgAcc acc{0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int p = 0; p < R; ++p) {
+        float gv[R];
+        const float *row = gp0 + (size_t)p * Wd;
+        if constexpr (R % 4 == 0) {
+#pragma unroll
+            for (int k = 0; k < R; k += 4) {
+                const float4 t4 = __ldcs(reinterpret_cast<const float4 *>(row + k));
+                gv[k] = t4.x; gv[k + 1] = t4.y; gv[k + 2] = t4.z; gv[k + 3] = t4.w;
+            }
+        } else if constexpr (R == 2) {
+            const float2 t2 = __ldcs(reinterpret_cast<const float2 *>(row));
+            gv[0] = t2.x; gv[1] = t2.y;
+        } else {
+#pragma unroll
+            for (int k = 0; k < R; ++k) gv[k] = __ldcs(row + k);
+        }
+        const float v = lpg_offset(p, R);
+        const float n2v = __fmul_rn(pl.n2, v);
+#pragma unroll
+        for (int k = 0; k < R; ++k) {
+            const float u = lpg_offset(k, R);
+            lpg_bwd_accum(acc, gv[k], __fmul_rn(pl.n1, u), n2v, pl.n3, u, v, a.eps);
+        }
+    }
+    g[0] = -pl.n4 * acc.tu; g[1] = -pl.n4 * acc.tv; g[2] = -pl.n4 * acc.t; g[3] = acc.s4;
+}
+
+// MODE 0: sigmoid head (grad [B][1][hw]); 1: plane parameters (grad [B][4][hw]); 2: fused LPG (grad_depth)
+template <class CFG, int MODE, int R, int NWG>
+__global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_bwd1_kernel(BwdArgs ba)
+{
+    constexpr bool FINAL = (MODE == 0);
+    constexpr int LAST = FINAL ? 1 : 3;
+    constexpr int PACK = CFG::pack_floats(LAST);
+    constexpr int KMAX = CFG::kmax(), NMAX = CFG::nmax();
+    constexpr int COLS = 2 * KMAX + NMAX;
+    constexpr int D0 = CFG::dim(0);
+    static_assert(NWG * COLS <= 512, "TMEM budget");
+    const TcArgs &a = ba.a;
+
+    extern __shared__ __align__(128) float smem[];
+    float *sw = smem;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + PACK);
+    uint32_t *slot = reinterpret_cast<uint32_t *>(bars + NWG);
+
+    const int tid = threadIdx.x, wg = tid / kTile, t = tid % kTile;
+    for (int i = tid * 4; i < PACK; i += NWG * kTile * 4)
+        *reinterpret_cast<float4 *>(sw + i) = __ldg(reinterpret_cast<const float4 *>(a.wpack + i));
+    fence_smem_to_async();
+    if (tid < 32) tmem_alloc(slot, 512);
+    if (tid == 0) {
+        for (int i = 0; i < NWG; ++i) mbar_init(&bars[i], 1);
+        fence_mbar_init();
+    }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tbase = *slot;
+    const uint32_t wg_base = tbase + wg * COLS;
+    const uint32_t lane_addr = wg_base + ((uint32_t)((t >> 5) * 32) << 16);
+    uint64_t *bar = &bars[wg];
+    uint32_t phase = 0;
+    const float *tw = sw + CFG::tail_off();
+    const float *w5 = tw + kTailMid * kTailIn;
+    const long long npp = ba.npx_pad;
+
+    const long long ntiles = npp / kTile;
+    for (long long tile = (long long)blockIdx.x * NWG + wg; tile < ntiles; tile += (long long)gridDim.x * NWG) {
+        const long long gp = tile * kTile + t;
+        const bool valid = gp < a.npx;
+        const int b = valid ? (int)(gp / a.hw) : 0;
+        const int p = valid ? (int)(gp - (long long)b * a.hw) : 0;
+        const float *xp = a.x + (size_t)b * D0 * a.hw + p;
+        float *act_gp = ba.act + gp;
+        float *del_gp = ba.del + gp;
+#pragma unroll 1
+        for (int c0 = 0; c0 < D0; c0 += 32) {
+            uint32_t hi[32], lo[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) hi[j] = valid ? __float_as_uint(__ldg(xp + (size_t)(c0 + j) * a.hw)) : 0u;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) lo[j] = __float_as_uint(tf32_lo(__uint_as_float(hi[j])));
+            tmem_st<32>(lane_addr + c0, hi);
+            tmem_st<32>(lane_addr + KMAX + c0, lo);
+        }
+        tc_run_layer<CFG, 0>(wg_base, sw, bar, phase, wg, t);
+        if constexpr (CFG::NW > 1) {
+            tc_epilogue_to_a_spill<CFG, 0>(lane_addr, act_gp, npp);
+            tc_run_layer<CFG, 1>(wg_base, sw, bar, phase, wg, t);
+        }
+        if constexpr (CFG::NW > 2) {
+            tc_epilogue_to_a_spill<CFG, 1>(lane_addr, act_gp, npp);
+            tc_run_layer<CFG, 2>(wg_base, sw, bar, phase, wg, t);
+        }
+        if constexpr (CFG::NW > 3) {
+            tc_epilogue_to_a_spill<CFG, 2>(lane_addr, act_gp, npp);
+            tc_run_layer<CFG, 3>(wg_base, sw, bar, phase, wg, t);
+        }
+        float a16[kTailIn], a8[kTailMid], z[LAST];
+        {
+            uint32_t r[16];
+            tmem_ld<16>(lane_addr + 2 * KMAX, r);
+            wait_ld();
+            float *dst = act_gp + (size_t)BwdRows<CFG>::row(CFG::NW) * npp;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                a16[j] = elu_fast(__uint_as_float(r[j]));
+                dst[(size_t)j * npp] = a16[j];
+            }
+        }
+        tail_forward<LAST>(tw, a16, a8, z);
+        {
+            float *dst = act_gp + (size_t)BwdRows<CFG>::row8() * npp;
+#pragma unroll
+            for (int j = 0; j < kTailMid; ++j) dst[(size_t)j * npp] = a8[j];
+        }
+        // upstream gradient -> dz
+        float dz[3] = {0.f, 0.f, 0.f};
+        if constexpr (MODE == 0) {
+            const float s = sigmoidf(z[0]);
+            const float g = valid ? __ldcs(a.grad + gp) : 0.f;
+            dz[0] = g * s * (1.f - s);
+        } else {
+            const PlaneFwd pl = plane_from_logits(z[0], z[1], z[2], a.max_depth);
+            float g[4] = {0.f, 0.f, 0.f, 0.f};
+            if (valid) {
+                if constexpr (MODE == 1) {
+                    const float *gq = a.grad + (size_t)b * 4 * a.hw + p;
+                    g[0] = __ldcs(gq); g[1] = __ldcs(gq + a.hw); g[2] = __ldcs(gq + (size_t)2 * a.hw); g[3] = __ldcs(gq + (size_t)3 * a.hw);
+                } else {
+                    lpg_block_grad<R>(a, pl, gp, g);
+                }
+                plane_bwd(pl, g[0], g[1], g[2], g[3], a.max_depth, dz);
+            }
+        }
+        // tail backward: d8 = (W5^T dz) * ELU'(a8);  d16 = (W4^T d8) * ELU'(a16)
+        float d8[kTailMid], d16[kTailIn];
+#pragma unroll
+        for (int o = 0; o < kTailMid; ++o) {
+            float s = 0.f;
+#pragma unroll
+            for (int j = 0; j < LAST; ++j) s = fmaf(w5[j * kTailMid + o], dz[j], s);
+            d8[o] = s * elu_grad_from_out(a8[o]);
+        }
+#pragma unroll
+        for (int c = 0; c < kTailIn; ++c) d16[c] = 0.f;
+#pragma unroll
+        for (int o = 0; o < kTailMid; ++o) {
+#pragma unroll
+            for (int c = 0; c < kTailIn; c += 4) {
+                const float4 w4 = *reinterpret_cast<const float4 *>(tw + o * kTailIn + c);
+                d16[c] = fmaf(w4.x, d8[o], d16[c]); d16[c + 1] = fmaf(w4.y, d8[o], d16[c + 1]);
+                d16[c + 2] = fmaf(w4.z, d8[o], d16[c + 2]); d16[c + 3] = fmaf(w4.w, d8[o], d16[c + 3]);
+            }
+        }
+        {
+            float *dz_dst = del_gp + (size_t)BwdRows<CFG>::rowz() * npp;
+#pragma unroll
+            for (int j = 0; j < LAST; ++j) dz_dst[(size_t)j * npp] = dz[j];
+            float *d8_dst = del_gp + (size_t)BwdRows<CFG>::row8() * npp;
+#pragma unroll
+            for (int j = 0; j < kTailMid; ++j) d8_dst[(size_t)j * npp] = d8[j];
+            float *d16_dst = del_gp + (size_t)BwdRows<CFG>::row(CFG::NW) * npp;
+#pragma unroll
+            for (int j = 0; j < kTailIn; ++j) d16_dst[(size_t)j * npp] = d16[j] * elu_grad_from_out(a16[j]);
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (tid < 32) tmem_dealloc(tbase, 512);
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2: data gradient through the wide layers. A = delta_{l+1} (TMEM, hi/lo), B = W_l^T image
+// (rows = input channel c, K' = output channel o, K-major), D = delta_{l+1} W_l  [128 px x K_l].
+// ------------------------------------------------------------------------------------------------
+template <class CFG>
+struct DgradCfg {
+    __host__ __device__ static constexpr int kmax()   // widest A operand: N_l = dim(l+1)
+    {
+        int m = 0;
+        for (int l = 0; l < CFG::NW; ++l) m = CFG::N(l) > m ? CFG::N(l) : m;
+        return m;
+    }
+    __host__ __device__ static constexpr int nmax() { return CFG::kmax(); }
+};
+
+template <class CFG, int L>
+__device__ __forceinline__ void tc_issue_dgrad(uint32_t wg_base, const float *swt, uint64_t *bar)
+{
+    constexpr int KP = CFG::N(L), NP = CFG::K(L), KMAX = DgradCfg<CFG>::kmax();
+    constexpr uint32_t LBO = 128, SBO = (KP / 4) * 128;
+    constexpr uint32_t idesc = idesc_tf32(kTile, NP, 0, 0);
+    const uint32_t whi = smem_u32(swt + CFG::w_off(L));
+    const uint32_t wlo = whi + NP * KP * 4;
+    const uint32_t d = wg_base + 2 * KMAX;
+#pragma unroll
+    for (int k0 = 0; k0 < KP; k0 += 8)
+        mma_tf32_ts(d, wg_base + KMAX + k0, smem_desc(whi + (k0 / 4) * LBO, LBO, SBO), idesc, k0 > 0);
+#pragma unroll
+    for (int k0 = 0; k0 < KP; k0 += 8)
+        mma_tf32_ts(d, wg_base + k0, smem_desc(wlo + (k0 / 4) * LBO, LBO, SBO), idesc, 1);
+#pragma unroll
+    for (int k0 = 0; k0 < KP; k0 += 8)
+        mma_tf32_ts(d, wg_base + k0, smem_desc(whi + (k0 / 4) * LBO, LBO, SBO), idesc, 1);
+    mma_commit(bar);
+}
+
+template <class CFG, int L>
+__device__ __forceinline__ void dgrad_layer(const BwdArgs &ba, uint32_t wg_base, uint32_t lane_addr, const float *swt,
+                                            uint64_t *bar, uint32_t &phase, int wg, int t, long long gp, bool valid,
+                                            int b, int p)
+{
+    constexpr int NP = CFG::K(L), KMAX = DgradCfg<CFG>::kmax();
+    const long long npp = ba.npx_pad;
+    wait_st();
+    fence_before_sync();
+    named_bar_sync(1 + wg, kTile);
+    if (t == 0) {
+        fence_after_sync();
+        tc_issue_dgrad<CFG, L>(wg_base, swt, bar);
+    }
+    mbar_wait(bar, phase);
+    phase ^= 1;
+    fence_after_sync();
+    if constexpr (L == 0) {
+        float *gx = ba.a.grad_x + (size_t)b * NP * ba.a.hw + p;
+#pragma unroll 1
+        for (int n0 = 0; n0 < NP; n0 += 16) {
+            uint32_t r[16];
+            tmem_ld<16>(lane_addr + 2 * KMAX + n0, r);
+            wait_ld();
+            if (valid) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) gx[(size_t)(n0 + j) * ba.a.hw] = __uint_as_float(r[j]);
+            }
+        }
+    } else {
+        const float *act = ba.act + (size_t)BwdRows<CFG>::row(L) * npp + gp;
+        float *del = ba.del + (size_t)BwdRows<CFG>::row(L) * npp + gp;
+#pragma unroll 1
+        for (int n0 = 0; n0 < NP; n0 += 16) {
+            uint32_t r[16], lo[16];
+            float av[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) av[j] = __ldcg(act + (size_t)(n0 + j) * npp);
+            tmem_ld<16>(lane_addr + 2 * KMAX + n0, r);
+            wait_ld();
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const float v = __uint_as_float(r[j]) * elu_grad_from_out(av[j]);
+                del[(size_t)(n0 + j) * npp] = v;
+                r[j] = __float_as_uint(v);
+                lo[j] = __float_as_uint(tf32_lo(v));
+            }
+            tmem_st<16>(lane_addr + n0, r);
+            tmem_st<16>(lane_addr + KMAX + n0, lo);
+        }
+    }
+}
+
+template <class CFG, int NWG>
+__global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_dgrad_kernel(BwdArgs ba)
+{
+    constexpr int KMAX = DgradCfg<CFG>::kmax(), NMAX = DgradCfg<CFG>::nmax();
+    constexpr int COLS = 2 * KMAX + NMAX;
+    constexpr int IMG = CFG::tail_off();          // floats of transposed images
+    static_assert(NWG * COLS <= 512, "TMEM budget");
+    extern __shared__ __align__(128) float smem[];
+    float *swt = smem;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + IMG);
+    uint32_t *slot = reinterpret_cast<uint32_t *>(bars + NWG);
+    const int tid = threadIdx.x, wg = tid / kTile, t = tid % kTile;
+    for (int i = tid * 4; i < IMG; i += NWG * kTile * 4)
+        *reinterpret_cast<float4 *>(swt + i) = __ldg(reinterpret_cast<const float4 *>(ba.wpack_t + i));
+    fence_smem_to_async();
+    if (tid < 32) tmem_alloc(slot, 512);
+    if (tid == 0) {
+        for (int i = 0; i < NWG; ++i) mbar_init(&bars[i], 1);
+        fence_mbar_init();
+    }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tbase = *slot;
+    const uint32_t wg_base = tbase + wg * COLS;
+    const uint32_t lane_addr = wg_base + ((uint32_t)((t >> 5) * 32) << 16);
+    uint64_t *bar = &bars[wg];
+    uint32_t phase = 0;
+    const long long npp = ba.npx_pad;
+    const long long ntiles = npp / kTile;
+    for (long long tile = (long long)blockIdx.x * NWG + wg; tile < ntiles; tile += (long long)gridDim.x * NWG) {
+        const long long gp = tile * kTile + t;
+        const bool valid = gp < ba.a.npx;
+        const int b = valid ? (int)(gp / ba.a.hw) : 0;
+        const int p = valid ? (int)(gp - (long long)b * ba.a.hw) : 0;
+        {
+            const float *d16 = ba.del + (size_t)BwdRows<CFG>::row(CFG::NW) * npp + gp;
+            uint32_t hi[16], lo[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) hi[j] = __float_as_uint(__ldcg(d16 + (size_t)j * npp));
+#pragma unroll
+            for (int j = 0; j < 16; ++j) lo[j] = __float_as_uint(tf32_lo(__uint_as_float(hi[j])));
+            tmem_st<16>(lane_addr, hi);
+            tmem_st<16>(lane_addr + KMAX, lo);
+        }
+        if constexpr (CFG::NW > 3) dgrad_layer<CFG, 3>(ba, wg_base, lane_addr, swt, bar, phase, wg, t, gp, valid, b, p);
+        if constexpr (CFG::NW > 2) dgrad_layer<CFG, 2>(ba, wg_base, lane_addr, swt, bar, phase, wg, t, gp, valid, b, p);
+        if constexpr (CFG::NW > 1) dgrad_layer<CFG, 1>(ba, wg_base, lane_addr, swt, bar, phase, wg, t, gp, valid, b, p);
+        if (ba.a.grad_x != nullptr) dgrad_layer<CFG, 0>(ba, wg_base, lane_addr, swt, bar, phase, wg, t, gp, valid, b, p);
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (tid < 32) tmem_dealloc(tbase, 512);
+}
+
+// transposed images: layer l, rows = input channel c (N' = K_l), K' = output channel o (N_l)
+template <class CFG>
+__global__ void tc_pack_weights_t_kernel(ChainParams cp, float *wpack_t)
+{
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+#pragma unroll
+    for (int l = 0; l < CFG::NW; ++l) {
+        const int K = CFG::K(l), N = CFG::N(l);
+        float *hi = wpack_t + CFG::w_off(l), *lo = hi + N * K;
+        for (int e = tid; e < N * K; e += nth) {
+            const int o = e / K, c = e - o * K;
+            const float v = __ldg(cp.W[l] + e);
+            const uint32_t off = kmajor_off_floats(c, o, N);
+            hi[off] = v;
+            lo[off] = tc::tf32_lo(v);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3: weight gradients. For a tile of 64 pixels the activations (A operand) and deltas (B operand)
+// of a "job" are staged as K-major images with the PIXEL axis as K (thread = pixel, chunk stride
+// padded to 144 B so the 4-byte stores of a warp hit 32 different banks), hi and lo halves, and
+// multiplied by 3 x 8 SS-mode MMAs into a TMEM accumulator that lives for the whole kernel.
+// The plan (which rows go where) is data, built on the host from the chain description.
+// ------------------------------------------------------------------------------------------------
+constexpr int kWP = 64;                      // pixels per staging tile (K of one MMA batch)
+constexpr int kWLbo = 144;                   // bytes between 4-pixel chunks
+constexpr int kWSbo = (kWP / 4) * kWLbo;     // bytes between 8-row groups
+constexpr int kWMaxBlk = 5;
+
+struct WBlock {
+    const float *src;   // [rows][npx_pad] workspace matrix, or the NCHW input when is_x
+    int rows;
+    int is_x;
+};
+struct WJob {
+    WBlock a[kWMaxBlk], b[kWMaxBlk];
+    int na, nb;
+    int MA, NB;         // MMA shape (rows padded: 64|128, multiple of 8|16)
+    int tmem_col;
+};
+struct WExtract {       // layer l: D_job[row0 + k][col0 + n] -> partial[dst_off + n*K + k]
+    int job, row0, col0, K, N, dst_off;
+};
+struct WPlan {
+    WJob jobs[4];
+    WExtract ex[BTS_MAX_LAYERS];
+    int njobs, nlayers, total_w, tmem_cols;
+    int imgA_floats, imgB_floats;           // per half (hi or lo)
+    long long npx, npx_pad;
+    int hw, C0;
+    float *partials;                         // [gridDim.x][total_w]
+};
+
+__device__ __forceinline__ void wgrad_stage_block(const WBlock &blk, int row_base, float *hi, float *lo,
+                                                  int px, int rq, long long gp, bool valid, int b, int p,
+                                                  const WPlan &pl)
+{
+    const int chunk = (px >> 2) * (kWLbo / 4) + (px & 3);
+    if (blk.is_x) {
+        const float *src = blk.src + (size_t)b * pl.C0 * pl.hw + p;
+#pragma unroll 4
+        for (int r = rq; r < blk.rows; r += 4) {
+            const float v = valid ? __ldg(src + (size_t)r * pl.hw) : 0.f;
+            const int row = row_base + r;
+            const int off = (row & 7) * 4 + (row >> 3) * (kWSbo / 4) + chunk;
+            hi[off] = v;
+            lo[off] = tc::tf32_lo(v);
+        }
+    } else {
+        const float *src = blk.src + gp;
+#pragma unroll 4
+        for (int r = rq; r < blk.rows; r += 4) {
+            const float v = __ldcg(src + (size_t)r * pl.npx_pad);
+            const int row = row_base + r;
+            const int off = (row & 7) * 4 + (row >> 3) * (kWSbo / 4) + chunk;
+            hi[off] = v;
+            lo[off] = tc::tf32_lo(v);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256, 1) chain_tc_wgrad_kernel(const __grid_constant__ WPlan pl)
+{
+    extern __shared__ __align__(128) float smem[];
+    float *a_hi = smem, *a_lo = a_hi + pl.imgA_floats;
+    float *b_hi = a_lo + pl.imgA_floats, *b_lo = b_hi + pl.imgB_floats;
+    __shared__ uint64_t bar;
+    __shared__ uint32_t slot;
+    const int tid = threadIdx.x;
+    if (tid < 32) tmem_alloc(&slot, pl.tmem_cols);
+    if (tid == 0) {
+        mbar_init(&bar, 1);
+        fence_mbar_init();
+    }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tbase = slot;
+    const int px = tid & (kWP - 1), rq = tid >> 6;
+    uint32_t phase = 0;
+    bool pending = false, first = true;
+    const long long ntiles = pl.npx_pad / kWP;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const long long gp = tile * kWP + px;
+        const bool valid = gp < pl.npx;
+        const int b = valid ? (int)(gp / pl.hw) : 0;
+        const int p = valid ? (int)(gp - (long long)b * pl.hw) : 0;
+        for (int j = 0; j < pl.njobs; ++j) {
+            const WJob &job = pl.jobs[j];
+            if (pending) {                    // the previous MMAs still read the images
+                mbar_wait(&bar, phase);
+                phase ^= 1;
+                pending = false;
+            }
+            int rb = 0;
+            for (int i = 0; i < job.na; ++i) {
+                wgrad_stage_block(job.a[i], rb, a_hi, a_lo, px, rq, gp, valid, b, p, pl);
+                rb += job.a[i].rows;
+            }
+            rb = 0;
+            for (int i = 0; i < job.nb; ++i) {
+                wgrad_stage_block(job.b[i], rb, b_hi, b_lo, px, rq, gp, valid, b, p, pl);
+                rb += job.b[i].rows;
+            }
+            fence_smem_to_async();
+            __syncthreads();
+            if (tid == 0) {
+                fence_after_sync();
+                const uint32_t idesc = idesc_tf32(job.MA, job.NB, 0, 0);
+                const uint32_t d = tbase + job.tmem_col;
+                const uint32_t ah = smem_u32(a_hi), al = smem_u32(a_lo), bh = smem_u32(b_hi), bl = smem_u32(b_lo);
+                uint32_t acc = first ? 0u : 1u;
+#pragma unroll 1
+                for (int pass = 0; pass < 3; ++pass) {
+                    const uint32_t sa = pass == 0 ? al : ah, sb = pass == 1 ? bl : bh;
+#pragma unroll
+                    for (int ks = 0; ks < kWP / 8; ++ks) {
+                        mma_tf32_ss(d, smem_desc(sa + ks * 2 * kWLbo, kWLbo, kWSbo),
+                                    smem_desc(sb + ks * 2 * kWLbo, kWLbo, kWSbo), idesc, acc);
+                        acc = 1u;
+                    }
+                }
+                mma_commit(&bar);
+            }
+            pending = true;
+        }
+        first = false;
+    }
+    if (pending) {
+        mbar_wait(&bar, phase);
+        phase ^= 1;
+    }
+    fence_after_sync();
+    // accumulators -> this CTA's partial sums
+    float *part = pl.partials + (size_t)blockIdx.x * pl.total_w;
+    if (first) {                              // CTA had no tile: contribute zeros
+        for (int e = tid; e < pl.total_w; e += blockDim.x) part[e] = 0.f;
+    } else if (tid < 128) {
+        const int lane_row_base = (tid >> 5) * 32;
+        const uint32_t lane_addr = tbase + ((uint32_t)lane_row_base << 16);
+        for (int l = 0; l < pl.nlayers; ++l) {
+            const WExtract &ex = pl.ex[l];
+            const int MA = pl.jobs[ex.job].MA;
+            // TMEM lane -> accumulator row: identity for M=128; M=64 keeps 16 rows per 32-lane quarter
+            const int li = tid & 31;
+            const int m = (MA == 128) ? tid : ((li < 16) ? (tid >> 5) * 16 + li : -1);
+            const int k = m - ex.row0;
+            const bool mine = (m >= 0) && k >= 0 && k < ex.K;
+            for (int n0 = 0; n0 < ex.N; n0 += 8) {
+                uint32_t r[8];
+                tmem_ld<8>(lane_addr + pl.jobs[ex.job].tmem_col + ex.col0 + n0, r);
+                wait_ld();
+                if (mine) {
+#pragma unroll
+                    for (int jn = 0; jn < 8; ++jn)
+                        if (n0 + jn < ex.N) part[ex.dst_off + (size_t)(n0 + jn) * ex.K + k] = __uint_as_float(r[jn]);
+                }
+            }
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (tid < 32) tmem_dealloc(tbase, pl.tmem_cols);
+}
+
+// K4: grad_W[l] += sum over CTAs of the partial sums
+__global__ void chain_tc_wreduce_kernel(ChainParams cp, const float *partials, int nparts, int total_w)
+{
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= total_w) return;
+    float s = 0.f;
+    for (int c = 0; c < nparts; ++c) s += __ldcg(partials + (size_t)c * total_w + e);
+    int off = 0;
+    for (int l = 0; l < cp.n_layers; ++l) {
+        const int n = cp.dims[l] * cp.dims[l + 1];
+        if (e < off + n) {
+            cp.gW[l][e - off] += s;
+            return;
+        }
+        off += n;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+size_t tc_pack_bytes();
+
+static long long pad128(long long n) { return (n + kTile - 1) / kTile * kTile; }
+
+static void bwd_rows(const ChainParams &cp, int *ra, int *rd, int *total_w)
+{
+    int a = 0, d = 0, w = 0;
+    for (int l = 1; l < cp.n_layers; ++l) a += cp.dims[l];
+    for (int l = 1; l <= cp.n_layers; ++l) d += cp.dims[l];
+    for (int l = 0; l < cp.n_layers; ++l) w += cp.dims[l] * cp.dims[l + 1];
+    *ra = a; *rd = d; *total_w = w;
+}
+
+// bytes the tensor-core backward needs after the two packed-weight regions
+size_t tc_bwd_workspace_bytes(const ChainParams &cp, long long npx, int sms)
+{
+    int ra, rd, tw;
+    bwd_rows(cp, &ra, &rd, &tw);
+    return sizeof(float) * ((size_t)(ra + rd) * (size_t)pad128(npx) + (size_t)sms * tw);
+}
+
+static int build_wgrad_plan(const ChainParams &cp, WPlan &pl, const float *x, float *act, float *del,
+                            long long npx, long long npp, int hw)
+{
+    memset(&pl, 0, sizeof(pl));
+    const int L = cp.n_layers;
+    int fc = L, sum = 0;
+    while (fc > 0 && sum + cp.dims[fc - 1] <= 128) sum += cp.dims[--fc];
+    if (fc == L) return set_error(BTS_ERR_UNSUPPORTED, "layer wider than 128 channels");
+    int prefix[BTS_MAX_LAYERS + 2];                     // prefix[l] = sum_{j=1}^{l-1} dims[j]
+    prefix[0] = prefix[1] = 0;
+    for (int l = 2; l <= L + 1; ++l) prefix[l] = prefix[l - 1] + cp.dims[l - 1];
+    int col = 0, maxMA = 0, maxNB = 0, woff = 0;
+    int woffs[BTS_MAX_LAYERS];
+    for (int l = 0; l < L; ++l) { woffs[l] = woff; woff += cp.dims[l] * cp.dims[l + 1]; }
+    pl.njobs = fc + 1;
+    if (pl.njobs > 4) return set_error(BTS_ERR_UNSUPPORTED, "too many weight-gradient jobs");
+    for (int j = 0; j < pl.njobs; ++j) {
+        WJob &job = pl.jobs[j];
+        const int l0 = j < fc ? j : fc, l1 = j < fc ? j + 1 : L;
+        if (l1 - l0 > kWMaxBlk) return set_error(BTS_ERR_UNSUPPORTED, "too many layers in one job");
+        int ra = 0, rb = 0;
+        for (int l = l0; l < l1; ++l) {
+            if (cp.dims[l] > 128) return set_error(BTS_ERR_UNSUPPORTED, "layer wider than 128 channels");
+            WBlock &ba = job.a[job.na++];
+            ba.is_x = (l == 0);
+            ba.src = (l == 0) ? x : act + (size_t)prefix[l] * npp;
+            ba.rows = cp.dims[l];
+            WBlock &bb = job.b[job.nb++];
+            bb.is_x = 0;
+            bb.src = del + (size_t)prefix[l + 1] * npp;
+            bb.rows = cp.dims[l + 1];
+            WExtract &ex = pl.ex[l];
+            ex.job = j; ex.row0 = ra; ex.col0 = rb; ex.K = cp.dims[l]; ex.N = cp.dims[l + 1]; ex.dst_off = woffs[l];
+            ra += cp.dims[l];
+            rb += cp.dims[l + 1];
+        }
+        job.MA = ra <= 64 ? 64 : 128;
+        const int g = job.MA == 128 ? 16 : 8;
+        job.NB = (rb + g - 1) / g * g;
+        if (job.NB < g) job.NB = g;
+        if (job.NB > 256) return set_error(BTS_ERR_UNSUPPORTED, "delta block wider than 256");
+        job.tmem_col = col;
+        col += job.NB;
+        if (job.MA > maxMA) maxMA = job.MA;
+        if (job.NB > maxNB) maxNB = job.NB;
+    }
+    if (col > 512) return set_error(BTS_ERR_UNSUPPORTED, "weight-gradient accumulators exceed TMEM");
+    int cols = 32;
+    while (cols < col) cols <<= 1;
+    pl.tmem_cols = cols;
+    pl.nlayers = L;
+    pl.total_w = woff;
+    pl.imgA_floats = (maxMA / 8) * (kWSbo / 4);
+    pl.imgB_floats = ((maxNB + 7) / 8) * (kWSbo / 4);
+    pl.npx = npx; pl.npx_pad = npp; pl.hw = hw; pl.C0 = cp.dims[0];
+    return BTS_OK;
+}
+
+template <class CFG, int MODE, int R, int NWG1, int NWG2>
+static int launch_bwd_cfg(const ChainParams &cp, const TcArgs &a, char *ws, int sms, cudaStream_t s)
+{
+    constexpr int LAST = MODE == 0 ? 1 : 3;
+    float *wpack = reinterpret_cast<float *>(ws);
+    float *wpack_t = reinterpret_cast<float *>(ws + tc_pack_bytes());
+    const long long npp = pad128(a.npx);
+    int ra, rd, tw;
+    bwd_rows(cp, &ra, &rd, &tw);
+    float *act = reinterpret_cast<float *>(ws + 2 * tc_pack_bytes());
+    float *del = act + (size_t)ra * npp;
+    float *partials = del + (size_t)rd * npp;
+
+    tc_pack_weights_kernel<CFG><<<16, 256, 0, s>>>(cp, wpack, LAST);
+    if (int e = check_launch("tc_pack_weights")) return e;
+    tc_pack_weights_t_kernel<CFG><<<16, 256, 0, s>>>(cp, wpack_t);
+    if (int e = check_launch("tc_pack_weights_t")) return e;
+
+    BwdArgs ba;
+    ba.a = a;
+    ba.a.wpack = wpack;
+    ba.wpack_t = wpack_t;
+    ba.act = act; ba.del = del; ba.npx_pad = npp;
+    const long long ntiles = npp / kTile;
+    {
+        auto k1 = chain_tc_bwd1_kernel<CFG, MODE, R, NWG1>;
+        const size_t smem = sizeof(float) * CFG::pack_floats(LAST) + 8 * NWG1 + 16;
+        cudaError_t e = cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        long long grid = (ntiles + NWG1 - 1) / NWG1;
+        if (grid > sms) grid = sms;
+        k1<<<(unsigned)grid, NWG1 * kTile, smem, s>>>(ba);
+        if (int e2 = check_launch("chain_tc_bwd1")) return e2;
+    }
+    {
+        auto k2 = chain_tc_dgrad_kernel<CFG, NWG2>;
+        const size_t smem = sizeof(float) * CFG::tail_off() + 8 * NWG2 + 16;
+        cudaError_t e = cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        long long grid = (ntiles + NWG2 - 1) / NWG2;
+        if (grid > sms) grid = sms;
+        // with no grad_x and a single wide layer there is nothing for K2 to do
+        if (a.grad_x != nullptr || CFG::NW > 1) {
+            k2<<<(unsigned)grid, NWG2 * kTile, smem, s>>>(ba);
+            if (int e2 = check_launch("chain_tc_dgrad")) return e2;
+        }
+    }
+    if (cp.gW[0] != nullptr) {
+        WPlan pl;
+        if (int e = build_wgrad_plan(cp, pl, a.x, act, del, a.npx, npp, a.hw)) return e;
+        pl.partials = partials;
+        const size_t smem = sizeof(float) * 2 * (size_t)(pl.imgA_floats + pl.imgB_floats);
+        cudaError_t e = cudaFuncSetAttribute(chain_tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        long long grid = npp / kWP;
+        if (grid > sms) grid = sms;
+        chain_tc_wgrad_kernel<<<(unsigned)grid, 256, smem, s>>>(pl);
+        if (int e2 = check_launch("chain_tc_wgrad")) return e2;
+        chain_tc_wreduce_kernel<<<(pl.total_w + 255) / 256, 256, 0, s>>>(cp, partials, (int)grid, pl.total_w);
+        if (int e2 = check_launch("chain_tc_wreduce")) return e2;
+    }
+    return BTS_OK;
+}
+
+template <class CFG, int NWG1, int NWG2>
+static int dispatch_bwd_mode(const ChainParams &cp, const TcArgs &a, int mode, int r, char *ws, int sms, cudaStream_t s)
+{
+    if (mode == 0) return launch_bwd_cfg<CFG, 0, 1, NWG1, NWG2>(cp, a, ws, sms, s);
+    if (mode == 1) return launch_bwd_cfg<CFG, 1, 1, NWG1, NWG2>(cp, a, ws, sms, s);
+    switch (r) {
+    case 8: return launch_bwd_cfg<CFG, 2, 8, NWG1, NWG2>(cp, a, ws, sms, s);
+    case 4: return launch_bwd_cfg<CFG, 2, 4, NWG1, NWG2>(cp, a, ws, sms, s);
+    case 2: return launch_bwd_cfg<CFG, 2, 2, NWG1, NWG2>(cp, a, ws, sms, s);
+    default: return launch_bwd_cfg<CFG, 2, 1, NWG1, NWG2>(cp, a, ws, sms, s);
+    }
+}
+
+// mode: 0 head (grad [B,1,hw]), 1 plane parameters (grad [B,4,hw]), 2 fused LPG (grad_depth, upratio r)
+int launch_chain_tc_bwd(const ChainParams &cp, const TcArgs &a, int mode, int r, void *ws, int sms, cudaStream_t s)
+{
+    char *w = static_cast<char *>(ws);
+    if (cfg_matches<Cfg128_128>(cp)) return dispatch_bwd_mode<Cfg128_128, 1, 1>(cp, a, mode, r, w, sms, s);
+    if (cfg_matches<Cfg128_64>(cp)) return dispatch_bwd_mode<Cfg128_64, 1, 2>(cp, a, mode, r, w, sms, s);
+    if (cfg_matches<Cfg64_64>(cp)) return dispatch_bwd_mode<Cfg64_64, 2, 2>(cp, a, mode, r, w, sms, s);
+    if (cfg_matches<Cfg64_32>(cp)) return dispatch_bwd_mode<Cfg64_32, 3, 3>(cp, a, mode, r, w, sms, s);
+    if (cfg_matches<Cfg32_32>(cp)) return dispatch_bwd_mode<Cfg32_32, 3, 3>(cp, a, mode, r, w, sms, s);
+    if (cfg_matches<Cfg32_16>(cp)) return dispatch_bwd_mode<Cfg32_16, 3, 3>(cp, a, mode, r, w, sms, s);
+    return set_error(BTS_ERR_UNSUPPORTED, "chain not covered by the tensor-core path");
+}
+
+}  // namespace bts

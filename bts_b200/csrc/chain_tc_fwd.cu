@@ -1,0 +1,168 @@
+// chain_tc_fwd.cu -- fused forward of one BTS decoder stage on sm_100a tensor cores:
+//   reduction_1x1 chain (pytorch/bts.py:124-136)  ->  plane parameterisation (127-134)
+//   -> [normalise/cat glue 250-253: identity on a unit normal]  ->  LPG expansion (149-173)
+// in ONE persistent kernel. Features are read once from HBM, depth is written once; no intermediate
+// ever leaves the SM. See chain_tc.cuh for the split between tcgen05 (wide layers) and SIMT (tail).
+//
+// Work decomposition: a warpgroup (128 threads) owns one tile of 128 consecutive low-res pixels;
+// thread t <-> pixel t <-> TMEM lane t. NWG independent warpgroups per CTA (each with its own TMEM
+// columns, mbarrier and MMA-issuing thread) keep the tensor core, the LSU and the FMA pipes busy at
+// the same time: while one warpgroup waits for its MMAs another one loads or runs its epilogue.
+#include "chain_tc.cuh"
+
+namespace bts {
+
+
+
+template <class CFG, int R, bool FINAL, int NWG>
+__global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
+{
+    constexpr int LAST = FINAL ? 1 : 3;
+    constexpr int PACK = CFG::pack_floats(LAST);
+    constexpr int KMAX = CFG::kmax(), NMAX = CFG::nmax();
+    constexpr int COLS = 2 * KMAX + NMAX;
+    constexpr int D0 = CFG::dim(0);
+    static_assert(NWG * COLS <= 512, "TMEM budget");
+    static_assert(CFG::dim(CFG::NW) == kTailIn, "tensor-core part must end at 16 channels");
+
+    extern __shared__ __align__(128) float smem[];
+    float *sw = smem;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + PACK);
+    uint32_t *slot = reinterpret_cast<uint32_t *>(bars + NWG);
+
+    const int tid = threadIdx.x, wg = tid / kTile, t = tid % kTile, lane = tid & 31;
+    for (int i = tid * 4; i < PACK; i += NWG * kTile * 4)
+        *reinterpret_cast<float4 *>(sw + i) = __ldg(reinterpret_cast<const float4 *>(a.wpack + i));
+    fence_smem_to_async();
+    if (tid < 32) tmem_alloc(slot, 512);
+    if (tid == 0) {
+        for (int i = 0; i < NWG; ++i) mbar_init(&bars[i], 1);
+        fence_mbar_init();
+    }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tbase = *slot;
+    const uint32_t wg_base = tbase + wg * COLS;
+    const uint32_t lane_addr = wg_base + ((uint32_t)((t >> 5) * 32) << 16);
+    uint64_t *bar = &bars[wg];
+    uint32_t phase = 0;
+    const float *tw = sw + CFG::tail_off();
+    int key = 0x7f800000;
+
+    const long long ntiles = (a.npx + kTile - 1) / kTile;
+    for (long long tile = (long long)blockIdx.x * NWG + wg; tile < ntiles; tile += (long long)gridDim.x * NWG) {
+        const long long gp = tile * kTile + t;
+        const bool valid = gp < a.npx;
+        const int b = valid ? (int)(gp / a.hw) : 0;
+        const int p = valid ? (int)(gp - (long long)b * a.hw) : 0;
+        const float *xp = a.x + (size_t)b * D0 * a.hw + p;
+        // features -> (hi, lo) -> TMEM A operand; 32 independent coalesced loads in flight per thread
+#pragma unroll 1
+        for (int c0 = 0; c0 < D0; c0 += 32) {
+            uint32_t hi[32], lo[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) hi[j] = valid ? __float_as_uint(__ldg(xp + (size_t)(c0 + j) * a.hw)) : 0u;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) lo[j] = __float_as_uint(tf32_lo(__uint_as_float(hi[j])));
+            tmem_st<32>(lane_addr + c0, hi);
+            tmem_st<32>(lane_addr + KMAX + c0, lo);
+        }
+        // wide layers
+        tc_run_layer<CFG, 0>(wg_base, sw, bar, phase, wg, t);
+        if constexpr (CFG::NW > 1) {
+            tc_epilogue_to_a<CFG, 0>(lane_addr);
+            tc_run_layer<CFG, 1>(wg_base, sw, bar, phase, wg, t);
+        }
+        if constexpr (CFG::NW > 2) {
+            tc_epilogue_to_a<CFG, 1>(lane_addr);
+            tc_run_layer<CFG, 2>(wg_base, sw, bar, phase, wg, t);
+        }
+        if constexpr (CFG::NW > 3) {
+            tc_epilogue_to_a<CFG, 2>(lane_addr);
+            tc_run_layer<CFG, 3>(wg_base, sw, bar, phase, wg, t);
+        }
+        float a16[kTailIn], a8[kTailMid], z[LAST];
+        {
+            uint32_t r[16];
+            tmem_ld<16>(lane_addr + 2 * KMAX, r);
+            wait_ld();
+#pragma unroll
+            for (int j = 0; j < 16; ++j) a16[j] = elu_fast(__uint_as_float(r[j]));
+        }
+        tail_forward<LAST>(tw, a16, a8, z);
+        if constexpr (FINAL) {
+            if (valid) a.out[gp] = sigmoidf(z[0]);
+        } else {
+            const PlaneFwd pl = plane_from_logits(z[0], z[1], z[2], a.max_depth);
+            if (a.out != nullptr && valid) {
+                float *o = a.out + (size_t)b * 4 * a.hw + p;
+                o[0] = pl.n1; o[(size_t)a.hw] = pl.n2; o[(size_t)2 * a.hw] = pl.n3; o[(size_t)3 * a.hw] = pl.n4;
+            }
+            if (a.depth != nullptr) key = min(key, lpg_expand<R>(a, pl.n1, pl.n2, pl.n3, pl.n4, gp, valid, lane));
+        }
+    }
+    if constexpr (!FINAL) {
+        if (a.depth != nullptr && a.abs_min != nullptr) {
+            key = warp_min_int(key);
+            int *addr = reinterpret_cast<int *>(a.abs_min);
+            if (lane == 0 && key < *reinterpret_cast<volatile int *>(addr)) atomicMin(addr, key);
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (tid < 32) tmem_dealloc(tbase, 512);
+}
+
+template <class CFG, int R, bool FINAL, int NWG>
+static int launch_one(const ChainParams &cp, const TcArgs &a, float *wpack, int sms, cudaStream_t s)
+{
+    constexpr int LAST = FINAL ? 1 : 3;
+    tc_pack_weights_kernel<CFG><<<16, 256, 0, s>>>(cp, wpack, LAST);
+    if (int e = check_launch("tc_pack_weights")) return e;
+    const size_t smem = sizeof(float) * CFG::pack_floats(LAST) + 8 * NWG + 16;
+    auto kern = chain_tc_fwd_kernel<CFG, R, FINAL, NWG>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    const long long ntiles = (a.npx + kTile - 1) / kTile;
+    long long grid = (ntiles + NWG - 1) / NWG;
+    if (grid > sms) grid = sms;
+    TcArgs aa = a;
+    aa.wpack = wpack;
+    kern<<<(unsigned)grid, NWG * kTile, smem, s>>>(aa);
+    return check_launch("chain_tc_fwd");
+}
+
+size_t tc_pack_bytes() { return 256 * 1024; }
+
+bool tc_supported(const ChainParams &cp)
+{
+    return cfg_matches<Cfg128_128>(cp) || cfg_matches<Cfg128_64>(cp) || cfg_matches<Cfg64_64>(cp) ||
+           cfg_matches<Cfg64_32>(cp) || cfg_matches<Cfg32_32>(cp) || cfg_matches<Cfg32_16>(cp);
+}
+
+template <class CFG, int NWG>
+static int dispatch_r(const ChainParams &cp, const TcArgs &a, int r, float *wpack, int sms, cudaStream_t s)
+{
+    if (cp.is_final) return launch_one<CFG, 1, true, NWG>(cp, a, wpack, sms, s);
+    switch (r) {
+    case 8: return launch_one<CFG, 8, false, NWG>(cp, a, wpack, sms, s);
+    case 4: return launch_one<CFG, 4, false, NWG>(cp, a, wpack, sms, s);
+    case 2: return launch_one<CFG, 2, false, NWG>(cp, a, wpack, sms, s);
+    default: return launch_one<CFG, 1, false, NWG>(cp, a, wpack, sms, s);   // r == 1, or plane_eq only
+    }
+}
+
+// r = 0: no LPG (reduction only). Returns BTS_ERR_UNSUPPORTED when the chain is not covered.
+int launch_chain_tc_fwd(const ChainParams &cp, const TcArgs &a, int r, float *wpack, int sms, cudaStream_t s)
+{
+    if (cfg_matches<Cfg128_128>(cp)) return dispatch_r<Cfg128_128, 1>(cp, a, r, wpack, sms, s);
+    if (cfg_matches<Cfg128_64>(cp)) return dispatch_r<Cfg128_64, 1>(cp, a, r, wpack, sms, s);
+    if (cfg_matches<Cfg64_64>(cp)) return dispatch_r<Cfg64_64, 2>(cp, a, r, wpack, sms, s);
+    if (cfg_matches<Cfg64_32>(cp)) return dispatch_r<Cfg64_32, 3>(cp, a, r, wpack, sms, s);
+    if (cfg_matches<Cfg32_32>(cp)) return dispatch_r<Cfg32_32, 4>(cp, a, r, wpack, sms, s);
+    if (cfg_matches<Cfg32_16>(cp)) return dispatch_r<Cfg32_16, 4>(cp, a, r, wpack, sms, s);
+    return set_error(BTS_ERR_UNSUPPORTED, "chain not covered by the tensor-core path");
+}
+
+}  // namespace bts

@@ -76,6 +76,24 @@ __device__ __forceinline__ float lpg_clamp(float den, float eps)
     return den;
 }
 
+// ---- LPG backward accumulation for one output pixel
+struct LpgAcc {
+    float s4, t, tu, tv;
+};
+__device__ __forceinline__ void lpg_bwd_accum(LpgAcc &a, float g, float n1u, float n2v, float n3,
+                                              float u, float v, float eps)
+{
+    const float den = lpg_den(n1u, n2v, n3);
+    const float denc = lpg_clamp(den, eps);
+    const float inv = __fdiv_rn(1.f, denc);
+    const float gi = g * inv;
+    a.s4 += gi;
+    const float gi2 = (denc == den) ? gi * inv : 0.f;   // clamped => no gradient to n1..n3
+    a.t += gi2;
+    a.tu = fmaf(gi2, u, a.tu);
+    a.tv = fmaf(gi2, v, a.tv);
+}
+
 // ---- abs_min bookkeeping: key = bits(|den|) as signed int, NaN -> 0xFFC00000 (negative => wins the
 // signed min and reads back as NaN, like torch.min).
 __device__ __forceinline__ int absmin_key(float den)

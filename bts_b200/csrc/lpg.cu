@@ -105,23 +105,6 @@ lpg_fwd_scalar_kernel(const float *__restrict__ plane_eq, float *__restrict__ de
 //   G4 = sum g / den_c ;  unclamped pixels: G1 = -n4 sum g u / den^2, G2 = -n4 sum g v / den^2,
 //   G3 = -n4 sum g / den^2 ; clamped pixels add nothing to G1..G3 (torch.where blocks the gradient).
 // ------------------------------------------------------------------------------------------------
-struct LpgAcc {
-    float s4, t, tu, tv;
-};
-__device__ __forceinline__ void lpg_bwd_accum(LpgAcc &a, float g, float n1u, float n2v, float n3,
-                                              float u, float v, float eps)
-{
-    const float den = lpg_den(n1u, n2v, n3);
-    const float denc = lpg_clamp(den, eps);
-    const float inv = __fdiv_rn(1.f, denc);
-    const float gi = g * inv;
-    a.s4 += gi;
-    const float gi2 = (denc == den) ? gi * inv : 0.f;   // clamped => no gradient to n1..n3
-    a.t += gi2;
-    a.tu = fmaf(gi2, u, a.tu);
-    a.tv = fmaf(gi2, v, a.tv);
-}
-
 template <int R>
 __global__ void __launch_bounds__(256)
 lpg_bwd_vec_kernel(const float *__restrict__ grad_depth, const float *__restrict__ plane_eq,

@@ -191,3 +191,16 @@ def reduc(x, weights, max_depth, is_final=False):
 def reduc_lpg(x, weights, max_depth, upratio, return_plane_eq=False):
     """Fused stage -> (depth, abs_min[, plane_eq])."""
     return _ReducLPG.apply(x, max_depth, upratio, return_plane_eq, *weights)
+
+
+PATH_AUTO, PATH_GENERIC, PATH_TCGEN05 = -1, 0, 2
+
+
+def force_path(path):
+    """Test / profiling hook: pin the chain implementation for calls from this thread (PATH_AUTO resets)."""
+    _cabi.lib().bts_force_path(int(path))
+
+
+def chain_path(dims, is_final):
+    """Which implementation serves this chain (PATH_GENERIC or PATH_TCGEN05)."""
+    return _cabi.lib().bts_reduc_path(_cabi.int_array(list(dims)), len(dims) - 1, int(bool(is_final)))

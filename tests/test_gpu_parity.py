@@ -286,3 +286,50 @@ def test_ddp_wraps_the_modules():
     finally:
         if created:
             dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("cfg", [(128, 128, False, 8, 3, 19, 23), (128, 64, False, 4, 2, 33, 41), (64, 32, False, 2, 2, 50, 70),
+                                 (32, 16, True, 1, 2, 100, 130), (64, 64, False, 8, 1, 17, 9), (32, 32, False, 4, 1, 40, 40),
+                                 (32, 16, False, 2, 1, 31, 33), (128, 128, False, 1, 1, 9, 20)],
+                         ids=lambda c: "x".join(map(str, c)))
+def test_tensor_core_path_vs_generic_path(cfg):
+    """The tcgen05 kernels and the generic SIMT kernels are independent implementations: they must
+    agree to fp32 rounding (3xTF32 keeps fp32 accuracy) on shapes with partial tiles and image wraps."""
+    import bts_b200
+    from bts_b200 import functional as Fn
+    num_in, num_out, is_final, r, B, h, w = cfg
+    dims = bts_b200.chain_channels(num_in, num_out, is_final)
+    assert Fn.chain_path(dims, is_final) == Fn.PATH_TCGEN05
+    torch.manual_seed(5)
+    red = bts_b200.reduction_1x1(num_in, num_out, 10.0, is_final).cuda()
+    for p in red.parameters():
+        torch.nn.init.xavier_uniform_(p)
+    x = torch.randn(B, num_in, h, w, device="cuda")
+    g = torch.randn((B, 1, h, w) if is_final else (B, h * r, w * r), device="cuda")
+
+    def run():
+        xx = x.clone().requires_grad_(True)
+        red.zero_grad()
+        if is_final:
+            out, amin = red(xx), None
+        else:
+            lpg = bts_b200.local_planar_guidance(r)
+            out = bts_b200.fused_stage(red, lpg, xx)
+            amin = float(lpg.abs_min)
+        out.backward(g)
+        return out.detach(), amin, xx.grad, [p.grad.clone() for p in red.parameters()]
+
+    try:
+        Fn.force_path(Fn.PATH_GENERIC)
+        ref = run()
+    finally:
+        Fn.force_path(Fn.PATH_AUTO)
+    got = run()
+    if is_final:
+        close_peak(got[0], ref[0].cpu().numpy())
+    else:
+        assert torch.allclose(got[0], ref[0], rtol=RTOL, atol=1e-5)
+        assert abs(got[1] - ref[1]) <= 1e-5
+    close_peak(got[2], ref[2].cpu().numpy())
+    for a, b in zip(got[3], ref[3]):
+        close_peak(a, b.cpu().numpy())
