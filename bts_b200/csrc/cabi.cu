@@ -37,6 +37,8 @@ int launch_chain_generic_fwd(const ChainParams &, const float *, float *, int, i
 int launch_chain_generic_bwd(const ChainParams &, const float *, const float *, float *, int, int, cudaStream_t);
 int launch_chain_tc_fwd(const ChainParams &, const TcArgs &, int r, float *wpack, int sms, cudaStream_t);
 int launch_chain_tc_bwd(const ChainParams &, const TcArgs &, int mode, int r, void *ws, int sms, cudaStream_t);
+int launch_chain_bwd_fused(const ChainParams &, const TcArgs &, int mode, int r, void *ws, int sms, cudaStream_t);
+bool fused_bwd_supported(const ChainParams &);
 bool tc_supported(const ChainParams &);
 size_t tc_pack_bytes();
 size_t tc_bwd_workspace_bytes(const ChainParams &, long long npx, int sms);
@@ -199,6 +201,8 @@ int bts_reduc_bwd(const float *x, const float *const *W, const int *dims, int n_
     if (use_tc_bwd(cp, ws, ws_bytes, (long long)B * h * w, nullptr)) {
         TcArgs a = make_tc_args(x, B, h, w, max_depth, 0.f);
         a.grad = grad_out; a.grad_x = grad_x;
+        if (fused_bwd_supported(cp) && g_force_path != BTS_PATH_TCGEN05_SPLIT)
+            return launch_chain_bwd_fused(cp, a, is_final ? 0 : 1, 0, ws, sm_count(), (cudaStream_t)stream);
         return launch_chain_tc_bwd(cp, a, is_final ? 0 : 1, 0, ws, sm_count(), (cudaStream_t)stream);
     }
     return launch_chain_generic_bwd(cp, x, grad_out, grad_x, B, h * w, (cudaStream_t)stream);
@@ -243,6 +247,8 @@ int bts_reduc_lpg_bwd(const float *grad_depth, const float *x, const float *cons
     if ((r == 1 || r == 2 || r == 4 || r == 8) && use_tc_bwd(cp, ws, ws_bytes, (long long)B * h * w, grad_depth)) {
         TcArgs a = make_tc_args(x, B, h, w, max_depth, eps);
         a.grad = grad_depth; a.grad_x = grad_x;
+        if (fused_bwd_supported(cp) && g_force_path != BTS_PATH_TCGEN05_SPLIT)
+            return launch_chain_bwd_fused(cp, a, 2, r, ws, sm_count(), (cudaStream_t)stream);
         return launch_chain_tc_bwd(cp, a, 2, r, ws, sm_count(), (cudaStream_t)stream);
     }
     const size_t one = (size_t)4 * sizeof(float) * (size_t)B * h * w;

@@ -1,0 +1,626 @@
+// chain_bwd_fused.cu -- ONE-PASS backward of a narrow BTS decoder stage on sm_100a.
+//
+// Autograd backward of reduction_1x1 (+ local_planar_guidance) (pytorch/bts.py:124-173; SURVEY.md
+// 8(a) row a8) for the chains whose first layer is at most 64 channels wide -- the full-resolution
+// head 32->16->8->1 and the half-resolution stage 64->32->16->8->3, which together move 81 % of the
+// decoder's bytes. x and grad are read once, grad_x is written once, nothing else touches HBM:
+//   recompute the chain (3xTF32 tcgen05, A in TMEM)  ->  upstream gradient (sigmoid head / plane
+//   parameterisation / LPG block reduction)  ->  SIMT tail backward  ->  dgrad through the wide layers
+//   (tcgen05, transposed weight images)  ->  grad_x;   weight gradients accumulate in TMEM for the whole
+//   kernel: every 64-pixel half tile is staged once as K-major SWIZZLE_128B operands with the PIXEL
+//   axis as K, activations and their tf32 remainders stacked along M ([a_hi ; a_lo], M = 128), deltas
+//   stacked along N ([d_hi ; d_lo], N = 64), so ONE MMA per 8 pixels yields hi*hi + hi*lo + lo*hi (+lo*lo).
+//
+// Roles: NWG compute warpgroups (thread = low-res pixel = TMEM lane) + one MMA-issuing warp. Hand-offs
+// are mbarriers only (no CTA-wide barrier inside the tile loop):
+//   ready[g]  128 arrivals  compute -> issuer   "A operand for the next chain MMA is in TMEM"
+//   done[g]   tcgen05.commit issuer -> compute  "chain MMA finished, D is readable"
+//   stg[g]    64 arrivals   compute -> issuer   "a 64-pixel half tile is staged in shared memory"
+//   wfree[g][h] tcgen05.commit issuer -> compute "the weight-gradient MMAs of pair h's half finished"
+// The two warp pairs of a warpgroup share one staging buffer and take turns: pair 1 waits for
+// wfree[g][0], pair 0 for wfree[g][1] (one waiter group per mbarrier, so nobody lags two phases).
+#include "chain_tc.cuh"
+
+namespace bts {
+
+constexpr int kSubRowsA = 128, kSubRowsB = 64;
+constexpr int kSubB = kSubRowsA * 128;                 // byte offset of the delta image in a sub-buffer
+constexpr int kSubBytes = (kSubRowsA + kSubRowsB) * 128;  // 32 pixels x (128 + 64) rows = 24 KB
+constexpr int kALo = 64 * 128, kBLo = 32 * 128;        // byte offset of the remainder rows
+
+struct FusedArgs {
+    TcArgs a;
+    const float *wpack_t;   // transposed weight images (dgrad B operands)
+    float *partials;        // [gridDim.x][total_w]
+    int total_w;
+};
+
+// D[128 x N](TMEM, col d) = A[128 x K](TMEM; hi at a_hi, lo at a_lo) * B[N x K]^T (smem image at w: hi | lo)
+template <int K, int N>
+__device__ __forceinline__ void issue_ts3(uint32_t d, uint32_t a_hi, uint32_t a_lo, const float *w)
+{
+    constexpr uint32_t LBO = 128, SBO = (K / 4) * 128;
+    constexpr uint32_t idesc = idesc_tf32(kTile, N, 0, 0);
+    const uint32_t whi = smem_u32(w), wlo = whi + N * K * 4;
+#pragma unroll
+    for (int k0 = 0; k0 < K; k0 += 8)
+        mma_tf32_ts(d, a_lo + k0, smem_desc(whi + (k0 / 4) * LBO, LBO, SBO), idesc, k0 > 0);
+#pragma unroll
+    for (int k0 = 0; k0 < K; k0 += 8)
+        mma_tf32_ts(d, a_hi + k0, smem_desc(wlo + (k0 / 4) * LBO, LBO, SBO), idesc, 1);
+#pragma unroll
+    for (int k0 = 0; k0 < K; k0 += 8)
+        mma_tf32_ts(d, a_hi + k0, smem_desc(whi + (k0 / 4) * LBO, LBO, SBO), idesc, 1);
+}
+
+// weight-gradient MMAs of one staged half tile (two 32-pixel sub-buffers): D[128 x 64] += A_cat * B_cat^T
+__device__ __forceinline__ void issue_wgrad_half(uint32_t d, uint32_t sub0)
+{
+    constexpr uint32_t idesc = idesc_tf32(128, 64, 0, 0);
+#pragma unroll
+    for (int s = 0; s < 2; ++s)
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks)
+            mma_tf32_ss(d, smem_desc_sw128(sub0 + s * kSubBytes + ks * 32),
+                        smem_desc_sw128(sub0 + s * kSubBytes + kSubB + ks * 32), idesc, 1);
+}
+
+template <class CFG, int MODE, int R, int NWG>
+struct FusedLayout {
+    static constexpr bool FINAL = MODE == 0;
+    static constexpr int LAST = FINAL ? 1 : 3;
+    static constexpr int NW = CFG::NW;
+    static constexpr int K0 = CFG::dim(0);
+    static constexpr int NJOBS = NW;                       // tail round (+ the x round when NW == 2)
+    static constexpr int ACC = NJOBS * 64;                 // TMEM columns of the weight-gradient accumulators
+    static constexpr int WGCOLS = 3 * K0;                  // per warpgroup: x_hi | x_lo / A2 | D
+    static constexpr int PACK = CFG::pack_floats(LAST);
+    static constexpr int IMG = CFG::tail_off();
+    static constexpr int NCMD = NW == 1 ? 4 : 8;
+    static constexpr size_t stage_bytes = (size_t)NWG * 2 * kSubBytes;
+    static constexpr size_t xs_bytes = (size_t)NWG * K0 * kTile * sizeof(float);   // next tile's features (cp.async)
+    static constexpr size_t smem_bytes = 1024 + stage_bytes + xs_bytes + sizeof(float) * (PACK + IMG) + 8 * 5 * NWG + 16;
+    static_assert(NW == 1 || NW == 2, "one or two tensor-core layers");
+    static_assert(CFG::dim(NW) == kTailIn && CFG::dim(NW - 1) == 32, "chain must end ... -> 32 -> 16 -> 8");
+    static_assert(ACC + NWG * WGCOLS <= 512, "TMEM budget");
+};
+
+// ---- the MMA-issuing thread: walks every warpgroup's fixed command list, in order per warpgroup,
+// round-robin across warpgroups.  NW == 1: F0, DG0, WT(h0), WT(h1).
+//                                 NW == 2: F0, F1, DG1, WT(h0), DG0, WT(h1), WX(h0), WX(h1).
+template <class CFG, int MODE, int R, int NWG>
+__device__ __forceinline__ void fused_issuer(const float *sw, const float *swt, uint32_t stage_addr, uint64_t *bars,
+                                             uint32_t tbase, long long ntiles)
+{
+    using L = FusedLayout<CFG, MODE, R, NWG>;
+    constexpr int K0 = L::K0, NW = L::NW;
+    int cmd[NWG], rph[NWG], sph[NWG];
+    long long left[NWG];
+    long long remaining = 0;
+#pragma unroll
+    for (int g = 0; g < NWG; ++g) {
+        const long long first = (long long)blockIdx.x * NWG + g, stride = (long long)gridDim.x * NWG;
+        left[g] = first < ntiles ? (ntiles - first + stride - 1) / stride : 0;
+        remaining += left[g];
+        cmd[g] = 0; rph[g] = 0; sph[g] = 0;
+    }
+    uint32_t idle = 0;
+    while (remaining > 0) {
+        bool progressed = false;
+#pragma unroll
+        for (int g = 0; g < NWG; ++g) {
+            if (left[g] == 0) continue;
+            uint64_t *ready = bars + 5 * g, *done = ready + 1, *stg = ready + 2, *wfree0 = ready + 3, *wfree1 = ready + 4;
+            const int c = cmd[g];
+            const bool is_w = (NW == 1) ? (c >= 2) : (c == 3 || c >= 5);
+            if (!mbar_try_wait(is_w ? stg : ready, is_w ? sph[g] : rph[g])) continue;
+            if (is_w) sph[g] ^= 1; else rph[g] ^= 1;
+            fence_after_sync();
+            progressed = true;
+            const uint32_t wb = tbase + L::ACC + g * L::WGCOLS;       // x_hi
+            const uint32_t xl = wb + K0, dd = wb + 2 * K0;
+            const uint32_t sub0 = stage_addr + g * 2 * kSubBytes;
+            if constexpr (NW == 1) {
+                if (c == 0) { issue_ts3<CFG::K(0), CFG::N(0)>(dd, wb, xl, sw + CFG::w_off(0)); mma_commit(done); }
+                else if (c == 1) { issue_ts3<CFG::N(0), CFG::K(0)>(dd, xl, xl + 16, swt + CFG::w_off(0)); mma_commit(done); }
+                else { issue_wgrad_half(tbase, sub0); mma_commit(c == 2 ? wfree0 : wfree1); }
+            } else {
+                if (c == 0) { issue_ts3<CFG::K(0), CFG::N(0)>(dd, wb, xl, sw + CFG::w_off(0)); mma_commit(done); }
+                else if (c == 1) { issue_ts3<CFG::K(1), CFG::N(1)>(dd, xl, xl + 32, sw + CFG::w_off(1)); mma_commit(done); }
+                else if (c == 2) { issue_ts3<CFG::N(1), CFG::K(1)>(dd, xl + 32, xl + 48, swt + CFG::w_off(1)); mma_commit(done); }
+                else if (c == 4) { issue_ts3<CFG::N(0), CFG::K(0)>(dd, xl, xl + 32, swt + CFG::w_off(0)); mma_commit(done); }
+                else if (c == 3 || c == 5) { issue_wgrad_half(tbase, sub0); mma_commit(c == 3 ? wfree0 : wfree1); }
+                else { issue_wgrad_half(tbase + 64, sub0); mma_commit(c == 6 ? wfree0 : wfree1); }
+            }
+            if (c + 1 == L::NCMD) { cmd[g] = 0; --left[g]; --remaining; }
+            else cmd[g] = c + 1;
+        }
+        if (progressed) idle = 0;
+        else if (++idle > (1u << 26)) __trap();
+    }
+}
+
+// ---- staging helpers. A thread owns pixel `lane` of its warp's 32-pixel sub-buffer; row r of an image
+// sits at r*128 bytes, its 16-byte chunks XOR-swizzled with r%8 (a warp's 32 stores of one row cover
+// all 32 banks). `coff[q]` is the thread's byte offset inside a row with r%8 == q. Callers pass
+// compile-time rows (fully unrolled loops), so coff[] stays in registers.
+struct StageCtx {
+    unsigned char *sub;     // this warp's sub-buffer
+    uint32_t coff[8];
+};
+__device__ __forceinline__ void stage_a(const StageCtx &s, int row, float v)
+{
+    unsigned char *p = s.sub + row * 128 + s.coff[row & 7];
+    *reinterpret_cast<float *>(p) = v;
+    *reinterpret_cast<float *>(p + kALo) = tf32_lo(v);
+}
+__device__ __forceinline__ void stage_b(const StageCtx &s, int row, float v)
+{
+    unsigned char *p = s.sub + kSubB + row * 128 + s.coff[row & 7];
+    *reinterpret_cast<float *>(p) = v;
+    *reinterpret_cast<float *>(p + kBLo) = tf32_lo(v);
+}
+// rows row0 .. row0+31 of the A image <- 32 TMEM columns of this thread's lane (raw fp32 words)
+__device__ __forceinline__ void stage_a_from_tmem32(const StageCtx &s, int row0, uint32_t taddr)
+{
+#pragma unroll
+    for (int c0 = 0; c0 < 32; c0 += 16) {
+        uint32_t r[16];
+        tmem_ld<16>(taddr + c0, r);
+        wait_ld();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) stage_a(s, row0 + c0 + j, __uint_as_float(r[j]));
+    }
+}
+
+// wait until `n` completions of `bar` have been observed by this thread
+__device__ __forceinline__ void wait_count(uint64_t *bar, uint32_t &seen, uint32_t n)
+{
+    while (seen < n) {
+        mbar_wait(bar, seen & 1);
+        ++seen;
+    }
+}
+
+// MODE 0: sigmoid head (grad [B][1][hw]); 1: plane parameters (grad [B][4][hw]); 2: fused LPG (grad_depth, upratio R)
+template <class CFG, int MODE, int R, int NWG>
+__global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(const __grid_constant__ FusedArgs fa)
+{
+    using L = FusedLayout<CFG, MODE, R, NWG>;
+    constexpr int LAST = L::LAST, NW = L::NW, K0 = L::K0;
+    constexpr int NT = NWG * kTile + 32;
+    constexpr int NG = MODE == 0 ? 1 : MODE == 1 ? 4 : (R <= 2 ? R * R : 1);   // prefetched upstream-gradient words
+    constexpr bool GPRE = MODE != 2 || R <= 2;
+    const TcArgs &a = fa.a;
+
+    extern __shared__ unsigned char smem_raw[];
+    // round the staging area up to the 1024-byte alignment of a SWIZZLE_128B atom (offset arithmetic on
+    // the shared array keeps the address space known to the compiler)
+    unsigned char *stage = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    float *xs_all = reinterpret_cast<float *>(stage + L::stage_bytes);
+    float *sw = reinterpret_cast<float *>(stage + L::stage_bytes + L::xs_bytes);
+    float *swt = sw + L::PACK;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(swt + L::IMG);
+    uint32_t *slot = reinterpret_cast<uint32_t *>(bars + 5 * NWG);
+
+    const int tid = threadIdx.x;
+    for (int i = tid * 4; i < L::PACK; i += NT * 4)
+        *reinterpret_cast<float4 *>(sw + i) = __ldg(reinterpret_cast<const float4 *>(a.wpack + i));
+    for (int i = tid * 4; i < L::IMG; i += NT * 4)
+        *reinterpret_cast<float4 *>(swt + i) = __ldg(reinterpret_cast<const float4 *>(fa.wpack_t + i));
+    fence_smem_to_async();
+    if (tid < 32) tmem_alloc(slot, 512);
+    if (tid == 0) {
+        for (int g = 0; g < NWG; ++g) {
+            mbar_init(bars + 5 * g, kTile);
+            mbar_init(bars + 5 * g + 1, 1);
+            mbar_init(bars + 5 * g + 2, kTile / 2);
+            mbar_init(bars + 5 * g + 3, 1);
+            mbar_init(bars + 5 * g + 4, 1);
+        }
+        fence_mbar_init();
+    }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tbase = *slot;
+    if (tid < kTile) {   // weight-gradient accumulators start at zero; every MMA into them accumulates
+        uint32_t z[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) z[j] = 0u;
+#pragma unroll
+        for (int c0 = 0; c0 < L::ACC; c0 += 32) tmem_st<32>(tbase + ((uint32_t)((tid >> 5) * 32) << 16) + c0, z);
+        wait_st();
+    }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+
+    const long long ntiles = (a.npx + kTile - 1) / kTile;
+    const long long stride = (long long)gridDim.x * NWG;
+
+    if (tid >= NWG * kTile) {
+        if (tid == NWG * kTile) fused_issuer<CFG, MODE, R, NWG>(sw, swt, smem_u32(stage), bars, tbase, ntiles);
+        __syncwarp();
+    } else {
+        const int g = tid / kTile, t = tid % kTile, lane = tid & 31, wj = t >> 5, half = wj >> 1;
+        uint64_t *ready = bars + 5 * g, *done = ready + 1, *stg = ready + 2;
+        uint64_t *wfree = ready + 3 + (half ^ 1);                 // the OTHER pair's completions free the buffer for me
+        const uint32_t xh = tbase + L::ACC + g * L::WGCOLS + ((uint32_t)(wj * 32) << 16);
+        const uint32_t xl = xh + K0, dd = xh + 2 * K0;
+        StageCtx sc;
+        sc.sub = stage + (size_t)(g * 2 + (wj & 1)) * kSubBytes;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) sc.coff[q] = (uint32_t)((((lane >> 2) ^ q) << 4) | ((lane & 3) << 2));
+        const float *tw = sw + CFG::tail_off();
+        const float *w5 = tw + kTailMid * kTailIn;
+        uint32_t done_seen = 0, wseen = 0, nstage = 0;
+        auto done_wait = [&]() {
+            mbar_wait(done, done_seen & 1);
+            ++done_seen;
+            fence_after_sync();
+        };
+
+        float *xs = xs_all + (size_t)g * K0 * kTile + t;          // [channel][pixel]: this thread's column
+        float gn[NG];
+        auto prefetch = [&](long long tl) {
+            const long long gp = tl * kTile + t;
+            const bool ok = tl < ntiles && gp < a.npx;
+            const int b = ok ? (int)(gp / a.hw) : 0;
+            const int p = ok ? (int)(gp - (long long)b * a.hw) : 0;
+            const float *xp = a.x + (size_t)b * K0 * a.hw + p;
+            const uint32_t dst = smem_u32(xs);
+#pragma unroll
+            for (int c = 0; c < K0; ++c) cp_async4(dst + c * kTile * 4, xp + (size_t)c * a.hw, ok);
+            cp_async_commit();
+#pragma unroll
+            for (int j = 0; j < NG; ++j) gn[j] = 0.f;
+            if (ok && GPRE) {
+                if constexpr (MODE == 0) {
+                    gn[0] = __ldcs(a.grad + gp);
+                } else if constexpr (MODE == 1) {
+                    const float *gq = a.grad + (size_t)b * 4 * a.hw + p;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) gn[j] = __ldcs(gq + (size_t)j * a.hw);
+                } else if constexpr (R == 1) {
+                    gn[0] = __ldcs(a.grad + gp);
+                } else if constexpr (R == 2) {
+                    const int i = p / a.w, j = p - i * a.w;
+                    const int Wd = a.w * 2;
+                    const float *g0 = a.grad + ((size_t)b * a.h + i) * 2 * (size_t)Wd + (size_t)j * 2;
+                    const float2 r0 = __ldcs(reinterpret_cast<const float2 *>(g0));
+                    const float2 r1 = __ldcs(reinterpret_cast<const float2 *>(g0 + Wd));
+                    gn[0] = r0.x; gn[1] = r0.y; gn[2] = r1.x; gn[3] = r1.y;
+                }
+            }
+        };
+
+        long long tile = (long long)blockIdx.x * NWG + g;
+        prefetch(tile);
+        for (; tile < ntiles; tile += stride) {
+            const long long gp = tile * kTile + t;
+            const bool valid = gp < a.npx;
+            const int b = valid ? (int)(gp / a.hw) : 0;
+            const int p = valid ? (int)(gp - (long long)b * a.hw) : 0;
+            // ---- x -> (hi, lo) -> TMEM A operand of layer 0; then the next tile's loads take off
+            cp_async_wait_all();
+#pragma unroll
+            for (int c0 = 0; c0 < K0; c0 += 16) {
+                uint32_t hi[16], lo[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const float v = xs[(c0 + j) * kTile];
+                    hi[j] = __float_as_uint(v);
+                    lo[j] = __float_as_uint(tf32_lo(v));
+                }
+                tmem_st<16>(xh + c0, hi);
+                tmem_st<16>(xl + c0, lo);
+            }
+            float gcur[NG];
+#pragma unroll
+            for (int j = 0; j < NG; ++j) gcur[j] = gn[j];
+            wait_st();
+            fence_before_sync();
+            mbar_arrive(ready);                                   // F0
+            prefetch(tile + stride);
+            done_wait();
+            float a1[NW == 2 ? 32 : 1];
+            if constexpr (NW == 2) {                              // a1 = ELU(D) -> A operand of layer 1
+#pragma unroll
+                for (int n0 = 0; n0 < 32; n0 += 16) {
+                    uint32_t r[16], lo[16];
+                    tmem_ld<16>(dd + n0, r);
+                    wait_ld();
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        a1[n0 + j] = elu_fast(__uint_as_float(r[j]));
+                        r[j] = __float_as_uint(a1[n0 + j]);
+                        lo[j] = __float_as_uint(tf32_lo(a1[n0 + j]));
+                    }
+                    tmem_st<16>(xl + n0, r);
+                    tmem_st<16>(xl + 32 + n0, lo);
+                }
+                wait_st();
+                fence_before_sync();
+                mbar_arrive(ready);                               // F1
+                done_wait();
+            }
+            float a16[kTailIn], a8[kTailMid], z[LAST];
+            {
+                uint32_t r[16];
+                tmem_ld<16>(dd, r);
+                wait_ld();
+#pragma unroll
+                for (int j = 0; j < 16; ++j) a16[j] = elu_fast(__uint_as_float(r[j]));
+            }
+            tail_forward<LAST>(tw, a16, a8, z);
+            // ---- upstream gradient -> dz
+            float dz[3] = {0.f, 0.f, 0.f};
+            if constexpr (MODE == 0) {
+                const float s = sigmoidf(z[0]);
+                dz[0] = gcur[0] * s * (1.f - s);
+            } else {
+                const PlaneFwd pl = plane_from_logits(z[0], z[1], z[2], a.max_depth);
+                if (valid) {
+                    float gg[4];
+                    if constexpr (MODE == 1) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) gg[j] = gcur[j];
+                    } else if constexpr (R <= 2) {
+                        LpgAcc acc{0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                        for (int pp = 0; pp < R; ++pp) {
+                            const float v = lpg_offset(pp, R);
+                            const float n2v = __fmul_rn(pl.n2, v);
+#pragma unroll
+                            for (int k = 0; k < R; ++k) {
+                                const float u = lpg_offset(k, R);
+                                lpg_bwd_accum(acc, gcur[pp * R + k], __fmul_rn(pl.n1, u), n2v, pl.n3, u, v, a.eps);
+                            }
+                        }
+                        gg[0] = -pl.n4 * acc.tu; gg[1] = -pl.n4 * acc.tv; gg[2] = -pl.n4 * acc.t; gg[3] = acc.s4;
+                    } else {
+                        lpg_block_grad<R>(a, pl, gp, gg);
+                    }
+                    plane_bwd(pl, gg[0], gg[1], gg[2], gg[3], a.max_depth, dz);
+                }
+            }
+            // ---- tail backward: d8 = (W5^T dz) * ELU'(a8);  dl16 = (W4^T d8) * ELU'(a16)
+            float d8[kTailMid], dl16[kTailIn];
+#pragma unroll
+            for (int o = 0; o < kTailMid; ++o) {
+                float s = 0.f;
+#pragma unroll
+                for (int j = 0; j < LAST; ++j) s = fmaf(w5[j * kTailMid + o], dz[j], s);
+                d8[o] = s * elu_grad_from_out(a8[o]);
+            }
+#pragma unroll
+            for (int c = 0; c < kTailIn; ++c) dl16[c] = 0.f;
+#pragma unroll
+            for (int o = 0; o < kTailMid; ++o) {
+#pragma unroll
+                for (int c = 0; c < kTailIn; c += 4) {
+                    const float4 w4 = *reinterpret_cast<const float4 *>(tw + o * kTailIn + c);
+                    dl16[c] = fmaf(w4.x, d8[o], dl16[c]); dl16[c + 1] = fmaf(w4.y, d8[o], dl16[c + 1]);
+                    dl16[c + 2] = fmaf(w4.z, d8[o], dl16[c + 2]); dl16[c + 3] = fmaf(w4.w, d8[o], dl16[c + 3]);
+                }
+            }
+            {
+                uint32_t hi[16], lo[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    dl16[j] *= elu_grad_from_out(a16[j]);
+                    hi[j] = __float_as_uint(dl16[j]);
+                    lo[j] = __float_as_uint(tf32_lo(dl16[j]));
+                }
+                constexpr int OFF = NW == 1 ? 0 : 32;
+                tmem_st<16>(xl + OFF, hi);
+                tmem_st<16>(xl + OFF + 16, lo);
+            }
+            wait_st();
+            fence_before_sync();
+            mbar_arrive(ready);                                   // DG(NW-1)
+
+            auto stage_tail = [&]() {
+                wait_count(wfree, wseen, nstage + half);
+                ++nstage;
+                if constexpr (NW == 2) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) stage_a(sc, j, a1[j]);
+                }
+#pragma unroll
+                for (int j = 0; j < kTailIn; ++j) stage_a(sc, 32 + j, a16[j]);
+#pragma unroll
+                for (int j = 0; j < kTailMid; ++j) stage_a(sc, 48 + j, a8[j]);
+#pragma unroll
+                for (int j = 0; j < kTailIn; ++j) stage_b(sc, j, dl16[j]);
+#pragma unroll
+                for (int j = 0; j < kTailMid; ++j) stage_b(sc, 16 + j, d8[j]);
+#pragma unroll
+                for (int j = 0; j < LAST; ++j) stage_b(sc, 24 + j, dz[j]);
+                if constexpr (NW == 1) stage_a_from_tmem32(sc, 0, xh);
+                fence_smem_to_async();
+                mbar_arrive(stg);
+            };
+            auto gradx_epilogue = [&]() {
+                done_wait();
+                float *gx = a.grad_x + (size_t)b * K0 * a.hw + p;
+#pragma unroll
+                for (int n0 = 0; n0 < K0; n0 += 16) {
+                    uint32_t r[16];
+                    tmem_ld<16>(dd + n0, r);
+                    wait_ld();
+                    if (valid && a.grad_x != nullptr) {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) gx[(size_t)(n0 + j) * a.hw] = __uint_as_float(r[j]);
+                    }
+                }
+            };
+            if constexpr (NW == 1) {
+#pragma unroll 1
+                for (int ph = 0; ph < 2; ++ph) {                  // pair 0 stages first, pair 1 second
+                    if (ph == half) stage_tail();
+                    else gradx_epilogue();
+                }
+            } else {
+                float d1[32];
+                auto dg1_epilogue = [&]() {                       // delta_1 = (delta_16 W1) * ELU'(a1) -> A operand of DG0
+                    done_wait();
+#pragma unroll
+                    for (int n0 = 0; n0 < 32; n0 += 16) {
+                        uint32_t r[16], lo[16];
+                        tmem_ld<16>(dd + n0, r);
+                        wait_ld();
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            d1[n0 + j] = __uint_as_float(r[j]) * elu_grad_from_out(a1[n0 + j]);
+                            r[j] = __float_as_uint(d1[n0 + j]);
+                            lo[j] = __float_as_uint(tf32_lo(d1[n0 + j]));
+                        }
+                        tmem_st<16>(xl + n0, r);
+                        tmem_st<16>(xl + 32 + n0, lo);
+                    }
+                    wait_st();
+                    fence_before_sync();
+                    mbar_arrive(ready);                           // DG0
+                };
+                auto stage_x = [&]() {
+                    wait_count(wfree, wseen, nstage + half);
+                    ++nstage;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) stage_b(sc, j, d1[j]);
+                    stage_a_from_tmem32(sc, 0, xh);
+                    stage_a_from_tmem32(sc, 32, xh + 32);
+                    fence_smem_to_async();
+                    mbar_arrive(stg);
+                };
+#pragma unroll 1
+                for (int ph = 0; ph < 2; ++ph) {
+                    if (ph == half) stage_tail();
+                    else dg1_epilogue();
+                }
+#pragma unroll 1
+                for (int ph = 0; ph < 2; ++ph) {
+                    if (ph == half) stage_x();
+                    else gradx_epilogue();
+                }
+            }
+        }
+        // every weight-gradient MMA of this warpgroup has completed before the accumulators are read
+        wait_count(wfree, wseen, nstage);
+    }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+
+    // ---- accumulators -> this CTA's partial weight gradients. Row m of a job sits in TMEM lane m; the hi
+    // rows (0..63) and the remainder rows (64..127) of the same channel are summed, and so are the hi
+    // and remainder column halves.
+    constexpr int SP = 33;
+    float *scratch = reinterpret_cast<float *>(stage);            // [NJOBS][128][SP], staging is idle now
+    if (tid < kTile) {
+#pragma unroll
+        for (int job = 0; job < L::NJOBS; ++job) {
+            uint32_t r0[32], r1[32];
+            const uint32_t addr = tbase + ((uint32_t)((tid >> 5) * 32) << 16) + job * 64;
+            tmem_ld<32>(addr, r0);
+            tmem_ld<32>(addr + 32, r1);
+            wait_ld();
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                scratch[(job * kTile + tid) * SP + j] = __uint_as_float(r0[j]) + __uint_as_float(r1[j]);
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (fa.partials != nullptr) {
+        float *part = fa.partials + (size_t)blockIdx.x * fa.total_w;
+        // layer l of the chain: (job, first row, first column, K = inputs, N = outputs)
+        constexpr int NL = NW + 2;
+        int off = 0;
+#pragma unroll
+        for (int l = 0; l < NL; ++l) {
+            const int t_l = l - (NW - 1);                         // 0: 32->16 layer, 1: 16->8, 2: 8->LAST; <0: x round
+            const int job = t_l < 0 ? 1 : 0;
+            const int row0 = t_l <= 0 ? 0 : (t_l == 1 ? 32 : 48);
+            const int col0 = t_l <= 0 ? 0 : (t_l == 1 ? 16 : 24);
+            const int K = t_l < 0 ? K0 : (t_l == 0 ? 32 : (t_l == 1 ? kTailIn : kTailMid));
+            const int N = t_l < 0 ? 32 : (t_l == 0 ? kTailIn : (t_l == 1 ? kTailMid : LAST));
+            for (int e = tid; e < K * N; e += NT) {
+                const int o = e / K, c = e - o * K;
+                const float *s = scratch + (job * kTile + row0 + c) * SP + col0 + o;
+                part[off + e] = s[0] + s[64 * SP];
+            }
+            off += K * N;
+        }
+    }
+    __syncthreads();
+    if (tid < 32) tmem_dealloc(tbase, 512);
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+int launch_wreduce(const ChainParams &cp, const float *partials, int nparts, int total_w, cudaStream_t s);
+size_t tc_pack_bytes();
+
+template <class CFG, int MODE, int R, int NWG>
+static int launch_fused_cfg(const ChainParams &cp, const TcArgs &a, char *ws, int sms, cudaStream_t s)
+{
+    using L = FusedLayout<CFG, MODE, R, NWG>;
+    float *wpack = reinterpret_cast<float *>(ws);
+    float *wpack_t = reinterpret_cast<float *>(ws + tc_pack_bytes());
+    float *partials = reinterpret_cast<float *>(ws + 2 * tc_pack_bytes());
+    int total_w = 0;
+    for (int l = 0; l < cp.n_layers; ++l) total_w += cp.dims[l] * cp.dims[l + 1];
+
+    tc_pack_weights_kernel<CFG><<<16, 256, 0, s>>>(cp, wpack, L::LAST);
+    if (int e = check_launch("tc_pack_weights")) return e;
+    tc_pack_weights_t_kernel<CFG><<<16, 256, 0, s>>>(cp, wpack_t);
+    if (int e = check_launch("tc_pack_weights_t")) return e;
+
+    FusedArgs fa;
+    fa.a = a;
+    fa.a.wpack = wpack;
+    fa.wpack_t = wpack_t;
+    fa.partials = cp.gW[0] != nullptr ? partials : nullptr;
+    fa.total_w = total_w;
+    auto kern = chain_bwd_fused_kernel<CFG, MODE, R, NWG>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::smem_bytes);
+    if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    const long long ntiles = (a.npx + kTile - 1) / kTile;
+    long long grid = (ntiles + NWG - 1) / NWG;
+    if (grid > sms) grid = sms;
+    kern<<<(unsigned)grid, NWG * kTile + 32, L::smem_bytes, s>>>(fa);
+    if (int e2 = check_launch("chain_bwd_fused")) return e2;
+    if (cp.gW[0] != nullptr) {
+        if (int e2 = launch_wreduce(cp, partials, (int)grid, total_w, s)) return e2;
+    }
+    return BTS_OK;
+}
+
+template <class CFG, int NWG>
+static int dispatch_fused(const ChainParams &cp, const TcArgs &a, int mode, int r, char *ws, int sms, cudaStream_t s)
+{
+    if (mode == 0) return launch_fused_cfg<CFG, 0, 1, NWG>(cp, a, ws, sms, s);
+    if (mode == 1) return launch_fused_cfg<CFG, 1, 1, NWG>(cp, a, ws, sms, s);
+    switch (r) {
+    case 8: return launch_fused_cfg<CFG, 2, 8, NWG>(cp, a, ws, sms, s);
+    case 4: return launch_fused_cfg<CFG, 2, 4, NWG>(cp, a, ws, sms, s);
+    case 2: return launch_fused_cfg<CFG, 2, 2, NWG>(cp, a, ws, sms, s);
+    default: return launch_fused_cfg<CFG, 2, 1, NWG>(cp, a, ws, sms, s);
+    }
+}
+
+bool fused_bwd_supported(const ChainParams &cp) { return cfg_matches<Cfg32_16>(cp) || cfg_matches<Cfg64_32>(cp); }
+
+// mode: 0 head (grad [B,1,hw]), 1 plane parameters (grad [B,4,hw]), 2 fused LPG (grad_depth, upratio r)
+int launch_chain_bwd_fused(const ChainParams &cp, const TcArgs &a, int mode, int r, void *ws, int sms, cudaStream_t s)
+{
+    char *w = static_cast<char *>(ws);
+    if (cfg_matches<Cfg32_16>(cp)) return dispatch_fused<Cfg32_16, 3>(cp, a, mode, r, w, sms, s);
+    if (cfg_matches<Cfg64_32>(cp)) return dispatch_fused<Cfg64_32, 2>(cp, a, mode, r, w, sms, s);
+    return set_error(BTS_ERR_UNSUPPORTED, "chain not covered by the fused backward");
+}
+
+}  // namespace bts

@@ -215,6 +215,44 @@ __device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, f
     return key;
 }
 
+// ---- upstream gradient of one low-res pixel in fused mode: reduce grad_depth over its R x R block
+template <int R>
+__device__ __forceinline__ void lpg_block_grad(const TcArgs &a, const PlaneFwd &pl, long long gp, float g[4])
+{
+    const int b = (int)(gp / a.hw);
+    const int rem = (int)(gp - (long long)b * a.hw);
+    const int i = rem / a.w, j = rem - i * a.w;
+    const int Wd = a.w * R;
+    const float *gp0 = a.grad + ((size_t)b * a.h + i) * R * (size_t)Wd + (size_t)j * R;
+    LpgAcc acc{0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int p = 0; p < R; ++p) {
+        float gv[R];
+        const float *row = gp0 + (size_t)p * Wd;
+        if constexpr (R % 4 == 0) {
+#pragma unroll
+            for (int k = 0; k < R; k += 4) {
+                const float4 t4 = __ldcs(reinterpret_cast<const float4 *>(row + k));
+                gv[k] = t4.x; gv[k + 1] = t4.y; gv[k + 2] = t4.z; gv[k + 3] = t4.w;
+            }
+        } else if constexpr (R == 2) {
+            const float2 t2 = __ldcs(reinterpret_cast<const float2 *>(row));
+            gv[0] = t2.x; gv[1] = t2.y;
+        } else {
+#pragma unroll
+            for (int k = 0; k < R; ++k) gv[k] = __ldcs(row + k);
+        }
+        const float v = lpg_offset(p, R);
+        const float n2v = __fmul_rn(pl.n2, v);
+#pragma unroll
+        for (int k = 0; k < R; ++k) {
+            const float u = lpg_offset(k, R);
+            lpg_bwd_accum(acc, gv[k], __fmul_rn(pl.n1, u), n2v, pl.n3, u, v, a.eps);
+        }
+    }
+    g[0] = -pl.n4 * acc.tu; g[1] = -pl.n4 * acc.tv; g[2] = -pl.n4 * acc.t; g[3] = acc.s4;
+}
+
 // ---- the 16 -> 8 -> (3|1) tail on registers; weights broadcast from shared memory
 template <int LAST>
 __device__ __forceinline__ void tail_forward(const float *tw, const float (&a16)[kTailIn], float (&a8)[kTailMid],
@@ -265,6 +303,25 @@ __global__ void tc_pack_weights_kernel(ChainParams cp, float *wpack, int last)
     float *tw = wpack + CFG::tail_off();
     for (int e = tid; e < kTailMid * kTailIn; e += nth) tw[e] = __ldg(cp.W[CFG::NW] + e);
     for (int e = tid; e < last * kTailMid; e += nth) tw[kTailMid * kTailIn + e] = __ldg(cp.W[CFG::NW + 1] + e);
+}
+
+// transposed images: layer l, rows = input channel c (N' = K_l), K' = output channel o (N_l)
+template <class CFG>
+__global__ void tc_pack_weights_t_kernel(ChainParams cp, float *wpack_t)
+{
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+#pragma unroll
+    for (int l = 0; l < CFG::NW; ++l) {
+        const int K = CFG::K(l), N = CFG::N(l);
+        float *hi = wpack_t + CFG::w_off(l), *lo = hi + N * K;
+        for (int e = tid; e < N * K; e += nth) {
+            const int o = e / K, c = e - o * K;
+            const float v = __ldg(cp.W[l] + e);
+            const uint32_t off = kmajor_off_floats(c, o, N);
+            hi[off] = v;
+            lo[off] = tc::tf32_lo(v);
+        }
+    }
 }
 
 // chain signatures served by the tensor-core path (bts_size = 512 and 256 decoders)

@@ -61,44 +61,6 @@ __device__ __forceinline__ void tc_epilogue_to_a_spill(uint32_t lane_addr, float
     }
 }
 
-// upstream gradient of one low-res pixel in fused mode: reduce grad_depth over its R x R block
-template <int R>
-__device__ __forceinline__ void lpg_block_grad(const TcArgs &a, const PlaneFwd &pl, long long gp, float g[4])
-{
-    const int b = (int)(gp / a.hw);
-    const int rem = (int)(gp - (long long)b * a.hw);
-    const int i = rem / a.w, j = rem - i * a.w;
-    const int Wd = a.w * R;
-    const float *gp0 = a.grad + ((size_t)b * a.h + i) * R * (size_t)Wd + (size_t)j * R;
-    LpgAcc acc{0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-    for (int p = 0; p < R; ++p) {
-        float gv[R];
-        const float *row = gp0 + (size_t)p * Wd;
-        if constexpr (R % 4 == 0) {
-#pragma unroll
-            for (int k = 0; k < R; k += 4) {
-                const float4 t4 = __ldcs(reinterpret_cast<const float4 *>(row + k));
-                gv[k] = t4.x; gv[k + 1] = t4.y; gv[k + 2] = t4.z; gv[k + 3] = t4.w;
-            }
-        } else if constexpr (R == 2) {
-            const float2 t2 = __ldcs(reinterpret_cast<const float2 *>(row));
-            gv[0] = t2.x; gv[1] = t2.y;
-        } else {
-#pragma unroll
-            for (int k = 0; k < R; ++k) gv[k] = __ldcs(row + k);
-        }
-        const float v = lpg_offset(p, R);
-        const float n2v = __fmul_rn(pl.n2, v);
-#pragma unroll
-        for (int k = 0; k < R; ++k) {
-            const float u = lpg_offset(k, R);
-            lpg_bwd_accum(acc, gv[k], __fmul_rn(pl.n1, u), n2v, pl.n3, u, v, a.eps);
-        }
-    }
-    g[0] = -pl.n4 * acc.tu; g[1] = -pl.n4 * acc.tv; g[2] = -pl.n4 * acc.t; g[3] = acc.s4;
-}
-
 // MODE 0: sigmoid head (grad [B][1][hw]); 1: plane parameters (grad [B][4][hw]); 2: fused LPG (grad_depth)
 template <class CFG, int MODE, int R, int NWG>
 __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_bwd1_kernel(BwdArgs ba)
@@ -388,25 +350,6 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_dgrad_kernel(BwdArgs 
     if (tid < 32) tmem_dealloc(tbase, 512);
 }
 
-// transposed images: layer l, rows = input channel c (N' = K_l), K' = output channel o (N_l)
-template <class CFG>
-__global__ void tc_pack_weights_t_kernel(ChainParams cp, float *wpack_t)
-{
-    const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
-#pragma unroll
-    for (int l = 0; l < CFG::NW; ++l) {
-        const int K = CFG::K(l), N = CFG::N(l);
-        float *hi = wpack_t + CFG::w_off(l), *lo = hi + N * K;
-        for (int e = tid; e < N * K; e += nth) {
-            const int o = e / K, c = e - o * K;
-            const float v = __ldg(cp.W[l] + e);
-            const uint32_t off = kmajor_off_floats(c, o, N);
-            hi[off] = v;
-            lo[off] = tc::tf32_lo(v);
-        }
-    }
-}
-
 // ------------------------------------------------------------------------------------------------
 // K3: weight gradients. For a tile of 64 pixels the activations (A operand) and deltas (B operand)
 // of a "job" are staged as K-major images with the PIXEL axis as K (thread = pixel, chunk stride
@@ -591,6 +534,12 @@ __global__ void chain_tc_wreduce_kernel(ChainParams cp, const float *partials, i
         }
         off += n;
     }
+}
+
+int launch_wreduce(const ChainParams &cp, const float *partials, int nparts, int total_w, cudaStream_t s)
+{
+    chain_tc_wreduce_kernel<<<(total_w + 255) / 256, 256, 0, s>>>(cp, partials, nparts, total_w);
+    return check_launch("chain_tc_wreduce");
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -116,6 +116,10 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity)
                  : "memory");
     return ok != 0;
 }
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 // Bounded wait: a descriptor mistake must surface as a trapped launch, never as a hung GPU.
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
 {
@@ -139,6 +143,15 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes
 {
     return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) |
            ((uint64_t)(sbo_bytes >> 4) << 32) | (1ull << 46);
+}
+// Shared-memory matrix descriptor, SWIZZLE_128B, K-major: rows of 128 bytes (32 fp32 K-elements), the
+// 16-byte chunk index XOR-ed with (row % 8); 8-row atoms (1024 B, 1024-B aligned) follow each other
+// every `sbo_bytes`. A K-step of 8 elements inside the row advances the start address by 32 bytes.
+// (verified on B200 by tests/cuda/probe_sw128.cu; MN-major kind::tf32 operands return zeros there)
+__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr, uint32_t sbo_bytes = 1024)
+{
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) |
+           (1ull << 46) | (2ull << 61);
 }
 // Instruction descriptor for kind::tf32, fp32 accumulate. *_mn = 1 selects an MN-major operand.
 __host__ __device__ constexpr uint32_t idesc_tf32(int M, int N, int a_mn, int b_mn)
@@ -164,6 +177,14 @@ __device__ __forceinline__ void mma_tf32_ss(uint32_t d_tmem, uint64_t a_desc, ui
                  "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
                  : "memory");
 }
+
+// 4-byte asynchronous global -> shared copy (LDGSTS); `ok == false` writes a zero instead of reading
+__device__ __forceinline__ void cp_async4(uint32_t dst_smem, const void *src, bool ok)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst_smem), "l"(src), "r"(ok ? 4 : 0) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 // Sub-block barrier: `nthreads` threads (a multiple of 32) meet on hardware barrier `id` (1..15).
 __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads)

@@ -53,7 +53,8 @@ enum {
 enum {
     BTS_PATH_GENERIC = 0,      /* any dims: one thread per low-res pixel                          */
     BTS_PATH_SIMT_REG = 1,     /* narrow chains (<= 32 input channels): register-resident SIMT    */
-    BTS_PATH_TCGEN05 = 2       /* wide chains: 3xTF32 tcgen05 MMAs for the >= 64-channel layers   */
+    BTS_PATH_TCGEN05 = 2,      /* wide chains: 3xTF32 tcgen05 MMAs for the >= 64-channel layers   */
+    BTS_PATH_TCGEN05_SPLIT = 3 /* force only: tcgen05 path with the multi-kernel (workspace) backward  */
 };
 
 BTS_API int bts_abi_version(void);
