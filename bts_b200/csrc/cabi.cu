@@ -41,7 +41,7 @@ int launch_chain_bwd_fused(const ChainParams &, const TcArgs &, int mode, int r,
 bool fused_bwd_supported(const ChainParams &);
 bool tc_supported(const ChainParams &);
 size_t tc_pack_bytes();
-size_t tc_bwd_workspace_bytes(const ChainParams &, long long npx, int sms);
+size_t tc_bwd_workspace_bytes(const ChainParams &, int B, int hw, int sms);
 
 static int sm_count()
 {
@@ -61,10 +61,10 @@ static bool use_tc(const ChainParams &cp, const void *ws, size_t ws_bytes, const
     return depth == nullptr || aligned16(depth);
 }
 
-static bool use_tc_bwd(const ChainParams &cp, const void *ws, size_t ws_bytes, long long npx, const void *grad16)
+static bool use_tc_bwd(const ChainParams &cp, const void *ws, size_t ws_bytes, int B, int hw, const void *grad16)
 {
     if (!use_tc(cp, ws, ws_bytes, grad16)) return false;
-    return ws_bytes >= 2 * tc_pack_bytes() + tc_bwd_workspace_bytes(cp, npx, sm_count());
+    return ws_bytes >= 2 * tc_pack_bytes() + tc_bwd_workspace_bytes(cp, B, hw, sm_count());
 }
 
 static TcArgs make_tc_args(const float *x, int B, int h, int w, float max_depth, float eps)
@@ -167,7 +167,7 @@ size_t bts_workspace_bytes(const int *dims, int n_layers, int B, int h, int w, i
     for (int l = 0; l < BTS_MAX_LAYERS; ++l) fake[l] = reinterpret_cast<const float *>(16);
     const int last = (dims && n_layers >= 1 && n_layers <= BTS_MAX_LAYERS) ? dims[n_layers] : 0;
     if (last && fill_chain(cp, fake, nullptr, dims, n_layers, last == 1, 1.f) == BTS_OK && tc_supported(cp)) {
-        const size_t t = tc_bwd_workspace_bytes(cp, (long long)npx, sm_count());
+        const size_t t = tc_bwd_workspace_bytes(cp, B, h * w, sm_count());
         if (t > tail) tail = t;
     }
     return 2 * tc_pack_bytes() + tail;
@@ -198,7 +198,7 @@ int bts_reduc_bwd(const float *x, const float *const *W, const int *dims, int n_
     if (int e = check_shape(B, h, w)) return e;
     if ((long long)B * h * w == 0) return BTS_OK;
     if (!x || !grad_out) return set_error(BTS_ERR_BAD_ARG, "x / grad_out is NULL");
-    if (use_tc_bwd(cp, ws, ws_bytes, (long long)B * h * w, nullptr)) {
+    if (use_tc_bwd(cp, ws, ws_bytes, B, h * w, nullptr)) {
         TcArgs a = make_tc_args(x, B, h, w, max_depth, 0.f);
         a.grad = grad_out; a.grad_x = grad_x;
         if (fused_bwd_supported(cp) && g_force_path != BTS_PATH_TCGEN05_SPLIT)
@@ -244,7 +244,7 @@ int bts_reduc_lpg_bwd(const float *grad_depth, const float *x, const float *cons
     if (r < 1) return set_error(BTS_ERR_BAD_ARG, "upratio r=%d must be >= 1", r);
     if ((long long)B * h * w == 0) return BTS_OK;
     if (!x || !grad_depth) return set_error(BTS_ERR_BAD_ARG, "x / grad_depth is NULL");
-    if ((r == 1 || r == 2 || r == 4 || r == 8) && use_tc_bwd(cp, ws, ws_bytes, (long long)B * h * w, grad_depth)) {
+    if ((r == 1 || r == 2 || r == 4 || r == 8) && use_tc_bwd(cp, ws, ws_bytes, B, h * w, grad_depth)) {
         TcArgs a = make_tc_args(x, B, h, w, max_depth, eps);
         a.grad = grad_depth; a.grad_x = grad_x;
         if (fused_bwd_supported(cp) && g_force_path != BTS_PATH_TCGEN05_SPLIT)

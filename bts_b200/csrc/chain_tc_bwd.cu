@@ -23,6 +23,7 @@ struct BwdArgs {
     float *act;            // [RA][npx_pad]   a_1 .. a_NW (=a16), a8
     float *del;            // [RD][npx_pad]   delta_1 .. delta_NW (=d16), d8, dz
     long long npx_pad;
+    int hw_pad;            // pixels per image on the workspace's pixel axis (hw, or hw rounded up to 32)
 };
 
 template <class CFG>
@@ -102,10 +103,12 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_bwd1_kernel(BwdArgs b
 
     const long long ntiles = npp / kTile;
     for (long long tile = (long long)blockIdx.x * NWG + wg; tile < ntiles; tile += (long long)gridDim.x * NWG) {
-        const long long gp = tile * kTile + t;
-        const bool valid = gp < a.npx;
-        const int b = valid ? (int)(gp / a.hw) : 0;
-        const int p = valid ? (int)(gp - (long long)b * a.hw) : 0;
+        const long long gp = tile * kTile + t;                    // index on the (per image padded) workspace pixel axis
+        const int bb = (int)(gp / ba.hw_pad), pp = (int)(gp - (long long)bb * ba.hw_pad);
+        const bool valid = bb < a.B && pp < a.hw;
+        const int b = valid ? bb : 0;
+        const int p = valid ? pp : 0;
+        const long long gpt = (long long)b * a.hw + p;           // index in the tensors
         const float *xp = a.x + (size_t)b * D0 * a.hw + p;
         float *act_gp = ba.act + gp;
         float *del_gp = ba.del + gp;
@@ -154,7 +157,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_bwd1_kernel(BwdArgs b
         float dz[3] = {0.f, 0.f, 0.f};
         if constexpr (MODE == 0) {
             const float s = sigmoidf(z[0]);
-            const float g = valid ? __ldcs(a.grad + gp) : 0.f;
+            const float g = valid ? __ldcs(a.grad + gpt) : 0.f;
             dz[0] = g * s * (1.f - s);
         } else {
             const PlaneFwd pl = plane_from_logits(z[0], z[1], z[2], a.max_depth);
@@ -164,7 +167,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_bwd1_kernel(BwdArgs b
                     const float *gq = a.grad + (size_t)b * 4 * a.hw + p;
                     g[0] = __ldcs(gq); g[1] = __ldcs(gq + a.hw); g[2] = __ldcs(gq + (size_t)2 * a.hw); g[3] = __ldcs(gq + (size_t)3 * a.hw);
                 } else {
-                    lpg_block_grad<R>(a, pl, gp, g);
+                    lpg_block_grad<R>(a, pl, gpt, g);
                 }
                 plane_bwd(pl, g[0], g[1], g[2], g[3], a.max_depth, dz);
             }
@@ -327,9 +330,10 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_dgrad_kernel(BwdArgs 
     const long long ntiles = npp / kTile;
     for (long long tile = (long long)blockIdx.x * NWG + wg; tile < ntiles; tile += (long long)gridDim.x * NWG) {
         const long long gp = tile * kTile + t;
-        const bool valid = gp < ba.a.npx;
-        const int b = valid ? (int)(gp / ba.a.hw) : 0;
-        const int p = valid ? (int)(gp - (long long)b * ba.a.hw) : 0;
+        const int bb = (int)(gp / ba.hw_pad), pp = (int)(gp - (long long)bb * ba.hw_pad);
+        const bool valid = bb < ba.a.B && pp < ba.a.hw;
+        const int b = valid ? bb : 0;
+        const int p = valid ? pp : 0;
         {
             const float *d16 = ba.del + (size_t)BwdRows<CFG>::row(CFG::NW) * npp + gp;
             uint32_t hi[16], lo[16];
@@ -559,12 +563,18 @@ static void bwd_rows(const ChainParams &cp, int *ra, int *rd, int *total_w)
 }
 
 // bytes the tensor-core backward needs after the two packed-weight regions
-size_t tc_bwd_workspace_bytes(const ChainParams &cp, long long npx, int sms)
+static int pad32(int n) { return (n + 31) / 32 * 32; }
+
+size_t tc_bwd_workspace_bytes(const ChainParams &cp, int B, int hw, int sms)
 {
     int ra, rd, tw;
     bwd_rows(cp, &ra, &rd, &tw);
-    return sizeof(float) * ((size_t)(ra + rd) * (size_t)pad128(npx) + (size_t)sms * tw);
+    return sizeof(float) * ((size_t)(ra + rd) * (size_t)pad128((long long)B * pad32(hw)) + (size_t)sms * tw);
 }
+
+bool wgrad_tma_supported(const ChainParams &cp, int hw, const void *x);
+int launch_wgrad_tma(const ChainParams &cp, const float *x, const float *act, const float *del, float *partials,
+                     int B, int hw, int hw_pad, long long npp, int sms, cudaStream_t s);
 
 static int build_wgrad_plan(const ChainParams &cp, WPlan &pl, const float *x, float *act, float *del,
                             long long npx, long long npp, int hw)
@@ -630,7 +640,9 @@ static int launch_bwd_cfg(const ChainParams &cp, const TcArgs &a, char *ws, int 
     constexpr int LAST = MODE == 0 ? 1 : 3;
     float *wpack = reinterpret_cast<float *>(ws);
     float *wpack_t = reinterpret_cast<float *>(ws + tc_pack_bytes());
-    const long long npp = pad128(a.npx);
+    const bool tma = wgrad_tma_supported(cp, a.hw, a.x);
+    const int hw_pad = tma ? pad32(a.hw) : a.hw;
+    const long long npp = pad128((long long)a.B * hw_pad);
     int ra, rd, tw;
     bwd_rows(cp, &ra, &rd, &tw);
     float *act = reinterpret_cast<float *>(ws + 2 * tc_pack_bytes());
@@ -646,7 +658,7 @@ static int launch_bwd_cfg(const ChainParams &cp, const TcArgs &a, char *ws, int 
     ba.a = a;
     ba.a.wpack = wpack;
     ba.wpack_t = wpack_t;
-    ba.act = act; ba.del = del; ba.npx_pad = npp;
+    ba.act = act; ba.del = del; ba.npx_pad = npp; ba.hw_pad = hw_pad;
     const long long ntiles = npp / kTile;
     {
         auto k1 = chain_tc_bwd1_kernel<CFG, MODE, R, NWG1>;
@@ -671,7 +683,9 @@ static int launch_bwd_cfg(const ChainParams &cp, const TcArgs &a, char *ws, int 
             if (int e2 = check_launch("chain_tc_dgrad")) return e2;
         }
     }
-    if (cp.gW[0] != nullptr) {
+    if (cp.gW[0] != nullptr && tma) {
+        if (int e = launch_wgrad_tma(cp, a.x, act, del, partials, a.B, a.hw, hw_pad, npp, sms, s)) return e;
+    } else if (cp.gW[0] != nullptr) {
         WPlan pl;
         if (int e = build_wgrad_plan(cp, pl, a.x, act, del, a.npx, npp, a.hw)) return e;
         pl.partials = partials;

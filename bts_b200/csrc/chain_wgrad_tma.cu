@@ -1,0 +1,314 @@
+// chain_wgrad_tma.cu -- weight gradients of the WIDE chains (first layer > 64 channels) on sm_100a.
+//
+// dW_l = sum over pixels of delta_{l+1} (x) a_l  (SURVEY.md 8(a) row a8). The multi-kernel backward
+// (chain_tc_bwd.cu) leaves a_l and delta_l as [channel][pixel] fp32 rows in an L2-sized workspace; x is
+// NCHW. With the PIXEL axis as the MMA K dimension those rows are K-major operands as they lie, so the
+// TMA engine drops [8 channels][32 pixels] boxes straight into SWIZZLE_128B shared-memory images
+// (cp.async.bulk.tensor, zero-filled out of bounds) -- no register staging, no transposition:
+//   warp 0      producer : per (32-pixel chunk, job) one transaction barrier + nops box loads
+//   warps 2..5  splitters: remainder images lo = v - tf32(v) next to the raw ones (element-wise, 16 B)
+//   warp 1      issuer   : per K-step of 8 pixels  D += A_hi * [B_hi ; B_lo]^T  and  D[:, :nb] += A_lo * B_hi^T
+//                          (tcgen05.mma kind::tf32, both operands from shared memory, fp32 accumulators
+//                          resident in TMEM for the whole kernel), tcgen05.commit frees the slot
+// A job is one wide layer (A = a_l rows, B = delta_{l+1} rows) or the concatenated narrow layers
+// (block-diagonal). Per-CTA partial sums go to the workspace and are reduced deterministically.
+#include <cuda.h>
+#include <cudaTypedefs.h>
+
+#include <cstring>
+
+#include "chain_tc.cuh"
+
+namespace bts {
+
+constexpr int kWtSlots = 3;
+constexpr int kWtSlotBytes = 64 * 1024;      // A_hi 16K | A_lo 16K | B_hi, B_lo (2 x nb rows, <= 32K)
+constexpr int kWtMaxOps = 32;                // box loads per job: (128 + 128) rows / 8
+constexpr int kWtThreads = 192;
+
+struct WtOp {
+    unsigned short src_row;                  // first source row (channel) of the 8-row box
+    unsigned char src;                       // 0: x (NCHW), 1: activation rows, 2: delta rows
+    unsigned char dst_atom;                  // 8-row group: 0..15 in the A image, 16..31 in the B image
+};
+struct WtJob {
+    WtOp ops[kWtMaxOps];
+    int nops, a_rows, nb, tmem_col;
+};
+struct WtExtract {                           // layer l: D_job[row0 + k][col0 + n] -> partial[dst_off + n*K + k]
+    int job, row0, col0, K, N, dst_off;
+};
+struct WtPlan {
+    WtJob jobs[3];
+    WtExtract ex[BTS_MAX_LAYERS];
+    int njobs, nlayers, total_w, hw_pad;
+    long long nchunks;                       // 32-pixel chunks of the padded pixel axis
+    float *partials;                         // [gridDim.x][total_w]
+};
+
+__global__ void __launch_bounds__(kWtThreads, 1)
+chain_wgrad_tma_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_act,
+                       const __grid_constant__ CUtensorMap tm_del, const __grid_constant__ WtPlan pl)
+{
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char *slots = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(slots + kWtSlots * kWtSlotBytes);
+    uint64_t *full = bars, *split = bars + kWtSlots, *empty = bars + 2 * kWtSlots, *fin = bars + 3 * kWtSlots;
+    uint32_t *slot_tmem = reinterpret_cast<uint32_t *>(fin + 1);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    if (tid == 0) {
+        for (int s = 0; s < kWtSlots; ++s) {
+            mbar_init(full + s, 1);
+            mbar_init(split + s, 128);
+            mbar_init(empty + s, 1);
+        }
+        mbar_init(fin, 1);
+        fence_mbar_init();
+        tma_prefetch_desc(&tm_x);
+        tma_prefetch_desc(&tm_act);
+        tma_prefetch_desc(&tm_del);
+    }
+    if (warp == 0) tmem_alloc(slot_tmem, 512);
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tbase = *slot_tmem;
+    const uint32_t lane_addr = tbase + ((uint32_t)((warp & 3) * 32) << 16);   // warps 2..5 cover all four lane quarters
+    if (warp >= 2) {
+        uint32_t z[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) z[j] = 0u;
+#pragma unroll 1
+        for (int c0 = 0; c0 < 512; c0 += 32) tmem_st<32>(lane_addr + c0, z);
+        wait_st();
+    }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+
+    const uint32_t slot0 = smem_u32(slots);
+    if (warp == 0) {
+        if (lane == 0) {                                          // ---- producer
+            long long it = 0;
+            for (long long ck = blockIdx.x; ck < pl.nchunks; ck += gridDim.x) {
+                const long long gp = ck * 32;
+                const int b = (int)(gp / pl.hw_pad), p0 = (int)(gp - (long long)b * pl.hw_pad);
+                for (int j = 0; j < pl.njobs; ++j, ++it) {
+                    const int s = (int)(it % kWtSlots);
+                    const long long n = it / kWtSlots;
+                    if (n > 0) mbar_wait(empty + s, (uint32_t)((n - 1) & 1));
+                    const WtJob &job = pl.jobs[j];
+                    mbar_arrive_expect_tx(full + s, (uint32_t)job.nops * 1024u);
+                    const uint32_t base = slot0 + s * kWtSlotBytes;
+                    for (int o = 0; o < job.nops; ++o) {
+                        const WtOp op = job.ops[o];
+                        const uint32_t dst = base + (op.dst_atom < 16 ? op.dst_atom * 1024u : 32768u + (op.dst_atom - 16) * 1024u);
+                        if (op.src == 0) tma_load_3d(dst, &tm_x, p0, op.src_row, b, full + s);
+                        else tma_load_2d(dst, op.src == 1 ? &tm_act : &tm_del, (int)gp, op.src_row, full + s);
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (lane == 0) {                                          // ---- MMA issuer
+            long long it = 0;
+            for (long long ck = blockIdx.x; ck < pl.nchunks; ck += gridDim.x) {
+                for (int j = 0; j < pl.njobs; ++j, ++it) {
+                    const int s = (int)(it % kWtSlots);
+                    mbar_wait(split + s, (uint32_t)((it / kWtSlots) & 1));
+                    fence_after_sync();
+                    const WtJob &job = pl.jobs[j];
+                    const uint32_t base = slot0 + s * kWtSlotBytes;
+                    const uint32_t a_hi = base, a_lo = base + 16384u, b_hi = base + 32768u;
+                    const uint32_t d = tbase + job.tmem_col;
+                    const uint32_t id_cat = idesc_tf32(128, 2 * job.nb, 0, 0), id_hi = idesc_tf32(128, job.nb, 0, 0);
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks) {
+                        mma_tf32_ss(d, smem_desc_sw128(a_hi + ks * 32), smem_desc_sw128(b_hi + ks * 32), id_cat, 1);
+                        mma_tf32_ss(d, smem_desc_sw128(a_lo + ks * 32), smem_desc_sw128(b_hi + ks * 32), id_hi, 1);
+                    }
+                    mma_commit(empty + s);
+                }
+            }
+            mma_commit(fin);
+        }
+        __syncwarp();
+    } else {                                                      // ---- splitters
+        const int st = tid - 64;
+        long long it = 0;
+        for (long long ck = blockIdx.x; ck < pl.nchunks; ck += gridDim.x) {
+            for (int j = 0; j < pl.njobs; ++j, ++it) {
+                const int s = (int)(it % kWtSlots);
+                mbar_wait(full + s, (uint32_t)((it / kWtSlots) & 1));
+                const WtJob &job = pl.jobs[j];
+                float4 *a_hi = reinterpret_cast<float4 *>(slots + (size_t)s * kWtSlotBytes);
+                float4 *a_lo = a_hi + 1024, *b_hi = a_hi + 2048, *b_lo = b_hi + job.nb * 8;
+                for (int i = st; i < job.a_rows * 8; i += 128) {
+                    const float4 v = a_hi[i];
+                    a_lo[i] = make_float4(tf32_lo(v.x), tf32_lo(v.y), tf32_lo(v.z), tf32_lo(v.w));
+                }
+                for (int i = st; i < job.nb * 8; i += 128) {
+                    const float4 v = b_hi[i];
+                    b_lo[i] = make_float4(tf32_lo(v.x), tf32_lo(v.y), tf32_lo(v.z), tf32_lo(v.w));
+                }
+                fence_smem_to_async();
+                mbar_arrive(split + s);
+            }
+        }
+        // ---- accumulators -> this CTA's partial sums (row m of a job = TMEM lane m)
+        mbar_wait(fin, 0);
+        fence_after_sync();
+        float *part = pl.partials + (size_t)blockIdx.x * pl.total_w;
+        const int m = (warp & 3) * 32 + lane;
+        for (int l = 0; l < pl.nlayers; ++l) {
+            const WtExtract ex = pl.ex[l];
+            const WtJob &job = pl.jobs[ex.job];
+            const int k = m - ex.row0;
+            const bool mine = k >= 0 && k < ex.K;
+            for (int n0 = 0; n0 < ex.N; n0 += 8) {
+                uint32_t r0[8], r1[8];
+                tmem_ld<8>(lane_addr + job.tmem_col + ex.col0 + n0, r0);
+                tmem_ld<8>(lane_addr + job.tmem_col + job.nb + ex.col0 + n0, r1);
+                wait_ld();
+                if (mine) {
+#pragma unroll
+                    for (int jn = 0; jn < 8; ++jn)
+                        if (n0 + jn < ex.N)
+                            part[ex.dst_off + (size_t)(n0 + jn) * ex.K + k] = __uint_as_float(r0[jn]) + __uint_as_float(r1[jn]);
+                }
+            }
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tbase, 512);
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+int launch_wreduce(const ChainParams &cp, const float *partials, int nparts, int total_w, cudaStream_t s);
+
+static PFN_cuTensorMapEncodeTiled encode_fn()
+{
+    static PFN_cuTensorMapEncodeTiled fn = nullptr;     // resolved once; the pointer is immutable afterwards
+    if (fn == nullptr) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled>(p);
+    }
+    return fn;
+}
+
+// fp32 tensor, innermost dimension = pixels, boxes of [8 rows][32 pixels], 128-byte swizzle, zero fill
+static int make_map(CUtensorMap *m, const void *base, int rank, const cuuint64_t *dims, const cuuint64_t *strides_bytes)
+{
+    PFN_cuTensorMapEncodeTiled fn = encode_fn();
+    if (fn == nullptr) return set_error(BTS_ERR_UNSUPPORTED, "cuTensorMapEncodeTiled is not available");
+    const cuuint32_t box[3] = {32, 8, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<void *>(base), dims, strides_bytes, box,
+                          estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return set_error(BTS_ERR_UNSUPPORTED, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return BTS_OK;
+}
+
+// usable when every layer is at most 128 wide and the NCHW plane stride is a multiple of 16 bytes
+bool wgrad_tma_supported(const ChainParams &cp, int hw, const void *x)
+{
+    if (hw % 4 != 0 || (reinterpret_cast<uintptr_t>(x) & 15u) != 0) return false;
+    for (int l = 0; l <= cp.n_layers; ++l)
+        if (cp.dims[l] > 128) return false;
+    return encode_fn() != nullptr;
+}
+
+// act = [ra][npp] rows a_1 .. a_{L-1}; del = [rd][npp] rows delta_1 .. delta_L (chain order); the pixel
+// axis is padded per image to hw_pad (a multiple of 32), npp = padded total (a multiple of 128).
+int launch_wgrad_tma(const ChainParams &cp, const float *x, const float *act, const float *del, float *partials,
+                     int B, int hw, int hw_pad, long long npp, int sms, cudaStream_t s)
+{
+    const int L = cp.n_layers;
+    WtPlan pl;
+    memset(&pl, 0, sizeof(pl));
+    int prefix[BTS_MAX_LAYERS + 2];                     // prefix[l] = sum_{j=1}^{l-1} dims[j]: first row of a_l / delta_l
+    prefix[0] = prefix[1] = 0;
+    for (int l = 2; l <= L + 1; ++l) prefix[l] = prefix[l - 1] + cp.dims[l - 1];
+    const int ra = prefix[L], rd = prefix[L + 1];
+    int woffs[BTS_MAX_LAYERS], woff = 0;
+    for (int l = 0; l < L; ++l) { woffs[l] = woff; woff += cp.dims[l] * cp.dims[l + 1]; }
+    // trailing layers are concatenated into one block-diagonal job while their inputs fit 128 rows
+    int fc = L, sum = 0;
+    while (fc > 0 && sum + cp.dims[fc - 1] <= 128) sum += cp.dims[--fc];
+    if (fc == L) return set_error(BTS_ERR_UNSUPPORTED, "layer wider than 128 channels");
+    pl.njobs = fc + 1;
+    if (pl.njobs > 3) return set_error(BTS_ERR_UNSUPPORTED, "too many weight-gradient jobs");
+    int col = 0;
+    for (int j = 0; j < pl.njobs; ++j) {
+        WtJob &job = pl.jobs[j];
+        const int l0 = j < fc ? j : fc, l1 = j < fc ? j + 1 : L;
+        int arow = 0, brow = 0;
+        for (int l = l0; l < l1; ++l) {
+            const int K = cp.dims[l], N = cp.dims[l + 1];
+            if (arow % 8 || brow % 8) return set_error(BTS_ERR_UNSUPPORTED, "layer width not a multiple of 8");
+            for (int r = 0; r < K; r += 8) {
+                if (job.nops >= kWtMaxOps) return set_error(BTS_ERR_UNSUPPORTED, "too many box loads");
+                WtOp &op = job.ops[job.nops++];
+                op.src = l == 0 ? 0 : 1;
+                op.src_row = (unsigned short)((l == 0 ? 0 : prefix[l]) + r);
+                op.dst_atom = (unsigned char)((arow + r) / 8);
+            }
+            for (int r = 0; r < N; r += 8) {
+                if (job.nops >= kWtMaxOps) return set_error(BTS_ERR_UNSUPPORTED, "too many box loads");
+                WtOp &op = job.ops[job.nops++];
+                op.src = 2;
+                op.src_row = (unsigned short)(prefix[l + 1] + r);
+                op.dst_atom = (unsigned char)(16 + (brow + r) / 8);
+            }
+            WtExtract &ex = pl.ex[l];
+            ex.job = j; ex.row0 = arow; ex.col0 = brow; ex.K = K; ex.N = N; ex.dst_off = woffs[l];
+            arow += K;
+            brow += (N + 7) / 8 * 8;
+        }
+        if (arow > 128 || brow > 128) return set_error(BTS_ERR_UNSUPPORTED, "job exceeds 128 rows");
+        job.a_rows = (arow + 7) / 8 * 8;
+        job.nb = (brow + 15) / 16 * 16;
+        job.tmem_col = col;
+        col += 2 * job.nb;
+    }
+    if (col > 512) return set_error(BTS_ERR_UNSUPPORTED, "weight-gradient accumulators exceed TMEM");
+    pl.nlayers = L;
+    pl.total_w = woff;
+    pl.hw_pad = hw_pad;
+    pl.nchunks = npp / 32;
+    pl.partials = partials;
+
+    CUtensorMap tm_x, tm_act, tm_del;
+    {
+        const cuuint64_t dims[3] = {(cuuint64_t)hw, (cuuint64_t)cp.dims[0], (cuuint64_t)B};
+        const cuuint64_t str[2] = {(cuuint64_t)hw * 4, (cuuint64_t)hw * 4 * cp.dims[0]};
+        if (int e = make_map(&tm_x, x, 3, dims, str)) return e;
+    }
+    {
+        const cuuint64_t dims[2] = {(cuuint64_t)npp, (cuuint64_t)ra};
+        const cuuint64_t str[1] = {(cuuint64_t)npp * 4};
+        if (int e = make_map(&tm_act, act, 2, dims, str)) return e;
+    }
+    {
+        const cuuint64_t dims[2] = {(cuuint64_t)npp, (cuuint64_t)rd};
+        const cuuint64_t str[1] = {(cuuint64_t)npp * 4};
+        if (int e = make_map(&tm_del, del, 2, dims, str)) return e;
+    }
+    const size_t smem = 1024 + (size_t)kWtSlots * kWtSlotBytes + 8 * (3 * kWtSlots + 1) + 16;
+    cudaError_t e = cudaFuncSetAttribute(chain_wgrad_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    long long grid = pl.nchunks < sms ? pl.nchunks : sms;
+    chain_wgrad_tma_kernel<<<(unsigned)grid, kWtThreads, smem, s>>>(tm_x, tm_act, tm_del, pl);
+    if (int e2 = check_launch("chain_wgrad_tma")) return e2;
+    return launch_wreduce(cp, partials, (int)grid, pl.total_w, s);
+}
+
+}  // namespace bts

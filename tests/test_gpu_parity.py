@@ -290,7 +290,8 @@ def test_ddp_wraps_the_modules():
 
 @pytest.mark.parametrize("cfg", [(128, 128, False, 8, 3, 19, 23), (128, 64, False, 4, 2, 33, 41), (64, 32, False, 2, 2, 50, 70),
                                  (32, 16, True, 1, 2, 100, 130), (64, 64, False, 8, 1, 17, 9), (32, 32, False, 4, 1, 40, 40),
-                                 (32, 16, False, 2, 1, 31, 33), (128, 128, False, 1, 1, 9, 20)],
+                                 (32, 16, False, 2, 1, 31, 33), (128, 128, False, 1, 1, 9, 20), (128, 128, False, 8, 3, 20, 28),
+                                 (128, 64, False, 4, 2, 36, 44), (64, 32, False, 2, 3, 60, 84), (32, 16, True, 1, 2, 96, 160)],
                          ids=lambda c: "x".join(map(str, c)))
 def test_tensor_core_path_vs_generic_path(cfg):
     """The tcgen05 kernels and the generic SIMT kernels are independent implementations: they must
