@@ -13,9 +13,9 @@
 //
 // Roles: NWG compute warpgroups (thread = low-res pixel = TMEM lane) + one MMA-issuing warp. Hand-offs
 // are mbarriers only (no CTA-wide barrier inside the tile loop):
-//   ready[g]  128 arrivals  compute -> issuer   "A operand for the next chain MMA is in TMEM"
+//   ready[g]  4 warp arrivals compute -> issuer   "A operand for the next chain MMA is in TMEM"
 //   done[g]   tcgen05.commit issuer -> compute  "chain MMA finished, D is readable"
-//   stg[g]    64 arrivals   compute -> issuer   "a 64-pixel half tile is staged in shared memory"
+//   stg[g]    2 warp arrivals compute -> issuer   "a 64-pixel half tile is staged in shared memory"
 //   wfree[g][h] tcgen05.commit issuer -> compute "the weight-gradient MMAs of pair h's half finished"
 // The two warp pairs of a warpgroup share one staging buffer and take turns: pair 1 waits for
 // wfree[g][0], pair 0 for wfree[g][1] (one waiter group per mbarrier, so nobody lags two phases).
@@ -88,55 +88,63 @@ struct FusedLayout {
 // ---- the MMA-issuing thread: walks every warpgroup's fixed command list, in order per warpgroup,
 // round-robin across warpgroups.  NW == 1: F0, DG0, WT(h0), WT(h1).
 //                                 NW == 2: F0, F1, DG1, WT(h0), DG0, WT(h1), WX(h0), WX(h1).
-template <class CFG, int MODE, int R, int NWG>
-__device__ __forceinline__ void fused_issuer(const float *sw, const float *swt, uint32_t stage_addr, uint64_t *bars,
-                                             uint32_t tbase, long long ntiles)
+struct IssuerWg {            // per-warpgroup progress of the issuer (scalars: must stay in registers)
+    int cmd, rph, sph;
+    long long left;
+};
+
+// one poll of warpgroup G: issue its next command if the operands are ready. Returns true on progress.
+template <class CFG, int MODE, int R, int NWG, int G>
+__device__ __forceinline__ bool fused_issuer_step(IssuerWg &w, const float *sw, const float *swt, uint32_t stage_addr,
+                                                  uint64_t *bars, uint32_t tbase)
 {
     using L = FusedLayout<CFG, MODE, R, NWG>;
     constexpr int K0 = L::K0, NW = L::NW;
-    int cmd[NWG], rph[NWG], sph[NWG];
-    long long left[NWG];
-    long long remaining = 0;
-#pragma unroll
-    for (int g = 0; g < NWG; ++g) {
-        const long long first = (long long)blockIdx.x * NWG + g, stride = (long long)gridDim.x * NWG;
-        left[g] = first < ntiles ? (ntiles - first + stride - 1) / stride : 0;
-        remaining += left[g];
-        cmd[g] = 0; rph[g] = 0; sph[g] = 0;
+    if (w.left == 0) return false;
+    uint64_t *ready = bars + 5 * G, *done = ready + 1, *stg = ready + 2, *wfree0 = ready + 3, *wfree1 = ready + 4;
+    const int c = w.cmd;
+    const bool is_w = (NW == 1) ? (c >= 2) : (c == 3 || c >= 5);
+    if (!mbar_test_wait(is_w ? stg : ready, is_w ? w.sph : w.rph)) return false;
+    if (is_w) w.sph ^= 1; else w.rph ^= 1;
+    fence_after_sync();
+    const uint32_t wb = tbase + L::ACC + G * L::WGCOLS;           // x_hi
+    const uint32_t xl = wb + K0, dd = wb + 2 * K0;
+    const uint32_t sub0 = stage_addr + G * 2 * kSubBytes;
+    if constexpr (NW == 1) {
+        if (c == 0) { issue_ts3<CFG::K(0), CFG::N(0)>(dd, wb, xl, sw + CFG::w_off(0)); mma_commit(done); }
+        else if (c == 1) { issue_ts3<CFG::N(0), CFG::K(0)>(dd, xl, xl + 16, swt + CFG::w_off(0)); mma_commit(done); }
+        else { issue_wgrad_half(tbase, sub0); mma_commit(c == 2 ? wfree0 : wfree1); }
+    } else {
+        if (c == 0) { issue_ts3<CFG::K(0), CFG::N(0)>(dd, wb, xl, sw + CFG::w_off(0)); mma_commit(done); }
+        else if (c == 1) { issue_ts3<CFG::K(1), CFG::N(1)>(dd, xl, xl + 32, sw + CFG::w_off(1)); mma_commit(done); }
+        else if (c == 2) { issue_ts3<CFG::N(1), CFG::K(1)>(dd, xl + 32, xl + 48, swt + CFG::w_off(1)); mma_commit(done); }
+        else if (c == 4) { issue_ts3<CFG::N(0), CFG::K(0)>(dd, xl, xl + 32, swt + CFG::w_off(0)); mma_commit(done); }
+        else if (c == 3 || c == 5) { issue_wgrad_half(tbase, sub0); mma_commit(c == 3 ? wfree0 : wfree1); }
+        else { issue_wgrad_half(tbase + 64, sub0); mma_commit(c == 6 ? wfree0 : wfree1); }
     }
+    if (c + 1 == L::NCMD) { w.cmd = 0; --w.left; }
+    else w.cmd = c + 1;
+    return true;
+}
+
+template <class CFG, int MODE, int R, int NWG>
+__device__ __noinline__ void fused_issuer(const float *sw, const float *swt, uint32_t stage_addr, uint64_t *bars,
+                                             uint32_t tbase, long long ntiles)
+{
+    static_assert(NWG >= 1 && NWG <= 3, "one to three warpgroups");
+    const long long stride = (long long)gridDim.x * NWG;
+    auto tiles_of = [&](int g) {
+        const long long first = (long long)blockIdx.x * NWG + g;
+        return first < ntiles ? (ntiles - first + stride - 1) / stride : 0ll;
+    };
+    IssuerWg w0{0, 0, 0, tiles_of(0)}, w1{0, 0, 0, NWG > 1 ? tiles_of(1) : 0ll}, w2{0, 0, 0, NWG > 2 ? tiles_of(2) : 0ll};
     uint32_t idle = 0;
-    while (remaining > 0) {
-        bool progressed = false;
-#pragma unroll
-        for (int g = 0; g < NWG; ++g) {
-            if (left[g] == 0) continue;
-            uint64_t *ready = bars + 5 * g, *done = ready + 1, *stg = ready + 2, *wfree0 = ready + 3, *wfree1 = ready + 4;
-            const int c = cmd[g];
-            const bool is_w = (NW == 1) ? (c >= 2) : (c == 3 || c >= 5);
-            if (!mbar_try_wait(is_w ? stg : ready, is_w ? sph[g] : rph[g])) continue;
-            if (is_w) sph[g] ^= 1; else rph[g] ^= 1;
-            fence_after_sync();
-            progressed = true;
-            const uint32_t wb = tbase + L::ACC + g * L::WGCOLS;       // x_hi
-            const uint32_t xl = wb + K0, dd = wb + 2 * K0;
-            const uint32_t sub0 = stage_addr + g * 2 * kSubBytes;
-            if constexpr (NW == 1) {
-                if (c == 0) { issue_ts3<CFG::K(0), CFG::N(0)>(dd, wb, xl, sw + CFG::w_off(0)); mma_commit(done); }
-                else if (c == 1) { issue_ts3<CFG::N(0), CFG::K(0)>(dd, xl, xl + 16, swt + CFG::w_off(0)); mma_commit(done); }
-                else { issue_wgrad_half(tbase, sub0); mma_commit(c == 2 ? wfree0 : wfree1); }
-            } else {
-                if (c == 0) { issue_ts3<CFG::K(0), CFG::N(0)>(dd, wb, xl, sw + CFG::w_off(0)); mma_commit(done); }
-                else if (c == 1) { issue_ts3<CFG::K(1), CFG::N(1)>(dd, xl, xl + 32, sw + CFG::w_off(1)); mma_commit(done); }
-                else if (c == 2) { issue_ts3<CFG::N(1), CFG::K(1)>(dd, xl + 32, xl + 48, swt + CFG::w_off(1)); mma_commit(done); }
-                else if (c == 4) { issue_ts3<CFG::N(0), CFG::K(0)>(dd, xl, xl + 32, swt + CFG::w_off(0)); mma_commit(done); }
-                else if (c == 3 || c == 5) { issue_wgrad_half(tbase, sub0); mma_commit(c == 3 ? wfree0 : wfree1); }
-                else { issue_wgrad_half(tbase + 64, sub0); mma_commit(c == 6 ? wfree0 : wfree1); }
-            }
-            if (c + 1 == L::NCMD) { cmd[g] = 0; --left[g]; --remaining; }
-            else cmd[g] = c + 1;
-        }
+    while (w0.left + w1.left + w2.left > 0) {
+        bool progressed = fused_issuer_step<CFG, MODE, R, NWG, 0>(w0, sw, swt, stage_addr, bars, tbase);
+        if constexpr (NWG > 1) progressed |= fused_issuer_step<CFG, MODE, R, NWG, 1>(w1, sw, swt, stage_addr, bars, tbase);
+        if constexpr (NWG > 2) progressed |= fused_issuer_step<CFG, MODE, R, NWG, 2>(w2, sw, swt, stage_addr, bars, tbase);
         if (progressed) idle = 0;
-        else if (++idle > (1u << 26)) __trap();
+        else if (++idle > (1u << 28)) __trap();
     }
 }
 
@@ -212,9 +220,9 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
     if (tid < 32) tmem_alloc(slot, 512);
     if (tid == 0) {
         for (int g = 0; g < NWG; ++g) {
-            mbar_init(bars + 5 * g, kTile);
+            mbar_init(bars + 5 * g, kTile / 32);                  // one arrival per warp
             mbar_init(bars + 5 * g + 1, 1);
-            mbar_init(bars + 5 * g + 2, kTile / 2);
+            mbar_init(bars + 5 * g + 2, kTile / 64);
             mbar_init(bars + 5 * g + 3, 1);
             mbar_init(bars + 5 * g + 4, 1);
         }
@@ -255,6 +263,10 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
         const float *tw = sw + CFG::tail_off();
         const float *w5 = tw + kTailMid * kTailIn;
         uint32_t done_seen = 0, wseen = 0, nstage = 0;
+        auto warp_arrive = [&](uint64_t *bar) {                   // the warp's writes are ordered before lane 0's arrival
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar);
+        };
         auto done_wait = [&]() {
             mbar_wait(done, done_seen & 1);
             ++done_seen;
@@ -321,7 +333,7 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
             for (int j = 0; j < NG; ++j) gcur[j] = gn[j];
             wait_st();
             fence_before_sync();
-            mbar_arrive(ready);                                   // F0
+            warp_arrive(ready);                                   // F0
             prefetch(tile + stride);
             done_wait();
             float a1[NW == 2 ? 32 : 1];
@@ -342,7 +354,7 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
                 }
                 wait_st();
                 fence_before_sync();
-                mbar_arrive(ready);                               // F1
+                warp_arrive(ready);                               // F1
                 done_wait();
             }
             float a16[kTailIn], a8[kTailMid], z[LAST];
@@ -419,7 +431,7 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
             }
             wait_st();
             fence_before_sync();
-            mbar_arrive(ready);                                   // DG(NW-1)
+            warp_arrive(ready);                                   // DG(NW-1)
 
             auto stage_tail = [&]() {
                 wait_count(wfree, wseen, nstage + half);
@@ -440,7 +452,7 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
                 for (int j = 0; j < LAST; ++j) stage_b(sc, 24 + j, dz[j]);
                 if constexpr (NW == 1) stage_a_from_tmem32(sc, 0, xh);
                 fence_smem_to_async();
-                mbar_arrive(stg);
+                warp_arrive(stg);
             };
             auto gradx_epilogue = [&]() {
                 done_wait();
@@ -482,7 +494,7 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
                     }
                     wait_st();
                     fence_before_sync();
-                    mbar_arrive(ready);                           // DG0
+                    warp_arrive(ready);                           // DG0
                 };
                 auto stage_x = [&]() {
                     wait_count(wfree, wseen, nstage + half);
@@ -492,7 +504,7 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
                     stage_a_from_tmem32(sc, 0, xh);
                     stage_a_from_tmem32(sc, 32, xh + 32);
                     fence_smem_to_async();
-                    mbar_arrive(stg);
+                    warp_arrive(stg);
                 };
 #pragma unroll 1
                 for (int ph = 0; ph < 2; ++ph) {

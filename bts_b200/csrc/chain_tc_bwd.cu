@@ -522,13 +522,21 @@ __global__ void __launch_bounds__(256, 1) chain_tc_wgrad_kernel(const __grid_con
     if (tid < 32) tmem_dealloc(tbase, pl.tmem_cols);
 }
 
-// K4: grad_W[l] += sum over CTAs of the partial sums
-__global__ void chain_tc_wreduce_kernel(ChainParams cp, const float *partials, int nparts, int total_w)
+// K4: grad_W[l] += sum over CTAs of the partial sums. 32 elements x 8 slices of the partial list per
+// block (coalesced 128-byte rows, 8-way parallel over the list), fixed summation order.
+__global__ void __launch_bounds__(256) chain_tc_wreduce_kernel(ChainParams cp, const float *partials, int nparts, int total_w)
 {
-    const int e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= total_w) return;
+    __shared__ float red[8][33];
+    const int el = threadIdx.x & 31, sl = threadIdx.x >> 5;
+    const int e = blockIdx.x * 32 + el;
     float s = 0.f;
-    for (int c = 0; c < nparts; ++c) s += __ldcg(partials + (size_t)c * total_w + e);
+    if (e < total_w)
+        for (int c = sl; c < nparts; c += 8) s += __ldcg(partials + (size_t)c * total_w + e);
+    red[sl][el] = s;
+    __syncthreads();
+    if (sl != 0 || e >= total_w) return;
+#pragma unroll
+    for (int j = 1; j < 8; ++j) s += red[j][el];
     int off = 0;
     for (int l = 0; l < cp.n_layers; ++l) {
         const int n = cp.dims[l] * cp.dims[l + 1];
@@ -542,7 +550,7 @@ __global__ void chain_tc_wreduce_kernel(ChainParams cp, const float *partials, i
 
 int launch_wreduce(const ChainParams &cp, const float *partials, int nparts, int total_w, cudaStream_t s)
 {
-    chain_tc_wreduce_kernel<<<(total_w + 255) / 256, 256, 0, s>>>(cp, partials, nparts, total_w);
+    chain_tc_wreduce_kernel<<<(total_w + 31) / 32, 256, 0, s>>>(cp, partials, nparts, total_w);
     return check_launch("chain_tc_wreduce");
 }
 
@@ -696,8 +704,7 @@ static int launch_bwd_cfg(const ChainParams &cp, const TcArgs &a, char *ws, int 
         if (grid > sms) grid = sms;
         chain_tc_wgrad_kernel<<<(unsigned)grid, 256, smem, s>>>(pl);
         if (int e2 = check_launch("chain_tc_wgrad")) return e2;
-        chain_tc_wreduce_kernel<<<(pl.total_w + 255) / 256, 256, 0, s>>>(cp, partials, (int)grid, pl.total_w);
-        if (int e2 = check_launch("chain_tc_wreduce")) return e2;
+        if (int e2 = launch_wreduce(cp, partials, (int)grid, pl.total_w, s)) return e2;
     }
     return BTS_OK;
 }
