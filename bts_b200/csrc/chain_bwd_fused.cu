@@ -78,7 +78,8 @@ struct FusedLayout {
     static constexpr int IMG = CFG::tail_off();
     static constexpr int NCMD = NW == 1 ? 4 : 8;
     static constexpr size_t stage_bytes = (size_t)NWG * 2 * kSubBytes;
-    static constexpr size_t xs_bytes = (size_t)NWG * K0 * kTile * sizeof(float);   // next tile's features (cp.async)
+    // next tile's features [channel][pixel] + 4 upstream-gradient words per pixel (cp.async)
+    static constexpr size_t xs_bytes = (size_t)NWG * (K0 + 4) * kTile * sizeof(float);
     static constexpr size_t smem_bytes = 1024 + stage_bytes + xs_bytes + sizeof(float) * (PACK + IMG) + 8 * 5 * NWG + 16;
     static_assert(NW == 1 || NW == 2, "one or two tensor-core layers");
     static_assert(CFG::dim(NW) == kTailIn && CFG::dim(NW - 1) == 32, "chain must end ... -> 32 -> 16 -> 8");
@@ -197,7 +198,6 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
     using L = FusedLayout<CFG, MODE, R, NWG>;
     constexpr int LAST = L::LAST, NW = L::NW, K0 = L::K0;
     constexpr int NT = NWG * kTile + 32;
-    constexpr int NG = MODE == 0 ? 1 : MODE == 1 ? 4 : (R <= 2 ? R * R : 1);   // prefetched upstream-gradient words
     constexpr bool GPRE = MODE != 2 || R <= 2;
     const TcArgs &a = fa.a;
 
@@ -273,8 +273,8 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
             fence_after_sync();
         };
 
-        float *xs = xs_all + (size_t)g * K0 * kTile + t;          // [channel][pixel]: this thread's column
-        float gn[NG];
+        float *xs = xs_all + (size_t)g * (K0 + 4) * kTile + t;    // [channel][pixel]: this thread's column
+        float *gs = xs_all + (size_t)g * (K0 + 4) * kTile + K0 * kTile + t * 4;   // this pixel's gradient words
         auto prefetch = [&](long long tl) {
             const long long gp = tl * kTile + t;
             const bool ok = tl < ntiles && gp < a.npx;
@@ -284,27 +284,23 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
             const uint32_t dst = smem_u32(xs);
 #pragma unroll
             for (int c = 0; c < K0; ++c) cp_async4(dst + c * kTile * 4, xp + (size_t)c * a.hw, ok);
-            cp_async_commit();
-#pragma unroll
-            for (int j = 0; j < NG; ++j) gn[j] = 0.f;
-            if (ok && GPRE) {
-                if constexpr (MODE == 0) {
-                    gn[0] = __ldcs(a.grad + gp);
+            if constexpr (GPRE) {
+                const uint32_t gd = smem_u32(gs);
+                if constexpr (MODE == 0 || (MODE == 2 && R == 1)) {
+                    cp_async4(gd, a.grad + (ok ? gp : 0), ok);
                 } else if constexpr (MODE == 1) {
                     const float *gq = a.grad + (size_t)b * 4 * a.hw + p;
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) gn[j] = __ldcs(gq + (size_t)j * a.hw);
-                } else if constexpr (R == 1) {
-                    gn[0] = __ldcs(a.grad + gp);
-                } else if constexpr (R == 2) {
+                    for (int j = 0; j < 4; ++j) cp_async4(gd + 4 * j, gq + (size_t)j * a.hw, ok);
+                } else {                                          // R == 2: the 2 x 2 block of grad_depth
                     const int i = p / a.w, j = p - i * a.w;
                     const int Wd = a.w * 2;
                     const float *g0 = a.grad + ((size_t)b * a.h + i) * 2 * (size_t)Wd + (size_t)j * 2;
-                    const float2 r0 = __ldcs(reinterpret_cast<const float2 *>(g0));
-                    const float2 r1 = __ldcs(reinterpret_cast<const float2 *>(g0 + Wd));
-                    gn[0] = r0.x; gn[1] = r0.y; gn[2] = r1.x; gn[3] = r1.y;
+                    cp_async8(gd, g0, ok);
+                    cp_async8(gd + 8, g0 + Wd, ok);
                 }
             }
+            cp_async_commit();
         };
 
         long long tile = (long long)blockIdx.x * NWG + g;
@@ -328,9 +324,11 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
                 tmem_st<16>(xh + c0, hi);
                 tmem_st<16>(xl + c0, lo);
             }
-            float gcur[NG];
-#pragma unroll
-            for (int j = 0; j < NG; ++j) gcur[j] = gn[j];
+            float gcur[4] = {0.f, 0.f, 0.f, 0.f};
+            if constexpr (GPRE) {
+                const float4 g4 = *reinterpret_cast<const float4 *>(gs);
+                gcur[0] = g4.x; gcur[1] = g4.y; gcur[2] = g4.z; gcur[3] = g4.w;
+            }
             wait_st();
             fence_before_sync();
             warp_arrive(ready);                                   // F0
@@ -416,6 +414,7 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
                     dl16[c] = fmaf(w4.x, d8[o], dl16[c]); dl16[c + 1] = fmaf(w4.y, d8[o], dl16[c + 1]);
                     dl16[c + 2] = fmaf(w4.z, d8[o], dl16[c + 2]); dl16[c + 3] = fmaf(w4.w, d8[o], dl16[c + 3]);
                 }
+                asm volatile("" ::: "memory");                    // bound the hoisting of weight loads
             }
             {
                 uint32_t hi[16], lo[16];

@@ -268,6 +268,7 @@ __device__ __forceinline__ void tail_forward(const float *tw, const float (&a16)
             s = fmaf(w4.z, a16[c + 2], s); s = fmaf(w4.w, a16[c + 3], s);
         }
         a8[o] = elu_fast(s);
+        asm volatile("" ::: "memory");   // keep the weight loads of later rows from being hoisted (register pressure)
     }
     const float *w5 = tw + kTailMid * kTailIn;
 #pragma unroll
