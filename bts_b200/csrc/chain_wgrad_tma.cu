@@ -23,17 +23,23 @@ namespace bts {
 
 constexpr int kWtSlots = 3;
 constexpr int kWtSlotBytes = 64 * 1024;      // A_hi 16K | A_lo 16K | B_hi, B_lo (2 x nb rows, <= 32K)
-constexpr int kWtMaxOps = 32;                // box loads per job: (128 + 128) rows / 8
+constexpr int kWtMaxOps = 3;                 // box loads per job: [x] [activation rows] [delta rows]
+constexpr int kWtMaxMaps = 6;                // distinct (tensor, box height) pairs
 constexpr int kWtThreads = 192;
 
 struct WtOp {
-    unsigned short src_row;                  // first source row (channel) of the 8-row box
-    unsigned char src;                       // 0: x (NCHW), 1: activation rows, 2: delta rows
-    unsigned char dst_atom;                  // 8-row group: 0..15 in the A image, 16..31 in the B image
+    unsigned short src_row;                  // first source row (channel) of the box
+    unsigned short dst_row;                  // first row in the A image, or 128 + first row in the B image
+    unsigned short rows;                     // box height
+    unsigned char map;                       // index into WtMaps
+    unsigned char is_x;                      // 3-D map over the NCHW input
 };
 struct WtJob {
     WtOp ops[kWtMaxOps];
-    int nops, a_rows, nb, tmem_col;
+    int nops, a_rows, nb, tmem_col, tx_bytes;
+};
+struct WtMaps {
+    CUtensorMap m[kWtMaxMaps];
 };
 struct WtExtract {                           // layer l: D_job[row0 + k][col0 + n] -> partial[dst_off + n*K + k]
     int job, row0, col0, K, N, dst_off;
@@ -41,14 +47,13 @@ struct WtExtract {                           // layer l: D_job[row0 + k][col0 + 
 struct WtPlan {
     WtJob jobs[3];
     WtExtract ex[BTS_MAX_LAYERS];
-    int njobs, nlayers, total_w, hw_pad;
+    int njobs, nlayers, total_w, hw_pad, nmaps;
     long long nchunks;                       // 32-pixel chunks of the padded pixel axis
     float *partials;                         // [gridDim.x][total_w]
 };
 
 __global__ void __launch_bounds__(kWtThreads, 1)
-chain_wgrad_tma_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_act,
-                       const __grid_constant__ CUtensorMap tm_del, const __grid_constant__ WtPlan pl)
+chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constant__ WtPlan pl)
 {
     extern __shared__ unsigned char smem_raw[];
     unsigned char *slots = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -65,9 +70,7 @@ chain_wgrad_tma_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
         }
         mbar_init(fin, 1);
         fence_mbar_init();
-        tma_prefetch_desc(&tm_x);
-        tma_prefetch_desc(&tm_act);
-        tma_prefetch_desc(&tm_del);
+        for (int i = 0; i < pl.nmaps; ++i) tma_prefetch_desc(&maps.m[i]);
     }
     if (warp == 0) tmem_alloc(slot_tmem, 512);
     fence_before_sync();
@@ -99,13 +102,13 @@ chain_wgrad_tma_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                     const long long n = it / kWtSlots;
                     if (n > 0) mbar_wait(empty + s, (uint32_t)((n - 1) & 1));
                     const WtJob &job = pl.jobs[j];
-                    mbar_arrive_expect_tx(full + s, (uint32_t)job.nops * 1024u);
+                    mbar_arrive_expect_tx(full + s, (uint32_t)job.tx_bytes);
                     const uint32_t base = slot0 + s * kWtSlotBytes;
                     for (int o = 0; o < job.nops; ++o) {
                         const WtOp op = job.ops[o];
-                        const uint32_t dst = base + (op.dst_atom < 16 ? op.dst_atom * 1024u : 32768u + (op.dst_atom - 16) * 1024u);
-                        if (op.src == 0) tma_load_3d(dst, &tm_x, p0, op.src_row, b, full + s);
-                        else tma_load_2d(dst, op.src == 1 ? &tm_act : &tm_del, (int)gp, op.src_row, full + s);
+                        const uint32_t dst = base + (op.dst_row < 128 ? op.dst_row * 128u : 32768u + (op.dst_row - 128) * 128u);
+                        if (op.is_x) tma_load_3d(dst, &maps.m[op.map], p0, op.src_row, b, full + s);
+                        else tma_load_2d(dst, &maps.m[op.map], (int)gp, op.src_row, full + s);
                     }
                 }
             }
@@ -203,12 +206,13 @@ static PFN_cuTensorMapEncodeTiled encode_fn()
     return fn;
 }
 
-// fp32 tensor, innermost dimension = pixels, boxes of [8 rows][32 pixels], 128-byte swizzle, zero fill
-static int make_map(CUtensorMap *m, const void *base, int rank, const cuuint64_t *dims, const cuuint64_t *strides_bytes)
+// fp32 tensor, innermost dimension = pixels, boxes of [box_rows][32 pixels], 128-byte swizzle, zero fill
+static int make_map(CUtensorMap *m, const void *base, int rank, const cuuint64_t *dims, const cuuint64_t *strides_bytes,
+                    int box_rows)
 {
     PFN_cuTensorMapEncodeTiled fn = encode_fn();
     if (fn == nullptr) return set_error(BTS_ERR_UNSUPPORTED, "cuTensorMapEncodeTiled is not available");
-    const cuuint32_t box[3] = {32, 8, 1};
+    const cuuint32_t box[3] = {32, (cuuint32_t)box_rows, 1};
     const cuuint32_t estr[3] = {1, 1, 1};
     const CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<void *>(base), dims, strides_bytes, box,
                           estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -246,6 +250,29 @@ int launch_wgrad_tma(const ChainParams &cp, const float *x, const float *act, co
     if (fc == L) return set_error(BTS_ERR_UNSUPPORTED, "layer wider than 128 channels");
     pl.njobs = fc + 1;
     if (pl.njobs > 3) return set_error(BTS_ERR_UNSUPPORTED, "too many weight-gradient jobs");
+    // tensor maps are created on demand, one per (tensor, box height)
+    WtMaps maps;
+    memset(&maps, 0, sizeof(maps));
+    int map_src[kWtMaxMaps], map_rows[kWtMaxMaps];
+    auto get_map = [&](int src, int rows) -> int {       // src 0: x, 1: activation rows, 2: delta rows
+        for (int i = 0; i < pl.nmaps; ++i)
+            if (map_src[i] == src && map_rows[i] == rows) return i;
+        if (pl.nmaps == kWtMaxMaps) return -1;
+        const int i = pl.nmaps;
+        int e;
+        if (src == 0) {
+            const cuuint64_t dims[3] = {(cuuint64_t)hw, (cuuint64_t)cp.dims[0], (cuuint64_t)B};
+            const cuuint64_t str[2] = {(cuuint64_t)hw * 4, (cuuint64_t)hw * 4 * cp.dims[0]};
+            e = make_map(&maps.m[i], x, 3, dims, str, rows);
+        } else {
+            const cuuint64_t dims[2] = {(cuuint64_t)npp, (cuuint64_t)(src == 1 ? ra : rd)};
+            const cuuint64_t str[1] = {(cuuint64_t)npp * 4};
+            e = make_map(&maps.m[i], src == 1 ? act : del, 2, dims, str, rows);
+        }
+        if (e) return -1;
+        map_src[i] = src; map_rows[i] = rows;
+        return pl.nmaps++;
+    };
     int col = 0;
     for (int j = 0; j < pl.njobs; ++j) {
         WtJob &job = pl.jobs[j];
@@ -253,31 +280,40 @@ int launch_wgrad_tma(const ChainParams &cp, const float *x, const float *act, co
         int arow = 0, brow = 0;
         for (int l = l0; l < l1; ++l) {
             const int K = cp.dims[l], N = cp.dims[l + 1];
-            if (arow % 8 || brow % 8) return set_error(BTS_ERR_UNSUPPORTED, "layer width not a multiple of 8");
-            for (int r = 0; r < K; r += 8) {
-                if (job.nops >= kWtMaxOps) return set_error(BTS_ERR_UNSUPPORTED, "too many box loads");
-                WtOp &op = job.ops[job.nops++];
-                op.src = l == 0 ? 0 : 1;
-                op.src_row = (unsigned short)((l == 0 ? 0 : prefix[l]) + r);
-                op.dst_atom = (unsigned char)((arow + r) / 8);
-            }
-            for (int r = 0; r < N; r += 8) {
-                if (job.nops >= kWtMaxOps) return set_error(BTS_ERR_UNSUPPORTED, "too many box loads");
-                WtOp &op = job.ops[job.nops++];
-                op.src = 2;
-                op.src_row = (unsigned short)(prefix[l + 1] + r);
-                op.dst_atom = (unsigned char)(16 + (brow + r) / 8);
-            }
+            // the rows of consecutive layers follow each other in the workspace exactly as in the images
+            if (arow % 8 || brow % 8 || K % 8) return set_error(BTS_ERR_UNSUPPORTED, "layer width not a multiple of 8");
             WtExtract &ex = pl.ex[l];
             ex.job = j; ex.row0 = arow; ex.col0 = brow; ex.K = K; ex.N = N; ex.dst_off = woffs[l];
             arow += K;
-            brow += (N + 7) / 8 * 8;
+            brow += N;
         }
         if (arow > 128 || brow > 128) return set_error(BTS_ERR_UNSUPPORTED, "job exceeds 128 rows");
-        job.a_rows = (arow + 7) / 8 * 8;
+        job.a_rows = arow;
         job.nb = (brow + 15) / 16 * 16;
         job.tmem_col = col;
         col += 2 * job.nb;
+        // box loads: [x] [a_l0' .. a_(l1-1)] [delta_(l0+1) .. delta_l1]; rows past a tensor's end are zero-filled
+        int act_first = l0, act_dst = 0;
+        if (l0 == 0) {
+            const int m = get_map(0, cp.dims[0]);
+            if (m < 0) return set_error(BTS_ERR_UNSUPPORTED, "tensor map for x");
+            job.ops[job.nops++] = WtOp{0, 0, (unsigned short)cp.dims[0], (unsigned char)m, 1};
+            act_first = 1;
+            act_dst = cp.dims[0];
+        }
+        if (act_first < l1) {
+            const int rows = arow - act_dst;
+            const int m = get_map(1, rows);
+            if (m < 0) return set_error(BTS_ERR_UNSUPPORTED, "tensor map for the activation rows");
+            job.ops[job.nops++] = WtOp{(unsigned short)prefix[act_first], (unsigned short)act_dst, (unsigned short)rows, (unsigned char)m, 0};
+        }
+        {
+            const int m = get_map(2, job.nb);
+            if (m < 0) return set_error(BTS_ERR_UNSUPPORTED, "tensor map for the delta rows");
+            job.ops[job.nops++] = WtOp{(unsigned short)prefix[l0 + 1], 128, (unsigned short)job.nb, (unsigned char)m, 0};
+        }
+        job.tx_bytes = 0;
+        for (int o = 0; o < job.nops; ++o) job.tx_bytes += job.ops[o].rows * 128;
     }
     if (col > 512) return set_error(BTS_ERR_UNSUPPORTED, "weight-gradient accumulators exceed TMEM");
     pl.nlayers = L;
@@ -286,27 +322,11 @@ int launch_wgrad_tma(const ChainParams &cp, const float *x, const float *act, co
     pl.nchunks = npp / 32;
     pl.partials = partials;
 
-    CUtensorMap tm_x, tm_act, tm_del;
-    {
-        const cuuint64_t dims[3] = {(cuuint64_t)hw, (cuuint64_t)cp.dims[0], (cuuint64_t)B};
-        const cuuint64_t str[2] = {(cuuint64_t)hw * 4, (cuuint64_t)hw * 4 * cp.dims[0]};
-        if (int e = make_map(&tm_x, x, 3, dims, str)) return e;
-    }
-    {
-        const cuuint64_t dims[2] = {(cuuint64_t)npp, (cuuint64_t)ra};
-        const cuuint64_t str[1] = {(cuuint64_t)npp * 4};
-        if (int e = make_map(&tm_act, act, 2, dims, str)) return e;
-    }
-    {
-        const cuuint64_t dims[2] = {(cuuint64_t)npp, (cuuint64_t)rd};
-        const cuuint64_t str[1] = {(cuuint64_t)npp * 4};
-        if (int e = make_map(&tm_del, del, 2, dims, str)) return e;
-    }
     const size_t smem = 1024 + (size_t)kWtSlots * kWtSlotBytes + 8 * (3 * kWtSlots + 1) + 16;
     cudaError_t e = cudaFuncSetAttribute(chain_wgrad_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     long long grid = pl.nchunks < sms ? pl.nchunks : sms;
-    chain_wgrad_tma_kernel<<<(unsigned)grid, kWtThreads, smem, s>>>(tm_x, tm_act, tm_del, pl);
+    chain_wgrad_tma_kernel<<<(unsigned)grid, kWtThreads, smem, s>>>(maps, pl);
     if (int e2 = check_launch("chain_wgrad_tma")) return e2;
     return launch_wreduce(cp, partials, (int)grid, pl.total_w, s);
 }
