@@ -109,10 +109,10 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity)
 {
     uint32_t ok;
     asm volatile("{\n\t.reg .pred p;\n\t"
-                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
                  "selp.u32 %0, 1, 0, p;\n\t}"
                  : "=r"(ok)
-                 : "r"(smem_u32(bar)), "r"(parity)
+                 : "r"(smem_u32(bar)), "r"(parity), "r"(1000u)   // suspend-time hint (ns): wait in hardware, not in a spin loop
                  : "memory");
     return ok != 0;
 }
