@@ -15,18 +15,17 @@
 // are mbarriers only (no CTA-wide barrier inside the tile loop):
 //   ready[g]  4 warp arrivals compute -> issuer   "A operand for the next chain MMA is in TMEM"
 //   done[g]   tcgen05.commit issuer -> compute  "chain MMA finished, D is readable"
-//   stg[g]    2 warp arrivals compute -> issuer   "a 64-pixel half tile is staged in shared memory"
+//   stg[g][h] 2 warp arrivals compute -> issuer   "pair h's 64-pixel half tile is staged in shared memory"
 //   wfree[g][h] tcgen05.commit issuer -> compute "the weight-gradient MMAs of pair h's half finished"
 // The two warp pairs of a warpgroup share one staging buffer and take turns: pair 1 waits for
 // wfree[g][0], pair 0 for wfree[g][1] (one waiter group per mbarrier, so nobody lags two phases).
+#include <cstdlib>
+
 #include "chain_tc.cuh"
 
 namespace bts {
 
-constexpr int kSubRowsA = 128, kSubRowsB = 64;
-constexpr int kSubB = kSubRowsA * 128;                 // byte offset of the delta image in a sub-buffer
-constexpr int kSubBytes = (kSubRowsA + kSubRowsB) * 128;  // 32 pixels x (128 + 64) rows = 24 KB
-constexpr int kALo = 64 * 128, kBLo = 32 * 128;        // byte offset of the remainder rows
+constexpr int kBLo = 32 * 128;                         // byte offset of the remainder rows in the delta image
 
 struct FusedArgs {
     TcArgs a;
@@ -54,6 +53,7 @@ __device__ __forceinline__ void issue_ts3(uint32_t d, uint32_t a_hi, uint32_t a_
 }
 
 // weight-gradient MMAs of one staged half tile (two 32-pixel sub-buffers): D[128 x 64] += A_cat * B_cat^T
+template <int kSubBytes, int kSubB>
 __device__ __forceinline__ void issue_wgrad_half(uint32_t d, uint32_t sub0)
 {
     constexpr uint32_t idesc = idesc_tf32(128, 64, 0, 0);
@@ -77,10 +77,19 @@ struct FusedLayout {
     static constexpr int PACK = CFG::pack_floats(LAST);
     static constexpr int IMG = CFG::tail_off();
     static constexpr int NCMD = NW == 1 ? 4 : 8;
-    static constexpr size_t stage_bytes = (size_t)NWG * 2 * kSubBytes;
+    // staging: one sub-buffer per 32 pixels = activation image [hi rows | lo rows at ALO] + delta image
+    // [hi | lo at +32 rows]. PRIV (head with <= 2 warpgroups): every warp pair owns its two sub-buffers, the
+    // remainder rows start right after the 56 used rows; otherwise the pairs of a warpgroup share two.
+    static constexpr bool PRIV = NW == 1 && NWG <= 2;
+    static constexpr int ALO_ROWS = PRIV ? 56 : 64;
+    static constexpr int ALO = ALO_ROWS * 128;
+    static constexpr int SUBB = PRIV ? 112 * 128 : 128 * 128;
+    static constexpr int SUB = SUBB + 64 * 128;
+    static constexpr int NSUB = PRIV ? 4 : 2;
+    static constexpr size_t stage_bytes = (size_t)NWG * NSUB * SUB;
     // next tile's features [channel][pixel] + 4 upstream-gradient words per pixel (cp.async)
     static constexpr size_t xs_bytes = (size_t)NWG * (K0 + 4) * kTile * sizeof(float);
-    static constexpr size_t smem_bytes = 1024 + stage_bytes + xs_bytes + sizeof(float) * (PACK + IMG) + 8 * 5 * NWG + 16;
+    static constexpr size_t smem_bytes = 1024 + stage_bytes + xs_bytes + sizeof(float) * (PACK + IMG) + 8 * 6 * NWG + 16;
     static_assert(NW == 1 || NW == 2, "one or two tensor-core layers");
     static_assert(CFG::dim(NW) == kTailIn && CFG::dim(NW - 1) == 32, "chain must end ... -> 32 -> 16 -> 8");
     static_assert(ACC + NWG * WGCOLS <= 512, "TMEM budget");
@@ -90,7 +99,7 @@ struct FusedLayout {
 // round-robin across warpgroups.  NW == 1: F0, DG0, WT(h0), WT(h1).
 //                                 NW == 2: F0, F1, DG1, WT(h0), DG0, WT(h1), WX(h0), WX(h1).
 struct IssuerWg {            // per-warpgroup progress of the issuer (scalars: must stay in registers)
-    int cmd, rph, sph;
+    int cmd, rph, sph0, sph1;
     long long left;
 };
 
@@ -102,26 +111,37 @@ __device__ __forceinline__ bool fused_issuer_step(IssuerWg &w, const float *sw, 
     using L = FusedLayout<CFG, MODE, R, NWG>;
     constexpr int K0 = L::K0, NW = L::NW;
     if (w.left == 0) return false;
-    uint64_t *ready = bars + 5 * G, *done = ready + 1, *stg = ready + 2, *wfree0 = ready + 3, *wfree1 = ready + 4;
+    uint64_t *ready = bars + 6 * G, *done = ready + 1, *stg0 = ready + 2, *stg1 = ready + 3, *wfree0 = ready + 4, *wfree1 = ready + 5;
     const int c = w.cmd;
     const bool is_w = (NW == 1) ? (c >= 2) : (c == 3 || c >= 5);
-    if (!mbar_test_wait(is_w ? stg : ready, is_w ? w.sph : w.rph)) return false;
-    if (is_w) w.sph ^= 1; else w.rph ^= 1;
+    const bool h1 = is_w && ((NW == 1) ? (c == 3) : (c == 5 || c == 7));   // which pair's half this command multiplies
+    if (!is_w) {
+        if (!mbar_test_wait(ready, w.rph)) return false;
+        w.rph ^= 1;
+    } else if (!h1) {
+        if (!mbar_test_wait(stg0, w.sph0)) return false;
+        w.sph0 ^= 1;
+    } else {
+        if (!mbar_test_wait(stg1, w.sph1)) return false;
+        w.sph1 ^= 1;
+    }
     fence_after_sync();
     const uint32_t wb = tbase + L::ACC + G * L::WGCOLS;           // x_hi
     const uint32_t xl = wb + K0, dd = wb + 2 * K0;
-    const uint32_t sub0 = stage_addr + G * 2 * kSubBytes;
+    // shared staging: both pairs use sub-buffers 0,1; private: pair h uses 2h, 2h+1
+    const uint32_t sub0 = stage_addr + G * L::NSUB * L::SUB + ((L::PRIV && h1) ? 2 * L::SUB : 0);
+    static_assert(!L::PRIV || NW == 1, "private staging is laid out for the single-round chains");
     if constexpr (NW == 1) {
         if (c == 0) { issue_ts3<CFG::K(0), CFG::N(0)>(dd, wb, xl, sw + CFG::w_off(0)); mma_commit(done); }
         else if (c == 1) { issue_ts3<CFG::N(0), CFG::K(0)>(dd, xl, xl + 16, swt + CFG::w_off(0)); mma_commit(done); }
-        else { issue_wgrad_half(tbase, sub0); mma_commit(c == 2 ? wfree0 : wfree1); }
+        else { issue_wgrad_half<L::SUB, L::SUBB>(tbase, sub0); mma_commit(h1 ? wfree1 : wfree0); }
     } else {
         if (c == 0) { issue_ts3<CFG::K(0), CFG::N(0)>(dd, wb, xl, sw + CFG::w_off(0)); mma_commit(done); }
         else if (c == 1) { issue_ts3<CFG::K(1), CFG::N(1)>(dd, xl, xl + 32, sw + CFG::w_off(1)); mma_commit(done); }
         else if (c == 2) { issue_ts3<CFG::N(1), CFG::K(1)>(dd, xl + 32, xl + 48, swt + CFG::w_off(1)); mma_commit(done); }
         else if (c == 4) { issue_ts3<CFG::N(0), CFG::K(0)>(dd, xl, xl + 32, swt + CFG::w_off(0)); mma_commit(done); }
-        else if (c == 3 || c == 5) { issue_wgrad_half(tbase, sub0); mma_commit(c == 3 ? wfree0 : wfree1); }
-        else { issue_wgrad_half(tbase + 64, sub0); mma_commit(c == 6 ? wfree0 : wfree1); }
+        else if (c == 3 || c == 5) { issue_wgrad_half<L::SUB, L::SUBB>(tbase, sub0); mma_commit(h1 ? wfree1 : wfree0); }
+        else { issue_wgrad_half<L::SUB, L::SUBB>(tbase + 64, sub0); mma_commit(h1 ? wfree1 : wfree0); }
     }
     if (c + 1 == L::NCMD) { w.cmd = 0; --w.left; }
     else w.cmd = c + 1;
@@ -138,7 +158,7 @@ __device__ __noinline__ void fused_issuer(const float *sw, const float *swt, uin
         const long long first = (long long)blockIdx.x * NWG + g;
         return first < ntiles ? (ntiles - first + stride - 1) / stride : 0ll;
     };
-    IssuerWg w0{0, 0, 0, tiles_of(0)}, w1{0, 0, 0, NWG > 1 ? tiles_of(1) : 0ll}, w2{0, 0, 0, NWG > 2 ? tiles_of(2) : 0ll};
+    IssuerWg w0{0, 0, 0, 0, tiles_of(0)}, w1{0, 0, 0, 0, NWG > 1 ? tiles_of(1) : 0ll}, w2{0, 0, 0, 0, NWG > 2 ? tiles_of(2) : 0ll};
     uint32_t idle = 0;
     while (w0.left + w1.left + w2.left > 0) {
         bool progressed = fused_issuer_step<CFG, MODE, R, NWG, 0>(w0, sw, swt, stage_addr, bars, tbase);
@@ -157,12 +177,14 @@ struct StageCtx {
     unsigned char *sub;     // this warp's sub-buffer
     uint32_t coff[8];
 };
+template <int kALo>
 __device__ __forceinline__ void stage_a(const StageCtx &s, int row, float v)
 {
     unsigned char *p = s.sub + row * 128 + s.coff[row & 7];
     *reinterpret_cast<float *>(p) = v;
     *reinterpret_cast<float *>(p + kALo) = tf32_lo(v);
 }
+template <int kSubB>
 __device__ __forceinline__ void stage_b(const StageCtx &s, int row, float v)
 {
     unsigned char *p = s.sub + kSubB + row * 128 + s.coff[row & 7];
@@ -170,6 +192,7 @@ __device__ __forceinline__ void stage_b(const StageCtx &s, int row, float v)
     *reinterpret_cast<float *>(p + kBLo) = tf32_lo(v);
 }
 // rows row0 .. row0+31 of the A image <- 32 TMEM columns of this thread's lane (raw fp32 words)
+template <int kALo>
 __device__ __forceinline__ void stage_a_from_tmem32(const StageCtx &s, int row0, uint32_t taddr)
 {
 #pragma unroll
@@ -178,7 +201,7 @@ __device__ __forceinline__ void stage_a_from_tmem32(const StageCtx &s, int row0,
         tmem_ld<16>(taddr + c0, r);
         wait_ld();
 #pragma unroll
-        for (int j = 0; j < 16; ++j) stage_a(s, row0 + c0 + j, __uint_as_float(r[j]));
+        for (int j = 0; j < 16; ++j) stage_a<kALo>(s, row0 + c0 + j, __uint_as_float(r[j]));
     }
 }
 
@@ -209,7 +232,7 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
     float *sw = reinterpret_cast<float *>(stage + L::stage_bytes + L::xs_bytes);
     float *swt = sw + L::PACK;
     uint64_t *bars = reinterpret_cast<uint64_t *>(swt + L::IMG);
-    uint32_t *slot = reinterpret_cast<uint32_t *>(bars + 5 * NWG);
+    uint32_t *slot = reinterpret_cast<uint32_t *>(bars + 6 * NWG);
 
     const int tid = threadIdx.x;
     for (int i = tid * 4; i < L::PACK; i += NT * 4)
@@ -220,11 +243,12 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
     if (tid < 32) tmem_alloc(slot, 512);
     if (tid == 0) {
         for (int g = 0; g < NWG; ++g) {
-            mbar_init(bars + 5 * g, kTile / 32);                  // one arrival per warp
-            mbar_init(bars + 5 * g + 1, 1);
-            mbar_init(bars + 5 * g + 2, kTile / 64);
-            mbar_init(bars + 5 * g + 3, 1);
-            mbar_init(bars + 5 * g + 4, 1);
+            mbar_init(bars + 6 * g, kTile / 32);                  // one arrival per warp
+            mbar_init(bars + 6 * g + 1, 1);
+            mbar_init(bars + 6 * g + 2, kTile / 64);
+            mbar_init(bars + 6 * g + 3, kTile / 64);
+            mbar_init(bars + 6 * g + 4, 1);
+            mbar_init(bars + 6 * g + 5, 1);
         }
         fence_mbar_init();
     }
@@ -252,12 +276,14 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
         __syncwarp();
     } else {
         const int g = tid / kTile, t = tid % kTile, lane = tid & 31, wj = t >> 5, half = wj >> 1;
-        uint64_t *ready = bars + 5 * g, *done = ready + 1, *stg = ready + 2;
-        uint64_t *wfree = ready + 3 + (half ^ 1);                 // the OTHER pair's completions free the buffer for me
+        uint64_t *ready = bars + 6 * g, *done = ready + 1, *stg = ready + 2 + half;
+        // shared staging: the OTHER pair's completions free the buffer for me; private: my own
+        uint64_t *wfree = ready + 4 + (L::PRIV ? half : (half ^ 1));
+        const uint32_t wlag = L::PRIV ? 0u : (uint32_t)half;
         const uint32_t xh = tbase + L::ACC + g * L::WGCOLS + ((uint32_t)(wj * 32) << 16);
         const uint32_t xl = xh + K0, dd = xh + 2 * K0;
         StageCtx sc;
-        sc.sub = stage + (size_t)(g * 2 + (wj & 1)) * kSubBytes;
+        sc.sub = stage + (size_t)(g * L::NSUB + (L::PRIV ? wj : (wj & 1))) * L::SUB;
 #pragma unroll
         for (int q = 0; q < 8; ++q) sc.coff[q] = (uint32_t)((((lane >> 2) ^ q) << 4) | ((lane & 3) << 2));
         const float *tw = sw + CFG::tail_off();
@@ -433,23 +459,23 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
             warp_arrive(ready);                                   // DG(NW-1)
 
             auto stage_tail = [&]() {
-                wait_count(wfree, wseen, nstage + half);
+                wait_count(wfree, wseen, nstage + wlag);
                 ++nstage;
                 if constexpr (NW == 2) {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) stage_a(sc, j, a1[j]);
+                    for (int j = 0; j < 32; ++j) stage_a<L::ALO>(sc, j, a1[j]);
                 }
 #pragma unroll
-                for (int j = 0; j < kTailIn; ++j) stage_a(sc, 32 + j, a16[j]);
+                for (int j = 0; j < kTailIn; ++j) stage_a<L::ALO>(sc, 32 + j, a16[j]);
 #pragma unroll
-                for (int j = 0; j < kTailMid; ++j) stage_a(sc, 48 + j, a8[j]);
+                for (int j = 0; j < kTailMid; ++j) stage_a<L::ALO>(sc, 48 + j, a8[j]);
 #pragma unroll
-                for (int j = 0; j < kTailIn; ++j) stage_b(sc, j, dl16[j]);
+                for (int j = 0; j < kTailIn; ++j) stage_b<L::SUBB>(sc, j, dl16[j]);
 #pragma unroll
-                for (int j = 0; j < kTailMid; ++j) stage_b(sc, 16 + j, d8[j]);
+                for (int j = 0; j < kTailMid; ++j) stage_b<L::SUBB>(sc, 16 + j, d8[j]);
 #pragma unroll
-                for (int j = 0; j < LAST; ++j) stage_b(sc, 24 + j, dz[j]);
-                if constexpr (NW == 1) stage_a_from_tmem32(sc, 0, xh);
+                for (int j = 0; j < LAST; ++j) stage_b<L::SUBB>(sc, 24 + j, dz[j]);
+                if constexpr (NW == 1) stage_a_from_tmem32<L::ALO>(sc, 0, xh);
                 fence_smem_to_async();
                 warp_arrive(stg);
             };
@@ -496,12 +522,12 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
                     warp_arrive(ready);                           // DG0
                 };
                 auto stage_x = [&]() {
-                    wait_count(wfree, wseen, nstage + half);
+                    wait_count(wfree, wseen, nstage + wlag);
                     ++nstage;
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) stage_b(sc, j, d1[j]);
-                    stage_a_from_tmem32(sc, 0, xh);
-                    stage_a_from_tmem32(sc, 32, xh + 32);
+                    for (int j = 0; j < 32; ++j) stage_b<L::SUBB>(sc, j, d1[j]);
+                    stage_a_from_tmem32<L::ALO>(sc, 0, xh);
+                    stage_a_from_tmem32<L::ALO>(sc, 32, xh + 32);
                     fence_smem_to_async();
                     warp_arrive(stg);
                 };
@@ -560,7 +586,7 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
             for (int e = tid; e < K * N; e += NT) {
                 const int o = e / K, c = e - o * K;
                 const float *s = scratch + (job * kTile + row0 + c) * SP + col0 + o;
-                part[off + e] = s[0] + s[64 * SP];
+                part[off + e] = s[0] + s[L::ALO_ROWS * SP];
             }
             off += K * N;
         }
@@ -629,7 +655,11 @@ bool fused_bwd_supported(const ChainParams &cp) { return cfg_matches<Cfg32_16>(c
 int launch_chain_bwd_fused(const ChainParams &cp, const TcArgs &a, int mode, int r, void *ws, int sms, cudaStream_t s)
 {
     char *w = static_cast<char *>(ws);
-    if (cfg_matches<Cfg32_16>(cp)) return dispatch_fused<Cfg32_16, 3>(cp, a, mode, r, w, sms, s);
+    if (cfg_matches<Cfg32_16>(cp)) {
+        static const int head_nwg = getenv("BTS_HEAD_NWG") ? atoi(getenv("BTS_HEAD_NWG")) : 3;   // tuning hook
+        if (head_nwg == 2) return dispatch_fused<Cfg32_16, 2>(cp, a, mode, r, w, sms, s);
+        return dispatch_fused<Cfg32_16, 3>(cp, a, mode, r, w, sms, s);
+    }
     if (cfg_matches<Cfg64_32>(cp)) return dispatch_fused<Cfg64_32, 2>(cp, a, mode, r, w, sms, s);
     return set_error(BTS_ERR_UNSUPPORTED, "chain not covered by the fused backward");
 }
