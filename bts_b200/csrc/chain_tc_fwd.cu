@@ -14,7 +14,9 @@ namespace bts {
 
 
 
-template <class CFG, int R, bool FINAL, int NWG>
+// PREFETCH: the next tile's features travel global -> shared with cp.async while the current tile is
+// computed (needs D0*512 B of shared memory per warpgroup next to the weight images).
+template <class CFG, int R, bool FINAL, int NWG, bool PREFETCH>
 __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
 {
     constexpr int LAST = FINAL ? 1 : 3;
@@ -29,6 +31,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
     float *sw = smem;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + PACK);
     uint32_t *slot = reinterpret_cast<uint32_t *>(bars + NWG);
+    float *xs_all = reinterpret_cast<float *>(bars + NWG + 2);  // [NWG][D0][128] when PREFETCH
 
     const int tid = threadIdx.x, wg = tid / kTile, t = tid % kTile, lane = tid & 31;
     for (int i = tid * 4; i < PACK; i += NWG * kTile * 4)
@@ -51,22 +54,54 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
     int key = 0x7f800000;
 
     const long long ntiles = (a.npx + kTile - 1) / kTile;
-    for (long long tile = (long long)blockIdx.x * NWG + wg; tile < ntiles; tile += (long long)gridDim.x * NWG) {
+    const long long stride = (long long)gridDim.x * NWG;
+    float *xs = xs_all + (size_t)wg * D0 * kTile + t;             // this thread's column of the staged tile
+    auto prefetch = [&](long long tl) {
+        const long long gpn = tl * kTile + t;
+        const bool ok = tl < ntiles && gpn < a.npx;
+        const int bn = ok ? (int)(gpn / a.hw) : 0;
+        const int pn = ok ? (int)(gpn - (long long)bn * a.hw) : 0;
+        const float *xq = a.x + (size_t)bn * D0 * a.hw + pn;
+        const uint32_t dst = smem_u32(xs);
+#pragma unroll
+        for (int c = 0; c < D0; ++c) cp_async4(dst + c * kTile * 4, xq + (size_t)c * a.hw, ok);
+        cp_async_commit();
+    };
+    if constexpr (PREFETCH) prefetch((long long)blockIdx.x * NWG + wg);
+    for (long long tile = (long long)blockIdx.x * NWG + wg; tile < ntiles; tile += stride) {
         const long long gp = tile * kTile + t;
         const bool valid = gp < a.npx;
         const int b = valid ? (int)(gp / a.hw) : 0;
         const int p = valid ? (int)(gp - (long long)b * a.hw) : 0;
         const float *xp = a.x + (size_t)b * D0 * a.hw + p;
-        // features -> (hi, lo) -> TMEM A operand; 32 independent coalesced loads in flight per thread
+        // features -> (hi, lo) -> TMEM A operand
+        if constexpr (PREFETCH) {
+            cp_async_wait_all();
 #pragma unroll 1
-        for (int c0 = 0; c0 < D0; c0 += 32) {
-            uint32_t hi[32], lo[32];
+            for (int c0 = 0; c0 < D0; c0 += 16) {
+                uint32_t hi[16], lo[16];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) hi[j] = valid ? __float_as_uint(__ldg(xp + (size_t)(c0 + j) * a.hw)) : 0u;
+                for (int j = 0; j < 16; ++j) {
+                    const float v = xs[(c0 + j) * kTile];
+                    hi[j] = __float_as_uint(v);
+                    lo[j] = __float_as_uint(tf32_lo(v));
+                }
+                tmem_st<16>(lane_addr + c0, hi);
+                tmem_st<16>(lane_addr + KMAX + c0, lo);
+            }
+            prefetch(tile + stride);
+        } else {
+            // 32 independent coalesced loads in flight per thread
+#pragma unroll 1
+            for (int c0 = 0; c0 < D0; c0 += 32) {
+                uint32_t hi[32], lo[32];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) lo[j] = __float_as_uint(tf32_lo(__uint_as_float(hi[j])));
-            tmem_st<32>(lane_addr + c0, hi);
-            tmem_st<32>(lane_addr + KMAX + c0, lo);
+                for (int j = 0; j < 32; ++j) hi[j] = valid ? __float_as_uint(__ldg(xp + (size_t)(c0 + j) * a.hw)) : 0u;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) lo[j] = __float_as_uint(tf32_lo(__uint_as_float(hi[j])));
+                tmem_st<32>(lane_addr + c0, hi);
+                tmem_st<32>(lane_addr + KMAX + c0, lo);
+            }
         }
         // wide layers
         tc_run_layer<CFG, 0>(wg_base, sw, bar, phase, wg, t);
@@ -120,8 +155,11 @@ static int launch_one(const ChainParams &cp, const TcArgs &a, float *wpack, int 
     constexpr int LAST = FINAL ? 1 : 3;
     tc_pack_weights_kernel<CFG><<<16, 256, 0, s>>>(cp, wpack, LAST);
     if (int e = check_launch("tc_pack_weights")) return e;
-    const size_t smem = sizeof(float) * CFG::pack_floats(LAST) + 8 * NWG + 16;
-    auto kern = chain_tc_fwd_kernel<CFG, R, FINAL, NWG>;
+    constexpr size_t base = sizeof(float) * CFG::pack_floats(LAST) + 8 * NWG + 16;
+    constexpr size_t xs_bytes = (size_t)NWG * CFG::dim(0) * kTile * sizeof(float);
+    constexpr bool PREFETCH = base + xs_bytes <= 227 * 1024;
+    const size_t smem = base + (PREFETCH ? xs_bytes : 0);
+    auto kern = chain_tc_fwd_kernel<CFG, R, FINAL, NWG, PREFETCH>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     const long long ntiles = (a.npx + kTile - 1) / kTile;
