@@ -73,6 +73,7 @@ static TcArgs make_tc_args(const float *x, int B, int h, int w, float max_depth,
     memset(&a, 0, sizeof(a));
     a.x = x; a.B = B; a.h = h; a.w = w; a.hw = h * w; a.npx = (long long)B * h * w;
     a.max_depth = max_depth; a.eps = eps;
+    a.x_vec16 = ((h * w) % 4 == 0 && aligned16(x)) ? 1 : 0;
     return a;
 }
 
@@ -201,7 +202,7 @@ int bts_reduc_bwd(const float *x, const float *const *W, const int *dims, int n_
     if (use_tc_bwd(cp, ws, ws_bytes, B, h * w, nullptr)) {
         TcArgs a = make_tc_args(x, B, h, w, max_depth, 0.f);
         a.grad = grad_out; a.grad_x = grad_x;
-        if (fused_bwd_supported(cp) && g_force_path != BTS_PATH_TCGEN05_SPLIT)
+        if (fused_bwd_supported(cp) && a.x_vec16 && g_force_path != BTS_PATH_TCGEN05_SPLIT)
             return launch_chain_bwd_fused(cp, a, is_final ? 0 : 1, 0, ws, sm_count(), (cudaStream_t)stream);
         return launch_chain_tc_bwd(cp, a, is_final ? 0 : 1, 0, ws, sm_count(), (cudaStream_t)stream);
     }
@@ -247,7 +248,7 @@ int bts_reduc_lpg_bwd(const float *grad_depth, const float *x, const float *cons
     if ((r == 1 || r == 2 || r == 4 || r == 8) && use_tc_bwd(cp, ws, ws_bytes, B, h * w, grad_depth)) {
         TcArgs a = make_tc_args(x, B, h, w, max_depth, eps);
         a.grad = grad_depth; a.grad_x = grad_x;
-        if (fused_bwd_supported(cp) && g_force_path != BTS_PATH_TCGEN05_SPLIT)
+        if (fused_bwd_supported(cp) && a.x_vec16 && g_force_path != BTS_PATH_TCGEN05_SPLIT)
             return launch_chain_bwd_fused(cp, a, 2, r, ws, sm_count(), (cudaStream_t)stream);
         return launch_chain_tc_bwd(cp, a, 2, r, ws, sm_count(), (cudaStream_t)stream);
     }

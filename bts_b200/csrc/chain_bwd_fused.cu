@@ -299,17 +299,25 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
             fence_after_sync();
         };
 
-        float *xs = xs_all + (size_t)g * (K0 + 4) * kTile + t;    // [channel][pixel]: this thread's column
-        float *gs = xs_all + (size_t)g * (K0 + 4) * kTile + K0 * kTile + t * 4;   // this pixel's gradient words
+        float *xs_wg = xs_all + (size_t)g * (K0 + 4) * kTile;    // [channel][pixel] of the staged tile
+        float *xs = xs_wg + t;                                    // this thread's pixel column
+        float *gs = xs_wg + K0 * kTile + t * 4;                   // this pixel's gradient words
         auto prefetch = [&](long long tl) {
             const long long gp = tl * kTile + t;
             const bool ok = tl < ntiles && gp < a.npx;
-            const int b = ok ? (int)(gp / a.hw) : 0;
-            const int p = ok ? (int)(gp - (long long)b * a.hw) : 0;
-            const float *xp = a.x + (size_t)b * K0 * a.hw + p;
-            const uint32_t dst = smem_u32(xs);
+            const int b = ok ? (int)((unsigned)gp / (unsigned)a.hw) : 0;
+            const int p = ok ? (int)gp - b * a.hw : 0;
+            {                                                     // 128-bit copies (host checks x_vec16), see chain_tc_fwd.cu
+                const int q = t & 31, cw = t >> 5;
+                const long long g0 = tl * kTile + 4 * q;
+                const bool okv = tl < ntiles && g0 < a.npx;
+                const int bn = okv ? (int)((unsigned)g0 / (unsigned)a.hw) : 0;
+                const int pn = okv ? (int)g0 - bn * a.hw : 0;
+                const float *xq = a.x + ((size_t)bn * K0 + cw) * a.hw + pn;
+                const uint32_t dst = smem_u32(xs_wg + cw * kTile + 4 * q);
 #pragma unroll
-            for (int c = 0; c < K0; ++c) cp_async4(dst + c * kTile * 4, xp + (size_t)c * a.hw, ok);
+                for (int i = 0; i < K0 / 4; ++i) cp_async16(dst + i * 4 * kTile * 4, xq + (size_t)i * 4 * a.hw, okv);
+            }
             if constexpr (GPRE) {
                 const uint32_t gd = smem_u32(gs);
                 if constexpr (MODE == 0 || (MODE == 2 && R == 1)) {
@@ -338,6 +346,7 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
             const int p = valid ? (int)(gp - (long long)b * a.hw) : 0;
             // ---- x -> (hi, lo) -> TMEM A operand of layer 0; then the next tile's loads take off
             cp_async_wait_all();
+            named_bar_sync(1 + g, kTile);                         // the tile was copied by all threads of the warpgroup
 #pragma unroll
             for (int c0 = 0; c0 < K0; c0 += 16) {
                 uint32_t hi[16], lo[16];
@@ -358,6 +367,7 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
             wait_st();
             fence_before_sync();
             warp_arrive(ready);                                   // F0
+            named_bar_sync(1 + g, kTile);                         // everybody has read the staged tile
             prefetch(tile + stride);
             done_wait();
             float a1[NW == 2 ? 32 : 1];
@@ -500,7 +510,7 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
                     else gradx_epilogue();
                 }
             } else {
-                float d1[32];
+                // delta_1 lives only in TMEM (hi words at xl[0:32) until the next tile): not in registers
                 auto dg1_epilogue = [&]() {                       // delta_1 = (delta_16 W1) * ELU'(a1) -> A operand of DG0
                     done_wait();
 #pragma unroll
@@ -510,9 +520,9 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
                         wait_ld();
 #pragma unroll
                         for (int j = 0; j < 16; ++j) {
-                            d1[n0 + j] = __uint_as_float(r[j]) * elu_grad_from_out(a1[n0 + j]);
-                            r[j] = __float_as_uint(d1[n0 + j]);
-                            lo[j] = __float_as_uint(tf32_lo(d1[n0 + j]));
+                            const float v = __uint_as_float(r[j]) * elu_grad_from_out(a1[n0 + j]);
+                            r[j] = __float_as_uint(v);
+                            lo[j] = __float_as_uint(tf32_lo(v));
                         }
                         tmem_st<16>(xl + n0, r);
                         tmem_st<16>(xl + 32 + n0, lo);
@@ -525,7 +535,13 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
                     wait_count(wfree, wseen, nstage + wlag);
                     ++nstage;
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) stage_b<L::SUBB>(sc, j, d1[j]);
+                    for (int n0 = 0; n0 < 32; n0 += 16) {
+                        uint32_t r[16];
+                        tmem_ld<16>(xl + n0, r);
+                        wait_ld();
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) stage_b<L::SUBB>(sc, n0 + j, __uint_as_float(r[j]));
+                    }
                     stage_a_from_tmem32<L::ALO>(sc, 0, xh);
                     stage_a_from_tmem32<L::ALO>(sc, 32, xh + 32);
                     fence_smem_to_async();
@@ -649,6 +665,7 @@ static int dispatch_fused(const ChainParams &cp, const TcArgs &a, int mode, int 
     }
 }
 
+// (the caller also requires a.x_vec16: the feature prefetch moves 4 pixels per 128-bit cp.async)
 bool fused_bwd_supported(const ChainParams &cp) { return cfg_matches<Cfg32_16>(cp) || cfg_matches<Cfg64_32>(cp); }
 
 // mode: 0 head (grad [B,1,hw]), 1 plane parameters (grad [B,4,hw]), 2 fused LPG (grad_depth, upratio r)

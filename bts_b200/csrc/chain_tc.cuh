@@ -78,6 +78,7 @@ struct TcArgs {
     float *grad_x;
     float *gw[BTS_MAX_LAYERS];
     int B, h, w, hw;
+    int x_vec16;             // hw % 4 == 0 and x 16-byte aligned: 128-bit cp.async of 4 pixels is legal
     long long npx;           // B*hw
     float max_depth, eps;
 };

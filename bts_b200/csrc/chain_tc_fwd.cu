@@ -31,7 +31,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
     float *sw = smem;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + PACK);
     uint32_t *slot = reinterpret_cast<uint32_t *>(bars + NWG);
-    float *xs_all = reinterpret_cast<float *>(bars + NWG + 2);  // [NWG][D0][128] when PREFETCH
+    float *xs_all = smem + PACK + (8 * NWG + 16 + 15) / 16 * 4;   // [NWG][D0][128] when PREFETCH (16-byte aligned)
 
     const int tid = threadIdx.x, wg = tid / kTile, t = tid % kTile, lane = tid & 31;
     for (int i = tid * 4; i < PACK; i += NWG * kTile * 4)
@@ -55,16 +55,20 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
 
     const long long ntiles = (a.npx + kTile - 1) / kTile;
     const long long stride = (long long)gridDim.x * NWG;
-    float *xs = xs_all + (size_t)wg * D0 * kTile + t;             // this thread's column of the staged tile
+    float *xs_wg = xs_all + (size_t)wg * D0 * kTile;              // [channel][pixel] of the staged tile
+    float *xs = xs_wg + t;                                        // this thread's pixel column
+    // 128-bit copies: thread t moves pixels 4q..4q+3 (q = t%32) of channels t/32, t/32+4, ...; 4 pixels never
+    // straddle two images because hw % 4 == 0 (the launcher picks the non-prefetching kernel otherwise).
     auto prefetch = [&](long long tl) {
-        const long long gpn = tl * kTile + t;
-        const bool ok = tl < ntiles && gpn < a.npx;
-        const int bn = ok ? (int)(gpn / a.hw) : 0;
-        const int pn = ok ? (int)(gpn - (long long)bn * a.hw) : 0;
-        const float *xq = a.x + (size_t)bn * D0 * a.hw + pn;
-        const uint32_t dst = smem_u32(xs);
+        const int q = t & 31, cw = t >> 5;
+        const long long g0 = tl * kTile + 4 * q;
+        const bool ok = tl < ntiles && g0 < a.npx;
+        const int bn = ok ? (int)((unsigned)g0 / (unsigned)a.hw) : 0;
+        const int pn = ok ? (int)g0 - bn * a.hw : 0;
+        const float *xq = a.x + ((size_t)bn * D0 + cw) * a.hw + pn;
+        const uint32_t dst = smem_u32(xs_wg + cw * kTile + 4 * q);
 #pragma unroll
-        for (int c = 0; c < D0; ++c) cp_async4(dst + c * kTile * 4, xq + (size_t)c * a.hw, ok);
+        for (int i = 0; i < D0 / 4; ++i) cp_async16(dst + i * 4 * kTile * 4, xq + (size_t)i * 4 * a.hw, ok);
         cp_async_commit();
     };
     if constexpr (PREFETCH) prefetch((long long)blockIdx.x * NWG + wg);
@@ -77,6 +81,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
         // features -> (hi, lo) -> TMEM A operand
         if constexpr (PREFETCH) {
             cp_async_wait_all();
+            named_bar_sync(1 + wg, kTile);                        // the tile was copied by all threads of the warpgroup
 #pragma unroll 1
             for (int c0 = 0; c0 < D0; c0 += 16) {
                 uint32_t hi[16], lo[16];
@@ -89,6 +94,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
                 tmem_st<16>(lane_addr + c0, hi);
                 tmem_st<16>(lane_addr + KMAX + c0, lo);
             }
+            named_bar_sync(1 + wg, kTile);                        // everybody has read the staged tile
             prefetch(tile + stride);
         } else {
             // 32 independent coalesced loads in flight per thread
@@ -155,11 +161,12 @@ static int launch_one(const ChainParams &cp, const TcArgs &a, float *wpack, int 
     constexpr int LAST = FINAL ? 1 : 3;
     tc_pack_weights_kernel<CFG><<<16, 256, 0, s>>>(cp, wpack, LAST);
     if (int e = check_launch("tc_pack_weights")) return e;
-    constexpr size_t base = sizeof(float) * CFG::pack_floats(LAST) + 8 * NWG + 16;
+    constexpr size_t base = sizeof(float) * CFG::pack_floats(LAST) + (8 * NWG + 16 + 15) / 16 * 16;
     constexpr size_t xs_bytes = (size_t)NWG * CFG::dim(0) * kTile * sizeof(float);
-    constexpr bool PREFETCH = base + xs_bytes <= 227 * 1024;
-    const size_t smem = base + (PREFETCH ? xs_bytes : 0);
-    auto kern = chain_tc_fwd_kernel<CFG, R, FINAL, NWG, PREFETCH>;
+    constexpr bool CAN_PREFETCH = base + xs_bytes <= 227 * 1024;
+    const bool prefetch = CAN_PREFETCH && a.x_vec16;
+    const size_t smem = base + (prefetch ? xs_bytes : 0);
+    auto kern = prefetch ? chain_tc_fwd_kernel<CFG, R, FINAL, NWG, CAN_PREFETCH> : chain_tc_fwd_kernel<CFG, R, FINAL, NWG, false>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     const long long ntiles = (a.npx + kTile - 1) / kTile;

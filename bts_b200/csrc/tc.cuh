@@ -199,6 +199,10 @@ __device__ __forceinline__ void cp_async8(uint32_t dst_smem, const void *src, bo
 {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(dst_smem), "l"(src), "r"(ok ? 8 : 0) : "memory");
 }
+__device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void *src, bool ok)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst_smem), "l"(src), "r"(ok ? 16 : 0) : "memory");
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
