@@ -53,6 +53,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the CPU port timing (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer end-to-end leg (profiling runs)")
     ap.add_argument("--kernel-only", action="store_true", help="only the timed device loop (for ncu)")
+    ap.add_argument("--no-graph", action="store_true", help="launch every step eagerly instead of replaying a CUDA graph")
     return ap.parse_args()
 
 
@@ -212,32 +213,82 @@ def gpu_step(stages):
     return outs
 
 
-def time_calls(stages, wl, iters=10):
-    """Per-call device times (CUDA events on the launching stream): each stage's forward and backward."""
+def stage_calls(st, wl, device):
+    """(forward, backward) closures that call the C ABI of one stage directly on resident buffers."""
     import torch
+    from bts_b200 import _cabi
+    from bts_b200 import functional as Fn
+    lib = _cabi.lib()
+    stream = torch.cuda.current_stream().cuda_stream
+    x, g, r, final = st["x"].detach(), st["g"], st["r"], st["final"]
+    ws = [w.detach() for w in st["red"].chain_weights()]
+    dims = [x.shape[1]] + [w.shape[0] for w in ws]
+    B, _, h, w = x.shape
+    W = _cabi.ptr_array([t.data_ptr() for t in ws])
+    D = _cabi.int_array(dims)
+    nws = lib.bts_workspace_bytes(D, len(ws), B, h, w, 0 if final else r)
+    wsb = torch.empty((nws + 3) // 4, dtype=torch.float32, device=device)
+    gx = torch.empty_like(x)
+    gws = [torch.zeros_like(t) for t in ws]
+    GW = _cabi.ptr_array([t.data_ptr() for t in gws])
+    md = float(wl["max_depth"])
+    keep = (x, g, ws, wsb, gx, gws, W, D, GW)
+    if final:
+        out = torch.empty(B, 1, h, w, device=device)
+        f = lambda: _cabi.check(lib.bts_reduc_fwd(x.data_ptr(), W, D, len(ws), 1, md, B, h, w, out.data_ptr(),
+                                                  wsb.data_ptr(), nws, stream), "bts_reduc_fwd")
+        b = lambda: _cabi.check(lib.bts_reduc_bwd(x.data_ptr(), W, D, len(ws), 1, md, B, h, w, g.data_ptr(),
+                                                  gx.data_ptr(), GW, wsb.data_ptr(), nws, stream), "bts_reduc_bwd")
+    else:
+        out = torch.empty(B, h * r, w * r, device=device)
+        amin = torch.full((), float("inf"), device=device)
+        keep += (amin,)
+        f = lambda: _cabi.check(lib.bts_reduc_lpg_fwd(x.data_ptr(), W, D, len(ws), md, B, h, w, r, Fn.EPS, None,
+                                                      out.data_ptr(), amin.data_ptr(), wsb.data_ptr(), nws, stream),
+                                "bts_reduc_lpg_fwd")
+        b = lambda: _cabi.check(lib.bts_reduc_lpg_bwd(g.data_ptr(), x.data_ptr(), W, D, len(ws), md, B, h, w, r, Fn.EPS,
+                                                      gx.data_ptr(), GW, wsb.data_ptr(), nws, stream), "bts_reduc_lpg_bwd")
+    f.keep = b.keep = keep + (out,)
+    return f, b
+
+
+def time_back_to_back(fn, iters):
+    """Average DEVICE duration of one call: `iters` calls queued back to back between two CUDA events on
+    the launching stream, so host launch cost is pipelined away. Inputs of a call (>= 79 MB for the
+    dominant one, 1.2 GB across a step) do not survive in L2 between calls of the big stages."""
+    import torch
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def time_calls(stages, wl, device, iters=20):
+    """Per-call device times of each stage's forward and backward C-ABI call."""
     res = {}
     px = wl["B"] * wl["H"] * wl["W"]
     for st in stages:
-        fwd, bwd = [], []
-        for it in range(iters + 2):
-            st["x"].grad = None
-            for p in st["red"].parameters():
-                p.grad = None
-            e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
-            e[0].record()
-            out = stage_forward(st)
-            e[1].record()
-            out.backward(st["g"])
-            e[2].record()
-            torch.cuda.synchronize()
-            if it >= 2:
-                fwd.append(e[0].elapsed_time(e[1]))
-                bwd.append(e[1].elapsed_time(e[2]))
+        f, b = stage_calls(st, wl, device)
+        tf, tb = time_back_to_back(f, iters), time_back_to_back(b, iters)
         fb, bb = ALGO_BYTES[st["name"]]
-        res[st["name"]] = dict(fwd_ms=statistics.median(fwd), bwd_ms=statistics.median(bwd),
-                               fwd_gbs=fb * px / statistics.median(fwd) / 1e6,
-                               bwd_gbs=bb * px / statistics.median(bwd) / 1e6)
+        res[st["name"]] = dict(fwd_ms=tf, bwd_ms=tb, fwd_gbs=fb * px / tf / 1e6, bwd_gbs=bb * px / tb / 1e6)
     return res
+
+
+def measured_traffic(kernel):
+    """DRAM bytes per launch of the dominant call from the committed ncu --set full capture, or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)
+        return t.get(kernel, {}).get("dram_bytes_per_launch")
+    except Exception:
+        return None
 
 
 def e2e_leg(stages, wl, steps, warmup, device):
@@ -369,6 +420,24 @@ def main():
     for _ in range(max(3, args.warmup)):
         gpu_step(stages)
     torch.cuda.synchronize()
+    # The step is ~30 short launches behind Python/autograd dispatch: capture it once (the C ABI only
+    # enqueues on the given stream) and replay the graph, so the timed loop is device-bound.
+    graph, launch_mode, per_step = None, "eager", None
+    if not args.no_graph:
+        try:
+            l0 = lib.bts_launch_count()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                gpu_step(stages)
+            per_step = lib.bts_launch_count() - l0
+            for _ in range(2):
+                graph.replay()
+            torch.cuda.synchronize()
+            launch_mode = "cuda_graph"
+        except Exception as exc:  # noqa: BLE001 -- report and fall back to eager launches (same kernels)
+            sys.stderr.write("bench: CUDA graph capture failed (%s); timing eager launches\n" % exc)
+            graph = None
+            torch.cuda.synchronize()
     barrier()
     launches0 = lib.bts_launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -376,11 +445,14 @@ def main():
         torch.cuda.synchronize()
         ev0.record()
         for _ in range(args.steps):
-            gpu_step(stages)
+            if graph is not None:
+                graph.replay()
+            else:
+                gpu_step(stages)
         ev1.record()
         torch.cuda.synchronize()
     barrier()
-    launches = lib.bts_launch_count() - launches0
+    launches = per_step * args.steps if graph is not None else lib.bts_launch_count() - launches0
     ms_total = max_over_ranks(ev0.elapsed_time(ev1), device)
     ms_step = ms_total / args.steps
     value = world * px_per_rank / (ms_step * 1e-3) / 1e6
@@ -388,11 +460,11 @@ def main():
     if args.kernel_only:
         if rank == 0:
             print(json.dumps({"metric": "LPG decoder Mpixels/s fwd+bwd", "value": value, "ms_per_step": ms_step,
-                              "gpu_launches": int(launches)}), flush=True)
+                              "gpu_launches": int(launches), "launch": launch_mode}), flush=True)
         return
 
     # per-call device times -> roofline of the dominant call (the one that moves the most bytes)
-    calls = time_calls(stages, wl)
+    calls = time_calls(stages, wl, device)
     peak, peak_src = hbm_peak()
     dom = max(((n, d, k) for n, d in calls.items() for k in ("fwd", "bwd")),
               key=lambda t: ALGO_BYTES[t[0]][0 if t[2] == "fwd" else 1])
@@ -401,7 +473,7 @@ def main():
     achieved = dd[dk + "_gbs"]
     step_bytes = sum(sum(ALGO_BYTES[n]) for n in calls) * px_per_rank
     roofline = {"bound": "hbm", "kernel": "%s %s" % (dn, dk), "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "frac": achieved / peak, "traffic": measured_traffic("%s %s" % (dn, dk)), "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": algo_b, "launch_ms": dd[dk + "_ms"],
                 "whole_step": {"algorithmic_bytes": step_bytes, "achieved": step_bytes / (ms_step * 1e-3) / 1e9,
                                "frac": step_bytes / (ms_step * 1e-3) / 1e9 / peak},
@@ -430,7 +502,8 @@ def main():
             "config": {"workload": wl["desc"], "per_gpu_batch": wl["B"], "H": wl["H"], "W": wl["W"],
                        "max_depth": wl["max_depth"], "stages": [s[0] for s in STAGES], "parallelism": "batch-sharded x%d" % world,
                        "l2": "inputs %.0f MB per step > 126 MB L2 (no flush needed)" % (in_bytes / 1e6),
-                       "api": "bts_b200.reduction_1x1 / fused_stage via libbts_b200.so C ABI"},
+                       "api": "bts_b200.reduction_1x1 / fused_stage via libbts_b200.so C ABI",
+                       "launch": launch_mode},
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches),
             "clocks": clocks.summary(),
         }

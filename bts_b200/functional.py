@@ -45,6 +45,16 @@ def _dims(x, ws):
     return dims
 
 
+def _zero_grads(ws):
+    """One zero-filled buffer carved into per-layer views: a single fill launch per backward call."""
+    sizes = [t.numel() for t in ws]
+    offs = [0]
+    for n in sizes:
+        offs.append(offs[-1] + (n + 3) // 4 * 4)  # 16-byte aligned views
+    flat = torch.zeros(offs[-1], dtype=torch.float32, device=ws[0].device)
+    return [flat[o:o + n].view(t.shape) for o, n, t in zip(offs, sizes, ws)]
+
+
 def _workspace(dims, B, h, w, r, device):
     n = _cabi.lib().bts_workspace_bytes(_cabi.int_array(dims), len(dims) - 1, B, h, w, r)
     if n == 0:
@@ -116,7 +126,7 @@ class _Reduc(torch.autograd.Function):
         need_x = ctx.needs_input_grad[0]
         need_w = any(ctx.needs_input_grad[3:])
         gx = torch.empty_like(x) if need_x else None
-        gws = [torch.zeros_like(t) for t in ws] if need_w else None
+        gws = _zero_grads(ws) if need_w else None
         wsb, wsp, wsn = _workspace(dims, B, h, w, 0, x.device)
         with torch.cuda.device(x.device):
             _cabi.check(_cabi.lib().bts_reduc_bwd(
@@ -166,7 +176,7 @@ class _ReducLPG(torch.autograd.Function):
         need_x = ctx.needs_input_grad[0]
         need_w = any(ctx.needs_input_grad[4:])
         gx = torch.empty_like(x) if need_x else None
-        gws = [torch.zeros_like(t) for t in ws] if need_w else None
+        gws = _zero_grads(ws) if need_w else None
         wsb, wsp, wsn = _workspace(dims, B, h, w, r, x.device)
         with torch.cuda.device(x.device):
             _cabi.check(_cabi.lib().bts_reduc_lpg_bwd(

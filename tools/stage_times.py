@@ -10,21 +10,6 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch  # noqa: E402
 import bench  # noqa: E402
-from bts_b200 import _cabi  # noqa: E402
-from bts_b200 import functional as Fn  # noqa: E402
-
-
-def timed(fn, iters):
-    for _ in range(3):
-        fn()
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(iters):
-        fn()
-    e1.record()
-    torch.cuda.synchronize()
-    return e0.elapsed_time(e1) / iters
 
 
 def main():
@@ -34,39 +19,13 @@ def main():
     stages = bench.build_stages(wl, dev, 0)
     px = wl["B"] * wl["H"] * wl["W"]
     peak, _ = bench.hbm_peak()
-    lib = _cabi.lib()
-    stream = torch.cuda.current_stream().cuda_stream
     tot = 0.0
     only = sys.argv[3] if len(sys.argv) > 3 else ""
     for st in stages:
         if only not in st["name"]:
             continue
-        x, g, r, final = st["x"].detach(), st["g"], st["r"], st["final"]
-        ws = [w.detach() for w in st["red"].chain_weights()]
-        dims = [x.shape[1]] + [w.shape[0] for w in ws]
-        B, _, h, w = x.shape
-        W = _cabi.ptr_array([t.data_ptr() for t in ws])
-        D = _cabi.int_array(dims)
-        nws = lib.bts_workspace_bytes(D, len(ws), B, h, w, 0 if final else r)
-        wsb = torch.empty((nws + 3) // 4, dtype=torch.float32, device=dev)
-        gx = torch.empty_like(x)
-        gws = [torch.zeros_like(t) for t in ws]
-        GW = _cabi.ptr_array([t.data_ptr() for t in gws])
-        md = float(wl["max_depth"])
-        if final:
-            out = torch.empty(B, 1, h, w, device=dev)
-            f = lambda: _cabi.check(lib.bts_reduc_fwd(x.data_ptr(), W, D, len(ws), 1, md, B, h, w, out.data_ptr(),
-                                                      wsb.data_ptr(), nws, stream), "fwd")
-            b = lambda: _cabi.check(lib.bts_reduc_bwd(x.data_ptr(), W, D, len(ws), 1, md, B, h, w, g.data_ptr(),
-                                                      gx.data_ptr(), GW, wsb.data_ptr(), nws, stream), "bwd")
-        else:
-            depth = torch.empty(B, h * r, w * r, device=dev)
-            amin = torch.full((), float("inf"), device=dev)
-            f = lambda: _cabi.check(lib.bts_reduc_lpg_fwd(x.data_ptr(), W, D, len(ws), md, B, h, w, r, Fn.EPS, None,
-                                                          depth.data_ptr(), amin.data_ptr(), wsb.data_ptr(), nws, stream), "fwd")
-            b = lambda: _cabi.check(lib.bts_reduc_lpg_bwd(g.data_ptr(), x.data_ptr(), W, D, len(ws), md, B, h, w, r, Fn.EPS,
-                                                          gx.data_ptr(), GW, wsb.data_ptr(), nws, stream), "bwd")
-        tf, tb = timed(f, iters), timed(b, iters)
+        f, b = bench.stage_calls(st, wl, dev)
+        tf, tb = bench.time_back_to_back(f, iters), bench.time_back_to_back(b, iters)
         fb, bb = bench.ALGO_BYTES[st["name"]]
         tot += tf + tb
         print("%-18s fwd %7.1f us (%5.1f%% of HBM peak)   bwd %7.1f us (%5.1f%%)" % (
