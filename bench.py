@@ -232,22 +232,26 @@ def stage_calls(st, wl, device):
     gws = [torch.zeros_like(t) for t in ws]
     GW = _cabi.ptr_array([t.data_ptr() for t in gws])
     md = float(wl["max_depth"])
-    keep = (x, g, ws, wsb, gx, gws, W, D, GW)
+    nst = lib.bts_stash_bytes(D, len(ws), B, h, w)            # activation stash, as the autograd Functions use it
+    stb = torch.empty((nst + 3) // 4, dtype=torch.float32, device=device) if nst else None
+    stp = stb.data_ptr() if nst else None
+    keep = (x, g, ws, wsb, gx, gws, W, D, GW, stb)
     if final:
         out = torch.empty(B, 1, h, w, device=device)
-        f = lambda: _cabi.check(lib.bts_reduc_fwd(x.data_ptr(), W, D, len(ws), 1, md, B, h, w, out.data_ptr(),
-                                                  wsb.data_ptr(), nws, stream), "bts_reduc_fwd")
-        b = lambda: _cabi.check(lib.bts_reduc_bwd(x.data_ptr(), W, D, len(ws), 1, md, B, h, w, g.data_ptr(),
-                                                  gx.data_ptr(), GW, wsb.data_ptr(), nws, stream), "bts_reduc_bwd")
+        f = lambda: _cabi.check(lib.bts_reduc_fwd_stash(x.data_ptr(), W, D, len(ws), 1, md, B, h, w, out.data_ptr(),
+                                                        wsb.data_ptr(), nws, stp, nst, stream), "bts_reduc_fwd")
+        b = lambda: _cabi.check(lib.bts_reduc_bwd_stash(x.data_ptr(), W, D, len(ws), 1, md, B, h, w, g.data_ptr(), gx.data_ptr(),
+                                                        GW, wsb.data_ptr(), nws, stp, nst, stream), "bts_reduc_bwd")
     else:
         out = torch.empty(B, h * r, w * r, device=device)
         amin = torch.full((), float("inf"), device=device)
         keep += (amin,)
-        f = lambda: _cabi.check(lib.bts_reduc_lpg_fwd(x.data_ptr(), W, D, len(ws), md, B, h, w, r, Fn.EPS, None,
-                                                      out.data_ptr(), amin.data_ptr(), wsb.data_ptr(), nws, stream),
-                                "bts_reduc_lpg_fwd")
-        b = lambda: _cabi.check(lib.bts_reduc_lpg_bwd(g.data_ptr(), x.data_ptr(), W, D, len(ws), md, B, h, w, r, Fn.EPS,
-                                                      gx.data_ptr(), GW, wsb.data_ptr(), nws, stream), "bts_reduc_lpg_bwd")
+        f = lambda: _cabi.check(lib.bts_reduc_lpg_fwd_stash(x.data_ptr(), W, D, len(ws), md, B, h, w, r, Fn.EPS, None,
+                                                            out.data_ptr(), amin.data_ptr(), wsb.data_ptr(), nws, stp, nst,
+                                                            stream), "bts_reduc_lpg_fwd")
+        b = lambda: _cabi.check(lib.bts_reduc_lpg_bwd_stash(g.data_ptr(), x.data_ptr(), W, D, len(ws), md, B, h, w, r, Fn.EPS,
+                                                            gx.data_ptr(), GW, wsb.data_ptr(), nws, stp, nst, stream),
+                                "bts_reduc_lpg_bwd")
     f.keep = b.keep = keep + (out,)
     return f, b
 

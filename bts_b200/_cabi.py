@@ -38,6 +38,13 @@ _SIGNATURES = {
                                          ctypes.POINTER(ctypes.c_void_p), ctypes.c_void_p, ctypes.c_size_t,
                                          ctypes.c_void_p]),
 }
+_STASH_TAIL = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]   # stash, stash_bytes, stream
+for _n in ("bts_reduc_fwd", "bts_reduc_bwd", "bts_reduc_lpg_fwd", "bts_reduc_lpg_bwd"):
+    _res, _args = _SIGNATURES[_n]
+    _SIGNATURES[_n + "_stash"] = (_res, _args[:-1] + _STASH_TAIL)
+_SIGNATURES["bts_stash_bytes"] = (ctypes.c_size_t, [ctypes.POINTER(ctypes.c_int), ctypes.c_int, ctypes.c_int,
+                                                    ctypes.c_int, ctypes.c_int])
+ABI_VERSION = 2
 
 _lib = None
 
@@ -65,8 +72,8 @@ def lib():
             fn = getattr(l, name)
             fn.restype = res
             fn.argtypes = args
-        if l.bts_abi_version() != 1:
-            raise BtsLibraryError("libbts_b200.so ABI version %d, expected 1" % l.bts_abi_version())
+        if l.bts_abi_version() != ABI_VERSION:
+            raise BtsLibraryError("libbts_b200.so ABI version %d, expected %d" % (l.bts_abi_version(), ABI_VERSION))
         _lib = l
     return _lib
 

@@ -42,6 +42,10 @@ bool fused_bwd_supported(const ChainParams &);
 bool tc_supported(const ChainParams &);
 size_t tc_pack_bytes();
 size_t tc_bwd_workspace_bytes(const ChainParams &, int B, int hw, int sms);
+int launch_chain_tc_bwd_stash(const ChainParams &, const TcArgs &, int mode, int r, void *ws, int sms, cudaStream_t);
+bool tc_stash_supported(const ChainParams &, int hw, const void *x);
+size_t tc_stash_bytes(const ChainParams &, int B, int hw);
+int tc_stash_bind(const ChainParams &, TcArgs &, void *stash, bool clear, cudaStream_t);
 
 static int sm_count()
 {
@@ -65,6 +69,14 @@ static bool use_tc_bwd(const ChainParams &cp, const void *ws, size_t ws_bytes, i
 {
     if (!use_tc(cp, ws, ws_bytes, grad16)) return false;
     return ws_bytes >= 2 * tc_pack_bytes() + tc_bwd_workspace_bytes(cp, B, hw, sm_count());
+}
+
+// the stash is honoured when the chain stashes at all, the buffer is big enough and the call takes the
+// tensor-core route; forward and backward evaluate the same predicate on the same (chain, x, shape)
+static bool use_stash(const ChainParams &cp, const float *x, int B, int hw, const void *stash, size_t stash_bytes)
+{
+    if (stash == nullptr || !aligned16(stash) || g_force_path == BTS_PATH_GENERIC) return false;
+    return tc_stash_supported(cp, hw, x) && stash_bytes >= tc_stash_bytes(cp, B, hw);
 }
 
 static TcArgs make_tc_args(const float *x, int B, int h, int w, float max_depth, float eps)
@@ -174,8 +186,27 @@ size_t bts_workspace_bytes(const int *dims, int n_layers, int B, int h, int w, i
     return 2 * tc_pack_bytes() + tail;
 }
 
+size_t bts_stash_bytes(const int *dims, int n_layers, int B, int h, int w)
+{
+    if (B <= 0 || h <= 0 || w <= 0 || g_force_path == BTS_PATH_GENERIC) return 0;
+    ChainParams cp;
+    const float *fake[BTS_MAX_LAYERS];
+    for (int l = 0; l < BTS_MAX_LAYERS; ++l) fake[l] = reinterpret_cast<const float *>(16);
+    const int last = (dims && n_layers >= 1 && n_layers <= BTS_MAX_LAYERS) ? dims[n_layers] : 0;
+    if (!last || fill_chain(cp, fake, nullptr, dims, n_layers, last == 1, 1.f) != BTS_OK) return 0;
+    if (!tc_stash_supported(cp, h * w, fake[0])) return 0;
+    return tc_stash_bytes(cp, B, h * w);
+}
+
 int bts_reduc_fwd(const float *x, const float *const *W, const int *dims, int n_layers, int is_final,
                   float max_depth, int B, int h, int w, float *out, void *ws, size_t ws_bytes, void *stream)
+{
+    return bts_reduc_fwd_stash(x, W, dims, n_layers, is_final, max_depth, B, h, w, out, ws, ws_bytes, nullptr, 0, stream);
+}
+
+int bts_reduc_fwd_stash(const float *x, const float *const *W, const int *dims, int n_layers, int is_final,
+                        float max_depth, int B, int h, int w, float *out, void *ws, size_t ws_bytes,
+                        void *stash, size_t stash_bytes, void *stream)
 {
     ChainParams cp;
     if (int e = fill_chain(cp, W, nullptr, dims, n_layers, is_final, max_depth)) return e;
@@ -185,6 +216,8 @@ int bts_reduc_fwd(const float *x, const float *const *W, const int *dims, int n_
     if (use_tc(cp, ws, ws_bytes, nullptr)) {
         TcArgs a = make_tc_args(x, B, h, w, max_depth, 0.f);
         a.out = out;
+        if (use_stash(cp, x, B, h * w, stash, stash_bytes))
+            if (int e = tc_stash_bind(cp, a, stash, true, (cudaStream_t)stream)) return e;
         return launch_chain_tc_fwd(cp, a, 0, static_cast<float *>(ws), sm_count(), (cudaStream_t)stream);
     }
     return launch_chain_generic_fwd(cp, x, out, B, h * w, (cudaStream_t)stream);
@@ -194,6 +227,15 @@ int bts_reduc_bwd(const float *x, const float *const *W, const int *dims, int n_
                   float max_depth, int B, int h, int w, const float *grad_out, float *grad_x,
                   float *const *grad_W, void *ws, size_t ws_bytes, void *stream)
 {
+    return bts_reduc_bwd_stash(x, W, dims, n_layers, is_final, max_depth, B, h, w, grad_out, grad_x, grad_W, ws,
+                               ws_bytes, nullptr, 0, stream);
+}
+
+int bts_reduc_bwd_stash(const float *x, const float *const *W, const int *dims, int n_layers, int is_final,
+                        float max_depth, int B, int h, int w, const float *grad_out, float *grad_x,
+                        float *const *grad_W, void *ws, size_t ws_bytes, const void *stash, size_t stash_bytes,
+                        void *stream)
+{
     ChainParams cp;
     if (int e = fill_chain(cp, W, grad_W, dims, n_layers, is_final, max_depth)) return e;
     if (int e = check_shape(B, h, w)) return e;
@@ -202,6 +244,10 @@ int bts_reduc_bwd(const float *x, const float *const *W, const int *dims, int n_
     if (use_tc_bwd(cp, ws, ws_bytes, B, h * w, nullptr)) {
         TcArgs a = make_tc_args(x, B, h, w, max_depth, 0.f);
         a.grad = grad_out; a.grad_x = grad_x;
+        if (use_stash(cp, x, B, h * w, stash, stash_bytes)) {
+            if (int e = tc_stash_bind(cp, a, const_cast<void *>(stash), false, (cudaStream_t)stream)) return e;
+            return launch_chain_tc_bwd_stash(cp, a, is_final ? 0 : 1, 0, ws, sm_count(), (cudaStream_t)stream);
+        }
         if (fused_bwd_supported(cp) && a.x_vec16 && g_force_path != BTS_PATH_TCGEN05_SPLIT)
             return launch_chain_bwd_fused(cp, a, is_final ? 0 : 1, 0, ws, sm_count(), (cudaStream_t)stream);
         return launch_chain_tc_bwd(cp, a, is_final ? 0 : 1, 0, ws, sm_count(), (cudaStream_t)stream);
@@ -213,6 +259,15 @@ int bts_reduc_lpg_fwd(const float *x, const float *const *W, const int *dims, in
                       float max_depth, int B, int h, int w, int r, float eps, float *plane_eq_out,
                       float *depth, float *abs_min, void *ws, size_t ws_bytes, void *stream)
 {
+    return bts_reduc_lpg_fwd_stash(x, W, dims, n_layers, max_depth, B, h, w, r, eps, plane_eq_out, depth, abs_min, ws,
+                                   ws_bytes, nullptr, 0, stream);
+}
+
+int bts_reduc_lpg_fwd_stash(const float *x, const float *const *W, const int *dims, int n_layers,
+                            float max_depth, int B, int h, int w, int r, float eps, float *plane_eq_out,
+                            float *depth, float *abs_min, void *ws, size_t ws_bytes, void *stash,
+                            size_t stash_bytes, void *stream)
+{
     ChainParams cp;
     if (int e = fill_chain(cp, W, nullptr, dims, n_layers, 0, max_depth)) return e;
     if (int e = check_shape(B, h, w)) return e;
@@ -222,6 +277,8 @@ int bts_reduc_lpg_fwd(const float *x, const float *const *W, const int *dims, in
     if ((r == 1 || r == 2 || r == 4 || r == 8) && use_tc(cp, ws, ws_bytes, depth)) {
         TcArgs a = make_tc_args(x, B, h, w, max_depth, eps);
         a.out = plane_eq_out; a.depth = depth; a.abs_min = abs_min;
+        if (use_stash(cp, x, B, h * w, stash, stash_bytes))
+            if (int e = tc_stash_bind(cp, a, stash, true, (cudaStream_t)stream)) return e;
         return launch_chain_tc_fwd(cp, a, r, static_cast<float *>(ws), sm_count(), (cudaStream_t)stream);
     }
     float *pe = plane_eq_out;
@@ -239,6 +296,15 @@ int bts_reduc_lpg_bwd(const float *grad_depth, const float *x, const float *cons
                       int n_layers, float max_depth, int B, int h, int w, int r, float eps,
                       float *grad_x, float *const *grad_W, void *ws, size_t ws_bytes, void *stream)
 {
+    return bts_reduc_lpg_bwd_stash(grad_depth, x, W, dims, n_layers, max_depth, B, h, w, r, eps, grad_x, grad_W, ws,
+                                   ws_bytes, nullptr, 0, stream);
+}
+
+int bts_reduc_lpg_bwd_stash(const float *grad_depth, const float *x, const float *const *W, const int *dims,
+                            int n_layers, float max_depth, int B, int h, int w, int r, float eps,
+                            float *grad_x, float *const *grad_W, void *ws, size_t ws_bytes, const void *stash,
+                            size_t stash_bytes, void *stream)
+{
     ChainParams cp;
     if (int e = fill_chain(cp, W, grad_W, dims, n_layers, 0, max_depth)) return e;
     if (int e = check_shape(B, h, w)) return e;
@@ -248,6 +314,10 @@ int bts_reduc_lpg_bwd(const float *grad_depth, const float *x, const float *cons
     if ((r == 1 || r == 2 || r == 4 || r == 8) && use_tc_bwd(cp, ws, ws_bytes, B, h * w, grad_depth)) {
         TcArgs a = make_tc_args(x, B, h, w, max_depth, eps);
         a.grad = grad_depth; a.grad_x = grad_x;
+        if (use_stash(cp, x, B, h * w, stash, stash_bytes)) {
+            if (int e = tc_stash_bind(cp, a, const_cast<void *>(stash), false, (cudaStream_t)stream)) return e;
+            return launch_chain_tc_bwd_stash(cp, a, 2, r, ws, sm_count(), (cudaStream_t)stream);
+        }
         if (fused_bwd_supported(cp) && a.x_vec16 && g_force_path != BTS_PATH_TCGEN05_SPLIT)
             return launch_chain_bwd_fused(cp, a, 2, r, ws, sm_count(), (cudaStream_t)stream);
         return launch_chain_tc_bwd(cp, a, 2, r, ws, sm_count(), (cudaStream_t)stream);

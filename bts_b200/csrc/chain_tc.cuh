@@ -81,6 +81,31 @@ struct TcArgs {
     int x_vec16;             // hw % 4 == 0 and x 16-byte aligned: 128-bit cp.async of 4 pixels is legal
     long long npx;           // B*hw
     float max_depth, eps;
+    // activation stash (forward writes, backward reads; null = recompute): rows [channel][stash_npp] of
+    // a_1 .. a_NW (= a16), a8 on a pixel axis padded per image to stash_hw_pad, and plane_eq [B][4][hw]
+    float *stash_act;
+    float *stash_pe;
+    long long stash_npp;
+    int stash_hw_pad;
+};
+
+// Chains whose backward is the multi-kernel one (chain_tc_bwd.cu) can leave their activations in a
+// caller-provided stash so that backward skips the recompute; the two narrow chains are recomputed
+// inside the one-pass backward (chain_bwd_fused.cu) and never stash.
+template <class CFG>
+constexpr bool kStashCfg = !(CFG::NW <= 2 && CFG::dim(0) >= 2 * CFG::dim(1));
+
+// first row of a_l / delta_l (l = 1..NW) in the backward workspace / the stash; the tail rows follow
+template <class CFG>
+struct BwdRows {
+    __host__ __device__ static constexpr int row(int l)
+    {
+        int r = 0;
+        for (int j = 1; j < l; ++j) r += CFG::dim(j);
+        return r;
+    }
+    __host__ __device__ static constexpr int row8() { return row(CFG::NW + 1); }
+    __host__ __device__ static constexpr int rowz() { return row8() + kTailMid; }
 };
 
 using namespace tc;
@@ -137,6 +162,29 @@ __device__ __forceinline__ void tc_epilogue_to_a(uint32_t lane_addr)
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
             const float v = elu_fast(__uint_as_float(r[j]));
+            r[j] = __float_as_uint(v);
+            lo[j] = __float_as_uint(tf32_lo(v));
+        }
+        tmem_st<16>(lane_addr + n0, r);
+        tmem_st<16>(lane_addr + KMAX + n0, lo);
+    }
+}
+
+// same, and a_{L+1} also goes to its [channel][pixel] rows (row stride npx_pad) when `store`
+template <class CFG, int L>
+__device__ __forceinline__ void tc_epilogue_to_a_spill(uint32_t lane_addr, float *act_gp, long long npx_pad, bool store = true)
+{
+    constexpr int N = CFG::N(L), KMAX = CFG::kmax();
+    float *dst = act_gp + (size_t)BwdRows<CFG>::row(L + 1) * npx_pad;
+#pragma unroll
+    for (int n0 = 0; n0 < N; n0 += 16) {
+        uint32_t r[16], lo[16];
+        tmem_ld<16>(lane_addr + 2 * KMAX + n0, r);
+        wait_ld();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const float v = elu_fast(__uint_as_float(r[j]));
+            if (store) dst[(size_t)(n0 + j) * npx_pad] = v;
             r[j] = __float_as_uint(v);
             lo[j] = __float_as_uint(tf32_lo(v));
         }
@@ -254,6 +302,24 @@ __device__ __forceinline__ void lpg_block_grad(const TcArgs &a, const PlaneFwd &
     g[0] = -pl.n4 * acc.tu; g[1] = -pl.n4 * acc.tv; g[2] = -pl.n4 * acc.t; g[3] = acc.s4;
 }
 
+// ---- last layer 8 -> (3|1): logits from a8 (shared by the forward tail and the stash backward, so both
+// see bit-identical logits)
+template <int LAST>
+__device__ __forceinline__ void tail_logits(const float *w5, const float (&a8)[kTailMid], float (&z)[LAST])
+{
+#pragma unroll
+    for (int o = 0; o < LAST; ++o) {
+        float s = 0.f;
+#pragma unroll
+        for (int c = 0; c < kTailMid; c += 4) {
+            const float4 w4 = *reinterpret_cast<const float4 *>(w5 + o * kTailMid + c);
+            s = fmaf(w4.x, a8[c], s); s = fmaf(w4.y, a8[c + 1], s);
+            s = fmaf(w4.z, a8[c + 2], s); s = fmaf(w4.w, a8[c + 3], s);
+        }
+        z[o] = s;
+    }
+}
+
 // ---- the 16 -> 8 -> (3|1) tail on registers; weights broadcast from shared memory
 template <int LAST>
 __device__ __forceinline__ void tail_forward(const float *tw, const float (&a16)[kTailIn], float (&a8)[kTailMid],
@@ -271,18 +337,7 @@ __device__ __forceinline__ void tail_forward(const float *tw, const float (&a16)
         a8[o] = elu_fast(s);
         asm volatile("" ::: "memory");   // keep the weight loads of later rows from being hoisted (register pressure)
     }
-    const float *w5 = tw + kTailMid * kTailIn;
-#pragma unroll
-    for (int o = 0; o < LAST; ++o) {
-        float s = 0.f;
-#pragma unroll
-        for (int c = 0; c < kTailMid; c += 4) {
-            const float4 w4 = *reinterpret_cast<const float4 *>(w5 + o * kTailMid + c);
-            s = fmaf(w4.x, a8[c], s); s = fmaf(w4.y, a8[c + 1], s);
-            s = fmaf(w4.z, a8[c + 2], s); s = fmaf(w4.w, a8[c + 3], s);
-        }
-        z[o] = s;
-    }
+    tail_logits<LAST>(tw + kTailMid * kTailIn, a8, z);
 }
 
 // ---- weight packing: fp32 [N][K] -> canonical K-major (hi | lo) images + raw tail weights

@@ -24,43 +24,8 @@ struct BwdArgs {
     float *del;            // [RD][npx_pad]   delta_1 .. delta_NW (=d16), d8, dz
     long long npx_pad;
     int hw_pad;            // pixels per image on the workspace's pixel axis (hw, or hw rounded up to 32)
+    const float *w4, *w5;  // stash backward: raw tail weights [8][16], [LAST][8] (device)
 };
-
-template <class CFG>
-struct BwdRows {
-    // first workspace row of a_l / delta_l for l = 1..NW; the tail rows follow
-    __host__ __device__ static constexpr int row(int l)
-    {
-        int r = 0;
-        for (int j = 1; j < l; ++j) r += CFG::dim(j);
-        return r;
-    }
-    __host__ __device__ static constexpr int row8() { return row(CFG::NW + 1); }
-    __host__ __device__ static constexpr int rowz() { return row8() + kTailMid; }
-};
-
-// D -> ELU -> spill a_{L+1} -> (hi, lo) -> A
-template <class CFG, int L>
-__device__ __forceinline__ void tc_epilogue_to_a_spill(uint32_t lane_addr, float *act_gp, long long npx_pad)
-{
-    constexpr int N = CFG::N(L), KMAX = CFG::kmax();
-    float *dst = act_gp + (size_t)BwdRows<CFG>::row(L + 1) * npx_pad;
-#pragma unroll
-    for (int n0 = 0; n0 < N; n0 += 16) {
-        uint32_t r[16], lo[16];
-        tmem_ld<16>(lane_addr + 2 * KMAX + n0, r);
-        wait_ld();
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-            const float v = elu_fast(__uint_as_float(r[j]));
-            dst[(size_t)(n0 + j) * npx_pad] = v;
-            r[j] = __float_as_uint(v);
-            lo[j] = __float_as_uint(tf32_lo(v));
-        }
-        tmem_st<16>(lane_addr + n0, r);
-        tmem_st<16>(lane_addr + KMAX + n0, lo);
-    }
-}
 
 // MODE 0: sigmoid head (grad [B][1][hw]); 1: plane parameters (grad [B][4][hw]); 2: fused LPG (grad_depth)
 template <class CFG, int MODE, int R, int NWG>
@@ -259,6 +224,12 @@ __device__ __forceinline__ void dgrad_layer(const BwdArgs &ba, uint32_t wg_base,
         fence_after_sync();
         tc_issue_dgrad<CFG, L>(wg_base, swt, bar);
     }
+    float av[16];
+    if constexpr (L > 0) {                                        // first chunk of a_l travels under the MMAs
+        const float *act0 = ba.act + (size_t)BwdRows<CFG>::row(L) * npp + gp;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) av[j] = __ldcg(act0 + (size_t)j * npp);
+    }
     mbar_wait(bar, phase);
     phase ^= 1;
     fence_after_sync();
@@ -277,12 +248,15 @@ __device__ __forceinline__ void dgrad_layer(const BwdArgs &ba, uint32_t wg_base,
     } else {
         const float *act = ba.act + (size_t)BwdRows<CFG>::row(L) * npp + gp;
         float *del = ba.del + (size_t)BwdRows<CFG>::row(L) * npp + gp;
-#pragma unroll 1
+        // a_l chunks are fetched one chunk ahead of their use (the first one before the MMA wait)
+#pragma unroll
         for (int n0 = 0; n0 < NP; n0 += 16) {
             uint32_t r[16], lo[16];
-            float av[16];
+            float nx[16];
+            if (n0 + 16 < NP) {
 #pragma unroll
-            for (int j = 0; j < 16; ++j) av[j] = __ldcg(act + (size_t)(n0 + j) * npp);
+                for (int j = 0; j < 16; ++j) nx[j] = __ldcg(act + (size_t)(n0 + 16 + j) * npp);
+            }
             tmem_ld<16>(lane_addr + 2 * KMAX + n0, r);
             wait_ld();
 #pragma unroll
@@ -294,11 +268,18 @@ __device__ __forceinline__ void dgrad_layer(const BwdArgs &ba, uint32_t wg_base,
             }
             tmem_st<16>(lane_addr + n0, r);
             tmem_st<16>(lane_addr + KMAX + n0, lo);
+            if (n0 + 16 < NP) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) av[j] = nx[j];
+            }
         }
     }
 }
 
-template <class CFG, int NWG>
+// TM (tail mode): -1 = delta_16 was left in the workspace by K1; 0 / 1 = stash backward -- the kernel
+// starts from the stashed a16, a8 and the gradient of the head output (0: [B][1][hw]) or of the plane
+// parameters (1: [B][4][hw]) and back-propagates through the SIMT tail itself.
+template <class CFG, int NWG, int TM>
 __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_dgrad_kernel(BwdArgs ba)
 {
     constexpr int KMAX = DgradCfg<CFG>::kmax(), NMAX = DgradCfg<CFG>::nmax();
@@ -306,12 +287,19 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_dgrad_kernel(BwdArgs 
     constexpr int IMG = CFG::tail_off();          // floats of transposed images
     static_assert(NWG * COLS <= 512, "TMEM budget");
     extern __shared__ __align__(128) float smem[];
+    constexpr int TAILW = kTailMid * kTailIn + 3 * kTailMid;   // raw W4 [8][16], W5 [LAST][8]
     float *swt = smem;
-    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + IMG);
+    float *stw = smem + IMG;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(stw + TAILW);
     uint32_t *slot = reinterpret_cast<uint32_t *>(bars + NWG);
     const int tid = threadIdx.x, wg = tid / kTile, t = tid % kTile;
     for (int i = tid * 4; i < IMG; i += NWG * kTile * 4)
         *reinterpret_cast<float4 *>(swt + i) = __ldg(reinterpret_cast<const float4 *>(ba.wpack_t + i));
+    if constexpr (TM >= 0) {
+        constexpr int LAST = TM == 0 ? 1 : 3;
+        for (int i = tid; i < kTailMid * kTailIn; i += NWG * kTile) stw[i] = __ldg(ba.w4 + i);
+        for (int i = tid; i < LAST * kTailMid; i += NWG * kTile) stw[kTailMid * kTailIn + i] = __ldg(ba.w5 + i);
+    }
     fence_smem_to_async();
     if (tid < 32) tmem_alloc(slot, 512);
     if (tid == 0) {
@@ -334,13 +322,78 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_dgrad_kernel(BwdArgs 
         const bool valid = bb < ba.a.B && pp < ba.a.hw;
         const int b = valid ? bb : 0;
         const int p = valid ? pp : 0;
-        {
+        if constexpr (TM < 0) {
             const float *d16 = ba.del + (size_t)BwdRows<CFG>::row(CFG::NW) * npp + gp;
             uint32_t hi[16], lo[16];
 #pragma unroll
             for (int j = 0; j < 16; ++j) hi[j] = __float_as_uint(__ldcg(d16 + (size_t)j * npp));
 #pragma unroll
             for (int j = 0; j < 16; ++j) lo[j] = __float_as_uint(tf32_lo(__uint_as_float(hi[j])));
+            tmem_st<16>(lane_addr, hi);
+            tmem_st<16>(lane_addr + KMAX, lo);
+        } else {
+            constexpr int LAST = TM == 0 ? 1 : 3;
+            const TcArgs &a = ba.a;
+            const float *tw = stw, *w5 = stw + kTailMid * kTailIn;
+            const float *a16p = ba.act + (size_t)BwdRows<CFG>::row(CFG::NW) * npp + gp;
+            const float *a8p = ba.act + (size_t)BwdRows<CFG>::row8() * npp + gp;
+            float a16[kTailIn], a8[kTailMid], z[LAST], g[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int j = 0; j < kTailIn; ++j) a16[j] = __ldcg(a16p + (size_t)j * npp);
+#pragma unroll
+            for (int j = 0; j < kTailMid; ++j) a8[j] = __ldcg(a8p + (size_t)j * npp);
+            if (valid) {
+                if constexpr (TM == 0) {
+                    g[0] = __ldcs(a.grad + (size_t)b * a.hw + p);
+                } else {
+                    const float *gq = a.grad + (size_t)b * 4 * a.hw + p;
+                    g[0] = __ldcg(gq); g[1] = __ldcg(gq + a.hw); g[2] = __ldcg(gq + (size_t)2 * a.hw); g[3] = __ldcg(gq + (size_t)3 * a.hw);
+                }
+            }
+            tail_logits<LAST>(w5, a8, z);
+            float dz[3] = {0.f, 0.f, 0.f};
+            if constexpr (TM == 0) {
+                const float sg = sigmoidf(z[0]);
+                dz[0] = g[0] * sg * (1.f - sg);
+            } else {
+                const PlaneFwd pl = plane_from_logits(z[0], z[1], z[2], a.max_depth);
+                if (valid) plane_bwd(pl, g[0], g[1], g[2], g[3], a.max_depth, dz);
+            }
+            float d8[kTailMid], d16[kTailIn];
+#pragma unroll
+            for (int o = 0; o < kTailMid; ++o) {
+                float sm = 0.f;
+#pragma unroll
+                for (int j = 0; j < LAST; ++j) sm = fmaf(w5[j * kTailMid + o], dz[j], sm);
+                d8[o] = sm * elu_grad_from_out(a8[o]);
+            }
+#pragma unroll
+            for (int c = 0; c < kTailIn; ++c) d16[c] = 0.f;
+#pragma unroll
+            for (int o = 0; o < kTailMid; ++o) {
+#pragma unroll
+                for (int c = 0; c < kTailIn; c += 4) {
+                    const float4 w4 = *reinterpret_cast<const float4 *>(tw + o * kTailIn + c);
+                    d16[c] = fmaf(w4.x, d8[o], d16[c]); d16[c + 1] = fmaf(w4.y, d8[o], d16[c + 1]);
+                    d16[c + 2] = fmaf(w4.z, d8[o], d16[c + 2]); d16[c + 3] = fmaf(w4.w, d8[o], d16[c + 3]);
+                }
+            }
+            float *del_gp = ba.del + gp;
+            float *dz_dst = del_gp + (size_t)BwdRows<CFG>::rowz() * npp;
+#pragma unroll
+            for (int j = 0; j < LAST; ++j) dz_dst[(size_t)j * npp] = dz[j];
+            float *d8_dst = del_gp + (size_t)BwdRows<CFG>::row8() * npp;
+#pragma unroll
+            for (int j = 0; j < kTailMid; ++j) d8_dst[(size_t)j * npp] = d8[j];
+            float *d16_dst = del_gp + (size_t)BwdRows<CFG>::row(CFG::NW) * npp;
+            uint32_t hi[16], lo[16];
+#pragma unroll
+            for (int j = 0; j < kTailIn; ++j) {
+                const float v = d16[j] * elu_grad_from_out(a16[j]);
+                d16_dst[(size_t)j * npp] = v;
+                hi[j] = __float_as_uint(v);
+                lo[j] = __float_as_uint(tf32_lo(v));
+            }
             tmem_st<16>(lane_addr, hi);
             tmem_st<16>(lane_addr + KMAX, lo);
         }
@@ -642,6 +695,12 @@ static int build_wgrad_plan(const ChainParams &cp, WPlan &pl, const float *x, fl
     return BTS_OK;
 }
 
+template <class CFG, int NWG>
+static constexpr size_t dgrad_smem_bytes()
+{
+    return sizeof(float) * (CFG::tail_off() + kTailMid * kTailIn + 3 * kTailMid) + 8 * NWG + 16;
+}
+
 template <class CFG, int MODE, int R, int NWG1, int NWG2>
 static int launch_bwd_cfg(const ChainParams &cp, const TcArgs &a, char *ws, int sms, cudaStream_t s)
 {
@@ -679,8 +738,8 @@ static int launch_bwd_cfg(const ChainParams &cp, const TcArgs &a, char *ws, int 
         if (int e2 = check_launch("chain_tc_bwd1")) return e2;
     }
     {
-        auto k2 = chain_tc_dgrad_kernel<CFG, NWG2>;
-        const size_t smem = sizeof(float) * CFG::tail_off() + 8 * NWG2 + 16;
+        auto k2 = chain_tc_dgrad_kernel<CFG, NWG2, -1>;
+        const size_t smem = dgrad_smem_bytes<CFG, NWG2>();
         cudaError_t e = cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
         long long grid = (ntiles + NWG2 - 1) / NWG2;
@@ -707,6 +766,104 @@ static int launch_bwd_cfg(const ChainParams &cp, const TcArgs &a, char *ws, int 
         if (int e2 = launch_wreduce(cp, partials, (int)grid, pl.total_w, s)) return e2;
     }
     return BTS_OK;
+}
+
+// ---- stash backward: the forward left a_1 .. a8 (and plane_eq for the fused stage) in the caller's stash,
+// so K1 disappears: [LPG block reduction at full parallelism ->] tail backward + dgrad -> wgrad -> reduce.
+int launch_lpg_bwd(const float *, const float *, float *, int, int, int, int, float, cudaStream_t);
+bool fused_bwd_supported(const ChainParams &);
+bool tc_supported(const ChainParams &);
+
+bool tc_stash_supported(const ChainParams &cp, int hw, const void *x)
+{
+    return tc_supported(cp) && !fused_bwd_supported(cp) && wgrad_tma_supported(cp, hw, x);
+}
+
+static size_t stash_act_rows(const ChainParams &cp)
+{
+    size_t ra = 0;
+    for (int l = 1; l < cp.n_layers; ++l) ra += cp.dims[l];
+    return ra;
+}
+
+size_t tc_stash_bytes(const ChainParams &cp, int B, int hw)
+{
+    const long long npp = pad128((long long)B * pad32(hw));
+    return sizeof(float) * (stash_act_rows(cp) * (size_t)npp + (cp.is_final ? 0 : (size_t)4 * B * hw));
+}
+
+// point the TcArgs at the stash; with `clear`, zero the activation rows when the padded pixel axis has
+// columns no forward thread writes (the weight-gradient MMAs read whole rows)
+int tc_stash_bind(const ChainParams &cp, TcArgs &a, void *stash, bool clear, cudaStream_t s)
+{
+    a.stash_hw_pad = pad32(a.hw);
+    a.stash_npp = pad128((long long)a.B * a.stash_hw_pad);
+    a.stash_act = static_cast<float *>(stash);
+    a.stash_pe = cp.is_final ? nullptr : a.stash_act + stash_act_rows(cp) * (size_t)a.stash_npp;
+    if (clear && a.stash_npp != a.npx) {
+        cudaError_t e = cudaMemsetAsync(stash, 0, sizeof(float) * stash_act_rows(cp) * (size_t)a.stash_npp, s);
+        if (e != cudaSuccess) return set_error((int)e, "cudaMemsetAsync(stash): %s", cudaGetErrorString(e));
+    }
+    return BTS_OK;
+}
+
+template <class CFG, int TM, int NWG2>
+static int launch_bwd_stash_cfg(const ChainParams &cp, const TcArgs &a, int r, char *ws, int sms, cudaStream_t s)
+{
+    if constexpr (!kStashCfg<CFG>) {
+        return set_error(BTS_ERR_UNSUPPORTED, "chain does not stash");
+    } else {
+        float *wpack_t = reinterpret_cast<float *>(ws + tc_pack_bytes());
+        const long long npp = a.stash_npp;
+        int ra, rd, tw;
+        bwd_rows(cp, &ra, &rd, &tw);
+        float *scratch = reinterpret_cast<float *>(ws + 2 * tc_pack_bytes());   // the recompute path's a_l rows: free here
+        float *del = scratch + (size_t)ra * npp;
+        float *partials = del + (size_t)rd * npp;
+
+        tc_pack_weights_t_kernel<CFG><<<16, 256, 0, s>>>(cp, wpack_t);
+        if (int e = check_launch("tc_pack_weights_t")) return e;
+
+        BwdArgs ba;
+        ba.a = a;
+        ba.wpack_t = wpack_t;
+        ba.act = a.stash_act; ba.del = del; ba.npx_pad = npp; ba.hw_pad = a.stash_hw_pad;
+        ba.w4 = cp.W[CFG::NW]; ba.w5 = cp.W[CFG::NW + 1];
+        if (TM == 1 && r > 0) {              // grad_depth -> gradient of the plane parameters [B][4][hw]
+            if (int e = launch_lpg_bwd(a.grad, a.stash_pe, scratch, a.B, a.h, a.w, r, a.eps, s)) return e;
+            ba.a.grad = scratch;
+        }
+        const long long ntiles = npp / kTile;
+        auto k2 = chain_tc_dgrad_kernel<CFG, NWG2, TM>;
+        const size_t smem = dgrad_smem_bytes<CFG, NWG2>();
+        cudaError_t e = cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        long long grid = (ntiles + NWG2 - 1) / NWG2;
+        if (grid > sms) grid = sms;
+        k2<<<(unsigned)grid, NWG2 * kTile, smem, s>>>(ba);
+        if (int e2 = check_launch("chain_tc_dgrad")) return e2;
+        if (cp.gW[0] != nullptr)
+            return launch_wgrad_tma(cp, a.x, a.stash_act, del, partials, a.B, a.hw, a.stash_hw_pad, npp, sms, s);
+        return BTS_OK;
+    }
+}
+
+template <class CFG, int NWG2>
+static int dispatch_bwd_stash(const ChainParams &cp, const TcArgs &a, int mode, int r, char *ws, int sms, cudaStream_t s)
+{
+    if (mode == 0) return launch_bwd_stash_cfg<CFG, 0, NWG2>(cp, a, 0, ws, sms, s);
+    return launch_bwd_stash_cfg<CFG, 1, NWG2>(cp, a, mode == 2 ? r : 0, ws, sms, s);
+}
+
+// same modes as launch_chain_tc_bwd; a.stash_* must be bound to the buffer the forward filled
+int launch_chain_tc_bwd_stash(const ChainParams &cp, const TcArgs &a, int mode, int r, void *ws, int sms, cudaStream_t s)
+{
+    char *w = static_cast<char *>(ws);
+    if (cfg_matches<Cfg128_128>(cp)) return dispatch_bwd_stash<Cfg128_128, 1>(cp, a, mode, r, w, sms, s);
+    if (cfg_matches<Cfg128_64>(cp)) return dispatch_bwd_stash<Cfg128_64, 2>(cp, a, mode, r, w, sms, s);
+    if (cfg_matches<Cfg64_64>(cp)) return dispatch_bwd_stash<Cfg64_64, 2>(cp, a, mode, r, w, sms, s);
+    if (cfg_matches<Cfg32_32>(cp)) return dispatch_bwd_stash<Cfg32_32, 3>(cp, a, mode, r, w, sms, s);
+    return set_error(BTS_ERR_UNSUPPORTED, "chain does not stash");
 }
 
 template <class CFG, int NWG1, int NWG2>

@@ -12,8 +12,6 @@
 
 namespace bts {
 
-
-
 // PREFETCH: the next tile's features travel global -> shared with cp.async while the current tile is
 // computed (needs D0*512 B of shared memory per warpgroup next to the weight images).
 template <class CFG, int R, bool FINAL, int NWG, bool PREFETCH>
@@ -78,6 +76,12 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
         const int b = valid ? (int)(gp / a.hw) : 0;
         const int p = valid ? (int)(gp - (long long)b * a.hw) : 0;
         const float *xp = a.x + (size_t)b * D0 * a.hw + p;
+        bool stash = false;
+        float *act_gp = nullptr;
+        if constexpr (kStashCfg<CFG>) {
+            stash = valid && a.stash_act != nullptr;
+            act_gp = a.stash_act + (long long)b * a.stash_hw_pad + p;
+        }
         // features -> (hi, lo) -> TMEM A operand
         if constexpr (PREFETCH) {
             cp_async_wait_all();
@@ -112,15 +116,18 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
         // wide layers
         tc_run_layer<CFG, 0>(wg_base, sw, bar, phase, wg, t);
         if constexpr (CFG::NW > 1) {
-            tc_epilogue_to_a<CFG, 0>(lane_addr);
+            if constexpr (kStashCfg<CFG>) tc_epilogue_to_a_spill<CFG, 0>(lane_addr, act_gp, a.stash_npp, stash);
+            else tc_epilogue_to_a<CFG, 0>(lane_addr);
             tc_run_layer<CFG, 1>(wg_base, sw, bar, phase, wg, t);
         }
         if constexpr (CFG::NW > 2) {
-            tc_epilogue_to_a<CFG, 1>(lane_addr);
+            if constexpr (kStashCfg<CFG>) tc_epilogue_to_a_spill<CFG, 1>(lane_addr, act_gp, a.stash_npp, stash);
+            else tc_epilogue_to_a<CFG, 1>(lane_addr);
             tc_run_layer<CFG, 2>(wg_base, sw, bar, phase, wg, t);
         }
         if constexpr (CFG::NW > 3) {
-            tc_epilogue_to_a<CFG, 2>(lane_addr);
+            if constexpr (kStashCfg<CFG>) tc_epilogue_to_a_spill<CFG, 2>(lane_addr, act_gp, a.stash_npp, stash);
+            else tc_epilogue_to_a<CFG, 2>(lane_addr);
             tc_run_layer<CFG, 3>(wg_base, sw, bar, phase, wg, t);
         }
         float a16[kTailIn], a8[kTailMid], z[LAST];
@@ -132,6 +139,16 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
             for (int j = 0; j < 16; ++j) a16[j] = elu_fast(__uint_as_float(r[j]));
         }
         tail_forward<LAST>(tw, a16, a8, z);
+        if constexpr (kStashCfg<CFG>) {
+            if (stash) {
+                float *d16 = act_gp + (size_t)BwdRows<CFG>::row(CFG::NW) * a.stash_npp;
+#pragma unroll
+                for (int j = 0; j < kTailIn; ++j) d16[(size_t)j * a.stash_npp] = a16[j];
+                float *d8 = act_gp + (size_t)BwdRows<CFG>::row8() * a.stash_npp;
+#pragma unroll
+                for (int j = 0; j < kTailMid; ++j) d8[(size_t)j * a.stash_npp] = a8[j];
+            }
+        }
         if constexpr (FINAL) {
             if (valid) a.out[gp] = sigmoidf(z[0]);
         } else {
@@ -139,6 +156,12 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
             if (a.out != nullptr && valid) {
                 float *o = a.out + (size_t)b * 4 * a.hw + p;
                 o[0] = pl.n1; o[(size_t)a.hw] = pl.n2; o[(size_t)2 * a.hw] = pl.n3; o[(size_t)3 * a.hw] = pl.n4;
+            }
+            if constexpr (kStashCfg<CFG>) {
+                if (stash && a.stash_pe != nullptr) {
+                    float *o = a.stash_pe + (size_t)b * 4 * a.hw + p;
+                    o[0] = pl.n1; o[(size_t)a.hw] = pl.n2; o[(size_t)2 * a.hw] = pl.n3; o[(size_t)3 * a.hw] = pl.n4;
+                }
             }
             if (a.depth != nullptr) key = min(key, lpg_expand<R>(a, pl.n1, pl.n2, pl.n3, pl.n4, gp, valid, lane));
         }

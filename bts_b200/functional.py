@@ -63,6 +63,27 @@ def _workspace(dims, B, h, w, r, device):
     return ws, ws.data_ptr(), n
 
 
+_STASH = {"on": True}
+
+
+def set_stash(on):
+    """Keep (default) or drop the activation stash of the wide chains; without it their backward recomputes
+    the chain from x (less memory, one more kernel). Returns the previous setting."""
+    prev = _STASH["on"]
+    _STASH["on"] = bool(on)
+    return prev
+
+
+def _stash(dims, B, h, w, device, wanted):
+    """Activation stash for chains whose backward would otherwise recompute them in a separate kernel
+    (include/bts_b200.h, ABI 2). (tensor | None, pointer, bytes); 0 bytes when nothing is stashed."""
+    n = _cabi.lib().bts_stash_bytes(_cabi.int_array(dims), len(dims) - 1, B, h, w) if (wanted and _STASH["on"]) else 0
+    if n == 0:
+        return None, None, 0
+    st = torch.empty((n + 3) // 4, dtype=torch.float32, device=device)
+    return st, st.data_ptr(), n
+
+
 class _LPG(torch.autograd.Function):
     """local_planar_guidance.forward (pytorch/bts.py:149-173) and its autograd backward."""
 
@@ -108,11 +129,13 @@ class _Reduc(torch.autograd.Function):
         B, _, h, w = x.shape
         out = torch.empty((B, 1 if is_final else 4, h, w), dtype=torch.float32, device=x.device)
         wsb, wsp, wsn = _workspace(dims, B, h, w, 0, x.device)
+        st, stp, stn = _stash(dims, B, h, w, x.device, any(ctx.needs_input_grad))
         with torch.cuda.device(x.device):
-            _cabi.check(_cabi.lib().bts_reduc_fwd(x.data_ptr(), _cabi.ptr_array([t.data_ptr() for t in ws]),
-                                                  _cabi.int_array(dims), len(ws), int(bool(is_final)),
-                                                  float(max_depth), B, h, w, out.data_ptr(), wsp, wsn, _stream()),
-                        "bts_reduc_fwd")
+            _cabi.check(_cabi.lib().bts_reduc_fwd_stash(
+                x.data_ptr(), _cabi.ptr_array([t.data_ptr() for t in ws]), _cabi.int_array(dims), len(ws),
+                int(bool(is_final)), float(max_depth), B, h, w, out.data_ptr(), wsp, wsn, stp, stn, _stream()),
+                "bts_reduc_fwd")
+        ctx.stash = st
         ctx.save_for_backward(x, *ws)
         ctx.cfg = (float(max_depth), bool(is_final), dims, [tuple(t.shape) for t in weights])
         return out
@@ -128,11 +151,13 @@ class _Reduc(torch.autograd.Function):
         gx = torch.empty_like(x) if need_x else None
         gws = _zero_grads(ws) if need_w else None
         wsb, wsp, wsn = _workspace(dims, B, h, w, 0, x.device)
+        st = ctx.stash
         with torch.cuda.device(x.device):
-            _cabi.check(_cabi.lib().bts_reduc_bwd(
+            _cabi.check(_cabi.lib().bts_reduc_bwd_stash(
                 x.data_ptr(), _cabi.ptr_array([t.data_ptr() for t in ws]), _cabi.int_array(dims), len(ws),
                 int(is_final), max_depth, B, h, w, grad_out.data_ptr(), gx.data_ptr() if need_x else None,
-                _cabi.ptr_array([t.data_ptr() for t in gws]) if need_w else None, wsp, wsn, _stream()),
+                _cabi.ptr_array([t.data_ptr() for t in gws]) if need_w else None, wsp, wsn,
+                st.data_ptr() if st is not None else None, st.numel() * 4 if st is not None else 0, _stream()),
                 "bts_reduc_bwd")
         gw_out = [g.view(s) for g, s in zip(gws, shapes)] if need_w else [None] * len(ws)
         return (gx, None, None, *gw_out)
@@ -154,11 +179,13 @@ class _ReducLPG(torch.autograd.Function):
         abs_min = torch.full((), float("inf"), dtype=torch.float32, device=x.device)
         plane_eq = torch.empty((B, 4, h, w), dtype=torch.float32, device=x.device) if want_plane_eq else None
         wsb, wsp, wsn = _workspace(dims, B, h, w, r, x.device)
+        st, stp, stn = _stash(dims, B, h, w, x.device, any(ctx.needs_input_grad))
         with torch.cuda.device(x.device):
-            _cabi.check(_cabi.lib().bts_reduc_lpg_fwd(
+            _cabi.check(_cabi.lib().bts_reduc_lpg_fwd_stash(
                 x.data_ptr(), _cabi.ptr_array([t.data_ptr() for t in ws]), _cabi.int_array(dims), len(ws),
                 float(max_depth), B, h, w, r, EPS, plane_eq.data_ptr() if want_plane_eq else None,
-                depth.data_ptr(), abs_min.data_ptr(), wsp, wsn, _stream()), "bts_reduc_lpg_fwd")
+                depth.data_ptr(), abs_min.data_ptr(), wsp, wsn, stp, stn, _stream()), "bts_reduc_lpg_fwd")
+        ctx.stash = st
         ctx.save_for_backward(x, *ws)
         ctx.cfg = (float(max_depth), r, dims, [tuple(t.shape) for t in weights])
         ctx.mark_non_differentiable(abs_min)
@@ -178,11 +205,13 @@ class _ReducLPG(torch.autograd.Function):
         gx = torch.empty_like(x) if need_x else None
         gws = _zero_grads(ws) if need_w else None
         wsb, wsp, wsn = _workspace(dims, B, h, w, r, x.device)
+        st = ctx.stash
         with torch.cuda.device(x.device):
-            _cabi.check(_cabi.lib().bts_reduc_lpg_bwd(
+            _cabi.check(_cabi.lib().bts_reduc_lpg_bwd_stash(
                 grad_depth.data_ptr(), x.data_ptr(), _cabi.ptr_array([t.data_ptr() for t in ws]),
                 _cabi.int_array(dims), len(ws), max_depth, B, h, w, r, EPS, gx.data_ptr() if need_x else None,
-                _cabi.ptr_array([t.data_ptr() for t in gws]) if need_w else None, wsp, wsn, _stream()),
+                _cabi.ptr_array([t.data_ptr() for t in gws]) if need_w else None, wsp, wsn,
+                st.data_ptr() if st is not None else None, st.numel() * 4 if st is not None else 0, _stream()),
                 "bts_reduc_lpg_bwd")
         gw_out = [g.view(s) for g, s in zip(gws, shapes)] if need_w else [None] * len(ws)
         return (gx, None, None, None, *gw_out)

@@ -38,7 +38,7 @@ extern "C" {
 #define BTS_API
 #endif
 
-#define BTS_ABI_VERSION 1
+#define BTS_ABI_VERSION 2
 #define BTS_MAX_LAYERS 8      /* reduction_1x1 builds at most log2(num_out) layers */
 #define BTS_MAX_CHANNELS 512  /* per layer */
 
@@ -127,6 +127,34 @@ BTS_API int bts_reduc_lpg_bwd(const float *grad_depth, const float *x, const flo
                       int n_layers, float max_depth, int B, int h, int w, int r, float eps,
                       float *grad_x, float *const *grad_W,
                       void *ws, size_t ws_bytes, void *stream);
+
+/*
+ * Activation stash (ABI 2). PyTorch autograd keeps every intermediate of reduction_1x1 alive for the
+ * backward pass (pytorch/bts.py:124-136 under autograd); the entry points above keep nothing and
+ * recompute. The *_stash variants make that a per-call choice: a forward call that is handed a
+ * `stash` buffer of bts_stash_bytes() bytes leaves the chain's ELU outputs (and, for the fused stage,
+ * plane_eq) there, and the backward call that is handed the SAME buffer, x, W and shape skips the
+ * recompute. bts_stash_bytes() == 0 means the chain is always recomputed (narrow chains, whose
+ * one-pass backward is cheaper than the extra traffic; chains outside the tensor-core path).
+ * stash == NULL / too small / misaligned (16 B) -> exactly the behaviour of the plain entry points.
+ */
+BTS_API size_t bts_stash_bytes(const int *dims, int n_layers, int B, int h, int w);
+
+BTS_API int bts_reduc_fwd_stash(const float *x, const float *const *W, const int *dims, int n_layers, int is_final,
+                        float max_depth, int B, int h, int w, float *out,
+                        void *ws, size_t ws_bytes, void *stash, size_t stash_bytes, void *stream);
+BTS_API int bts_reduc_bwd_stash(const float *x, const float *const *W, const int *dims, int n_layers, int is_final,
+                        float max_depth, int B, int h, int w, const float *grad_out,
+                        float *grad_x, float *const *grad_W,
+                        void *ws, size_t ws_bytes, const void *stash, size_t stash_bytes, void *stream);
+BTS_API int bts_reduc_lpg_fwd_stash(const float *x, const float *const *W, const int *dims, int n_layers,
+                        float max_depth, int B, int h, int w, int r, float eps,
+                        float *plane_eq_out, float *depth, float *abs_min,
+                        void *ws, size_t ws_bytes, void *stash, size_t stash_bytes, void *stream);
+BTS_API int bts_reduc_lpg_bwd_stash(const float *grad_depth, const float *x, const float *const *W, const int *dims,
+                        int n_layers, float max_depth, int B, int h, int w, int r, float eps,
+                        float *grad_x, float *const *grad_W,
+                        void *ws, size_t ws_bytes, const void *stash, size_t stash_bytes, void *stream);
 
 #ifdef __cplusplus
 }

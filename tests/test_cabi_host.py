@@ -17,7 +17,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(raw, n), "libbts_b200.so does not export " + n
     assert set(names) == set(_cabi._SIGNATURES), "ctypes table and header disagree"
-    assert _cabi.lib().bts_abi_version() == 1
+    assert _cabi.lib().bts_abi_version() == _cabi.ABI_VERSION
 
 
 def test_argument_validation_needs_no_gpu():

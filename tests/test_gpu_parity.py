@@ -334,3 +334,50 @@ def test_tensor_core_path_vs_generic_path(cfg):
     close_peak(got[2], ref[2].cpu().numpy())
     for a, b in zip(got[3], ref[3]):
         close_peak(a, b.cpu().numpy())
+
+
+@pytest.mark.parametrize("cfg", [(128, 128, False, 8, 3, 20, 28, True), (128, 128, False, 8, 3, 19, 23, False),
+                                 (128, 64, False, 4, 2, 36, 44, True), (64, 64, False, 8, 1, 16, 24, True),
+                                 (32, 32, False, 4, 1, 40, 40, True), (128, 128, False, 0, 2, 24, 20, True),
+                                 (64, 64, True, 0, 2, 12, 36, True), (128, 64, False, 1, 1, 8, 16, True),
+                                 (64, 32, False, 2, 2, 32, 32, False)],
+                         ids=lambda c: "x".join(map(str, c)))
+def test_stash_backward_vs_recompute_backward(cfg):
+    """ABI 2: the forward may leave the wide chains' activations in a stash so that backward skips the
+    recompute. Both backward routes must agree to rounding; shapes cover padded pixel axes (hw % 32 != 0),
+    hw % 4 != 0 (no stash: identical route), the plain reduction (r = 0) and a wide sigmoid head."""
+    import bts_b200
+    from bts_b200 import _cabi, functional as Fn
+    num_in, num_out, is_final, r, B, h, w, stashes = cfg
+    dims = bts_b200.chain_channels(num_in, num_out, is_final)
+    nbytes = _cabi.lib().bts_stash_bytes(_cabi.int_array(dims), len(dims) - 1, B, h, w)
+    assert (nbytes > 0) == stashes
+    torch.manual_seed(11)
+    red = bts_b200.reduction_1x1(num_in, num_out, 10.0, is_final).cuda()
+    for p in red.parameters():
+        torch.nn.init.xavier_uniform_(p)
+    x = torch.randn(B, num_in, h, w, device="cuda")
+    if is_final:
+        g = torch.randn(B, 1, h, w, device="cuda")
+    elif r == 0:
+        g = torch.randn(B, 4, h, w, device="cuda")
+    else:
+        g = torch.randn(B, h * r, w * r, device="cuda")
+
+    def run():
+        xx = x.clone().requires_grad_(True)
+        red.zero_grad()
+        out = red(xx) if (is_final or r == 0) else bts_b200.fused_stage(red, bts_b200.local_planar_guidance(r), xx)
+        out.backward(g)
+        return out.detach(), xx.grad, [p.grad.clone() for p in red.parameters()]
+
+    prev = Fn.set_stash(False)
+    try:
+        ref = run()
+    finally:
+        Fn.set_stash(prev)
+    got = run()
+    assert torch.equal(got[0], ref[0])                      # the stash does not touch the forward result
+    close_peak(got[1], ref[1].cpu().numpy())
+    for a, b in zip(got[2], ref[2]):
+        close_peak(a, b.cpu().numpy())
