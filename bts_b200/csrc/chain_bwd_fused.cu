@@ -100,7 +100,7 @@ struct FusedLayout {
 //                                 NW == 2: F0, F1, DG1, WT(h0), DG0, WT(h1), WX(h0), WX(h1).
 struct IssuerWg {            // per-warpgroup progress of the issuer (scalars: must stay in registers)
     int cmd, rph, sph0, sph1;
-    long long left;
+    int left;
 };
 
 // one poll of warpgroup G: issue its next command if the operands are ready. Returns true on progress.
@@ -150,15 +150,15 @@ __device__ __forceinline__ bool fused_issuer_step(IssuerWg &w, const float *sw, 
 
 template <class CFG, int MODE, int R, int NWG>
 __device__ __noinline__ void fused_issuer(const float *sw, const float *swt, uint32_t stage_addr, uint64_t *bars,
-                                             uint32_t tbase, long long ntiles)
+                                             uint32_t tbase, int ntiles)
 {
     static_assert(NWG >= 1 && NWG <= 3, "one to three warpgroups");
-    const long long stride = (long long)gridDim.x * NWG;
+    const int stride = (int)gridDim.x * NWG;
     auto tiles_of = [&](int g) {
-        const long long first = (long long)blockIdx.x * NWG + g;
-        return first < ntiles ? (ntiles - first + stride - 1) / stride : 0ll;
+        const int first = (int)blockIdx.x * NWG + g;
+        return first < ntiles ? (ntiles - first + stride - 1) / stride : 0;
     };
-    IssuerWg w0{0, 0, 0, 0, tiles_of(0)}, w1{0, 0, 0, 0, NWG > 1 ? tiles_of(1) : 0ll}, w2{0, 0, 0, 0, NWG > 2 ? tiles_of(2) : 0ll};
+    IssuerWg w0{0, 0, 0, 0, tiles_of(0)}, w1{0, 0, 0, 0, NWG > 1 ? tiles_of(1) : 0}, w2{0, 0, 0, 0, NWG > 2 ? tiles_of(2) : 0};
     uint32_t idle = 0;
     while (w0.left + w1.left + w2.left > 0) {
         bool progressed = fused_issuer_step<CFG, MODE, R, NWG, 0>(w0, sw, swt, stage_addr, bars, tbase);
@@ -268,8 +268,10 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
     __syncthreads();
     fence_after_sync();
 
-    const long long ntiles = (a.npx + kTile - 1) / kTile;
-    const long long stride = (long long)gridDim.x * NWG;
+    // 32-bit index arithmetic throughout (the C ABI rejects more than 2^31 - 1 low-res pixels)
+    const unsigned npx = (unsigned)a.npx, hw = (unsigned)a.hw;
+    const int ntiles = (int)((npx + kTile - 1) / kTile);
+    const int stride = (int)gridDim.x * NWG;
 
     if (tid >= NWG * kTile) {
         if (tid == NWG * kTile) fused_issuer<CFG, MODE, R, NWG>(sw, swt, smem_u32(stage), bars, tbase, ntiles);
@@ -302,17 +304,17 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
         float *xs_wg = xs_all + (size_t)g * (K0 + 4) * kTile;    // [channel][pixel] of the staged tile
         float *xs = xs_wg + t;                                    // this thread's pixel column
         float *gs = xs_wg + K0 * kTile + t * 4;                   // this pixel's gradient words
-        auto prefetch = [&](long long tl) {
-            const long long gp = tl * kTile + t;
-            const bool ok = tl < ntiles && gp < a.npx;
-            const int b = ok ? (int)((unsigned)gp / (unsigned)a.hw) : 0;
-            const int p = ok ? (int)gp - b * a.hw : 0;
+        auto prefetch = [&](int tl) {
+            const unsigned gp = (unsigned)tl * kTile + t;
+            const bool ok = tl < ntiles && gp < npx;
+            [[maybe_unused]] const int b = ok ? (int)(gp / hw) : 0;
+            [[maybe_unused]] const int p = ok ? (int)(gp - (unsigned)b * hw) : 0;
             {                                                     // 128-bit copies (host checks x_vec16), see chain_tc_fwd.cu
                 const int q = t & 31, cw = t >> 5;
-                const long long g0 = tl * kTile + 4 * q;
-                const bool okv = tl < ntiles && g0 < a.npx;
-                const int bn = okv ? (int)((unsigned)g0 / (unsigned)a.hw) : 0;
-                const int pn = okv ? (int)g0 - bn * a.hw : 0;
+                const unsigned g0 = (unsigned)tl * kTile + 4 * q;
+                const bool okv = tl < ntiles && g0 < npx;
+                const int bn = okv ? (int)(g0 / hw) : 0;
+                const int pn = okv ? (int)(g0 - (unsigned)bn * hw) : 0;
                 const float *xq = a.x + ((size_t)bn * K0 + cw) * a.hw + pn;
                 const uint32_t dst = smem_u32(xs_wg + cw * kTile + 4 * q);
 #pragma unroll
@@ -337,13 +339,13 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
             cp_async_commit();
         };
 
-        long long tile = (long long)blockIdx.x * NWG + g;
+        int tile = (int)blockIdx.x * NWG + g;
         prefetch(tile);
         for (; tile < ntiles; tile += stride) {
-            const long long gp = tile * kTile + t;
-            const bool valid = gp < a.npx;
-            const int b = valid ? (int)(gp / a.hw) : 0;
-            const int p = valid ? (int)(gp - (long long)b * a.hw) : 0;
+            const unsigned gp = (unsigned)tile * kTile + t;
+            const bool valid = gp < npx;
+            const int b = valid ? (int)(gp / hw) : 0;
+            const int p = valid ? (int)(gp - (unsigned)b * hw) : 0;
             // ---- x -> (hi, lo) -> TMEM A operand of layer 0; then the next tile's loads take off
             cp_async_wait_all();
             named_bar_sync(1 + g, kTile);                         // the tile was copied by all threads of the warpgroup
@@ -426,7 +428,7 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
                         }
                         gg[0] = -pl.n4 * acc.tu; gg[1] = -pl.n4 * acc.tv; gg[2] = -pl.n4 * acc.t; gg[3] = acc.s4;
                     } else {
-                        lpg_block_grad<R>(a, pl, gp, gg);
+                        lpg_block_grad<R>(a, pl, b, p, gg);
                     }
                     plane_bwd(pl, gg[0], gg[1], gg[2], gg[3], a.max_depth, dz);
                 }

@@ -196,21 +196,22 @@ __device__ __forceinline__ void tc_epilogue_to_a_spill(uint32_t lane_addr, float
 // ---- LPG expansion of this thread's plane (n1..n4) into depth; returns the abs_min key
 template <int R>
 __device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, float n3, float n4,
-                                          long long gp, bool valid, int lane)
+                                          unsigned gp, int b_own, int p_own, bool valid, int lane)
 {
+    // all index arithmetic is 32-bit: the C ABI rejects more than 2^31 - 1 low-res pixels
     int key = 0x7f800000;
     if constexpr (R == 8) {
         // two 512 B stores per output row and warp: lane L writes columns (L&1)*4..+3 of pixel 16*half + L/2
-        const long long gp0 = gp - lane;
+        const unsigned gp0 = gp - (unsigned)lane;
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
             const int src = half * 16 + (lane >> 1);
             const float m1 = __shfl_sync(0xffffffffu, n1, src), m2 = __shfl_sync(0xffffffffu, n2, src);
             const float m3 = __shfl_sync(0xffffffffu, n3, src), m4 = __shfl_sync(0xffffffffu, n4, src);
-            const long long gs = gp0 + src;
-            if (gs < a.npx) {
-                const int b = (int)(gs / a.hw);
-                const int rem = (int)(gs - (long long)b * a.hw);
+            const unsigned gs = gp0 + (unsigned)src;
+            if (gs < (unsigned)a.npx) {
+                const int b = (int)(gs / (unsigned)a.hw);
+                const int rem = (int)(gs - (unsigned)b * (unsigned)a.hw);
                 const int i = rem / a.w, j = rem - i * a.w;
                 const int q0 = (lane & 1) * 4;
                 const int Wd = a.w * 8;
@@ -234,8 +235,7 @@ __device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, f
             }
         }
     } else if (valid) {
-        const int b = (int)(gp / a.hw);
-        const int rem = (int)(gp - (long long)b * a.hw);
+        const int b = b_own, rem = p_own;
         const int i = rem / a.w, j = rem - i * a.w;
         const int Wd = a.w * R;
         float *out = a.depth + ((size_t)b * a.h + i) * R * (size_t)Wd + (size_t)j * R;
@@ -266,10 +266,8 @@ __device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, f
 
 // ---- upstream gradient of one low-res pixel in fused mode: reduce grad_depth over its R x R block
 template <int R>
-__device__ __forceinline__ void lpg_block_grad(const TcArgs &a, const PlaneFwd &pl, long long gp, float g[4])
+__device__ __forceinline__ void lpg_block_grad(const TcArgs &a, const PlaneFwd &pl, int b, int rem, float g[4])
 {
-    const int b = (int)(gp / a.hw);
-    const int rem = (int)(gp - (long long)b * a.hw);
     const int i = rem / a.w, j = rem - i * a.w;
     const int Wd = a.w * R;
     const float *gp0 = a.grad + ((size_t)b * a.h + i) * R * (size_t)Wd + (size_t)j * R;

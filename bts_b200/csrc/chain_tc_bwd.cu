@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_bwd1_kernel(BwdArgs b
                     const float *gq = a.grad + (size_t)b * 4 * a.hw + p;
                     g[0] = __ldcs(gq); g[1] = __ldcs(gq + a.hw); g[2] = __ldcs(gq + (size_t)2 * a.hw); g[3] = __ldcs(gq + (size_t)3 * a.hw);
                 } else {
-                    lpg_block_grad<R>(a, pl, gpt, g);
+                    lpg_block_grad<R>(a, pl, b, p, g);
                 }
                 plane_bwd(pl, g[0], g[1], g[2], g[3], a.max_depth, dz);
             }

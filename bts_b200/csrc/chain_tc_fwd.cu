@@ -51,36 +51,38 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
     const float *tw = sw + CFG::tail_off();
     int key = 0x7f800000;
 
-    const long long ntiles = (a.npx + kTile - 1) / kTile;
-    const long long stride = (long long)gridDim.x * NWG;
+    // 32-bit index arithmetic throughout (the C ABI rejects more than 2^31 - 1 low-res pixels)
+    const unsigned npx = (unsigned)a.npx, hw = (unsigned)a.hw;
+    const int ntiles = (int)((npx + kTile - 1) / kTile);
+    const int stride = (int)gridDim.x * NWG;
     float *xs_wg = xs_all + (size_t)wg * D0 * kTile;              // [channel][pixel] of the staged tile
     float *xs = xs_wg + t;                                        // this thread's pixel column
     // 128-bit copies: thread t moves pixels 4q..4q+3 (q = t%32) of channels t/32, t/32+4, ...; 4 pixels never
     // straddle two images because hw % 4 == 0 (the launcher picks the non-prefetching kernel otherwise).
-    auto prefetch = [&](long long tl) {
+    auto prefetch = [&](int tl) {
         const int q = t & 31, cw = t >> 5;
-        const long long g0 = tl * kTile + 4 * q;
-        const bool ok = tl < ntiles && g0 < a.npx;
-        const int bn = ok ? (int)((unsigned)g0 / (unsigned)a.hw) : 0;
-        const int pn = ok ? (int)g0 - bn * a.hw : 0;
+        const unsigned g0 = (unsigned)tl * kTile + 4 * q;
+        const bool ok = tl < ntiles && g0 < npx;
+        const int bn = ok ? (int)(g0 / hw) : 0;
+        const int pn = ok ? (int)(g0 - (unsigned)bn * hw) : 0;
         const float *xq = a.x + ((size_t)bn * D0 + cw) * a.hw + pn;
         const uint32_t dst = smem_u32(xs_wg + cw * kTile + 4 * q);
 #pragma unroll
         for (int i = 0; i < D0 / 4; ++i) cp_async16(dst + i * 4 * kTile * 4, xq + (size_t)i * 4 * a.hw, ok);
         cp_async_commit();
     };
-    if constexpr (PREFETCH) prefetch((long long)blockIdx.x * NWG + wg);
-    for (long long tile = (long long)blockIdx.x * NWG + wg; tile < ntiles; tile += stride) {
-        const long long gp = tile * kTile + t;
-        const bool valid = gp < a.npx;
-        const int b = valid ? (int)(gp / a.hw) : 0;
-        const int p = valid ? (int)(gp - (long long)b * a.hw) : 0;
+    if constexpr (PREFETCH) prefetch((int)blockIdx.x * NWG + wg);
+    for (int tile = (int)blockIdx.x * NWG + wg; tile < ntiles; tile += stride) {
+        const unsigned gp = (unsigned)tile * kTile + t;
+        const bool valid = gp < npx;
+        const int b = valid ? (int)(gp / hw) : 0;
+        const int p = valid ? (int)(gp - (unsigned)b * hw) : 0;
         const float *xp = a.x + (size_t)b * D0 * a.hw + p;
         bool stash = false;
         float *act_gp = nullptr;
         if constexpr (kStashCfg<CFG>) {
             stash = valid && a.stash_act != nullptr;
-            act_gp = a.stash_act + (long long)b * a.stash_hw_pad + p;
+            act_gp = a.stash_act + (size_t)b * a.stash_hw_pad + p;
         }
         // features -> (hi, lo) -> TMEM A operand
         if constexpr (PREFETCH) {
@@ -163,7 +165,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
                     o[0] = pl.n1; o[(size_t)a.hw] = pl.n2; o[(size_t)2 * a.hw] = pl.n3; o[(size_t)3 * a.hw] = pl.n4;
                 }
             }
-            if (a.depth != nullptr) key = min(key, lpg_expand<R>(a, pl.n1, pl.n2, pl.n3, pl.n4, gp, valid, lane));
+            if (a.depth != nullptr) key = min(key, lpg_expand<R>(a, pl.n1, pl.n2, pl.n3, pl.n4, gp, b, p, valid, lane));
         }
     }
     if constexpr (!FINAL) {
