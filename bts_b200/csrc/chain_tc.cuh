@@ -193,6 +193,89 @@ __device__ __forceinline__ void tc_epilogue_to_a_spill(uint32_t lane_addr, float
     }
 }
 
+// ---- chunked variants: the A operand region is AW columns wide (hi at [0,AW), lo at [AW,2AW), D at 2AW),
+// so a layer with K > AW input channels runs as K/AW rounds of MMAs that accumulate into the same D.
+// With AW = 64 a 128-channel chain needs 256 TMEM columns per warpgroup and two warpgroups fit.
+template <class CFG, int L, int AW, int KOFF, int KC>
+__device__ __forceinline__ void tc_issue_chunk(uint32_t wg_base, const float *sw, uint64_t *bar)
+{
+    constexpr int K = CFG::K(L), N = CFG::N(L);
+    constexpr uint32_t LBO = 128, SBO = (K / 4) * 128;
+    constexpr uint32_t idesc = idesc_tf32(kTile, N, 0, 0);
+    const uint32_t whi = smem_u32(sw + CFG::w_off(L));
+    const uint32_t wlo = whi + N * K * 4;
+    const uint32_t d = wg_base + 2 * AW;
+#pragma unroll
+    for (int k0 = 0; k0 < KC; k0 += 8)   // lo(a) * hi(W)
+        mma_tf32_ts(d, wg_base + AW + k0, smem_desc(whi + ((KOFF + k0) / 4) * LBO, LBO, SBO), idesc, (KOFF + k0) > 0);
+#pragma unroll
+    for (int k0 = 0; k0 < KC; k0 += 8)   // hi(a) * lo(W)
+        mma_tf32_ts(d, wg_base + k0, smem_desc(wlo + ((KOFF + k0) / 4) * LBO, LBO, SBO), idesc, 1);
+#pragma unroll
+    for (int k0 = 0; k0 < KC; k0 += 8)   // hi(a) * hi(W)
+        mma_tf32_ts(d, wg_base + k0, smem_desc(whi + ((KOFF + k0) / 4) * LBO, LBO, SBO), idesc, 1);
+    mma_commit(bar);
+}
+
+template <class CFG, int L, int AW, int KOFF, int KC>
+__device__ __forceinline__ void tc_run_chunk(uint32_t wg_base, const float *sw, uint64_t *bar, uint32_t &phase,
+                                             int wg, int t)
+{
+    wait_st();
+    fence_before_sync();
+    named_bar_sync(1 + wg, kTile);
+    if (t == 0) {
+        fence_after_sync();
+        tc_issue_chunk<CFG, L, AW, KOFF, KC>(wg_base, sw, bar);
+    }
+    mbar_wait(bar, phase);
+    phase ^= 1;
+    fence_after_sync();
+}
+
+// channels [C0, C0+KC) of a_{L+1} = ELU(D[C0 ..]) -> (hi, lo) -> A columns [0, KC); optionally to the stash rows
+template <class CFG, int L, int AW, int C0, int KC, bool SPILL>
+__device__ __forceinline__ void tc_epilogue_chunk(uint32_t lane_addr, float *act_gp, long long npx_pad, bool store)
+{
+    float *dst = SPILL ? act_gp + (size_t)(BwdRows<CFG>::row(L + 1) + C0) * npx_pad : nullptr;
+#pragma unroll
+    for (int n0 = 0; n0 < KC; n0 += 16) {
+        uint32_t r[16], lo[16];
+        tmem_ld<16>(lane_addr + 2 * AW + C0 + n0, r);
+        wait_ld();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const float v = elu_fast(__uint_as_float(r[j]));
+            if constexpr (SPILL) {
+                if (store) dst[(size_t)(n0 + j) * npx_pad] = v;
+            }
+            r[j] = __float_as_uint(v);
+            lo[j] = __float_as_uint(tf32_lo(v));
+        }
+        tmem_st<16>(lane_addr + n0, r);
+        tmem_st<16>(lane_addr + AW + n0, lo);
+    }
+}
+
+// layer L >= 1 from the previous layer's accumulator: K/AW rounds of (epilogue chunk, MMAs). The MMAs of
+// round 0 overwrite D[0, N): legal because round 0's epilogue has consumed D[0, AW) and N <= AW.
+template <class CFG, int L, int AW, bool SPILL>
+__device__ __forceinline__ void tc_layer_from_d(uint32_t wg_base, uint32_t lane_addr, const float *sw, uint64_t *bar,
+                                                uint32_t &phase, int wg, int t, float *act_gp, long long npx_pad, bool store)
+{
+    constexpr int K = CFG::K(L);
+    if constexpr (K <= AW) {
+        tc_epilogue_chunk<CFG, L - 1, AW, 0, K, SPILL>(lane_addr, act_gp, npx_pad, store);
+        tc_run_chunk<CFG, L, AW, 0, K>(wg_base, sw, bar, phase, wg, t);
+    } else {
+        static_assert(K == 2 * AW && CFG::N(L) <= AW, "two rounds, accumulator no wider than one round's inputs");
+        tc_epilogue_chunk<CFG, L - 1, AW, 0, AW, SPILL>(lane_addr, act_gp, npx_pad, store);
+        tc_run_chunk<CFG, L, AW, 0, AW>(wg_base, sw, bar, phase, wg, t);
+        tc_epilogue_chunk<CFG, L - 1, AW, AW, AW, SPILL>(lane_addr, act_gp, npx_pad, store);
+        tc_run_chunk<CFG, L, AW, AW, AW>(wg_base, sw, bar, phase, wg, t);
+    }
+}
+
 // ---- LPG expansion of this thread's plane (n1..n4) into depth; returns the abs_min key
 template <int R>
 __device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, float n3, float n4,

@@ -12,6 +12,7 @@
 //   K4 reduce : grad_W += sum of partials
 // Workspace rows are [channel][pixel] fp32 matrices padded to a multiple of 128 pixels.
 #include <cstring>
+#include <type_traits>
 
 #include "chain_tc.cuh"
 
@@ -28,15 +29,18 @@ struct BwdArgs {
 };
 
 // MODE 0: sigmoid head (grad [B][1][hw]); 1: plane parameters (grad [B][4][hw]); 2: fused LPG (grad_depth)
-template <class CFG, int MODE, int R, int NWG>
+// AW: width of the A operand region in TMEM, as in the forward kernel (the recompute follows the forward's
+// accumulation order exactly, so both see bit-identical activations)
+template <class CFG, int MODE, int R, int NWG, int AW>
 __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_bwd1_kernel(BwdArgs ba)
 {
     constexpr bool FINAL = (MODE == 0);
     constexpr int LAST = FINAL ? 1 : 3;
     constexpr int PACK = CFG::pack_floats(LAST);
-    constexpr int KMAX = CFG::kmax(), NMAX = CFG::nmax();
-    constexpr int COLS = 2 * KMAX + NMAX;
+    constexpr int NMAX = CFG::nmax();
+    constexpr int COLS = 2 * AW + NMAX;
     constexpr int D0 = CFG::dim(0);
+    constexpr int KC0 = D0 < AW ? D0 : AW;
     static_assert(NWG * COLS <= 512, "TMEM budget");
     const TcArgs &a = ba.a;
 
@@ -69,7 +73,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_bwd1_kernel(BwdArgs b
     const long long ntiles = npp / kTile;
     for (long long tile = (long long)blockIdx.x * NWG + wg; tile < ntiles; tile += (long long)gridDim.x * NWG) {
         const long long gp = tile * kTile + t;                    // index on the (per image padded) workspace pixel axis
-        const int bb = (int)(gp / ba.hw_pad), pp = (int)(gp - (long long)bb * ba.hw_pad);
+        const int bb = (int)((unsigned)gp / (unsigned)ba.hw_pad), pp = (int)((unsigned)gp - (unsigned)bb * (unsigned)ba.hw_pad);
         const bool valid = bb < a.B && pp < a.hw;
         const int b = valid ? bb : 0;
         const int p = valid ? pp : 0;
@@ -77,33 +81,32 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_bwd1_kernel(BwdArgs b
         const float *xp = a.x + (size_t)b * D0 * a.hw + p;
         float *act_gp = ba.act + gp;
         float *del_gp = ba.del + gp;
+        auto load_x = [&](auto c0_tag) {
+            constexpr int C0 = decltype(c0_tag)::value;
 #pragma unroll 1
-        for (int c0 = 0; c0 < D0; c0 += 32) {
-            uint32_t hi[32], lo[32];
+            for (int c0 = 0; c0 < KC0; c0 += 32) {
+                uint32_t hi[32], lo[32];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) hi[j] = valid ? __float_as_uint(__ldg(xp + (size_t)(c0 + j) * a.hw)) : 0u;
+                for (int j = 0; j < 32; ++j) hi[j] = valid ? __float_as_uint(__ldg(xp + (size_t)(C0 + c0 + j) * a.hw)) : 0u;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) lo[j] = __float_as_uint(tf32_lo(__uint_as_float(hi[j])));
-            tmem_st<32>(lane_addr + c0, hi);
-            tmem_st<32>(lane_addr + KMAX + c0, lo);
+                for (int j = 0; j < 32; ++j) lo[j] = __float_as_uint(tf32_lo(__uint_as_float(hi[j])));
+                tmem_st<32>(lane_addr + c0, hi);
+                tmem_st<32>(lane_addr + AW + c0, lo);
+            }
+        };
+        load_x(std::integral_constant<int, 0>{});
+        if constexpr (D0 > KC0) {
+            tc_run_chunk<CFG, 0, AW, 0, KC0>(wg_base, sw, bar, phase, wg, t);
+            load_x(std::integral_constant<int, KC0>{});
         }
-        tc_run_layer<CFG, 0>(wg_base, sw, bar, phase, wg, t);
-        if constexpr (CFG::NW > 1) {
-            tc_epilogue_to_a_spill<CFG, 0>(lane_addr, act_gp, npp);
-            tc_run_layer<CFG, 1>(wg_base, sw, bar, phase, wg, t);
-        }
-        if constexpr (CFG::NW > 2) {
-            tc_epilogue_to_a_spill<CFG, 1>(lane_addr, act_gp, npp);
-            tc_run_layer<CFG, 2>(wg_base, sw, bar, phase, wg, t);
-        }
-        if constexpr (CFG::NW > 3) {
-            tc_epilogue_to_a_spill<CFG, 2>(lane_addr, act_gp, npp);
-            tc_run_layer<CFG, 3>(wg_base, sw, bar, phase, wg, t);
-        }
+        tc_run_chunk<CFG, 0, AW, D0 - KC0, KC0>(wg_base, sw, bar, phase, wg, t);
+        if constexpr (CFG::NW > 1) tc_layer_from_d<CFG, 1, AW, true>(wg_base, lane_addr, sw, bar, phase, wg, t, act_gp, npp, true);
+        if constexpr (CFG::NW > 2) tc_layer_from_d<CFG, 2, AW, true>(wg_base, lane_addr, sw, bar, phase, wg, t, act_gp, npp, true);
+        if constexpr (CFG::NW > 3) tc_layer_from_d<CFG, 3, AW, true>(wg_base, lane_addr, sw, bar, phase, wg, t, act_gp, npp, true);
         float a16[kTailIn], a8[kTailMid], z[LAST];
         {
             uint32_t r[16];
-            tmem_ld<16>(lane_addr + 2 * KMAX, r);
+            tmem_ld<16>(lane_addr + 2 * AW, r);
             wait_ld();
             float *dst = act_gp + (size_t)BwdRows<CFG>::row(CFG::NW) * npp;
 #pragma unroll
@@ -318,7 +321,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_dgrad_kernel(BwdArgs 
     const long long ntiles = npp / kTile;
     for (long long tile = (long long)blockIdx.x * NWG + wg; tile < ntiles; tile += (long long)gridDim.x * NWG) {
         const long long gp = tile * kTile + t;
-        const int bb = (int)(gp / ba.hw_pad), pp = (int)(gp - (long long)bb * ba.hw_pad);
+        const int bb = (int)((unsigned)gp / (unsigned)ba.hw_pad), pp = (int)((unsigned)gp - (unsigned)bb * (unsigned)ba.hw_pad);
         const bool valid = bb < ba.a.B && pp < ba.a.hw;
         const int b = valid ? bb : 0;
         const int p = valid ? pp : 0;
@@ -701,7 +704,7 @@ static constexpr size_t dgrad_smem_bytes()
     return sizeof(float) * (CFG::tail_off() + kTailMid * kTailIn + 3 * kTailMid) + 8 * NWG + 16;
 }
 
-template <class CFG, int MODE, int R, int NWG1, int NWG2>
+template <class CFG, int MODE, int R, int NWG1, int NWG2, int AW>
 static int launch_bwd_cfg(const ChainParams &cp, const TcArgs &a, char *ws, int sms, cudaStream_t s)
 {
     constexpr int LAST = MODE == 0 ? 1 : 3;
@@ -728,7 +731,7 @@ static int launch_bwd_cfg(const ChainParams &cp, const TcArgs &a, char *ws, int 
     ba.act = act; ba.del = del; ba.npx_pad = npp; ba.hw_pad = hw_pad;
     const long long ntiles = npp / kTile;
     {
-        auto k1 = chain_tc_bwd1_kernel<CFG, MODE, R, NWG1>;
+        auto k1 = chain_tc_bwd1_kernel<CFG, MODE, R, NWG1, AW>;
         const size_t smem = sizeof(float) * CFG::pack_floats(LAST) + 8 * NWG1 + 16;
         cudaError_t e = cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
@@ -866,16 +869,16 @@ int launch_chain_tc_bwd_stash(const ChainParams &cp, const TcArgs &a, int mode, 
     return set_error(BTS_ERR_UNSUPPORTED, "chain does not stash");
 }
 
-template <class CFG, int NWG1, int NWG2>
+template <class CFG, int NWG1, int NWG2, int AW = CFG::kmax()>
 static int dispatch_bwd_mode(const ChainParams &cp, const TcArgs &a, int mode, int r, char *ws, int sms, cudaStream_t s)
 {
-    if (mode == 0) return launch_bwd_cfg<CFG, 0, 1, NWG1, NWG2>(cp, a, ws, sms, s);
-    if (mode == 1) return launch_bwd_cfg<CFG, 1, 1, NWG1, NWG2>(cp, a, ws, sms, s);
+    if (mode == 0) return launch_bwd_cfg<CFG, 0, 1, NWG1, NWG2, AW>(cp, a, ws, sms, s);
+    if (mode == 1) return launch_bwd_cfg<CFG, 1, 1, NWG1, NWG2, AW>(cp, a, ws, sms, s);
     switch (r) {
-    case 8: return launch_bwd_cfg<CFG, 2, 8, NWG1, NWG2>(cp, a, ws, sms, s);
-    case 4: return launch_bwd_cfg<CFG, 2, 4, NWG1, NWG2>(cp, a, ws, sms, s);
-    case 2: return launch_bwd_cfg<CFG, 2, 2, NWG1, NWG2>(cp, a, ws, sms, s);
-    default: return launch_bwd_cfg<CFG, 2, 1, NWG1, NWG2>(cp, a, ws, sms, s);
+    case 8: return launch_bwd_cfg<CFG, 2, 8, NWG1, NWG2, AW>(cp, a, ws, sms, s);
+    case 4: return launch_bwd_cfg<CFG, 2, 4, NWG1, NWG2, AW>(cp, a, ws, sms, s);
+    case 2: return launch_bwd_cfg<CFG, 2, 2, NWG1, NWG2, AW>(cp, a, ws, sms, s);
+    default: return launch_bwd_cfg<CFG, 2, 1, NWG1, NWG2, AW>(cp, a, ws, sms, s);
     }
 }
 
@@ -883,8 +886,8 @@ static int dispatch_bwd_mode(const ChainParams &cp, const TcArgs &a, int mode, i
 int launch_chain_tc_bwd(const ChainParams &cp, const TcArgs &a, int mode, int r, void *ws, int sms, cudaStream_t s)
 {
     char *w = static_cast<char *>(ws);
-    if (cfg_matches<Cfg128_128>(cp)) return dispatch_bwd_mode<Cfg128_128, 1, 1>(cp, a, mode, r, w, sms, s);
-    if (cfg_matches<Cfg128_64>(cp)) return dispatch_bwd_mode<Cfg128_64, 1, 2>(cp, a, mode, r, w, sms, s);
+    if (cfg_matches<Cfg128_128>(cp)) return dispatch_bwd_mode<Cfg128_128, 2, 1, 64>(cp, a, mode, r, w, sms, s);
+    if (cfg_matches<Cfg128_64>(cp)) return dispatch_bwd_mode<Cfg128_64, 2, 2, 64>(cp, a, mode, r, w, sms, s);
     if (cfg_matches<Cfg64_64>(cp)) return dispatch_bwd_mode<Cfg64_64, 2, 2>(cp, a, mode, r, w, sms, s);
     if (cfg_matches<Cfg64_32>(cp)) return dispatch_bwd_mode<Cfg64_32, 3, 3>(cp, a, mode, r, w, sms, s);
     if (cfg_matches<Cfg32_32>(cp)) return dispatch_bwd_mode<Cfg32_32, 3, 3>(cp, a, mode, r, w, sms, s);

@@ -8,22 +8,27 @@
 // thread t <-> pixel t <-> TMEM lane t. NWG independent warpgroups per CTA (each with its own TMEM
 // columns, mbarrier and MMA-issuing thread) keep the tensor core, the LSU and the FMA pipes busy at
 // the same time: while one warpgroup waits for its MMAs another one loads or runs its epilogue.
+#include <type_traits>
+
 #include "chain_tc.cuh"
 
 namespace bts {
 
 // PREFETCH: the next tile's features travel global -> shared with cp.async while the current tile is
 // computed (needs D0*512 B of shared memory per warpgroup next to the weight images).
-template <class CFG, int R, bool FINAL, int NWG, bool PREFETCH>
+template <class CFG, int R, bool FINAL, int NWG, bool PREFETCH, int AW>
 __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
 {
     constexpr int LAST = FINAL ? 1 : 3;
     constexpr int PACK = CFG::pack_floats(LAST);
-    constexpr int KMAX = CFG::kmax(), NMAX = CFG::nmax();
-    constexpr int COLS = 2 * KMAX + NMAX;
+    constexpr int NMAX = CFG::nmax();
+    constexpr int COLS = 2 * AW + NMAX;                           // A hi | A lo | D
     constexpr int D0 = CFG::dim(0);
+    constexpr int KC0 = D0 < AW ? D0 : AW;                        // input channels per round of layer 0
     static_assert(NWG * COLS <= 512, "TMEM budget");
+    static_assert(D0 % KC0 == 0 && D0 / KC0 <= 2, "layer 0 runs in one or two rounds");
     static_assert(CFG::dim(CFG::NW) == kTailIn, "tensor-core part must end at 16 channels");
+    constexpr bool SPILL = kStashCfg<CFG>;
 
     extern __shared__ __align__(128) float smem[];
     float *sw = smem;
@@ -80,62 +85,62 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
         const float *xp = a.x + (size_t)b * D0 * a.hw + p;
         bool stash = false;
         float *act_gp = nullptr;
-        if constexpr (kStashCfg<CFG>) {
+        if constexpr (SPILL) {
             stash = valid && a.stash_act != nullptr;
             act_gp = a.stash_act + (size_t)b * a.stash_hw_pad + p;
         }
-        // features -> (hi, lo) -> TMEM A operand
+        // channels [C0, C0+KC0) of the features -> (hi, lo) -> TMEM A operand
+        auto load_x = [&](auto c0_tag) {
+            constexpr int C0 = decltype(c0_tag)::value;
+            if constexpr (PREFETCH) {
+#pragma unroll 1
+                for (int c0 = 0; c0 < KC0; c0 += 16) {
+                    uint32_t hi[16], lo[16];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        const float v = xs[(C0 + c0 + j) * kTile];
+                        hi[j] = __float_as_uint(v);
+                        lo[j] = __float_as_uint(tf32_lo(v));
+                    }
+                    tmem_st<16>(lane_addr + c0, hi);
+                    tmem_st<16>(lane_addr + AW + c0, lo);
+                }
+            } else {
+                // 32 independent coalesced loads in flight per thread
+#pragma unroll 1
+                for (int c0 = 0; c0 < KC0; c0 += 32) {
+                    uint32_t hi[32], lo[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) hi[j] = valid ? __float_as_uint(__ldg(xp + (size_t)(C0 + c0 + j) * a.hw)) : 0u;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) lo[j] = __float_as_uint(tf32_lo(__uint_as_float(hi[j])));
+                    tmem_st<32>(lane_addr + c0, hi);
+                    tmem_st<32>(lane_addr + AW + c0, lo);
+                }
+            }
+        };
         if constexpr (PREFETCH) {
             cp_async_wait_all();
             named_bar_sync(1 + wg, kTile);                        // the tile was copied by all threads of the warpgroup
-#pragma unroll 1
-            for (int c0 = 0; c0 < D0; c0 += 16) {
-                uint32_t hi[16], lo[16];
-#pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    const float v = xs[(c0 + j) * kTile];
-                    hi[j] = __float_as_uint(v);
-                    lo[j] = __float_as_uint(tf32_lo(v));
-                }
-                tmem_st<16>(lane_addr + c0, hi);
-                tmem_st<16>(lane_addr + KMAX + c0, lo);
-            }
+        }
+        load_x(std::integral_constant<int, 0>{});
+        if constexpr (D0 > KC0) {
+            tc_run_chunk<CFG, 0, AW, 0, KC0>(wg_base, sw, bar, phase, wg, t);
+            load_x(std::integral_constant<int, KC0>{});
+        }
+        if constexpr (PREFETCH) {
             named_bar_sync(1 + wg, kTile);                        // everybody has read the staged tile
             prefetch(tile + stride);
-        } else {
-            // 32 independent coalesced loads in flight per thread
-#pragma unroll 1
-            for (int c0 = 0; c0 < D0; c0 += 32) {
-                uint32_t hi[32], lo[32];
-#pragma unroll
-                for (int j = 0; j < 32; ++j) hi[j] = valid ? __float_as_uint(__ldg(xp + (size_t)(c0 + j) * a.hw)) : 0u;
-#pragma unroll
-                for (int j = 0; j < 32; ++j) lo[j] = __float_as_uint(tf32_lo(__uint_as_float(hi[j])));
-                tmem_st<32>(lane_addr + c0, hi);
-                tmem_st<32>(lane_addr + KMAX + c0, lo);
-            }
         }
+        tc_run_chunk<CFG, 0, AW, D0 - KC0, KC0>(wg_base, sw, bar, phase, wg, t);
         // wide layers
-        tc_run_layer<CFG, 0>(wg_base, sw, bar, phase, wg, t);
-        if constexpr (CFG::NW > 1) {
-            if constexpr (kStashCfg<CFG>) tc_epilogue_to_a_spill<CFG, 0>(lane_addr, act_gp, a.stash_npp, stash);
-            else tc_epilogue_to_a<CFG, 0>(lane_addr);
-            tc_run_layer<CFG, 1>(wg_base, sw, bar, phase, wg, t);
-        }
-        if constexpr (CFG::NW > 2) {
-            if constexpr (kStashCfg<CFG>) tc_epilogue_to_a_spill<CFG, 1>(lane_addr, act_gp, a.stash_npp, stash);
-            else tc_epilogue_to_a<CFG, 1>(lane_addr);
-            tc_run_layer<CFG, 2>(wg_base, sw, bar, phase, wg, t);
-        }
-        if constexpr (CFG::NW > 3) {
-            if constexpr (kStashCfg<CFG>) tc_epilogue_to_a_spill<CFG, 2>(lane_addr, act_gp, a.stash_npp, stash);
-            else tc_epilogue_to_a<CFG, 2>(lane_addr);
-            tc_run_layer<CFG, 3>(wg_base, sw, bar, phase, wg, t);
-        }
+        if constexpr (CFG::NW > 1) tc_layer_from_d<CFG, 1, AW, SPILL>(wg_base, lane_addr, sw, bar, phase, wg, t, act_gp, a.stash_npp, stash);
+        if constexpr (CFG::NW > 2) tc_layer_from_d<CFG, 2, AW, SPILL>(wg_base, lane_addr, sw, bar, phase, wg, t, act_gp, a.stash_npp, stash);
+        if constexpr (CFG::NW > 3) tc_layer_from_d<CFG, 3, AW, SPILL>(wg_base, lane_addr, sw, bar, phase, wg, t, act_gp, a.stash_npp, stash);
         float a16[kTailIn], a8[kTailMid], z[LAST];
         {
             uint32_t r[16];
-            tmem_ld<16>(lane_addr + 2 * KMAX, r);
+            tmem_ld<16>(lane_addr + 2 * AW, r);
             wait_ld();
 #pragma unroll
             for (int j = 0; j < 16; ++j) a16[j] = elu_fast(__uint_as_float(r[j]));
@@ -180,7 +185,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
     if (tid < 32) tmem_dealloc(tbase, 512);
 }
 
-template <class CFG, int R, bool FINAL, int NWG>
+template <class CFG, int R, bool FINAL, int NWG, int AW>
 static int launch_one(const ChainParams &cp, const TcArgs &a, float *wpack, int sms, cudaStream_t s)
 {
     constexpr int LAST = FINAL ? 1 : 3;
@@ -191,7 +196,7 @@ static int launch_one(const ChainParams &cp, const TcArgs &a, float *wpack, int 
     constexpr bool CAN_PREFETCH = base + xs_bytes <= 227 * 1024;
     const bool prefetch = CAN_PREFETCH && a.x_vec16;
     const size_t smem = base + (prefetch ? xs_bytes : 0);
-    auto kern = prefetch ? chain_tc_fwd_kernel<CFG, R, FINAL, NWG, CAN_PREFETCH> : chain_tc_fwd_kernel<CFG, R, FINAL, NWG, false>;
+    auto kern = prefetch ? chain_tc_fwd_kernel<CFG, R, FINAL, NWG, CAN_PREFETCH, AW> : chain_tc_fwd_kernel<CFG, R, FINAL, NWG, false, AW>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     const long long ntiles = (a.npx + kTile - 1) / kTile;
@@ -211,23 +216,23 @@ bool tc_supported(const ChainParams &cp)
            cfg_matches<Cfg64_32>(cp) || cfg_matches<Cfg32_32>(cp) || cfg_matches<Cfg32_16>(cp);
 }
 
-template <class CFG, int NWG>
+template <class CFG, int NWG, int AW = CFG::kmax()>
 static int dispatch_r(const ChainParams &cp, const TcArgs &a, int r, float *wpack, int sms, cudaStream_t s)
 {
-    if (cp.is_final) return launch_one<CFG, 1, true, NWG>(cp, a, wpack, sms, s);
+    if (cp.is_final) return launch_one<CFG, 1, true, NWG, AW>(cp, a, wpack, sms, s);
     switch (r) {
-    case 8: return launch_one<CFG, 8, false, NWG>(cp, a, wpack, sms, s);
-    case 4: return launch_one<CFG, 4, false, NWG>(cp, a, wpack, sms, s);
-    case 2: return launch_one<CFG, 2, false, NWG>(cp, a, wpack, sms, s);
-    default: return launch_one<CFG, 1, false, NWG>(cp, a, wpack, sms, s);   // r == 1, or plane_eq only
+    case 8: return launch_one<CFG, 8, false, NWG, AW>(cp, a, wpack, sms, s);
+    case 4: return launch_one<CFG, 4, false, NWG, AW>(cp, a, wpack, sms, s);
+    case 2: return launch_one<CFG, 2, false, NWG, AW>(cp, a, wpack, sms, s);
+    default: return launch_one<CFG, 1, false, NWG, AW>(cp, a, wpack, sms, s);   // r == 1, or plane_eq only
     }
 }
 
 // r = 0: no LPG (reduction only). Returns BTS_ERR_UNSUPPORTED when the chain is not covered.
 int launch_chain_tc_fwd(const ChainParams &cp, const TcArgs &a, int r, float *wpack, int sms, cudaStream_t s)
 {
-    if (cfg_matches<Cfg128_128>(cp)) return dispatch_r<Cfg128_128, 1>(cp, a, r, wpack, sms, s);
-    if (cfg_matches<Cfg128_64>(cp)) return dispatch_r<Cfg128_64, 1>(cp, a, r, wpack, sms, s);
+    if (cfg_matches<Cfg128_128>(cp)) return dispatch_r<Cfg128_128, 2, 64>(cp, a, r, wpack, sms, s);
+    if (cfg_matches<Cfg128_64>(cp)) return dispatch_r<Cfg128_64, 2, 64>(cp, a, r, wpack, sms, s);
     if (cfg_matches<Cfg64_64>(cp)) return dispatch_r<Cfg64_64, 2>(cp, a, r, wpack, sms, s);
     if (cfg_matches<Cfg64_32>(cp)) return dispatch_r<Cfg64_32, 3>(cp, a, r, wpack, sms, s);
     if (cfg_matches<Cfg32_32>(cp)) return dispatch_r<Cfg32_32, 4>(cp, a, r, wpack, sms, s);
