@@ -35,7 +35,7 @@ int launch_lpg_fwd(const float *, float *, float *, int, int, int, int, float, c
 int launch_lpg_bwd(const float *, const float *, float *, int, int, int, int, float, cudaStream_t);
 int launch_chain_generic_fwd(const ChainParams &, const float *, float *, int, int, cudaStream_t);
 int launch_chain_generic_bwd(const ChainParams &, const float *, const float *, float *, int, int, cudaStream_t);
-int launch_chain_tc_fwd(const ChainParams &, const TcArgs &, int r, float *wpack, int sms, cudaStream_t);
+int launch_chain_tc_fwd(const ChainParams &, const TcArgs &, int r, int sms, cudaStream_t);
 int launch_chain_tc_bwd(const ChainParams &, const TcArgs &, int mode, int r, void *ws, int sms, cudaStream_t);
 int launch_chain_bwd_fused(const ChainParams &, const TcArgs &, int mode, int r, void *ws, int sms, cudaStream_t);
 bool fused_bwd_supported(const ChainParams &);
@@ -218,7 +218,7 @@ int bts_reduc_fwd_stash(const float *x, const float *const *W, const int *dims, 
         a.out = out;
         if (use_stash(cp, x, B, h * w, stash, stash_bytes))
             if (int e = tc_stash_bind(cp, a, stash, true, (cudaStream_t)stream)) return e;
-        return launch_chain_tc_fwd(cp, a, 0, static_cast<float *>(ws), sm_count(), (cudaStream_t)stream);
+        return launch_chain_tc_fwd(cp, a, 0, sm_count(), (cudaStream_t)stream);
     }
     return launch_chain_generic_fwd(cp, x, out, B, h * w, (cudaStream_t)stream);
 }
@@ -279,7 +279,7 @@ int bts_reduc_lpg_fwd_stash(const float *x, const float *const *W, const int *di
         a.out = plane_eq_out; a.depth = depth; a.abs_min = abs_min;
         if (use_stash(cp, x, B, h * w, stash, stash_bytes))
             if (int e = tc_stash_bind(cp, a, stash, true, (cudaStream_t)stream)) return e;
-        return launch_chain_tc_fwd(cp, a, r, static_cast<float *>(ws), sm_count(), (cudaStream_t)stream);
+        return launch_chain_tc_fwd(cp, a, r, sm_count(), (cudaStream_t)stream);
     }
     float *pe = plane_eq_out;
     if (pe == nullptr) {

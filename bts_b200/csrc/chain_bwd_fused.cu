@@ -29,7 +29,6 @@ constexpr int kBLo = 32 * 128;                         // byte offset of the rem
 
 struct FusedArgs {
     TcArgs a;
-    const float *wpack_t;   // transposed weight images (dgrad B operands)
     float *partials;        // [gridDim.x][total_w]
     int total_w;
 };
@@ -235,10 +234,8 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
     uint32_t *slot = reinterpret_cast<uint32_t *>(bars + 6 * NWG);
 
     const int tid = threadIdx.x;
-    for (int i = tid * 4; i < L::PACK; i += NT * 4)
-        *reinterpret_cast<float4 *>(sw + i) = __ldg(reinterpret_cast<const float4 *>(a.wpack + i));
-    for (int i = tid * 4; i < L::IMG; i += NT * 4)
-        *reinterpret_cast<float4 *>(swt + i) = __ldg(reinterpret_cast<const float4 *>(fa.wpack_t + i));
+    tc_pack_to_smem<CFG>(a.W, sw, LAST, tid, NT);
+    tc_pack_t_to_smem<CFG>(a.W, swt, tid, NT);
     fence_smem_to_async();
     if (tid < 32) tmem_alloc(slot, 512);
     if (tid == 0) {
@@ -623,21 +620,13 @@ template <class CFG, int MODE, int R, int NWG>
 static int launch_fused_cfg(const ChainParams &cp, const TcArgs &a, char *ws, int sms, cudaStream_t s)
 {
     using L = FusedLayout<CFG, MODE, R, NWG>;
-    float *wpack = reinterpret_cast<float *>(ws);
-    float *wpack_t = reinterpret_cast<float *>(ws + tc_pack_bytes());
     float *partials = reinterpret_cast<float *>(ws + 2 * tc_pack_bytes());
     int total_w = 0;
     for (int l = 0; l < cp.n_layers; ++l) total_w += cp.dims[l] * cp.dims[l + 1];
 
-    tc_pack_weights_kernel<CFG><<<16, 256, 0, s>>>(cp, wpack, L::LAST);
-    if (int e = check_launch("tc_pack_weights")) return e;
-    tc_pack_weights_t_kernel<CFG><<<16, 256, 0, s>>>(cp, wpack_t);
-    if (int e = check_launch("tc_pack_weights_t")) return e;
-
     FusedArgs fa;
     fa.a = a;
-    fa.a.wpack = wpack;
-    fa.wpack_t = wpack_t;
+    tc_set_weights(fa.a, cp);
     fa.partials = cp.gW[0] != nullptr ? partials : nullptr;
     fa.total_w = total_w;
     auto kern = chain_bwd_fused_kernel<CFG, MODE, R, NWG>;

@@ -70,7 +70,7 @@ __device__ __forceinline__ float elu_fast(float t)
 // Parameters shared by the forward and backward tensor-core kernels.
 struct TcArgs {
     const float *x;          // [B][D0][hw]
-    const float *wpack;      // packed weight image built by tc_pack_weights_kernel
+    const float *W[BTS_MAX_LAYERS];  // raw weights [out][in] of every layer; each CTA builds its operand images itself
     float *out;              // forward: plane_eq [B][4][hw] (may be null) or head output [B][1][hw]
     float *depth;            // forward fused: [B][h*r][w*r] (null when not fused)
     float *abs_min;
@@ -421,45 +421,58 @@ __device__ __forceinline__ void tail_forward(const float *tw, const float (&a16)
     tail_logits<LAST>(tw + kTailMid * kTailIn, a8, z);
 }
 
-// ---- weight packing: fp32 [N][K] -> canonical K-major (hi | lo) images + raw tail weights
-template <class CFG>
-__global__ void tc_pack_weights_kernel(ChainParams cp, float *wpack, int last)
+// ---- weight packing, done by every CTA for itself straight from the raw fp32 weights (they are a few
+// hundred KB at most and L2-resident; no pack launch, no packed copy in HBM).
+// Canonical K-major (hi | lo) operand images: with float4 unit u <-> (row%8 = u%8, k/4 = (u/8)%(K/4),
+// row/8 = u/(2K)) the unit lands at float offset 4u (see kmajor_off_floats), so shared-memory stores are linear.
+__device__ __forceinline__ float4 tf32_lo4(float4 v)
 {
-    const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
-#pragma unroll
-    for (int l = 0; l < CFG::NW; ++l) {
-        const int K = CFG::K(l), N = CFG::N(l);
-        float *hi = wpack + CFG::w_off(l), *lo = hi + N * K;
-        for (int e = tid; e < N * K; e += nth) {
-            const int n = e / K, k = e - n * K;
-            const float v = __ldg(cp.W[l] + e);
-            const uint32_t off = kmajor_off_floats(n, k, K);
-            hi[off] = v;
-            lo[off] = tc::tf32_lo(v);
-        }
-    }
-    float *tw = wpack + CFG::tail_off();
-    for (int e = tid; e < kTailMid * kTailIn; e += nth) tw[e] = __ldg(cp.W[CFG::NW] + e);
-    for (int e = tid; e < last * kTailMid; e += nth) tw[kTailMid * kTailIn + e] = __ldg(cp.W[CFG::NW + 1] + e);
+    return make_float4(tc::tf32_lo(v.x), tc::tf32_lo(v.y), tc::tf32_lo(v.z), tc::tf32_lo(v.w));
 }
 
-// transposed images: layer l, rows = input channel c (N' = K_l), K' = output channel o (N_l)
+// forward images (rows = output channel n, K = input channel) + raw tail weights W4 [8][16], W5 [last][8]
 template <class CFG>
-__global__ void tc_pack_weights_t_kernel(ChainParams cp, float *wpack_t)
+__device__ __forceinline__ void tc_pack_to_smem(const float *const *W, float *sw, int last, int tid, int nth)
 {
-    const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
 #pragma unroll
     for (int l = 0; l < CFG::NW; ++l) {
         const int K = CFG::K(l), N = CFG::N(l);
-        float *hi = wpack_t + CFG::w_off(l), *lo = hi + N * K;
-        for (int e = tid; e < N * K; e += nth) {
-            const int o = e / K, c = e - o * K;
-            const float v = __ldg(cp.W[l] + e);
-            const uint32_t off = kmajor_off_floats(c, o, N);
-            hi[off] = v;
-            lo[off] = tc::tf32_lo(v);
+        float *hi = sw + CFG::w_off(l), *lo = hi + N * K;
+        const float *w = W[l];
+        for (int u = tid; u < N * K / 4; u += nth) {
+            const int n = (u / (2 * K)) * 8 + (u & 7), kq = (u >> 3) % (K / 4);
+            const float4 v = __ldg(reinterpret_cast<const float4 *>(w + (size_t)n * K + 4 * kq));
+            *reinterpret_cast<float4 *>(hi + 4 * u) = v;
+            *reinterpret_cast<float4 *>(lo + 4 * u) = tf32_lo4(v);
         }
     }
+    float *tw = sw + CFG::tail_off();
+    for (int e = tid; e < kTailMid * kTailIn; e += nth) tw[e] = __ldg(W[CFG::NW] + e);
+    for (int e = tid; e < last * kTailMid; e += nth) tw[kTailMid * kTailIn + e] = __ldg(W[CFG::NW + 1] + e);
+}
+
+// transposed images for dgrad: layer l, rows = input channel c, K' = output channel o
+template <class CFG>
+__device__ __forceinline__ void tc_pack_t_to_smem(const float *const *W, float *swt, int tid, int nth)
+{
+#pragma unroll
+    for (int l = 0; l < CFG::NW; ++l) {
+        const int K = CFG::K(l), N = CFG::N(l);
+        float *hi = swt + CFG::w_off(l), *lo = hi + N * K;
+        const float *w = W[l];
+        for (int u = tid; u < N * K / 4; u += nth) {
+            const int c = (u / (2 * N)) * 8 + (u & 7), oq = (u >> 3) % (N / 4);
+            const float *src = w + (size_t)(4 * oq) * K + c;
+            const float4 v = make_float4(__ldg(src), __ldg(src + K), __ldg(src + 2 * K), __ldg(src + 3 * K));
+            *reinterpret_cast<float4 *>(hi + 4 * u) = v;
+            *reinterpret_cast<float4 *>(lo + 4 * u) = tf32_lo4(v);
+        }
+    }
+}
+
+inline void tc_set_weights(TcArgs &a, const ChainParams &cp)
+{
+    for (int l = 0; l < BTS_MAX_LAYERS; ++l) a.W[l] = l < cp.n_layers ? cp.W[l] : nullptr;
 }
 
 // chain signatures served by the tensor-core path (bts_size = 512 and 256 decoders)

@@ -19,8 +19,7 @@
 namespace bts {
 
 struct BwdArgs {
-    TcArgs a;              // x, wpack (forward images + tail weights), grad, grad_x, sizes
-    const float *wpack_t;  // transposed images for dgrad
+    TcArgs a;              // x, raw weights, grad, grad_x, sizes
     float *act;            // [RA][npx_pad]   a_1 .. a_NW (=a16), a8
     float *del;            // [RD][npx_pad]   delta_1 .. delta_NW (=d16), d8, dz
     long long npx_pad;
@@ -50,8 +49,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_bwd1_kernel(BwdArgs b
     uint32_t *slot = reinterpret_cast<uint32_t *>(bars + NWG);
 
     const int tid = threadIdx.x, wg = tid / kTile, t = tid % kTile;
-    for (int i = tid * 4; i < PACK; i += NWG * kTile * 4)
-        *reinterpret_cast<float4 *>(sw + i) = __ldg(reinterpret_cast<const float4 *>(a.wpack + i));
+    tc_pack_to_smem<CFG>(a.W, sw, LAST, tid, NWG * kTile);
     fence_smem_to_async();
     if (tid < 32) tmem_alloc(slot, 512);
     if (tid == 0) {
@@ -296,8 +294,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_dgrad_kernel(BwdArgs 
     uint64_t *bars = reinterpret_cast<uint64_t *>(stw + TAILW);
     uint32_t *slot = reinterpret_cast<uint32_t *>(bars + NWG);
     const int tid = threadIdx.x, wg = tid / kTile, t = tid % kTile;
-    for (int i = tid * 4; i < IMG; i += NWG * kTile * 4)
-        *reinterpret_cast<float4 *>(swt + i) = __ldg(reinterpret_cast<const float4 *>(ba.wpack_t + i));
+    tc_pack_t_to_smem<CFG>(ba.a.W, swt, tid, NWG * kTile);
     if constexpr (TM >= 0) {
         constexpr int LAST = TM == 0 ? 1 : 3;
         for (int i = tid; i < kTailMid * kTailIn; i += NWG * kTile) stw[i] = __ldg(ba.w4 + i);
@@ -708,8 +705,6 @@ template <class CFG, int MODE, int R, int NWG1, int NWG2, int AW>
 static int launch_bwd_cfg(const ChainParams &cp, const TcArgs &a, char *ws, int sms, cudaStream_t s)
 {
     constexpr int LAST = MODE == 0 ? 1 : 3;
-    float *wpack = reinterpret_cast<float *>(ws);
-    float *wpack_t = reinterpret_cast<float *>(ws + tc_pack_bytes());
     const bool tma = wgrad_tma_supported(cp, a.hw, a.x);
     const int hw_pad = tma ? pad32(a.hw) : a.hw;
     const long long npp = pad128((long long)a.B * hw_pad);
@@ -719,15 +714,9 @@ static int launch_bwd_cfg(const ChainParams &cp, const TcArgs &a, char *ws, int 
     float *del = act + (size_t)ra * npp;
     float *partials = del + (size_t)rd * npp;
 
-    tc_pack_weights_kernel<CFG><<<16, 256, 0, s>>>(cp, wpack, LAST);
-    if (int e = check_launch("tc_pack_weights")) return e;
-    tc_pack_weights_t_kernel<CFG><<<16, 256, 0, s>>>(cp, wpack_t);
-    if (int e = check_launch("tc_pack_weights_t")) return e;
-
     BwdArgs ba;
     ba.a = a;
-    ba.a.wpack = wpack;
-    ba.wpack_t = wpack_t;
+    tc_set_weights(ba.a, cp);
     ba.act = act; ba.del = del; ba.npx_pad = npp; ba.hw_pad = hw_pad;
     const long long ntiles = npp / kTile;
     {
@@ -816,7 +805,6 @@ static int launch_bwd_stash_cfg(const ChainParams &cp, const TcArgs &a, int r, c
     if constexpr (!kStashCfg<CFG>) {
         return set_error(BTS_ERR_UNSUPPORTED, "chain does not stash");
     } else {
-        float *wpack_t = reinterpret_cast<float *>(ws + tc_pack_bytes());
         const long long npp = a.stash_npp;
         int ra, rd, tw;
         bwd_rows(cp, &ra, &rd, &tw);
@@ -824,12 +812,9 @@ static int launch_bwd_stash_cfg(const ChainParams &cp, const TcArgs &a, int r, c
         float *del = scratch + (size_t)ra * npp;
         float *partials = del + (size_t)rd * npp;
 
-        tc_pack_weights_t_kernel<CFG><<<16, 256, 0, s>>>(cp, wpack_t);
-        if (int e = check_launch("tc_pack_weights_t")) return e;
-
         BwdArgs ba;
         ba.a = a;
-        ba.wpack_t = wpack_t;
+        tc_set_weights(ba.a, cp);
         ba.act = a.stash_act; ba.del = del; ba.npx_pad = npp; ba.hw_pad = a.stash_hw_pad;
         ba.w4 = cp.W[CFG::NW]; ba.w5 = cp.W[CFG::NW + 1];
         if (TM == 1 && r > 0) {              // grad_depth -> gradient of the plane parameters [B][4][hw]

@@ -37,8 +37,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
     float *xs_all = smem + PACK + (8 * NWG + 16 + 15) / 16 * 4;   // [NWG][D0][128] when PREFETCH (16-byte aligned)
 
     const int tid = threadIdx.x, wg = tid / kTile, t = tid % kTile, lane = tid & 31;
-    for (int i = tid * 4; i < PACK; i += NWG * kTile * 4)
-        *reinterpret_cast<float4 *>(sw + i) = __ldg(reinterpret_cast<const float4 *>(a.wpack + i));
+    tc_pack_to_smem<CFG>(a.W, sw, LAST, tid, NWG * kTile);
     fence_smem_to_async();
     if (tid < 32) tmem_alloc(slot, 512);
     if (tid == 0) {
@@ -186,11 +185,9 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
 }
 
 template <class CFG, int R, bool FINAL, int NWG, int AW>
-static int launch_one(const ChainParams &cp, const TcArgs &a, float *wpack, int sms, cudaStream_t s)
+static int launch_one(const ChainParams &cp, const TcArgs &a, int sms, cudaStream_t s)
 {
     constexpr int LAST = FINAL ? 1 : 3;
-    tc_pack_weights_kernel<CFG><<<16, 256, 0, s>>>(cp, wpack, LAST);
-    if (int e = check_launch("tc_pack_weights")) return e;
     constexpr size_t base = sizeof(float) * CFG::pack_floats(LAST) + (8 * NWG + 16 + 15) / 16 * 16;
     constexpr size_t xs_bytes = (size_t)NWG * CFG::dim(0) * kTile * sizeof(float);
     constexpr bool CAN_PREFETCH = base + xs_bytes <= 227 * 1024;
@@ -203,7 +200,7 @@ static int launch_one(const ChainParams &cp, const TcArgs &a, float *wpack, int 
     long long grid = (ntiles + NWG - 1) / NWG;
     if (grid > sms) grid = sms;
     TcArgs aa = a;
-    aa.wpack = wpack;
+    tc_set_weights(aa, cp);
     kern<<<(unsigned)grid, NWG * kTile, smem, s>>>(aa);
     return check_launch("chain_tc_fwd");
 }
@@ -217,26 +214,26 @@ bool tc_supported(const ChainParams &cp)
 }
 
 template <class CFG, int NWG, int AW = CFG::kmax()>
-static int dispatch_r(const ChainParams &cp, const TcArgs &a, int r, float *wpack, int sms, cudaStream_t s)
+static int dispatch_r(const ChainParams &cp, const TcArgs &a, int r, int sms, cudaStream_t s)
 {
-    if (cp.is_final) return launch_one<CFG, 1, true, NWG, AW>(cp, a, wpack, sms, s);
+    if (cp.is_final) return launch_one<CFG, 1, true, NWG, AW>(cp, a, sms, s);
     switch (r) {
-    case 8: return launch_one<CFG, 8, false, NWG, AW>(cp, a, wpack, sms, s);
-    case 4: return launch_one<CFG, 4, false, NWG, AW>(cp, a, wpack, sms, s);
-    case 2: return launch_one<CFG, 2, false, NWG, AW>(cp, a, wpack, sms, s);
-    default: return launch_one<CFG, 1, false, NWG, AW>(cp, a, wpack, sms, s);   // r == 1, or plane_eq only
+    case 8: return launch_one<CFG, 8, false, NWG, AW>(cp, a, sms, s);
+    case 4: return launch_one<CFG, 4, false, NWG, AW>(cp, a, sms, s);
+    case 2: return launch_one<CFG, 2, false, NWG, AW>(cp, a, sms, s);
+    default: return launch_one<CFG, 1, false, NWG, AW>(cp, a, sms, s);   // r == 1, or plane_eq only
     }
 }
 
 // r = 0: no LPG (reduction only). Returns BTS_ERR_UNSUPPORTED when the chain is not covered.
-int launch_chain_tc_fwd(const ChainParams &cp, const TcArgs &a, int r, float *wpack, int sms, cudaStream_t s)
+int launch_chain_tc_fwd(const ChainParams &cp, const TcArgs &a, int r, int sms, cudaStream_t s)
 {
-    if (cfg_matches<Cfg128_128>(cp)) return dispatch_r<Cfg128_128, 2, 64>(cp, a, r, wpack, sms, s);
-    if (cfg_matches<Cfg128_64>(cp)) return dispatch_r<Cfg128_64, 2, 64>(cp, a, r, wpack, sms, s);
-    if (cfg_matches<Cfg64_64>(cp)) return dispatch_r<Cfg64_64, 2>(cp, a, r, wpack, sms, s);
-    if (cfg_matches<Cfg64_32>(cp)) return dispatch_r<Cfg64_32, 3>(cp, a, r, wpack, sms, s);
-    if (cfg_matches<Cfg32_32>(cp)) return dispatch_r<Cfg32_32, 4>(cp, a, r, wpack, sms, s);
-    if (cfg_matches<Cfg32_16>(cp)) return dispatch_r<Cfg32_16, 4>(cp, a, r, wpack, sms, s);
+    if (cfg_matches<Cfg128_128>(cp)) return dispatch_r<Cfg128_128, 2, 64>(cp, a, r, sms, s);
+    if (cfg_matches<Cfg128_64>(cp)) return dispatch_r<Cfg128_64, 2, 64>(cp, a, r, sms, s);
+    if (cfg_matches<Cfg64_64>(cp)) return dispatch_r<Cfg64_64, 2>(cp, a, r, sms, s);
+    if (cfg_matches<Cfg64_32>(cp)) return dispatch_r<Cfg64_32, 3>(cp, a, r, sms, s);
+    if (cfg_matches<Cfg32_32>(cp)) return dispatch_r<Cfg32_32, 4>(cp, a, r, sms, s);
+    if (cfg_matches<Cfg32_16>(cp)) return dispatch_r<Cfg32_16, 4>(cp, a, r, sms, s);
     return set_error(BTS_ERR_UNSUPPORTED, "chain not covered by the tensor-core path");
 }
 
