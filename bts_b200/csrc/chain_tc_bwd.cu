@@ -190,40 +190,50 @@ struct DgradCfg {
     __host__ __device__ static constexpr int nmax() { return CFG::kmax(); }
 };
 
-template <class CFG, int L>
+// A operand region width of the dgrad kernel: 64 columns at most, so that a 128-channel chain needs
+// 2*64 + 128 = 256 TMEM columns per warpgroup and two warpgroups fit (the 128-wide delta goes in two rounds)
+template <class CFG>
+constexpr int kDgradAW = DgradCfg<CFG>::kmax() > 64 ? 64 : DgradCfg<CFG>::kmax();
+
+// MMAs over delta channels [KOFF, KOFF+KC) of layer L's input gradient; A columns [0,KC) hi, [AW,AW+KC) lo
+template <class CFG, int L, int KOFF, int KC>
 __device__ __forceinline__ void tc_issue_dgrad(uint32_t wg_base, const float *swt, uint64_t *bar)
 {
-    constexpr int KP = CFG::N(L), NP = CFG::K(L), KMAX = DgradCfg<CFG>::kmax();
+    constexpr int KP = CFG::N(L), NP = CFG::K(L), AW = kDgradAW<CFG>;
     constexpr uint32_t LBO = 128, SBO = (KP / 4) * 128;
     constexpr uint32_t idesc = idesc_tf32(kTile, NP, 0, 0);
     const uint32_t whi = smem_u32(swt + CFG::w_off(L));
     const uint32_t wlo = whi + NP * KP * 4;
-    const uint32_t d = wg_base + 2 * KMAX;
+    const uint32_t d = wg_base + 2 * AW;
 #pragma unroll
-    for (int k0 = 0; k0 < KP; k0 += 8)
-        mma_tf32_ts(d, wg_base + KMAX + k0, smem_desc(whi + (k0 / 4) * LBO, LBO, SBO), idesc, k0 > 0);
+    for (int k0 = 0; k0 < KC; k0 += 8)
+        mma_tf32_ts(d, wg_base + AW + k0, smem_desc(whi + ((KOFF + k0) / 4) * LBO, LBO, SBO), idesc, (KOFF + k0) > 0);
 #pragma unroll
-    for (int k0 = 0; k0 < KP; k0 += 8)
-        mma_tf32_ts(d, wg_base + k0, smem_desc(wlo + (k0 / 4) * LBO, LBO, SBO), idesc, 1);
+    for (int k0 = 0; k0 < KC; k0 += 8)
+        mma_tf32_ts(d, wg_base + k0, smem_desc(wlo + ((KOFF + k0) / 4) * LBO, LBO, SBO), idesc, 1);
 #pragma unroll
-    for (int k0 = 0; k0 < KP; k0 += 8)
-        mma_tf32_ts(d, wg_base + k0, smem_desc(whi + (k0 / 4) * LBO, LBO, SBO), idesc, 1);
+    for (int k0 = 0; k0 < KC; k0 += 8)
+        mma_tf32_ts(d, wg_base + k0, smem_desc(whi + ((KOFF + k0) / 4) * LBO, LBO, SBO), idesc, 1);
     mma_commit(bar);
 }
 
+// `keep` carries the second half of a 128-wide delta from one layer's epilogue to the next layer's second
+// round of MMAs (the first round overwrites the accumulator the values came from).
 template <class CFG, int L>
 __device__ __forceinline__ void dgrad_layer(const BwdArgs &ba, uint32_t wg_base, uint32_t lane_addr, const float *swt,
                                             uint64_t *bar, uint32_t &phase, int wg, int t, long long gp, bool valid,
-                                            int b, int p)
+                                            int b, int p, float (&keep)[64])
 {
-    constexpr int NP = CFG::K(L), KMAX = DgradCfg<CFG>::kmax();
+    constexpr int KP = CFG::N(L), NP = CFG::K(L), AW = kDgradAW<CFG>;
+    constexpr int KC = KP < AW ? KP : AW;
+    static_assert(KP == KC || KP == 2 * AW, "one or two rounds");
     const long long npp = ba.npx_pad;
     wait_st();
     fence_before_sync();
     named_bar_sync(1 + wg, kTile);
     if (t == 0) {
         fence_after_sync();
-        tc_issue_dgrad<CFG, L>(wg_base, swt, bar);
+        tc_issue_dgrad<CFG, L, 0, KC>(wg_base, swt, bar);
     }
     float av[16];
     if constexpr (L > 0) {                                        // first chunk of a_l travels under the MMAs
@@ -234,12 +244,35 @@ __device__ __forceinline__ void dgrad_layer(const BwdArgs &ba, uint32_t wg_base,
     mbar_wait(bar, phase);
     phase ^= 1;
     fence_after_sync();
+    if constexpr (KP > KC) {                                      // second round: channels AW .. 2AW-1 of delta
+#pragma unroll
+        for (int n0 = 0; n0 < AW; n0 += 16) {
+            uint32_t r[16], lo[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                r[j] = __float_as_uint(keep[n0 + j]);
+                lo[j] = __float_as_uint(tf32_lo(keep[n0 + j]));
+            }
+            tmem_st<16>(lane_addr + n0, r);
+            tmem_st<16>(lane_addr + AW + n0, lo);
+        }
+        wait_st();
+        fence_before_sync();
+        named_bar_sync(1 + wg, kTile);
+        if (t == 0) {
+            fence_after_sync();
+            tc_issue_dgrad<CFG, L, AW, AW>(wg_base, swt, bar);
+        }
+        mbar_wait(bar, phase);
+        phase ^= 1;
+        fence_after_sync();
+    }
     if constexpr (L == 0) {
         float *gx = ba.a.grad_x + (size_t)b * NP * ba.a.hw + p;
 #pragma unroll 1
         for (int n0 = 0; n0 < NP; n0 += 16) {
             uint32_t r[16];
-            tmem_ld<16>(lane_addr + 2 * KMAX + n0, r);
+            tmem_ld<16>(lane_addr + 2 * AW + n0, r);
             wait_ld();
             if (valid) {
 #pragma unroll
@@ -258,17 +291,23 @@ __device__ __forceinline__ void dgrad_layer(const BwdArgs &ba, uint32_t wg_base,
 #pragma unroll
                 for (int j = 0; j < 16; ++j) nx[j] = __ldcg(act + (size_t)(n0 + 16 + j) * npp);
             }
-            tmem_ld<16>(lane_addr + 2 * KMAX + n0, r);
+            tmem_ld<16>(lane_addr + 2 * AW + n0, r);
             wait_ld();
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
                 const float v = __uint_as_float(r[j]) * elu_grad_from_out(av[j]);
                 del[(size_t)(n0 + j) * npp] = v;
-                r[j] = __float_as_uint(v);
-                lo[j] = __float_as_uint(tf32_lo(v));
+                if (n0 < AW) {
+                    r[j] = __float_as_uint(v);
+                    lo[j] = __float_as_uint(tf32_lo(v));
+                } else {
+                    keep[n0 - AW + j] = v;
+                }
             }
-            tmem_st<16>(lane_addr + n0, r);
-            tmem_st<16>(lane_addr + KMAX + n0, lo);
+            if (n0 < AW) {
+                tmem_st<16>(lane_addr + n0, r);
+                tmem_st<16>(lane_addr + AW + n0, lo);
+            }
             if (n0 + 16 < NP) {
 #pragma unroll
                 for (int j = 0; j < 16; ++j) av[j] = nx[j];
@@ -283,8 +322,8 @@ __device__ __forceinline__ void dgrad_layer(const BwdArgs &ba, uint32_t wg_base,
 template <class CFG, int NWG, int TM>
 __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_dgrad_kernel(BwdArgs ba)
 {
-    constexpr int KMAX = DgradCfg<CFG>::kmax(), NMAX = DgradCfg<CFG>::nmax();
-    constexpr int COLS = 2 * KMAX + NMAX;
+    constexpr int AW = kDgradAW<CFG>, NMAX = DgradCfg<CFG>::nmax();
+    constexpr int COLS = 2 * AW + NMAX;
     constexpr int IMG = CFG::tail_off();          // floats of transposed images
     static_assert(NWG * COLS <= 512, "TMEM budget");
     extern __shared__ __align__(128) float smem[];
@@ -330,7 +369,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_dgrad_kernel(BwdArgs 
 #pragma unroll
             for (int j = 0; j < 16; ++j) lo[j] = __float_as_uint(tf32_lo(__uint_as_float(hi[j])));
             tmem_st<16>(lane_addr, hi);
-            tmem_st<16>(lane_addr + KMAX, lo);
+            tmem_st<16>(lane_addr + AW, lo);
         } else {
             constexpr int LAST = TM == 0 ? 1 : 3;
             const TcArgs &a = ba.a;
@@ -395,12 +434,13 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_dgrad_kernel(BwdArgs 
                 lo[j] = __float_as_uint(tf32_lo(v));
             }
             tmem_st<16>(lane_addr, hi);
-            tmem_st<16>(lane_addr + KMAX, lo);
+            tmem_st<16>(lane_addr + AW, lo);
         }
-        if constexpr (CFG::NW > 3) dgrad_layer<CFG, 3>(ba, wg_base, lane_addr, swt, bar, phase, wg, t, gp, valid, b, p);
-        if constexpr (CFG::NW > 2) dgrad_layer<CFG, 2>(ba, wg_base, lane_addr, swt, bar, phase, wg, t, gp, valid, b, p);
-        if constexpr (CFG::NW > 1) dgrad_layer<CFG, 1>(ba, wg_base, lane_addr, swt, bar, phase, wg, t, gp, valid, b, p);
-        if (ba.a.grad_x != nullptr) dgrad_layer<CFG, 0>(ba, wg_base, lane_addr, swt, bar, phase, wg, t, gp, valid, b, p);
+        float keep[64];
+        if constexpr (CFG::NW > 3) dgrad_layer<CFG, 3>(ba, wg_base, lane_addr, swt, bar, phase, wg, t, gp, valid, b, p, keep);
+        if constexpr (CFG::NW > 2) dgrad_layer<CFG, 2>(ba, wg_base, lane_addr, swt, bar, phase, wg, t, gp, valid, b, p, keep);
+        if constexpr (CFG::NW > 1) dgrad_layer<CFG, 1>(ba, wg_base, lane_addr, swt, bar, phase, wg, t, gp, valid, b, p, keep);
+        if (ba.a.grad_x != nullptr) dgrad_layer<CFG, 0>(ba, wg_base, lane_addr, swt, bar, phase, wg, t, gp, valid, b, p, keep);
     }
     fence_before_sync();
     __syncthreads();
@@ -847,7 +887,7 @@ static int dispatch_bwd_stash(const ChainParams &cp, const TcArgs &a, int mode, 
 int launch_chain_tc_bwd_stash(const ChainParams &cp, const TcArgs &a, int mode, int r, void *ws, int sms, cudaStream_t s)
 {
     char *w = static_cast<char *>(ws);
-    if (cfg_matches<Cfg128_128>(cp)) return dispatch_bwd_stash<Cfg128_128, 1>(cp, a, mode, r, w, sms, s);
+    if (cfg_matches<Cfg128_128>(cp)) return dispatch_bwd_stash<Cfg128_128, 2>(cp, a, mode, r, w, sms, s);
     if (cfg_matches<Cfg128_64>(cp)) return dispatch_bwd_stash<Cfg128_64, 2>(cp, a, mode, r, w, sms, s);
     if (cfg_matches<Cfg64_64>(cp)) return dispatch_bwd_stash<Cfg64_64, 2>(cp, a, mode, r, w, sms, s);
     if (cfg_matches<Cfg32_32>(cp)) return dispatch_bwd_stash<Cfg32_32, 3>(cp, a, mode, r, w, sms, s);
@@ -871,7 +911,7 @@ static int dispatch_bwd_mode(const ChainParams &cp, const TcArgs &a, int mode, i
 int launch_chain_tc_bwd(const ChainParams &cp, const TcArgs &a, int mode, int r, void *ws, int sms, cudaStream_t s)
 {
     char *w = static_cast<char *>(ws);
-    if (cfg_matches<Cfg128_128>(cp)) return dispatch_bwd_mode<Cfg128_128, 2, 1, 64>(cp, a, mode, r, w, sms, s);
+    if (cfg_matches<Cfg128_128>(cp)) return dispatch_bwd_mode<Cfg128_128, 2, 2, 64>(cp, a, mode, r, w, sms, s);
     if (cfg_matches<Cfg128_64>(cp)) return dispatch_bwd_mode<Cfg128_64, 2, 2, 64>(cp, a, mode, r, w, sms, s);
     if (cfg_matches<Cfg64_64>(cp)) return dispatch_bwd_mode<Cfg64_64, 2, 2>(cp, a, mode, r, w, sms, s);
     if (cfg_matches<Cfg64_32>(cp)) return dispatch_bwd_mode<Cfg64_32, 3, 3>(cp, a, mode, r, w, sms, s);
