@@ -413,6 +413,8 @@ def main():
     device = torch.device("cuda", local_rank)
     if world > 1:
         import torch.distributed as dist
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"          # keep NCCL's version banner off stdout: ONE JSON line
         dist.init_process_group("nccl", device_id=device)
         _DIST["on"] = True
     lib = _cabi.lib()
@@ -508,7 +510,7 @@ def main():
                        "l2": "inputs %.0f MB per step > 126 MB L2 (no flush needed)" % (in_bytes / 1e6),
                        "api": "bts_b200.reduction_1x1 / fused_stage via libbts_b200.so C ABI",
                        "launch": launch_mode},
-            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches),
+            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches) * world,
             "clocks": clocks.summary(),
         }
         print(json.dumps(line), flush=True)
