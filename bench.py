@@ -53,6 +53,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the CPU port timing (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer end-to-end leg (profiling runs)")
     ap.add_argument("--kernel-only", action="store_true", help="only the timed device loop (for ncu)")
+    ap.add_argument("--e2e-serial", action="store_true", help="end-to-end leg on one stream (no upload/download overlap)")
     ap.add_argument("--no-graph", action="store_true", help="launch every step eagerly instead of replaying a CUDA graph")
     return ap.parse_args()
 
@@ -295,57 +296,82 @@ def measured_traffic(kernel):
         return None
 
 
-def e2e_leg(stages, wl, steps, warmup, device):
+def e2e_leg(stages, wl, steps, warmup, device, pipelined=True):
     """Same step through the public module API with HOST buffers: every step copies the features and
     upstream gradients from pinned host memory, and reads every result (depth maps / head output,
-    grad_x, grad_W, abs_min) back to pinned host memory, inside the timed region."""
+    grad_x, grad_W, abs_min) back to pinned host memory, inside the timed region.
+
+    pipelined: three streams (upload / compute / download) and two sets of device input and host output
+    buffers, so step i+1's upload and step i-1's download overlap step i (PCIe is full duplex); every
+    dependency is an event, the timed region ends with a full device synchronisation. serial: one stream."""
     import torch
-    host_in, host_out = [], []
+    host_in = []
     for st in stages:
-        hx = st["x"].detach().cpu().pin_memory()
-        hg = st["g"].cpu().pin_memory()
-        host_in.append((hx, hg))
+        host_in.append((st["x"].detach().cpu().pin_memory(), st["g"].cpu().pin_memory()))
     h2d = sum(hx.numel() * 4 + hg.numel() * 4 for hx, hg in host_in)
-    dev_in = [(torch.empty_like(st["x"]).requires_grad_(True), torch.empty_like(st["g"])) for st in stages]
-    outs_host = None
-    d2h = 0
+    nset = 2 if pipelined else 1
+    dev_in = [[(torch.empty_like(st["x"]).requires_grad_(True), torch.empty_like(st["g"])) for st in stages]
+              for _ in range(nset)]
+    host_out = [None] * nset
+    d2h = [0]
+    cur = torch.cuda.current_stream()
+    s_in, s_comp, s_out = (torch.cuda.Stream(), torch.cuda.Stream(), torch.cuda.Stream()) if pipelined else (cur, cur, cur)
+    ev_free = [None] * nset          # compute of the step that last used input set j has finished
 
-    def step():
-        nonlocal outs_host, d2h
-        results = []
-        for st, (hx, hg), (dx, dg) in zip(stages, host_in, dev_in):
-            with torch.no_grad():
-                dx.copy_(hx, non_blocking=True)
-                dg.copy_(hg, non_blocking=True)
-            dx.grad = None
-            for p in st["red"].parameters():
-                p.grad = None
-            saved = st["x"]
-            st["x"] = dx
-            out = stage_forward(st)
-            out.backward(dg)
-            st["x"] = saved
-            res = [out.detach(), dx.grad] + [p.grad for p in st["red"].parameters()]
-            if st["lpg"] is not None:
-                res.append(st["lpg"].abs_min)
-            results.append(res)
-        if outs_host is None:
-            outs_host = [[torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in res] for res in results]
-            d2h = sum(t.numel() * 4 for res in results for t in res)
-        for res, hres in zip(results, outs_host):
-            for t, ht in zip(res, hres):
-                ht.copy_(t, non_blocking=True)
+    def step(i):
+        j = i % nset
+        ev_in, ev_comp, results = [], [], []
+        with torch.cuda.stream(s_in):
+            if ev_free[j] is not None:
+                s_in.wait_event(ev_free[j])
+            for (hx, hg), (dx, dg) in zip(host_in, dev_in[j]):
+                with torch.no_grad():
+                    dx.copy_(hx, non_blocking=True)
+                    dg.copy_(hg, non_blocking=True)
+                e = torch.cuda.Event()
+                e.record(s_in)
+                ev_in.append(e)
+        with torch.cuda.stream(s_comp):
+            for k, (st, (dx, dg)) in enumerate(zip(stages, dev_in[j])):
+                s_comp.wait_event(ev_in[k])
+                dx.grad = None
+                for p in st["red"].parameters():
+                    p.grad = None
+                saved = st["x"]
+                st["x"] = dx
+                out = stage_forward(st)
+                out.backward(dg)
+                st["x"] = saved
+                res = [out.detach(), dx.grad] + [p.grad for p in st["red"].parameters()]
+                if st["lpg"] is not None:
+                    res.append(st["lpg"].abs_min)
+                if pipelined:
+                    for t in res:
+                        t.record_stream(s_out)
+                results.append(res)
+                e = torch.cuda.Event()
+                e.record(s_comp)
+                ev_comp.append(e)
+            ev_free[j] = ev_comp[-1]
+        if host_out[j] is None:
+            host_out[j] = [[torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in res] for res in results]
+            d2h[0] = sum(t.numel() * 4 for res in results for t in res)
+        with torch.cuda.stream(s_out):
+            for k, (res, hres) in enumerate(zip(results, host_out[j])):
+                s_out.wait_event(ev_comp[k])
+                for t, ht in zip(res, hres):
+                    ht.copy_(t, non_blocking=True)
 
-    for _ in range(max(1, warmup)):
-        step()
+    for i in range(max(2, warmup)):
+        step(i)
     torch.cuda.synchronize()
     barrier()
     t0 = time.perf_counter()
-    for _ in range(steps):
-        step()
+    for i in range(steps):
+        step(i)
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
-    return dt, h2d, d2h
+    return dt, h2d, d2h[0], host_out
 
 
 _DIST = {"on": False}
@@ -488,11 +514,13 @@ def main():
     e2e = None
     if not args.no_e2e:
         e_steps = max(2, min(args.steps, 10))
-        dt, h2d, d2h = e2e_leg(stages, wl, e_steps, 2, device)
+        dt, h2d, d2h, _ = e2e_leg(stages, wl, e_steps, 2, device, pipelined=not args.e2e_serial)
         dt = max_over_ranks(dt, device)
         e2e = {"value": world * px_per_rank * e_steps / dt / 1e6, "unit": "Mpixels/s",
                "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": e_steps,
                "ms_per_step": dt / e_steps * 1e3,
+               "mode": "serial (one stream)" if args.e2e_serial else
+                       "pipelined (upload / compute / download streams, double-buffered inputs and host outputs)",
                "what": "module API with pinned HOST buffers: H2D of features + upstream grads, D2H of every "
                        "output (depths, grad_x, grad_W, abs_min) inside the timed region"}
 
