@@ -286,6 +286,34 @@ def time_calls(stages, wl, device, iters=20):
     return res
 
 
+def time_standalone_lpg(wl, device, iters=20):
+    """Strict drop-in local_planar_guidance alone (SURVEY.md 8(d) report 4): plane_eq [B,4,h,w] -> depth
+    [B,H,W] and back, per upratio; algorithmic bytes fwd 16/r^2 + 4, bwd 4 + 32/r^2 per full-res pixel."""
+    import torch
+    from bts_b200 import _cabi
+    from bts_b200 import functional as Fn
+    lib = _cabi.lib()
+    stream = torch.cuda.current_stream().cuda_stream
+    B, H, W = wl["B"], wl["H"], wl["W"]
+    px = B * H * W
+    res = {}
+    for r in (8, 4, 2):
+        h, w = H // r, W // r
+        th = torch.rand(B, h, w, device=device) * 1.0
+        ph = torch.rand(B, h, w, device=device) * 6.28
+        pe = torch.stack([th.sin() * ph.cos(), th.sin() * ph.sin(), th.cos(), torch.rand(B, h, w, device=device) * 10], 1).contiguous()
+        depth = torch.empty(B, H, W, device=device)
+        g = torch.randn(B, H, W, device=device)
+        gpe = torch.empty_like(pe)
+        amin = torch.full((), float("inf"), device=device)
+        f = lambda: _cabi.check(lib.bts_lpg_fwd(pe.data_ptr(), depth.data_ptr(), amin.data_ptr(), B, h, w, r, Fn.EPS, stream), "bts_lpg_fwd")
+        b = lambda: _cabi.check(lib.bts_lpg_bwd(g.data_ptr(), pe.data_ptr(), gpe.data_ptr(), B, h, w, r, Fn.EPS, stream), "bts_lpg_bwd")
+        tf, tb = time_back_to_back(f, iters), time_back_to_back(b, iters)
+        fb, bb = 16.0 / (r * r) + 4.0, 4.0 + 32.0 / (r * r)
+        res["lpg%dx%d_standalone" % (r, r)] = dict(fwd_ms=tf, bwd_ms=tb, fwd_gbs=fb * px / tf / 1e6, bwd_gbs=bb * px / tb / 1e6)
+    return res
+
+
 def measured_traffic(kernel):
     """DRAM bytes per launch of the dominant call from the committed ncu --set full capture, or None."""
     try:
@@ -509,7 +537,7 @@ def main():
                 "algorithmic_bytes_per_launch": algo_b, "launch_ms": dd[dk + "_ms"],
                 "whole_step": {"algorithmic_bytes": step_bytes, "achieved": step_bytes / (ms_step * 1e-3) / 1e9,
                                "frac": step_bytes / (ms_step * 1e-3) / 1e9 / peak},
-                "per_call": calls}
+                "per_call": calls, "standalone_lpg": time_standalone_lpg(wl, device)}
 
     e2e = None
     if not args.no_e2e:

@@ -44,7 +44,16 @@ for _n in ("bts_reduc_fwd", "bts_reduc_bwd", "bts_reduc_lpg_fwd", "bts_reduc_lpg
     _SIGNATURES[_n + "_stash"] = (_res, _args[:-1] + _STASH_TAIL)
 _SIGNATURES["bts_stash_bytes"] = (ctypes.c_size_t, [ctypes.POINTER(ctypes.c_int), ctypes.c_int, ctypes.c_int,
                                                     ctypes.c_int, ctypes.c_int])
-ABI_VERSION = 2
+_P, _I, _F, _LL, _SZ = ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_longlong, ctypes.c_size_t
+_SIGNATURES["bts_reduc_lpg_fwd_glue"] = (ctypes.c_int, [
+    _P, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_int), _I, _F, _I, _I, _I, _I, _F, _F,   # x .. eps, depth_div
+    _P, _P, _LL, _P, _LL, _P,                                    # plane_eq_out, depth, depth_bstride, ds_out, ds_bstride, abs_min
+    _P, _SZ, _P, _SZ, _P])                                       # ws, ws_bytes, stash, stash_bytes, stream
+_SIGNATURES["bts_reduc_lpg_bwd_glue"] = (ctypes.c_int, [
+    _P, _LL, _P, _LL, _F,                                        # grad_depth, grad_bstride, grad_ds, grad_ds_bstride, depth_div
+    _P, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_int), _I, _F, _I, _I, _I, _I, _F,       # x .. eps
+    _P, ctypes.POINTER(ctypes.c_void_p), _P, _SZ, _P, _SZ, _P])  # grad_x, grad_W, ws, ws_bytes, stash, stash_bytes, stream
+ABI_VERSION = 3
 
 _lib = None
 

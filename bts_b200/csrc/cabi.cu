@@ -33,6 +33,8 @@ int check_launch(const char *what)
 // kernels / launchers implemented elsewhere
 int launch_lpg_fwd(const float *, float *, float *, int, int, int, int, float, cudaStream_t);
 int launch_lpg_bwd(const float *, const float *, float *, int, int, int, int, float, cudaStream_t);
+int launch_lpg_fwd_glue(const float *, float *, float *, int, int, int, int, float, const LpgGlue &, cudaStream_t);
+int launch_lpg_bwd_glue(const float *, const float *, float *, int, int, int, int, float, const LpgGlue &, cudaStream_t);
 int launch_chain_generic_fwd(const ChainParams &, const float *, float *, int, int, cudaStream_t);
 int launch_chain_generic_bwd(const ChainParams &, const float *, const float *, float *, int, int, cudaStream_t);
 int launch_chain_tc_fwd(const ChainParams &, const TcArgs &, int r, int sms, cudaStream_t);
@@ -86,6 +88,7 @@ static TcArgs make_tc_args(const float *x, int B, int h, int w, float max_depth,
     a.x = x; a.B = B; a.h = h; a.w = w; a.hw = h * w; a.npx = (long long)B * h * w;
     a.max_depth = max_depth; a.eps = eps;
     a.x_vec16 = ((h * w) % 4 == 0 && aligned16(x)) ? 1 : 0;
+    a.depth_div = 1.f;
     return a;
 }
 
@@ -268,15 +271,41 @@ int bts_reduc_lpg_fwd_stash(const float *x, const float *const *W, const int *di
                             float *depth, float *abs_min, void *ws, size_t ws_bytes, void *stash,
                             size_t stash_bytes, void *stream)
 {
+    return bts_reduc_lpg_fwd_glue(x, W, dims, n_layers, max_depth, B, h, w, r, eps, 1.f, plane_eq_out, depth, 0, nullptr,
+                                  0, abs_min, ws, ws_bytes, stash, stash_bytes, stream);
+}
+
+static int check_glue(int r, float depth_div, long long bstride, const void *ds, long long ds_bstride, int h, int w)
+{
+    if (!(depth_div > 0.f)) return set_error(BTS_ERR_BAD_ARG, "depth_div must be positive");
+    if (bstride != 0 && bstride < (long long)h * r * w * r)
+        return set_error(BTS_ERR_BAD_ARG, "batch stride %lld smaller than one %dx%d map", bstride, h * r, w * r);
+    if (ds != nullptr && (r % 2 != 0))
+        return set_error(BTS_ERR_BAD_ARG, "the down-sampled map needs an even upratio, got %d", r);
+    if (ds != nullptr && ds_bstride != 0 && ds_bstride < (long long)4 * h * w)
+        return set_error(BTS_ERR_BAD_ARG, "down-sampled batch stride %lld smaller than one %dx%d map", ds_bstride, 2 * h, 2 * w);
+    return BTS_OK;
+}
+
+int bts_reduc_lpg_fwd_glue(const float *x, const float *const *W, const int *dims, int n_layers,
+                           float max_depth, int B, int h, int w, int r, float eps, float depth_div,
+                           float *plane_eq_out, float *depth, long long depth_bstride, float *ds_out,
+                           long long ds_bstride, float *abs_min, void *ws, size_t ws_bytes, void *stash,
+                           size_t stash_bytes, void *stream)
+{
     ChainParams cp;
     if (int e = fill_chain(cp, W, nullptr, dims, n_layers, 0, max_depth)) return e;
     if (int e = check_shape(B, h, w)) return e;
     if (r < 1) return set_error(BTS_ERR_BAD_ARG, "upratio r=%d must be >= 1", r);
+    if (int e = check_glue(r, depth_div, depth_bstride, ds_out, ds_bstride, h, w)) return e;
     if ((long long)B * h * w == 0) return BTS_OK;
     if (!x || !depth) return set_error(BTS_ERR_BAD_ARG, "x / depth is NULL");
-    if ((r == 1 || r == 2 || r == 4 || r == 8) && use_tc(cp, ws, ws_bytes, depth)) {
+    const long long dbs = depth_bstride ? depth_bstride : (long long)h * r * w * r;
+    const long long sbs = ds_bstride ? ds_bstride : (long long)4 * h * w;
+    if ((r == 1 || r == 2 || r == 4 || r == 8) && dbs % 4 == 0 && use_tc(cp, ws, ws_bytes, depth)) {
         TcArgs a = make_tc_args(x, B, h, w, max_depth, eps);
         a.out = plane_eq_out; a.depth = depth; a.abs_min = abs_min;
+        a.depth_div = depth_div; a.depth_bstride = dbs; a.ds_out = ds_out; a.ds_bstride = sbs;
         if (use_stash(cp, x, B, h * w, stash, stash_bytes))
             if (int e = tc_stash_bind(cp, a, stash, true, (cudaStream_t)stream)) return e;
         return launch_chain_tc_fwd(cp, a, r, sm_count(), (cudaStream_t)stream);
@@ -289,7 +318,8 @@ int bts_reduc_lpg_fwd_stash(const float *x, const float *const *W, const int *di
         pe = reinterpret_cast<float *>(static_cast<char *>(ws) + tc_pack_bytes());
     }
     if (int e = launch_chain_generic_fwd(cp, x, pe, B, h * w, (cudaStream_t)stream)) return e;
-    return launch_lpg_fwd(pe, depth, abs_min, B, h, w, r, eps, (cudaStream_t)stream);
+    const LpgGlue gl{depth_div, dbs, ds_out, nullptr, sbs};
+    return launch_lpg_fwd_glue(pe, depth, abs_min, B, h, w, r, eps, gl, (cudaStream_t)stream);
 }
 
 int bts_reduc_lpg_bwd(const float *grad_depth, const float *x, const float *const *W, const int *dims,
@@ -305,15 +335,29 @@ int bts_reduc_lpg_bwd_stash(const float *grad_depth, const float *x, const float
                             float *grad_x, float *const *grad_W, void *ws, size_t ws_bytes, const void *stash,
                             size_t stash_bytes, void *stream)
 {
+    return bts_reduc_lpg_bwd_glue(grad_depth, 0, nullptr, 0, 1.f, x, W, dims, n_layers, max_depth, B, h, w, r, eps, grad_x,
+                                  grad_W, ws, ws_bytes, stash, stash_bytes, stream);
+}
+
+int bts_reduc_lpg_bwd_glue(const float *grad_depth, long long grad_bstride, const float *grad_ds,
+                           long long grad_ds_bstride, float depth_div, const float *x, const float *const *W,
+                           const int *dims, int n_layers, float max_depth, int B, int h, int w, int r, float eps,
+                           float *grad_x, float *const *grad_W, void *ws, size_t ws_bytes, const void *stash,
+                           size_t stash_bytes, void *stream)
+{
     ChainParams cp;
     if (int e = fill_chain(cp, W, grad_W, dims, n_layers, 0, max_depth)) return e;
     if (int e = check_shape(B, h, w)) return e;
     if (r < 1) return set_error(BTS_ERR_BAD_ARG, "upratio r=%d must be >= 1", r);
+    if (int e = check_glue(r, depth_div, grad_bstride, grad_ds, grad_ds_bstride, h, w)) return e;
     if ((long long)B * h * w == 0) return BTS_OK;
     if (!x || !grad_depth) return set_error(BTS_ERR_BAD_ARG, "x / grad_depth is NULL");
-    if ((r == 1 || r == 2 || r == 4 || r == 8) && use_tc_bwd(cp, ws, ws_bytes, B, h * w, grad_depth)) {
+    const long long gbs = grad_bstride ? grad_bstride : (long long)h * r * w * r;
+    const long long sbs = grad_ds_bstride ? grad_ds_bstride : (long long)4 * h * w;
+    if ((r == 1 || r == 2 || r == 4 || r == 8) && gbs % 4 == 0 && use_tc_bwd(cp, ws, ws_bytes, B, h * w, grad_depth)) {
         TcArgs a = make_tc_args(x, B, h, w, max_depth, eps);
         a.grad = grad_depth; a.grad_x = grad_x;
+        a.depth_div = depth_div; a.grad_bstride = gbs; a.grad_ds = grad_ds; a.grad_ds_bstride = sbs;
         if (use_stash(cp, x, B, h * w, stash, stash_bytes)) {
             if (int e = tc_stash_bind(cp, a, const_cast<void *>(stash), false, (cudaStream_t)stream)) return e;
             return launch_chain_tc_bwd_stash(cp, a, 2, r, ws, sm_count(), (cudaStream_t)stream);
@@ -332,7 +376,8 @@ int bts_reduc_lpg_bwd_stash(const float *grad_depth, const float *x, const float
     ChainParams cf = cp;
     for (int l = 0; l < BTS_MAX_LAYERS; ++l) cf.gW[l] = nullptr;
     if (int e = launch_chain_generic_fwd(cf, x, pe, B, h * w, s)) return e;
-    if (int e = launch_lpg_bwd(grad_depth, pe, gpe, B, h, w, r, eps, s)) return e;
+    const LpgGlue gl{depth_div, gbs, nullptr, grad_ds, sbs};
+    if (int e = launch_lpg_bwd_glue(grad_depth, pe, gpe, B, h, w, r, eps, gl, s)) return e;
     return launch_chain_generic_bwd(cp, x, gpe, grad_x, B, h * w, s);
 }
 

@@ -319,8 +319,10 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
             }
             if constexpr (GPRE) {
                 const uint32_t gd = smem_u32(gs);
-                if constexpr (MODE == 0 || (MODE == 2 && R == 1)) {
+                if constexpr (MODE == 0) {
                     cp_async4(gd, a.grad + (ok ? gp : 0), ok);
+                } else if constexpr (MODE == 2 && R == 1) {
+                    cp_async4(gd, a.grad + (size_t)b * a.grad_bstride + p, ok);
                 } else if constexpr (MODE == 1) {
                     const float *gq = a.grad + (size_t)b * 4 * a.hw + p;
 #pragma unroll
@@ -328,7 +330,7 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
                 } else {                                          // R == 2: the 2 x 2 block of grad_depth
                     const int i = p / a.w, j = p - i * a.w;
                     const int Wd = a.w * 2;
-                    const float *g0 = a.grad + ((size_t)b * a.h + i) * 2 * (size_t)Wd + (size_t)j * 2;
+                    const float *g0 = a.grad + (size_t)b * a.grad_bstride + (size_t)i * 2 * (size_t)Wd + (size_t)j * 2;
                     cp_async8(gd, g0, ok);
                     cp_async8(gd + 8, g0 + Wd, ok);
                 }
@@ -423,7 +425,8 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
                                 lpg_bwd_accum(acc, gcur[pp * R + k], __fmul_rn(pl.n1, u), n2v, pl.n3, u, v, a.eps);
                             }
                         }
-                        gg[0] = -pl.n4 * acc.tu; gg[1] = -pl.n4 * acc.tv; gg[2] = -pl.n4 * acc.t; gg[3] = acc.s4;
+                        const float sc = a.depth_div != 1.f ? __fdiv_rn(1.f, a.depth_div) : 1.f;
+                        gg[0] = -pl.n4 * acc.tu * sc; gg[1] = -pl.n4 * acc.tv * sc; gg[2] = -pl.n4 * acc.t * sc; gg[3] = acc.s4 * sc;
                     } else {
                         lpg_block_grad<R>(a, pl, b, p, gg);
                     }

@@ -87,6 +87,18 @@ struct TcArgs {
     float *stash_pe;
     long long stash_npp;
     int stash_hw_pad;
+    // post-LPG glue (pytorch/bts.py:255-256, 269-270, 283) folded into the fused stage: the depth map is divided
+    // by depth_div (max_depth; 1 = plain depth), images are depth_bstride elements apart (a channel slice of a
+    // concat buffer; h*R*w*R when dense), and ds_out [B][2h][2w] (nullable, upratio 8 / 4 only) receives the
+    // nearest-neighbour down-sampling by R/2 = rows/cols 0 and R/2 of every block. Backward twins: grad of the
+    // scaled map with its batch stride, grad of the down-sampled map (nullable).
+    float depth_div;
+    long long depth_bstride;
+    float *ds_out;
+    long long ds_bstride;
+    long long grad_bstride;
+    const float *grad_ds;
+    long long grad_ds_bstride;
 };
 
 // Chains whose backward is the multi-kernel one (chain_tc_bwd.cu) can leave their activations in a
@@ -283,6 +295,7 @@ __device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, f
 {
     // all index arithmetic is 32-bit: the C ABI rejects more than 2^31 - 1 low-res pixels
     int key = 0x7f800000;
+    if (a.depth_div != 1.f) n4 = __fdiv_rn(n4, a.depth_div);       // depth / max_depth = (n4 / max_depth) / den
     if constexpr (R == 8) {
         // two 512 B stores per output row and warp: lane L writes columns (L&1)*4..+3 of pixel 16*half + L/2
         const unsigned gp0 = gp - (unsigned)lane;
@@ -298,7 +311,8 @@ __device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, f
                 const int i = rem / a.w, j = rem - i * a.w;
                 const int q0 = (lane & 1) * 4;
                 const int Wd = a.w * 8;
-                float *out = a.depth + ((size_t)b * a.h + i) * 8 * (size_t)Wd + (size_t)j * 8 + q0;
+                float *out = a.depth + (size_t)b * a.depth_bstride + (size_t)i * 8 * (size_t)Wd + (size_t)j * 8 + q0;
+                float *ds = a.ds_out ? a.ds_out + (size_t)b * a.ds_bstride + (size_t)(2 * i) * (2 * a.w) + 2 * j + (lane & 1) : nullptr;
                 float n1u[4];
 #pragma unroll
                 for (int k = 0; k < 4; ++k) n1u[k] = __fmul_rn(m1, lpg_offset(q0 + k, 8));
@@ -314,6 +328,7 @@ __device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, f
                         op[k] = __fdiv_rn(m4, lpg_clamp(den, a.eps));
                     }
                     *reinterpret_cast<float4 *>(out + (size_t)p * Wd) = o;
+                    if ((p & 3) == 0 && ds != nullptr) ds[(size_t)(p >> 2) * (2 * a.w)] = op[0];   // rows 0, 4; cols 0, 4
                 }
             }
         }
@@ -321,7 +336,7 @@ __device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, f
         const int b = b_own, rem = p_own;
         const int i = rem / a.w, j = rem - i * a.w;
         const int Wd = a.w * R;
-        float *out = a.depth + ((size_t)b * a.h + i) * R * (size_t)Wd + (size_t)j * R;
+        float *out = a.depth + (size_t)b * a.depth_bstride + (size_t)i * R * (size_t)Wd + (size_t)j * R;
         float n1u[R];
 #pragma unroll
         for (int k = 0; k < R; ++k) n1u[k] = __fmul_rn(n1, lpg_offset(k, R));
@@ -336,6 +351,12 @@ __device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, f
                 o[k] = __fdiv_rn(n4, lpg_clamp(den, a.eps));
             }
             float *row = out + (size_t)p * Wd;
+            if constexpr (R == 4) {
+                if ((p & 1) == 0 && a.ds_out != nullptr) {        // rows 0, 2; cols 0, 2
+                    float *ds = a.ds_out + (size_t)b * a.ds_bstride + (size_t)(2 * i + (p >> 1)) * (2 * a.w) + 2 * j;
+                    ds[0] = o[0]; ds[1] = o[2];
+                }
+            }
             if constexpr (R == 4) *reinterpret_cast<float4 *>(row) = make_float4(o[0], o[1], o[2], o[3]);
             else if constexpr (R == 2) *reinterpret_cast<float2 *>(row) = make_float2(o[0], o[1]);
             else {
@@ -353,7 +374,7 @@ __device__ __forceinline__ void lpg_block_grad(const TcArgs &a, const PlaneFwd &
 {
     const int i = rem / a.w, j = rem - i * a.w;
     const int Wd = a.w * R;
-    const float *gp0 = a.grad + ((size_t)b * a.h + i) * R * (size_t)Wd + (size_t)j * R;
+    const float *gp0 = a.grad + (size_t)b * a.grad_bstride + (size_t)i * R * (size_t)Wd + (size_t)j * R;
     LpgAcc acc{0.f, 0.f, 0.f, 0.f};
 #pragma unroll
     for (int p = 0; p < R; ++p) {
@@ -372,6 +393,13 @@ __device__ __forceinline__ void lpg_block_grad(const TcArgs &a, const PlaneFwd &
 #pragma unroll
             for (int k = 0; k < R; ++k) gv[k] = __ldcs(row + k);
         }
+        if constexpr (R == 4 || R == 8) {                          // gradient of the down-sampled map lands on rows/cols 0, R/2
+            if (a.grad_ds != nullptr && (p % (R / 2)) == 0) {
+                const float *gd = a.grad_ds + (size_t)b * a.grad_ds_bstride + (size_t)(2 * i + p / (R / 2)) * (2 * a.w) + 2 * j;
+                gv[0] += __ldcs(gd);
+                gv[R / 2] += __ldcs(gd + 1);
+            }
+        }
         const float v = lpg_offset(p, R);
         const float n2v = __fmul_rn(pl.n2, v);
 #pragma unroll
@@ -380,7 +408,8 @@ __device__ __forceinline__ void lpg_block_grad(const TcArgs &a, const PlaneFwd &
             lpg_bwd_accum(acc, gv[k], __fmul_rn(pl.n1, u), n2v, pl.n3, u, v, a.eps);
         }
     }
-    g[0] = -pl.n4 * acc.tu; g[1] = -pl.n4 * acc.tv; g[2] = -pl.n4 * acc.t; g[3] = acc.s4;
+    const float sc = a.depth_div != 1.f ? __fdiv_rn(1.f, a.depth_div) : 1.f;   // d(depth / max_depth) / d depth
+    g[0] = -pl.n4 * acc.tu * sc; g[1] = -pl.n4 * acc.tv * sc; g[2] = -pl.n4 * acc.t * sc; g[3] = acc.s4 * sc;
 }
 
 // ---- last layer 8 -> (3|1): logits from a8 (shared by the forward tail and the stash backward, so both

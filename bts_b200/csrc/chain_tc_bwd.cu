@@ -802,7 +802,7 @@ static int launch_bwd_cfg(const ChainParams &cp, const TcArgs &a, char *ws, int 
 
 // ---- stash backward: the forward left a_1 .. a8 (and plane_eq for the fused stage) in the caller's stash,
 // so K1 disappears: [LPG block reduction at full parallelism ->] tail backward + dgrad -> wgrad -> reduce.
-int launch_lpg_bwd(const float *, const float *, float *, int, int, int, int, float, cudaStream_t);
+int launch_lpg_bwd_glue(const float *, const float *, float *, int, int, int, int, float, const LpgGlue &, cudaStream_t);
 bool fused_bwd_supported(const ChainParams &);
 bool tc_supported(const ChainParams &);
 
@@ -858,7 +858,8 @@ static int launch_bwd_stash_cfg(const ChainParams &cp, const TcArgs &a, int r, c
         ba.act = a.stash_act; ba.del = del; ba.npx_pad = npp; ba.hw_pad = a.stash_hw_pad;
         ba.w4 = cp.W[CFG::NW]; ba.w5 = cp.W[CFG::NW + 1];
         if (TM == 1 && r > 0) {              // grad_depth -> gradient of the plane parameters [B][4][hw]
-            if (int e = launch_lpg_bwd(a.grad, a.stash_pe, scratch, a.B, a.h, a.w, r, a.eps, s)) return e;
+            const LpgGlue gl{a.depth_div, a.grad_bstride, nullptr, a.grad_ds, a.grad_ds_bstride};
+            if (int e = launch_lpg_bwd_glue(a.grad, a.stash_pe, scratch, a.B, a.h, a.w, r, a.eps, gl, s)) return e;
             ba.a.grad = scratch;
         }
         const long long ntiles = npp / kTile;

@@ -77,6 +77,17 @@ __device__ __forceinline__ float lpg_clamp(float den, float eps)
 }
 
 // ---- LPG backward accumulation for one output pixel
+// post-LPG glue of the decoder (pytorch/bts.py:255-256, 269-270, 283) carried by the standalone LPG kernels when
+// they serve the fused stage on the generic route / the stash backward. Defaults = plain local_planar_guidance.
+struct LpgGlue {
+    float div;                 // depth is divided by this (max_depth); 1 = plain
+    long long bstride;         // elements between images of the full-resolution map (0 = dense H*W)
+    float *ds;                 // forward: nearest down-sampling by r/2, [B][2h][2w] (nullable; even r only)
+    const float *gds;          // backward: gradient of that map (nullable)
+    long long ds_bstride;
+};
+inline LpgGlue lpg_glue_none() { return LpgGlue{1.f, 0, nullptr, nullptr, 0}; }
+
 struct LpgAcc {
     float s4, t, tu, tv;
 };

@@ -21,7 +21,7 @@ namespace bts {
 template <int R>
 __global__ void __launch_bounds__(256)
 lpg_fwd_vec_kernel(const float *__restrict__ plane_eq, float *__restrict__ depth, float *abs_min,
-                   int B, int h, int w, float eps)
+                   int B, int h, int w, float eps, LpgGlue gl)
 {
     const int Wd = w * R;              // output width
     const int W4 = Wd >> 2;            // float4 groups per output row
@@ -54,8 +54,12 @@ lpg_fwd_vec_kernel(const float *__restrict__ plane_eq, float *__restrict__ depth
         }
 #pragma unroll
         for (int k = 0; k < 4; ++k) n1u[k] = __fmul_rn(n1u[k], lpg_offset((x0 + k) % R, R));
-
-        float *out = depth + ((size_t)b * h * R + (size_t)i * R) * Wd + x0;
+        if (gl.div != 1.f) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) n4[k] = __fdiv_rn(n4[k], gl.div);
+        }
+        const size_t bstride = gl.bstride ? (size_t)gl.bstride : (size_t)h * R * Wd;
+        float *out = depth + (size_t)b * bstride + (size_t)i * R * Wd + x0;
 #pragma unroll
         for (int p = 0; p < R; ++p) {
             const float v = lpg_offset(p, R);
@@ -69,6 +73,13 @@ lpg_fwd_vec_kernel(const float *__restrict__ plane_eq, float *__restrict__ depth
                 op[k] = __fdiv_rn(n4[k], den);
             }
             *reinterpret_cast<float4 *>(out + (size_t)p * Wd) = o;
+            if constexpr (R == 4 || R == 8) {                      // rows/cols 0 and R/2 of every block
+                if (gl.ds != nullptr && p % (R / 2) == 0) {
+                    float *d = gl.ds + (size_t)b * gl.ds_bstride + (size_t)(2 * i + p / (R / 2)) * (2 * w) + x0 / (R / 2);
+                    d[0] = op[0];
+                    if (R == 4) d[1] = op[2];
+                }
+            }
         }
     }
     block_absmin_commit(key, abs_min);
@@ -77,7 +88,7 @@ lpg_fwd_vec_kernel(const float *__restrict__ plane_eq, float *__restrict__ depth
 // forward, scalar path: any r >= 1, any w. One thread per output pixel.
 __global__ void __launch_bounds__(256)
 lpg_fwd_scalar_kernel(const float *__restrict__ plane_eq, float *__restrict__ depth, float *abs_min,
-                      int B, int h, int w, int r, float eps)
+                      int B, int h, int w, int r, float eps, LpgGlue gl)
 {
     const int Wd = w * r, Hd = h * r;
     const long long total = (long long)B * Hd * Wd;
@@ -95,7 +106,13 @@ lpg_fwd_scalar_kernel(const float *__restrict__ plane_eq, float *__restrict__ de
         float den = lpg_den(n1u, n2v, __ldg(pe + 2 * hw));
         key = absmin_key(den);
         den = lpg_clamp(den, eps);
-        depth[t] = __fdiv_rn(__ldg(pe + 3 * hw), den);
+        float n4 = __ldg(pe + 3 * hw);
+        if (gl.div != 1.f) n4 = __fdiv_rn(n4, gl.div);
+        const float o = __fdiv_rn(n4, den);
+        const size_t bstride = gl.bstride ? (size_t)gl.bstride : (size_t)Hd * Wd;
+        depth[(size_t)b * bstride + (size_t)y * Wd + xx] = o;
+        if (gl.ds != nullptr && (r & 1) == 0 && y % (r / 2) == 0 && xx % (r / 2) == 0)
+            gl.ds[(size_t)b * gl.ds_bstride + (size_t)(y / (r / 2)) * (2 * w) + xx / (r / 2)] = o;
     }
     block_absmin_commit(key, abs_min);
 }
@@ -108,7 +125,7 @@ lpg_fwd_scalar_kernel(const float *__restrict__ plane_eq, float *__restrict__ de
 template <int R>
 __global__ void __launch_bounds__(256)
 lpg_bwd_vec_kernel(const float *__restrict__ grad_depth, const float *__restrict__ plane_eq,
-                   float *__restrict__ grad_plane_eq, int B, int h, int w, float eps)
+                   float *__restrict__ grad_plane_eq, int B, int h, int w, float eps, LpgGlue gl)
 {
     constexpr int NPX = (R >= 4) ? 1 : 4 / R;    // low-res pixels fully or partly covered by a thread
     const int Wd = w * R;
@@ -138,10 +155,21 @@ lpg_bwd_vec_kernel(const float *__restrict__ grad_depth, const float *__restrict
             n3[n] = __ldg(plane_eq + base + 2 * hw + n);
             n4[n] = __ldg(plane_eq + base + 3 * hw + n);
         }
-        const float *gp = grad_depth + ((size_t)b * h * R + (size_t)i * R) * Wd + x0;
+        const size_t bstride = gl.bstride ? (size_t)gl.bstride : (size_t)h * R * Wd;
+        const float *gp = grad_depth + (size_t)b * bstride + (size_t)i * R * Wd + x0;
         float4 g[R];
 #pragma unroll
         for (int p = 0; p < R; ++p) g[p] = __ldcs(reinterpret_cast<const float4 *>(gp + (size_t)p * Wd));
+        if constexpr (R == 4 || R == 8) {                          // gradient of the down-sampled map
+            if (gl.gds != nullptr) {
+#pragma unroll
+                for (int p = 0; p < R; p += R / 2) {
+                    const float *d = gl.gds + (size_t)b * gl.ds_bstride + (size_t)(2 * i + p / (R / 2)) * (2 * w) + x0 / (R / 2);
+                    g[p].x += __ldcs(d);
+                    if (R == 4) g[p].z += __ldcs(d + 1);
+                }
+            }
+        }
 #pragma unroll
         for (int p = 0; p < R; ++p) {
             const float v = lpg_offset(p, R);
@@ -166,12 +194,13 @@ lpg_bwd_vec_kernel(const float *__restrict__ grad_depth, const float *__restrict
         }
     }
     if (valid && (R <= 4 || (threadIdx.x & (R / 4 - 1)) == 0)) {
+        const float sc = gl.div != 1.f ? __fdiv_rn(1.f, gl.div) : 1.f;
 #pragma unroll
         for (int n = 0; n < NPX; ++n) {
-            grad_plane_eq[base + n] = -n4[n] * acc[n].tu;
-            grad_plane_eq[base + hw + n] = -n4[n] * acc[n].tv;
-            grad_plane_eq[base + 2 * hw + n] = -n4[n] * acc[n].t;
-            grad_plane_eq[base + 3 * hw + n] = acc[n].s4;
+            grad_plane_eq[base + n] = -n4[n] * acc[n].tu * sc;
+            grad_plane_eq[base + hw + n] = -n4[n] * acc[n].tv * sc;
+            grad_plane_eq[base + 2 * hw + n] = -n4[n] * acc[n].t * sc;
+            grad_plane_eq[base + 3 * hw + n] = acc[n].s4 * sc;
         }
     }
 }
@@ -179,7 +208,7 @@ lpg_bwd_vec_kernel(const float *__restrict__ grad_depth, const float *__restrict
 // backward, scalar path: one thread per low-res pixel, any r / w.
 __global__ void __launch_bounds__(256)
 lpg_bwd_scalar_kernel(const float *__restrict__ grad_depth, const float *__restrict__ plane_eq,
-                      float *__restrict__ grad_plane_eq, int B, int h, int w, int r, float eps)
+                      float *__restrict__ grad_plane_eq, int B, int h, int w, int r, float eps, LpgGlue gl)
 {
     const size_t hw = (size_t)h * w;
     const long long total = (long long)B * hw;
@@ -192,19 +221,25 @@ lpg_bwd_scalar_kernel(const float *__restrict__ grad_depth, const float *__restr
     const float n1 = __ldg(plane_eq + base), n2 = __ldg(plane_eq + base + hw);
     const float n3 = __ldg(plane_eq + base + 2 * hw), n4 = __ldg(plane_eq + base + 3 * hw);
     const int Wd = w * r;
-    const float *gp = grad_depth + ((size_t)b * h * r + (size_t)i * r) * Wd + (size_t)j * r;
+    const size_t bstride = gl.bstride ? (size_t)gl.bstride : (size_t)h * r * Wd;
+    const float *gp = grad_depth + (size_t)b * bstride + (size_t)i * r * Wd + (size_t)j * r;
+    const bool ds = gl.gds != nullptr && (r & 1) == 0;
     LpgAcc a{0.f, 0.f, 0.f, 0.f};
     for (int p = 0; p < r; ++p) {
         const float v = lpg_offset(p, r);
         for (int q = 0; q < r; ++q) {
             const float u = lpg_offset(q, r);
-            lpg_bwd_accum(a, __ldg(gp + (size_t)p * Wd + q), __fmul_rn(n1, u), __fmul_rn(n2, v), n3, u, v, eps);
+            float g = __ldg(gp + (size_t)p * Wd + q);
+            if (ds && p % (r / 2) == 0 && q % (r / 2) == 0)
+                g += __ldg(gl.gds + (size_t)b * gl.ds_bstride + (size_t)(2 * i + p / (r / 2)) * (2 * w) + 2 * j + q / (r / 2));
+            lpg_bwd_accum(a, g, __fmul_rn(n1, u), __fmul_rn(n2, v), n3, u, v, eps);
         }
     }
-    grad_plane_eq[base] = -n4 * a.tu;
-    grad_plane_eq[base + hw] = -n4 * a.tv;
-    grad_plane_eq[base + 2 * hw] = -n4 * a.t;
-    grad_plane_eq[base + 3 * hw] = a.s4;
+    const float sc = gl.div != 1.f ? __fdiv_rn(1.f, gl.div) : 1.f;
+    grad_plane_eq[base] = -n4 * a.tu * sc;
+    grad_plane_eq[base + hw] = -n4 * a.tv * sc;
+    grad_plane_eq[base + 2 * hw] = -n4 * a.t * sc;
+    grad_plane_eq[base + 3 * hw] = a.s4 * sc;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -212,44 +247,61 @@ lpg_bwd_scalar_kernel(const float *__restrict__ grad_depth, const float *__restr
 // ------------------------------------------------------------------------------------------------
 static inline bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
+int launch_lpg_fwd_glue(const float *plane_eq, float *depth, float *abs_min, int B, int h, int w, int r,
+                        float eps, const LpgGlue &gl, cudaStream_t s);
+int launch_lpg_bwd_glue(const float *grad_depth, const float *plane_eq, float *grad_plane_eq, int B, int h,
+                        int w, int r, float eps, const LpgGlue &gl, cudaStream_t s);
+
 int launch_lpg_fwd(const float *plane_eq, float *depth, float *abs_min, int B, int h, int w, int r,
                    float eps, cudaStream_t s)
 {
-    const bool vec = ((w * r) % 4 == 0) && aligned16(depth) && (r == 1 || r == 2 || r == 4 || r == 8);
-    if (vec) {
-        const long long total = (long long)B * h * (w * r / 4);
-        const unsigned grid = (unsigned)((total + 255) / 256);
-        switch (r) {
-        case 8: lpg_fwd_vec_kernel<8><<<grid, 256, 0, s>>>(plane_eq, depth, abs_min, B, h, w, eps); break;
-        case 4: lpg_fwd_vec_kernel<4><<<grid, 256, 0, s>>>(plane_eq, depth, abs_min, B, h, w, eps); break;
-        case 2: lpg_fwd_vec_kernel<2><<<grid, 256, 0, s>>>(plane_eq, depth, abs_min, B, h, w, eps); break;
-        default: lpg_fwd_vec_kernel<1><<<grid, 256, 0, s>>>(plane_eq, depth, abs_min, B, h, w, eps); break;
-        }
-    } else {
-        const long long total = (long long)B * h * r * w * r;
-        const unsigned grid = (unsigned)((total + 255) / 256);
-        lpg_fwd_scalar_kernel<<<grid, 256, 0, s>>>(plane_eq, depth, abs_min, B, h, w, r, eps);
-    }
-    return check_launch("bts_lpg_fwd");
+    return launch_lpg_fwd_glue(plane_eq, depth, abs_min, B, h, w, r, eps, lpg_glue_none(), s);
 }
 
 int launch_lpg_bwd(const float *grad_depth, const float *plane_eq, float *grad_plane_eq, int B, int h,
                    int w, int r, float eps, cudaStream_t s)
 {
-    const bool vec = ((w * r) % 4 == 0) && aligned16(grad_depth) && (r == 1 || r == 2 || r == 4 || r == 8);
+    return launch_lpg_bwd_glue(grad_depth, plane_eq, grad_plane_eq, B, h, w, r, eps, lpg_glue_none(), s);
+}
+
+int launch_lpg_fwd_glue(const float *plane_eq, float *depth, float *abs_min, int B, int h, int w, int r,
+                        float eps, const LpgGlue &gl, cudaStream_t s)
+{
+    const bool vec = ((w * r) % 4 == 0) && aligned16(depth) && gl.bstride % 4 == 0 && (r == 1 || r == 2 || r == 4 || r == 8);
     if (vec) {
         const long long total = (long long)B * h * (w * r / 4);
         const unsigned grid = (unsigned)((total + 255) / 256);
         switch (r) {
-        case 8: lpg_bwd_vec_kernel<8><<<grid, 256, 0, s>>>(grad_depth, plane_eq, grad_plane_eq, B, h, w, eps); break;
-        case 4: lpg_bwd_vec_kernel<4><<<grid, 256, 0, s>>>(grad_depth, plane_eq, grad_plane_eq, B, h, w, eps); break;
-        case 2: lpg_bwd_vec_kernel<2><<<grid, 256, 0, s>>>(grad_depth, plane_eq, grad_plane_eq, B, h, w, eps); break;
-        default: lpg_bwd_vec_kernel<1><<<grid, 256, 0, s>>>(grad_depth, plane_eq, grad_plane_eq, B, h, w, eps); break;
+        case 8: lpg_fwd_vec_kernel<8><<<grid, 256, 0, s>>>(plane_eq, depth, abs_min, B, h, w, eps, gl); break;
+        case 4: lpg_fwd_vec_kernel<4><<<grid, 256, 0, s>>>(plane_eq, depth, abs_min, B, h, w, eps, gl); break;
+        case 2: lpg_fwd_vec_kernel<2><<<grid, 256, 0, s>>>(plane_eq, depth, abs_min, B, h, w, eps, gl); break;
+        default: lpg_fwd_vec_kernel<1><<<grid, 256, 0, s>>>(plane_eq, depth, abs_min, B, h, w, eps, gl); break;
+        }
+    } else {
+        const long long total = (long long)B * h * r * w * r;
+        const unsigned grid = (unsigned)((total + 255) / 256);
+        lpg_fwd_scalar_kernel<<<grid, 256, 0, s>>>(plane_eq, depth, abs_min, B, h, w, r, eps, gl);
+    }
+    return check_launch("bts_lpg_fwd");
+}
+
+int launch_lpg_bwd_glue(const float *grad_depth, const float *plane_eq, float *grad_plane_eq, int B, int h,
+                        int w, int r, float eps, const LpgGlue &gl, cudaStream_t s)
+{
+    const bool vec = ((w * r) % 4 == 0) && aligned16(grad_depth) && gl.bstride % 4 == 0 && (r == 1 || r == 2 || r == 4 || r == 8);
+    if (vec) {
+        const long long total = (long long)B * h * (w * r / 4);
+        const unsigned grid = (unsigned)((total + 255) / 256);
+        switch (r) {
+        case 8: lpg_bwd_vec_kernel<8><<<grid, 256, 0, s>>>(grad_depth, plane_eq, grad_plane_eq, B, h, w, eps, gl); break;
+        case 4: lpg_bwd_vec_kernel<4><<<grid, 256, 0, s>>>(grad_depth, plane_eq, grad_plane_eq, B, h, w, eps, gl); break;
+        case 2: lpg_bwd_vec_kernel<2><<<grid, 256, 0, s>>>(grad_depth, plane_eq, grad_plane_eq, B, h, w, eps, gl); break;
+        default: lpg_bwd_vec_kernel<1><<<grid, 256, 0, s>>>(grad_depth, plane_eq, grad_plane_eq, B, h, w, eps, gl); break;
         }
     } else {
         const long long total = (long long)B * h * w;
         const unsigned grid = (unsigned)((total + 255) / 256);
-        lpg_bwd_scalar_kernel<<<grid, 256, 0, s>>>(grad_depth, plane_eq, grad_plane_eq, B, h, w, r, eps);
+        lpg_bwd_scalar_kernel<<<grid, 256, 0, s>>>(grad_depth, plane_eq, grad_plane_eq, B, h, w, r, eps, gl);
     }
     return check_launch("bts_lpg_bwd");
 }

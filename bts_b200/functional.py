@@ -164,10 +164,11 @@ class _Reduc(torch.autograd.Function):
 
 
 class _ReducLPG(torch.autograd.Function):
-    """Fused decoder stage reducNxN -> normalise/cat -> lpgNxN (pytorch/bts.py:249-254)."""
+    """Fused decoder stage reducNxN -> normalise/cat -> lpgNxN (pytorch/bts.py:249-254), optionally with the
+    post-LPG glue `unsqueeze(1) / max_depth` and the nearest down-sampling by upratio/2 (bts.py:255-256, 269-270)."""
 
     @staticmethod
-    def forward(ctx, x, max_depth, upratio, want_plane_eq, *weights):
+    def forward(ctx, x, max_depth, upratio, want_plane_eq, scaled, downsample, *weights):
         x = _require_cuda_f32(x, "net")
         if x.dim() != 4:
             raise RuntimeError("net must be [B,C,h,w], got %s" % (tuple(x.shape),))
@@ -175,46 +176,60 @@ class _ReducLPG(torch.autograd.Function):
         dims = _dims(x, ws)
         B, _, h, w = x.shape
         r = int(upratio)
-        depth = torch.empty((B, h * r, w * r), dtype=torch.float32, device=x.device)
+        if downsample and (not scaled or r % 2):
+            raise RuntimeError("the down-sampled map is the scaled map's (bts.py:256) and needs an even upratio")
+        depth = torch.empty((B, 1, h * r, w * r) if scaled else (B, h * r, w * r), dtype=torch.float32, device=x.device)
+        ds = torch.empty((B, 1, 2 * h, 2 * w), dtype=torch.float32, device=x.device) if downsample else None
         abs_min = torch.full((), float("inf"), dtype=torch.float32, device=x.device)
         plane_eq = torch.empty((B, 4, h, w), dtype=torch.float32, device=x.device) if want_plane_eq else None
         wsb, wsp, wsn = _workspace(dims, B, h, w, r, x.device)
         st, stp, stn = _stash(dims, B, h, w, x.device, any(ctx.needs_input_grad))
         with torch.cuda.device(x.device):
-            _cabi.check(_cabi.lib().bts_reduc_lpg_fwd_stash(
+            _cabi.check(_cabi.lib().bts_reduc_lpg_fwd_glue(
                 x.data_ptr(), _cabi.ptr_array([t.data_ptr() for t in ws]), _cabi.int_array(dims), len(ws),
-                float(max_depth), B, h, w, r, EPS, plane_eq.data_ptr() if want_plane_eq else None,
-                depth.data_ptr(), abs_min.data_ptr(), wsp, wsn, stp, stn, _stream()), "bts_reduc_lpg_fwd")
+                float(max_depth), B, h, w, r, EPS, float(max_depth) if scaled else 1.0,
+                plane_eq.data_ptr() if want_plane_eq else None, depth.data_ptr(), 0,
+                ds.data_ptr() if downsample else None, 0, abs_min.data_ptr(), wsp, wsn, stp, stn, _stream()),
+                "bts_reduc_lpg_fwd")
         ctx.stash = st
         ctx.save_for_backward(x, *ws)
-        ctx.cfg = (float(max_depth), r, dims, [tuple(t.shape) for t in weights])
+        ctx.cfg = (float(max_depth), r, dims, [tuple(t.shape) for t in weights], bool(scaled), bool(downsample))
         ctx.mark_non_differentiable(abs_min)
+        outs = [depth, abs_min]
+        if downsample:
+            outs.append(ds)
         if want_plane_eq:
             ctx.mark_non_differentiable(plane_eq)
-            return depth, abs_min, plane_eq
-        return depth, abs_min
+            outs.append(plane_eq)
+        return tuple(outs)
 
     @staticmethod
-    def backward(ctx, grad_depth, *_ignored):
+    def backward(ctx, grad_depth, _g_abs_min, *rest):
         x, *ws = ctx.saved_tensors
-        max_depth, r, dims, shapes = ctx.cfg
-        grad_depth = _require_cuda_f32(grad_depth, "grad_depth")
+        max_depth, r, dims, shapes, scaled, downsample = ctx.cfg
         B, _, h, w = x.shape
+        if grad_depth is None:                                     # only the down-sampled map was used downstream
+            grad_depth = torch.zeros((B, h * r, w * r), dtype=torch.float32, device=x.device)
+        grad_depth = _require_cuda_f32(grad_depth, "grad_depth")
+        grad_ds = rest[0] if downsample and rest and rest[0] is not None else None
+        if grad_ds is not None:
+            grad_ds = _require_cuda_f32(grad_ds, "grad_depth_ds")
         need_x = ctx.needs_input_grad[0]
-        need_w = any(ctx.needs_input_grad[4:])
+        need_w = any(ctx.needs_input_grad[6:])
         gx = torch.empty_like(x) if need_x else None
         gws = _zero_grads(ws) if need_w else None
         wsb, wsp, wsn = _workspace(dims, B, h, w, r, x.device)
         st = ctx.stash
         with torch.cuda.device(x.device):
-            _cabi.check(_cabi.lib().bts_reduc_lpg_bwd_stash(
-                grad_depth.data_ptr(), x.data_ptr(), _cabi.ptr_array([t.data_ptr() for t in ws]),
+            _cabi.check(_cabi.lib().bts_reduc_lpg_bwd_glue(
+                grad_depth.data_ptr(), 0, grad_ds.data_ptr() if grad_ds is not None else None, 0,
+                max_depth if scaled else 1.0, x.data_ptr(), _cabi.ptr_array([t.data_ptr() for t in ws]),
                 _cabi.int_array(dims), len(ws), max_depth, B, h, w, r, EPS, gx.data_ptr() if need_x else None,
                 _cabi.ptr_array([t.data_ptr() for t in gws]) if need_w else None, wsp, wsn,
                 st.data_ptr() if st is not None else None, st.numel() * 4 if st is not None else 0, _stream()),
                 "bts_reduc_lpg_bwd")
         gw_out = [g.view(s) for g, s in zip(gws, shapes)] if need_w else [None] * len(ws)
-        return (gx, None, None, None, *gw_out)
+        return (gx, None, None, None, None, None, *gw_out)
 
 
 def lpg(plane_eq, upratio):
@@ -227,9 +242,10 @@ def reduc(x, weights, max_depth, is_final=False):
     return _Reduc.apply(x, max_depth, is_final, *weights)
 
 
-def reduc_lpg(x, weights, max_depth, upratio, return_plane_eq=False):
-    """Fused stage -> (depth, abs_min[, plane_eq])."""
-    return _ReducLPG.apply(x, max_depth, upratio, return_plane_eq, *weights)
+def reduc_lpg(x, weights, max_depth, upratio, return_plane_eq=False, scaled=False, downsample=False):
+    """Fused stage -> (depth, abs_min[, depth_ds][, plane_eq]). scaled: depth is [B,1,H,W] / max_depth
+    (bts.py:255); downsample: also its nearest down-sampling by upratio/2, [B,1,2h,2w] (bts.py:256)."""
+    return _ReducLPG.apply(x, max_depth, upratio, return_plane_eq, scaled, downsample, *weights)
 
 
 PATH_AUTO, PATH_GENERIC, PATH_TCGEN05 = -1, 0, 2

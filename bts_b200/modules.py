@@ -82,15 +82,19 @@ class local_planar_guidance(nn.Module):
         return depth
 
 
-def fused_stage(reduc, lpg, net, return_plane_eq=False):
+def fused_stage(reduc, lpg, net, return_plane_eq=False, scaled=False, downsample=False):
     """reducNxN -> normalise/cat -> lpgNxN (pytorch/bts.py:249-254) as ONE fused call.
 
-    Returns depth [B,H,W] (and plane_eq [B,4,h,w] when asked); sets lpg.abs_min like the module would."""
+    Returns depth [B,H,W] (and plane_eq [B,4,h,w] when asked); sets lpg.abs_min like the module would.
+    scaled=True folds `depth.unsqueeze(1) / max_depth` (bts.py:255, 269, 283) in and returns [B,1,H,W];
+    downsample=True (upratio 8 / 4) also returns `F.interpolate(depth_scaled, scale_factor=2/upratio,
+    mode='nearest')` (bts.py:256, 270), [B,1,2h,2w], right after the depth map."""
     if reduc.is_final:
         raise ValueError("fused_stage needs a plane-parameter reduction (is_final=False)")
-    res = Fn.reduc_lpg(net, reduc.chain_weights(), reduc.max_depth, int(lpg.upratio), return_plane_eq)
+    res = Fn.reduc_lpg(net, reduc.chain_weights(), reduc.max_depth, int(lpg.upratio), return_plane_eq, scaled, downsample)
     lpg.abs_min = res[1]
-    return (res[0], res[2]) if return_plane_eq else res[0]
+    out = [res[0]] + list(res[2:])
+    return out[0] if len(out) == 1 else tuple(out)
 
 
 _STAGES = (("reduc8x8", "lpg8x8"), ("reduc4x4", "lpg4x4"), ("reduc2x2", "lpg2x2"))

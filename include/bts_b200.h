@@ -38,7 +38,7 @@ extern "C" {
 #define BTS_API
 #endif
 
-#define BTS_ABI_VERSION 2
+#define BTS_ABI_VERSION 3
 #define BTS_MAX_LAYERS 8      /* reduction_1x1 builds at most log2(num_out) layers */
 #define BTS_MAX_CHANNELS 512  /* per layer */
 
@@ -153,6 +153,29 @@ BTS_API int bts_reduc_lpg_fwd_stash(const float *x, const float *const *W, const
                         void *ws, size_t ws_bytes, void *stash, size_t stash_bytes, void *stream);
 BTS_API int bts_reduc_lpg_bwd_stash(const float *grad_depth, const float *x, const float *const *W, const int *dims,
                         int n_layers, float max_depth, int B, int h, int w, int r, float eps,
+                        float *grad_x, float *const *grad_W,
+                        void *ws, size_t ws_bytes, const void *stash, size_t stash_bytes, void *stream);
+
+/*
+ * Post-LPG glue folded into the fused stage (ABI 3)            pytorch/bts.py:255-256, 269-270, 283
+ *   depth_NxN_scaled    = depth_NxN.unsqueeze(1) / max_depth
+ *   depth_NxN_scaled_ds = F.interpolate(depth_NxN_scaled, scale_factor=2/N, mode='nearest')   (N = 8, 4)
+ * The forward writes depth / depth_div (pass max_depth; 1 = plain depth) with `depth_bstride` elements between
+ * images -- 0 = dense h*r*w*r, anything larger lets the map land in a channel slice of a concat buffer
+ * (bts.py:260, 274, 287) -- and, when ds_out != NULL (even r), the nearest-neighbour down-sampling by r/2
+ * (= rows / columns 0 and r/2 of every r x r block) as [B][2h][2w] with batch stride ds_bstride (0 = dense).
+ * The backward takes the gradient of the scaled map (same stride convention) and, optionally, the gradient of
+ * the down-sampled map; everything else as the *_stash entry points.
+ */
+BTS_API int bts_reduc_lpg_fwd_glue(const float *x, const float *const *W, const int *dims, int n_layers,
+                        float max_depth, int B, int h, int w, int r, float eps, float depth_div,
+                        float *plane_eq_out, float *depth, long long depth_bstride,
+                        float *ds_out, long long ds_bstride, float *abs_min,
+                        void *ws, size_t ws_bytes, void *stash, size_t stash_bytes, void *stream);
+BTS_API int bts_reduc_lpg_bwd_glue(const float *grad_depth, long long grad_bstride,
+                        const float *grad_ds, long long grad_ds_bstride, float depth_div,
+                        const float *x, const float *const *W, const int *dims, int n_layers,
+                        float max_depth, int B, int h, int w, int r, float eps,
                         float *grad_x, float *const *grad_W,
                         void *ws, size_t ws_bytes, const void *stash, size_t stash_bytes, void *stream);
 

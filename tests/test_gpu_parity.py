@@ -381,3 +381,117 @@ def test_stash_backward_vs_recompute_backward(cfg):
     close_peak(got[1], ref[1].cpu().numpy())
     for a, b in zip(got[2], ref[2]):
         close_peak(a, b.cpu().numpy())
+
+
+def _glue_reference(x, ws, md, r, g_full, g_ds):
+    """The reference's own operator sequence (oracle/torch_port.py restates pytorch/bts.py:124-173, 250-254) followed
+    by the post-LPG glue lines bts.py:255-256 / 269-270, in fp64 on the CPU, with autograd for the gradients."""
+    from oracle import torch_port as tp
+    xt = torch.from_numpy(x).double().requires_grad_(True)
+    wt = [torch.from_numpy(w).double().reshape(w.shape[0], w.shape[1], 1, 1).requires_grad_(True) for w in ws]
+    depth, _ = tp.stage_forward(xt, wt, md, r)
+    scaled = depth.unsqueeze(1) / md
+    loss = (scaled * torch.from_numpy(g_full).double()).sum()
+    ds = None
+    if g_ds is not None:
+        ds = torch.nn.functional.interpolate(scaled, scale_factor=2.0 / r, mode="nearest")
+        loss = loss + (ds * torch.from_numpy(g_ds).double()).sum()
+    loss.backward()
+    return (scaled.detach().numpy(), None if ds is None else ds.detach().numpy(), xt.grad.numpy(),
+            [w.grad[:, :, 0, 0].numpy() for w in wt])
+
+
+@pytest.mark.parametrize("cfg", [(128, 128, 8, 2, 20, 28, True, None), (128, 128, 8, 2, 19, 23, True, None),
+                                 (128, 64, 4, 2, 36, 44, True, None), (64, 32, 2, 2, 40, 56, False, None),
+                                 (32, 16, 4, 1, 24, 40, True, None), (128, 128, 8, 1, 16, 24, True, "generic"),
+                                 (64, 32, 4, 2, 17, 21, True, "generic"), (128, 64, 4, 2, 36, 44, True, "nostash")],
+                         ids=lambda c: "x".join(map(str, c)))
+def test_fused_stage_with_post_lpg_glue(cfg):
+    """`depth.unsqueeze(1) / max_depth` and the nearest down-sampling folded into the
+    fused stage, forward and backward, on every route (stash, recompute, one-pass, generic)."""
+    import bts_b200
+    from bts_b200 import functional as Fn
+    from oracle import torch_port as tp
+    num_in, num_out, r, B, h, w, with_ds, route = cfg
+    md = 10.0
+    gen = torch.Generator().manual_seed(77 + num_in + r)
+    dims = tp.chain_dims(num_in, num_out, False)
+    ws = [t[:, :, 0, 0].numpy() for t in tp.xavier_weights(dims, False, gen)]
+    x = torch.randn(B, num_in, h, w, generator=gen).numpy()
+    g_full = torch.randn(B, 1, h * r, w * r, generator=gen).numpy()
+    g_ds = torch.randn(B, 1, 2 * h, 2 * w, generator=gen).numpy() if with_ds else None
+    ref_scaled, ref_ds, ref_gx, ref_gw = _glue_reference(x, ws, md, r, g_full, g_ds)
+
+    red = bts_b200.reduction_1x1(num_in, num_out, md, False).cuda()
+    with torch.no_grad():
+        for p, wt in zip(red.chain_weights(), ws):
+            p.copy_(dev(wt).view_as(p))
+    xd = dev(x, True)
+    lpg = bts_b200.local_planar_guidance(r)
+    prev = Fn.set_stash(route != "nostash")
+    try:
+        if route == "generic":
+            Fn.force_path(Fn.PATH_GENERIC)
+        out = bts_b200.fused_stage(red, lpg, xd, scaled=True, downsample=with_ds)
+        scaled, ds = (out if with_ds else (out, None))
+        assert scaled.shape == (B, 1, h * r, w * r)
+        loss = (scaled * dev(g_full)).sum()
+        if with_ds:
+            assert ds.shape == (B, 1, 2 * h, 2 * w)
+            loss = loss + (ds * dev(g_ds)).sum()
+        loss.backward()
+    finally:
+        Fn.force_path(Fn.PATH_AUTO)
+        Fn.set_stash(prev)
+    close_depth(scaled, ref_scaled, 1.0)
+    if with_ds:
+        close_depth(ds, ref_ds, 1.0)
+        # the down-sampled map is exactly rows / columns 0 and r/2 of every block of the full map
+        assert torch.equal(ds, scaled[:, :, ::r // 2, ::r // 2])
+    close_peak(xd.grad, ref_gx)
+    for p, gr in zip(red.chain_weights(), ref_gw):
+        close_peak(p.grad.view(p.shape[0], p.shape[1]), gr)
+
+
+def test_glue_writes_into_a_channel_slice():
+    """C ABI, batch strides: the scaled depth lands in channel 1 of a [B,3,H,W] buffer (as concat1 of bts.py:287
+    would hold it) and the backward reads its gradient from the same slice; neighbours stay untouched."""
+    import bts_b200
+    from bts_b200 import _cabi, functional as Fn
+    torch.manual_seed(9)
+    B, h, w, r, md = 2, 24, 32, 4, 10.0
+    red = bts_b200.reduction_1x1(128, 64, md, False).cuda()
+    for p in red.parameters():
+        torch.nn.init.xavier_uniform_(p)
+    x = torch.randn(B, 128, h, w, device="cuda")
+    H, W = h * r, w * r
+    buf = torch.full((B, 3, H, W), 7.0, device="cuda")
+    gbuf = torch.randn(B, 3, H, W, device="cuda")
+    # dense route through the module API
+    xd = x.clone().requires_grad_(True)
+    dense = bts_b200.fused_stage(red, bts_b200.local_planar_guidance(r), xd, scaled=True)
+    dense.backward(gbuf[:, 1:2].contiguous())
+    ref_gw = [p.grad.clone() for p in red.parameters()]
+    # strided route through the C ABI
+    lib = _cabi.lib()
+    wts = [t.detach() for t in red.chain_weights()]
+    dims = [128] + [t.shape[0] for t in wts]
+    Wp, D = _cabi.ptr_array([t.data_ptr() for t in wts]), _cabi.int_array(dims)
+    nws = lib.bts_workspace_bytes(D, len(wts), B, h, w, r)
+    wsb = torch.empty((nws + 3) // 4, device="cuda")
+    amin = torch.full((), float("inf"), device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    _cabi.check(lib.bts_reduc_lpg_fwd_glue(x.data_ptr(), Wp, D, len(wts), md, B, h, w, r, Fn.EPS, md, None,
+                                           buf[:, 1].data_ptr(), 3 * H * W, None, 0, amin.data_ptr(),
+                                           wsb.data_ptr(), nws, None, 0, st), "fwd")
+    assert torch.equal(buf[:, 1:2], dense.detach())
+    assert bool((buf[:, 0] == 7.0).all()) and bool((buf[:, 2] == 7.0).all())
+    gx = torch.empty_like(x)
+    gws = [torch.zeros_like(t) for t in wts]
+    _cabi.check(lib.bts_reduc_lpg_bwd_glue(gbuf[:, 1].data_ptr(), 3 * H * W, None, 0, md, x.data_ptr(), Wp, D, len(wts),
+                                           md, B, h, w, r, Fn.EPS, gx.data_ptr(),
+                                           _cabi.ptr_array([t.data_ptr() for t in gws]), wsb.data_ptr(), nws, None, 0, st),
+                "bwd")
+    close_peak(gx, xd.grad.cpu().numpy())
+    for a, b in zip(gws, ref_gw):
+        close_peak(a, b.cpu().numpy())

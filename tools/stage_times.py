@@ -30,6 +30,10 @@ def main():
         tot += tf + tb
         print("%-18s fwd %7.1f us (%5.1f%% of HBM peak)   bwd %7.1f us (%5.1f%%)" % (
             st["name"], tf * 1e3, 100 * fb * px / tf / 1e6 / peak, tb * 1e3, 100 * bb * px / tb / 1e6 / peak))
+    if not only or "lpg" in only:
+        for name, d in bench.time_standalone_lpg(wl, dev, iters).items():
+            print("%-18s fwd %7.1f us (%5.1f%% of HBM peak)   bwd %7.1f us (%5.1f%%)" % (
+                name, d["fwd_ms"] * 1e3, 100 * d["fwd_gbs"] / peak, d["bwd_ms"] * 1e3, 100 * d["bwd_gbs"] / peak))
     allb = sum(sum(v) for v in bench.ALGO_BYTES.values()) * px
     print("sum %.1f us -> %.1f Mpix/s, %.1f%% of HBM peak" % (tot * 1e3, px / tot / 1e3, 100 * allb / tot / 1e6 / peak))
 
