@@ -53,6 +53,9 @@ _SIGNATURES["bts_reduc_lpg_bwd_glue"] = (ctypes.c_int, [
     _P, _LL, _P, _LL, _F,                                        # grad_depth, grad_bstride, grad_ds, grad_ds_bstride, depth_div
     _P, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_int), _I, _F, _I, _I, _I, _I, _F,       # x .. eps
     _P, ctypes.POINTER(ctypes.c_void_p), _P, _SZ, _P, _SZ, _P])  # grad_x, grad_W, ws, ws_bytes, stash, stash_bytes, stream
+_SIGNATURES["bts_silog_workspace_bytes"] = (ctypes.c_size_t, [])
+_SIGNATURES["bts_silog_fwd"] = (ctypes.c_int, [_P, _P, _P, _LL, _F, _P, _P, _SZ, _P])
+_SIGNATURES["bts_silog_bwd"] = (ctypes.c_int, [_P, _P, _P, _LL, _F, _P, _P, _P, _P])
 ABI_VERSION = 3
 
 _lib = None

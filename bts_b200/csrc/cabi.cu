@@ -49,6 +49,12 @@ bool tc_stash_supported(const ChainParams &, int hw, const void *x);
 size_t tc_stash_bytes(const ChainParams &, int B, int hw);
 int tc_stash_bind(const ChainParams &, TcArgs &, void *stash, bool clear, cudaStream_t);
 
+size_t silog_workspace_bytes(int sms);
+int launch_silog_fwd(const float *, const float *, const unsigned char *, long long, float, float *, void *, void *, int,
+                     cudaStream_t);
+int launch_silog_bwd(const float *, const float *, const unsigned char *, long long, float, const float *, const void *,
+                     float *, int, cudaStream_t);
+
 static int sm_count()
 {
     int dev = 0, n = 148;
@@ -379,6 +385,31 @@ int bts_reduc_lpg_bwd_glue(const float *grad_depth, long long grad_bstride, cons
     const LpgGlue gl{depth_div, gbs, nullptr, grad_ds, sbs};
     if (int e = launch_lpg_bwd_glue(grad_depth, pe, gpe, B, h, w, r, eps, gl, s)) return e;
     return launch_chain_generic_bwd(cp, x, gpe, grad_x, B, h * w, s);
+}
+
+size_t bts_silog_workspace_bytes(void) { return BTS_SILOG_STATE_BYTES + silog_workspace_bytes(sm_count()); }
+
+int bts_silog_fwd(const float *depth_est, const float *depth_gt, const unsigned char *mask, long long n,
+                  float variance_focus, float *loss, void *ws, size_t ws_bytes, void *stream)
+{
+    if (n < 0) return set_error(BTS_ERR_BAD_ARG, "negative element count");
+    if (!depth_est || !depth_gt || !mask || !loss) return set_error(BTS_ERR_BAD_ARG, "depth_est / depth_gt / mask / loss is NULL");
+    if (ws == nullptr || ws_bytes < bts_silog_workspace_bytes() || (reinterpret_cast<uintptr_t>(ws) & 15u))
+        return set_error(BTS_ERR_WORKSPACE, "workspace %zu B < %zu B (or not 16-byte aligned)", ws_bytes, bts_silog_workspace_bytes());
+    char *w = static_cast<char *>(ws);
+    return launch_silog_fwd(depth_est, depth_gt, mask, n, variance_focus, loss, w, w + BTS_SILOG_STATE_BYTES, sm_count(),
+                            (cudaStream_t)stream);
+}
+
+int bts_silog_bwd(const float *depth_est, const float *depth_gt, const unsigned char *mask, long long n,
+                  float variance_focus, const float *grad_loss, const void *ws, float *grad_est, void *stream)
+{
+    if (n < 0) return set_error(BTS_ERR_BAD_ARG, "negative element count");
+    if (!depth_est || !depth_gt || !mask || !grad_loss || !ws || !grad_est)
+        return set_error(BTS_ERR_BAD_ARG, "NULL argument");
+    if (n == 0) return BTS_OK;
+    return launch_silog_bwd(depth_est, depth_gt, mask, n, variance_focus, grad_loss, ws, grad_est, sm_count(),
+                            (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -232,6 +232,46 @@ class _ReducLPG(torch.autograd.Function):
         return (gx, None, None, None, None, None, *gw_out)
 
 
+class _Silog(torch.autograd.Function):
+    """silog_loss.forward (pytorch/bts.py:46-48) and its autograd backward, without the mask gather."""
+
+    @staticmethod
+    def forward(ctx, depth_est, depth_gt, mask, variance_focus):
+        est = _require_cuda_f32(depth_est, "depth_est")
+        gt = _require_cuda_f32(depth_gt, "depth_gt")
+        if mask.dtype != torch.bool or not mask.is_cuda:
+            raise RuntimeError("mask must be a CUDA torch.bool tensor")
+        if est.shape != gt.shape or est.shape != mask.shape:
+            raise RuntimeError("depth_est, depth_gt and mask must have the same shape")
+        mask = mask.contiguous()
+        loss = torch.empty((), dtype=torch.float32, device=est.device)
+        nws = _cabi.lib().bts_silog_workspace_bytes()
+        ws = torch.empty((nws + 7) // 8, dtype=torch.float64, device=est.device)
+        with torch.cuda.device(est.device):
+            _cabi.check(_cabi.lib().bts_silog_fwd(est.data_ptr(), gt.data_ptr(), mask.data_ptr(), est.numel(),
+                                                  float(variance_focus), loss.data_ptr(), ws.data_ptr(), nws, _stream()),
+                        "bts_silog_fwd")
+        ctx.save_for_backward(est, gt, mask, ws)
+        ctx.vf = float(variance_focus)
+        return loss
+
+    @staticmethod
+    def backward(ctx, grad_loss):
+        est, gt, mask, ws = ctx.saved_tensors
+        grad_loss = _require_cuda_f32(grad_loss, "grad_loss")
+        g = torch.empty_like(est)
+        with torch.cuda.device(est.device):
+            _cabi.check(_cabi.lib().bts_silog_bwd(est.data_ptr(), gt.data_ptr(), mask.data_ptr(), est.numel(), ctx.vf,
+                                                  grad_loss.data_ptr(), ws.data_ptr(), g.data_ptr(), _stream()),
+                        "bts_silog_bwd")
+        return g, None, None, None
+
+
+def silog(depth_est, depth_gt, mask, variance_focus):
+    """-> 0-dim loss. Drop-in math of silog_loss.forward (gradient flows to depth_est only, as in training)."""
+    return _Silog.apply(depth_est, depth_gt, mask, variance_focus)
+
+
 def lpg(plane_eq, upratio):
     """-> (depth [B,h*r,w*r], abs_min 0-dim). Drop-in math of local_planar_guidance.forward."""
     return _LPG.apply(plane_eq, upratio)

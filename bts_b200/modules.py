@@ -82,6 +82,17 @@ class local_planar_guidance(nn.Module):
         return depth
 
 
+class silog_loss(nn.Module):
+    """Same constructor / forward as the reference silog_loss (pytorch/bts.py:41-48)."""
+
+    def __init__(self, variance_focus):
+        super(silog_loss, self).__init__()
+        self.variance_focus = variance_focus
+
+    def forward(self, depth_est, depth_gt, mask):
+        return Fn.silog(depth_est, depth_gt, mask, self.variance_focus)
+
+
 def fused_stage(reduc, lpg, net, return_plane_eq=False, scaled=False, downsample=False):
     """reducNxN -> normalise/cat -> lpgNxN (pytorch/bts.py:249-254) as ONE fused call.
 

@@ -179,6 +179,22 @@ BTS_API int bts_reduc_lpg_bwd_glue(const float *grad_depth, long long grad_bstri
                         float *grad_x, float *const *grad_W,
                         void *ws, size_t ws_bytes, const void *stash, size_t stash_bytes, void *stream);
 
+/*
+ * silog_loss.forward(depth_est, depth_gt, mask)                 pytorch/bts.py:41-48
+ *   d = log(depth_est[mask]) - log(depth_gt[mask]);  loss = sqrt(mean(d^2) - variance_focus * mean(d)^2) * 10
+ * as one streaming reduction (no boolean-mask gather, no host synchronisation). `mask` is one byte per element
+ * (torch.bool), `n` the element count of the three equally shaped tensors, `loss` ONE device float.
+ * `ws` (bts_silog_workspace_bytes(), 16-byte aligned) keeps the sums the backward needs: hand the same buffer to
+ * bts_silog_bwd, which writes grad_est (zeros outside the mask) for the upstream gradient `grad_loss` (one float).
+ * An empty mask yields NaN, as the reference's mean of an empty tensor does.
+ */
+#define BTS_SILOG_STATE_BYTES 64
+BTS_API size_t bts_silog_workspace_bytes(void);
+BTS_API int bts_silog_fwd(const float *depth_est, const float *depth_gt, const unsigned char *mask, long long n,
+                  float variance_focus, float *loss, void *ws, size_t ws_bytes, void *stream);
+BTS_API int bts_silog_bwd(const float *depth_est, const float *depth_gt, const unsigned char *mask, long long n,
+                  float variance_focus, const float *grad_loss, const void *ws, float *grad_est, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

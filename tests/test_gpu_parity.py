@@ -495,3 +495,43 @@ def test_glue_writes_into_a_channel_slice():
     close_peak(gx, xd.grad.cpu().numpy())
     for a, b in zip(gws, ref_gw):
         close_peak(a, b.cpu().numpy())
+
+
+@pytest.mark.parametrize("shape,frac", [((4, 1, 52, 68), 0.6), ((8, 1, 480, 640), 0.35), ((3, 1, 37, 41), 0.9),
+                                        ((2, 1, 16, 16), 1.0)], ids=str)
+def test_silog_loss_vs_reference_ops(shape, frac):
+    """silog_loss (pytorch/bts.py:41-48) as one masked reduction; the reference's own operator
+    sequence (gather by boolean mask, log, mean, sqrt) in fp64 on the CPU is the oracle, autograd its backward."""
+    import bts_b200
+    gen = torch.Generator().manual_seed(5)
+    est = (torch.rand(shape, generator=gen) * 9.5 + 0.5)
+    gt = (torch.rand(shape, generator=gen) * 9.5 + 0.5)
+    mask = torch.rand(shape, generator=gen) < frac
+    e64 = est.double().requires_grad_(True)
+    d = torch.log(e64[mask]) - torch.log(gt.double()[mask])
+    ref = torch.sqrt((d ** 2).mean() - 0.85 * (d.mean() ** 2)) * 10.0
+    ref.backward()
+    crit = bts_b200.silog_loss(variance_focus=0.85)
+    ed = est.cuda().requires_grad_(True)
+    loss = crit(ed, gt.cuda(), mask.cuda())
+    assert loss.dim() == 0
+    (loss * 1.7).backward()
+    assert abs(float(loss) - float(ref)) <= 1e-5 * abs(float(ref))
+    close_peak(ed.grad, 1.7 * e64.grad.numpy())
+    assert bool((ed.grad[~mask.cuda()] == 0).all())
+
+
+def test_silog_loss_edge_cases():
+    import bts_b200
+    crit = bts_b200.silog_loss(0.85)
+    est = torch.rand(2, 1, 9, 7, device="cuda") + 0.5            # odd size: scalar tail, unaligned row ends
+    gt = torch.rand(2, 1, 9, 7, device="cuda") + 0.5
+    none = torch.zeros(2, 1, 9, 7, dtype=torch.bool, device="cuda")
+    assert torch.isnan(crit(est, gt, none))                        # mean of an empty selection, as the reference
+    one = none.clone()
+    one[1, 0, 3, 4] = True
+    # a single pixel: mean(d^2) - vf * mean(d)^2 = (1 - vf) d^2
+    d = float(torch.log(est[1, 0, 3, 4]) - torch.log(gt[1, 0, 3, 4]))
+    assert abs(float(crit(est, gt, one)) - 10.0 * (0.15 * d * d) ** 0.5) <= 1e-5 * (10.0 * (0.15 * d * d) ** 0.5) + 1e-7
+    with pytest.raises(RuntimeError):
+        crit(est, gt, one.float())
