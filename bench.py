@@ -538,6 +538,11 @@ def main():
                 "whole_step": {"algorithmic_bytes": step_bytes, "achieved": step_bytes / (ms_step * 1e-3) / 1e9,
                                "frac": step_bytes / (ms_step * 1e-3) / 1e9 / peak},
                 "per_call": calls, "standalone_lpg": time_standalone_lpg(wl, device)}
+    # SURVEY.md 8(d) reports 2 and 3 from the per-call device times: the three LPG stages, and all four
+    for key, names in (("lpg3", [n for n in calls if "lpg" in n]), ("lpg3_head", list(calls))):
+        ms = sum(calls[n]["fwd_ms"] + calls[n]["bwd_ms"] for n in names)
+        by = sum(sum(ALGO_BYTES[n]) for n in names) * px_per_rank
+        roofline[key] = {"ms": ms, "mpixels_per_s": px_per_rank / ms / 1e3, "achieved": by / ms / 1e6, "frac": by / ms / 1e6 / peak}
 
     e2e = None
     if not args.no_e2e:
