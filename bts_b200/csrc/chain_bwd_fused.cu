@@ -176,6 +176,31 @@ struct StageCtx {
     unsigned char *sub;     // this warp's sub-buffer
     uint32_t coff[8];
 };
+// two consecutive rows at once (packed remainder)
+template <int kALo>
+__device__ __forceinline__ void stage_a2(const StageCtx &s, int row, float v0, float v1)
+{
+    unsigned char *p0 = s.sub + row * 128 + s.coff[row & 7];
+    unsigned char *p1 = s.sub + (row + 1) * 128 + s.coff[(row + 1) & 7];
+    float l0, l1;
+    tf32_lo2(v0, v1, l0, l1);
+    *reinterpret_cast<float *>(p0) = v0;
+    *reinterpret_cast<float *>(p1) = v1;
+    *reinterpret_cast<float *>(p0 + kALo) = l0;
+    *reinterpret_cast<float *>(p1 + kALo) = l1;
+}
+template <int kSubB>
+__device__ __forceinline__ void stage_b2(const StageCtx &s, int row, float v0, float v1)
+{
+    unsigned char *p0 = s.sub + kSubB + row * 128 + s.coff[row & 7];
+    unsigned char *p1 = s.sub + kSubB + (row + 1) * 128 + s.coff[(row + 1) & 7];
+    float l0, l1;
+    tf32_lo2(v0, v1, l0, l1);
+    *reinterpret_cast<float *>(p0) = v0;
+    *reinterpret_cast<float *>(p1) = v1;
+    *reinterpret_cast<float *>(p0 + kBLo) = l0;
+    *reinterpret_cast<float *>(p1 + kBLo) = l1;
+}
 template <int kALo>
 __device__ __forceinline__ void stage_a(const StageCtx &s, int row, float v)
 {
@@ -200,7 +225,7 @@ __device__ __forceinline__ void stage_a_from_tmem32(const StageCtx &s, int row0,
         tmem_ld<16>(taddr + c0, r);
         wait_ld();
 #pragma unroll
-        for (int j = 0; j < 16; ++j) stage_a<kALo>(s, row0 + c0 + j, __uint_as_float(r[j]));
+        for (int j = 0; j < 16; j += 2) stage_a2<kALo>(s, row0 + c0 + j, __uint_as_float(r[j]), __uint_as_float(r[j + 1]));
     }
 }
 
@@ -352,10 +377,11 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
             for (int c0 = 0; c0 < K0; c0 += 16) {
                 uint32_t hi[16], lo[16];
 #pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    const float v = xs[(c0 + j) * kTile];
-                    hi[j] = __float_as_uint(v);
-                    lo[j] = __float_as_uint(tf32_lo(v));
+                for (int j = 0; j < 16; j += 2) {
+                    const float v0 = xs[(c0 + j) * kTile], v1 = xs[(c0 + j + 1) * kTile];
+                    hi[j] = __float_as_uint(v0);
+                    hi[j + 1] = __float_as_uint(v1);
+                    tf32_lo2(v0, v1, lo[j], lo[j + 1]);
                 }
                 tmem_st<16>(xh + c0, hi);
                 tmem_st<16>(xl + c0, lo);
@@ -400,7 +426,7 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
 #pragma unroll
                 for (int j = 0; j < 16; ++j) a16[j] = elu_fast(__uint_as_float(r[j]));
             }
-            tail_forward<LAST>(tw, a16, a8, z);
+            tail_forward<LAST, NW == 1>(tw, a16, a8, z);
             // ---- upstream gradient -> dz
             float dz[3] = {0.f, 0.f, 0.f};
             if constexpr (MODE == 0) {
@@ -442,25 +468,16 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
                 for (int j = 0; j < LAST; ++j) s = fmaf(w5[j * kTailMid + o], dz[j], s);
                 d8[o] = s * elu_grad_from_out(a8[o]);
             }
-#pragma unroll
-            for (int c = 0; c < kTailIn; ++c) dl16[c] = 0.f;
-#pragma unroll
-            for (int o = 0; o < kTailMid; ++o) {
-#pragma unroll
-                for (int c = 0; c < kTailIn; c += 4) {
-                    const float4 w4 = *reinterpret_cast<const float4 *>(tw + o * kTailIn + c);
-                    dl16[c] = fmaf(w4.x, d8[o], dl16[c]); dl16[c + 1] = fmaf(w4.y, d8[o], dl16[c + 1]);
-                    dl16[c + 2] = fmaf(w4.z, d8[o], dl16[c + 2]); dl16[c + 3] = fmaf(w4.w, d8[o], dl16[c + 3]);
-                }
-                asm volatile("" ::: "memory");                    // bound the hoisting of weight loads
-            }
+            tail_dgrad16<NW == 1>(tw, d8, dl16);
             {
                 uint32_t hi[16], lo[16];
 #pragma unroll
-                for (int j = 0; j < 16; ++j) {
+                for (int j = 0; j < 16; j += 2) {
                     dl16[j] *= elu_grad_from_out(a16[j]);
+                    dl16[j + 1] *= elu_grad_from_out(a16[j + 1]);
                     hi[j] = __float_as_uint(dl16[j]);
-                    lo[j] = __float_as_uint(tf32_lo(dl16[j]));
+                    hi[j + 1] = __float_as_uint(dl16[j + 1]);
+                    tf32_lo2(dl16[j], dl16[j + 1], lo[j], lo[j + 1]);
                 }
                 constexpr int OFF = NW == 1 ? 0 : 32;
                 tmem_st<16>(xl + OFF, hi);
@@ -475,16 +492,16 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
                 ++nstage;
                 if constexpr (NW == 2) {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) stage_a<L::ALO>(sc, j, a1[j]);
+                    for (int j = 0; j < 32; j += 2) stage_a2<L::ALO>(sc, j, a1[j], a1[j + 1]);
                 }
 #pragma unroll
-                for (int j = 0; j < kTailIn; ++j) stage_a<L::ALO>(sc, 32 + j, a16[j]);
+                for (int j = 0; j < kTailIn; j += 2) stage_a2<L::ALO>(sc, 32 + j, a16[j], a16[j + 1]);
 #pragma unroll
-                for (int j = 0; j < kTailMid; ++j) stage_a<L::ALO>(sc, 48 + j, a8[j]);
+                for (int j = 0; j < kTailMid; j += 2) stage_a2<L::ALO>(sc, 48 + j, a8[j], a8[j + 1]);
 #pragma unroll
-                for (int j = 0; j < kTailIn; ++j) stage_b<L::SUBB>(sc, j, dl16[j]);
+                for (int j = 0; j < kTailIn; j += 2) stage_b2<L::SUBB>(sc, j, dl16[j], dl16[j + 1]);
 #pragma unroll
-                for (int j = 0; j < kTailMid; ++j) stage_b<L::SUBB>(sc, 16 + j, d8[j]);
+                for (int j = 0; j < kTailMid; j += 2) stage_b2<L::SUBB>(sc, 16 + j, d8[j], d8[j + 1]);
 #pragma unroll
                 for (int j = 0; j < LAST; ++j) stage_b<L::SUBB>(sc, 24 + j, dz[j]);
                 if constexpr (NW == 1) stage_a_from_tmem32<L::ALO>(sc, 0, xh);
@@ -542,7 +559,7 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
                         tmem_ld<16>(xl + n0, r);
                         wait_ld();
 #pragma unroll
-                        for (int j = 0; j < 16; ++j) stage_b<L::SUBB>(sc, n0 + j, __uint_as_float(r[j]));
+                        for (int j = 0; j < 16; j += 2) stage_b2<L::SUBB>(sc, n0 + j, __uint_as_float(r[j]), __uint_as_float(r[j + 1]));
                     }
                     stage_a_from_tmem32<L::ALO>(sc, 0, xh);
                     stage_a_from_tmem32<L::ALO>(sc, 32, xh + 32);

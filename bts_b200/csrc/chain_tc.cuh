@@ -256,13 +256,17 @@ __device__ __forceinline__ void tc_epilogue_chunk(uint32_t lane_addr, float *act
         tmem_ld<16>(lane_addr + 2 * AW + C0 + n0, r);
         wait_ld();
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-            const float v = elu_fast(__uint_as_float(r[j]));
+        for (int j = 0; j < 16; j += 2) {
+            const float v0 = elu_fast(__uint_as_float(r[j])), v1 = elu_fast(__uint_as_float(r[j + 1]));
             if constexpr (SPILL) {
-                if (store) dst[(size_t)(n0 + j) * npx_pad] = v;
+                if (store) {
+                    dst[(size_t)(n0 + j) * npx_pad] = v0;
+                    dst[(size_t)(n0 + j + 1) * npx_pad] = v1;
+                }
             }
-            r[j] = __float_as_uint(v);
-            lo[j] = __float_as_uint(tf32_lo(v));
+            r[j] = __float_as_uint(v0);
+            r[j + 1] = __float_as_uint(v1);
+            tf32_lo2(v0, v1, lo[j], lo[j + 1]);
         }
         tmem_st<16>(lane_addr + n0, r);
         tmem_st<16>(lane_addr + AW + n0, lo);
@@ -413,41 +417,102 @@ __device__ __forceinline__ void lpg_block_grad(const TcArgs &a, const PlaneFwd &
 }
 
 // ---- last layer 8 -> (3|1): logits from a8 (shared by the forward tail and the stash backward, so both
-// see bit-identical logits)
+// see bit-identical logits). Packed FMAs: the even and the odd input channels accumulate in the two halves.
 template <int LAST>
 __device__ __forceinline__ void tail_logits(const float *w5, const float (&a8)[kTailMid], float (&z)[LAST])
 {
+    f32x2 a2[kTailMid / 2];
+#pragma unroll
+    for (int c = 0; c < kTailMid; c += 2) a2[c / 2] = pack2(a8[c], a8[c + 1]);
 #pragma unroll
     for (int o = 0; o < LAST; ++o) {
-        float s = 0.f;
+        f32x2 s = 0ull;
 #pragma unroll
         for (int c = 0; c < kTailMid; c += 4) {
-            const float4 w4 = *reinterpret_cast<const float4 *>(w5 + o * kTailMid + c);
-            s = fmaf(w4.x, a8[c], s); s = fmaf(w4.y, a8[c + 1], s);
-            s = fmaf(w4.z, a8[c + 2], s); s = fmaf(w4.w, a8[c + 3], s);
+            const ulonglong2 w4 = *reinterpret_cast<const ulonglong2 *>(w5 + o * kTailMid + c);
+            s = fma2(w4.x, a2[c / 2], s);
+            s = fma2(w4.y, a2[c / 2 + 1], s);
         }
-        z[o] = s;
+        z[o] = hsum2(s);
     }
 }
 
 // ---- the 16 -> 8 -> (3|1) tail on registers; weights broadcast from shared memory
-template <int LAST>
+// PACKED = false keeps scalar FMAs: the packed operands cost 16 more live registers, which the 2 x 2 stage's
+// one-pass backward (168-register cap) pays for in spills.
+template <int LAST, bool PACKED = true>
 __device__ __forceinline__ void tail_forward(const float *tw, const float (&a16)[kTailIn], float (&a8)[kTailMid],
                                              float (&z)[LAST])
 {
+    if constexpr (!PACKED) {
+#pragma unroll
+        for (int o = 0; o < kTailMid; ++o) {
+            float s = 0.f;
+#pragma unroll
+            for (int c = 0; c < kTailIn; c += 4) {
+                const float4 w4 = *reinterpret_cast<const float4 *>(tw + o * kTailIn + c);
+                s = fmaf(w4.x, a16[c], s); s = fmaf(w4.y, a16[c + 1], s);
+                s = fmaf(w4.z, a16[c + 2], s); s = fmaf(w4.w, a16[c + 3], s);
+            }
+            a8[o] = elu_fast(s);
+            asm volatile("" ::: "memory");
+        }
+        tail_logits<LAST>(tw + kTailMid * kTailIn, a8, z);
+        return;
+    }
+    f32x2 a2[kTailIn / 2];
+#pragma unroll
+    for (int c = 0; c < kTailIn; c += 2) a2[c / 2] = pack2(a16[c], a16[c + 1]);
 #pragma unroll
     for (int o = 0; o < kTailMid; ++o) {
-        float s = 0.f;
+        f32x2 s = 0ull;
 #pragma unroll
         for (int c = 0; c < kTailIn; c += 4) {
-            const float4 w4 = *reinterpret_cast<const float4 *>(tw + o * kTailIn + c);
-            s = fmaf(w4.x, a16[c], s); s = fmaf(w4.y, a16[c + 1], s);
-            s = fmaf(w4.z, a16[c + 2], s); s = fmaf(w4.w, a16[c + 3], s);
+            const ulonglong2 w4 = *reinterpret_cast<const ulonglong2 *>(tw + o * kTailIn + c);
+            s = fma2(w4.x, a2[c / 2], s);
+            s = fma2(w4.y, a2[c / 2 + 1], s);
         }
-        a8[o] = elu_fast(s);
+        a8[o] = elu_fast(hsum2(s));
         asm volatile("" ::: "memory");   // keep the weight loads of later rows from being hoisted (register pressure)
     }
     tail_logits<LAST>(tw + kTailMid * kTailIn, a8, z);
+}
+
+// dl16 = W4^T d8 (16 <- 8) with packed FMAs: channel pairs (c, c+1) share an accumulator register pair
+template <bool PACKED = true>
+__device__ __forceinline__ void tail_dgrad16(const float *tw, const float (&d8)[kTailMid], float (&dl16)[kTailIn])
+{
+    if constexpr (!PACKED) {
+#pragma unroll
+        for (int c = 0; c < kTailIn; ++c) dl16[c] = 0.f;
+#pragma unroll
+        for (int o = 0; o < kTailMid; ++o) {
+#pragma unroll
+            for (int c = 0; c < kTailIn; c += 4) {
+                const float4 w4 = *reinterpret_cast<const float4 *>(tw + o * kTailIn + c);
+                dl16[c] = fmaf(w4.x, d8[o], dl16[c]); dl16[c + 1] = fmaf(w4.y, d8[o], dl16[c + 1]);
+                dl16[c + 2] = fmaf(w4.z, d8[o], dl16[c + 2]); dl16[c + 3] = fmaf(w4.w, d8[o], dl16[c + 3]);
+            }
+            asm volatile("" ::: "memory");
+        }
+        return;
+    }
+    f32x2 acc[kTailIn / 2];
+#pragma unroll
+    for (int c = 0; c < kTailIn / 2; ++c) acc[c] = 0ull;
+#pragma unroll
+    for (int o = 0; o < kTailMid; ++o) {
+        const f32x2 d2 = pack2(d8[o], d8[o]);
+#pragma unroll
+        for (int c = 0; c < kTailIn; c += 4) {
+            const ulonglong2 w4 = *reinterpret_cast<const ulonglong2 *>(tw + o * kTailIn + c);
+            acc[c / 2] = fma2(w4.x, d2, acc[c / 2]);
+            acc[c / 2 + 1] = fma2(w4.y, d2, acc[c / 2 + 1]);
+        }
+        asm volatile("" ::: "memory");   // bound the hoisting of weight loads
+    }
+#pragma unroll
+    for (int c = 0; c < kTailIn; c += 2) unpack2(acc[c / 2], dl16[c], dl16[c + 1]);
 }
 
 // ---- weight packing, done by every CTA for itself straight from the raw fp32 weights (they are a few

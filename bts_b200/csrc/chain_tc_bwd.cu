@@ -147,17 +147,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_bwd1_kernel(BwdArgs b
             for (int j = 0; j < LAST; ++j) s = fmaf(w5[j * kTailMid + o], dz[j], s);
             d8[o] = s * elu_grad_from_out(a8[o]);
         }
-#pragma unroll
-        for (int c = 0; c < kTailIn; ++c) d16[c] = 0.f;
-#pragma unroll
-        for (int o = 0; o < kTailMid; ++o) {
-#pragma unroll
-            for (int c = 0; c < kTailIn; c += 4) {
-                const float4 w4 = *reinterpret_cast<const float4 *>(tw + o * kTailIn + c);
-                d16[c] = fmaf(w4.x, d8[o], d16[c]); d16[c + 1] = fmaf(w4.y, d8[o], d16[c + 1]);
-                d16[c + 2] = fmaf(w4.z, d8[o], d16[c + 2]); d16[c + 3] = fmaf(w4.w, d8[o], d16[c + 3]);
-            }
-        }
+            tail_dgrad16(tw, d8, d16);
         {
             float *dz_dst = del_gp + (size_t)BwdRows<CFG>::rowz() * npp;
 #pragma unroll
@@ -406,17 +396,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_dgrad_kernel(BwdArgs 
                 for (int j = 0; j < LAST; ++j) sm = fmaf(w5[j * kTailMid + o], dz[j], sm);
                 d8[o] = sm * elu_grad_from_out(a8[o]);
             }
-#pragma unroll
-            for (int c = 0; c < kTailIn; ++c) d16[c] = 0.f;
-#pragma unroll
-            for (int o = 0; o < kTailMid; ++o) {
-#pragma unroll
-                for (int c = 0; c < kTailIn; c += 4) {
-                    const float4 w4 = *reinterpret_cast<const float4 *>(tw + o * kTailIn + c);
-                    d16[c] = fmaf(w4.x, d8[o], d16[c]); d16[c + 1] = fmaf(w4.y, d8[o], d16[c + 1]);
-                    d16[c + 2] = fmaf(w4.z, d8[o], d16[c + 2]); d16[c + 3] = fmaf(w4.w, d8[o], d16[c + 3]);
-                }
-            }
+            tail_dgrad16(tw, d8, d16);
             float *del_gp = ba.del + gp;
             float *dz_dst = del_gp + (size_t)BwdRows<CFG>::rowz() * npp;
 #pragma unroll

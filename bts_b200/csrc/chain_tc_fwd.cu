@@ -96,10 +96,11 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
                 for (int c0 = 0; c0 < KC0; c0 += 16) {
                     uint32_t hi[16], lo[16];
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        const float v = xs[(C0 + c0 + j) * kTile];
-                        hi[j] = __float_as_uint(v);
-                        lo[j] = __float_as_uint(tf32_lo(v));
+                    for (int j = 0; j < 16; j += 2) {
+                        const float v0 = xs[(C0 + c0 + j) * kTile], v1 = xs[(C0 + c0 + j + 1) * kTile];
+                        hi[j] = __float_as_uint(v0);
+                        hi[j + 1] = __float_as_uint(v1);
+                        tf32_lo2(v0, v1, lo[j], lo[j + 1]);
                     }
                     tmem_st<16>(lane_addr + c0, hi);
                     tmem_st<16>(lane_addr + AW + c0, lo);
@@ -112,7 +113,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
 #pragma unroll
                     for (int j = 0; j < 32; ++j) hi[j] = valid ? __float_as_uint(__ldg(xp + (size_t)(C0 + c0 + j) * a.hw)) : 0u;
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) lo[j] = __float_as_uint(tf32_lo(__uint_as_float(hi[j])));
+                    for (int j = 0; j < 32; j += 2) tf32_lo2(__uint_as_float(hi[j]), __uint_as_float(hi[j + 1]), lo[j], lo[j + 1]);
                     tmem_st<32>(lane_addr + c0, hi);
                     tmem_st<32>(lane_addr + AW + c0, lo);
                 }

@@ -236,8 +236,48 @@ __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads)
 
 // 3xTF32 operand split. The tensor core reads only the top 19 bits of an fp32 word, so hi is the
 // word itself (hardware truncation) and lo is the exactly representable remainder.
+// ---- packed fp32 pairs (FFMA2 / FADD2 / FMUL2 on sm_100a): one issue slot for two fp32 operations. The FMA
+// pipe rate is unchanged (tests/cuda/probe_ffma2.cu: 127 vs 124 FMA/clk/SM), but these kernels are bound by
+// issue slots, not by the pipe.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi)
+{
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float &lo, float &hi)
+{
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c)
+{
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ float hsum2(f32x2 v)
+{
+    float lo, hi;
+    unpack2(v, lo, hi);
+    return lo + hi;
+}
+
 __device__ __forceinline__ float tf32_hi(float v) { return __uint_as_float(__float_as_uint(v) & 0xFFFFE000u); }
 __device__ __forceinline__ float tf32_lo(float v) { return v - tf32_hi(v); }
+// two remainders for three instructions: v - hi evaluated as fma(hi, -1, v), exact like the subtraction
+__device__ __forceinline__ void tf32_lo2(float v0, float v1, float &l0, float &l1)
+{
+    const f32x2 v = pack2(v0, v1);
+    unpack2(fma2(v & 0xFFFFE000FFFFE000ull, 0xBF800000BF800000ull, v), l0, l1);
+}
+__device__ __forceinline__ void tf32_lo2(float v0, float v1, uint32_t &l0, uint32_t &l1)
+{
+    float a, b;
+    tf32_lo2(v0, v1, a, b);
+    l0 = __float_as_uint(a);
+    l1 = __float_as_uint(b);
+}
 
 }  // namespace tc
 }  // namespace bts
