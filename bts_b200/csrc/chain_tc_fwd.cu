@@ -61,10 +61,19 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
     const int stride = (int)gridDim.x * NWG;
     float *xs_wg = xs_all + (size_t)wg * D0 * kTile;              // [channel][pixel] of the staged tile
     float *xs = xs_wg + t;                                        // this thread's pixel column
-    // 128-bit copies: thread t moves pixels 4q..4q+3 (q = t%32) of channels t/32, t/32+4, ...; 4 pixels never
-    // straddle two images because hw % 4 == 0 (the launcher picks the non-prefetching kernel otherwise).
+    // 128-bit copies: 4 pixels never straddle two images because hw % 4 == 0 (the launcher picks the
+    // non-prefetching kernel otherwise). Two mappings, chosen by measurement: WARP_PRIVATE (32-channel head) -- each
+    // warp copies its own 32 pixels (lane l: pixels 4(l%8)..+3 of channels l/8, l/8+4, ...) and the staged tile
+    // needs no barrier wider than the warp; otherwise a warp copies 512 contiguous bytes of one channel per
+    // instruction (thread t: pixels 4(t%32)..+3 of channels t/32, t/32+4, ...), which DRAM prefers for wider
+    // chains, and the warpgroup synchronises on a named barrier.
+    constexpr bool WARP_PRIVATE = D0 <= 32;
+    auto tile_sync = [&]() {
+        if constexpr (WARP_PRIVATE) __syncwarp();
+        else named_bar_sync(1 + wg, kTile);
+    };
     auto prefetch = [&](int tl) {
-        const int q = t & 31, cw = t >> 5;
+        const int q = WARP_PRIVATE ? (((t >> 5) << 3) | (lane & 7)) : (t & 31), cw = WARP_PRIVATE ? (lane >> 3) : (t >> 5);
         const unsigned g0 = (unsigned)tl * kTile + 4 * q;
         const bool ok = tl < ntiles && g0 < npx;
         const int bn = ok ? (int)(g0 / hw) : 0;
@@ -121,7 +130,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
         };
         if constexpr (PREFETCH) {
             cp_async_wait_all();
-            named_bar_sync(1 + wg, kTile);                        // the tile was copied by all threads of the warpgroup
+            tile_sync();                                          // the staged pixels this thread reads have landed
         }
         load_x(std::integral_constant<int, 0>{});
         if constexpr (D0 > KC0) {
@@ -129,7 +138,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
             load_x(std::integral_constant<int, KC0>{});
         }
         if constexpr (PREFETCH) {
-            named_bar_sync(1 + wg, kTile);                        // everybody has read the staged tile
+            tile_sync();                                          // the staged tile has been read by everyone who shares it
             prefetch(tile + stride);
         }
         tc_run_chunk<CFG, 0, AW, D0 - KC0, KC0>(wg_base, sw, bar, phase, wg, t);
