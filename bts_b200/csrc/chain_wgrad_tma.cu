@@ -148,14 +148,27 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
                 const WtJob &job = pl.jobs[j];
                 float4 *a_hi = reinterpret_cast<float4 *>(slots + (size_t)s * kWtSlotBytes);
                 float4 *a_lo = a_hi + 1024, *b_hi = a_hi + 2048, *b_lo = b_hi + job.nb * 8;
-                for (int i = st; i < job.a_rows * 8; i += 128) {
-                    const float4 v = a_hi[i];
-                    a_lo[i] = make_float4(tf32_lo(v.x), tf32_lo(v.y), tf32_lo(v.z), tf32_lo(v.w));
-                }
-                for (int i = st; i < job.nb * 8; i += 128) {
-                    const float4 v = b_hi[i];
-                    b_lo[i] = make_float4(tf32_lo(v.x), tf32_lo(v.y), tf32_lo(v.z), tf32_lo(v.w));
-                }
+                // remainder images, four independent 16-byte units in flight per thread
+                auto split_image = [&](const float4 *hi, float4 *lo, int units) {
+#pragma unroll 1
+                    for (int i = st; i < units; i += 512) {
+                        float4 v[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u)
+                            if (i + u * 128 < units) v[u] = hi[i + u * 128];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            if (i + u * 128 < units) {
+                                float4 r;
+                                tf32_lo2(v[u].x, v[u].y, r.x, r.y);
+                                tf32_lo2(v[u].z, v[u].w, r.z, r.w);
+                                lo[i + u * 128] = r;
+                            }
+                        }
+                    }
+                };
+                split_image(a_hi, a_lo, job.a_rows * 8);
+                split_image(b_hi, b_lo, job.nb * 8);
                 fence_smem_to_async();
                 mbar_arrive(split + s);
             }

@@ -28,7 +28,9 @@ WANT = [
     ("launch__shared_mem_per_block_dynamic", "dynamic smem/block"),
     ("launch__grid_size", "grid"),
     ("launch__block_size", "block"),
-    ("sm__pipe_tensor_subpipe_umma_cycles_active.avg.pct_of_peak_sustained_active", "tensor (umma) pipe %"),
+    ("TPC.TriageCompute.sm__pipe_tensor_cycles_active_realtime.avg.pct_of_peak_sustained_elapsed", "tensor pipe active %"),
+    ("sm__mem_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed", "tensor memory (TMEM) active %"),
+    ("sm__inst_executed_pipe_tmem.avg.pct_of_peak_sustained_active", "tcgen05.ld/st pipe %"),
     ("smsp__cycles_active.avg", "SMSP active cycles"),
 ]
 
