@@ -533,11 +533,25 @@ __device__ __forceinline__ void tc_pack_to_smem(const float *const *W, float *sw
         const int K = CFG::K(l), N = CFG::N(l);
         float *hi = sw + CFG::w_off(l), *lo = hi + N * K;
         const float *w = W[l];
-        for (int u = tid; u < N * K / 4; u += nth) {
-            const int n = (u / (2 * K)) * 8 + (u & 7), kq = (u >> 3) % (K / 4);
-            const float4 v = __ldg(reinterpret_cast<const float4 *>(w + (size_t)n * K + 4 * kq));
-            *reinterpret_cast<float4 *>(hi + 4 * u) = v;
-            *reinterpret_cast<float4 *>(lo + 4 * u) = tf32_lo4(v);
+        // four loads in flight per thread: the packing is the kernel's prologue and pure load latency otherwise
+        for (int u0 = tid; u0 < N * K / 4; u0 += 4 * nth) {
+            float4 v[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int u = u0 + i * nth;
+                if (u < N * K / 4) {
+                    const int n = (u / (2 * K)) * 8 + (u & 7), kq = (u >> 3) % (K / 4);
+                    v[i] = __ldg(reinterpret_cast<const float4 *>(w + (size_t)n * K + 4 * kq));
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int u = u0 + i * nth;
+                if (u < N * K / 4) {
+                    *reinterpret_cast<float4 *>(hi + 4 * u) = v[i];
+                    *reinterpret_cast<float4 *>(lo + 4 * u) = tf32_lo4(v[i]);
+                }
+            }
         }
     }
     float *tw = sw + CFG::tail_off();
@@ -554,12 +568,25 @@ __device__ __forceinline__ void tc_pack_t_to_smem(const float *const *W, float *
         const int K = CFG::K(l), N = CFG::N(l);
         float *hi = swt + CFG::w_off(l), *lo = hi + N * K;
         const float *w = W[l];
-        for (int u = tid; u < N * K / 4; u += nth) {
-            const int c = (u / (2 * N)) * 8 + (u & 7), oq = (u >> 3) % (N / 4);
-            const float *src = w + (size_t)(4 * oq) * K + c;
-            const float4 v = make_float4(__ldg(src), __ldg(src + K), __ldg(src + 2 * K), __ldg(src + 3 * K));
-            *reinterpret_cast<float4 *>(hi + 4 * u) = v;
-            *reinterpret_cast<float4 *>(lo + 4 * u) = tf32_lo4(v);
+        for (int u0 = tid; u0 < N * K / 4; u0 += 4 * nth) {
+            float4 v[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int u = u0 + i * nth;
+                if (u < N * K / 4) {
+                    const int c = (u / (2 * N)) * 8 + (u & 7), oq = (u >> 3) % (N / 4);
+                    const float *src = w + (size_t)(4 * oq) * K + c;
+                    v[i] = make_float4(__ldg(src), __ldg(src + K), __ldg(src + 2 * K), __ldg(src + 3 * K));
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int u = u0 + i * nth;
+                if (u < N * K / 4) {
+                    *reinterpret_cast<float4 *>(hi + 4 * u) = v[i];
+                    *reinterpret_cast<float4 *>(lo + 4 * u) = tf32_lo4(v[i]);
+                }
+            }
         }
     }
 }
