@@ -55,6 +55,10 @@ int launch_silog_fwd(const float *, const float *, const unsigned char *, long l
 int launch_silog_bwd(const float *, const float *, const unsigned char *, long long, float, const float *, const void *,
                      float *, int, cudaStream_t);
 
+size_t eval_workspace_bytes(int B, int H, int W, int sms);
+int launch_eval_metrics(const float *, const float *, int, int, int, float, float, int, int, int, int, float *, int *, void *,
+                        int, cudaStream_t);
+
 static int sm_count()
 {
     int dev = 0, n = 148;
@@ -410,6 +414,27 @@ int bts_silog_bwd(const float *depth_est, const float *depth_gt, const unsigned 
     if (n == 0) return BTS_OK;
     return launch_silog_bwd(depth_est, depth_gt, mask, n, variance_focus, grad_loss, ws, grad_est, sm_count(),
                             (cudaStream_t)stream);
+}
+
+size_t bts_eval_workspace_bytes(int B, int H, int W)
+{
+    if (B <= 0 || H <= 0 || W <= 0) return 0;
+    return eval_workspace_bytes(B, H, W, sm_count());
+}
+
+int bts_eval_metrics(const float *pred, const float *gt, int B, int H, int W, float min_depth, float max_depth,
+                     int crop_top, int crop_bottom, int crop_left, int crop_right, float *out, int *count,
+                     void *ws, size_t ws_bytes, void *stream)
+{
+    if (B < 0 || H < 0 || W < 0) return set_error(BTS_ERR_BAD_ARG, "negative size B=%d H=%d W=%d", B, H, W);
+    if ((long long)B * H * W == 0) return BTS_OK;
+    if (!pred || !gt || !out) return set_error(BTS_ERR_BAD_ARG, "pred / gt / out is NULL");
+    if (ws == nullptr || ws_bytes < bts_eval_workspace_bytes(B, H, W) || (reinterpret_cast<uintptr_t>(ws) & 7u))
+        return set_error(BTS_ERR_WORKSPACE, "workspace %zu B < %zu B (or not 8-byte aligned)", ws_bytes,
+                         bts_eval_workspace_bytes(B, H, W));
+    if (B > 65535) return set_error(BTS_ERR_UNSUPPORTED, "more than 65535 images per call");
+    return launch_eval_metrics(pred, gt, B, H, W, min_depth, max_depth, crop_top, crop_bottom, crop_left, crop_right, out,
+                               count, ws, sm_count(), (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -272,6 +272,36 @@ def silog(depth_est, depth_gt, mask, variance_focus):
     return _Silog.apply(depth_est, depth_gt, mask, variance_focus)
 
 
+EVAL_METRICS = ("silog", "abs_rel", "log10", "rms", "sq_rel", "log_rms", "d1", "d2", "d3")   # bts_main.py:84
+
+
+def eval_metrics(pred, gt, min_depth, max_depth, crop=None):
+    """compute_errors (pytorch/bts_main.py:87-108) with the clamp and validity mask of online_eval (:233-252), per
+    image, on the GPU. pred, gt: [B,H,W] (or [B,1,H,W] / [H,W]); crop = (top, bottom, left, right) or None.
+    -> (metrics [B,9] in EVAL_METRICS order, valid-pixel counts [B])."""
+    pred = _require_cuda_f32(pred, "pred")
+    gt = _require_cuda_f32(gt, "gt")
+    if pred.shape != gt.shape:
+        raise RuntimeError("pred and gt must have the same shape")
+    if pred.dim() == 2:
+        pred, gt = pred[None], gt[None]
+    if pred.dim() == 4:
+        if pred.shape[1] != 1:
+            raise RuntimeError("expected a single-channel depth map")
+        pred, gt = pred[:, 0], gt[:, 0]
+    B, H, W = pred.shape
+    top, bottom, left, right = (0, H, 0, W) if crop is None else [int(v) for v in crop]
+    out = torch.empty((B, 9), dtype=torch.float32, device=pred.device)
+    count = torch.empty((B,), dtype=torch.int32, device=pred.device)
+    nws = _cabi.lib().bts_eval_workspace_bytes(B, H, W)
+    ws = torch.empty(((nws + 7) // 8,), dtype=torch.float64, device=pred.device)
+    with torch.cuda.device(pred.device):
+        _cabi.check(_cabi.lib().bts_eval_metrics(pred.data_ptr(), gt.data_ptr(), B, H, W, float(min_depth), float(max_depth),
+                                                 top, bottom, left, right, out.data_ptr(), count.data_ptr(), ws.data_ptr(),
+                                                 nws, _stream()), "bts_eval_metrics")
+    return out, count
+
+
 def lpg(plane_eq, upratio):
     """-> (depth [B,h*r,w*r], abs_min 0-dim). Drop-in math of local_planar_guidance.forward."""
     return _LPG.apply(plane_eq, upratio)

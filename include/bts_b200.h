@@ -195,6 +195,19 @@ BTS_API int bts_silog_fwd(const float *depth_est, const float *depth_gt, const u
 BTS_API int bts_silog_bwd(const float *depth_est, const float *depth_gt, const unsigned char *mask, long long n,
                   float variance_focus, const float *grad_loss, const void *ws, float *grad_est, void *stream);
 
+/*
+ * online_eval's per-sample metrics                       pytorch/bts_main.py:218-254, compute_errors :87-108
+ * (SURVEY.md 8(f)-5). For each of the B images: clamp the prediction to [min_depth, max_depth] (inf -> max,
+ * nan -> min, :233-236), mask = min_depth < gt < max_depth inside the crop rectangle [crop_top, crop_bottom) x
+ * [crop_left, crop_right) (:238-252; pass 0, H, 0, W for no crop), and reduce the nine metrics in ONE pass:
+ *   out[b][0..8] = silog, abs_rel, log10, rms, sq_rel, log_rms, d1, d2, d3     (order of eval_metrics, :84)
+ * `count[b]` (nullable) receives the number of valid pixels. No device->host copy, no boolean-mask gather.
+ */
+BTS_API size_t bts_eval_workspace_bytes(int B, int H, int W);
+BTS_API int bts_eval_metrics(const float *pred, const float *gt, int B, int H, int W, float min_depth, float max_depth,
+                     int crop_top, int crop_bottom, int crop_left, int crop_right, float *out, int *count,
+                     void *ws, size_t ws_bytes, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

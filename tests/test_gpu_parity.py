@@ -535,3 +535,42 @@ def test_silog_loss_edge_cases():
     assert abs(float(crit(est, gt, one)) - 10.0 * (0.15 * d * d) ** 0.5) <= 1e-5 * (10.0 * (0.15 * d * d) ** 0.5) + 1e-7
     with pytest.raises(RuntimeError):
         crit(est, gt, one.float())
+
+
+def _compute_errors_ref(gt, pred):
+    """Restatement of compute_errors, pytorch/bts_main.py:87-108 (numpy, evaluated in fp64 here)."""
+    gt, pred = gt.astype(np.float64), pred.astype(np.float64)
+    thresh = np.maximum(gt / pred, pred / gt)
+    d1, d2, d3 = (thresh < 1.25).mean(), (thresh < 1.25 ** 2).mean(), (thresh < 1.25 ** 3).mean()
+    rms = np.sqrt(((gt - pred) ** 2).mean())
+    log_rms = np.sqrt(((np.log(gt) - np.log(pred)) ** 2).mean())
+    abs_rel = np.mean(np.abs(gt - pred) / gt)
+    sq_rel = np.mean(((gt - pred) ** 2) / gt)
+    err = np.log(pred) - np.log(gt)
+    silog = np.sqrt(np.mean(err ** 2) - np.mean(err) ** 2) * 100
+    log10 = np.mean(np.abs(np.log10(pred) - np.log10(gt)))
+    return [silog, abs_rel, log10, rms, sq_rel, log_rms, d1, d2, d3]
+
+
+@pytest.mark.parametrize("B,H,W,crop,lo,hi", [(3, 480, 640, (45, 471, 41, 601), 1e-3, 10.0), (2, 352, 1216, None, 1e-3, 80.0),
+                                              (1, 37, 53, (5, 30, 7, 50), 0.5, 8.0)], ids=str)
+def test_eval_metrics_vs_reference(B, H, W, crop, lo, hi):
+    """online_eval's clamp + validity mask + compute_errors (bts_main.py:233-254, 87-108)."""
+    from bts_b200 import functional as Fn
+    gen = torch.Generator().manual_seed(21)
+    gt = torch.rand(B, H, W, generator=gen) * (hi * 1.2)            # some gt beyond max_depth, some ~0
+    gt[torch.rand(B, H, W, generator=gen) < 0.3] = 0.0              # sparse ground truth
+    pred = gt * (1 + 0.3 * torch.randn(B, H, W, generator=gen)) + 0.05 * torch.rand(B, H, W, generator=gen)
+    pred[0, 3, 4], pred[0, 5, 6], pred[0, 7, 8], pred[0, 9, 10] = float("inf"), float("nan"), -1.0, 1e9
+    got, cnt = Fn.eval_metrics(pred.cuda(), gt.cuda(), lo, hi, crop)
+    for b in range(B):
+        p, g = pred[b].numpy().copy(), gt[b].numpy()
+        p[p < lo] = lo; p[p > hi] = hi; p[np.isinf(p)] = hi; p[np.isnan(p)] = lo     # bts_main.py:233-236
+        valid = np.logical_and(g > lo, g < hi)
+        if crop is not None:
+            m = np.zeros_like(valid)
+            m[crop[0]:crop[1], crop[2]:crop[3]] = 1
+            valid = np.logical_and(valid, m)
+        ref = _compute_errors_ref(g[valid], p[valid])
+        assert int(cnt[b]) == int(valid.sum())
+        assert np.allclose(got[b].cpu().numpy(), np.array(ref), rtol=1e-5, atol=1e-7), (got[b].cpu().numpy(), ref)
