@@ -59,6 +59,8 @@ size_t eval_workspace_bytes(int B, int H, int W, int sms);
 int launch_eval_metrics(const float *, const float *, int, int, int, float, float, int, int, int, int, float *, int *, void *,
                         int, cudaStream_t);
 
+int launch_backproject(const float *, float *, int, int, int, float, float, float, float, float, float, cudaStream_t);
+
 static int sm_count()
 {
     int dev = 0, n = 148;
@@ -435,6 +437,17 @@ int bts_eval_metrics(const float *pred, const float *gt, int B, int H, int W, fl
     if (B > 65535) return set_error(BTS_ERR_UNSUPPORTED, "more than 65535 images per call");
     return launch_eval_metrics(pred, gt, B, H, W, min_depth, max_depth, crop_top, crop_bottom, crop_left, crop_right, out,
                                count, ws, sm_count(), (cudaStream_t)stream);
+}
+
+int bts_backproject(const float *depth, float *points, int B, int H, int W, float fx, float fy, float cx, float cy,
+                    float edge_thresh, float hidden, void *stream)
+{
+    if (B < 0 || H < 0 || W < 0) return set_error(BTS_ERR_BAD_ARG, "negative size B=%d H=%d W=%d", B, H, W);
+    if ((long long)B * H * W == 0) return BTS_OK;
+    if (!depth || !points) return set_error(BTS_ERR_BAD_ARG, "depth / points is NULL");
+    if (fx == 0.f || fy == 0.f) return set_error(BTS_ERR_BAD_ARG, "zero focal length");
+    if ((long long)B * H * W > (1ll << 31) - 1) return set_error(BTS_ERR_UNSUPPORTED, "more than 2^31 pixels");
+    return launch_backproject(depth, points, B, H, W, fx, fy, cx, cy, edge_thresh, hidden, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -302,6 +302,24 @@ def eval_metrics(pred, gt, min_depth, max_depth, crop=None):
     return out, count
 
 
+def backproject(depth, fx=518.8579, fy=518.8579, cx=None, cy=None, edge_thresh=0.3, hidden=1e6):
+    """posFromDepth (pytorch/bts_live_3d.py:422-429) on the GPU: depth [B,H,W] or [H,W] -> points [B,H*W,3] with depth
+    edges (Sobel magnitude > edge_thresh) pushed to `hidden`. Defaults are the viewer's constants (:415-417, 425)."""
+    depth = _require_cuda_f32(depth, "depth")
+    single = depth.dim() == 2
+    if single:
+        depth = depth[None]
+    if depth.dim() != 3:
+        raise RuntimeError("depth must be [B,H,W] or [H,W]")
+    B, H, W = depth.shape
+    pts = torch.empty((B, H * W, 3), dtype=torch.float32, device=depth.device)
+    with torch.cuda.device(depth.device):
+        _cabi.check(_cabi.lib().bts_backproject(depth.data_ptr(), pts.data_ptr(), B, H, W, float(fx), float(fy),
+                                                float(W / 2 if cx is None else cx), float(H / 2 if cy is None else cy),
+                                                float(edge_thresh), float(hidden), _stream()), "bts_backproject")
+    return pts[0] if single else pts
+
+
 def lpg(plane_eq, upratio):
     """-> (depth [B,h*r,w*r], abs_min 0-dim). Drop-in math of local_planar_guidance.forward."""
     return _LPG.apply(plane_eq, upratio)

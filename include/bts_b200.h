@@ -208,6 +208,17 @@ BTS_API int bts_eval_metrics(const float *pred, const float *gt, int B, int H, i
                      int crop_top, int crop_bottom, int crop_left, int crop_right, float *out, int *count,
                      void *ws, size_t ws_bytes, void *stream);
 
+/*
+ * Live-viewer point cloud, headless            pytorch/bts_live_3d.py:132-136 (edges), 414-429 (worldCoords,
+ * posFromDepth). depth [B][H][W] -> points [B][H*W][3]:
+ *   hide (z := hidden) where |sobel_rows| + |sobel_cols| > edge_thresh  (scipy.ndimage.sobel, reflect boundary),
+ *   (x, y, z) = ((u - cx) / fx * z, (v - cy) / fy * z, z).   The viewer uses fx = fy = 518.8579, cx = W/2,
+ *   cy = H/2, edge_thresh = 0.3, hidden = 1e6. The OpenGL window / VBO upload is unavailable on this box; the
+ *   buffer written here is what it would upload.
+ */
+BTS_API int bts_backproject(const float *depth, float *points, int B, int H, int W, float fx, float fy, float cx, float cy,
+                    float edge_thresh, float hidden, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

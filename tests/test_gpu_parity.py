@@ -574,3 +574,31 @@ def test_eval_metrics_vs_reference(B, H, W, crop, lo, hi):
         ref = _compute_errors_ref(g[valid], p[valid])
         assert int(cnt[b]) == int(valid.sum())
         assert np.allclose(got[b].cpu().numpy(), np.array(ref), rtol=1e-5, atol=1e-7), (got[b].cpu().numpy(), ref)
+
+
+@pytest.mark.parametrize("B,H,W", [(1, 480, 640), (2, 37, 53), (1, 3, 5)], ids=str)
+def test_backproject_vs_viewer_math(B, H, W):
+    """posFromDepth / worldCoords / edges of pytorch/bts_live_3d.py:132-136, 414-429 -- the oracle is
+    the viewer's own numpy + scipy.ndimage.sobel sequence (restated below line by line)."""
+    from scipy import ndimage
+    from bts_b200 import functional as Fn
+    gen = torch.Generator().manual_seed(4)
+    depth = (torch.rand(B, H, W, generator=gen) * 0.2 + torch.linspace(1, 6, W)[None, None, :]).contiguous()
+    depth[:, H // 2:, W // 2:] += 2.5                                      # a depth discontinuity -> hidden points
+    got = Fn.backproject(depth.cuda()).cpu().numpy()
+    for b in range(B):
+        d = depth[b].numpy().astype(np.float32).copy()
+        cx, cy, fx, fy = W / 2, H / 2, 518.8579, 518.8579                  # bts_live_3d.py:415-417
+        xx, yy = np.tile(range(W), H), np.repeat(range(H), W)
+        xx, yy = (xx - cx) / fx, (yy - cy) / fy
+        e = np.abs(ndimage.sobel(d, 0)) + np.abs(ndimage.sobel(d, 1))      # :133-136
+        d[e > 0.3] = 1e6                                                   # :425
+        z = d.reshape(H * W)
+        ref = np.dstack((xx * z, yy * z, z)).reshape((H * W, 3))
+        hidden_ref, hidden_got = ref[:, 2] == 1e6, got[b][:, 2] == 1e6
+        # the Sobel sums are evaluated in a different order: only a pixel within rounding of the threshold may flip
+        clear = (np.abs(e - 0.3) > 1e-4).reshape(H * W)
+        assert (hidden_ref == hidden_got)[clear].all()
+        assert np.allclose(got[b][clear], ref[clear], rtol=1e-5, atol=1e-6)
+    if H * W > 1000:
+        assert (got[..., 2] == 1e6).any() and (got[..., 2] != 1e6).any()
