@@ -11,7 +11,7 @@
 //   axis as K, activations and their tf32 remainders stacked along M ([a_hi ; a_lo], M = 128), deltas
 //   stacked along N ([d_hi ; d_lo], N = 64), so ONE MMA per 8 pixels yields hi*hi + hi*lo + lo*hi (+lo*lo).
 //
-// Roles: NWG compute warpgroups (thread = low-res pixel = TMEM lane) + one MMA-issuing warp. Hand-offs
+// Roles: NWG compute warpgroups (thread = low-res pixel = TMEM lane) + one MMA-issuing warp per warpgroup. Hand-offs
 // are mbarriers only (no CTA-wide barrier inside the tile loop):
 //   ready[g]  4 warp arrivals compute -> issuer   "A operand for the next chain MMA is in TMEM"
 //   done[g]   tcgen05.commit issuer -> compute  "chain MMA finished, D is readable"
@@ -94,77 +94,62 @@ struct FusedLayout {
     static_assert(ACC + NWG * WGCOLS <= 512, "TMEM budget");
 };
 
-// ---- the MMA-issuing thread: walks every warpgroup's fixed command list, in order per warpgroup,
-// round-robin across warpgroups.  NW == 1: F0, DG0, WT(h0), WT(h1).
-//                                 NW == 2: F0, F1, DG1, WT(h0), DG0, WT(h1), WX(h0), WX(h1).
-struct IssuerWg {            // per-warpgroup progress of the issuer (scalars: must stay in registers)
-    int cmd, rph, sph0, sph1;
-    int left;
-};
-
-// one poll of warpgroup G: issue its next command if the operands are ready. Returns true on progress.
-template <class CFG, int MODE, int R, int NWG, int G>
-__device__ __forceinline__ bool fused_issuer_step(IssuerWg &w, const float *sw, const float *swt, uint32_t stage_addr,
-                                                  uint64_t *bars, uint32_t tbase)
+// ---- the MMA-issuing warps: one per warpgroup, each walks its warpgroup's fixed command list in order.
+//        NW == 1: F0, DG0, WT(h0), WT(h1).     NW == 2: F0, F1, DG1, WT(h0), DG0, WT(h1), WX(h0), WX(h1).
+// The whole warp runs the control flow (blocking mbarrier waits); the MMAs and the commit sit behind elect.sync
+// with warp-uniform operands, so they compile to back-to-back UTCHMMA. (A single polling thread behind
+// `if (tid == k)` cost ~8 instructions / ~45 cycles per MMA and was ~80 % busy: it bounded the kernel.)
+template <class CFG, int MODE, int R, int NWG>
+__device__ __noinline__ void fused_issuer(int g, const float *sw, const float *swt, uint32_t stage_addr, uint64_t *bars,
+                                          uint32_t tbase, int ntiles)
 {
     using L = FusedLayout<CFG, MODE, R, NWG>;
     constexpr int K0 = L::K0, NW = L::NW;
-    if (w.left == 0) return false;
-    uint64_t *ready = bars + 6 * G, *done = ready + 1, *stg0 = ready + 2, *stg1 = ready + 3, *wfree0 = ready + 4, *wfree1 = ready + 5;
-    const int c = w.cmd;
-    const bool is_w = (NW == 1) ? (c >= 2) : (c == 3 || c >= 5);
-    const bool h1 = is_w && ((NW == 1) ? (c == 3) : (c == 5 || c == 7));   // which pair's half this command multiplies
-    if (!is_w) {
-        if (!mbar_test_wait(ready, w.rph)) return false;
-        w.rph ^= 1;
-    } else if (!h1) {
-        if (!mbar_test_wait(stg0, w.sph0)) return false;
-        w.sph0 ^= 1;
-    } else {
-        if (!mbar_test_wait(stg1, w.sph1)) return false;
-        w.sph1 ^= 1;
-    }
-    fence_after_sync();
-    const uint32_t wb = tbase + L::ACC + G * L::WGCOLS;           // x_hi
+    const int stride = (int)gridDim.x * NWG;
+    const int first = (int)blockIdx.x * NWG + g;
+    const int mine = first < ntiles ? (ntiles - first + stride - 1) / stride : 0;
+    uint64_t *ready = bars + 6 * g, *done = ready + 1, *stg0 = ready + 2, *stg1 = ready + 3, *wfree0 = ready + 4, *wfree1 = ready + 5;
+    const uint32_t wb = tbase + L::ACC + g * L::WGCOLS;           // x_hi
     const uint32_t xl = wb + K0, dd = wb + 2 * K0;
     // shared staging: both pairs use sub-buffers 0,1; private: pair h uses 2h, 2h+1
-    const uint32_t sub0 = stage_addr + G * L::NSUB * L::SUB + ((L::PRIV && h1) ? 2 * L::SUB : 0);
+    const uint32_t subA = stage_addr + g * L::NSUB * L::SUB;
+    const uint32_t subB = subA + (L::PRIV ? 2 * L::SUB : 0);
     static_assert(!L::PRIV || NW == 1, "private staging is laid out for the single-round chains");
-    if constexpr (NW == 1) {
-        if (c == 0) { issue_ts3<CFG::K(0), CFG::N(0)>(dd, wb, xl, sw + CFG::w_off(0)); mma_commit(done); }
-        else if (c == 1) { issue_ts3<CFG::N(0), CFG::K(0)>(dd, xl, xl + 16, swt + CFG::w_off(0)); mma_commit(done); }
-        else { issue_wgrad_half<L::SUB, L::SUBB>(tbase, sub0); mma_commit(h1 ? wfree1 : wfree0); }
-    } else {
-        if (c == 0) { issue_ts3<CFG::K(0), CFG::N(0)>(dd, wb, xl, sw + CFG::w_off(0)); mma_commit(done); }
-        else if (c == 1) { issue_ts3<CFG::K(1), CFG::N(1)>(dd, xl, xl + 32, sw + CFG::w_off(1)); mma_commit(done); }
-        else if (c == 2) { issue_ts3<CFG::N(1), CFG::K(1)>(dd, xl + 32, xl + 48, swt + CFG::w_off(1)); mma_commit(done); }
-        else if (c == 4) { issue_ts3<CFG::N(0), CFG::K(0)>(dd, xl, xl + 32, swt + CFG::w_off(0)); mma_commit(done); }
-        else if (c == 3 || c == 5) { issue_wgrad_half<L::SUB, L::SUBB>(tbase, sub0); mma_commit(h1 ? wfree1 : wfree0); }
-        else { issue_wgrad_half<L::SUB, L::SUBB>(tbase + 64, sub0); mma_commit(h1 ? wfree1 : wfree0); }
-    }
-    if (c + 1 == L::NCMD) { w.cmd = 0; --w.left; }
-    else w.cmd = c + 1;
-    return true;
-}
-
-template <class CFG, int MODE, int R, int NWG>
-__device__ __noinline__ void fused_issuer(const float *sw, const float *swt, uint32_t stage_addr, uint64_t *bars,
-                                             uint32_t tbase, int ntiles)
-{
-    static_assert(NWG >= 1 && NWG <= 3, "one to three warpgroups");
-    const int stride = (int)gridDim.x * NWG;
-    auto tiles_of = [&](int g) {
-        const int first = (int)blockIdx.x * NWG + g;
-        return first < ntiles ? (ntiles - first + stride - 1) / stride : 0;
-    };
-    IssuerWg w0{0, 0, 0, 0, tiles_of(0)}, w1{0, 0, 0, 0, NWG > 1 ? tiles_of(1) : 0}, w2{0, 0, 0, 0, NWG > 2 ? tiles_of(2) : 0};
-    uint32_t idle = 0;
-    while (w0.left + w1.left + w2.left > 0) {
-        bool progressed = fused_issuer_step<CFG, MODE, R, NWG, 0>(w0, sw, swt, stage_addr, bars, tbase);
-        if constexpr (NWG > 1) progressed |= fused_issuer_step<CFG, MODE, R, NWG, 1>(w1, sw, swt, stage_addr, bars, tbase);
-        if constexpr (NWG > 2) progressed |= fused_issuer_step<CFG, MODE, R, NWG, 2>(w2, sw, swt, stage_addr, bars, tbase);
-        if (progressed) idle = 0;
-        else if (++idle > (1u << 28)) __trap();
+    uint32_t rph = 0, sph0 = 0, sph1 = 0;
+#pragma unroll 1
+    for (int i = 0; i < mine; ++i) {
+#pragma unroll
+        for (int c = 0; c < L::NCMD; ++c) {
+            const bool is_w = (NW == 1) ? (c >= 2) : (c == 3 || c >= 5);
+            const bool h1 = is_w && ((NW == 1) ? (c == 3) : (c == 5 || c == 7));   // which pair's half this command multiplies
+            if (!is_w) {
+                mbar_wait(ready, rph);
+                rph ^= 1;
+            } else if (!h1) {
+                mbar_wait(stg0, sph0);
+                sph0 ^= 1;
+            } else {
+                mbar_wait(stg1, sph1);
+                sph1 ^= 1;
+            }
+            fence_after_sync();
+            if (elect_one()) {
+                const uint32_t sub0 = h1 ? subB : subA;
+                if constexpr (NW == 1) {
+                    if (c == 0) { issue_ts3<CFG::K(0), CFG::N(0)>(dd, wb, xl, sw + CFG::w_off(0)); mma_commit(done); }
+                    else if (c == 1) { issue_ts3<CFG::N(0), CFG::K(0)>(dd, xl, xl + 16, swt + CFG::w_off(0)); mma_commit(done); }
+                    else { issue_wgrad_half<L::SUB, L::SUBB>(tbase, sub0); mma_commit(h1 ? wfree1 : wfree0); }
+                } else {
+                    if (c == 0) { issue_ts3<CFG::K(0), CFG::N(0)>(dd, wb, xl, sw + CFG::w_off(0)); mma_commit(done); }
+                    else if (c == 1) { issue_ts3<CFG::K(1), CFG::N(1)>(dd, xl, xl + 32, sw + CFG::w_off(1)); mma_commit(done); }
+                    else if (c == 2) { issue_ts3<CFG::N(1), CFG::K(1)>(dd, xl + 32, xl + 48, swt + CFG::w_off(1)); mma_commit(done); }
+                    else if (c == 4) { issue_ts3<CFG::N(0), CFG::K(0)>(dd, xl, xl + 32, swt + CFG::w_off(0)); mma_commit(done); }
+                    else if (c == 3 || c == 5) { issue_wgrad_half<L::SUB, L::SUBB>(tbase, sub0); mma_commit(h1 ? wfree1 : wfree0); }
+                    else { issue_wgrad_half<L::SUB, L::SUBB>(tbase + 64, sub0); mma_commit(h1 ? wfree1 : wfree0); }
+                }
+            }
+            __syncwarp();
+        }
     }
 }
 
@@ -240,11 +225,11 @@ __device__ __forceinline__ void wait_count(uint64_t *bar, uint32_t &seen, uint32
 
 // MODE 0: sigmoid head (grad [B][1][hw]); 1: plane parameters (grad [B][4][hw]); 2: fused LPG (grad_depth, upratio R)
 template <class CFG, int MODE, int R, int NWG>
-__global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(const __grid_constant__ FusedArgs fa)
+__global__ void __launch_bounds__(NWG *(kTile + 32), 1) chain_bwd_fused_kernel(const __grid_constant__ FusedArgs fa)
 {
     using L = FusedLayout<CFG, MODE, R, NWG>;
     constexpr int LAST = L::LAST, NW = L::NW, K0 = L::K0;
-    constexpr int NT = NWG * kTile + 32;
+    constexpr int NT = NWG * (kTile + 32);                         // NWG compute warpgroups + NWG issuer warps
     constexpr bool GPRE = MODE != 2 || R <= 2;
     const TcArgs &a = fa.a;
 
@@ -277,7 +262,7 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
     fence_before_sync();
     __syncthreads();
     fence_after_sync();
-    const uint32_t tbase = *slot;
+    const uint32_t tbase = (uint32_t)uniform((int)*slot);
     if (tid < kTile) {   // weight-gradient accumulators start at zero; every MMA into them accumulates
         uint32_t z[32];
 #pragma unroll
@@ -296,8 +281,7 @@ __global__ void __launch_bounds__(NWG *kTile + 32, 1) chain_bwd_fused_kernel(con
     const int stride = (int)gridDim.x * NWG;
 
     if (tid >= NWG * kTile) {
-        if (tid == NWG * kTile) fused_issuer<CFG, MODE, R, NWG>(sw, swt, smem_u32(stage), bars, tbase, ntiles);
-        __syncwarp();
+        fused_issuer<CFG, MODE, R, NWG>(uniform((tid - NWG * kTile) >> 5), sw, swt, smem_u32(stage), bars, tbase, ntiles);
     } else {
         const int g = tid / kTile, t = tid % kTile, lane = tid & 31, wj = t >> 5, half = wj >> 1;
         uint64_t *ready = bars + 6 * g, *done = ready + 1, *stg = ready + 2 + half;
@@ -655,7 +639,7 @@ static int launch_fused_cfg(const ChainParams &cp, const TcArgs &a, char *ws, in
     const long long ntiles = (a.npx + kTile - 1) / kTile;
     long long grid = (ntiles + NWG - 1) / NWG;
     if (grid > sms) grid = sms;
-    kern<<<(unsigned)grid, NWG * kTile + 32, L::smem_bytes, s>>>(fa);
+    kern<<<(unsigned)grid, NWG * (kTile + 32), L::smem_bytes, s>>>(fa);
     if (int e2 = check_launch("chain_bwd_fused")) return e2;
     if (cp.gW[0] != nullptr) {
         if (int e2 = launch_wreduce(cp, partials, (int)grid, total_w, s)) return e2;

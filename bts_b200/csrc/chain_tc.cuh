@@ -152,9 +152,12 @@ __device__ __forceinline__ void tc_run_layer(uint32_t wg_base, const float *sw, 
     wait_st();
     fence_before_sync();
     named_bar_sync(1 + wg, kTile);
-    if (t == 0) {
-        fence_after_sync();
-        tc_issue_layer<CFG, L>(wg_base, sw, bar);
+    if (uniform(t >> 5) == 0) {
+        if (elect_one()) {
+            fence_after_sync();
+            tc_issue_layer<CFG, L>(wg_base, sw, bar);
+        }
+        __syncwarp();
     }
     mbar_wait(bar, phase);
     phase ^= 1;
@@ -236,9 +239,12 @@ __device__ __forceinline__ void tc_run_chunk(uint32_t wg_base, const float *sw, 
     wait_st();
     fence_before_sync();
     named_bar_sync(1 + wg, kTile);
-    if (t == 0) {
-        fence_after_sync();
-        tc_issue_chunk<CFG, L, AW, KOFF, KC>(wg_base, sw, bar);
+    if (uniform(t >> 5) == 0) {
+        if (elect_one()) {
+            fence_after_sync();
+            tc_issue_chunk<CFG, L, AW, KOFF, KC>(wg_base, sw, bar);
+        }
+        __syncwarp();
     }
     mbar_wait(bar, phase);
     phase ^= 1;
@@ -250,7 +256,9 @@ template <class CFG, int L, int AW, int C0, int KC, bool SPILL>
 __device__ __forceinline__ void tc_epilogue_chunk(uint32_t lane_addr, float *act_gp, long long npx_pad, bool store)
 {
     float *dst = SPILL ? act_gp + (size_t)(BwdRows<CFG>::row(L + 1) + C0) * npx_pad : nullptr;
-#pragma unroll
+    // rolled: the wide chains run two to five tiles per warpgroup, so their straight-line code is fetched cold
+    // (instruction-cache misses were the top stall of the 8x8 stage's forward when this was unrolled)
+#pragma unroll 1
     for (int n0 = 0; n0 < KC; n0 += 16) {
         uint32_t r[16], lo[16];
         tmem_ld<16>(lane_addr + 2 * AW + C0 + n0, r);
@@ -303,7 +311,7 @@ __device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, f
     if constexpr (R == 8) {
         // two 512 B stores per output row and warp: lane L writes columns (L&1)*4..+3 of pixel 16*half + L/2
         const unsigned gp0 = gp - (unsigned)lane;
-#pragma unroll
+#pragma unroll 1
         for (int half = 0; half < 2; ++half) {
             const int src = half * 16 + (lane >> 1);
             const float m1 = __shfl_sync(0xffffffffu, n1, src), m2 = __shfl_sync(0xffffffffu, n2, src);
@@ -320,7 +328,7 @@ __device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, f
                 float n1u[4];
 #pragma unroll
                 for (int k = 0; k < 4; ++k) n1u[k] = __fmul_rn(m1, lpg_offset(q0 + k, 8));
-#pragma unroll
+#pragma unroll 2
                 for (int p = 0; p < 8; ++p) {
                     const float n2v = __fmul_rn(m2, lpg_offset(p, 8));
                     float4 o;

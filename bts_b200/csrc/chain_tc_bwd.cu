@@ -48,7 +48,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_bwd1_kernel(BwdArgs b
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + PACK);
     uint32_t *slot = reinterpret_cast<uint32_t *>(bars + NWG);
 
-    const int tid = threadIdx.x, wg = tid / kTile, t = tid % kTile;
+    const int tid = threadIdx.x, wg = uniform(tid / kTile), t = tid % kTile;
     tc_pack_to_smem<CFG>(a.W, sw, LAST, tid, NWG * kTile);
     fence_smem_to_async();
     if (tid < 32) tmem_alloc(slot, 512);
@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_bwd1_kernel(BwdArgs b
     fence_before_sync();
     __syncthreads();
     fence_after_sync();
-    const uint32_t tbase = *slot;
+    const uint32_t tbase = (uint32_t)uniform((int)*slot);
     const uint32_t wg_base = tbase + wg * COLS;
     const uint32_t lane_addr = wg_base + ((uint32_t)((t >> 5) * 32) << 16);
     uint64_t *bar = &bars[wg];
@@ -221,9 +221,12 @@ __device__ __forceinline__ void dgrad_layer(const BwdArgs &ba, uint32_t wg_base,
     wait_st();
     fence_before_sync();
     named_bar_sync(1 + wg, kTile);
-    if (t == 0) {
-        fence_after_sync();
-        tc_issue_dgrad<CFG, L, 0, KC>(wg_base, swt, bar);
+    if (uniform(t >> 5) == 0) {
+        if (elect_one()) {
+            fence_after_sync();
+            tc_issue_dgrad<CFG, L, 0, KC>(wg_base, swt, bar);
+        }
+        __syncwarp();
     }
     float av[16];
     if constexpr (L > 0) {                                        // first chunk of a_l travels under the MMAs
@@ -249,9 +252,12 @@ __device__ __forceinline__ void dgrad_layer(const BwdArgs &ba, uint32_t wg_base,
         wait_st();
         fence_before_sync();
         named_bar_sync(1 + wg, kTile);
-        if (t == 0) {
-            fence_after_sync();
-            tc_issue_dgrad<CFG, L, AW, AW>(wg_base, swt, bar);
+        if (uniform(t >> 5) == 0) {
+            if (elect_one()) {
+                fence_after_sync();
+                tc_issue_dgrad<CFG, L, AW, AW>(wg_base, swt, bar);
+            }
+            __syncwarp();
         }
         mbar_wait(bar, phase);
         phase ^= 1;
@@ -322,7 +328,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_dgrad_kernel(BwdArgs 
     float *stw = smem + IMG;
     uint64_t *bars = reinterpret_cast<uint64_t *>(stw + TAILW);
     uint32_t *slot = reinterpret_cast<uint32_t *>(bars + NWG);
-    const int tid = threadIdx.x, wg = tid / kTile, t = tid % kTile;
+    const int tid = threadIdx.x, wg = uniform(tid / kTile), t = tid % kTile;
     tc_pack_t_to_smem<CFG>(ba.a.W, swt, tid, NWG * kTile);
     if constexpr (TM >= 0) {
         constexpr int LAST = TM == 0 ? 1 : 3;
@@ -338,7 +344,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_dgrad_kernel(BwdArgs 
     fence_before_sync();
     __syncthreads();
     fence_after_sync();
-    const uint32_t tbase = *slot;
+    const uint32_t tbase = (uint32_t)uniform((int)*slot);
     const uint32_t wg_base = tbase + wg * COLS;
     const uint32_t lane_addr = wg_base + ((uint32_t)((t >> 5) * 32) << 16);
     uint64_t *bar = &bars[wg];
@@ -536,7 +542,7 @@ __global__ void __launch_bounds__(256, 1) chain_tc_wgrad_kernel(const __grid_con
             }
             fence_smem_to_async();
             __syncthreads();
-            if (tid == 0) {
+            if (uniform(tid >> 5) == 0 && elect_one()) {
                 fence_after_sync();
                 const uint32_t idesc = idesc_tf32(job.MA, job.NB, 0, 0);
                 const uint32_t d = tbase + job.tmem_col;

@@ -36,7 +36,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
     uint32_t *slot = reinterpret_cast<uint32_t *>(bars + NWG);
     float *xs_all = smem + PACK + (8 * NWG + 16 + 15) / 16 * 4;   // [NWG][D0][128] when PREFETCH (16-byte aligned)
 
-    const int tid = threadIdx.x, wg = tid / kTile, t = tid % kTile, lane = tid & 31;
+    const int tid = threadIdx.x, wg = uniform(tid / kTile), t = tid % kTile, lane = tid & 31;
     tc_pack_to_smem<CFG>(a.W, sw, LAST, tid, NWG * kTile);
     fence_smem_to_async();
     if (tid < 32) tmem_alloc(slot, 512);
@@ -47,7 +47,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
     fence_before_sync();
     __syncthreads();
     fence_after_sync();
-    const uint32_t tbase = *slot;
+    const uint32_t tbase = (uint32_t)uniform((int)*slot);
     const uint32_t wg_base = tbase + wg * COLS;
     const uint32_t lane_addr = wg_base + ((uint32_t)((t >> 5) * 32) << 16);
     uint64_t *bar = &bars[wg];

@@ -76,7 +76,7 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
     fence_before_sync();
     __syncthreads();
     fence_after_sync();
-    const uint32_t tbase = *slot_tmem;
+    const uint32_t tbase = (uint32_t)uniform((int)*slot_tmem);
     const uint32_t lane_addr = tbase + ((uint32_t)((warp & 3) * 32) << 16);   // warps 2..5 cover all four lane quarters
     if (warp >= 2) {
         uint32_t z[32];
@@ -115,27 +115,30 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
         }
         __syncwarp();
     } else if (warp == 1) {
-        if (lane == 0) {                                          // ---- MMA issuer
+        {                                                         // ---- MMA issuer (whole warp waits, one elected lane issues)
             long long it = 0;
             for (long long ck = blockIdx.x; ck < pl.nchunks; ck += gridDim.x) {
                 for (int j = 0; j < pl.njobs; ++j, ++it) {
                     const int s = (int)(it % kWtSlots);
                     mbar_wait(split + s, (uint32_t)((it / kWtSlots) & 1));
                     fence_after_sync();
-                    const WtJob &job = pl.jobs[j];
-                    const uint32_t base = slot0 + s * kWtSlotBytes;
-                    const uint32_t a_hi = base, a_lo = base + 16384u, b_hi = base + 32768u;
-                    const uint32_t d = tbase + job.tmem_col;
-                    const uint32_t id_cat = idesc_tf32(128, 2 * job.nb, 0, 0), id_hi = idesc_tf32(128, job.nb, 0, 0);
+                    if (elect_one()) {
+                        const WtJob &job = pl.jobs[j];
+                        const uint32_t base = slot0 + s * kWtSlotBytes;
+                        const uint32_t a_hi = base, a_lo = base + 16384u, b_hi = base + 32768u;
+                        const uint32_t d = tbase + job.tmem_col;
+                        const uint32_t id_cat = idesc_tf32(128, 2 * job.nb, 0, 0), id_hi = idesc_tf32(128, job.nb, 0, 0);
 #pragma unroll
-                    for (int ks = 0; ks < 4; ++ks) {
-                        mma_tf32_ss(d, smem_desc_sw128(a_hi + ks * 32), smem_desc_sw128(b_hi + ks * 32), id_cat, 1);
-                        mma_tf32_ss(d, smem_desc_sw128(a_lo + ks * 32), smem_desc_sw128(b_hi + ks * 32), id_hi, 1);
+                        for (int ks = 0; ks < 4; ++ks) {
+                            mma_tf32_ss(d, smem_desc_sw128(a_hi + ks * 32), smem_desc_sw128(b_hi + ks * 32), id_cat, 1);
+                            mma_tf32_ss(d, smem_desc_sw128(a_lo + ks * 32), smem_desc_sw128(b_hi + ks * 32), id_hi, 1);
+                        }
+                        mma_commit(empty + s);
                     }
-                    mma_commit(empty + s);
+                    __syncwarp();
                 }
             }
-            mma_commit(fin);
+            if (elect_one()) mma_commit(fin);
         }
         __syncwarp();
     } else {                                                      // ---- splitters

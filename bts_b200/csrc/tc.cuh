@@ -145,6 +145,18 @@ __device__ __forceinline__ void mma_commit(uint64_t *bar)
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
+// One lane of a converged warp (elect.sync): the compiler knows the guarded code runs on exactly one thread and
+// emits the warp-uniform tcgen05 instructions plainly. Behind a data-dependent `if (tid == k)` it has to wrap
+// every tcgen05.mma in an ELECT / BRA.U.ANY loop (~8 instructions and ~45 cycles per MMA, measured).
+__device__ __forceinline__ bool elect_one()
+{
+    uint32_t pred = 0, lane = 0;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync %1|p, 0xffffffff;\n\t@p mov.s32 %0, 1;\n\t}" : "+r"(pred), "+r"(lane));
+    return pred != 0;
+}
+// warp-uniform value the compiler can see as uniform
+__device__ __forceinline__ int uniform(int v) { return __shfl_sync(0xffffffffu, v, 0); }
+
 // ---------------------------------------------------------------------------------- descriptors
 // Shared-memory matrix descriptor, SWIZZLE_NONE. The operand is tiled in 8x(16 B) "core matrices",
 // each 128 contiguous bytes. For a K-major operand (the K elements of one row are contiguous):
