@@ -536,16 +536,16 @@ __device__ __forceinline__ float4 tf32_lo4(float4 v)
 template <class CFG>
 __device__ __forceinline__ void tc_pack_to_smem(const float *const *W, float *sw, int last, int tid, int nth)
 {
+    constexpr int PF = 8;   // loads in flight per thread: the packing is the kernel's prologue and pure L2 latency otherwise
 #pragma unroll
     for (int l = 0; l < CFG::NW; ++l) {
         const int K = CFG::K(l), N = CFG::N(l);
         float *hi = sw + CFG::w_off(l), *lo = hi + N * K;
         const float *w = W[l];
-        // four loads in flight per thread: the packing is the kernel's prologue and pure load latency otherwise
-        for (int u0 = tid; u0 < N * K / 4; u0 += 4 * nth) {
-            float4 v[4];
+        for (int u0 = tid; u0 < N * K / 4; u0 += PF * nth) {
+            float4 v[PF];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
+            for (int i = 0; i < PF; ++i) {
                 const int u = u0 + i * nth;
                 if (u < N * K / 4) {
                     const int n = (u / (2 * K)) * 8 + (u & 7), kq = (u >> 3) % (K / 4);
@@ -553,7 +553,7 @@ __device__ __forceinline__ void tc_pack_to_smem(const float *const *W, float *sw
                 }
             }
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
+            for (int i = 0; i < PF; ++i) {
                 const int u = u0 + i * nth;
                 if (u < N * K / 4) {
                     *reinterpret_cast<float4 *>(hi + 4 * u) = v[i];

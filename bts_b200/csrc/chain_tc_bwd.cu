@@ -228,11 +228,15 @@ __device__ __forceinline__ void dgrad_layer(const BwdArgs &ba, uint32_t wg_base,
         }
         __syncwarp();
     }
-    float av[16];
-    if constexpr (L > 0) {                                        // first chunk of a_l travels under the MMAs
+    float av[16], nx[16];
+    if constexpr (L > 0) {                                        // the first two chunks of a_l travel under the MMAs
         const float *act0 = ba.act + (size_t)BwdRows<CFG>::row(L) * npp + gp;
 #pragma unroll
         for (int j = 0; j < 16; ++j) av[j] = __ldcg(act0 + (size_t)j * npp);
+        if constexpr (NP > 16) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) nx[j] = __ldcg(act0 + (size_t)(16 + j) * npp);
+        }
     }
     mbar_wait(bar, phase);
     phase ^= 1;
@@ -278,14 +282,18 @@ __device__ __forceinline__ void dgrad_layer(const BwdArgs &ba, uint32_t wg_base,
     } else {
         const float *act = ba.act + (size_t)BwdRows<CFG>::row(L) * npp + gp;
         float *del = ba.del + (size_t)BwdRows<CFG>::row(L) * npp + gp;
-        // a_l chunks are fetched one chunk ahead of their use (the first one before the MMA wait)
-#pragma unroll
-        for (int n0 = 0; n0 < NP; n0 += 16) {
+        // a_l chunks are fetched TWO chunks ahead of their use (one chunk of processing is ~0.2 us, a DRAM round trip
+        // ~0.8 us, and there are only eight warps per SM to hide it). The first AW channels go back to TMEM in a ROLLED
+        // loop (these kernels run two to five tiles per warpgroup: straight-line code is fetched cold); the rest
+        // stay in `keep` for the second round and need compile-time indices.
+        constexpr int N1 = NP < AW ? NP : AW;
+#pragma unroll 1
+        for (int n0 = 0; n0 < N1; n0 += 16) {
             uint32_t r[16], lo[16];
-            float nx[16];
-            if (n0 + 16 < NP) {
+            float nx2[16];
+            if (n0 + 32 < NP) {
 #pragma unroll
-                for (int j = 0; j < 16; ++j) nx[j] = __ldcg(act + (size_t)(n0 + 16 + j) * npp);
+                for (int j = 0; j < 16; ++j) nx2[j] = __ldcg(act + (size_t)(n0 + 32 + j) * npp);
             }
             tmem_ld<16>(lane_addr + 2 * AW + n0, r);
             wait_ld();
@@ -293,20 +301,37 @@ __device__ __forceinline__ void dgrad_layer(const BwdArgs &ba, uint32_t wg_base,
             for (int j = 0; j < 16; ++j) {
                 const float v = __uint_as_float(r[j]) * elu_grad_from_out(av[j]);
                 del[(size_t)(n0 + j) * npp] = v;
-                if (n0 < AW) {
-                    r[j] = __float_as_uint(v);
-                    lo[j] = __float_as_uint(tf32_lo(v));
-                } else {
-                    keep[n0 - AW + j] = v;
-                }
+                r[j] = __float_as_uint(v);
+                lo[j] = __float_as_uint(tf32_lo(v));
             }
-            if (n0 < AW) {
-                tmem_st<16>(lane_addr + n0, r);
-                tmem_st<16>(lane_addr + AW + n0, lo);
-            }
-            if (n0 + 16 < NP) {
+            tmem_st<16>(lane_addr + n0, r);
+            tmem_st<16>(lane_addr + AW + n0, lo);
 #pragma unroll
-                for (int j = 0; j < 16; ++j) av[j] = nx[j];
+            for (int j = 0; j < 16; ++j) {
+                av[j] = nx[j];
+                nx[j] = nx2[j];
+            }
+        }
+#pragma unroll
+        for (int n0 = N1; n0 < NP; n0 += 16) {
+            uint32_t r[16];
+            float nx2[16];
+            if (n0 + 32 < NP) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) nx2[j] = __ldcg(act + (size_t)(n0 + 32 + j) * npp);
+            }
+            tmem_ld<16>(lane_addr + 2 * AW + n0, r);
+            wait_ld();
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const float v = __uint_as_float(r[j]) * elu_grad_from_out(av[j]);
+                del[(size_t)(n0 + j) * npp] = v;
+                keep[n0 - AW + j] = v;
+            }
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                av[j] = nx[j];
+                nx[j] = nx2[j];
             }
         }
     }

@@ -138,6 +138,13 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
     for (uint32_t spins = 0; !mbar_try_wait(bar, parity); ++spins)
         if (spins > (1u << 24)) __trap();
 }
+// Busy poll (no hardware suspend): for a dedicated issuer warp, where the response time to a hand-off is on the
+// critical path of every tile. (Measured: sleeping 200 ns between polls of the staged-operand barriers costs 8 %.)
+__device__ __forceinline__ void mbar_wait_spin(uint64_t *bar, uint32_t parity)
+{
+    for (uint32_t spins = 0; !mbar_test_wait(bar, parity); ++spins)
+        if (spins > (1u << 28)) __trap();
+}
 // Arrive on `bar` once every tcgen05.mma issued so far by this thread has completed.
 // (implies tcgen05.fence::before_thread_sync)
 __device__ __forceinline__ void mma_commit(uint64_t *bar)
