@@ -29,8 +29,9 @@ constexpr int kBLo = 32 * 128;                         // byte offset of the rem
 
 struct FusedArgs {
     TcArgs a;
-    float *partials;        // [gridDim.x][total_w]
+    float *partials;        // [gridDim.x][total_w] (deterministic route: fixed-order reduction kernel afterwards)
     int total_w;
+    int atomic_w;           // 1: every CTA adds its partial sums to a.gw[] with red.global.add (no reduction launch)
 };
 
 // D[128 x N](TMEM, col d) = A[128 x K](TMEM; hi at a_hi, lo at a_lo) * B[N x K]^T (smem image at w: hi | lo)
@@ -310,17 +311,43 @@ __global__ void __launch_bounds__(NWG *(kTile + 32), 1) chain_bwd_fused_kernel(c
         float *xs_wg = xs_all + (size_t)g * (K0 + 4) * kTile;    // [channel][pixel] of the staged tile
         float *xs = xs_wg + t;                                    // this thread's pixel column
         float *gs = xs_wg + K0 * kTile + t * 4;                   // this pixel's gradient words
+        // (image, pixel) of this thread's own pixel and of the 4-pixel group it copies, for the tile the NEXT prefetch
+        // fetches. They advance by the same number of pixels every iteration, so the two divisions by hw per
+        // position and tile become one division per kernel (dq, dr) and an add with a wrap-around.
+        struct PixPos {
+            unsigned g;
+            int b, p;
+        };
+        const unsigned step = (unsigned)stride * kTile;
+        const unsigned dq = step / hw, dr = step - dq * hw;
+        auto pos_at = [&](unsigned g0) {
+            PixPos s;
+            s.g = g0;
+            s.b = g0 < npx ? (int)(g0 / hw) : 0;
+            s.p = g0 < npx ? (int)(g0 - (unsigned)s.b * hw) : 0;
+            return s;
+        };
+        auto pos_advance = [&](PixPos &s) {
+            s.g += step;
+            s.b += (int)dq;
+            s.p += (int)dr;
+            if ((unsigned)s.p >= hw) {
+                s.p -= (int)hw;
+                ++s.b;
+            }
+        };
+        const int tile0 = (int)blockIdx.x * NWG + g;
+        PixPos own = pos_at((unsigned)tile0 * kTile + t), quad = pos_at((unsigned)tile0 * kTile + 4 * (t & 31));
         auto prefetch = [&](int tl) {
-            const unsigned gp = (unsigned)tl * kTile + t;
+            const unsigned gp = own.g;
             const bool ok = tl < ntiles && gp < npx;
-            [[maybe_unused]] const int b = ok ? (int)(gp / hw) : 0;
-            [[maybe_unused]] const int p = ok ? (int)(gp - (unsigned)b * hw) : 0;
+            [[maybe_unused]] const int b = ok ? own.b : 0;
+            [[maybe_unused]] const int p = ok ? own.p : 0;
             {                                                     // 128-bit copies (host checks x_vec16), see chain_tc_fwd.cu
                 const int q = t & 31, cw = t >> 5;
-                const unsigned g0 = (unsigned)tl * kTile + 4 * q;
-                const bool okv = tl < ntiles && g0 < npx;
-                const int bn = okv ? (int)(g0 / hw) : 0;
-                const int pn = okv ? (int)(g0 - (unsigned)bn * hw) : 0;
+                const bool okv = tl < ntiles && quad.g < npx;
+                const int bn = okv ? quad.b : 0;
+                const int pn = okv ? quad.p : 0;
                 const float *xq = a.x + ((size_t)bn * K0 + cw) * a.hw + pn;
                 const uint32_t dst = smem_u32(xs_wg + cw * kTile + 4 * q);
 #pragma unroll
@@ -347,13 +374,15 @@ __global__ void __launch_bounds__(NWG *(kTile + 32), 1) chain_bwd_fused_kernel(c
             cp_async_commit();
         };
 
-        int tile = (int)blockIdx.x * NWG + g;
+        int tile = tile0;
         prefetch(tile);
         for (; tile < ntiles; tile += stride) {
-            const unsigned gp = (unsigned)tile * kTile + t;
+            const unsigned gp = own.g;                            // == tile * kTile + t
             const bool valid = gp < npx;
-            const int b = valid ? (int)(gp / hw) : 0;
-            const int p = valid ? (int)(gp - (unsigned)b * hw) : 0;
+            const int b = valid ? own.b : 0;
+            const int p = valid ? own.p : 0;
+            pos_advance(own);                                     // own / quad now describe tile + stride
+            pos_advance(quad);
             // ---- x -> (hi, lo) -> TMEM A operand of layer 0; then the next tile's loads take off
             cp_async_wait_all();
             named_bar_sync(1 + g, kTile);                         // the tile was copied by all threads of the warpgroup
@@ -589,7 +618,7 @@ __global__ void __launch_bounds__(NWG *(kTile + 32), 1) chain_bwd_fused_kernel(c
     }
     fence_before_sync();
     __syncthreads();
-    if (fa.partials != nullptr) {
+    if (fa.partials != nullptr || fa.atomic_w) {
         float *part = fa.partials + (size_t)blockIdx.x * fa.total_w;
         // layer l of the chain: (job, first row, first column, K = inputs, N = outputs)
         constexpr int NL = NW + 2;
@@ -602,10 +631,16 @@ __global__ void __launch_bounds__(NWG *(kTile + 32), 1) chain_bwd_fused_kernel(c
             const int col0 = t_l <= 0 ? 0 : (t_l == 1 ? 16 : 24);
             const int K = t_l < 0 ? K0 : (t_l == 0 ? 32 : (t_l == 1 ? kTailIn : kTailMid));
             const int N = t_l < 0 ? 32 : (t_l == 0 ? kTailIn : (t_l == 1 ? kTailMid : LAST));
-            for (int e = tid; e < K * N; e += NT) {
+            // atomic route: CTAs start at different elements so that they do not all hit the same address at once
+            const int shift = fa.atomic_w ? (int)((blockIdx.x * 67u) % (unsigned)(K * N)) : 0;
+            for (int i = tid; i < K * N; i += NT) {
+                int e = i + shift;
+                if (e >= K * N) e -= K * N;
                 const int o = e / K, c = e - o * K;
                 const float *s = scratch + (job * kTile + row0 + c) * SP + col0 + o;
-                part[off + e] = s[0] + s[L::ALO_ROWS * SP];
+                const float v = s[0] + s[L::ALO_ROWS * SP];
+                if (fa.atomic_w) atomicAdd(a.gw[l] + e, v);
+                else part[off + e] = v;
             }
             off += K * N;
         }
@@ -631,7 +666,13 @@ static int launch_fused_cfg(const ChainParams &cp, const TcArgs &a, char *ws, in
     FusedArgs fa;
     fa.a = a;
     tc_set_weights(fa.a, cp);
-    fa.partials = cp.gW[0] != nullptr ? partials : nullptr;
+    // weight gradients: by default every CTA adds its partial sums to grad_W with fp32 atomics (grad_W is an
+    // accumulate target by contract); BTS_DETERMINISTIC=1 keeps per-CTA partials + the fixed-order reduction kernel
+    static const bool deterministic = getenv("BTS_DETERMINISTIC") != nullptr && atoi(getenv("BTS_DETERMINISTIC")) != 0;
+    const bool want_w = cp.gW[0] != nullptr;
+    fa.atomic_w = want_w && !deterministic ? 1 : 0;
+    fa.partials = want_w && deterministic ? partials : nullptr;
+    for (int l = 0; l < BTS_MAX_LAYERS; ++l) fa.a.gw[l] = l < cp.n_layers ? cp.gW[l] : nullptr;
     fa.total_w = total_w;
     auto kern = chain_bwd_fused_kernel<CFG, MODE, R, NWG>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::smem_bytes);
@@ -641,7 +682,7 @@ static int launch_fused_cfg(const ChainParams &cp, const TcArgs &a, char *ws, in
     if (grid > sms) grid = sms;
     kern<<<(unsigned)grid, NWG * (kTile + 32), L::smem_bytes, s>>>(fa);
     if (int e2 = check_launch("chain_bwd_fused")) return e2;
-    if (cp.gW[0] != nullptr) {
+    if (fa.partials != nullptr) {
         if (int e2 = launch_wreduce(cp, partials, (int)grid, total_w, s)) return e2;
     }
     return BTS_OK;
@@ -668,9 +709,12 @@ int launch_chain_bwd_fused(const ChainParams &cp, const TcArgs &a, int mode, int
 {
     char *w = static_cast<char *>(ws);
     if (cfg_matches<Cfg32_16>(cp)) {
-        static const int head_nwg = getenv("BTS_HEAD_NWG") ? atoi(getenv("BTS_HEAD_NWG")) : 3;   // tuning hook
-        if (head_nwg == 2) return dispatch_fused<Cfg32_16, 2>(cp, a, mode, r, w, sms, s);
-        return dispatch_fused<Cfg32_16, 3>(cp, a, mode, r, w, sms, s);
+        // two warpgroups with private staging buffers per warp pair (168 registers, no spills, no turn-taking between
+        // the pairs) beat three warpgroups that share staging (128 registers, ~200 bytes of spills): 242 vs 248-256 us
+        // at nyu_b8. BTS_HEAD_NWG=3 selects the other variant for tuning.
+        static const int head_nwg = getenv("BTS_HEAD_NWG") ? atoi(getenv("BTS_HEAD_NWG")) : 2;
+        if (head_nwg == 3) return dispatch_fused<Cfg32_16, 3>(cp, a, mode, r, w, sms, s);
+        return dispatch_fused<Cfg32_16, 2>(cp, a, mode, r, w, sms, s);
     }
     if (cfg_matches<Cfg64_32>(cp)) return dispatch_fused<Cfg64_32, 2>(cp, a, mode, r, w, sms, s);
     return set_error(BTS_ERR_UNSUPPORTED, "chain not covered by the fused backward");

@@ -115,16 +115,26 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
                     tmem_st<16>(lane_addr + AW + c0, lo);
                 }
             } else {
-                // 32 independent coalesced loads in flight per thread
+                // up to 64 independent coalesced loads in flight per thread (a whole K round of the 128-channel chains:
+                // with eight warps per SM every DRAM round trip saved is ~1 us of the tile)
+                constexpr int LB = KC0 >= 64 ? 64 : 32;
 #pragma unroll 1
-                for (int c0 = 0; c0 < KC0; c0 += 32) {
-                    uint32_t hi[32], lo[32];
+                for (int c0 = 0; c0 < KC0; c0 += LB) {
+                    uint32_t hi[LB];
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) hi[j] = valid ? __float_as_uint(__ldg(xp + (size_t)(C0 + c0 + j) * a.hw)) : 0u;
+                    for (int j = 0; j < LB; ++j) hi[j] = valid ? __float_as_uint(__ldg(xp + (size_t)(C0 + c0 + j) * a.hw)) : 0u;
 #pragma unroll
-                    for (int j = 0; j < 32; j += 2) tf32_lo2(__uint_as_float(hi[j]), __uint_as_float(hi[j + 1]), lo[j], lo[j + 1]);
-                    tmem_st<32>(lane_addr + c0, hi);
-                    tmem_st<32>(lane_addr + AW + c0, lo);
+                    for (int h = 0; h < LB; h += 32) {
+                        uint32_t h32[32], lo[32];
+#pragma unroll
+                        for (int j = 0; j < 32; j += 2) {
+                            h32[j] = hi[h + j];
+                            h32[j + 1] = hi[h + j + 1];
+                            tf32_lo2(__uint_as_float(hi[h + j]), __uint_as_float(hi[h + j + 1]), lo[j], lo[j + 1]);
+                        }
+                        tmem_st<32>(lane_addr + c0 + h, h32);
+                        tmem_st<32>(lane_addr + AW + c0 + h, lo);
+                    }
                 }
             }
         };

@@ -95,7 +95,9 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
         if (lane == 0) {                                          // ---- producer
             long long it = 0;
             for (long long ck = blockIdx.x; ck < pl.nchunks; ck += gridDim.x) {
-                const long long gp = ck * 32;
+                // chunks are visited LAST to FIRST: the dgrad kernel has just written the delta rows (and read the
+                // activation rows) in ascending pixel order, so the highest pixels are what the L2 still holds
+                const long long gp = (pl.nchunks - 1 - ck) * 32;
                 const int b = (int)(gp / pl.hw_pad), p0 = (int)(gp - (long long)b * pl.hw_pad);
                 for (int j = 0; j < pl.njobs; ++j, ++it) {
                     const int s = (int)(it % kWtSlots);
