@@ -535,7 +535,12 @@ __global__ void __launch_bounds__(NWG *(kTile + 32), 1) chain_bwd_fused_kernel(c
                     }
                 }
             };
-            if constexpr (NW == 1) {
+            if constexpr (NW == 1 && L::PRIV) {
+                // private staging buffers: nobody takes turns, so every warp stages first and the dgrad MMAs
+                // (issued when the last warp arrived above) complete under the staging stores
+                stage_tail();
+                gradx_epilogue();
+            } else if constexpr (NW == 1) {
 #pragma unroll 1
                 for (int ph = 0; ph < 2; ++ph) {                  // pair 0 stages first, pair 1 second
                     if (ph == half) stage_tail();
