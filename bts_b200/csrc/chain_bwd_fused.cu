@@ -439,7 +439,7 @@ __global__ void __launch_bounds__(NWG *(kTile + 32), 1) chain_bwd_fused_kernel(c
 #pragma unroll
                 for (int j = 0; j < 16; ++j) a16[j] = elu_fast(__uint_as_float(r[j]));
             }
-            tail_forward<LAST, NW == 1>(tw, a16, a8, z);
+            tail_forward<LAST, NW == 1, !L::PRIV>(tw, a16, a8, z);   // private staging = 168 registers: let the weight loads float
             // ---- upstream gradient -> dz
             float dz[3] = {0.f, 0.f, 0.f};
             if constexpr (MODE == 0) {

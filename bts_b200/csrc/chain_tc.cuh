@@ -152,7 +152,7 @@ __device__ __forceinline__ void tc_run_layer(uint32_t wg_base, const float *sw, 
     wait_st();
     fence_before_sync();
     named_bar_sync(1 + wg, kTile);
-    if (uniform(t >> 5) == 0) {
+    if (t == 0) {                                                 // t: warp index inside the warpgroup, made warp-uniform once by the kernel
         if (elect_one()) {
             fence_after_sync();
             tc_issue_layer<CFG, L>(wg_base, sw, bar);
@@ -239,7 +239,7 @@ __device__ __forceinline__ void tc_run_chunk(uint32_t wg_base, const float *sw, 
     wait_st();
     fence_before_sync();
     named_bar_sync(1 + wg, kTile);
-    if (uniform(t >> 5) == 0) {
+    if (t == 0) {                                                 // t: warp index inside the warpgroup, made warp-uniform once by the kernel
         if (elect_one()) {
             fence_after_sync();
             tc_issue_chunk<CFG, L, AW, KOFF, KC>(wg_base, sw, bar);
@@ -448,7 +448,7 @@ __device__ __forceinline__ void tail_logits(const float *w5, const float (&a8)[k
 // ---- the 16 -> 8 -> (3|1) tail on registers; weights broadcast from shared memory
 // PACKED = false keeps scalar FMAs: the packed operands cost 16 more live registers, which the 2 x 2 stage's
 // one-pass backward (168-register cap) pays for in spills.
-template <int LAST, bool PACKED = true>
+template <int LAST, bool PACKED = true, bool FENCE = true>
 __device__ __forceinline__ void tail_forward(const float *tw, const float (&a16)[kTailIn], float (&a8)[kTailMid],
                                              float (&z)[LAST])
 {
@@ -481,13 +481,13 @@ __device__ __forceinline__ void tail_forward(const float *tw, const float (&a16)
             s = fma2(w4.y, a2[c / 2 + 1], s);
         }
         a8[o] = elu_fast(hsum2(s));
-        asm volatile("" ::: "memory");   // keep the weight loads of later rows from being hoisted (register pressure)
+        if constexpr (FENCE) asm volatile("" ::: "memory");   // keep the weight loads of later rows from being hoisted (register pressure)
     }
     tail_logits<LAST>(tw + kTailMid * kTailIn, a8, z);
 }
 
 // dl16 = W4^T d8 (16 <- 8) with packed FMAs: channel pairs (c, c+1) share an accumulator register pair
-template <bool PACKED = true>
+template <bool PACKED = true, bool FENCE = true>
 __device__ __forceinline__ void tail_dgrad16(const float *tw, const float (&d8)[kTailMid], float (&dl16)[kTailIn])
 {
     if constexpr (!PACKED) {
@@ -517,7 +517,7 @@ __device__ __forceinline__ void tail_dgrad16(const float *tw, const float (&d8)[
             acc[c / 2] = fma2(w4.x, d2, acc[c / 2]);
             acc[c / 2 + 1] = fma2(w4.y, d2, acc[c / 2 + 1]);
         }
-        asm volatile("" ::: "memory");   // bound the hoisting of weight loads
+        if constexpr (FENCE) asm volatile("" ::: "memory");   // bound the hoisting of weight loads
     }
 #pragma unroll
     for (int c = 0; c < kTailIn; c += 2) unpack2(acc[c / 2], dl16[c], dl16[c + 1]);

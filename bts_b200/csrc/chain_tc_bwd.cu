@@ -49,6 +49,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_bwd1_kernel(BwdArgs b
     uint32_t *slot = reinterpret_cast<uint32_t *>(bars + NWG);
 
     const int tid = threadIdx.x, wg = uniform(tid / kTile), t = tid % kTile;
+    const int lt = uniform(t >> 5);                               // warp index inside the warpgroup; warp 0 issues the MMAs
     tc_pack_to_smem<CFG>(a.W, sw, LAST, tid, NWG * kTile);
     fence_smem_to_async();
     if (tid < 32) tmem_alloc(slot, 512);
@@ -94,13 +95,13 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_bwd1_kernel(BwdArgs b
         };
         load_x(std::integral_constant<int, 0>{});
         if constexpr (D0 > KC0) {
-            tc_run_chunk<CFG, 0, AW, 0, KC0>(wg_base, sw, bar, phase, wg, t);
+            tc_run_chunk<CFG, 0, AW, 0, KC0>(wg_base, sw, bar, phase, wg, lt);
             load_x(std::integral_constant<int, KC0>{});
         }
-        tc_run_chunk<CFG, 0, AW, D0 - KC0, KC0>(wg_base, sw, bar, phase, wg, t);
-        if constexpr (CFG::NW > 1) tc_layer_from_d<CFG, 1, AW, true>(wg_base, lane_addr, sw, bar, phase, wg, t, act_gp, npp, true);
-        if constexpr (CFG::NW > 2) tc_layer_from_d<CFG, 2, AW, true>(wg_base, lane_addr, sw, bar, phase, wg, t, act_gp, npp, true);
-        if constexpr (CFG::NW > 3) tc_layer_from_d<CFG, 3, AW, true>(wg_base, lane_addr, sw, bar, phase, wg, t, act_gp, npp, true);
+        tc_run_chunk<CFG, 0, AW, D0 - KC0, KC0>(wg_base, sw, bar, phase, wg, lt);
+        if constexpr (CFG::NW > 1) tc_layer_from_d<CFG, 1, AW, true>(wg_base, lane_addr, sw, bar, phase, wg, lt, act_gp, npp, true);
+        if constexpr (CFG::NW > 2) tc_layer_from_d<CFG, 2, AW, true>(wg_base, lane_addr, sw, bar, phase, wg, lt, act_gp, npp, true);
+        if constexpr (CFG::NW > 3) tc_layer_from_d<CFG, 3, AW, true>(wg_base, lane_addr, sw, bar, phase, wg, lt, act_gp, npp, true);
         float a16[kTailIn], a8[kTailMid], z[LAST];
         {
             uint32_t r[16];
@@ -221,7 +222,7 @@ __device__ __forceinline__ void dgrad_layer(const BwdArgs &ba, uint32_t wg_base,
     wait_st();
     fence_before_sync();
     named_bar_sync(1 + wg, kTile);
-    if (uniform(t >> 5) == 0) {
+    if (t == 0) {                                                 // t: warp index inside the warpgroup (warp-uniform)
         if (elect_one()) {
             fence_after_sync();
             tc_issue_dgrad<CFG, L, 0, KC>(wg_base, swt, bar);
@@ -256,7 +257,7 @@ __device__ __forceinline__ void dgrad_layer(const BwdArgs &ba, uint32_t wg_base,
         wait_st();
         fence_before_sync();
         named_bar_sync(1 + wg, kTile);
-        if (uniform(t >> 5) == 0) {
+        if (t == 0) {                                                 // t: warp index inside the warpgroup (warp-uniform)
             if (elect_one()) {
                 fence_after_sync();
                 tc_issue_dgrad<CFG, L, AW, AW>(wg_base, swt, bar);
@@ -354,6 +355,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_dgrad_kernel(BwdArgs 
     uint64_t *bars = reinterpret_cast<uint64_t *>(stw + TAILW);
     uint32_t *slot = reinterpret_cast<uint32_t *>(bars + NWG);
     const int tid = threadIdx.x, wg = uniform(tid / kTile), t = tid % kTile;
+    const int lt = uniform(t >> 5);                               // warp index inside the warpgroup; warp 0 issues the MMAs
     tc_pack_t_to_smem<CFG>(ba.a.W, swt, tid, NWG * kTile);
     if constexpr (TM >= 0) {
         constexpr int LAST = TM == 0 ? 1 : 3;
@@ -448,10 +450,10 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_dgrad_kernel(BwdArgs 
             tmem_st<16>(lane_addr + AW, lo);
         }
         float keep[64];
-        if constexpr (CFG::NW > 3) dgrad_layer<CFG, 3>(ba, wg_base, lane_addr, swt, bar, phase, wg, t, gp, valid, b, p, keep);
-        if constexpr (CFG::NW > 2) dgrad_layer<CFG, 2>(ba, wg_base, lane_addr, swt, bar, phase, wg, t, gp, valid, b, p, keep);
-        if constexpr (CFG::NW > 1) dgrad_layer<CFG, 1>(ba, wg_base, lane_addr, swt, bar, phase, wg, t, gp, valid, b, p, keep);
-        if (ba.a.grad_x != nullptr) dgrad_layer<CFG, 0>(ba, wg_base, lane_addr, swt, bar, phase, wg, t, gp, valid, b, p, keep);
+        if constexpr (CFG::NW > 3) dgrad_layer<CFG, 3>(ba, wg_base, lane_addr, swt, bar, phase, wg, lt, gp, valid, b, p, keep);
+        if constexpr (CFG::NW > 2) dgrad_layer<CFG, 2>(ba, wg_base, lane_addr, swt, bar, phase, wg, lt, gp, valid, b, p, keep);
+        if constexpr (CFG::NW > 1) dgrad_layer<CFG, 1>(ba, wg_base, lane_addr, swt, bar, phase, wg, lt, gp, valid, b, p, keep);
+        if (ba.a.grad_x != nullptr) dgrad_layer<CFG, 0>(ba, wg_base, lane_addr, swt, bar, phase, wg, lt, gp, valid, b, p, keep);
     }
     fence_before_sync();
     __syncthreads();

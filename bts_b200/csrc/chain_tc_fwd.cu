@@ -37,6 +37,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
     float *xs_all = smem + PACK + (8 * NWG + 16 + 15) / 16 * 4;   // [NWG][D0][128] when PREFETCH (16-byte aligned)
 
     const int tid = threadIdx.x, wg = uniform(tid / kTile), t = tid % kTile, lane = tid & 31;
+    const int lt = uniform(t >> 5);                               // warp index inside the warpgroup; warp 0 issues the MMAs
     tc_pack_to_smem<CFG>(a.W, sw, LAST, tid, NWG * kTile);
     fence_smem_to_async();
     if (tid < 32) tmem_alloc(slot, 512);
@@ -72,24 +73,52 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
         if constexpr (WARP_PRIVATE) __syncwarp();
         else named_bar_sync(1 + wg, kTile);
     };
-    auto prefetch = [&](int tl) {
-        const int q = WARP_PRIVATE ? (((t >> 5) << 3) | (lane & 7)) : (t & 31), cw = WARP_PRIVATE ? (lane >> 3) : (t >> 5);
-        const unsigned g0 = (unsigned)tl * kTile + 4 * q;
-        const bool ok = tl < ntiles && g0 < npx;
-        const int bn = ok ? (int)(g0 / hw) : 0;
-        const int pn = ok ? (int)(g0 - (unsigned)bn * hw) : 0;
+    // (image, pixel) of this thread's own pixel and of the 4-pixel group it copies, advanced by the same number of
+    // pixels every iteration: one division per kernel (dq, dr) instead of two per position and tile
+    struct PixPos {
+        unsigned g;
+        int b, p;
+    };
+    const unsigned step = (unsigned)stride * kTile;
+    const unsigned dq = step / hw, dr = step - dq * hw;
+    auto pos_at = [&](unsigned g0) {
+        PixPos s;
+        s.g = g0;
+        s.b = g0 < npx ? (int)(g0 / hw) : 0;
+        s.p = g0 < npx ? (int)(g0 - (unsigned)s.b * hw) : 0;
+        return s;
+    };
+    auto pos_advance = [&](PixPos &s) {
+        s.g += step;
+        s.b += (int)dq;
+        s.p += (int)dr;
+        if ((unsigned)s.p >= hw) {
+            s.p -= (int)hw;
+            ++s.b;
+        }
+    };
+    const int tile0 = (int)blockIdx.x * NWG + wg;
+    const int pq = WARP_PRIVATE ? (((t >> 5) << 3) | (lane & 7)) : (t & 31);
+    PixPos own = pos_at((unsigned)tile0 * kTile + t), quad = pos_at((unsigned)tile0 * kTile + 4 * pq);
+    auto prefetch = [&](int tl) {                                 // fetches the tile `quad` points at
+        const int q = pq, cw = WARP_PRIVATE ? (lane >> 3) : (t >> 5);
+        const bool ok = tl < ntiles && quad.g < npx;
+        const int bn = ok ? quad.b : 0;
+        const int pn = ok ? quad.p : 0;
         const float *xq = a.x + ((size_t)bn * D0 + cw) * a.hw + pn;
         const uint32_t dst = smem_u32(xs_wg + cw * kTile + 4 * q);
 #pragma unroll
         for (int i = 0; i < D0 / 4; ++i) cp_async16(dst + i * 4 * kTile * 4, xq + (size_t)i * 4 * a.hw, ok);
         cp_async_commit();
     };
-    if constexpr (PREFETCH) prefetch((int)blockIdx.x * NWG + wg);
-    for (int tile = (int)blockIdx.x * NWG + wg; tile < ntiles; tile += stride) {
-        const unsigned gp = (unsigned)tile * kTile + t;
+    if constexpr (PREFETCH) prefetch(tile0);
+    for (int tile = tile0; tile < ntiles; tile += stride) {
+        const unsigned gp = own.g;                                // == tile * kTile + t
         const bool valid = gp < npx;
-        const int b = valid ? (int)(gp / hw) : 0;
-        const int p = valid ? (int)(gp - (unsigned)b * hw) : 0;
+        const int b = valid ? own.b : 0;
+        const int p = valid ? own.p : 0;
+        pos_advance(own);
+        if constexpr (PREFETCH) pos_advance(quad);                // now the tile the next prefetch fetches
         const float *xp = a.x + (size_t)b * D0 * a.hw + p;
         bool stash = false;
         float *act_gp = nullptr;
@@ -144,18 +173,18 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
         }
         load_x(std::integral_constant<int, 0>{});
         if constexpr (D0 > KC0) {
-            tc_run_chunk<CFG, 0, AW, 0, KC0>(wg_base, sw, bar, phase, wg, t);
+            tc_run_chunk<CFG, 0, AW, 0, KC0>(wg_base, sw, bar, phase, wg, lt);
             load_x(std::integral_constant<int, KC0>{});
         }
         if constexpr (PREFETCH) {
             tile_sync();                                          // the staged tile has been read by everyone who shares it
             prefetch(tile + stride);
         }
-        tc_run_chunk<CFG, 0, AW, D0 - KC0, KC0>(wg_base, sw, bar, phase, wg, t);
+        tc_run_chunk<CFG, 0, AW, D0 - KC0, KC0>(wg_base, sw, bar, phase, wg, lt);
         // wide layers
-        if constexpr (CFG::NW > 1) tc_layer_from_d<CFG, 1, AW, SPILL>(wg_base, lane_addr, sw, bar, phase, wg, t, act_gp, a.stash_npp, stash);
-        if constexpr (CFG::NW > 2) tc_layer_from_d<CFG, 2, AW, SPILL>(wg_base, lane_addr, sw, bar, phase, wg, t, act_gp, a.stash_npp, stash);
-        if constexpr (CFG::NW > 3) tc_layer_from_d<CFG, 3, AW, SPILL>(wg_base, lane_addr, sw, bar, phase, wg, t, act_gp, a.stash_npp, stash);
+        if constexpr (CFG::NW > 1) tc_layer_from_d<CFG, 1, AW, SPILL>(wg_base, lane_addr, sw, bar, phase, wg, lt, act_gp, a.stash_npp, stash);
+        if constexpr (CFG::NW > 2) tc_layer_from_d<CFG, 2, AW, SPILL>(wg_base, lane_addr, sw, bar, phase, wg, lt, act_gp, a.stash_npp, stash);
+        if constexpr (CFG::NW > 3) tc_layer_from_d<CFG, 3, AW, SPILL>(wg_base, lane_addr, sw, bar, phase, wg, lt, act_gp, a.stash_npp, stash);
         float a16[kTailIn], a8[kTailMid], z[LAST];
         {
             uint32_t r[16];
