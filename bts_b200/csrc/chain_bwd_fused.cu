@@ -481,7 +481,7 @@ __global__ void __launch_bounds__(NWG *(kTile + 32), 1) chain_bwd_fused_kernel(c
                 for (int j = 0; j < LAST; ++j) s = fmaf(w5[j * kTailMid + o], dz[j], s);
                 d8[o] = s * elu_grad_from_out(a8[o]);
             }
-            tail_dgrad16<NW == 1>(tw, d8, dl16);
+            tail_dgrad16<NW == 1, L::PRIV ? 4 : 1>(tw, d8, dl16);
             {
                 uint32_t hi[16], lo[16];
 #pragma unroll

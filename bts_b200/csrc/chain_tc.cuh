@@ -487,7 +487,7 @@ __device__ __forceinline__ void tail_forward(const float *tw, const float (&a16)
 }
 
 // dl16 = W4^T d8 (16 <- 8) with packed FMAs: channel pairs (c, c+1) share an accumulator register pair
-template <bool PACKED = true, bool FENCE = true>
+template <bool PACKED = true, int FENCE = 1>   // FENCE: scheduling fence after every FENCE-th row of W4 (0 = none)
 __device__ __forceinline__ void tail_dgrad16(const float *tw, const float (&d8)[kTailMid], float (&dl16)[kTailIn])
 {
     if constexpr (!PACKED) {
@@ -517,7 +517,9 @@ __device__ __forceinline__ void tail_dgrad16(const float *tw, const float (&d8)[
             acc[c / 2] = fma2(w4.x, d2, acc[c / 2]);
             acc[c / 2 + 1] = fma2(w4.y, d2, acc[c / 2 + 1]);
         }
-        if constexpr (FENCE) asm volatile("" ::: "memory");   // bound the hoisting of weight loads
+        if constexpr (FENCE > 0) {
+            if ((o + 1) % FENCE == 0) asm volatile("" ::: "memory");   // bound the hoisting of weight loads
+        }
     }
 #pragma unroll
     for (int c = 0; c < kTailIn; c += 2) unpack2(acc[c / 2], dl16[c], dl16[c + 1]);

@@ -429,7 +429,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_dgrad_kernel(BwdArgs 
                 for (int j = 0; j < LAST; ++j) sm = fmaf(w5[j * kTailMid + o], dz[j], sm);
                 d8[o] = sm * elu_grad_from_out(a8[o]);
             }
-            tail_dgrad16(tw, d8, d16);
+            tail_dgrad16<true, 0>(tw, d8, d16);
             float *del_gp = ba.del + gp;
             float *dz_dst = del_gp + (size_t)BwdRows<CFG>::rowz() * npp;
 #pragma unroll

@@ -193,7 +193,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
 #pragma unroll
             for (int j = 0; j < 16; ++j) a16[j] = elu_fast(__uint_as_float(r[j]));
         }
-        tail_forward<LAST>(tw, a16, a8, z);
+        tail_forward<LAST, true, false>(tw, a16, a8, z);           // no scheduling fences: the weight loads float above the FMAs
         if constexpr (kStashCfg<CFG>) {
             if (stash) {
                 float *d16 = act_gp + (size_t)BwdRows<CFG>::row(CFG::NW) * a.stash_npp;
