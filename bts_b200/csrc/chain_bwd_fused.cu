@@ -27,6 +27,15 @@ namespace bts {
 
 constexpr int kBLo = 32 * 128;                         // byte offset of the remainder rows in the delta image
 
+// MMA issue: 1 = inline, by the first warp of the warpgroup / warp pair that hands the operands over (split hardware
+// barriers: the other warps bar.arrive and go on, the issuing warp bar.syncs) -- no issuer warps, so the CTA is
+// NWG x 128 threads (255 registers at two warpgroups) and nobody polls; 0 = one dedicated issuer warp per warpgroup.
+#ifndef BTS_FUSED_INLINE_ISSUE
+#define BTS_FUSED_INLINE_ISSUE 1
+#endif
+constexpr bool kInlineIssue = BTS_FUSED_INLINE_ISSUE != 0;
+constexpr int fused_threads(int nwg) { return nwg * (kTile + (kInlineIssue ? 0 : 32)); }
+
 struct FusedArgs {
     TcArgs a;
     float *partials;        // [gridDim.x][total_w] (deterministic route: fixed-order reduction kernel afterwards)
@@ -226,11 +235,11 @@ __device__ __forceinline__ void wait_count(uint64_t *bar, uint32_t &seen, uint32
 
 // MODE 0: sigmoid head (grad [B][1][hw]); 1: plane parameters (grad [B][4][hw]); 2: fused LPG (grad_depth, upratio R)
 template <class CFG, int MODE, int R, int NWG>
-__global__ void __launch_bounds__(NWG *(kTile + 32), 1) chain_bwd_fused_kernel(const __grid_constant__ FusedArgs fa)
+__global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(const __grid_constant__ FusedArgs fa)
 {
     using L = FusedLayout<CFG, MODE, R, NWG>;
     constexpr int LAST = L::LAST, NW = L::NW, K0 = L::K0;
-    constexpr int NT = NWG * (kTile + 32);                         // NWG compute warpgroups + NWG issuer warps
+    constexpr int NT = fused_threads(NWG);                         // NWG compute warpgroups (+ NWG issuer warps)
     constexpr bool GPRE = MODE != 2 || R <= 2;
     const TcArgs &a = fa.a;
 
@@ -282,10 +291,40 @@ __global__ void __launch_bounds__(NWG *(kTile + 32), 1) chain_bwd_fused_kernel(c
     const int stride = (int)gridDim.x * NWG;
 
     if (tid >= NWG * kTile) {
-        fused_issuer<CFG, MODE, R, NWG>(uniform((tid - NWG * kTile) >> 5), sw, swt, smem_u32(stage), bars, tbase, ntiles);
+        if constexpr (!kInlineIssue)
+            fused_issuer<CFG, MODE, R, NWG>(uniform((tid - NWG * kTile) >> 5), sw, swt, smem_u32(stage), bars, tbase, ntiles);
     } else {
-        const int g = tid / kTile, t = tid % kTile, lane = tid & 31, wj = t >> 5, half = wj >> 1;
+        // g, wj, half are warp-uniform; routed through a shuffle once so that the compiler knows it too (the MMA
+        // operands derived from them must sit in uniform registers)
+        const int g = uniform(tid / kTile), t = tid % kTile, lane = tid & 31, wj = uniform((tid % kTile) >> 5), half = wj >> 1;
         uint64_t *ready = bars + 6 * g, *done = ready + 1, *stg = ready + 2 + half;
+        // inline issue: hardware barrier ids of this warpgroup, warpgroup-level TMEM / staging addresses, hand-off
+        const uint32_t bid = 1 + 5 * g;                           // +0 tile, +1 / +2 chain hand-offs (alternating), +3 / +4 pairs
+        const bool lead_wg = wj == 0, lead_pair = (wj & 1) == 0;
+        const uint32_t wbu = tbase + L::ACC + g * L::WGCOLS, xlu = wbu + K0, ddu = wbu + 2 * K0;
+        const uint32_t subu = smem_u32(stage) + g * L::NSUB * L::SUB + ((L::PRIV && half) ? 2 * L::SUB : 0);
+        uint64_t *wdone = ready + 4 + half;                       // completion of this pair's weight-gradient MMAs
+        // the first warp of the group waits for the others (who only signal) and issues; with dedicated issuer
+        // warps the hand-off is an mbarrier arrival instead
+        auto handoff = [&](uint32_t id, uint32_t nthr, bool lead, uint64_t *mbar, auto &&issue) {
+            if constexpr (kInlineIssue) {
+                if (lead) {
+                    named_bar_sync(id, nthr);
+                    fence_after_sync();
+                    if (elect_one()) issue();
+                    __syncwarp();
+                } else {
+                    named_bar_arrive(id, nthr);
+                }
+            } else {
+                __syncwarp();
+                if (lane == 0) mbar_arrive(mbar);
+            }
+        };
+        auto issue_wt = [&](uint32_t acc) {
+            issue_wgrad_half<L::SUB, L::SUBB>(acc, subu);
+            mma_commit(wdone);
+        };
         // shared staging: the OTHER pair's completions free the buffer for me; private: my own
         uint64_t *wfree = ready + 4 + (L::PRIV ? half : (half ^ 1));
         const uint32_t wlag = L::PRIV ? 0u : (uint32_t)half;
@@ -385,7 +424,7 @@ __global__ void __launch_bounds__(NWG *(kTile + 32), 1) chain_bwd_fused_kernel(c
             pos_advance(quad);
             // ---- x -> (hi, lo) -> TMEM A operand of layer 0; then the next tile's loads take off
             cp_async_wait_all();
-            named_bar_sync(1 + g, kTile);                         // the tile was copied by all threads of the warpgroup
+            named_bar_sync(kInlineIssue ? bid : 1 + g, kTile);     // the tile was copied by all threads of the warpgroup
 #pragma unroll
             for (int c0 = 0; c0 < K0; c0 += 16) {
                 uint32_t hi[16], lo[16];
@@ -406,8 +445,18 @@ __global__ void __launch_bounds__(NWG *(kTile + 32), 1) chain_bwd_fused_kernel(c
             }
             wait_st();
             fence_before_sync();
-            warp_arrive(ready);                                   // F0
-            named_bar_sync(1 + g, kTile);                         // everybody has read the staged tile
+            if constexpr (!kInlineIssue) warp_arrive(ready);      // F0
+            named_bar_sync(kInlineIssue ? bid : 1 + g, kTile);    // everybody has read the staged tile (and written its A operand)
+            if constexpr (kInlineIssue) {
+                if (lead_wg) {                                    // F0
+                    fence_after_sync();
+                    if (elect_one()) {
+                        issue_ts3<CFG::K(0), CFG::N(0)>(ddu, wbu, xlu, sw + CFG::w_off(0));
+                        mma_commit(done);
+                    }
+                    __syncwarp();
+                }
+            }
             prefetch(tile + stride);
             done_wait();
             float a1[NW == 2 ? 32 : 1];
@@ -428,7 +477,10 @@ __global__ void __launch_bounds__(NWG *(kTile + 32), 1) chain_bwd_fused_kernel(c
                 }
                 wait_st();
                 fence_before_sync();
-                warp_arrive(ready);                               // F1
+                handoff(bid + 1, kTile, lead_wg, ready, [&]() {   // F1
+                    issue_ts3<CFG::K(1), CFG::N(1)>(ddu, xlu, xlu + 32, sw + CFG::w_off(1));
+                    mma_commit(done);
+                });
                 done_wait();
             }
             float a16[kTailIn], a8[kTailMid], z[LAST];
@@ -498,7 +550,11 @@ __global__ void __launch_bounds__(NWG *(kTile + 32), 1) chain_bwd_fused_kernel(c
             }
             wait_st();
             fence_before_sync();
-            warp_arrive(ready);                                   // DG(NW-1)
+            handoff(bid + 2, kTile, lead_wg, ready, [&]() {       // DG(NW-1)
+                if constexpr (NW == 1) issue_ts3<CFG::N(0), CFG::K(0)>(ddu, xlu, xlu + 16, swt + CFG::w_off(0));
+                else issue_ts3<CFG::N(1), CFG::K(1)>(ddu, xlu + 32, xlu + 48, swt + CFG::w_off(1));
+                mma_commit(done);
+            });
 
             auto stage_tail = [&]() {
                 wait_count(wfree, wseen, nstage + wlag);
@@ -519,7 +575,7 @@ __global__ void __launch_bounds__(NWG *(kTile + 32), 1) chain_bwd_fused_kernel(c
                 for (int j = 0; j < LAST; ++j) stage_b<L::SUBB>(sc, 24 + j, dz[j]);
                 if constexpr (NW == 1) stage_a_from_tmem32<L::ALO>(sc, 0, xh);
                 fence_smem_to_async();
-                warp_arrive(stg);
+                handoff(bid + 3 + half, 64, lead_pair, stg, [&]() { issue_wt(tbase); });          // WT(half)
             };
             auto gradx_epilogue = [&]() {
                 done_wait();
@@ -566,7 +622,10 @@ __global__ void __launch_bounds__(NWG *(kTile + 32), 1) chain_bwd_fused_kernel(c
                     }
                     wait_st();
                     fence_before_sync();
-                    warp_arrive(ready);                           // DG0
+                    handoff(bid + 1, kTile, lead_wg, ready, [&]() {   // DG0
+                        issue_ts3<CFG::N(0), CFG::K(0)>(ddu, xlu, xlu + 32, swt + CFG::w_off(0));
+                        mma_commit(done);
+                    });
                 };
                 auto stage_x = [&]() {
                     wait_count(wfree, wseen, nstage + wlag);
@@ -582,7 +641,7 @@ __global__ void __launch_bounds__(NWG *(kTile + 32), 1) chain_bwd_fused_kernel(c
                     stage_a_from_tmem32<L::ALO>(sc, 0, xh);
                     stage_a_from_tmem32<L::ALO>(sc, 32, xh + 32);
                     fence_smem_to_async();
-                    warp_arrive(stg);
+                    handoff(bid + 3 + half, 64, lead_pair, stg, [&]() { issue_wt(tbase + 64); });   // WX(half)
                 };
 #pragma unroll 1
                 for (int ph = 0; ph < 2; ++ph) {
@@ -685,7 +744,7 @@ static int launch_fused_cfg(const ChainParams &cp, const TcArgs &a, char *ws, in
     const long long ntiles = (a.npx + kTile - 1) / kTile;
     long long grid = (ntiles + NWG - 1) / NWG;
     if (grid > sms) grid = sms;
-    kern<<<(unsigned)grid, NWG * (kTile + 32), L::smem_bytes, s>>>(fa);
+    kern<<<(unsigned)grid, fused_threads(NWG), L::smem_bytes, s>>>(fa);
     if (int e2 = check_launch("chain_bwd_fused")) return e2;
     if (fa.partials != nullptr) {
         if (int e2 = launch_wreduce(cp, partials, (int)grid, total_w, s)) return e2;

@@ -253,6 +253,14 @@ __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads)
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
+// Producer side of a split barrier: signal arrival on hardware barrier `id` without waiting (the consumer warps
+// run named_bar_sync with the same id and thread count). Prior memory accesses of the arriving threads are
+// ordered before the consumers' accesses after their bar.sync.
+__device__ __forceinline__ void named_bar_arrive(uint32_t id, uint32_t nthreads)
+{
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
 // 3xTF32 operand split. The tensor core reads only the top 19 bits of an fp32 word, so hi is the
 // word itself (hardware truncation) and lo is the exactly representable remainder.
 // ---- packed fp32 pairs (FFMA2 / FADD2 / FMUL2 on sm_100a): one issue slot for two fp32 operations. The FMA
