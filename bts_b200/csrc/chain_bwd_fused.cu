@@ -241,6 +241,9 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
     constexpr int LAST = L::LAST, NW = L::NW, K0 = L::K0;
     constexpr int NT = fused_threads(NWG);                         // NWG compute warpgroups (+ NWG issuer warps)
     constexpr bool GPRE = MODE != 2 || R <= 2;
+    // head with >= 168 registers: unfenced tails (measured 228 -> 207 us). The 2 x 2 stage is faster with scalar,
+    // fenced tails even at 255 registers (141 vs 147 us).
+    constexpr bool RICH = NW == 1 && (kInlineIssue ? NWG <= 2 : L::PRIV);
     const TcArgs &a = fa.a;
 
     extern __shared__ unsigned char smem_raw[];
@@ -491,7 +494,7 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
 #pragma unroll
                 for (int j = 0; j < 16; ++j) a16[j] = elu_fast(__uint_as_float(r[j]));
             }
-            tail_forward<LAST, NW == 1, !L::PRIV>(tw, a16, a8, z);   // private staging = 168 registers: let the weight loads float
+            tail_forward<LAST, NW == 1 || RICH, !RICH>(tw, a16, a8, z);   // registers to spare: packed FMAs, weight loads float
             // ---- upstream gradient -> dz
             float dz[3] = {0.f, 0.f, 0.f};
             if constexpr (MODE == 0) {
@@ -533,7 +536,7 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
                 for (int j = 0; j < LAST; ++j) s = fmaf(w5[j * kTailMid + o], dz[j], s);
                 d8[o] = s * elu_grad_from_out(a8[o]);
             }
-            tail_dgrad16<NW == 1, L::PRIV ? 4 : 1>(tw, d8, dl16);
+            tail_dgrad16<NW == 1 || RICH, RICH ? 4 : 1>(tw, d8, dl16);
             {
                 uint32_t hi[16], lo[16];
 #pragma unroll
