@@ -636,8 +636,18 @@ __global__ void __launch_bounds__(256) chain_tc_wreduce_kernel(ChainParams cp, c
     const int el = threadIdx.x & 31, sl = threadIdx.x >> 5;
     const int e = blockIdx.x * 32 + el;
     float s = 0.f;
-    if (e < total_w)
-        for (int c = sl; c < nparts; c += 8) s += __ldcg(partials + (size_t)c * total_w + e);
+    if (e < total_w) {
+        // eight independent loads in flight per thread, summed in the same (ascending) order as a plain loop
+        int c = sl;
+        for (; c + 56 < nparts; c += 64) {
+            float v[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = __ldcg(partials + (size_t)(c + 8 * i) * total_w + e);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) s += v[i];
+        }
+        for (; c < nparts; c += 8) s += __ldcg(partials + (size_t)c * total_w + e);
+    }
     red[sl][el] = s;
     __syncthreads();
     if (sl != 0 || e >= total_w) return;
