@@ -454,6 +454,13 @@ def main():
                os.path.abspath(__file__)] + sys.argv[1:]
         sys.exit(subprocess.call(cmd))
 
+    # stdout carries ONE JSON line and nothing else: whatever a library writes to file descriptor 1 (NCCL's version
+    # banner, for one) is sent to stderr; print() below goes through the saved descriptor.
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = real_stdout
+
     if args.impl == "reference":
         run_reference_arm(args, wl, rank)
         return
