@@ -24,6 +24,23 @@ def _require_cuda_f32(t, name):
     return t.contiguous()
 
 
+def _batch_strided(t, B, H, W, name):
+    """(tensor, pointer, batch stride in elements) of a [B,H,W] / [B,1,H,W] fp32 CUDA map whose rows are dense but
+    whose images may be further apart than H*W -- a channel slice of a concat buffer (pytorch/bts.py:260, 274, 287)
+    or the slice CatBackward hands back. Anything else is made contiguous (one copy)."""
+    if not isinstance(t, torch.Tensor):
+        raise TypeError("%s must be a torch.Tensor" % name)
+    if not t.is_cuda or t.dtype != torch.float32:
+        t = _require_cuda_f32(t, name)
+    shape_ok = tuple(t.shape) in ((B, H, W), (B, 1, H, W))
+    if shape_ok and t.stride(-1) == 1 and t.stride(-2) == W:
+        bs = t.stride(0) if B > 1 else H * W
+        if bs >= H * W and bs % 4 == 0 and t.data_ptr() % 16 == 0:
+            return t, t.data_ptr(), (0 if bs == H * W else bs)
+    t = t.contiguous()
+    return t, t.data_ptr(), 0
+
+
 def _weights2d(weights):
     ws = []
     for i, w in enumerate(weights):
@@ -168,7 +185,8 @@ class _ReducLPG(torch.autograd.Function):
     post-LPG glue `unsqueeze(1) / max_depth` and the nearest down-sampling by upratio/2 (bts.py:255-256, 269-270)."""
 
     @staticmethod
-    def forward(ctx, x, max_depth, upratio, want_plane_eq, scaled, downsample, *weights):
+    def forward(ctx, out, x, max_depth, upratio, want_plane_eq, scaled, downsample, abs_min_buf, *weights):
+        # `out` comes FIRST: autograd's CopySlices treats input 0 as the view that is modified in place
         x = _require_cuda_f32(x, "net")
         if x.dim() != 4:
             raise RuntimeError("net must be [B,C,h,w], got %s" % (tuple(x.shape),))
@@ -178,9 +196,25 @@ class _ReducLPG(torch.autograd.Function):
         r = int(upratio)
         if downsample and (not scaled or r % 2):
             raise RuntimeError("the down-sampled map is the scaled map's (bts.py:256) and needs an even upratio")
-        depth = torch.empty((B, 1, h * r, w * r) if scaled else (B, h * r, w * r), dtype=torch.float32, device=x.device)
+        depth_bs = 0
+        if out is not None:
+            # destination owned by the caller: a [B,1,H,W] channel slice of a concat buffer (bts.py:260, 274, 287)
+            if not scaled or downsample or want_plane_eq:
+                raise RuntimeError("out= receives the scaled map depth / max_depth (bts.py:255) and nothing else: "
+                                   "pass scaled=True, downsample=False, return_plane_eq=False")
+            if tuple(out.shape) != (B, 1, h * r, w * r) or not out.is_cuda or out.dtype != torch.float32:
+                raise RuntimeError("out must be a CUDA fp32 [B,1,H,W] = %s tensor or view, got %s %s on %s"
+                                   % ((B, 1, h * r, w * r), tuple(out.shape), out.dtype, out.device))
+            depth, _, depth_bs = _batch_strided(out, B, h * r, w * r, "out")
+            if depth.data_ptr() != out.data_ptr():
+                raise RuntimeError("out must have dense rows, a batch stride that is a multiple of 4 and 16-byte alignment")
+            ctx.mark_dirty(out)
+            depth = out
+        else:
+            depth = torch.empty((B, 1, h * r, w * r) if scaled else (B, h * r, w * r), dtype=torch.float32, device=x.device)
         ds = torch.empty((B, 1, 2 * h, 2 * w), dtype=torch.float32, device=x.device) if downsample else None
-        abs_min = torch.full((), float("inf"), dtype=torch.float32, device=x.device)
+        # abs_min_buf: pre-set to +inf by the caller (the out= route cannot return a second tensor, see below)
+        abs_min = abs_min_buf if abs_min_buf is not None else torch.full((), float("inf"), dtype=torch.float32, device=x.device)
         plane_eq = torch.empty((B, 4, h, w), dtype=torch.float32, device=x.device) if want_plane_eq else None
         wsb, wsp, wsn = _workspace(dims, B, h, w, r, x.device)
         st, stp, stn = _stash(dims, B, h, w, x.device, any(ctx.needs_input_grad))
@@ -188,12 +222,15 @@ class _ReducLPG(torch.autograd.Function):
             _cabi.check(_cabi.lib().bts_reduc_lpg_fwd_glue(
                 x.data_ptr(), _cabi.ptr_array([t.data_ptr() for t in ws]), _cabi.int_array(dims), len(ws),
                 float(max_depth), B, h, w, r, EPS, float(max_depth) if scaled else 1.0,
-                plane_eq.data_ptr() if want_plane_eq else None, depth.data_ptr(), 0,
+                plane_eq.data_ptr() if want_plane_eq else None, depth.data_ptr(), depth_bs,
                 ds.data_ptr() if downsample else None, 0, abs_min.data_ptr(), wsp, wsn, stp, stn, _stream()),
                 "bts_reduc_lpg_fwd")
         ctx.stash = st
         ctx.save_for_backward(x, *ws)
         ctx.cfg = (float(max_depth), r, dims, [tuple(t.shape) for t in weights], bool(scaled), bool(downsample))
+        if out is not None:
+            # autograd allows ONE returned tensor when an input view is modified in place: abs_min went to abs_min_buf
+            return out
         ctx.mark_non_differentiable(abs_min)
         outs = [depth, abs_min]
         if downsample:
@@ -204,32 +241,34 @@ class _ReducLPG(torch.autograd.Function):
         return tuple(outs)
 
     @staticmethod
-    def backward(ctx, grad_depth, _g_abs_min, *rest):
+    def backward(ctx, grad_depth, _g_abs_min=None, *rest):
         x, *ws = ctx.saved_tensors
         max_depth, r, dims, shapes, scaled, downsample = ctx.cfg
         B, _, h, w = x.shape
         if grad_depth is None:                                     # only the down-sampled map was used downstream
             grad_depth = torch.zeros((B, h * r, w * r), dtype=torch.float32, device=x.device)
-        grad_depth = _require_cuda_f32(grad_depth, "grad_depth")
+        # the gradient of a map that went into torch.cat (or into a caller-owned slice) comes back as a batch-strided
+        # slice: read it where it lies instead of copying it
+        grad_depth, gd_ptr, gd_bs = _batch_strided(grad_depth, B, h * r, w * r, "grad_depth")
         grad_ds = rest[0] if downsample and rest and rest[0] is not None else None
         if grad_ds is not None:
             grad_ds = _require_cuda_f32(grad_ds, "grad_depth_ds")
-        need_x = ctx.needs_input_grad[0]
-        need_w = any(ctx.needs_input_grad[6:])
+        need_x = ctx.needs_input_grad[1]
+        need_w = any(ctx.needs_input_grad[8:])
         gx = torch.empty_like(x) if need_x else None
         gws = _zero_grads(ws) if need_w else None
         wsb, wsp, wsn = _workspace(dims, B, h, w, r, x.device)
         st = ctx.stash
         with torch.cuda.device(x.device):
             _cabi.check(_cabi.lib().bts_reduc_lpg_bwd_glue(
-                grad_depth.data_ptr(), 0, grad_ds.data_ptr() if grad_ds is not None else None, 0,
+                gd_ptr, gd_bs, grad_ds.data_ptr() if grad_ds is not None else None, 0,
                 max_depth if scaled else 1.0, x.data_ptr(), _cabi.ptr_array([t.data_ptr() for t in ws]),
                 _cabi.int_array(dims), len(ws), max_depth, B, h, w, r, EPS, gx.data_ptr() if need_x else None,
                 _cabi.ptr_array([t.data_ptr() for t in gws]) if need_w else None, wsp, wsn,
                 st.data_ptr() if st is not None else None, st.numel() * 4 if st is not None else 0, _stream()),
                 "bts_reduc_lpg_bwd")
         gw_out = [g.view(s) for g, s in zip(gws, shapes)] if need_w else [None] * len(ws)
-        return (gx, None, None, None, None, None, *gw_out)
+        return (None, gx, None, None, None, None, None, None, *gw_out)
 
 
 class _Silog(torch.autograd.Function):
@@ -330,10 +369,15 @@ def reduc(x, weights, max_depth, is_final=False):
     return _Reduc.apply(x, max_depth, is_final, *weights)
 
 
-def reduc_lpg(x, weights, max_depth, upratio, return_plane_eq=False, scaled=False, downsample=False):
+def reduc_lpg(x, weights, max_depth, upratio, return_plane_eq=False, scaled=False, downsample=False, out=None):
     """Fused stage -> (depth, abs_min[, depth_ds][, plane_eq]). scaled: depth is [B,1,H,W] / max_depth
-    (bts.py:255); downsample: also its nearest down-sampling by upratio/2, [B,1,2h,2w] (bts.py:256)."""
-    return _ReducLPG.apply(x, max_depth, upratio, return_plane_eq, scaled, downsample, *weights)
+    (bts.py:255); downsample: also its nearest down-sampling by upratio/2, [B,1,2h,2w] (bts.py:256); out: a
+    caller-owned [B,1,H,W] view (channel slice of a concat buffer) that receives the scaled map in place."""
+    if out is None:
+        return _ReducLPG.apply(None, x, max_depth, upratio, return_plane_eq, scaled, downsample, None, *weights)
+    abs_min = torch.full((), float("inf"), dtype=torch.float32, device=x.device)
+    depth = _ReducLPG.apply(out, x, max_depth, upratio, return_plane_eq, scaled, downsample, abs_min, *weights)
+    return depth, abs_min
 
 
 PATH_AUTO, PATH_GENERIC, PATH_TCGEN05 = -1, 0, 2

@@ -93,16 +93,19 @@ class silog_loss(nn.Module):
         return Fn.silog(depth_est, depth_gt, mask, self.variance_focus)
 
 
-def fused_stage(reduc, lpg, net, return_plane_eq=False, scaled=False, downsample=False):
+def fused_stage(reduc, lpg, net, return_plane_eq=False, scaled=False, downsample=False, out=None):
     """reducNxN -> normalise/cat -> lpgNxN (pytorch/bts.py:249-254) as ONE fused call.
 
     Returns depth [B,H,W] (and plane_eq [B,4,h,w] when asked); sets lpg.abs_min like the module would.
     scaled=True folds `depth.unsqueeze(1) / max_depth` (bts.py:255, 269, 283) in and returns [B,1,H,W];
     downsample=True (upratio 8 / 4) also returns `F.interpolate(depth_scaled, scale_factor=2/upratio,
-    mode='nearest')` (bts.py:256, 270), [B,1,2h,2w], right after the depth map."""
+    mode='nearest')` (bts.py:256, 270), [B,1,2h,2w], right after the depth map.
+    out= (with scaled=True): a caller-owned [B,1,H,W] view -- e.g. `concat1[:, 1:2]` of a pre-allocated buffer that
+    replaces the `torch.cat` of bts.py:287 -- receives the map in place (no copy forward, and the backward reads its
+    gradient straight from the slice autograd hands back)."""
     if reduc.is_final:
         raise ValueError("fused_stage needs a plane-parameter reduction (is_final=False)")
-    res = Fn.reduc_lpg(net, reduc.chain_weights(), reduc.max_depth, int(lpg.upratio), return_plane_eq, scaled, downsample)
+    res = Fn.reduc_lpg(net, reduc.chain_weights(), reduc.max_depth, int(lpg.upratio), return_plane_eq, scaled, downsample, out)
     lpg.abs_min = res[1]
     out = [res[0]] + list(res[2:])
     return out[0] if len(out) == 1 else tuple(out)

@@ -497,6 +497,44 @@ def test_glue_writes_into_a_channel_slice():
         close_peak(a, b.cpu().numpy())
 
 
+@pytest.mark.parametrize("r,cin,cout", [(8, 128, 128), (4, 128, 64), (2, 64, 32)], ids=str)
+def test_fused_stage_writes_into_a_concat_slice(r, cin, cout):
+    """SURVEY.md 8(f)-1 through the module API: fused_stage(..., scaled=True, out=concat[:, 1:2]) writes the map in
+    place of the torch.cat of bts.py:287 and back-propagates from the slice autograd returns; the torch.cat route
+    (whose CatBackward hands a batch-strided gradient slice to the same Function) must give the same numbers."""
+    import bts_b200
+    torch.manual_seed(21)
+    B, h, w, md = 2, 12, 20, 10.0
+    H, W = h * r, w * r
+    red = bts_b200.reduction_1x1(cin, cout, md, False).cuda()
+    for p in red.parameters():
+        torch.nn.init.xavier_uniform_(p)
+    lpg = bts_b200.local_planar_guidance(r)
+    x = torch.randn(B, cin, h, w, device="cuda")
+    c0, c2 = torch.randn(B, 1, H, W, device="cuda"), torch.randn(B, 1, H, W, device="cuda")
+    gbuf = torch.randn(B, 3, H, W, device="cuda")
+    # route 1: torch.cat of a dense map (the reference's own structure)
+    x1 = x.clone().requires_grad_(True)
+    dense = bts_b200.fused_stage(red, lpg, x1, scaled=True)
+    (torch.cat([c0, dense, c2], 1) * gbuf).sum().backward()
+    gw1 = [p.grad.clone() for p in red.parameters()]
+    for p in red.parameters():
+        p.grad = None
+    # route 2: caller-owned buffer, the stage writes its channel slice
+    x2 = x.clone().requires_grad_(True)
+    concat = torch.empty(B, 3, H, W, device="cuda")
+    concat[:, 0:1] = c0
+    concat[:, 2:3] = c2
+    got = bts_b200.fused_stage(red, lpg, x2, scaled=True, out=concat[:, 1:2])
+    assert got.data_ptr() == concat[:, 1:2].data_ptr()
+    assert torch.equal(concat[:, 1:2].detach(), dense.detach())
+    assert torch.equal(concat[:, 0:1].detach(), c0) and torch.equal(concat[:, 2:3].detach(), c2)
+    (concat * gbuf).sum().backward()
+    close_peak(x2.grad, x1.grad.cpu().numpy())
+    for p, ref in zip(red.parameters(), gw1):
+        close_peak(p.grad, ref.cpu().numpy())
+
+
 @pytest.mark.parametrize("shape,frac", [((4, 1, 52, 68), 0.6), ((8, 1, 480, 640), 0.35), ((3, 1, 37, 41), 0.9),
                                         ((2, 1, 16, 16), 1.0)], ids=str)
 def test_silog_loss_vs_reference_ops(shape, frac):
