@@ -2,6 +2,7 @@
 // Argument validation, path selection and error plumbing only; kernels live in the other files.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "chain_tc.cuh"
@@ -28,6 +29,12 @@ int check_launch(const char *what)
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error((int)e, "%s: launch failed: %s", what, cudaGetErrorString(e));
     return BTS_OK;
+}
+
+bool pdl_enabled()
+{
+    static const bool on = !(getenv("BTS_PDL") != nullptr && atoi(getenv("BTS_PDL")) == 0);
+    return on;
 }
 
 // kernels / launchers implemented elsewhere

@@ -257,99 +257,55 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
     uint32_t *slot = reinterpret_cast<uint32_t *>(bars + 6 * NWG);
 
     const int tid = threadIdx.x;
-    tc_pack_to_smem<CFG>(a.W, sw, LAST, tid, NT);
-    tc_pack_t_to_smem<CFG>(a.W, swt, tid, NT);
-    fence_smem_to_async();
-    if (tid < 32) tmem_alloc(slot, 512);
-    if (tid == 0) {
-        for (int g = 0; g < NWG; ++g) {
-            mbar_init(bars + 6 * g, kTile / 32);                  // one arrival per warp
-            mbar_init(bars + 6 * g + 1, 1);
-            mbar_init(bars + 6 * g + 2, kTile / 64);
-            mbar_init(bars + 6 * g + 3, kTile / 64);
-            mbar_init(bars + 6 * g + 4, 1);
-            mbar_init(bars + 6 * g + 5, 1);
+    // weight images, barriers, TMEM and zeroed weight-gradient accumulators. With inline issue the compute threads
+    // run it AFTER their first tile's copies have taken off, so the DRAM round trip hides behind the packing.
+    uint32_t tbase = 0;
+    auto prologue = [&]() {
+        tc_pack_to_smem<CFG>(a.W, sw, LAST, tid, NT);
+        tc_pack_t_to_smem<CFG>(a.W, swt, tid, NT);
+        fence_smem_to_async();
+        if (tid < 32) tmem_alloc(slot, 512);
+        if (tid == 0) {
+            for (int g = 0; g < NWG; ++g) {
+                mbar_init(bars + 6 * g, kTile / 32);                  // one arrival per warp
+                mbar_init(bars + 6 * g + 1, 1);
+                mbar_init(bars + 6 * g + 2, kTile / 64);
+                mbar_init(bars + 6 * g + 3, kTile / 64);
+                mbar_init(bars + 6 * g + 4, 1);
+                mbar_init(bars + 6 * g + 5, 1);
+            }
+            fence_mbar_init();
         }
-        fence_mbar_init();
-    }
-    fence_before_sync();
-    __syncthreads();
-    fence_after_sync();
-    const uint32_t tbase = (uint32_t)uniform((int)*slot);
-    if (tid < kTile) {   // weight-gradient accumulators start at zero; every MMA into them accumulates
-        uint32_t z[32];
+        fence_before_sync();
+        __syncthreads();
+        fence_after_sync();
+        tbase = (uint32_t)uniform((int)*slot);
+        if (tid < kTile) {   // weight-gradient accumulators start at zero; every MMA into them accumulates
+            uint32_t z[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) z[j] = 0u;
+            for (int j = 0; j < 32; ++j) z[j] = 0u;
 #pragma unroll
-        for (int c0 = 0; c0 < L::ACC; c0 += 32) tmem_st<32>(tbase + ((uint32_t)((tid >> 5) * 32) << 16) + c0, z);
-        wait_st();
-    }
-    fence_before_sync();
-    __syncthreads();
-    fence_after_sync();
+            for (int c0 = 0; c0 < L::ACC; c0 += 32) tmem_st<32>(tbase + ((uint32_t)((tid >> 5) * 32) << 16) + c0, z);
+            wait_st();
+        }
+        fence_before_sync();
+        __syncthreads();
+        fence_after_sync();
+    };
 
     // 32-bit index arithmetic throughout (the C ABI rejects more than 2^31 - 1 low-res pixels)
     const unsigned npx = (unsigned)a.npx, hw = (unsigned)a.hw;
     const int ntiles = (int)((npx + kTile - 1) / kTile);
     const int stride = (int)gridDim.x * NWG;
 
-    if (tid >= NWG * kTile) {
+    if constexpr (!kInlineIssue) prologue();
+    if (!kInlineIssue && tid >= NWG * kTile) {
         if constexpr (!kInlineIssue)
             fused_issuer<CFG, MODE, R, NWG>(uniform((tid - NWG * kTile) >> 5), sw, swt, smem_u32(stage), bars, tbase, ntiles);
     } else {
         // g, wj, half are warp-uniform; routed through a shuffle once so that the compiler knows it too (the MMA
         // operands derived from them must sit in uniform registers)
         const int g = uniform(tid / kTile), t = tid % kTile, lane = tid & 31, wj = uniform((tid % kTile) >> 5), half = wj >> 1;
-        uint64_t *ready = bars + 6 * g, *done = ready + 1, *stg = ready + 2 + half;
-        // inline issue: hardware barrier ids of this warpgroup, warpgroup-level TMEM / staging addresses, hand-off
-        const uint32_t bid = 1 + 5 * g;                           // +0 tile, +1 / +2 chain hand-offs (alternating), +3 / +4 pairs
-        const bool lead_wg = wj == 0, lead_pair = (wj & 1) == 0;
-        const uint32_t wbu = tbase + L::ACC + g * L::WGCOLS, xlu = wbu + K0, ddu = wbu + 2 * K0;
-        const uint32_t subu = smem_u32(stage) + g * L::NSUB * L::SUB + ((L::PRIV && half) ? 2 * L::SUB : 0);
-        uint64_t *wdone = ready + 4 + half;                       // completion of this pair's weight-gradient MMAs
-        // the first warp of the group waits for the others (who only signal) and issues; with dedicated issuer
-        // warps the hand-off is an mbarrier arrival instead
-        auto handoff = [&](uint32_t id, uint32_t nthr, bool lead, uint64_t *mbar, auto &&issue) {
-            if constexpr (kInlineIssue) {
-                if (lead) {
-                    named_bar_sync(id, nthr);
-                    fence_after_sync();
-                    if (elect_one()) issue();
-                    __syncwarp();
-                } else {
-                    named_bar_arrive(id, nthr);
-                }
-            } else {
-                __syncwarp();
-                if (lane == 0) mbar_arrive(mbar);
-            }
-        };
-        auto issue_wt = [&](uint32_t acc) {
-            issue_wgrad_half<L::SUB, L::SUBB>(acc, subu);
-            mma_commit(wdone);
-        };
-        // shared staging: the OTHER pair's completions free the buffer for me; private: my own
-        uint64_t *wfree = ready + 4 + (L::PRIV ? half : (half ^ 1));
-        const uint32_t wlag = L::PRIV ? 0u : (uint32_t)half;
-        const uint32_t xh = tbase + L::ACC + g * L::WGCOLS + ((uint32_t)(wj * 32) << 16);
-        const uint32_t xl = xh + K0, dd = xh + 2 * K0;
-        StageCtx sc;
-        sc.sub = stage + (size_t)(g * L::NSUB + (L::PRIV ? wj : (wj & 1))) * L::SUB;
-#pragma unroll
-        for (int q = 0; q < 8; ++q) sc.coff[q] = (uint32_t)((((lane >> 2) ^ q) << 4) | ((lane & 3) << 2));
-        const float *tw = sw + CFG::tail_off();
-        const float *w5 = tw + kTailMid * kTailIn;
-        uint32_t done_seen = 0, wseen = 0, nstage = 0;
-        auto warp_arrive = [&](uint64_t *bar) {                   // the warp's writes are ordered before lane 0's arrival
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar);
-        };
-        auto done_wait = [&]() {
-            mbar_wait(done, done_seen & 1);
-            ++done_seen;
-            fence_after_sync();
-        };
-
         float *xs_wg = xs_all + (size_t)g * (K0 + 4) * kTile;    // [channel][pixel] of the staged tile
         float *xs = xs_wg + t;                                    // this thread's pixel column
         float *gs = xs_wg + K0 * kTile + t * 4;                   // this pixel's gradient words
@@ -416,8 +372,59 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
             cp_async_commit();
         };
 
+        prefetch(tile0);
+        if constexpr (kInlineIssue) prologue();
+        uint64_t *ready = bars + 6 * g, *done = ready + 1, *stg = ready + 2 + half;
+        // inline issue: hardware barrier ids of this warpgroup, warpgroup-level TMEM / staging addresses, hand-off
+        const uint32_t bid = 1 + 5 * g;                           // +0 tile, +1 / +2 chain hand-offs (alternating), +3 / +4 pairs
+        const bool lead_wg = wj == 0, lead_pair = (wj & 1) == 0;
+        const uint32_t wbu = tbase + L::ACC + g * L::WGCOLS, xlu = wbu + K0, ddu = wbu + 2 * K0;
+        const uint32_t subu = smem_u32(stage) + g * L::NSUB * L::SUB + ((L::PRIV && half) ? 2 * L::SUB : 0);
+        uint64_t *wdone = ready + 4 + half;                       // completion of this pair's weight-gradient MMAs
+        // the first warp of the group waits for the others (who only signal) and issues; with dedicated issuer
+        // warps the hand-off is an mbarrier arrival instead
+        auto handoff = [&](uint32_t id, uint32_t nthr, bool lead, uint64_t *mbar, auto &&issue) {
+            if constexpr (kInlineIssue) {
+                if (lead) {
+                    named_bar_sync(id, nthr);
+                    fence_after_sync();
+                    if (elect_one()) issue();
+                    __syncwarp();
+                } else {
+                    named_bar_arrive(id, nthr);
+                }
+            } else {
+                __syncwarp();
+                if (lane == 0) mbar_arrive(mbar);
+            }
+        };
+        auto issue_wt = [&](uint32_t acc) {
+            issue_wgrad_half<L::SUB, L::SUBB>(acc, subu);
+            mma_commit(wdone);
+        };
+        // shared staging: the OTHER pair's completions free the buffer for me; private: my own
+        uint64_t *wfree = ready + 4 + (L::PRIV ? half : (half ^ 1));
+        const uint32_t wlag = L::PRIV ? 0u : (uint32_t)half;
+        const uint32_t xh = tbase + L::ACC + g * L::WGCOLS + ((uint32_t)(wj * 32) << 16);
+        const uint32_t xl = xh + K0, dd = xh + 2 * K0;
+        StageCtx sc;
+        sc.sub = stage + (size_t)(g * L::NSUB + (L::PRIV ? wj : (wj & 1))) * L::SUB;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) sc.coff[q] = (uint32_t)((((lane >> 2) ^ q) << 4) | ((lane & 3) << 2));
+        const float *tw = sw + CFG::tail_off();
+        const float *w5 = tw + kTailMid * kTailIn;
+        uint32_t done_seen = 0, wseen = 0, nstage = 0;
+        auto warp_arrive = [&](uint64_t *bar) {                   // the warp's writes are ordered before lane 0's arrival
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar);
+        };
+        auto done_wait = [&]() {
+            mbar_wait(done, done_seen & 1);
+            ++done_seen;
+            fence_after_sync();
+        };
+
         int tile = tile0;
-        prefetch(tile);
         for (; tile < ntiles; tile += stride) {
             const unsigned gp = own.g;                            // == tile * kTile + t
             const bool valid = gp < npx;

@@ -371,6 +371,8 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_dgrad_kernel(BwdArgs 
     fence_before_sync();
     __syncthreads();
     fence_after_sync();
+    pdl_trigger();                                // the weight-gradient kernel may take my SM as soon as I leave it
+    pdl_wait();                                   // weights are packed; now the LPG reduction's output is needed
     const uint32_t tbase = (uint32_t)uniform((int)*slot);
     const uint32_t wg_base = tbase + wg * COLS;
     const uint32_t lane_addr = wg_base + ((uint32_t)((t >> 5) * 32) << 16);
@@ -633,6 +635,7 @@ __global__ void __launch_bounds__(256, 1) chain_tc_wgrad_kernel(const __grid_con
 __global__ void __launch_bounds__(256) chain_tc_wreduce_kernel(ChainParams cp, const float *partials, int nparts, int total_w)
 {
     __shared__ float red[8][33];
+    pdl_wait();
     const int el = threadIdx.x & 31, sl = threadIdx.x >> 5;
     const int e = blockIdx.x * 32 + el;
     float s = 0.f;
@@ -666,7 +669,8 @@ __global__ void __launch_bounds__(256) chain_tc_wreduce_kernel(ChainParams cp, c
 
 int launch_wreduce(const ChainParams &cp, const float *partials, int nparts, int total_w, cudaStream_t s)
 {
-    chain_tc_wreduce_kernel<<<(total_w + 31) / 32, 256, 0, s>>>(cp, partials, nparts, total_w);
+    // always follows a kernel of this library in the same call (weight-gradient or one-pass backward)
+    launch_dependent(chain_tc_wreduce_kernel, dim3((total_w + 31) / 32), dim3(256), 0, s, cp, partials, nparts, total_w);
     return check_launch("chain_tc_wreduce");
 }
 
@@ -892,7 +896,8 @@ static int launch_bwd_stash_cfg(const ChainParams &cp, const TcArgs &a, int r, c
         if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
         long long grid = (ntiles + NWG2 - 1) / NWG2;
         if (grid > sms) grid = sms;
-        k2<<<(unsigned)grid, NWG2 * kTile, smem, s>>>(ba);
+        if (TM == 1 && r > 0) launch_dependent(k2, dim3((unsigned)grid), dim3(NWG2 * kTile), smem, s, ba);
+        else k2<<<(unsigned)grid, NWG2 * kTile, smem, s>>>(ba);
         if (int e2 = check_launch("chain_tc_dgrad")) return e2;
         if (cp.gW[0] != nullptr)
             return launch_wgrad_tma(cp, a.x, a.stash_act, del, partials, a.B, a.hw, a.stash_hw_pad, npp, sms, s);

@@ -38,19 +38,6 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
 
     const int tid = threadIdx.x, wg = uniform(tid / kTile), t = tid % kTile, lane = tid & 31;
     const int lt = uniform(t >> 5);                               // warp index inside the warpgroup; warp 0 issues the MMAs
-    tc_pack_to_smem<CFG>(a.W, sw, LAST, tid, NWG * kTile);
-    fence_smem_to_async();
-    if (tid < 32) tmem_alloc(slot, 512);
-    if (tid == 0) {
-        for (int i = 0; i < NWG; ++i) mbar_init(&bars[i], 1);
-        fence_mbar_init();
-    }
-    fence_before_sync();
-    __syncthreads();
-    fence_after_sync();
-    const uint32_t tbase = (uint32_t)uniform((int)*slot);
-    const uint32_t wg_base = tbase + wg * COLS;
-    const uint32_t lane_addr = wg_base + ((uint32_t)((t >> 5) * 32) << 16);
     uint64_t *bar = &bars[wg];
     uint32_t phase = 0;
     const float *tw = sw + CFG::tail_off();
@@ -111,7 +98,20 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
         for (int i = 0; i < D0 / 4; ++i) cp_async16(dst + i * 4 * kTile * 4, xq + (size_t)i * 4 * a.hw, ok);
         cp_async_commit();
     };
-    if constexpr (PREFETCH) prefetch(tile0);
+    if constexpr (PREFETCH) prefetch(tile0);                      // in flight while the weight images are packed
+    tc_pack_to_smem<CFG>(a.W, sw, LAST, tid, NWG * kTile);
+    fence_smem_to_async();
+    if (tid < 32) tmem_alloc(slot, 512);
+    if (tid == 0) {
+        for (int i = 0; i < NWG; ++i) mbar_init(&bars[i], 1);
+        fence_mbar_init();
+    }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tbase = (uint32_t)uniform((int)*slot);
+    const uint32_t wg_base = tbase + wg * COLS;
+    const uint32_t lane_addr = wg_base + ((uint32_t)((t >> 5) * 32) << 16);
     for (int tile = tile0; tile < ntiles; tile += stride) {
         const unsigned gp = own.g;                                // == tile * kTile + t
         const bool valid = gp < npx;

@@ -90,6 +90,8 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
     __syncthreads();
     fence_after_sync();
 
+    pdl_trigger();
+    pdl_wait();                                   // the delta rows come from the dgrad kernel launched just before
     const uint32_t slot0 = smem_u32(slots);
     if (warp == 0) {
         if (lane == 0) {                                          // ---- producer
@@ -344,7 +346,8 @@ int launch_wgrad_tma(const ChainParams &cp, const float *x, const float *act, co
     cudaError_t e = cudaFuncSetAttribute(chain_wgrad_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     long long grid = pl.nchunks < sms ? pl.nchunks : sms;
-    chain_wgrad_tma_kernel<<<(unsigned)grid, kWtThreads, smem, s>>>(maps, pl);
+    // always follows the dgrad (or K1) kernel of the same call
+    launch_dependent(chain_wgrad_tma_kernel, dim3((unsigned)grid), dim3(kWtThreads), smem, s, maps, pl);
     if (int e2 = check_launch("chain_wgrad_tma")) return e2;
     return launch_wreduce(cp, partials, (int)grid, pl.total_w, s);
 }

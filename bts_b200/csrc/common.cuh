@@ -144,10 +144,36 @@ __device__ __forceinline__ float warp_sum(float v)
     return v;
 }
 
+// ---- programmatic dependent launch between kernels of ONE C-ABI call (lpg_bwd -> dgrad -> wgrad -> reduce).
+// A kernel that calls pdl_trigger() lets the next kernel of the stream, if launched with launch_dependent(), become
+// resident while this one still runs; the dependent kernel sets up (weight images, barriers, TMEM) and calls
+// pdl_wait() before it touches anything a predecessor wrote. Both are no-ops for plainly launched kernels.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 }  // namespace bts
 
 // ---- host-side error plumbing (defined in cabi.cu)
 namespace bts {
 int set_error(int code, const char *fmt, ...);
 int check_launch(const char *what);
+
+// launch `k` as a programmatic dependent of the preceding kernel of the stream (only ever used when that kernel is
+// ours and was launched by the same C-ABI call). BTS_PDL=0 falls back to a plain launch.
+bool pdl_enabled();
+template <class... KArgs, class... Args>
+inline void launch_dependent(void (*k)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args &&...args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, k, KArgs(args)...);
+}
 }  // namespace bts

@@ -128,6 +128,7 @@ lpg_bwd_vec_kernel(const float *__restrict__ grad_depth, const float *__restrict
                    float *__restrict__ grad_plane_eq, int B, int h, int w, float eps, LpgGlue gl)
 {
     constexpr int NPX = (R >= 4) ? 1 : 4 / R;    // low-res pixels fully or partly covered by a thread
+    pdl_trigger();                                // the dgrad kernel behind me may set up while I run
     const int Wd = w * R;
     const int W4 = Wd >> 2;
     const long long total = (long long)B * h * W4;
