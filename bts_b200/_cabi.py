@@ -4,7 +4,7 @@ import os
 import re
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libbts_b200.so")
+LIB_PATH = os.environ.get("BTS_LIB") or os.path.join(_HERE, "lib", "libbts_b200.so")   # BTS_LIB: an A/B build of the same ABI
 HEADER_PATH = os.path.join(_HERE, "..", "include", "bts_b200.h")
 
 _c_float_p = ctypes.c_void_p  # raw device pointers travel as integers

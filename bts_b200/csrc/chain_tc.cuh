@@ -534,11 +534,14 @@ __device__ __forceinline__ float4 tf32_lo4(float4 v)
     return make_float4(tc::tf32_lo(v.x), tc::tf32_lo(v.y), tc::tf32_lo(v.z), tc::tf32_lo(v.w));
 }
 
+#ifndef BTS_PACK_PF
+#define BTS_PACK_PF 8
+#endif
 // forward images (rows = output channel n, K = input channel) + raw tail weights W4 [8][16], W5 [last][8]
 template <class CFG>
 __device__ __forceinline__ void tc_pack_to_smem(const float *const *W, float *sw, int last, int tid, int nth)
 {
-    constexpr int PF = 8;   // loads in flight per thread: the packing is the kernel's prologue and pure L2 latency otherwise
+    constexpr int PF = BTS_PACK_PF;   // loads in flight per thread: the packing is the kernel's prologue and pure L2 latency otherwise
 #pragma unroll
     for (int l = 0; l < CFG::NW; ++l) {
         const int K = CFG::K(l), N = CFG::N(l);
@@ -578,10 +581,11 @@ __device__ __forceinline__ void tc_pack_t_to_smem(const float *const *W, float *
         const int K = CFG::K(l), N = CFG::N(l);
         float *hi = swt + CFG::w_off(l), *lo = hi + N * K;
         const float *w = W[l];
-        for (int u0 = tid; u0 < N * K / 4; u0 += 4 * nth) {
-            float4 v[4];
+        constexpr int PF = BTS_PACK_PF / 2;   // four scalar loads each
+        for (int u0 = tid; u0 < N * K / 4; u0 += PF * nth) {
+            float4 v[PF];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
+            for (int i = 0; i < PF; ++i) {
                 const int u = u0 + i * nth;
                 if (u < N * K / 4) {
                     const int c = (u / (2 * N)) * 8 + (u & 7), oq = (u >> 3) % (N / 4);
@@ -590,7 +594,7 @@ __device__ __forceinline__ void tc_pack_t_to_smem(const float *const *W, float *
                 }
             }
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
+            for (int i = 0; i < PF; ++i) {
                 const int u = u0 + i * nth;
                 if (u < N * K / 4) {
                     *reinterpret_cast<float4 *>(hi + 4 * u) = v[i];

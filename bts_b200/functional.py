@@ -119,6 +119,7 @@ class _LPG(torch.autograd.Function):
         ctx.save_for_backward(plane_eq)
         ctx.r = r
         ctx.mark_non_differentiable(abs_min)
+        ctx.set_materialize_grads(False)                           # no zero tensor (a fill kernel) for abs_min's gradient
         return depth, abs_min
 
     @staticmethod
@@ -228,6 +229,7 @@ class _ReducLPG(torch.autograd.Function):
         ctx.stash = st
         ctx.save_for_backward(x, *ws)
         ctx.cfg = (float(max_depth), r, dims, [tuple(t.shape) for t in weights], bool(scaled), bool(downsample))
+        ctx.set_materialize_grads(False)                           # no zero tensors (fill kernels) for unused outputs
         if out is not None:
             # autograd allows ONE returned tensor when an input view is modified in place: abs_min went to abs_min_buf
             return out
