@@ -383,6 +383,53 @@ def test_stash_backward_vs_recompute_backward(cfg):
         close_peak(a, b.cpu().numpy())
 
 
+@pytest.mark.parametrize("cfg", [(128, 128, 8, 2, 28, 36), (128, 64, 4, 2, 36, 44), (64, 32, 2, 2, 40, 56)],
+                         ids=lambda c: "x".join(map(str, c)))
+def test_cuda_graph_replay_matches_eager_launches(cfg):
+    """The C ABI only enqueues on the caller's stream, so a whole forward + backward can be captured into a CUDA
+    graph (bench.py does). The wide-chain backward chains its four kernels by programmatic dependent launch
+    (common.cuh launch_dependent): stream capture must record those edges and replays must return what eager
+    launches return -- bit for bit where the summation order is fixed (depth, grad_x, the wide chains' grad_W),
+    to rounding for the narrow chain's atomically accumulated grad_W."""
+    import bts_b200
+    num_in, num_out, r, B, h, w = cfg
+    torch.manual_seed(5)
+    red = bts_b200.reduction_1x1(num_in, num_out, 10.0).cuda()
+    for p in red.parameters():
+        torch.nn.init.xavier_uniform_(p)
+    lpg = bts_b200.local_planar_guidance(r)
+    x = torch.randn(B, num_in, h, w, device="cuda", requires_grad=True)
+    g = torch.randn(B, h * r, w * r, device="cuda")
+    params = list(red.parameters())
+
+    def step():
+        return torch.autograd.grad(bts_b200.fused_stage(red, lpg, x), [x] + params, g)
+
+    eager = [t.clone() for t in step()]
+    depth_eager = bts_b200.fused_stage(red, lpg, x).detach().clone()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for _ in range(2):
+            step()
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        depth_static = bts_b200.fused_stage(red, lpg, x)
+        static = torch.autograd.grad(depth_static, [x] + params, g)
+    for _ in range(3):
+        graph.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(depth_static.detach(), depth_eager)
+    assert torch.equal(static[0], eager[0])
+    wide = num_in >= 128
+    for a, b in zip(static[1:], eager[1:]):
+        if wide:
+            assert torch.equal(a, b)
+        else:
+            close_peak(a, b.cpu().numpy())
+
+
 def _glue_reference(x, ws, md, r, g_full, g_ds):
     """The reference's own operator sequence (oracle/torch_port.py restates pytorch/bts.py:124-173, 250-254) followed
     by the post-LPG glue lines bts.py:255-256 / 269-270, in fp64 on the CPU, with autograd for the gradients."""
