@@ -220,7 +220,7 @@ def stage_calls(st, wl, device):
     from bts_b200 import _cabi
     from bts_b200 import functional as Fn
     lib = _cabi.lib()
-    stream = torch.cuda.current_stream().cuda_stream
+    cur = lambda: torch.cuda.current_stream().cuda_stream      # looked up per call: the timing loop captures into a graph
     x, g, r, final = st["x"].detach(), st["g"], st["r"], st["final"]
     ws = [w.detach() for w in st["red"].chain_weights()]
     dims = [x.shape[1]] + [w.shape[0] for w in ws]
@@ -240,35 +240,42 @@ def stage_calls(st, wl, device):
     if final:
         out = torch.empty(B, 1, h, w, device=device)
         f = lambda: _cabi.check(lib.bts_reduc_fwd_stash(x.data_ptr(), W, D, len(ws), 1, md, B, h, w, out.data_ptr(),
-                                                        wsb.data_ptr(), nws, stp, nst, stream), "bts_reduc_fwd")
+                                                        wsb.data_ptr(), nws, stp, nst, cur()), "bts_reduc_fwd")
         b = lambda: _cabi.check(lib.bts_reduc_bwd_stash(x.data_ptr(), W, D, len(ws), 1, md, B, h, w, g.data_ptr(), gx.data_ptr(),
-                                                        GW, wsb.data_ptr(), nws, stp, nst, stream), "bts_reduc_bwd")
+                                                        GW, wsb.data_ptr(), nws, stp, nst, cur()), "bts_reduc_bwd")
     else:
         out = torch.empty(B, h * r, w * r, device=device)
         amin = torch.full((), float("inf"), device=device)
         keep += (amin,)
         f = lambda: _cabi.check(lib.bts_reduc_lpg_fwd_stash(x.data_ptr(), W, D, len(ws), md, B, h, w, r, Fn.EPS, None,
                                                             out.data_ptr(), amin.data_ptr(), wsb.data_ptr(), nws, stp, nst,
-                                                            stream), "bts_reduc_lpg_fwd")
+                                                            cur()), "bts_reduc_lpg_fwd")
         b = lambda: _cabi.check(lib.bts_reduc_lpg_bwd_stash(g.data_ptr(), x.data_ptr(), W, D, len(ws), md, B, h, w, r, Fn.EPS,
-                                                            gx.data_ptr(), GW, wsb.data_ptr(), nws, stp, nst, stream),
+                                                            gx.data_ptr(), GW, wsb.data_ptr(), nws, stp, nst, cur()),
                                 "bts_reduc_lpg_bwd")
     f.keep = b.keep = keep + (out,)
     return f, b
 
 
 def time_back_to_back(fn, iters):
-    """Average DEVICE duration of one call: `iters` calls queued back to back between two CUDA events on
-    the launching stream, so host launch cost is pipelined away. Inputs of a call (>= 79 MB for the
-    dominant one, 1.2 GB across a step) do not survive in L2 between calls of the big stages."""
+    """Average DEVICE duration of one call: `iters` calls back to back, captured once into a CUDA graph (the C ABI
+    only enqueues on the stream it is given) and replayed between two CUDA events on the launching stream, so no
+    host launch cost is in the figure -- a 5 us kernel is otherwise timed at the rate Python can call ctypes.
+    Inputs of a call (>= 79 MB for the dominant one, 1.2 GB across a step) do not survive in L2 between calls of
+    the big stages."""
     import torch
     for _ in range(3):
         fn()
     torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        for _ in range(iters):
+            fn()
+    graph.replay()
+    torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(iters):
-        fn()
+    graph.replay()
     e1.record()
     torch.cuda.synchronize()
     return e0.elapsed_time(e1) / iters
@@ -293,7 +300,7 @@ def time_standalone_lpg(wl, device, iters=20):
     from bts_b200 import _cabi
     from bts_b200 import functional as Fn
     lib = _cabi.lib()
-    stream = torch.cuda.current_stream().cuda_stream
+    cur = lambda: torch.cuda.current_stream().cuda_stream
     B, H, W = wl["B"], wl["H"], wl["W"]
     px = B * H * W
     res = {}
@@ -306,8 +313,8 @@ def time_standalone_lpg(wl, device, iters=20):
         g = torch.randn(B, H, W, device=device)
         gpe = torch.empty_like(pe)
         amin = torch.full((), float("inf"), device=device)
-        f = lambda: _cabi.check(lib.bts_lpg_fwd(pe.data_ptr(), depth.data_ptr(), amin.data_ptr(), B, h, w, r, Fn.EPS, stream), "bts_lpg_fwd")
-        b = lambda: _cabi.check(lib.bts_lpg_bwd(g.data_ptr(), pe.data_ptr(), gpe.data_ptr(), B, h, w, r, Fn.EPS, stream), "bts_lpg_bwd")
+        f = lambda: _cabi.check(lib.bts_lpg_fwd(pe.data_ptr(), depth.data_ptr(), amin.data_ptr(), B, h, w, r, Fn.EPS, cur()), "bts_lpg_fwd")
+        b = lambda: _cabi.check(lib.bts_lpg_bwd(g.data_ptr(), pe.data_ptr(), gpe.data_ptr(), B, h, w, r, Fn.EPS, cur()), "bts_lpg_bwd")
         tf, tb = time_back_to_back(f, iters), time_back_to_back(b, iters)
         fb, bb = 16.0 / (r * r) + 4.0, 4.0 + 32.0 / (r * r)
         res["lpg%dx%d_standalone" % (r, r)] = dict(fwd_ms=tf, bwd_ms=tb, fwd_gbs=fb * px / tf / 1e6, bwd_gbs=bb * px / tb / 1e6)
