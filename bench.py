@@ -55,6 +55,9 @@ def parse_args():
     ap.add_argument("--kernel-only", action="store_true", help="only the timed device loop (for ncu)")
     ap.add_argument("--e2e-serial", action="store_true", help="end-to-end leg on one stream (no upload/download overlap)")
     ap.add_argument("--no-graph", action="store_true", help="launch every step eagerly instead of replaying a CUDA graph")
+    ap.add_argument("--grad-allreduce", action="store_true",
+                    help="N > 1: every step ends with an NCCL all-reduce(avg) of the path's weight gradients as one "
+                         "bucket, as DDP does in training (BASELINE.json configs[3]; pytorch/bts_main.py:314)")
     return ap.parse_args()
 
 
@@ -211,6 +214,13 @@ def gpu_step(stages):
         out = stage_forward(st)
         out.backward(st["g"])
         outs.append(out)
+    if _DIST["on"] and _DIST.get("allreduce"):
+        # what DDP does for these parameters: one bucket, averaged over the ranks (NCCL over NVLink)
+        import torch
+        import torch.distributed as dist
+        bucket = torch.cat([p.grad.reshape(-1) for st in stages for p in st["red"].parameters()])
+        dist.all_reduce(bucket, op=dist.ReduceOp.AVG)
+        _DIST["bucket"] = bucket
     return outs
 
 
@@ -485,6 +495,7 @@ def main():
             os.environ["NCCL_DEBUG"] = "WARN"          # keep NCCL's version banner off stdout: ONE JSON line
         dist.init_process_group("nccl", device_id=device)
         _DIST["on"] = True
+        _DIST["allreduce"] = bool(args.grad_allreduce)
     lib = _cabi.lib()
 
     stages = build_stages(wl, device, seed=rank)
@@ -581,7 +592,8 @@ def main():
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl["desc"], "per_gpu_batch": wl["B"], "H": wl["H"], "W": wl["W"],
-                       "max_depth": wl["max_depth"], "stages": [s[0] for s in STAGES], "parallelism": "batch-sharded x%d" % world,
+                       "max_depth": wl["max_depth"], "stages": [s[0] for s in STAGES], "parallelism": "batch-sharded x%d" % world + (
+                           " + NCCL all-reduce(avg) of the weight gradients every step" if _DIST.get("allreduce") else ""),
                        "l2": "inputs %.0f MB per step > 126 MB L2 (no flush needed)" % (in_bytes / 1e6),
                        "api": "bts_b200.reduction_1x1 / fused_stage via libbts_b200.so C ABI",
                        "launch": launch_mode},
@@ -591,6 +603,11 @@ def main():
         print(json.dumps(line), flush=True)
     if world > 1:
         import torch.distributed as dist
+        # a captured graph that holds NCCL work (--grad-allreduce) must go before its communicator does
+        graph = None
+        _DIST.pop("bucket", None)
+        torch.cuda.synchronize()
+        barrier()
         dist.destroy_process_group()
 
 
