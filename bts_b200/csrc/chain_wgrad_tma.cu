@@ -21,8 +21,12 @@
 
 namespace bts {
 
-constexpr int kWtSlots = 3;
-constexpr int kWtSlotBytes = 64 * 1024;      // A_hi 16K | A_lo 16K | B_hi, B_lo (2 x nb rows, <= 32K)
+constexpr int kWtMaxSlots = 6;
+constexpr int kWtRingBytes = 192 * 1024;     // the ring: as many slots as fit, 3 (8x8 chain, 64 KB slots) to 6
+// one slot: A_hi 16K | A_lo 16K | B_hi, B_lo (2 x nb rows, <= 32K). The bytes in flight per SM are what the TMA
+// producer runs ahead of the splitters and the MMAs, i.e. about (slots - 2) x the loaded half of a slot: with three
+// 64 KB slots that is ~32 KB per SM = 4.7 MB on the chip, short of the ~10 MB the HBM needs in flight, so the slot
+// is sized to the widest job of the plan and chains with narrower delta blocks get a deeper ring.
 constexpr int kWtMaxOps = 3;                 // box loads per job: [x] [activation rows] [delta rows]
 constexpr int kWtMaxMaps = 6;                // distinct (tensor, box height) pairs
 constexpr int kWtThreads = 192;
@@ -47,7 +51,7 @@ struct WtExtract {                           // layer l: D_job[row0 + k][col0 + 
 struct WtPlan {
     WtJob jobs[3];
     WtExtract ex[BTS_MAX_LAYERS];
-    int njobs, nlayers, total_w, hw_pad, nmaps;
+    int njobs, nlayers, total_w, hw_pad, nmaps, nslots, slot_bytes;
     long long nchunks;                       // 32-pixel chunks of the padded pixel axis
     float *partials;                         // [gridDim.x][total_w]
 };
@@ -57,13 +61,15 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
 {
     extern __shared__ unsigned char smem_raw[];
     unsigned char *slots = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    uint64_t *bars = reinterpret_cast<uint64_t *>(slots + kWtSlots * kWtSlotBytes);
-    uint64_t *full = bars, *split = bars + kWtSlots, *empty = bars + 2 * kWtSlots, *fin = bars + 3 * kWtSlots;
+    const int nslots = pl.nslots;
+    const uint32_t slot_bytes = (uint32_t)pl.slot_bytes;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(slots + kWtRingBytes);
+    uint64_t *full = bars, *split = bars + kWtMaxSlots, *empty = bars + 2 * kWtMaxSlots, *fin = bars + 3 * kWtMaxSlots;
     uint32_t *slot_tmem = reinterpret_cast<uint32_t *>(fin + 1);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
     if (tid == 0) {
-        for (int s = 0; s < kWtSlots; ++s) {
+        for (int s = 0; s < nslots; ++s) {
             mbar_init(full + s, 1);
             mbar_init(split + s, 128);
             mbar_init(empty + s, 1);
@@ -95,40 +101,40 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
     const uint32_t slot0 = smem_u32(slots);
     if (warp == 0) {
         if (lane == 0) {                                          // ---- producer
-            long long it = 0;
+            int s = 0;
+            uint32_t n = 0;                                       // ring position: slot s, n-th pass over the ring
             for (long long ck = blockIdx.x; ck < pl.nchunks; ck += gridDim.x) {
                 // chunks are visited LAST to FIRST: the dgrad kernel has just written the delta rows (and read the
                 // activation rows) in ascending pixel order, so the highest pixels are what the L2 still holds
                 const long long gp = (pl.nchunks - 1 - ck) * 32;
                 const int b = (int)(gp / pl.hw_pad), p0 = (int)(gp - (long long)b * pl.hw_pad);
-                for (int j = 0; j < pl.njobs; ++j, ++it) {
-                    const int s = (int)(it % kWtSlots);
-                    const long long n = it / kWtSlots;
-                    if (n > 0) mbar_wait(empty + s, (uint32_t)((n - 1) & 1));
+                for (int j = 0; j < pl.njobs; ++j) {
+                    if (n > 0) mbar_wait(empty + s, (n - 1) & 1);
                     const WtJob &job = pl.jobs[j];
                     mbar_arrive_expect_tx(full + s, (uint32_t)job.tx_bytes);
-                    const uint32_t base = slot0 + s * kWtSlotBytes;
+                    const uint32_t base = slot0 + s * slot_bytes;
                     for (int o = 0; o < job.nops; ++o) {
                         const WtOp op = job.ops[o];
                         const uint32_t dst = base + (op.dst_row < 128 ? op.dst_row * 128u : 32768u + (op.dst_row - 128) * 128u);
                         if (op.is_x) tma_load_3d(dst, &maps.m[op.map], p0, op.src_row, b, full + s);
                         else tma_load_2d(dst, &maps.m[op.map], (int)gp, op.src_row, full + s);
                     }
+                    if (++s == nslots) { s = 0; ++n; }
                 }
             }
         }
         __syncwarp();
     } else if (warp == 1) {
         {                                                         // ---- MMA issuer (whole warp waits, one elected lane issues)
-            long long it = 0;
+            int s = 0;
+            uint32_t n = 0;
             for (long long ck = blockIdx.x; ck < pl.nchunks; ck += gridDim.x) {
-                for (int j = 0; j < pl.njobs; ++j, ++it) {
-                    const int s = (int)(it % kWtSlots);
-                    mbar_wait(split + s, (uint32_t)((it / kWtSlots) & 1));
+                for (int j = 0; j < pl.njobs; ++j) {
+                    mbar_wait(split + s, n & 1);
                     fence_after_sync();
                     if (elect_one()) {
                         const WtJob &job = pl.jobs[j];
-                        const uint32_t base = slot0 + s * kWtSlotBytes;
+                        const uint32_t base = slot0 + s * slot_bytes;
                         const uint32_t a_hi = base, a_lo = base + 16384u, b_hi = base + 32768u;
                         const uint32_t d = tbase + job.tmem_col;
                         const uint32_t id_cat = idesc_tf32(128, 2 * job.nb, 0, 0), id_hi = idesc_tf32(128, job.nb, 0, 0);
@@ -140,6 +146,7 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
                         mma_commit(empty + s);
                     }
                     __syncwarp();
+                    if (++s == nslots) { s = 0; ++n; }
                 }
             }
             if (elect_one()) mma_commit(fin);
@@ -147,13 +154,13 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
         __syncwarp();
     } else {                                                      // ---- splitters
         const int st = tid - 64;
-        long long it = 0;
+        int s = 0;
+        uint32_t n = 0;
         for (long long ck = blockIdx.x; ck < pl.nchunks; ck += gridDim.x) {
-            for (int j = 0; j < pl.njobs; ++j, ++it) {
-                const int s = (int)(it % kWtSlots);
-                mbar_wait(full + s, (uint32_t)((it / kWtSlots) & 1));
+            for (int j = 0; j < pl.njobs; ++j) {
+                mbar_wait(full + s, n & 1);
                 const WtJob &job = pl.jobs[j];
-                float4 *a_hi = reinterpret_cast<float4 *>(slots + (size_t)s * kWtSlotBytes);
+                float4 *a_hi = reinterpret_cast<float4 *>(slots + (size_t)s * slot_bytes);
                 float4 *a_lo = a_hi + 1024, *b_hi = a_hi + 2048, *b_lo = b_hi + job.nb * 8;
                 // remainder images, four independent 16-byte units in flight per thread
                 auto split_image = [&](const float4 *hi, float4 *lo, int units) {
@@ -178,6 +185,7 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
                 split_image(b_hi, b_lo, job.nb * 8);
                 fence_smem_to_async();
                 mbar_arrive(split + s);
+                if (++s == nslots) { s = 0; ++n; }
             }
         }
         // ---- accumulators -> this CTA's partial sums (row m of a job = TMEM lane m)
@@ -342,7 +350,11 @@ int launch_wgrad_tma(const ChainParams &cp, const float *x, const float *act, co
     pl.nchunks = npp / 32;
     pl.partials = partials;
 
-    const size_t smem = 1024 + (size_t)kWtSlots * kWtSlotBytes + 8 * (3 * kWtSlots + 1) + 16;
+    int max_nb = 8;
+    for (int j = 0; j < pl.njobs; ++j) max_nb = pl.jobs[j].nb > max_nb ? pl.jobs[j].nb : max_nb;
+    pl.slot_bytes = 32768 + 2 * max_nb * 128;
+    pl.nslots = kWtRingBytes / pl.slot_bytes < kWtMaxSlots ? kWtRingBytes / pl.slot_bytes : kWtMaxSlots;
+    const size_t smem = 1024 + (size_t)kWtRingBytes + 8 * (3 * kWtMaxSlots + 1) + 16;
     cudaError_t e = cudaFuncSetAttribute(chain_wgrad_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     long long grid = pl.nchunks < sms ? pl.nchunks : sms;
