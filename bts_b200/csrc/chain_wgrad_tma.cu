@@ -6,10 +6,11 @@
 // TMA engine drops [8 channels][32 pixels] boxes straight into SWIZZLE_128B shared-memory images
 // (cp.async.bulk.tensor, zero-filled out of bounds) -- no register staging, no transposition:
 //   warp 0      producer : per (32-pixel chunk, job) one transaction barrier + nops box loads
-//   warps 2..5  splitters: remainder images lo = v - tf32(v) next to the raw ones (element-wise, 16 B)
-//   warp 1      issuer   : per K-step of 8 pixels  D += A_hi * [B_hi ; B_lo]^T  and  D[:, :nb] += A_lo * B_hi^T
+//   warps 2..5  splitters: remainder images lo = v - tf32(v) into one of two remainder buffers (element-wise, 16 B)
+//   warp 1      issuer   : per K-step of 8 pixels  D[:, :nb] += A_hi * B_hi^T + A_lo * B_hi^T,  D[:, nb:] += A_hi * B_lo^T
 //                          (tcgen05.mma kind::tf32, both operands from shared memory, fp32 accumulators
-//                          resident in TMEM for the whole kernel), tcgen05.commit frees the slot
+//                          resident in TMEM for the whole kernel), tcgen05.commit frees the landing slot and
+//                          the remainder buffer
 // A job is one wide layer (A = a_l rows, B = delta_{l+1} rows) or the concatenated narrow layers
 // (block-diagonal). Per-CTA partial sums go to the workspace and are reduced deterministically.
 #include <cuda.h>
@@ -21,12 +22,14 @@
 
 namespace bts {
 
-constexpr int kWtMaxSlots = 6;
-constexpr int kWtRingBytes = 192 * 1024;     // the ring: as many slots as fit, 3 (8x8 chain, 64 KB slots) to 6
-// one slot: A_hi 16K | A_lo 16K | B_hi, B_lo (2 x nb rows, <= 32K). The bytes in flight per SM are what the TMA
-// producer runs ahead of the splitters and the MMAs, i.e. about (slots - 2) x the loaded half of a slot: with three
-// 64 KB slots that is ~32 KB per SM = 4.7 MB on the chip, short of the ~10 MB the HBM needs in flight, so the slot
-// is sized to the widest job of the plan and chains with narrower delta blocks get a deeper ring.
+constexpr int kWtMaxSlots = 8;
+constexpr int kWtRingBytes = 216 * 1024;
+// Shared memory: a ring of LANDING slots the TMA producer fills (A_hi 16K | B_hi nb rows, <= 16K: raw fp32 = the hi
+// operand) and TWO remainder buffers of the same shape (A_lo | B_lo) the splitter warps write. The bytes in flight
+// per SM are what the producer runs ahead of the splitters and the MMAs, about (landing slots - 2) slots. The first
+// version kept hi and lo images of a job in one 64 KB slot, three slots: ~32 KB in flight per SM = 4.7 MB on the
+// chip against the ~10 MB the HBM needs, and the kernel sat at 4 TB/s. The slot is sized to the widest job of the
+// plan: 4 landing slots for the 8x8 chain, 7 for the 4x4 chain.
 constexpr int kWtMaxOps = 3;                 // box loads per job: [x] [activation rows] [delta rows]
 constexpr int kWtMaxMaps = 6;                // distinct (tensor, box height) pairs
 constexpr int kWtThreads = 192;
@@ -65,7 +68,8 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
     const uint32_t slot_bytes = (uint32_t)pl.slot_bytes;
     uint64_t *bars = reinterpret_cast<uint64_t *>(slots + kWtRingBytes);
     uint64_t *full = bars, *split = bars + kWtMaxSlots, *empty = bars + 2 * kWtMaxSlots, *fin = bars + 3 * kWtMaxSlots;
-    uint32_t *slot_tmem = reinterpret_cast<uint32_t *>(fin + 1);
+    uint64_t *lofree = fin + 1;                                   // [2]: the MMAs that read a remainder buffer are done
+    uint32_t *slot_tmem = reinterpret_cast<uint32_t *>(lofree + 2);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
     if (tid == 0) {
@@ -75,6 +79,8 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
             mbar_init(empty + s, 1);
         }
         mbar_init(fin, 1);
+        mbar_init(lofree, 1);
+        mbar_init(lofree + 1, 1);
         fence_mbar_init();
         for (int i = 0; i < pl.nmaps; ++i) tma_prefetch_desc(&maps.m[i]);
     }
@@ -115,7 +121,7 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
                     const uint32_t base = slot0 + s * slot_bytes;
                     for (int o = 0; o < job.nops; ++o) {
                         const WtOp op = job.ops[o];
-                        const uint32_t dst = base + (op.dst_row < 128 ? op.dst_row * 128u : 32768u + (op.dst_row - 128) * 128u);
+                        const uint32_t dst = base + (op.dst_row < 128 ? op.dst_row * 128u : 16384u + (op.dst_row - 128) * 128u);
                         if (op.is_x) tma_load_3d(dst, &maps.m[op.map], p0, op.src_row, b, full + s);
                         else tma_load_2d(dst, &maps.m[op.map], (int)gp, op.src_row, full + s);
                     }
@@ -127,23 +133,25 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
     } else if (warp == 1) {
         {                                                         // ---- MMA issuer (whole warp waits, one elected lane issues)
             int s = 0;
-            uint32_t n = 0;
+            uint32_t n = 0, it = 0;
             for (long long ck = blockIdx.x; ck < pl.nchunks; ck += gridDim.x) {
-                for (int j = 0; j < pl.njobs; ++j) {
+                for (int j = 0; j < pl.njobs; ++j, ++it) {
                     mbar_wait(split + s, n & 1);
                     fence_after_sync();
                     if (elect_one()) {
                         const WtJob &job = pl.jobs[j];
-                        const uint32_t base = slot0 + s * slot_bytes;
-                        const uint32_t a_hi = base, a_lo = base + 16384u, b_hi = base + 32768u;
+                        const uint32_t base = slot0 + s * slot_bytes, lob = slot0 + (nslots + (it & 1)) * slot_bytes;
+                        const uint32_t a_hi = base, b_hi = base + 16384u, a_lo = lob, b_lo = lob + 16384u;
                         const uint32_t d = tbase + job.tmem_col;
-                        const uint32_t id_cat = idesc_tf32(128, 2 * job.nb, 0, 0), id_hi = idesc_tf32(128, job.nb, 0, 0);
+                        const uint32_t id = idesc_tf32(128, job.nb, 0, 0);
 #pragma unroll
-                        for (int ks = 0; ks < 4; ++ks) {
-                            mma_tf32_ss(d, smem_desc_sw128(a_hi + ks * 32), smem_desc_sw128(b_hi + ks * 32), id_cat, 1);
-                            mma_tf32_ss(d, smem_desc_sw128(a_lo + ks * 32), smem_desc_sw128(b_hi + ks * 32), id_hi, 1);
+                        for (int ks = 0; ks < 4; ++ks) {          // D[:, 0:nb] = A_hi B_hi + A_lo B_hi, D[:, nb:2nb] = A_hi B_lo
+                            mma_tf32_ss(d, smem_desc_sw128(a_hi + ks * 32), smem_desc_sw128(b_hi + ks * 32), id, 1);
+                            mma_tf32_ss(d + job.nb, smem_desc_sw128(a_hi + ks * 32), smem_desc_sw128(b_lo + ks * 32), id, 1);
+                            mma_tf32_ss(d, smem_desc_sw128(a_lo + ks * 32), smem_desc_sw128(b_hi + ks * 32), id, 1);
                         }
                         mma_commit(empty + s);
+                        mma_commit(lofree + (it & 1));
                     }
                     __syncwarp();
                     if (++s == nslots) { s = 0; ++n; }
@@ -155,13 +163,15 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
     } else {                                                      // ---- splitters
         const int st = tid - 64;
         int s = 0;
-        uint32_t n = 0;
+        uint32_t n = 0, it = 0;
         for (long long ck = blockIdx.x; ck < pl.nchunks; ck += gridDim.x) {
-            for (int j = 0; j < pl.njobs; ++j) {
+            for (int j = 0; j < pl.njobs; ++j, ++it) {
                 mbar_wait(full + s, n & 1);
+                if (it >= 2) mbar_wait(lofree + (it & 1), ((it >> 1) - 1) & 1);   // the job two back has read this buffer
                 const WtJob &job = pl.jobs[j];
                 float4 *a_hi = reinterpret_cast<float4 *>(slots + (size_t)s * slot_bytes);
-                float4 *a_lo = a_hi + 1024, *b_hi = a_hi + 2048, *b_lo = b_hi + job.nb * 8;
+                float4 *a_lo = reinterpret_cast<float4 *>(slots + (size_t)(nslots + (it & 1)) * slot_bytes);
+                float4 *b_hi = a_hi + 1024, *b_lo = a_lo + 1024;
                 // remainder images, four independent 16-byte units in flight per thread
                 auto split_image = [&](const float4 *hi, float4 *lo, int units) {
 #pragma unroll 1
@@ -352,9 +362,10 @@ int launch_wgrad_tma(const ChainParams &cp, const float *x, const float *act, co
 
     int max_nb = 8;
     for (int j = 0; j < pl.njobs; ++j) max_nb = pl.jobs[j].nb > max_nb ? pl.jobs[j].nb : max_nb;
-    pl.slot_bytes = 32768 + 2 * max_nb * 128;
-    pl.nslots = kWtRingBytes / pl.slot_bytes < kWtMaxSlots ? kWtRingBytes / pl.slot_bytes : kWtMaxSlots;
-    const size_t smem = 1024 + (size_t)kWtRingBytes + 8 * (3 * kWtMaxSlots + 1) + 16;
+    pl.slot_bytes = 16384 + max_nb * 128;
+    pl.nslots = kWtRingBytes / pl.slot_bytes - 2;                 // two slots' worth of room are the remainder buffers
+    if (pl.nslots > kWtMaxSlots) pl.nslots = kWtMaxSlots;
+    const size_t smem = 1024 + (size_t)kWtRingBytes + 8 * (3 * kWtMaxSlots + 3) + 16;
     cudaError_t e = cudaFuncSetAttribute(chain_wgrad_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     long long grid = pl.nchunks < sms ? pl.nchunks : sms;
