@@ -23,13 +23,13 @@
 namespace bts {
 
 constexpr int kWtMaxSlots = 8;
-constexpr int kWtRingBytes = 216 * 1024;
+constexpr int kWtRingBytes = 225 * 1024;   // all of the 227 KB a CTA may have, less barriers and alignment slack
 // Shared memory: a ring of LANDING slots the TMA producer fills (A_hi 16K | B_hi nb rows, <= 16K: raw fp32 = the hi
 // operand) and TWO remainder buffers of the same shape (A_lo | B_lo) the splitter warps write. The bytes in flight
 // per SM are what the producer runs ahead of the splitters and the MMAs, about (landing slots - 2) slots. The first
 // version kept hi and lo images of a job in one 64 KB slot, three slots: ~32 KB in flight per SM = 4.7 MB on the
 // chip against the ~10 MB the HBM needs, and the kernel sat at 4 TB/s. The slot is sized to the widest job of the
-// plan: 4 landing slots for the 8x8 chain, 7 for the 4x4 chain.
+// plan: 5 landing slots for the 8x8 chain, 7 for the 4x4 chain.
 constexpr int kWtMaxOps = 3;                 // box loads per job: [x] [activation rows] [delta rows]
 constexpr int kWtMaxMaps = 6;                // distinct (tensor, box height) pairs
 constexpr int kWtThreads = 192;
