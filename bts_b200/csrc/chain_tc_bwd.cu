@@ -380,7 +380,37 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_dgrad_kernel(BwdArgs 
     uint32_t phase = 0;
     const long long npp = ba.npx_pad;
     const long long ntiles = npp / kTile;
-    for (long long tile = (long long)blockIdx.x * NWG + wg; tile < ntiles; tile += (long long)gridDim.x * NWG) {
+    // stash backward: the next tile's a16 / a8 rows and upstream gradient are requested BEFORE this tile's wide
+    // layers, so their DRAM round trip hides behind the MMA hand-offs instead of opening every tile
+    [[maybe_unused]] float na16[kTailIn], na8[kTailMid], ng[4];
+    [[maybe_unused]] auto fetch_tail = [&](long long tl) {
+        if constexpr (TM >= 0) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) ng[j] = 0.f;
+            if (tl >= ntiles) return;
+            const long long gq_ = tl * kTile + t;
+            const int bb = (int)((unsigned)gq_ / (unsigned)ba.hw_pad), pp = (int)((unsigned)gq_ - (unsigned)bb * (unsigned)ba.hw_pad);
+            const bool ok = bb < ba.a.B && pp < ba.a.hw;
+            const float *a16p = ba.act + (size_t)BwdRows<CFG>::row(CFG::NW) * npp + gq_;
+            const float *a8p = ba.act + (size_t)BwdRows<CFG>::row8() * npp + gq_;
+#pragma unroll
+            for (int j = 0; j < kTailIn; ++j) na16[j] = __ldcg(a16p + (size_t)j * npp);
+#pragma unroll
+            for (int j = 0; j < kTailMid; ++j) na8[j] = __ldcg(a8p + (size_t)j * npp);
+            if (ok) {
+                const TcArgs &a = ba.a;
+                if constexpr (TM == 0) {
+                    ng[0] = __ldcs(a.grad + (size_t)bb * a.hw + pp);
+                } else {
+                    const float *gq = a.grad + (size_t)bb * 4 * a.hw + pp;
+                    ng[0] = __ldcg(gq); ng[1] = __ldcg(gq + a.hw); ng[2] = __ldcg(gq + (size_t)2 * a.hw); ng[3] = __ldcg(gq + (size_t)3 * a.hw);
+                }
+            }
+        }
+    };
+    const long long tstride = (long long)gridDim.x * NWG;
+    fetch_tail((long long)blockIdx.x * NWG + wg);
+    for (long long tile = (long long)blockIdx.x * NWG + wg; tile < ntiles; tile += tstride) {
         const long long gp = tile * kTile + t;
         const int bb = (int)((unsigned)gp / (unsigned)ba.hw_pad), pp = (int)((unsigned)gp - (unsigned)bb * (unsigned)ba.hw_pad);
         const bool valid = bb < ba.a.B && pp < ba.a.hw;
@@ -399,21 +429,13 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_dgrad_kernel(BwdArgs 
             constexpr int LAST = TM == 0 ? 1 : 3;
             const TcArgs &a = ba.a;
             const float *tw = stw, *w5 = stw + kTailMid * kTailIn;
-            const float *a16p = ba.act + (size_t)BwdRows<CFG>::row(CFG::NW) * npp + gp;
-            const float *a8p = ba.act + (size_t)BwdRows<CFG>::row8() * npp + gp;
-            float a16[kTailIn], a8[kTailMid], z[LAST], g[4] = {0.f, 0.f, 0.f, 0.f};
+            float a16[kTailIn], a8[kTailMid], z[LAST], g[4];
 #pragma unroll
-            for (int j = 0; j < kTailIn; ++j) a16[j] = __ldcg(a16p + (size_t)j * npp);
+            for (int j = 0; j < kTailIn; ++j) a16[j] = na16[j];
 #pragma unroll
-            for (int j = 0; j < kTailMid; ++j) a8[j] = __ldcg(a8p + (size_t)j * npp);
-            if (valid) {
-                if constexpr (TM == 0) {
-                    g[0] = __ldcs(a.grad + (size_t)b * a.hw + p);
-                } else {
-                    const float *gq = a.grad + (size_t)b * 4 * a.hw + p;
-                    g[0] = __ldcg(gq); g[1] = __ldcg(gq + a.hw); g[2] = __ldcg(gq + (size_t)2 * a.hw); g[3] = __ldcg(gq + (size_t)3 * a.hw);
-                }
-            }
+            for (int j = 0; j < kTailMid; ++j) a8[j] = na8[j];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) g[j] = ng[j];
             tail_logits<LAST>(w5, a8, z);
             float dz[3] = {0.f, 0.f, 0.f};
             if constexpr (TM == 0) {
@@ -450,6 +472,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_dgrad_kernel(BwdArgs 
             }
             tmem_st<16>(lane_addr, hi);
             tmem_st<16>(lane_addr + AW, lo);
+            fetch_tail(tile + tstride);
         }
         float keep[64];
         if constexpr (CFG::NW > 3) dgrad_layer<CFG, 3>(ba, wg_base, lane_addr, swt, bar, phase, wg, lt, gp, valid, b, p, keep);
