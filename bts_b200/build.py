@@ -38,16 +38,21 @@ def build(force=False, verbose=False):
     headers = glob.glob(os.path.join(CSRC, "*.cuh")) + glob.glob(os.path.join(HERE, "..", "include", "*.h"))
     objs = []
     log = []
+    todo = []
     for src in sources():
         obj = os.path.join(LIBDIR, os.path.basename(src)[:-3] + ".o")
         objs.append(obj)
         if force or _stale(obj, [src] + headers):
-            cmd = [NVCC] + FLAGS + ["-c", src, "-o", obj]
-            r = subprocess.run(cmd, capture_output=True, text=True)
-            log.append("$ " + " ".join(cmd) + "\n" + r.stdout + r.stderr)
-            if r.returncode != 0:
-                sys.stderr.write(log[-1])
-                raise RuntimeError("nvcc failed on " + src)
+            todo.append((src, [NVCC] + FLAGS + ["-c", src, "-o", obj]))
+    # translation units are independent: compile them side by side (the big kernel files take minutes each)
+    from concurrent.futures import ThreadPoolExecutor
+    with ThreadPoolExecutor(max_workers=max(1, min(len(todo), os.cpu_count() or 1))) as pool:
+        results = list(pool.map(lambda t: subprocess.run(t[1], capture_output=True, text=True), todo))
+    for (src, cmd), r in zip(todo, results):
+        log.append("$ " + " ".join(cmd) + "\n" + r.stdout + r.stderr)
+        if r.returncode != 0:
+            sys.stderr.write(log[-1])
+            raise RuntimeError("nvcc failed on " + src)
     if force or _stale(SO, objs):
         cmd = [NVCC, "-shared", "-o", SO] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lcuda"]
         r = subprocess.run(cmd, capture_output=True, text=True)

@@ -10,7 +10,10 @@
 namespace bts {
 
 static thread_local char g_err[512] = "";
-static thread_local int g_force_path = -1;
+// Process-wide on purpose: PyTorch runs a Function's backward on its autograd worker thread, not on the thread
+// that called bts_force_path(), so a thread-local hook would pin the forward only. Read with relaxed atomics.
+static int g_force_path_v = -1;
+#define g_force_path (__atomic_load_n(&g_force_path_v, __ATOMIC_RELAXED))
 
 int set_error(int code, const char *fmt, ...)
 {
@@ -156,7 +159,7 @@ extern "C" {
 
 int bts_abi_version(void) { return BTS_ABI_VERSION; }
 const char *bts_last_error(void) { return g_err; }
-void bts_force_path(int path) { g_force_path = path; }
+void bts_force_path(int path) { __atomic_store_n(&g_force_path_v, path, __ATOMIC_RELAXED); }
 unsigned long long bts_launch_count(void) { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
 
 int bts_reduc_path(const int *dims, int n_layers, int is_final)
@@ -299,8 +302,8 @@ static int check_glue(int r, float depth_div, long long bstride, const void *ds,
     if (!(depth_div > 0.f)) return set_error(BTS_ERR_BAD_ARG, "depth_div must be positive");
     if (bstride != 0 && bstride < (long long)h * r * w * r)
         return set_error(BTS_ERR_BAD_ARG, "batch stride %lld smaller than one %dx%d map", bstride, h * r, w * r);
-    if (ds != nullptr && (r % 2 != 0))
-        return set_error(BTS_ERR_BAD_ARG, "the down-sampled map needs an even upratio, got %d", r);
+    if (ds != nullptr && r != 4 && r != 8)     // bts.py:256, 270: only lpg8x8 (x1/4) and lpg4x4 (x1/2) are down-sampled
+        return set_error(BTS_ERR_BAD_ARG, "the down-sampled map exists for upratio 8 and 4 only, got %d", r);
     if (ds != nullptr && ds_bstride != 0 && ds_bstride < (long long)4 * h * w)
         return set_error(BTS_ERR_BAD_ARG, "down-sampled batch stride %lld smaller than one %dx%d map", ds_bstride, 2 * h, 2 * w);
     return BTS_OK;

@@ -73,7 +73,8 @@ def _zero_grads(ws):
 
 
 def _workspace(dims, B, h, w, r, device):
-    n = _cabi.lib().bts_workspace_bytes(_cabi.int_array(dims), len(dims) - 1, B, h, w, r)
+    with torch.cuda.device(device):                                # the library sizes per-CTA partials by THIS device's SM count
+        n = _cabi.lib().bts_workspace_bytes(_cabi.int_array(dims), len(dims) - 1, B, h, w, r)
     if n == 0:
         return None, 0, 0
     ws = torch.empty((n + 3) // 4, dtype=torch.float32, device=device)
@@ -94,7 +95,8 @@ def set_stash(on):
 def _stash(dims, B, h, w, device, wanted):
     """Activation stash for chains whose backward would otherwise recompute them in a separate kernel
     (include/bts_b200.h, ABI 2). (tensor | None, pointer, bytes); 0 bytes when nothing is stashed."""
-    n = _cabi.lib().bts_stash_bytes(_cabi.int_array(dims), len(dims) - 1, B, h, w) if (wanted and _STASH["on"]) else 0
+    with torch.cuda.device(device):
+        n = _cabi.lib().bts_stash_bytes(_cabi.int_array(dims), len(dims) - 1, B, h, w) if (wanted and _STASH["on"]) else 0
     if n == 0:
         return None, None, 0
     st = torch.empty((n + 3) // 4, dtype=torch.float32, device=device)
@@ -195,8 +197,8 @@ class _ReducLPG(torch.autograd.Function):
         dims = _dims(x, ws)
         B, _, h, w = x.shape
         r = int(upratio)
-        if downsample and (not scaled or r % 2):
-            raise RuntimeError("the down-sampled map is the scaled map's (bts.py:256) and needs an even upratio")
+        if downsample and (not scaled or r not in (4, 8)):
+            raise RuntimeError("the down-sampled map is the scaled map's (bts.py:256, 270): scaled=True and upratio 8 or 4")
         depth_bs = 0
         if out is not None:
             # destination owned by the caller: a [B,1,H,W] channel slice of a concat buffer (bts.py:260, 274, 287)

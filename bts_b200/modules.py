@@ -101,8 +101,10 @@ def fused_stage(reduc, lpg, net, return_plane_eq=False, scaled=False, downsample
     downsample=True (upratio 8 / 4) also returns `F.interpolate(depth_scaled, scale_factor=2/upratio,
     mode='nearest')` (bts.py:256, 270), [B,1,2h,2w], right after the depth map.
     out= (with scaled=True): a caller-owned [B,1,H,W] view -- e.g. `concat1[:, 1:2]` of a pre-allocated buffer that
-    replaces the `torch.cat` of bts.py:287 -- receives the map in place (no copy forward, and the backward reads its
-    gradient straight from the slice autograd hands back)."""
+    replaces the `torch.cat` of bts.py:287 -- receives the map in place (no copy forward). Backward: on this out= route
+    autograd's CopySlices hands the Function a contiguous clone of the gradient slice (one full-resolution copy made by
+    PyTorch, not by us); the zero-copy read of a batch-strided gradient slice applies to the plain `torch.cat` route,
+    where CatBackward returns a strided view."""
     if reduc.is_final:
         raise ValueError("fused_stage needs a plane-parameter reduction (is_final=False)")
     res = Fn.reduc_lpg(net, reduc.chain_weights(), reduc.max_depth, int(lpg.upratio), return_plane_eq, scaled, downsample, out)

@@ -60,7 +60,8 @@ enum {
 BTS_API int bts_abi_version(void);
 BTS_API const char *bts_last_error(void);
 
-/* Debug / test hook: force a path for subsequent calls from this thread (-1 = automatic). */
+/* Debug / test hook: force a path for subsequent calls of the PROCESS (-1 = automatic). Process-wide because
+ * PyTorch runs autograd backward nodes on its own worker threads. Not for production use. */
 BTS_API void bts_force_path(int path);
 BTS_API int bts_reduc_path(const int *dims, int n_layers, int is_final);
 
@@ -162,7 +163,7 @@ BTS_API int bts_reduc_lpg_bwd_stash(const float *grad_depth, const float *x, con
  *   depth_NxN_scaled_ds = F.interpolate(depth_NxN_scaled, scale_factor=2/N, mode='nearest')   (N = 8, 4)
  * The forward writes depth / depth_div (pass max_depth; 1 = plain depth) with `depth_bstride` elements between
  * images -- 0 = dense h*r*w*r, anything larger lets the map land in a channel slice of a concat buffer
- * (bts.py:260, 274, 287) -- and, when ds_out != NULL (even r), the nearest-neighbour down-sampling by r/2
+ * (bts.py:260, 274, 287) -- and, when ds_out != NULL (r = 8 or 4 only), the nearest-neighbour down-sampling by r/2
  * (= rows / columns 0 and r/2 of every r x r block) as [B][2h][2w] with batch stride ds_bstride (0 = dense).
  * The backward takes the gradient of the scaled map (same stride convention) and, optionally, the gradient of
  * the down-sampled map; everything else as the *_stash entry points.

@@ -91,3 +91,9 @@ def lpg_forward(plane_eq, upratio):
 def stage_forward(x, weights, max_depth, upratio):
     """One decoder LPG stage: reducNxN -> glue -> lpgNxN (bts.py:249-254). Returns (depth, abs_min)."""
     return lpg_forward(glue(chain_forward(x, weights, max_depth, False)), upratio)
+
+
+def silog_forward(depth_est, depth_gt, mask, variance_focus):
+    """silog_loss.forward, pytorch/bts.py:46-48 (pinned by tests/golden/silog_*.npz)."""
+    d = torch.log(depth_est[mask]) - torch.log(depth_gt[mask])
+    return torch.sqrt((d ** 2).mean() - variance_focus * (d.mean() ** 2)) * 10.0

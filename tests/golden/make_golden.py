@@ -172,6 +172,30 @@ def main():
         g = np.ones((1, 3 * r, 4 * r))
         lpg_case(ref, "lpg_r%d_planted" % r, r, pe, g, "den=n3 exactly: clamp edges, zero -> inf")
 
+    # --- silog_loss: the imported reference class, pytorch/bts.py:41-48, three mask densities
+    for name, shape, frac, vf, seed in (("silog_dense", (2, 1, 24, 32), 0.9, 0.85, 31), ("silog_half", (3, 1, 17, 23), 0.5, 0.85, 32),
+                                        ("silog_sparse", (2, 1, 40, 56), 0.05, 0.5, 33)):
+        silog_case(ref, name, shape, frac, vf, seed)
+
+
+def silog_case(ref, name, shape, frac, vf, seed):
+    gen = torch.Generator().manual_seed(seed)
+    est = (torch.rand(shape, generator=gen) * 9.5 + 0.5)
+    gt = (torch.rand(shape, generator=gen) * 9.5 + 0.5)
+    mask = torch.rand(shape, generator=gen) < frac
+    out = dict(depth_est=est.numpy(), depth_gt=gt.numpy(), mask=mask.numpy())
+    for tag, dt in (("f32", torch.float32), ("f64", torch.float64)):
+        e = est.detach().clone().to(dt).requires_grad_(True)
+        loss = ref.silog_loss(variance_focus=vf)(e, gt.to(dt), mask)        # the reference module itself
+        loss.backward()
+        out[tag + "_loss"] = np.asarray(loss.detach().numpy())
+        out[tag + "_grad_est"] = e.grad.numpy()
+    meta = dict(kind="silog", name=name, shape=list(shape), mask_fraction=frac, variance_focus=vf, seed=seed,
+                reference="pytorch/bts.py:41-48", torch=torch.__version__)
+    out["meta"] = json.dumps(meta)
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
+    print(name, {k: v.shape for k, v in out.items() if k != "meta"})
+
 
 if __name__ == "__main__":
     main()

@@ -1,0 +1,109 @@
+"""GPU (-m gpu): every fused stage and the head at the FULL shapes of BASELINE.json configs[0]-[3], against the
+oracle (oracle/torch_port.py = the reference's ATen operator sequence, pinned bit-exact to pytorch/bts.py by
+tests/test_oracle_golden.py) evaluated in fp64 on the host, image by image.
+
+Two routes per shape, as a user of the reference would reach them:
+  fused  : bts_b200.fused_stage(reduc, lpg, x)                      (one C-ABI call forward, one backward)
+  strict : reduction_1x1 -> the reference's Python glue (bts.py:250-253) -> local_planar_guidance
+
+Bars (north_star 1e-5): depth element-wise rtol 1e-5 (+1e-6*max_depth atol); plane_eq / head output,
+grad_x, grad_W: max|a-b| <= 1e-5 max|b| and L2-relative <= 1e-5. Tile scheduling at 300 ... 53 504 tiles, image wraps
+at hw = 4 800 ... 428 032 and the persistent loops are only exercised at these sizes.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from conftest import max_rel_to_peak, l2_rel
+from oracle import torch_port as tp
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-5
+# (config, B, H, W, max_depth)
+CONFIGS = {
+    "c0_nyu_train_b4": (4, 416, 544, 10.0),
+    "c1_nyu_b8": (8, 480, 640, 10.0),
+    "c2_kitti_b16": (16, 352, 1216, 80.0),
+    "c3_kitti_train_b4": (4, 352, 704, 80.0),
+}
+# decoder instances at bts_size = 512 (pytorch/bts.py:198-217): C_in, num_out, upratio, is_final
+STAGES = [(128, 128, 8, False), (128, 64, 4, False), (64, 32, 2, False), (32, 16, 1, True)]
+CASES = [(c, s) for c in CONFIGS for s in STAGES]
+
+
+def _oracle_fp64(x, ws, md, r, final, g):
+    """fp64 forward + backward of the torch port, one image at a time (bounded host memory); weight gradients are
+    summed over the images exactly as autograd would over the batch."""
+    torch.set_num_threads(os.cpu_count() or 1)
+    wd = [w.double().requires_grad_(True) for w in ws]
+    outs, gxs, amin = [], [], float("inf")
+    for i in range(x.shape[0]):
+        xi = x[i:i + 1].double().requires_grad_(True)
+        if final:
+            out = tp.chain_forward(xi, wd, md, True)
+        else:
+            out, am = tp.stage_forward(xi, wd, md, r)
+            amin = min(amin, float(am.detach()))
+        out.backward(g[i:i + 1].double())
+        outs.append(out.detach())
+        gxs.append(xi.grad)
+    return torch.cat(outs).numpy(), torch.cat(gxs).numpy(), [w.grad[:, :, 0, 0].numpy() for w in wd], amin
+
+
+def _close_peak(a, b, what):
+    a = a.detach().cpu().numpy() if isinstance(a, torch.Tensor) else a
+    e1, e2 = max_rel_to_peak(a, b), l2_rel(a, b)
+    assert e1 <= RTOL and e2 <= RTOL, (what, "max-rel-to-peak", e1, "l2-rel", e2)
+
+
+def _close_depth(a, b, md, what):
+    a = a.detach().cpu().numpy().astype(np.float64)
+    bad = np.abs(a - b) > (1e-6 * md + RTOL * np.abs(b))
+    assert not bad.any(), (what, int(bad.sum()), float(np.abs(a - b).max()))
+
+
+@pytest.mark.parametrize("cfg,stage", CASES, ids=lambda v: v if isinstance(v, str) else "x".join(map(str, v)))
+def test_full_size_vs_fp64_oracle(cfg, stage):
+    import bts_b200
+    B, H, W, md = CONFIGS[cfg]
+    cin, nout, r, final = stage
+    h, w = H // r, W // r
+    gen = torch.Generator().manual_seed(7000 + cin + 10 * r + B)
+    dims = tp.chain_dims(cin, nout, final)
+    ws = tp.xavier_weights(dims, final, gen)
+    x = torch.randn(B, cin, h, w, generator=gen)
+    g = torch.randn((B, 1, h, w) if final else (B, H, W), generator=gen)
+    ref_out, ref_gx, ref_gw, ref_amin = _oracle_fp64(x, ws, md, r, final, g)
+
+    red = bts_b200.reduction_1x1(cin, nout, md, is_final=final).cuda()
+    with torch.no_grad():
+        for p, wt in zip(red.chain_weights(), ws):
+            p.copy_(wt.cuda())
+    gd = g.cuda()
+    for route in (("head",) if final else ("fused", "strict")):
+        xd = x.cuda().requires_grad_(True)
+        for p in red.parameters():
+            p.grad = None
+        if final:
+            out = red(xd)
+            _close_peak(out, ref_out, (route, "out"))
+        else:
+            lpg = bts_b200.local_planar_guidance(r)
+            if route == "fused":
+                out = bts_b200.fused_stage(red, lpg, xd)
+            else:
+                pe4 = red(xd)
+                n = F.normalize(pe4[:, :3, :, :], 2, 1)                        # bts.py:250-253
+                out = lpg(torch.cat([n, pe4[:, 3, :, :].unsqueeze(1)], 1), None)
+            _close_depth(out, ref_out, md, (route, "depth"))
+            assert abs(float(lpg.abs_min) - ref_amin) <= 1e-5, (route, float(lpg.abs_min), ref_amin)
+        out.backward(gd)
+        torch.cuda.synchronize()
+        _close_peak(xd.grad, ref_gx, (route, "grad_x"))
+        for i, (p, gr) in enumerate(zip(red.chain_weights(), ref_gw)):
+            _close_peak(p.grad.view(p.shape[0], p.shape[1]), gr, (route, "grad_w%d" % i))
+        del xd, out

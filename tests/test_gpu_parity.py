@@ -606,6 +606,20 @@ def test_silog_loss_vs_reference_ops(shape, frac):
     assert bool((ed.grad[~mask.cuda()] == 0).all())
 
 
+@pytest.mark.parametrize("g", golden_cases("silog"), ids=lambda g: g.name)
+def test_silog_loss_vs_golden(g):
+    """bts_b200.silog_loss against the imported reference class (pytorch/bts.py:41-48; fixtures by make_golden.py)."""
+    import bts_b200
+    est = dev(g["depth_est"], True)
+    loss = bts_b200.silog_loss(g.meta["variance_focus"])(est, dev(g["depth_gt"]), torch.from_numpy(g["mask"]).cuda())
+    loss.backward()
+    ref = float(g["f64_loss"])
+    assert abs(float(loss) - ref) <= RTOL * abs(ref), (float(loss), ref)
+    close_peak(est.grad, g["f64_grad_est"])
+    masked_out = ~g["mask"]
+    assert not est.grad.cpu().numpy()[masked_out].any()            # no gradient outside the mask, as the gather gives
+
+
 def test_silog_loss_edge_cases():
     import bts_b200
     crit = bts_b200.silog_loss(0.85)

@@ -110,3 +110,19 @@ def test_known_answers_lpg():
     assert np.allclose(1.0 / d2[0, 0], [-0.25, 0.25])
     d8, _ = co.lpg_fwd(pe2, 8, np.float64)
     assert np.allclose(1.0 / d8[0, 0], (np.arange(8) - 3.5) / 8)
+
+
+SILOG = golden_cases("silog")
+
+
+@pytest.mark.parametrize("g", SILOG, ids=lambda g: g.name)
+@pytest.mark.parametrize("tag,dt", [("f32", torch.float32), ("f64", torch.float64)])
+def test_torch_port_silog(g, tag, dt):
+    """oracle silog_forward == the imported reference silog_loss (pytorch/bts.py:41-48) on its golden vectors."""
+    assert len(SILOG) == 3
+    est = torch.from_numpy(g["depth_est"]).to(dt).requires_grad_(True)
+    loss = tp.silog_forward(est, torch.from_numpy(g["depth_gt"]).to(dt), torch.from_numpy(g["mask"]), g.meta["variance_focus"])
+    loss.backward()
+    tol = 1e-6 if dt == torch.float32 else 1e-13
+    assert abs(float(loss) - float(g[tag + "_loss"])) <= tol * abs(float(g[tag + "_loss"]))
+    assert max_rel_to_peak(est.grad.numpy(), g[tag + "_grad_est"]) <= tol
