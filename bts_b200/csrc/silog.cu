@@ -150,4 +150,65 @@ int launch_silog_bwd(const float *est, const float *gt, const unsigned char *mas
     return check_launch("silog_bwd");
 }
 
+// ------------------------------------------------------------------------------------------------
+// No-allocation variant of the forward (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: code under CUDA graph capture, tight serving loops).
+// The scratch of bts_silog_fwd -- per-block fp64 partial sums + the 64-byte state -- lives in a file-scope device
+// array instead of a caller workspace. Every GPU that loads the library holds these 96 KB + 256 B until exit.
+// All calls on a device share the array and it keeps the last call's contents: every word the finish kernel
+// reads is written by the partial kernel of the SAME call (blocks 0..grid-1), so nothing has to start at zero;
+// two calls that overlap on the GPU (different streams) race on it.
+// ------------------------------------------------------------------------------------------------
+constexpr int kSilogStaticMaxBlocks = 4096;                       // 3 doubles each = 96 KB
+constexpr long long kSilogStaticMaxN = 1ll << 30;                 // elements per call (BTS_SILOG_STATIC_MAX_N)
+static __device__ __align__(256) double g_silog_scratch[3 * kSilogStaticMaxBlocks + 32];   // partials | state (256 B)
+
+constexpr int kMaxDevices = 64;
+static void *g_silog_scratch_ptr[kMaxDevices];                    // device address of the array, per device
+
+// In host code `g_silog_scratch` is a host-side stand-in, not a device address: look the address up once per
+// device, with that device current (it is: every entry point runs on the caller's current device).
+static int silog_static_scratch(double **out)
+{
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return set_error((int)e, "cudaGetDevice: %s", cudaGetErrorString(e));
+    if (dev < 0 || dev >= kMaxDevices) return set_error(BTS_ERR_UNSUPPORTED, "device ordinal %d >= %d", dev, kMaxDevices);
+    void *p = __atomic_load_n(&g_silog_scratch_ptr[dev], __ATOMIC_ACQUIRE);
+    if (p == nullptr) {
+        e = cudaGetSymbolAddress(&p, g_silog_scratch);
+        if (e != cudaSuccess || p == nullptr)
+            return set_error(e != cudaSuccess ? (int)e : BTS_ERR_UNSUPPORTED, "cudaGetSymbolAddress(silog scratch): %s", cudaGetErrorString(e));
+        __atomic_store_n(&g_silog_scratch_ptr[dev], p, __ATOMIC_RELEASE);   // two threads racing here store the same value
+    }
+    *out = static_cast<double *>(p);
+    return BTS_OK;
+}
+
 }  // namespace bts
+
+extern "C" BTS_API int bts_silog_fwd_static(const float *depth_est, const float *depth_gt, const unsigned char *mask,
+                                            long long n, float variance_focus, float *loss, void *state_out, void *stream)
+{
+    using namespace bts;
+    if (n < 0) return set_error(BTS_ERR_BAD_ARG, "negative element count");
+    if (n > kSilogStaticMaxN)
+        return set_error(BTS_ERR_UNSUPPORTED, "bts_silog_fwd_static: n = %lld exceeds the static scratch's limit of %lld elements "
+                         "(use bts_silog_fwd with a caller workspace)", n, kSilogStaticMaxN);
+    if (!depth_est || !depth_gt || !mask || !loss) return set_error(BTS_ERR_BAD_ARG, "depth_est / depth_gt / mask / loss is NULL");
+    if (state_out != nullptr && (reinterpret_cast<uintptr_t>(state_out) & 15u))
+        return set_error(BTS_ERR_BAD_ARG, "state_out must be 16-byte aligned");
+    double *scratch = nullptr;
+    if (int e = silog_static_scratch(&scratch)) return e;
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaStream_t s = (cudaStream_t)stream;
+    const int vec = al16(depth_est) && al16(depth_gt) && al4(mask);
+    int grid = silog_grid(n, sms);                                // same grid as bts_silog_fwd => same summation order
+    if (grid > kSilogStaticMaxBlocks) grid = kSilogStaticMaxBlocks;
+    SilogState *state = state_out ? static_cast<SilogState *>(state_out) : reinterpret_cast<SilogState *>(scratch + 3 * kSilogStaticMaxBlocks);
+    silog_partial_kernel<<<grid, kSilogThreads, 0, s>>>(depth_est, depth_gt, mask, n, vec, scratch);
+    if (int e = check_launch("silog_partial(static)")) return e;
+    silog_finish_kernel<<<1, 32, 0, s>>>(scratch, grid, variance_focus, loss, state);
+    return check_launch("silog_finish(static)");
+}

@@ -197,6 +197,21 @@ BTS_API int bts_silog_bwd(const float *depth_est, const float *depth_gt, const u
                   float variance_focus, const float *grad_loss, const void *ws, float *grad_est, void *stream);
 
 /*
+ * bts_silog_fwd without a workspace and without any allocation. NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops,
+ * harnesses that forbid it). The scratch (per-block fp64 partial sums) is a file-scope `static __device__` array
+ * of 96 KB + 256 B that every GPU that loads the library holds until exit; the entry point calls no cudaMalloc /
+ * cudaFree / allocating routine. Limit: n <= BTS_SILOG_STATIC_MAX_N elements per call (BTS_ERR_UNSUPPORTED beyond;
+ * use bts_silog_fwd). `state_out`: NULL, or BTS_SILOG_STATE_BYTES of caller device memory (16-byte aligned) that
+ * receives the sums bts_silog_bwd needs -- pass it there as `ws`. Result = bts_silog_fwd's, bit for bit (same grid,
+ * same summation order). All calls on a device SHARE the array, which keeps the last call's contents (every word
+ * read is rewritten by the same call, nothing needs clearing): calls that overlap on the GPU (two streams) race.
+ */
+#define BTS_SILOG_STATIC_MAX_N (1ll << 30)
+BTS_API int bts_silog_fwd_static(const float *depth_est, const float *depth_gt, const unsigned char *mask, long long n,
+                                 float variance_focus, float *loss, void *state_out, void *stream);
+
+/*
  * online_eval's per-sample metrics                       pytorch/bts_main.py:218-254, compute_errors :87-108
  * (SURVEY.md 8(f)-5). For each of the B images: clamp the prediction to [min_depth, max_depth] (inf -> max,
  * nan -> min, :233-236), mask = min_depth < gt < max_depth inside the crop rectangle [crop_top, crop_bottom) x
