@@ -88,34 +88,43 @@ def make_cpu_inputs(wl, B, seed=0):
     return items
 
 
-def cpu_step(wl, items):
-    """One fwd+bwd pass of the four stages with the reference's own operator sequence."""
+def cpu_step(wl, items, split=None):
+    """One fwd+bwd pass of the four stages with the reference's own operator sequence. `split`: a 2-element list
+    that receives the seconds spent in the forward and in the backward calls."""
     from oracle import torch_port as tp
     for name, r, final, ws, x, g in items:
         for t in ws + [x]:
             t.grad = None
+        t0 = time.perf_counter()
         if final:
             out = tp.chain_forward(x, ws, wl["max_depth"], True)
         else:
             out, _ = tp.stage_forward(x, ws, wl["max_depth"], r)
+        t1 = time.perf_counter()
         out.backward(g)
+        if split is not None:
+            split[0] += t1 - t0
+            split[1] += time.perf_counter() - t1
 
 
-def time_cpu(wl, B, steps, warmup):
+def time_cpu(wl, B, steps, warmup, threads=None):
     import torch
-    cores = os.cpu_count() or 1
+    cores = threads or os.cpu_count() or 1
     torch.set_num_threads(cores)
     items = make_cpu_inputs(wl, B)
     for _ in range(warmup):
         cpu_step(wl, items)
-    ts = []
+    ts, fb = [], []
     for _ in range(steps):
+        sp = [0.0, 0.0]
         t0 = time.perf_counter()
-        cpu_step(wl, items)
+        cpu_step(wl, items, sp)
         ts.append(time.perf_counter() - t0)
+        fb.append(sp)
     med = statistics.median(ts)
     px = B * wl["H"] * wl["W"]
     return dict(value=px / med / 1e6, unit="Mpixels/s", cores=cores, kind="port",
+                fwd_s=statistics.median(f for f, _ in fb), bwd_s=statistics.median(b for _, b in fb),
                 sample="batch %d of %dx%d, all four stages fwd+bwd, median of %d steps (%.3f s/step), "
                        "oracle/torch_port.py (reference ATen op sequence) with %d torch threads"
                        % (B, wl["H"], wl["W"], steps, med, cores)), med, ts
@@ -204,9 +213,23 @@ def stage_forward(st):
     return bts_b200.fused_stage(st["red"], st["lpg"], st["x"])
 
 
+def _flat_grads(params):
+    """One tensor over the weight gradients of a stage when they already share a buffer (the autograd Functions carve
+    them out of ONE zero-filled allocation, functional._zero_grads, and AccumulateGrad keeps those views), else None."""
+    import torch
+    gs = [p.grad for p in params]
+    st = gs[0].untyped_storage()
+    if any(g.untyped_storage().data_ptr() != st.data_ptr() or not g.is_contiguous() for g in gs):
+        return None
+    lo = min(g.storage_offset() for g in gs)
+    hi = max(g.storage_offset() + g.numel() for g in gs)
+    return torch.empty(0, dtype=gs[0].dtype, device=gs[0].device).set_(st, lo, (hi - lo,))   # padding words are zeros
+
+
 def gpu_step(stages):
     """fwd + bwd of the four stages through the public module API (autograd drives the backward)."""
-    outs = []
+    outs, works = [], []
+    allreduce = _DIST["on"] and _DIST.get("allreduce")
     for st in stages:
         st["x"].grad = None
         for p in st["red"].parameters():
@@ -214,13 +237,28 @@ def gpu_step(stages):
         out = stage_forward(st)
         out.backward(st["g"])
         outs.append(out)
-    if _DIST["on"] and _DIST.get("allreduce"):
-        # what DDP does for these parameters: one bucket, averaged over the ranks (NCCL over NVLink)
-        import torch
-        import torch.distributed as dist
-        bucket = torch.cat([p.grad.reshape(-1) for st in stages for p in st["red"].parameters()])
-        dist.all_reduce(bucket, op=dist.ReduceOp.AVG)
-        _DIST["bucket"] = bucket
+        if allreduce:
+            # what DDP's buckets do (pytorch/bts_main.py:314): a stage's weight gradients are averaged over the ranks as
+            # soon as its backward is enqueued -- on NCCL's own stream, under the next stage's kernels. Only the head's
+            # 648 floats are exposed at the end of the step.
+            import torch
+            import torch.distributed as dist
+            params = list(st["red"].parameters())
+            flat = _flat_grads(params)
+            if flat is None:                                       # foreign gradient layout: one copy each way
+                flat = torch.cat([p.grad.reshape(-1) for p in params])
+                works.append((dist.all_reduce(flat, op=dist.ReduceOp.AVG, async_op=True), flat, params))
+            else:
+                works.append((dist.all_reduce(flat, op=dist.ReduceOp.AVG, async_op=True), flat, None))
+    for work, flat, params in works:
+        work.wait()                                               # the compute stream waits for the collective
+        if params is not None:
+            off = 0
+            for p in params:
+                p.grad.copy_(flat[off:off + p.numel()].view_as(p.grad))
+                off += p.numel()
+    if works:
+        _DIST["bucket"] = [w[1] for w in works]
     return outs
 
 
@@ -440,17 +478,21 @@ def max_over_ranks(value, device):
 
 def run_reference_arm(args, wl, rank):
     """--impl reference: the reference's own CPU implementation of the path (torch port of
-    pytorch/bts.py:97-173 -- the reference tree itself does not travel to the GPU box) on the host
-    cores, each step a bounded sample (batch 1) of the workload. Rank 0 only."""
+    pytorch/bts.py:97-173, pinned bit-exact to it by tests/golden -- the reference tree itself does not travel to the
+    GPU box) on all host cores, SAME per-step batch as our arm (a step is 0.4 s at nyu_b8). Rank 0 only."""
     if rank != 0:
         return
-    B = 1
+    B = wl["B"]
     cb, med, ts = time_cpu(wl, B, args.steps, args.warmup)
+    one, _, _ = time_cpu(wl, 1, 3, 1, threads=1)                   # BASELINE.md section 3: the 1-thread figure (batch 1)
+    cb["one_thread_mpix_s"] = one["value"]
     line = {
         "impl": "reference", "metric": "LPG decoder Mpixels/s fwd+bwd", "value": cb["value"], "unit": "Mpixels/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": med * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": wl["desc"], "sample": "batch 1 per step", "H": wl["H"], "W": wl["W"]},
+        "config": {"workload": wl["desc"], "per_gpu_batch": B, "H": wl["H"], "W": wl["W"], "max_depth": wl["max_depth"],
+                   "stages": [s[0] for s in STAGES],
+                   "note": "one CPU process whatever --gpus says: compare with our arm at N=1 only"},
         "cpu_baseline": cb,
         "e2e": {"value": cb["value"], "unit": "Mpixels/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -491,8 +533,7 @@ def main():
     device = torch.device("cuda", local_rank)
     if world > 1:
         import torch.distributed as dist
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"          # keep NCCL's version banner off stdout: ONE JSON line
+        os.environ.setdefault("NCCL_DEBUG", "WARN")    # stdout is already redirected; NCCL_DEBUG=INFO from the env is kept
         dist.init_process_group("nccl", device_id=device)
         _DIST["on"] = True
         _DIST["allreduce"] = bool(args.grad_allreduce)
@@ -525,21 +566,25 @@ def main():
             torch.cuda.synchronize()
     barrier()
     launches0 = lib.bts_launch_count()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     with ClockSampler(local_rank) as clocks:
         torch.cuda.synchronize()
-        ev0.record()
-        for _ in range(args.steps):
+        evs[0].record()
+        for i in range(args.steps):
             if graph is not None:
                 graph.replay()
             else:
                 gpu_step(stages)
-        ev1.record()
+            evs[i + 1].record()                                   # an event record costs nothing on the device
         torch.cuda.synchronize()
     barrier()
     launches = per_step * args.steps if graph is not None else lib.bts_launch_count() - launches0
-    ms_total = max_over_ranks(ev0.elapsed_time(ev1), device)
+    ms_total = max_over_ranks(evs[0].elapsed_time(evs[-1]), device)
     ms_step = ms_total / args.steps
+    # per-step times beside the total: one rank's hiccup inside a 15 ms region shows up as max >> median
+    per = [evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]
+    ms_median = max_over_ranks(statistics.median(per), device)
+    ms_worst = max_over_ranks(max(per), device)
     value = world * px_per_rank / (ms_step * 1e-3) / 1e6
 
     if args.kernel_only:
@@ -584,12 +629,15 @@ def main():
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu_baseline, _, _ = time_cpu(wl, 1, 8, 2)
+        cpu_baseline, _, _ = time_cpu(wl, wl["B"], 10, 3)          # same batch as the GPU arm, median of 10
+        one, _, _ = time_cpu(wl, 1, 3, 1, threads=1)
+        cpu_baseline["one_thread_mpix_s"] = one["value"]
 
     if rank == 0:
         line = {
             "metric": "LPG decoder Mpixels/s fwd+bwd", "value": value, "unit": "Mpixels/s", "n_gpus": world,
-            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True,
+            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_step,
+            "ms_per_step_median": ms_median, "ms_per_step_max": ms_worst, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl["desc"], "per_gpu_batch": wl["B"], "H": wl["H"], "W": wl["W"],
                        "max_depth": wl["max_depth"], "stages": [s[0] for s in STAGES], "parallelism": "batch-sharded x%d" % world + (

@@ -33,7 +33,12 @@ def _stale(target, deps):
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False):
+def build(force=False, verbose=False, extra_flags=(), libdir=None):
+    """extra_flags / libdir: an A/B variant (-D switches) built into its own directory; BTS_LIB selects it at run time."""
+    global LIBDIR, SO
+    if libdir is not None:
+        LIBDIR = libdir
+        SO = os.path.join(LIBDIR, "libbts_b200.so")
     os.makedirs(LIBDIR, exist_ok=True)
     headers = glob.glob(os.path.join(CSRC, "*.cuh")) + glob.glob(os.path.join(HERE, "..", "include", "*.h"))
     objs = []
@@ -43,7 +48,7 @@ def build(force=False, verbose=False):
         obj = os.path.join(LIBDIR, os.path.basename(src)[:-3] + ".o")
         objs.append(obj)
         if force or _stale(obj, [src] + headers):
-            todo.append((src, [NVCC] + FLAGS + ["-c", src, "-o", obj]))
+            todo.append((src, [NVCC] + FLAGS + list(extra_flags) + ["-c", src, "-o", obj]))
     # translation units are independent: compile them side by side (the big kernel files take minutes each)
     from concurrent.futures import ThreadPoolExecutor
     with ThreadPoolExecutor(max_workers=max(1, min(len(todo), os.cpu_count() or 1))) as pool:
@@ -69,4 +74,11 @@ def build(force=False, verbose=False):
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))
+    # python -m bts_b200.build [--force] [--verbose] [--variant NAME -DX=1 ...]  (variant -> bts_b200/lib_NAME/)
+    argv = sys.argv[1:]
+    libdir, extra = None, []
+    if "--variant" in argv:
+        i = argv.index("--variant")
+        libdir = os.path.join(HERE, "lib_" + argv[i + 1])
+        extra = [f for f in argv[i + 2:] if f.startswith("-D")]
+    print(build(force="--force" in argv, verbose="--verbose" in argv, extra_flags=extra, libdir=libdir))

@@ -34,6 +34,21 @@ constexpr int kBLo = 32 * 128;                         // byte offset of the rem
 #define BTS_FUSED_INLINE_ISSUE 1
 #endif
 constexpr bool kInlineIssue = BTS_FUSED_INLINE_ISSUE != 0;
+
+// The tensor core adds into its fp32 TMEM accumulator with round-toward-zero: a weight-gradient accumulator that lives
+// in TMEM for the whole kernel loses ~3.4e-8 of its magnitude per accumulate step, ALWAYS toward zero, so the error is a
+// bias that grows with the pixels a CTA sees (measured against the fp64 oracle: 2.6e-5 at 416x544 b4, where a CTA issues
+// ~760 steps per accumulator; it would be 2e-4 at KITTI b16). Every kWgradDrain iterations of the tile loop the CTA
+// therefore drains the accumulators into fp32 registers (16 per thread and job, round-to-nearest adds) and zeroes them:
+// 32 x kWgradDrain steps per chain, i.e. a bias below 1e-6 per 2 iterations.
+#ifndef BTS_WGRAD_DRAIN
+#define BTS_WGRAD_DRAIN 2
+#endif
+constexpr int kWgradDrain = BTS_WGRAD_DRAIN;
+#ifndef BTS_DRAIN_DEFERRED
+#define BTS_DRAIN_DEFERRED 0
+#endif
+constexpr bool kDrainDeferred = BTS_DRAIN_DEFERRED != 0;   // drain one iteration late (see the tile loop) or at the iteration's end
 constexpr int fused_threads(int nwg) { return nwg * (kTile + (kInlineIssue ? 0 : 32)); }
 
 struct FusedArgs {
@@ -41,6 +56,7 @@ struct FusedArgs {
     float *partials;        // [gridDim.x][total_w] (deterministic route: fixed-order reduction kernel afterwards)
     int total_w;
     int atomic_w;           // 1: every CTA adds its partial sums to a.gw[] with red.global.add (no reduction launch)
+    int drain_every;        // tile-loop iterations between drains of the weight-gradient accumulators (kWgradDrain)
 };
 
 // D[128 x N](TMEM, col d) = A[128 x K](TMEM; hi at a_hi, lo at a_lo) * B[N x K]^T (smem image at w: hi | lo)
@@ -101,7 +117,16 @@ struct FusedLayout {
     static constexpr size_t smem_bytes = 1024 + stage_bytes + xs_bytes + sizeof(float) * (PACK + IMG) + 8 * 6 * NWG + 16;
     static_assert(NW == 1 || NW == 2, "one or two tensor-core layers");
     static_assert(CFG::dim(NW) == kTailIn && CFG::dim(NW - 1) == 32, "chain must end ... -> 32 -> 16 -> 8");
-    static_assert(ACC + NWG * WGCOLS <= 512, "TMEM budget");
+    // weight-gradient accumulators: one set per warpgroup when the 512 TMEM columns allow it (the head), so that a
+    // warpgroup drains its own set behind its own barrier; else one set shared by the CTA (2x2 stage), drained CTA-wide
+#ifndef BTS_FUSED_PERWG
+#define BTS_FUSED_PERWG 1
+#endif
+    static constexpr bool PERWG = BTS_FUSED_PERWG && NWG * ACC + NWG * WGCOLS <= 512;
+    static constexpr int NACC = PERWG ? NWG : 1;
+    static constexpr int WG0 = NACC * ACC;                 // first TMEM column of the warpgroups' own regions
+    static constexpr int DRC = PERWG ? 32 : 16;            // summed accumulator columns a thread drains per job
+    static_assert(WG0 + NWG * WGCOLS <= 512, "TMEM budget");
 };
 
 // ---- the MMA-issuing warps: one per warpgroup, each walks its warpgroup's fixed command list in order.
@@ -119,7 +144,8 @@ __device__ __noinline__ void fused_issuer(int g, const float *sw, const float *s
     const int first = (int)blockIdx.x * NWG + g;
     const int mine = first < ntiles ? (ntiles - first + stride - 1) / stride : 0;
     uint64_t *ready = bars + 6 * g, *done = ready + 1, *stg0 = ready + 2, *stg1 = ready + 3, *wfree0 = ready + 4, *wfree1 = ready + 5;
-    const uint32_t wb = tbase + L::ACC + g * L::WGCOLS;           // x_hi
+    const uint32_t wb = tbase + L::WG0 + g * L::WGCOLS;           // x_hi
+    const uint32_t tacc = tbase + (L::PERWG ? g * L::ACC : 0);
     const uint32_t xl = wb + K0, dd = wb + 2 * K0;
     // shared staging: both pairs use sub-buffers 0,1; private: pair h uses 2h, 2h+1
     const uint32_t subA = stage_addr + g * L::NSUB * L::SUB;
@@ -148,14 +174,14 @@ __device__ __noinline__ void fused_issuer(int g, const float *sw, const float *s
                 if constexpr (NW == 1) {
                     if (c == 0) { issue_ts3<CFG::K(0), CFG::N(0)>(dd, wb, xl, sw + CFG::w_off(0)); mma_commit(done); }
                     else if (c == 1) { issue_ts3<CFG::N(0), CFG::K(0)>(dd, xl, xl + 16, swt + CFG::w_off(0)); mma_commit(done); }
-                    else { issue_wgrad_half<L::SUB, L::SUBB>(tbase, sub0); mma_commit(h1 ? wfree1 : wfree0); }
+                    else { issue_wgrad_half<L::SUB, L::SUBB>(tacc, sub0); mma_commit(h1 ? wfree1 : wfree0); }
                 } else {
                     if (c == 0) { issue_ts3<CFG::K(0), CFG::N(0)>(dd, wb, xl, sw + CFG::w_off(0)); mma_commit(done); }
                     else if (c == 1) { issue_ts3<CFG::K(1), CFG::N(1)>(dd, xl, xl + 32, sw + CFG::w_off(1)); mma_commit(done); }
                     else if (c == 2) { issue_ts3<CFG::N(1), CFG::K(1)>(dd, xl + 32, xl + 48, swt + CFG::w_off(1)); mma_commit(done); }
                     else if (c == 4) { issue_ts3<CFG::N(0), CFG::K(0)>(dd, xl, xl + 32, swt + CFG::w_off(0)); mma_commit(done); }
-                    else if (c == 3 || c == 5) { issue_wgrad_half<L::SUB, L::SUBB>(tbase, sub0); mma_commit(h1 ? wfree1 : wfree0); }
-                    else { issue_wgrad_half<L::SUB, L::SUBB>(tbase + 64, sub0); mma_commit(h1 ? wfree1 : wfree0); }
+                    else if (c == 3 || c == 5) { issue_wgrad_half<L::SUB, L::SUBB>(tacc, sub0); mma_commit(h1 ? wfree1 : wfree0); }
+                    else { issue_wgrad_half<L::SUB, L::SUBB>(tacc + 64, sub0); mma_commit(h1 ? wfree1 : wfree0); }
                 }
             }
             __syncwarp();
@@ -285,7 +311,7 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
 #pragma unroll
             for (int j = 0; j < 32; ++j) z[j] = 0u;
 #pragma unroll
-            for (int c0 = 0; c0 < L::ACC; c0 += 32) tmem_st<32>(tbase + ((uint32_t)((tid >> 5) * 32) << 16) + c0, z);
+            for (int c0 = 0; c0 < L::WG0; c0 += 32) tmem_st<32>(tbase + ((uint32_t)((tid >> 5) * 32) << 16) + c0, z);
             wait_st();
         }
         fence_before_sync();
@@ -378,7 +404,8 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
         // inline issue: hardware barrier ids of this warpgroup, warpgroup-level TMEM / staging addresses, hand-off
         const uint32_t bid = 1 + 5 * g;                           // +0 tile, +1 / +2 chain hand-offs (alternating), +3 / +4 pairs
         const bool lead_wg = wj == 0, lead_pair = (wj & 1) == 0;
-        const uint32_t wbu = tbase + L::ACC + g * L::WGCOLS, xlu = wbu + K0, ddu = wbu + 2 * K0;
+        const uint32_t wbu = tbase + L::WG0 + g * L::WGCOLS, xlu = wbu + K0, ddu = wbu + 2 * K0;
+        const uint32_t tacc = tbase + (L::PERWG ? g * L::ACC : 0);   // this warpgroup's (or the CTA's) accumulators
         const uint32_t subu = smem_u32(stage) + g * L::NSUB * L::SUB + ((L::PRIV && half) ? 2 * L::SUB : 0);
         uint64_t *wdone = ready + 4 + half;                       // completion of this pair's weight-gradient MMAs
         // the first warp of the group waits for the others (who only signal) and issues; with dedicated issuer
@@ -405,7 +432,7 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
         // shared staging: the OTHER pair's completions free the buffer for me; private: my own
         uint64_t *wfree = ready + 4 + (L::PRIV ? half : (half ^ 1));
         const uint32_t wlag = L::PRIV ? 0u : (uint32_t)half;
-        const uint32_t xh = tbase + L::ACC + g * L::WGCOLS + ((uint32_t)(wj * 32) << 16);
+        const uint32_t xh = tbase + L::WG0 + g * L::WGCOLS + ((uint32_t)(wj * 32) << 16);
         const uint32_t xl = xh + K0, dd = xh + 2 * K0;
         StageCtx sc;
         sc.sub = stage + (size_t)(g * L::NSUB + (L::PRIV ? wj : (wj & 1))) * L::SUB;
@@ -424,8 +451,56 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
             fence_after_sync();
         };
 
+        // ---- drain of the weight-gradient accumulators (see kWgradDrain). Columns j and j + 32 of a job (hi and remainder
+        // halves of the deltas) are summed on the way. Per-warpgroup sets: every thread takes its TMEM lane t, all 32
+        // summed columns, behind the warpgroup's own barrier. Shared set: warpgroup 0 takes j = 0..15, warpgroup 1
+        // j = 16..31 (both can read every TMEM lane quarter), behind a CTA-wide barrier.
+        static_assert(NWG >= 2, "the shared-set drain splits the accumulator columns over two warpgroups");
+        constexpr int DRC = L::DRC;
+        float wacc[L::NJOBS][DRC];
+#pragma unroll
+        for (int job = 0; job < L::NJOBS; ++job)
+#pragma unroll
+            for (int j = 0; j < DRC; ++j) wacc[job][j] = 0.f;
+        auto drain_sync = [&]() {
+            if constexpr (L::PERWG) named_bar_sync(kInlineIssue ? bid : 1 + g, kTile);
+            else named_bar_sync(0, NWG * kTile);
+        };
+        auto drain = [&]() {
+            wait_count(wfree, wseen, nstage);                     // every weight-gradient MMA this warp can vouch for is done
+            fence_before_sync();
+            drain_sync();                                         // ... and so is everybody else's
+            fence_after_sync();
+            if (L::PERWG || g < 2) {
+                const uint32_t la = tacc + ((uint32_t)(wj * 32) << 16) + (L::PERWG ? 0u : (uint32_t)g * 16);
+#pragma unroll
+                for (int job = 0; job < L::NJOBS; ++job) {
+                    uint32_t r0[DRC], r1[DRC];
+                    tmem_ld<DRC>(la + job * 64, r0);
+                    tmem_ld<DRC>(la + job * 64 + 32, r1);
+                    wait_ld();
+#pragma unroll
+                    for (int j = 0; j < DRC; ++j) {
+                        wacc[job][j] += __uint_as_float(r0[j]) + __uint_as_float(r1[j]);
+                        r0[j] = 0u;
+                    }
+                    tmem_st<DRC>(la + job * 64, r0);
+                    tmem_st<DRC>(la + job * 64 + 32, r0);
+                }
+                wait_st();
+            }
+            fence_before_sync();
+            drain_sync();                                         // accumulators are zero again before anybody issues into them
+            fence_after_sync();
+        };
+        // CTA-uniform trip count (warpgroup 0 has the most tiles): every warpgroup joins every drain
+        // (per-warpgroup sets need no common schedule: every warpgroup runs its own tiles)
+        const int iters_cta = L::PERWG ? (tile0 < ntiles ? (ntiles - tile0 + stride - 1) / stride : 0)
+                                       : (ntiles - (int)blockIdx.x * NWG + stride - 1) / stride;
+        bool drain_due = false;
         int tile = tile0;
-        for (; tile < ntiles; tile += stride) {
+        for (int it = 0; it < iters_cta; ++it, tile += stride) {
+          if (tile < ntiles) {
             const unsigned gp = own.g;                            // == tile * kTile + t
             const bool valid = gp < npx;
             const int b = valid ? own.b : 0;
@@ -565,6 +640,13 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
                 else issue_ts3<CFG::N(1), CFG::K(1)>(ddu, xlu + 32, xlu + 48, swt + CFG::w_off(1));
                 mma_commit(done);
             });
+            // A due drain runs HERE, one iteration late: the previous tile's weight-gradient MMAs were issued more
+            // than a microsecond ago (waiting for them at the end of their own iteration cost ~0.7 us per drain), the
+            // dgrad MMAs issued above run underneath, and nobody issues into the accumulators before stage_tail.
+            if (kDrainDeferred && drain_due) {
+                drain();
+                drain_due = false;
+            }
 
             auto stage_tail = [&]() {
                 wait_count(wfree, wseen, nstage + wlag);
@@ -585,7 +667,7 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
                 for (int j = 0; j < LAST; ++j) stage_b<L::SUBB>(sc, 24 + j, dz[j]);
                 if constexpr (NW == 1) stage_a_from_tmem32<L::ALO>(sc, 0, xh);
                 fence_smem_to_async();
-                handoff(bid + 3 + half, 64, lead_pair, stg, [&]() { issue_wt(tbase); });          // WT(half)
+                handoff(bid + 3 + half, 64, lead_pair, stg, [&]() { issue_wt(tacc); });           // WT(half)
             };
             auto gradx_epilogue = [&]() {
                 done_wait();
@@ -651,7 +733,7 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
                     stage_a_from_tmem32<L::ALO>(sc, 0, xh);
                     stage_a_from_tmem32<L::ALO>(sc, 32, xh + 32);
                     fence_smem_to_async();
-                    handoff(bid + 3 + half, 64, lead_pair, stg, [&]() { issue_wt(tbase + 64); });   // WX(half)
+                    handoff(bid + 3 + half, 64, lead_pair, stg, [&]() { issue_wt(tacc + 64); });    // WX(half)
                 };
 #pragma unroll 1
                 for (int ph = 0; ph < 2; ++ph) {
@@ -664,32 +746,33 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
                     else gradx_epilogue();
                 }
             }
+          } else if (drain_due) {                                 // no tile of my own any more: still join the CTA's drain
+            drain();
+            drain_due = false;
+          }
+          drain_due = (it + 1) % fa.drain_every == 0;
+          if (!kDrainDeferred && drain_due) {
+            drain();
+            drain_due = false;
+          }
         }
-        // every weight-gradient MMA of this warpgroup has completed before the accumulators are read
-        wait_count(wfree, wseen, nstage);
+        drain();                                                  // whatever the last iterations accumulated
+        // ---- drained sums -> shared memory (the staging buffers are idle: the last drain waited for every MMA).
+        // Row m of a job sat in TMEM lane m; the hi rows and the remainder rows of the same channel are summed below.
+        if (L::PERWG || g < 2) {
+            // per-warpgroup sets: one [NJOBS][128][33] block per warpgroup, summed by the extraction below
+            // (a warpgroup may get here while another one still stages: each writes into its OWN idle staging buffers)
+            float *scr = reinterpret_cast<float *>(stage + (L::PERWG ? (size_t)g * L::NSUB * L::SUB : 0));
+#pragma unroll
+            for (int job = 0; job < L::NJOBS; ++job)
+#pragma unroll
+                for (int j = 0; j < DRC; ++j) scr[(job * kTile + t) * 33 + (L::PERWG ? 0 : g * 16) + j] = wacc[job][j];
+        }
     }
-    fence_before_sync();
-    __syncthreads();
-    fence_after_sync();
-
-    // ---- accumulators -> this CTA's partial weight gradients. Row m of a job sits in TMEM lane m; the hi
-    // rows (0..63) and the remainder rows (64..127) of the same channel are summed, and so are the hi
-    // and remainder column halves.
     constexpr int SP = 33;
-    float *scratch = reinterpret_cast<float *>(stage);            // [NJOBS][128][SP], staging is idle now
-    if (tid < kTile) {
-#pragma unroll
-        for (int job = 0; job < L::NJOBS; ++job) {
-            uint32_t r0[32], r1[32];
-            const uint32_t addr = tbase + ((uint32_t)((tid >> 5) * 32) << 16) + job * 64;
-            tmem_ld<32>(addr, r0);
-            tmem_ld<32>(addr + 32, r1);
-            wait_ld();
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-                scratch[(job * kTile + tid) * SP + j] = __uint_as_float(r0[j]) + __uint_as_float(r1[j]);
-        }
-    }
+    constexpr int SCR_SETS = L::PERWG ? NWG : 1, SCR_SET = L::PERWG ? L::NSUB * L::SUB / 4 : 0;   // floats between the sets
+    static_assert((size_t)L::NJOBS * kTile * SP * sizeof(float) <= (size_t)L::NSUB * L::SUB, "a set fits one warpgroup's staging");
+    float *scratch = reinterpret_cast<float *>(stage);            // [SCR_SETS][NJOBS][128][SP]
     fence_before_sync();
     __syncthreads();
     if (fa.partials != nullptr || fa.atomic_w) {
@@ -712,7 +795,9 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
                 if (e >= K * N) e -= K * N;
                 const int o = e / K, c = e - o * K;
                 const float *s = scratch + (job * kTile + row0 + c) * SP + col0 + o;
-                const float v = s[0] + s[L::ALO_ROWS * SP];
+                float v = s[0] + s[L::ALO_ROWS * SP];
+#pragma unroll
+                for (int q = 1; q < SCR_SETS; ++q) v += s[q * SCR_SET] + s[q * SCR_SET + L::ALO_ROWS * SP];
                 if (fa.atomic_w) atomicAdd(a.gw[l] + e, v);
                 else part[off + e] = v;
             }
@@ -748,6 +833,8 @@ static int launch_fused_cfg(const ChainParams &cp, const TcArgs &a, char *ws, in
     fa.partials = want_w && deterministic ? partials : nullptr;
     for (int l = 0; l < BTS_MAX_LAYERS; ++l) fa.a.gw[l] = l < cp.n_layers ? cp.gW[l] : nullptr;
     fa.total_w = total_w;
+    static const int drain_env = getenv("BTS_WGRAD_DRAIN") ? atoi(getenv("BTS_WGRAD_DRAIN")) : 0;   // tuning hook
+    fa.drain_every = drain_env > 0 ? drain_env : kWgradDrain;
     auto kern = chain_bwd_fused_kernel<CFG, MODE, R, NWG>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::smem_bytes);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));

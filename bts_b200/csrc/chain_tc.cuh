@@ -232,13 +232,15 @@ __device__ __forceinline__ void tc_issue_chunk(uint32_t wg_base, const float *sw
     mma_commit(bar);
 }
 
-template <class CFG, int L, int AW, int KOFF, int KC>
+// SUBS: threads per pixel. With SUBS = 2 a tile group is 256 threads: warps w and w + 4 share TMEM lane quarter w and
+// split every epilogue's columns (sub = 0 / 1), which halves the SIMT latency of a tile and doubles the warps per SM.
+template <class CFG, int L, int AW, int KOFF, int KC, int SUBS = 1>
 __device__ __forceinline__ void tc_run_chunk(uint32_t wg_base, const float *sw, uint64_t *bar, uint32_t &phase,
                                              int wg, int t)
 {
     wait_st();
     fence_before_sync();
-    named_bar_sync(1 + wg, kTile);
+    named_bar_sync(1 + wg, SUBS * kTile);
     if (t == 0) {                                                 // t: warp index inside the warpgroup, made warp-uniform once by the kernel
         if (elect_one()) {
             fence_after_sync();
@@ -252,14 +254,16 @@ __device__ __forceinline__ void tc_run_chunk(uint32_t wg_base, const float *sw, 
 }
 
 // channels [C0, C0+KC) of a_{L+1} = ELU(D[C0 ..]) -> (hi, lo) -> A columns [0, KC); optionally to the stash rows
-template <class CFG, int L, int AW, int C0, int KC, bool SPILL>
-__device__ __forceinline__ void tc_epilogue_chunk(uint32_t lane_addr, float *act_gp, long long npx_pad, bool store)
+template <class CFG, int L, int AW, int C0, int KC, bool SPILL, int SUBS = 1>
+__device__ __forceinline__ void tc_epilogue_chunk(uint32_t lane_addr, float *act_gp, long long npx_pad, bool store, int sub = 0)
 {
+    static_assert((KC / SUBS) % 16 == 0, "every sub-thread takes whole 16-column steps");
     float *dst = SPILL ? act_gp + (size_t)(BwdRows<CFG>::row(L + 1) + C0) * npx_pad : nullptr;
     // rolled: the wide chains run two to five tiles per warpgroup, so their straight-line code is fetched cold
     // (instruction-cache misses were the top stall of the 8x8 stage's forward when this was unrolled)
+    const int nb = sub * (KC / SUBS), ne = nb + KC / SUBS;
 #pragma unroll 1
-    for (int n0 = 0; n0 < KC; n0 += 16) {
+    for (int n0 = nb; n0 < ne; n0 += 16) {
         uint32_t r[16], lo[16];
         tmem_ld<16>(lane_addr + 2 * AW + C0 + n0, r);
         wait_ld();
@@ -283,41 +287,67 @@ __device__ __forceinline__ void tc_epilogue_chunk(uint32_t lane_addr, float *act
 
 // layer L >= 1 from the previous layer's accumulator: K/AW rounds of (epilogue chunk, MMAs). The MMAs of
 // round 0 overwrite D[0, N): legal because round 0's epilogue has consumed D[0, AW) and N <= AW.
-template <class CFG, int L, int AW, bool SPILL>
+template <class CFG, int L, int AW, bool SPILL, int SUBS = 1>
 __device__ __forceinline__ void tc_layer_from_d(uint32_t wg_base, uint32_t lane_addr, const float *sw, uint64_t *bar,
-                                                uint32_t &phase, int wg, int t, float *act_gp, long long npx_pad, bool store)
+                                                uint32_t &phase, int wg, int t, float *act_gp, long long npx_pad, bool store,
+                                                int sub = 0)
 {
     constexpr int K = CFG::K(L);
     if constexpr (K <= AW) {
-        tc_epilogue_chunk<CFG, L - 1, AW, 0, K, SPILL>(lane_addr, act_gp, npx_pad, store);
-        tc_run_chunk<CFG, L, AW, 0, K>(wg_base, sw, bar, phase, wg, t);
+        tc_epilogue_chunk<CFG, L - 1, AW, 0, K, SPILL, SUBS>(lane_addr, act_gp, npx_pad, store, sub);
+        tc_run_chunk<CFG, L, AW, 0, K, SUBS>(wg_base, sw, bar, phase, wg, t);
     } else {
         static_assert(K == 2 * AW && CFG::N(L) <= AW, "two rounds, accumulator no wider than one round's inputs");
-        tc_epilogue_chunk<CFG, L - 1, AW, 0, AW, SPILL>(lane_addr, act_gp, npx_pad, store);
-        tc_run_chunk<CFG, L, AW, 0, AW>(wg_base, sw, bar, phase, wg, t);
-        tc_epilogue_chunk<CFG, L - 1, AW, AW, AW, SPILL>(lane_addr, act_gp, npx_pad, store);
-        tc_run_chunk<CFG, L, AW, AW, AW>(wg_base, sw, bar, phase, wg, t);
+        tc_epilogue_chunk<CFG, L - 1, AW, 0, AW, SPILL, SUBS>(lane_addr, act_gp, npx_pad, store, sub);
+        tc_run_chunk<CFG, L, AW, 0, AW, SUBS>(wg_base, sw, bar, phase, wg, t);
+        tc_epilogue_chunk<CFG, L - 1, AW, AW, AW, SPILL, SUBS>(lane_addr, act_gp, npx_pad, store, sub);
+        tc_run_chunk<CFG, L, AW, AW, AW, SUBS>(wg_base, sw, bar, phase, wg, t);
     }
 }
 
-// ---- LPG expansion of this thread's plane (n1..n4) into depth; returns the abs_min key
-template <int R>
-__device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, float n3, float n4,
-                                          unsigned gp, int b_own, int p_own, bool valid, int lane)
+// ---- LPG expansion of this thread's plane (n1..n4) into depth; returns the abs_min key.
+// The FUSED stage is held to 1e-5 of the reference, not to bit-exactness (the standalone kernels in lpg.cu are, and
+// keep IEEE division): per output pixel this is 2 adds for den in the reference's order, one min for abs_min, the clamp
+// and  depth = n4 * rcp(den)  with the hardware reciprocal (relative error 2e-7) -- 10 instructions where IEEE
+// division, integer min keys and a NaN test per pixel took 22; the expansion was 27 % of the 8x8 forward's instructions.
+// NaN: den is NaN only when a plane coefficient is (they are sines / cosines of finite angles otherwise), so NaN is
+// looked for once per low-res pixel.
+__device__ __forceinline__ float rcp_fast(float v)
 {
+    float r;
+    asm("rcp.approx.f32 %0, %1;" : "=f"(r) : "f"(v));
+    return r;
+}
+// clamp of bts.py:168-171 on |den| (den == 0 stays 0 -> inf), then n4 / den
+__device__ __forceinline__ float lpg_depth_fast(float n4, float den, float eps)
+{
+    const float ad = fabsf(den);
+    const float dc = (ad < eps && ad > 0.f) ? copysignf(eps, den) : den;
+    return n4 * rcp_fast(dc);
+}
+__device__ __forceinline__ int lpg_key(float amin, bool nan) { return nan ? (int)0xFFC00000 : __float_as_int(amin); }
+
+// SUBS = 2: sub-thread `sub` writes half of the block: the 16 pixels of half `sub` (R = 8), rows [sub R/2, (sub+1) R/2)
+template <int R, int SUBS = 1>
+__device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, float n3, float n4,
+                                          unsigned gp, int b_own, int p_own, bool valid, int lane, int sub = 0)
+{
+    static_assert(SUBS == 1 || (R % 2) == 0, "two sub-threads split an even number of rows");
     // all index arithmetic is 32-bit: the C ABI rejects more than 2^31 - 1 low-res pixels
-    int key = 0x7f800000;
+    float amin = __int_as_float(0x7f800000);
+    bool nan = false;
     if (a.depth_div != 1.f) n4 = __fdiv_rn(n4, a.depth_div);       // depth / max_depth = (n4 / max_depth) / den
     if constexpr (R == 8) {
         // two 512 B stores per output row and warp: lane L writes columns (L&1)*4..+3 of pixel 16*half + L/2
         const unsigned gp0 = gp - (unsigned)lane;
 #pragma unroll 1
-        for (int half = 0; half < 2; ++half) {
+        for (int half = (SUBS == 2 ? sub : 0); half < (SUBS == 2 ? sub + 1 : 2); ++half) {
             const int src = half * 16 + (lane >> 1);
             const float m1 = __shfl_sync(0xffffffffu, n1, src), m2 = __shfl_sync(0xffffffffu, n2, src);
             const float m3 = __shfl_sync(0xffffffffu, n3, src), m4 = __shfl_sync(0xffffffffu, n4, src);
             const unsigned gs = gp0 + (unsigned)src;
             if (gs < (unsigned)a.npx) {
+                nan |= (m1 != m1) | (m2 != m2) | (m3 != m3);
                 const int b = (int)(gs / (unsigned)a.hw);
                 const int rem = (int)(gs - (unsigned)b * (unsigned)a.hw);
                 const int i = rem / a.w, j = rem - i * a.w;
@@ -335,9 +365,9 @@ __device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, f
                     float *op = reinterpret_cast<float *>(&o);
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
-                        float den = lpg_den(n1u[k], n2v, m3);
-                        key = min(key, absmin_key(den));
-                        op[k] = __fdiv_rn(m4, lpg_clamp(den, a.eps));
+                        const float den = lpg_den(n1u[k], n2v, m3);
+                        amin = fminf(amin, fabsf(den));
+                        op[k] = lpg_depth_fast(m4, den, a.eps);
                     }
                     *reinterpret_cast<float4 *>(out + (size_t)p * Wd) = o;
                     if ((p & 3) == 0 && ds != nullptr) ds[(size_t)(p >> 2) * (2 * a.w)] = op[0];   // rows 0, 4; cols 0, 4
@@ -345,6 +375,7 @@ __device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, f
             }
         }
     } else if (valid) {
+        nan = (n1 != n1) | (n2 != n2) | (n3 != n3);
         const int b = b_own, rem = p_own;
         const int i = rem / a.w, j = rem - i * a.w;
         const int Wd = a.w * R;
@@ -354,13 +385,14 @@ __device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, f
         for (int k = 0; k < R; ++k) n1u[k] = __fmul_rn(n1, lpg_offset(k, R));
 #pragma unroll
         for (int p = 0; p < R; ++p) {
+            if (SUBS == 2 && (p / (R / 2 > 0 ? R / 2 : 1)) != sub) continue;
             const float n2v = __fmul_rn(n2, lpg_offset(p, R));
             float o[R];
 #pragma unroll
             for (int k = 0; k < R; ++k) {
-                float den = lpg_den(n1u[k], n2v, n3);
-                key = min(key, absmin_key(den));
-                o[k] = __fdiv_rn(n4, lpg_clamp(den, a.eps));
+                const float den = lpg_den(n1u[k], n2v, n3);
+                amin = fminf(amin, fabsf(den));
+                o[k] = lpg_depth_fast(n4, den, a.eps);
             }
             float *row = out + (size_t)p * Wd;
             if constexpr (R == 4) {
@@ -377,7 +409,7 @@ __device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, f
             }
         }
     }
-    return key;
+    return lpg_key(amin, nan);
 }
 
 // ---- upstream gradient of one low-res pixel in fused mode: reduce grad_depth over its R x R block

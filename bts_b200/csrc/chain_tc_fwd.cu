@@ -14,11 +14,18 @@
 
 namespace bts {
 
+#ifndef BTS_WIDE_SUBS
+#define BTS_WIDE_SUBS 2
+#endif
+constexpr int kWideSubs = BTS_WIDE_SUBS;   // threads per pixel in the 128-channel chains' forward
+
 // PREFETCH: the next tile's features travel global -> shared with cp.async while the current tile is
 // computed (needs D0*512 B of shared memory per warpgroup next to the weight images).
-template <class CFG, int R, bool FINAL, int NWG, bool PREFETCH, int AW>
-__global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
+// SUBS: threads per pixel (chain_tc.cuh): 2 for the 128-channel chains, whose tiles are few and long.
+template <class CFG, int R, bool FINAL, int NWG, bool PREFETCH, int AW, int SUBS>
+__global__ void __launch_bounds__(NWG * SUBS * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
 {
+    constexpr int GT = SUBS * kTile;                              // threads of one tile group
     constexpr int LAST = FINAL ? 1 : 3;
     constexpr int PACK = CFG::pack_floats(LAST);
     constexpr int NMAX = CFG::nmax();
@@ -36,8 +43,9 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
     uint32_t *slot = reinterpret_cast<uint32_t *>(bars + NWG);
     float *xs_all = smem + PACK + (8 * NWG + 16 + 15) / 16 * 4;   // [NWG][D0][128] when PREFETCH (16-byte aligned)
 
-    const int tid = threadIdx.x, wg = uniform(tid / kTile), t = tid % kTile, lane = tid & 31;
-    const int lt = uniform(t >> 5);                               // warp index inside the warpgroup; warp 0 issues the MMAs
+    const int tid = threadIdx.x, wg = uniform(tid / GT), tt = tid % GT, t = tt % kTile, lane = tid & 31;
+    const int sub = uniform(tt / kTile);                          // which half of the columns / rows this thread takes
+    const int lt = uniform(tt >> 5);                              // warp index inside the tile group; warp 0 issues the MMAs
     uint64_t *bar = &bars[wg];
     uint32_t phase = 0;
     const float *tw = sw + CFG::tail_off();
@@ -55,10 +63,10 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
     // needs no barrier wider than the warp; otherwise a warp copies 512 contiguous bytes of one channel per
     // instruction (thread t: pixels 4(t%32)..+3 of channels t/32, t/32+4, ...), which DRAM prefers for wider
     // chains, and the warpgroup synchronises on a named barrier.
-    constexpr bool WARP_PRIVATE = D0 <= 32;
+    constexpr bool WARP_PRIVATE = D0 <= 32 && SUBS == 1;
     auto tile_sync = [&]() {
         if constexpr (WARP_PRIVATE) __syncwarp();
-        else named_bar_sync(1 + wg, kTile);
+        else named_bar_sync(1 + wg, GT);
     };
     // (image, pixel) of this thread's own pixel and of the 4-pixel group it copies, advanced by the same number of
     // pixels every iteration: one division per kernel (dq, dr) instead of two per position and tile
@@ -88,18 +96,19 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
     const int pq = WARP_PRIVATE ? (((t >> 5) << 3) | (lane & 7)) : (t & 31);
     PixPos own = pos_at((unsigned)tile0 * kTile + t), quad = pos_at((unsigned)tile0 * kTile + 4 * pq);
     auto prefetch = [&](int tl) {                                 // fetches the tile `quad` points at
-        const int q = pq, cw = WARP_PRIVATE ? (lane >> 3) : (t >> 5);
+        const int q = pq, cw = WARP_PRIVATE ? (lane >> 3) : (tt >> 5);
+        constexpr int CWN = 4 * SUBS;                             // channels copied per pass of the tile group
         const bool ok = tl < ntiles && quad.g < npx;
         const int bn = ok ? quad.b : 0;
         const int pn = ok ? quad.p : 0;
         const float *xq = a.x + ((size_t)bn * D0 + cw) * a.hw + pn;
         const uint32_t dst = smem_u32(xs_wg + cw * kTile + 4 * q);
 #pragma unroll
-        for (int i = 0; i < D0 / 4; ++i) cp_async16(dst + i * 4 * kTile * 4, xq + (size_t)i * 4 * a.hw, ok);
+        for (int i = 0; i < D0 / CWN; ++i) cp_async16(dst + i * CWN * kTile * 4, xq + (size_t)i * CWN * a.hw, ok);
         cp_async_commit();
     };
     if constexpr (PREFETCH) prefetch(tile0);                      // in flight while the weight images are packed
-    tc_pack_to_smem<CFG>(a.W, sw, LAST, tid, NWG * kTile);
+    tc_pack_to_smem<CFG>(a.W, sw, LAST, tid, NWG * GT);
     fence_smem_to_async();
     if (tid < 32) tmem_alloc(slot, 512);
     if (tid == 0) {
@@ -129,9 +138,11 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
         // channels [C0, C0+KC0) of the features -> (hi, lo) -> TMEM A operand
         auto load_x = [&](auto c0_tag) {
             constexpr int C0 = decltype(c0_tag)::value;
+            constexpr int KS = KC0 / SUBS;                        // channels of this round per sub-thread
+            const int cb = sub * KS;
             if constexpr (PREFETCH) {
 #pragma unroll 1
-                for (int c0 = 0; c0 < KC0; c0 += 16) {
+                for (int c0 = cb; c0 < cb + KS; c0 += 16) {
                     uint32_t hi[16], lo[16];
 #pragma unroll
                     for (int j = 0; j < 16; j += 2) {
@@ -145,10 +156,11 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
                 }
             } else {
                 // up to 64 independent coalesced loads in flight per thread (a whole K round of the 128-channel chains:
-                // with eight warps per SM every DRAM round trip saved is ~1 us of the tile)
-                constexpr int LB = KC0 >= 64 ? 64 : 32;
+                // with few warps per SM every DRAM round trip saved is ~1 us of the tile)
+                constexpr int LB = KS >= 64 ? 64 : 32;
+                static_assert(KS % 32 == 0, "whole 32-channel steps per sub-thread");
 #pragma unroll 1
-                for (int c0 = 0; c0 < KC0; c0 += LB) {
+                for (int c0 = cb; c0 < cb + KS; c0 += LB) {
                     uint32_t hi[LB];
 #pragma unroll
                     for (int j = 0; j < LB; ++j) hi[j] = valid ? __float_as_uint(__ldg(xp + (size_t)(C0 + c0 + j) * a.hw)) : 0u;
@@ -173,18 +185,18 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
         }
         load_x(std::integral_constant<int, 0>{});
         if constexpr (D0 > KC0) {
-            tc_run_chunk<CFG, 0, AW, 0, KC0>(wg_base, sw, bar, phase, wg, lt);
+            tc_run_chunk<CFG, 0, AW, 0, KC0, SUBS>(wg_base, sw, bar, phase, wg, lt);
             load_x(std::integral_constant<int, KC0>{});
         }
         if constexpr (PREFETCH) {
             tile_sync();                                          // the staged tile has been read by everyone who shares it
             prefetch(tile + stride);
         }
-        tc_run_chunk<CFG, 0, AW, D0 - KC0, KC0>(wg_base, sw, bar, phase, wg, lt);
+        tc_run_chunk<CFG, 0, AW, D0 - KC0, KC0, SUBS>(wg_base, sw, bar, phase, wg, lt);
         // wide layers
-        if constexpr (CFG::NW > 1) tc_layer_from_d<CFG, 1, AW, SPILL>(wg_base, lane_addr, sw, bar, phase, wg, lt, act_gp, a.stash_npp, stash);
-        if constexpr (CFG::NW > 2) tc_layer_from_d<CFG, 2, AW, SPILL>(wg_base, lane_addr, sw, bar, phase, wg, lt, act_gp, a.stash_npp, stash);
-        if constexpr (CFG::NW > 3) tc_layer_from_d<CFG, 3, AW, SPILL>(wg_base, lane_addr, sw, bar, phase, wg, lt, act_gp, a.stash_npp, stash);
+        if constexpr (CFG::NW > 1) tc_layer_from_d<CFG, 1, AW, SPILL, SUBS>(wg_base, lane_addr, sw, bar, phase, wg, lt, act_gp, a.stash_npp, stash, sub);
+        if constexpr (CFG::NW > 2) tc_layer_from_d<CFG, 2, AW, SPILL, SUBS>(wg_base, lane_addr, sw, bar, phase, wg, lt, act_gp, a.stash_npp, stash, sub);
+        if constexpr (CFG::NW > 3) tc_layer_from_d<CFG, 3, AW, SPILL, SUBS>(wg_base, lane_addr, sw, bar, phase, wg, lt, act_gp, a.stash_npp, stash, sub);
         float a16[kTailIn], a8[kTailMid], z[LAST];
         {
             uint32_t r[16];
@@ -195,30 +207,32 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
         }
         tail_forward<LAST, true, false>(tw, a16, a8, z);           // no scheduling fences: the weight loads float above the FMAs
         if constexpr (kStashCfg<CFG>) {
-            if (stash) {
+            if (stash && (SUBS == 1 || sub == 0)) {              // both sub-threads hold the tail: one stores a16, the other a8
                 float *d16 = act_gp + (size_t)BwdRows<CFG>::row(CFG::NW) * a.stash_npp;
 #pragma unroll
                 for (int j = 0; j < kTailIn; ++j) d16[(size_t)j * a.stash_npp] = a16[j];
+            }
+            if (stash && (SUBS == 1 || sub == 1)) {
                 float *d8 = act_gp + (size_t)BwdRows<CFG>::row8() * a.stash_npp;
 #pragma unroll
                 for (int j = 0; j < kTailMid; ++j) d8[(size_t)j * a.stash_npp] = a8[j];
             }
         }
         if constexpr (FINAL) {
-            if (valid) a.out[gp] = sigmoidf(z[0]);
+            if (valid && sub == 0) a.out[gp] = sigmoidf(z[0]);
         } else {
             const PlaneFwd pl = plane_from_logits(z[0], z[1], z[2], a.max_depth);
-            if (a.out != nullptr && valid) {
+            if (a.out != nullptr && valid && sub == 0) {
                 float *o = a.out + (size_t)b * 4 * a.hw + p;
                 o[0] = pl.n1; o[(size_t)a.hw] = pl.n2; o[(size_t)2 * a.hw] = pl.n3; o[(size_t)3 * a.hw] = pl.n4;
             }
             if constexpr (kStashCfg<CFG>) {
-                if (stash && a.stash_pe != nullptr) {
+                if (stash && a.stash_pe != nullptr && sub == SUBS - 1) {
                     float *o = a.stash_pe + (size_t)b * 4 * a.hw + p;
                     o[0] = pl.n1; o[(size_t)a.hw] = pl.n2; o[(size_t)2 * a.hw] = pl.n3; o[(size_t)3 * a.hw] = pl.n4;
                 }
             }
-            if (a.depth != nullptr) key = min(key, lpg_expand<R>(a, pl.n1, pl.n2, pl.n3, pl.n4, gp, b, p, valid, lane));
+            if (a.depth != nullptr) key = min(key, lpg_expand<R, (R % 2 == 0 ? SUBS : 1)>(a, pl.n1, pl.n2, pl.n3, pl.n4, gp, b, p, valid && (R % 2 == 0 || sub == 0), lane, sub));
         }
     }
     if constexpr (!FINAL) {
@@ -233,7 +247,7 @@ __global__ void __launch_bounds__(NWG * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
     if (tid < 32) tmem_dealloc(tbase, 512);
 }
 
-template <class CFG, int R, bool FINAL, int NWG, int AW>
+template <class CFG, int R, bool FINAL, int NWG, int AW, int SUBS>
 static int launch_one(const ChainParams &cp, const TcArgs &a, int sms, cudaStream_t s)
 {
     constexpr int LAST = FINAL ? 1 : 3;
@@ -242,7 +256,7 @@ static int launch_one(const ChainParams &cp, const TcArgs &a, int sms, cudaStrea
     constexpr bool CAN_PREFETCH = base + xs_bytes <= 227 * 1024;
     const bool prefetch = CAN_PREFETCH && a.x_vec16;
     const size_t smem = base + (prefetch ? xs_bytes : 0);
-    auto kern = prefetch ? chain_tc_fwd_kernel<CFG, R, FINAL, NWG, CAN_PREFETCH, AW> : chain_tc_fwd_kernel<CFG, R, FINAL, NWG, false, AW>;
+    auto kern = prefetch ? chain_tc_fwd_kernel<CFG, R, FINAL, NWG, CAN_PREFETCH, AW, SUBS> : chain_tc_fwd_kernel<CFG, R, FINAL, NWG, false, AW, SUBS>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     const long long ntiles = (a.npx + kTile - 1) / kTile;
@@ -250,12 +264,10 @@ static int launch_one(const ChainParams &cp, const TcArgs &a, int sms, cudaStrea
     if (grid > sms) grid = sms;
     TcArgs aa = a;
     tc_set_weights(aa, cp);
-    kern<<<(unsigned)grid, NWG * kTile, smem, s>>>(aa);
+    kern<<<(unsigned)grid, NWG * SUBS * kTile, smem, s>>>(aa);
     return check_launch("chain_tc_fwd");
 }
 
-// header bytes at the start of the workspace (nothing is packed in HBM any more: every CTA builds its operand
-// images in shared memory); kept as a 2 x 128 B aligned prefix so that the scratch rows start 256-byte aligned
 size_t tc_pack_bytes() { return 128; }
 
 bool tc_supported(const ChainParams &cp)
@@ -264,23 +276,23 @@ bool tc_supported(const ChainParams &cp)
            cfg_matches<Cfg64_32>(cp) || cfg_matches<Cfg32_32>(cp) || cfg_matches<Cfg32_16>(cp);
 }
 
-template <class CFG, int NWG, int AW = CFG::kmax()>
+template <class CFG, int NWG, int AW = CFG::kmax(), int SUBS = 1>
 static int dispatch_r(const ChainParams &cp, const TcArgs &a, int r, int sms, cudaStream_t s)
 {
-    if (cp.is_final) return launch_one<CFG, 1, true, NWG, AW>(cp, a, sms, s);
+    if (cp.is_final) return launch_one<CFG, 1, true, NWG, AW, SUBS>(cp, a, sms, s);
     switch (r) {
-    case 8: return launch_one<CFG, 8, false, NWG, AW>(cp, a, sms, s);
-    case 4: return launch_one<CFG, 4, false, NWG, AW>(cp, a, sms, s);
-    case 2: return launch_one<CFG, 2, false, NWG, AW>(cp, a, sms, s);
-    default: return launch_one<CFG, 1, false, NWG, AW>(cp, a, sms, s);   // r == 1, or plane_eq only
+    case 8: return launch_one<CFG, 8, false, NWG, AW, SUBS>(cp, a, sms, s);
+    case 4: return launch_one<CFG, 4, false, NWG, AW, SUBS>(cp, a, sms, s);
+    case 2: return launch_one<CFG, 2, false, NWG, AW, SUBS>(cp, a, sms, s);
+    default: return launch_one<CFG, 1, false, NWG, AW, SUBS>(cp, a, sms, s);   // r == 1, or plane_eq only
     }
 }
 
 // r = 0: no LPG (reduction only). Returns BTS_ERR_UNSUPPORTED when the chain is not covered.
 int launch_chain_tc_fwd(const ChainParams &cp, const TcArgs &a, int r, int sms, cudaStream_t s)
 {
-    if (cfg_matches<Cfg128_128>(cp)) return dispatch_r<Cfg128_128, 2, 64>(cp, a, r, sms, s);
-    if (cfg_matches<Cfg128_64>(cp)) return dispatch_r<Cfg128_64, 2, 64>(cp, a, r, sms, s);
+    if (cfg_matches<Cfg128_128>(cp)) return dispatch_r<Cfg128_128, 2, 64, kWideSubs>(cp, a, r, sms, s);
+    if (cfg_matches<Cfg128_64>(cp)) return dispatch_r<Cfg128_64, 2, 64, kWideSubs>(cp, a, r, sms, s);
     if (cfg_matches<Cfg64_64>(cp)) return dispatch_r<Cfg64_64, 2>(cp, a, r, sms, s);
     if (cfg_matches<Cfg64_32>(cp)) return dispatch_r<Cfg64_32, 3>(cp, a, r, sms, s);
     if (cfg_matches<Cfg32_32>(cp)) return dispatch_r<Cfg32_32, 4>(cp, a, r, sms, s);

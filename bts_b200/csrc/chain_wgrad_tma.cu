@@ -16,6 +16,7 @@
 #include <cuda.h>
 #include <cudaTypedefs.h>
 
+#include <cstdlib>
 #include <cstring>
 
 #include "chain_tc.cuh"
@@ -32,7 +33,18 @@ constexpr int kWtRingBytes = 225 * 1024;   // all of the 227 KB a CTA may have, 
 // plan: 5 landing slots for the 8x8 chain, 7 for the 4x4 chain.
 constexpr int kWtMaxOps = 3;                 // box loads per job: [x] [activation rows] [delta rows]
 constexpr int kWtMaxMaps = 6;                // distinct (tensor, box height) pairs
-constexpr int kWtThreads = 192;
+constexpr int kWtThreads = 320;              // producer, issuer, 4 splitter warps, 4 drainer warps
+// The tensor core accumulates into TMEM with round-toward-zero (see kWgradDrain in chain_bwd_fused.cu): an accumulator
+// loses ~3.4e-8 of its magnitude per accumulate step, always toward zero. A CTA therefore works in SEGMENTS of
+// kWtSegChunks 32-pixel chunks (8 steps each into the widest accumulator block; measured at KITTI b16: grad_W error
+// <= 4.7e-6 / 6.7e-6 / 8.6e-6 of peak for 16 / 32 / 64 chunks, where one segment per kernel gave 2.5e-5): at a
+// segment's end the splitter warps add the accumulators to this CTA's partial sums in the workspace (every element has
+// one owner thread: plain read-modify-write, L2-resident), and the next segment's first MMAs overwrite the
+// accumulators (accumulate flag 0) instead of adding to them.
+#ifndef BTS_WT_SEG_CHUNKS
+#define BTS_WT_SEG_CHUNKS 16
+#endif
+constexpr int kWtSegChunks = BTS_WT_SEG_CHUNKS;
 
 struct WtOp {
     unsigned short src_row;                  // first source row (channel) of the box
@@ -54,7 +66,8 @@ struct WtExtract {                           // layer l: D_job[row0 + k][col0 + 
 struct WtPlan {
     WtJob jobs[3];
     WtExtract ex[BTS_MAX_LAYERS];
-    int njobs, nlayers, total_w, hw_pad, nmaps, nslots, slot_bytes;
+    int njobs, nlayers, total_w, hw_pad, nmaps, nslots, slot_bytes, seg_chunks;
+    int set_cols;                            // > 0: two accumulator sets this many TMEM columns apart, alternating per segment
     long long nchunks;                       // 32-pixel chunks of the padded pixel axis
     float *partials;                         // [gridDim.x][total_w]
 };
@@ -68,8 +81,9 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
     const uint32_t slot_bytes = (uint32_t)pl.slot_bytes;
     uint64_t *bars = reinterpret_cast<uint64_t *>(slots + kWtRingBytes);
     uint64_t *full = bars, *split = bars + kWtMaxSlots, *empty = bars + 2 * kWtMaxSlots, *fin = bars + 3 * kWtMaxSlots;
-    uint64_t *lofree = fin + 1;                                   // [2]: the MMAs that read a remainder buffer are done
-    uint32_t *slot_tmem = reinterpret_cast<uint32_t *>(lofree + 2);
+    uint64_t *lofree = fin + 2;                                   // [2]: the MMAs that read a remainder buffer are done
+    uint64_t *drained = lofree + 2;                               // [2]: the splitters have read an accumulator set
+    uint32_t *slot_tmem = reinterpret_cast<uint32_t *>(drained + 2);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
     if (tid == 0) {
@@ -79,8 +93,11 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
             mbar_init(empty + s, 1);
         }
         mbar_init(fin, 1);
+        mbar_init(fin + 1, 1);
         mbar_init(lofree, 1);
         mbar_init(lofree + 1, 1);
+        mbar_init(drained, 128);
+        mbar_init(drained + 1, 128);
         fence_mbar_init();
         for (int i = 0; i < pl.nmaps; ++i) tma_prefetch_desc(&maps.m[i]);
     }
@@ -89,22 +106,15 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
     __syncthreads();
     fence_after_sync();
     const uint32_t tbase = (uint32_t)uniform((int)*slot_tmem);
-    const uint32_t lane_addr = tbase + ((uint32_t)((warp & 3) * 32) << 16);   // warps 2..5 cover all four lane quarters
-    if (warp >= 2) {
-        uint32_t z[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) z[j] = 0u;
-#pragma unroll 1
-        for (int c0 = 0; c0 < 512; c0 += 32) tmem_st<32>(lane_addr + c0, z);
-        wait_st();
-    }
-    fence_before_sync();
-    __syncthreads();
-    fence_after_sync();
-
+    const uint32_t lane_addr = tbase + ((uint32_t)((warp & 3) * 32) << 16);   // a warp reaches TMEM lane quarter warp % 4
+    // (no zero fill of the accumulators: the first MMAs of every segment run with the accumulate flag off)
     pdl_trigger();
     pdl_wait();                                   // the delta rows come from the dgrad kernel launched just before
     const uint32_t slot0 = smem_u32(slots);
+    // balanced segments: a CTA with 33 chunks and a limit of 32 runs 17 + 16, not 32 + 1 (a drain on the kernel's tail)
+    const int my_chunks = (int)((pl.nchunks - blockIdx.x + gridDim.x - 1) / gridDim.x);
+    const int my_segs = (my_chunks + pl.seg_chunks - 1) / pl.seg_chunks;
+    const int seg_len = my_segs > 0 ? (my_chunks + my_segs - 1) / my_segs : 1;
     if (warp == 0) {
         if (lane == 0) {                                          // ---- producer
             int s = 0;
@@ -132,9 +142,17 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
         __syncwarp();
     } else if (warp == 1) {
         {                                                         // ---- MMA issuer (whole warp waits, one elected lane issues)
-            int s = 0;
+            int s = 0, ci = 0;
             uint32_t n = 0, it = 0;
+            // Segment g accumulates into set g % nsets (nsets = 2 when two sets fit the 512 TMEM columns, else 1). Before
+            // it overwrites a set the issuer waits until the splitters have read the segment that used it last.
+            const int nsets = pl.set_cols > 0 ? 2 : 1;
+            int seg = 0;
             for (long long ck = blockIdx.x; ck < pl.nchunks; ck += gridDim.x) {
+                const uint32_t keep = (ci % seg_len) != 0;   // 0: first chunk of a segment overwrites the accumulators
+                const int set = seg % nsets;
+                if (!keep && seg >= nsets) mbar_wait(drained + set, (uint32_t)(seg / nsets - 1) & 1);
+                const uint32_t tset = tbase + (uint32_t)(set * pl.set_cols);
                 for (int j = 0; j < pl.njobs; ++j, ++it) {
                     mbar_wait(split + s, n & 1);
                     fence_after_sync();
@@ -142,12 +160,13 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
                         const WtJob &job = pl.jobs[j];
                         const uint32_t base = slot0 + s * slot_bytes, lob = slot0 + (nslots + (it & 1)) * slot_bytes;
                         const uint32_t a_hi = base, b_hi = base + 16384u, a_lo = lob, b_lo = lob + 16384u;
-                        const uint32_t d = tbase + job.tmem_col;
+                        const uint32_t d = tset + job.tmem_col;
                         const uint32_t id = idesc_tf32(128, job.nb, 0, 0);
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks) {          // D[:, 0:nb] = A_hi B_hi + A_lo B_hi, D[:, nb:2nb] = A_hi B_lo
-                            mma_tf32_ss(d, smem_desc_sw128(a_hi + ks * 32), smem_desc_sw128(b_hi + ks * 32), id, 1);
-                            mma_tf32_ss(d + job.nb, smem_desc_sw128(a_hi + ks * 32), smem_desc_sw128(b_lo + ks * 32), id, 1);
+                            const uint32_t acc = ks == 0 ? keep : 1u;
+                            mma_tf32_ss(d, smem_desc_sw128(a_hi + ks * 32), smem_desc_sw128(b_hi + ks * 32), id, acc);
+                            mma_tf32_ss(d + job.nb, smem_desc_sw128(a_hi + ks * 32), smem_desc_sw128(b_lo + ks * 32), id, acc);
                             mma_tf32_ss(d, smem_desc_sw128(a_lo + ks * 32), smem_desc_sw128(b_hi + ks * 32), id, 1);
                         }
                         mma_commit(empty + s);
@@ -156,11 +175,69 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
                     __syncwarp();
                     if (++s == nslots) { s = 0; ++n; }
                 }
+                ++ci;
+                const bool last = ck + gridDim.x >= pl.nchunks;
+                if (last || ci % seg_len == 0) {                  // segment end: hand the set to the splitters
+                    if (elect_one()) mma_commit(fin + set);
+                    __syncwarp();
+                    ++seg;
+                }
             }
-            if (elect_one()) mma_commit(fin);
         }
         __syncwarp();
-    } else {                                                      // ---- splitters
+    } else if (warp >= 6) {                                       // ---- drainers (warps 6..9 cover the four TMEM lane quarters)
+        // They sleep on the segment barriers, so the splitters keep splitting and the MMAs run on into the other
+        // accumulator set while a finished segment is added to the partial sums.
+        float *part = pl.partials + (size_t)blockIdx.x * pl.total_w;
+        const int m = (warp & 3) * 32 + lane;
+        // accumulators -> this CTA's partial sums (row m of a job = TMEM lane m); segments after the first add
+        const int nsets = pl.set_cols > 0 ? 2 : 1;
+        auto drain = [&](bool add, uint32_t lane_addr) {
+            for (int l = 0; l < pl.nlayers; ++l) {
+                const WtExtract ex = pl.ex[l];
+                const WtJob &job = pl.jobs[ex.job];
+                const int k = m - ex.row0;
+                const bool mine = k >= 0 && k < ex.K;
+                auto put = [&](int n, float v) {
+                    float *dst = part + ex.dst_off + (size_t)n * ex.K + k;
+                    // later segments add with a fire-and-forget reduction (no L2 round trip on the critical path).
+                    // One owner thread per element and in-order segments: the sum's order is fixed.
+                    if (add) asm volatile("red.global.add.f32 [%0], %1;" ::"l"(dst), "f"(v) : "memory");
+                    else *dst = v;
+                };
+                int n0 = 0;
+                for (; n0 + 32 <= ex.N; n0 += 32) {               // 32 columns per TMEM round trip
+                    uint32_t r0[32], r1[32];
+                    tmem_ld<32>(lane_addr + job.tmem_col + ex.col0 + n0, r0);
+                    tmem_ld<32>(lane_addr + job.tmem_col + job.nb + ex.col0 + n0, r1);
+                    wait_ld();
+                    if (mine) {
+#pragma unroll
+                        for (int jn = 0; jn < 32; ++jn) put(n0 + jn, __uint_as_float(r0[jn]) + __uint_as_float(r1[jn]));
+                    }
+                }
+                for (; n0 < ex.N; n0 += 8) {
+                    uint32_t r0[8], r1[8];
+                    tmem_ld<8>(lane_addr + job.tmem_col + ex.col0 + n0, r0);
+                    tmem_ld<8>(lane_addr + job.tmem_col + job.nb + ex.col0 + n0, r1);
+                    wait_ld();
+                    if (mine) {
+#pragma unroll
+                        for (int jn = 0; jn < 8; ++jn)
+                            if (n0 + jn < ex.N) put(n0 + jn, __uint_as_float(r0[jn]) + __uint_as_float(r1[jn]));
+                    }
+                }
+            }
+        };
+        for (int seg = 0; seg < my_segs; ++seg) {
+            const int set = seg % nsets;
+            mbar_wait(fin + set, (uint32_t)(seg / nsets) & 1);
+            fence_after_sync();
+            drain(seg > 0, lane_addr + (uint32_t)(set * pl.set_cols));
+            fence_before_sync();
+            mbar_arrive(drained + set);                           // the issuer may overwrite this set now
+        }
+    } else {                                                      // ---- splitters (warps 2..5)
         const int st = tid - 64;
         int s = 0;
         uint32_t n = 0, it = 0;
@@ -196,29 +273,6 @@ chain_wgrad_tma_kernel(const __grid_constant__ WtMaps maps, const __grid_constan
                 fence_smem_to_async();
                 mbar_arrive(split + s);
                 if (++s == nslots) { s = 0; ++n; }
-            }
-        }
-        // ---- accumulators -> this CTA's partial sums (row m of a job = TMEM lane m)
-        mbar_wait(fin, 0);
-        fence_after_sync();
-        float *part = pl.partials + (size_t)blockIdx.x * pl.total_w;
-        const int m = (warp & 3) * 32 + lane;
-        for (int l = 0; l < pl.nlayers; ++l) {
-            const WtExtract ex = pl.ex[l];
-            const WtJob &job = pl.jobs[ex.job];
-            const int k = m - ex.row0;
-            const bool mine = k >= 0 && k < ex.K;
-            for (int n0 = 0; n0 < ex.N; n0 += 8) {
-                uint32_t r0[8], r1[8];
-                tmem_ld<8>(lane_addr + job.tmem_col + ex.col0 + n0, r0);
-                tmem_ld<8>(lane_addr + job.tmem_col + job.nb + ex.col0 + n0, r1);
-                wait_ld();
-                if (mine) {
-#pragma unroll
-                    for (int jn = 0; jn < 8; ++jn)
-                        if (n0 + jn < ex.N)
-                            part[ex.dst_off + (size_t)(n0 + jn) * ex.K + k] = __uint_as_float(r0[jn]) + __uint_as_float(r1[jn]);
-                }
             }
         }
     }
@@ -354,18 +408,21 @@ int launch_wgrad_tma(const ChainParams &cp, const float *x, const float *act, co
         for (int o = 0; o < job.nops; ++o) job.tx_bytes += job.ops[o].rows * 128;
     }
     if (col > 512) return set_error(BTS_ERR_UNSUPPORTED, "weight-gradient accumulators exceed TMEM");
+    pl.set_cols = col <= 256 ? 256 : 0;
     pl.nlayers = L;
     pl.total_w = woff;
     pl.hw_pad = hw_pad;
     pl.nchunks = npp / 32;
     pl.partials = partials;
+    static const int seg_env = getenv("BTS_WT_SEG_CHUNKS") ? atoi(getenv("BTS_WT_SEG_CHUNKS")) : 0;   // tuning hook
+    pl.seg_chunks = seg_env > 0 ? seg_env : kWtSegChunks;
 
     int max_nb = 8;
     for (int j = 0; j < pl.njobs; ++j) max_nb = pl.jobs[j].nb > max_nb ? pl.jobs[j].nb : max_nb;
     pl.slot_bytes = 16384 + max_nb * 128;
     pl.nslots = kWtRingBytes / pl.slot_bytes - 2;                 // two slots' worth of room are the remainder buffers
     if (pl.nslots > kWtMaxSlots) pl.nslots = kWtMaxSlots;
-    const size_t smem = 1024 + (size_t)kWtRingBytes + 8 * (3 * kWtMaxSlots + 3) + 16;
+    const size_t smem = 1024 + (size_t)kWtRingBytes + 8 * (3 * kWtMaxSlots + 6) + 16;
     cudaError_t e = cudaFuncSetAttribute(chain_wgrad_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     long long grid = pl.nchunks < sms ? pl.nchunks : sms;

@@ -35,35 +35,59 @@ STAGES = [(128, 128, 8, False), (128, 64, 4, False), (64, 32, 2, False), (32, 16
 CASES = [(c, s) for c in CONFIGS for s in STAGES]
 
 
-def _oracle_fp64(x, ws, md, r, final, g):
+def _oracle_fp64(x, ws, md, r, final, g, dtype=torch.float64):
     """fp64 forward + backward of the torch port, one image at a time (bounded host memory); weight gradients are
-    summed over the images exactly as autograd would over the batch."""
+    summed over the images exactly as autograd would over the batch. Returns (out, grad_x, grad_W, abs_min, n4) with
+    n4 the plane distance of every low-res pixel (None for the head)."""
     torch.set_num_threads(os.cpu_count() or 1)
-    wd = [w.double().requires_grad_(True) for w in ws]
-    outs, gxs, amin = [], [], float("inf")
+    wd = [w.to(dtype).requires_grad_(True) for w in ws]
+    outs, gxs, n4s, amin = [], [], [], float("inf")
     for i in range(x.shape[0]):
-        xi = x[i:i + 1].double().requires_grad_(True)
+        xi = x[i:i + 1].to(dtype).requires_grad_(True)
         if final:
             out = tp.chain_forward(xi, wd, md, True)
         else:
-            out, am = tp.stage_forward(xi, wd, md, r)
+            pe = tp.glue(tp.chain_forward(xi, wd, md, False))      # = tp.stage_forward, with plane_eq kept
+            out, am = tp.lpg_forward(pe, r)
             amin = min(amin, float(am.detach()))
-        out.backward(g[i:i + 1].double())
+            n4s.append(pe[:, 3].detach())
+        out.backward(g[i:i + 1].to(dtype))
         outs.append(out.detach())
         gxs.append(xi.grad)
-    return torch.cat(outs).numpy(), torch.cat(gxs).numpy(), [w.grad[:, :, 0, 0].numpy() for w in wd], amin
+    n4 = torch.cat(n4s).numpy() if n4s else None
+    return torch.cat(outs).numpy(), torch.cat(gxs).numpy(), [w.grad[:, :, 0, 0].numpy() for w in wd], amin, n4
 
 
-def _close_peak(a, b, what):
+def _close_peak(a, b, what, own=None):
+    """max|a-b| <= 1e-5 max|b| and L2-relative <= 1e-5 -- or, where the REFERENCE's own fp32 run is further than that from
+    its fp64 run (`own()` -> its fp32 result, computed only when needed: the steep planes of upratio 8 put |den| near
+    zero, and the backward's 1 / den^2 makes a handful of pixels carry the peak), three times the reference's own distance."""
     a = a.detach().cpu().numpy() if isinstance(a, torch.Tensor) else a
     e1, e2 = max_rel_to_peak(a, b), l2_rel(a, b)
-    assert e1 <= RTOL and e2 <= RTOL, (what, "max-rel-to-peak", e1, "l2-rel", e2)
+    if e1 <= RTOL and e2 <= RTOL:
+        return
+    assert own is not None, (what, "max-rel-to-peak", e1, "l2-rel", e2)
+    r32 = own()
+    o1, o2 = max_rel_to_peak(r32, b), l2_rel(r32, b)
+    # 3x: two independent fp32 evaluations of an ill-conditioned quantity each sit about `own` away from fp64, in
+    # unrelated directions, and ours carries the 3xTF32 products' dropped lo*lo terms on top (measured 2.0x at KITTI b16)
+    assert e1 <= max(RTOL, 3 * o1) and e2 <= max(RTOL, 3 * o2), (what, "max-rel-to-peak", e1, "reference fp32's own", o1,
+                                                                  "l2-rel", e2, "reference fp32's own", o2)
 
 
-def _close_depth(a, b, md, what):
+def _close_depth(a, b, md, what, n4, r):
+    """depth = n4 / den with den = n1 u + n2 v + n3 a sum of O(1) terms: fp32 rounding of those terms (ours AND the
+    reference's own fp32 run) is an ABSOLUTE error ~1e-7 of den, i.e. a relative error of depth amplified by 1 / |den|
+    where the plane is steep (|den| << 1, reachable at upratio 8 only). The bar is therefore
+    rtol 1e-5 (+1e-6 max_depth) on depth, loosened by max(1, 1 / |den|) -- which is rtol 1e-5 on the O(1) scale of den --
+    and at most one pixel in 1e5 may need the loosening at all."""
     a = a.detach().cpu().numpy().astype(np.float64)
-    bad = np.abs(a - b) > (1e-6 * md + RTOL * np.abs(b))
+    den = np.repeat(np.repeat(n4, r, 1), r, 2) / b
+    plain = np.abs(a - b) > (1e-6 * md + RTOL * np.abs(b))
+    bad = np.abs(a - b) > (1e-6 * md + RTOL * np.abs(b) * np.maximum(1.0, 1.0 / np.abs(den)))
     assert not bad.any(), (what, int(bad.sum()), float(np.abs(a - b).max()))
+    assert plain.mean() <= 1e-5, (what, "pixels beyond the plain rtol", int(plain.sum()))
+    assert not (plain & (np.abs(den) > 0.5)).any(), (what, "well-conditioned pixel beyond rtol")
 
 
 @pytest.mark.parametrize("cfg,stage", CASES, ids=lambda v: v if isinstance(v, str) else "x".join(map(str, v)))
@@ -77,13 +101,27 @@ def test_full_size_vs_fp64_oracle(cfg, stage):
     ws = tp.xavier_weights(dims, final, gen)
     x = torch.randn(B, cin, h, w, generator=gen)
     g = torch.randn((B, 1, h, w) if final else (B, H, W), generator=gen)
-    ref_out, ref_gx, ref_gw, ref_amin = _oracle_fp64(x, ws, md, r, final, g)
+    ref_out, ref_gx, ref_gw, ref_amin, ref_n4 = _oracle_fp64(x, ws, md, r, final, g)
 
     red = bts_b200.reduction_1x1(cin, nout, md, is_final=final).cuda()
     with torch.no_grad():
         for p, wt in zip(red.chain_weights(), ws):
             p.copy_(wt.cuda())
     gd = g.cuda()
+    own32 = {}
+
+    def own(i):
+        """the reference's own fp32 run (the port on the host), only for the ill-conditioned upratio-8 stage"""
+        if r != 8:
+            return None
+
+        def get():
+            if not own32:
+                o, gx, gw, _, _ = _oracle_fp64(x, ws, md, r, final, g, torch.float32)
+                own32["v"] = [gx] + gw
+            return own32["v"][i].astype(np.float64)
+        return get
+
     for route in (("head",) if final else ("fused", "strict")):
         xd = x.cuda().requires_grad_(True)
         for p in red.parameters():
@@ -99,11 +137,11 @@ def test_full_size_vs_fp64_oracle(cfg, stage):
                 pe4 = red(xd)
                 n = F.normalize(pe4[:, :3, :, :], 2, 1)                        # bts.py:250-253
                 out = lpg(torch.cat([n, pe4[:, 3, :, :].unsqueeze(1)], 1), None)
-            _close_depth(out, ref_out, md, (route, "depth"))
+            _close_depth(out, ref_out, md, (route, "depth"), ref_n4, r)
             assert abs(float(lpg.abs_min) - ref_amin) <= 1e-5, (route, float(lpg.abs_min), ref_amin)
         out.backward(gd)
         torch.cuda.synchronize()
-        _close_peak(xd.grad, ref_gx, (route, "grad_x"))
+        _close_peak(xd.grad, ref_gx, (route, "grad_x"), own(0))
         for i, (p, gr) in enumerate(zip(red.chain_weights(), ref_gw)):
-            _close_peak(p.grad.view(p.shape[0], p.shape[1]), gr, (route, "grad_w%d" % i))
+            _close_peak(p.grad.view(p.shape[0], p.shape[1]), gr, (route, "grad_w%d" % i), own(1 + i))
         del xd, out

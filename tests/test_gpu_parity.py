@@ -113,6 +113,7 @@ SEEDED = [  # (num_in, num_out, is_final, r, B, h, w, max_depth): sizes the C or
     (64, 32, False, 2, 2, 44, 76, 80.0),
     (32, 16, True, 1, 2, 88, 152, 80.0),
     (64, 64, False, 8, 1, 11, 13, 10.0),
+    (64, 64, False, 8, 1, 17, 9, 10.0),      # hw % 4 != 0: recompute backward + non-TMA weight-gradient kernel
     (48, 24, False, 4, 1, 9, 7, 10.0),       # widths no fast path covers: generic kernel
     (16, 16, True, 1, 3, 33, 31, 10.0),
 ]
@@ -294,8 +295,10 @@ def test_ddp_wraps_the_modules():
                                  (128, 64, False, 4, 2, 36, 44), (64, 32, False, 2, 3, 60, 84), (32, 16, True, 1, 2, 96, 160)],
                          ids=lambda c: "x".join(map(str, c)))
 def test_tensor_core_path_vs_generic_path(cfg):
-    """The tcgen05 kernels and the generic SIMT kernels are independent implementations: they must
-    agree to fp32 rounding (3xTF32 keeps fp32 accuracy) on shapes with partial tiles and image wraps."""
+    """The tcgen05 kernels and the generic SIMT kernels are independent fp32 implementations (different summation
+    orders, ex2.approx vs expf in the ELU): each is held to 1e-5 of the fp64 oracle by the tests above, so they must
+    agree with EACH OTHER to 2e-5, on shapes with partial tiles and image wraps. (bts_force_path is process-wide
+    since round 2, so the generic run really takes the SIMT backward too.)"""
     import bts_b200
     from bts_b200 import functional as Fn
     num_in, num_out, is_final, r, B, h, w = cfg
@@ -327,13 +330,13 @@ def test_tensor_core_path_vs_generic_path(cfg):
         Fn.force_path(Fn.PATH_AUTO)
     got = run()
     if is_final:
-        close_peak(got[0], ref[0].cpu().numpy())
+        close_peak(got[0], ref[0].cpu().numpy(), tol=2 * RTOL)
     else:
-        assert torch.allclose(got[0], ref[0], rtol=RTOL, atol=1e-5)
+        assert torch.allclose(got[0], ref[0], rtol=2 * RTOL, atol=1e-5)
         assert abs(got[1] - ref[1]) <= 1e-5
-    close_peak(got[2], ref[2].cpu().numpy())
+    close_peak(got[2], ref[2].cpu().numpy(), tol=2 * RTOL)
     for a, b in zip(got[3], ref[3]):
-        close_peak(a, b.cpu().numpy())
+        close_peak(a, b.cpu().numpy(), tol=2 * RTOL)
 
 
 @pytest.mark.parametrize("cfg", [(128, 128, False, 8, 3, 20, 28, True), (128, 128, False, 8, 3, 19, 23, False),
