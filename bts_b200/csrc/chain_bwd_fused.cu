@@ -126,6 +126,10 @@ struct FusedLayout {
     static constexpr int NACC = PERWG ? NWG : 1;
     static constexpr int WG0 = NACC * ACC;                 // first TMEM column of the warpgroups' own regions
     static constexpr int DRC = PERWG ? 32 : 16;            // summed accumulator columns a thread drains per job
+    // where the drained sums live between drains: spare TMEM columns when there are some (the head: no registers are
+    // held across the tile loop, whose unfenced SIMT tails want them all), else registers
+    static constexpr bool TMASTER = PERWG && WG0 + NWG * WGCOLS + NWG * NJOBS * 32 <= 512;
+    static constexpr int MASTER0 = WG0 + NWG * WGCOLS;     // first master column
     static_assert(WG0 + NWG * WGCOLS <= 512, "TMEM budget");
 };
 
@@ -259,6 +263,38 @@ __device__ __forceinline__ void wait_count(uint64_t *bar, uint32_t &seen, uint32
     }
 }
 
+// TMEM part of a drain with TMEM-resident master sums: master[job] += acc[job][0:32) + acc[job][32:64), acc = 0.
+// Out of line on purpose: the tile loop's body is one long unrolled schedule, and this runs once in several iterations.
+#ifndef BTS_DRAIN_NOINLINE
+#define BTS_DRAIN_NOINLINE 0
+#endif
+#if BTS_DRAIN_NOINLINE
+#define BTS_DRAIN_ATTR __noinline__
+#else
+#define BTS_DRAIN_ATTR __forceinline__
+#endif
+template <int NJOBS>
+__device__ BTS_DRAIN_ATTR void drain_to_tmem_master(uint32_t la, uint32_t tmaster)
+{
+#pragma unroll
+    for (int job = 0; job < NJOBS; ++job) {
+        uint32_t r0[32], r1[32], m[32];
+        tmem_ld<32>(la + job * 64, r0);
+        tmem_ld<32>(la + job * 64 + 32, r1);
+        tmem_ld<32>(tmaster + job * 32, m);
+        wait_ld();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            m[j] = __float_as_uint(__uint_as_float(m[j]) + (__uint_as_float(r0[j]) + __uint_as_float(r1[j])));
+            r0[j] = 0u;
+        }
+        tmem_st<32>(tmaster + job * 32, m);
+        tmem_st<32>(la + job * 64, r0);
+        tmem_st<32>(la + job * 64 + 32, r0);
+    }
+    wait_st();
+}
+
 // MODE 0: sigmoid head (grad [B][1][hw]); 1: plane parameters (grad [B][4][hw]); 2: fused LPG (grad_depth, upratio R)
 template <class CFG, int MODE, int R, int NWG>
 __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(const __grid_constant__ FusedArgs fa)
@@ -312,6 +348,11 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
             for (int j = 0; j < 32; ++j) z[j] = 0u;
 #pragma unroll
             for (int c0 = 0; c0 < L::WG0; c0 += 32) tmem_st<32>(tbase + ((uint32_t)((tid >> 5) * 32) << 16) + c0, z);
+            if constexpr (L::TMASTER) {
+#pragma unroll
+                for (int c0 = 0; c0 < NWG * L::NJOBS * 32; c0 += 32)
+                    tmem_st<32>(tbase + ((uint32_t)((tid >> 5) * 32) << 16) + L::MASTER0 + c0, z);
+            }
             wait_st();
         }
         fence_before_sync();
@@ -457,11 +498,14 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
         // j = 16..31 (both can read every TMEM lane quarter), behind a CTA-wide barrier.
         static_assert(NWG >= 2, "the shared-set drain splits the accumulator columns over two warpgroups");
         constexpr int DRC = L::DRC;
-        float wacc[L::NJOBS][DRC];
+        float wacc[L::TMASTER ? 1 : L::NJOBS][L::TMASTER ? 1 : DRC];
+        if constexpr (!L::TMASTER) {
 #pragma unroll
-        for (int job = 0; job < L::NJOBS; ++job)
+            for (int job = 0; job < L::NJOBS; ++job)
 #pragma unroll
-            for (int j = 0; j < DRC; ++j) wacc[job][j] = 0.f;
+                for (int j = 0; j < DRC; ++j) wacc[job][j] = 0.f;
+        }
+        const uint32_t tmaster = tbase + ((uint32_t)(wj * 32) << 16) + L::MASTER0 + g * L::NJOBS * 32;
         auto drain_sync = [&]() {
             if constexpr (L::PERWG) named_bar_sync(kInlineIssue ? bid : 1 + g, kTile);
             else named_bar_sync(0, NWG * kTile);
@@ -471,18 +515,32 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
             fence_before_sync();
             drain_sync();                                         // ... and so is everybody else's
             fence_after_sync();
-            if (L::PERWG || g < 2) {
+            if constexpr (L::TMASTER) {
+                drain_to_tmem_master<L::NJOBS>(tacc + ((uint32_t)(wj * 32) << 16), tmaster);
+            } else if (L::PERWG || g < 2) {
                 const uint32_t la = tacc + ((uint32_t)(wj * 32) << 16) + (L::PERWG ? 0u : (uint32_t)g * 16);
 #pragma unroll
                 for (int job = 0; job < L::NJOBS; ++job) {
                     uint32_t r0[DRC], r1[DRC];
                     tmem_ld<DRC>(la + job * 64, r0);
                     tmem_ld<DRC>(la + job * 64 + 32, r1);
-                    wait_ld();
+                    if constexpr (L::TMASTER) {
+                        uint32_t m[DRC];
+                        tmem_ld<DRC>(tmaster + job * 32, m);
+                        wait_ld();
 #pragma unroll
-                    for (int j = 0; j < DRC; ++j) {
-                        wacc[job][j] += __uint_as_float(r0[j]) + __uint_as_float(r1[j]);
-                        r0[j] = 0u;
+                        for (int j = 0; j < DRC; ++j) {
+                            m[j] = __float_as_uint(__uint_as_float(m[j]) + (__uint_as_float(r0[j]) + __uint_as_float(r1[j])));
+                            r0[j] = 0u;
+                        }
+                        tmem_st<DRC>(tmaster + job * 32, m);
+                    } else {
+                        wait_ld();
+#pragma unroll
+                        for (int j = 0; j < DRC; ++j) {
+                            wacc[job][j] += __uint_as_float(r0[j]) + __uint_as_float(r1[j]);
+                            r0[j] = 0u;
+                        }
                     }
                     tmem_st<DRC>(la + job * 64, r0);
                     tmem_st<DRC>(la + job * 64 + 32, r0);
@@ -494,13 +552,14 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
             fence_after_sync();
         };
         // CTA-uniform trip count (warpgroup 0 has the most tiles): every warpgroup joins every drain
-        // (per-warpgroup sets need no common schedule: every warpgroup runs its own tiles)
-        const int iters_cta = L::PERWG ? (tile0 < ntiles ? (ntiles - tile0 + stride - 1) / stride : 0)
-                                       : (ntiles - (int)blockIdx.x * NWG + stride - 1) / stride;
+        const int iters_cta = (ntiles - (int)blockIdx.x * NWG + stride - 1) / stride;   // warpgroup 0's tiles: the most
         bool drain_due = false;
-        int tile = tile0;
-        for (int it = 0; it < iters_cta; ++it, tile += stride) {
-          if (tile < ntiles) {
+        int tile = tile0, since_drain = 0, drains_done = 0;
+        // The plain loop over my own tiles (a CTA-uniform trip count with the body under `if (tile < ntiles)` compiled
+        // to a 3 % slower kernel). Shared accumulator set: every warpgroup must join every CTA-wide drain, so the one
+        // with fewer tiles catches up after its loop.
+        for (; tile < ntiles; tile += stride) {
+          {
             const unsigned gp = own.g;                            // == tile * kTile + t
             const bool valid = gp < npx;
             const int b = valid ? own.b : 0;
@@ -746,15 +805,17 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
                     else gradx_epilogue();
                 }
             }
-          } else if (drain_due) {                                 // no tile of my own any more: still join the CTA's drain
-            drain();
-            drain_due = false;
           }
-          drain_due = (it + 1) % fa.drain_every == 0;
-          if (!kDrainDeferred && drain_due) {
-            drain();
-            drain_due = false;
+          if (++since_drain == fa.drain_every) {
+            since_drain = 0;
+            ++drains_done;
+            if (kDrainDeferred) drain_due = true;
+            else drain();
           }
+        }
+        if (kDrainDeferred && drain_due) drain();
+        if constexpr (!L::PERWG) {
+            for (; drains_done < iters_cta / fa.drain_every; ++drains_done) drain();   // warpgroup 0 ran that many
         }
         drain();                                                  // whatever the last iterations accumulated
         // ---- drained sums -> shared memory (the staging buffers are idle: the last drain waited for every MMA).
@@ -764,9 +825,18 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
             // (a warpgroup may get here while another one still stages: each writes into its OWN idle staging buffers)
             float *scr = reinterpret_cast<float *>(stage + (L::PERWG ? (size_t)g * L::NSUB * L::SUB : 0));
 #pragma unroll
-            for (int job = 0; job < L::NJOBS; ++job)
+            for (int job = 0; job < L::NJOBS; ++job) {
+                if constexpr (L::TMASTER) {
+                    uint32_t m[DRC];
+                    tmem_ld<DRC>(tmaster + job * 32, m);
+                    wait_ld();
 #pragma unroll
-                for (int j = 0; j < DRC; ++j) scr[(job * kTile + t) * 33 + (L::PERWG ? 0 : g * 16) + j] = wacc[job][j];
+                    for (int j = 0; j < DRC; ++j) scr[(job * kTile + t) * 33 + j] = __uint_as_float(m[j]);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < DRC; ++j) scr[(job * kTile + t) * 33 + (L::PERWG ? 0 : g * 16) + j] = wacc[job][j];
+                }
+            }
         }
     }
     constexpr int SP = 33;
