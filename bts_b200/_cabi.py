@@ -56,11 +56,19 @@ _SIGNATURES["bts_reduc_lpg_bwd_glue"] = (ctypes.c_int, [
 _SIGNATURES["bts_silog_workspace_bytes"] = (ctypes.c_size_t, [])
 _SIGNATURES["bts_silog_fwd"] = (ctypes.c_int, [_P, _P, _P, _LL, _F, _P, _P, _SZ, _P])
 _SIGNATURES["bts_silog_bwd"] = (ctypes.c_int, [_P, _P, _P, _LL, _F, _P, _P, _P, _P])
+_SIGNATURES["bts_bf16_supported"] = (ctypes.c_int, [_P, _I, _I, _I])
+_SIGNATURES["bts_workspace_bytes_bf16"] = (ctypes.c_size_t, [_P, _I, _I, _I, _I, _I])
+_SIGNATURES["bts_lpg_fwd_bf16"] = (ctypes.c_int, [_P, _P, _P, _I, _I, _I, _I, _F, _P])
+_SIGNATURES["bts_lpg_bwd_bf16"] = (ctypes.c_int, [_P, _P, _P, _I, _I, _I, _I, _F, _P])
+_SIGNATURES["bts_reduc_fwd_bf16"] = (ctypes.c_int, [_P, _P, _P, _I, _I, _F, _I, _I, _I, _P, _P, _SZ, _P])
+_SIGNATURES["bts_reduc_bwd_bf16"] = (ctypes.c_int, [_P, _P, _P, _I, _I, _F, _I, _I, _I, _P, _P, _P, _P, _SZ, _P])
+_SIGNATURES["bts_reduc_lpg_fwd_bf16"] = (ctypes.c_int, [_P, _P, _P, _I, _F, _I, _I, _I, _I, _F, _F, _P, _P, _P, _P, _SZ, _P])
+_SIGNATURES["bts_reduc_lpg_bwd_bf16"] = (ctypes.c_int, [_P, _F, _P, _P, _P, _I, _F, _I, _I, _I, _I, _F, _P, _P, _P, _SZ, _P])
 _SIGNATURES["bts_silog_fwd_static"] = (ctypes.c_int, [_P, _P, _P, _LL, _F, _P, _P, _P])
 _SIGNATURES["bts_eval_workspace_bytes"] = (ctypes.c_size_t, [_I, _I, _I])
 _SIGNATURES["bts_eval_metrics"] = (ctypes.c_int, [_P, _P, _I, _I, _I, _F, _F, _I, _I, _I, _I, _P, _P, _P, _SZ, _P])
 _SIGNATURES["bts_backproject"] = (ctypes.c_int, [_P, _P, _I, _I, _I, _F, _F, _F, _F, _F, _F, _P])
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 _lib = None
 

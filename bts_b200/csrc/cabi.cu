@@ -69,6 +69,9 @@ size_t eval_workspace_bytes(int B, int H, int W, int sms);
 int launch_eval_metrics(const float *, const float *, int, int, int, float, float, int, int, int, int, float *, int *, void *,
                         int, cudaStream_t);
 
+int launch_lpg_fwd_bf16(const void *, void *, float *, int, int, int, int, float, cudaStream_t);
+int launch_lpg_bwd_bf16(const void *, const void *, void *, int, int, int, int, float, cudaStream_t);
+
 int launch_backproject(const float *, float *, int, int, int, float, float, float, float, float, float, cudaStream_t);
 
 static int sm_count()
@@ -458,6 +461,135 @@ int bts_backproject(const float *depth, float *points, int B, int H, int W, floa
     if (fx == 0.f || fy == 0.f) return set_error(BTS_ERR_BAD_ARG, "zero focal length");
     if ((long long)B * H * W > (1ll << 31) - 1) return set_error(BTS_ERR_UNSUPPORTED, "more than 2^31 pixels");
     return launch_backproject(depth, points, B, H, W, fx, fy, cx, cy, edge_thresh, hidden, (cudaStream_t)stream);
+}
+
+/* ------------------------------------------------------------------ bf16 twin (ABI 4) ------------------------------ */
+
+static TcArgs make_tc_args_bf16(const void *x, int B, int h, int w, float max_depth, float eps)
+{
+    TcArgs a = make_tc_args(static_cast<const float *>(x), B, h, w, max_depth, eps);
+    a.bf16_io = 1;
+    a.x_vec16 = ((h * w) % 8 == 0 && aligned16(x)) ? 1 : 0;      // 16-byte copies move 8 bf16 pixels
+    return a;
+}
+
+// bytes the bf16 entry points need: the one-pass backward only keeps per-CTA partial sums (deterministic route)
+static size_t bf16_ws_bytes(const ChainParams &cp)
+{
+    size_t tw = 0;
+    for (int l = 0; l < cp.n_layers; ++l) tw += (size_t)cp.dims[l] * cp.dims[l + 1];
+    return 2 * tc_pack_bytes() + sizeof(float) * tw * (size_t)sm_count();
+}
+
+size_t bts_workspace_bytes_bf16(const int *dims, int n_layers, int B, int h, int w, int r)
+{
+    (void)r;
+    if (B <= 0 || h <= 0 || w <= 0) return 0;
+    ChainParams cp;
+    const float *fake[BTS_MAX_LAYERS];
+    for (int l = 0; l < BTS_MAX_LAYERS; ++l) fake[l] = reinterpret_cast<const float *>(16);
+    const int last = (dims && n_layers >= 1 && n_layers <= BTS_MAX_LAYERS) ? dims[n_layers] : 0;
+    if (!last || fill_chain(cp, fake, nullptr, dims, n_layers, last == 1, 1.f) != BTS_OK) return 0;
+    return bf16_ws_bytes(cp);
+}
+
+int bts_bf16_supported(const int *dims, int n_layers, int is_final, int backward)
+{
+    ChainParams cp;
+    const float *fake[BTS_MAX_LAYERS];
+    for (int l = 0; l < BTS_MAX_LAYERS; ++l) fake[l] = reinterpret_cast<const float *>(16);
+    if (fill_chain(cp, fake, nullptr, dims, n_layers, is_final, 1.f)) return 0;
+    if (!tc_supported(cp)) return 0;
+    return backward ? (fused_bwd_supported(cp) ? 1 : 0) : 1;
+}
+
+int bts_lpg_fwd_bf16(const void *plane_eq, void *depth, float *abs_min, int B, int h, int w, int r, float eps, void *stream)
+{
+    if (int e = check_shape(B, h, w)) return e;
+    if (r < 1) return set_error(BTS_ERR_BAD_ARG, "upratio r=%d must be >= 1", r);
+    if ((long long)B * h * w == 0) return BTS_OK;
+    if (!plane_eq || !depth) return set_error(BTS_ERR_BAD_ARG, "plane_eq / depth is NULL");
+    return launch_lpg_fwd_bf16(plane_eq, depth, abs_min, B, h, w, r, eps, (cudaStream_t)stream);
+}
+
+int bts_lpg_bwd_bf16(const void *grad_depth, const void *plane_eq, void *grad_plane_eq, int B, int h, int w, int r, float eps,
+                     void *stream)
+{
+    if (int e = check_shape(B, h, w)) return e;
+    if (r < 1) return set_error(BTS_ERR_BAD_ARG, "upratio r=%d must be >= 1", r);
+    if ((long long)B * h * w == 0) return BTS_OK;
+    if (!grad_depth || !plane_eq || !grad_plane_eq) return set_error(BTS_ERR_BAD_ARG, "grad_depth / plane_eq / grad_plane_eq is NULL");
+    return launch_lpg_bwd_bf16(grad_depth, plane_eq, grad_plane_eq, B, h, w, r, eps, (cudaStream_t)stream);
+}
+
+int bts_reduc_fwd_bf16(const void *x, const float *const *W, const int *dims, int n_layers, int is_final, float max_depth,
+                       int B, int h, int w, void *out, void *ws, size_t ws_bytes, void *stream)
+{
+    ChainParams cp;
+    if (int e = fill_chain(cp, W, nullptr, dims, n_layers, is_final, max_depth)) return e;
+    if (int e = check_shape(B, h, w)) return e;
+    if ((long long)B * h * w == 0) return BTS_OK;
+    if (!x || !out) return set_error(BTS_ERR_BAD_ARG, "x / out is NULL");
+    if (!use_tc(cp, ws, ws_bytes, nullptr))
+        return set_error(BTS_ERR_UNSUPPORTED, "the bf16 twin serves the chains of the tensor-core path (and needs a workspace)");
+    TcArgs a = make_tc_args_bf16(x, B, h, w, max_depth, 0.f);
+    a.out = static_cast<float *>(out);
+    return launch_chain_tc_fwd(cp, a, 0, sm_count(), (cudaStream_t)stream);
+}
+
+int bts_reduc_bwd_bf16(const void *x, const float *const *W, const int *dims, int n_layers, int is_final, float max_depth,
+                       int B, int h, int w, const void *grad_out, void *grad_x, float *const *grad_W, void *ws,
+                       size_t ws_bytes, void *stream)
+{
+    ChainParams cp;
+    if (int e = fill_chain(cp, W, grad_W, dims, n_layers, is_final, max_depth)) return e;
+    if (int e = check_shape(B, h, w)) return e;
+    if ((long long)B * h * w == 0) return BTS_OK;
+    if (!x || !grad_out) return set_error(BTS_ERR_BAD_ARG, "x / grad_out is NULL");
+    TcArgs a = make_tc_args_bf16(x, B, h, w, max_depth, 0.f);
+    if (!use_tc(cp, ws, ws_bytes, nullptr) || ws_bytes < bf16_ws_bytes(cp) || !fused_bwd_supported(cp) || !a.x_vec16)
+        return set_error(BTS_ERR_UNSUPPORTED, "bf16 backward: chains 32->16->8 and 64->32->16->8 with h*w %% 8 == 0 and 16-byte aligned x");
+    a.grad = static_cast<const float *>(grad_out);
+    a.grad_x = static_cast<float *>(grad_x);
+    return launch_chain_bwd_fused(cp, a, is_final ? 0 : 1, 0, ws, sm_count(), (cudaStream_t)stream);
+}
+
+int bts_reduc_lpg_fwd_bf16(const void *x, const float *const *W, const int *dims, int n_layers, float max_depth, int B, int h,
+                           int w, int r, float eps, float depth_div, void *plane_eq_out, void *depth, float *abs_min,
+                           void *ws, size_t ws_bytes, void *stream)
+{
+    ChainParams cp;
+    if (int e = fill_chain(cp, W, nullptr, dims, n_layers, 0, max_depth)) return e;
+    if (int e = check_shape(B, h, w)) return e;
+    if (int e = check_glue(r < 1 ? 1 : r, depth_div, 0, nullptr, 0, h, w)) return e;
+    if ((long long)B * h * w == 0) return BTS_OK;
+    if (!x || !depth) return set_error(BTS_ERR_BAD_ARG, "x / depth is NULL");
+    if (!(r == 1 || r == 2 || r == 4 || r == 8) || !use_tc(cp, ws, ws_bytes, depth))
+        return set_error(BTS_ERR_UNSUPPORTED, "the bf16 twin serves the tensor-core chains at upratio 1, 2, 4, 8 (16-byte aligned depth)");
+    TcArgs a = make_tc_args_bf16(x, B, h, w, max_depth, eps);
+    a.out = static_cast<float *>(plane_eq_out); a.depth = static_cast<float *>(depth); a.abs_min = abs_min;
+    a.depth_div = depth_div; a.depth_bstride = (long long)h * r * w * r;
+    return launch_chain_tc_fwd(cp, a, r, sm_count(), (cudaStream_t)stream);
+}
+
+int bts_reduc_lpg_bwd_bf16(const void *grad_depth, float depth_div, const void *x, const float *const *W, const int *dims,
+                           int n_layers, float max_depth, int B, int h, int w, int r, float eps, void *grad_x,
+                           float *const *grad_W, void *ws, size_t ws_bytes, void *stream)
+{
+    ChainParams cp;
+    if (int e = fill_chain(cp, W, grad_W, dims, n_layers, 0, max_depth)) return e;
+    if (int e = check_shape(B, h, w)) return e;
+    if (int e = check_glue(r < 1 ? 1 : r, depth_div, 0, nullptr, 0, h, w)) return e;
+    if ((long long)B * h * w == 0) return BTS_OK;
+    if (!x || !grad_depth) return set_error(BTS_ERR_BAD_ARG, "x / grad_depth is NULL");
+    TcArgs a = make_tc_args_bf16(x, B, h, w, max_depth, eps);
+    // the one-pass backward prefetches the r x r block of grad_depth per low-res pixel: upratio 1 and 2 only
+    if (!(r == 1 || r == 2) || !use_tc(cp, ws, ws_bytes, grad_depth) || ws_bytes < bf16_ws_bytes(cp) || !fused_bwd_supported(cp) ||
+        !a.x_vec16)
+        return set_error(BTS_ERR_UNSUPPORTED, "bf16 fused backward: chain 64->32->16->8->3 at upratio 1 or 2, h*w %% 8 == 0, aligned x");
+    a.grad = static_cast<const float *>(grad_depth); a.grad_x = static_cast<float *>(grad_x);
+    a.depth_div = depth_div; a.grad_bstride = (long long)h * r * w * r;
+    return launch_chain_bwd_fused(cp, a, 2, r, ws, sm_count(), (cudaStream_t)stream);
 }
 
 }  // extern "C"

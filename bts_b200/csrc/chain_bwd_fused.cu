@@ -20,6 +20,7 @@
 // The two warp pairs of a warpgroup share one staging buffer and take turns: pair 1 waits for
 // wfree[g][0], pair 0 for wfree[g][1] (one waiter group per mbarrier, so nobody lags two phases).
 #include <cstdlib>
+#include <type_traits>
 
 #include "chain_tc.cuh"
 
@@ -39,10 +40,11 @@ constexpr bool kInlineIssue = BTS_FUSED_INLINE_ISSUE != 0;
 // in TMEM for the whole kernel loses ~3.4e-8 of its magnitude per accumulate step, ALWAYS toward zero, so the error is a
 // bias that grows with the pixels a CTA sees (measured against the fp64 oracle: 2.6e-5 at 416x544 b4, where a CTA issues
 // ~760 steps per accumulator; it would be 2e-4 at KITTI b16). Every kWgradDrain iterations of the tile loop the CTA
-// therefore drains the accumulators into fp32 registers (16 per thread and job, round-to-nearest adds) and zeroes them:
-// 32 x kWgradDrain steps per chain, i.e. a bias below 1e-6 per 2 iterations.
+// therefore drains the accumulators into fp32 master sums (round-to-nearest adds; spare TMEM columns or registers)
+// and zeroes them. Measured at KITTI b16 with a drain every 4 iterations: grad_W within 2.6e-6 (head, one accumulator
+// set per warpgroup: 64 steps per chain) / 2.8e-6 (2x2 stage, one shared set: 128 steps) of the fp64 oracle's peak.
 #ifndef BTS_WGRAD_DRAIN
-#define BTS_WGRAD_DRAIN 2
+#define BTS_WGRAD_DRAIN 4
 #endif
 constexpr int kWgradDrain = BTS_WGRAD_DRAIN;
 #ifndef BTS_DRAIN_DEFERRED
@@ -90,7 +92,7 @@ __device__ __forceinline__ void issue_wgrad_half(uint32_t d, uint32_t sub0)
                         smem_desc_sw128(sub0 + s * kSubBytes + kSubB + ks * 32), idesc, 1);
 }
 
-template <class CFG, int MODE, int R, int NWG>
+template <class CFG, int MODE, int R, int NWG, bool BF = false>
 struct FusedLayout {
     static constexpr bool FINAL = MODE == 0;
     static constexpr int LAST = FINAL ? 1 : 3;
@@ -113,7 +115,9 @@ struct FusedLayout {
     static constexpr int NSUB = PRIV ? 4 : 2;
     static constexpr size_t stage_bytes = (size_t)NWG * NSUB * SUB;
     // next tile's features [channel][pixel] + 4 upstream-gradient words per pixel (cp.async)
-    static constexpr size_t xs_bytes = (size_t)NWG * (K0 + 4) * kTile * sizeof(float);
+    // (bf16 twin: the feature rows are 2-byte elements; the 4 gradient words per pixel stay fp32)
+    static constexpr size_t xs_wg_bytes = (size_t)K0 * kTile * (BF ? 2 : 4) + 4 * kTile * sizeof(float);
+    static constexpr size_t xs_bytes = (size_t)NWG * xs_wg_bytes;
     static constexpr size_t smem_bytes = 1024 + stage_bytes + xs_bytes + sizeof(float) * (PACK + IMG) + 8 * 6 * NWG + 16;
     static_assert(NW == 1 || NW == 2, "one or two tensor-core layers");
     static_assert(CFG::dim(NW) == kTailIn && CFG::dim(NW - 1) == 32, "chain must end ... -> 32 -> 16 -> 8");
@@ -296,10 +300,12 @@ __device__ BTS_DRAIN_ATTR void drain_to_tmem_master(uint32_t la, uint32_t tmaste
 }
 
 // MODE 0: sigmoid head (grad [B][1][hw]); 1: plane parameters (grad [B][4][hw]); 2: fused LPG (grad_depth, upratio R)
-template <class CFG, int MODE, int R, int NWG>
+template <class CFG, int MODE, int R, int NWG, bool BF>
 __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(const __grid_constant__ FusedArgs fa)
 {
-    using L = FusedLayout<CFG, MODE, R, NWG>;
+    using L = FusedLayout<CFG, MODE, R, NWG, BF>;
+    using TIO = std::conditional_t<BF, unsigned short, float>;   // storage type of x, grad and grad_x (bf16 twin)
+    constexpr int PXG = BF ? 8 : 4, NGRP = kTile / PXG;
     constexpr int LAST = L::LAST, NW = L::NW, K0 = L::K0;
     constexpr int NT = fused_threads(NWG);                         // NWG compute warpgroups (+ NWG issuer warps)
     constexpr bool GPRE = MODE != 2 || R <= 2;
@@ -373,9 +379,12 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
         // g, wj, half are warp-uniform; routed through a shuffle once so that the compiler knows it too (the MMA
         // operands derived from them must sit in uniform registers)
         const int g = uniform(tid / kTile), t = tid % kTile, lane = tid & 31, wj = uniform((tid % kTile) >> 5), half = wj >> 1;
-        float *xs_wg = xs_all + (size_t)g * (K0 + 4) * kTile;    // [channel][pixel] of the staged tile
-        float *xs = xs_wg + t;                                    // this thread's pixel column
-        float *gs = xs_wg + K0 * kTile + t * 4;                   // this pixel's gradient words
+        unsigned char *xs_raw = reinterpret_cast<unsigned char *>(xs_all) + (size_t)g * L::xs_wg_bytes;
+        TIO *xs_wg = reinterpret_cast<TIO *>(xs_raw);             // [channel][pixel] of the staged tile
+        TIO *xs = xs_wg + t;                                      // this thread's pixel column
+        float *gs = reinterpret_cast<float *>(xs_raw + (size_t)K0 * kTile * sizeof(TIO)) + t * 4;   // this pixel's gradient words
+        const TIO *const xg = reinterpret_cast<const TIO *>(a.x);
+        const TIO *const gg_in = reinterpret_cast<const TIO *>(a.grad);
         // (image, pixel) of this thread's own pixel and of the 4-pixel group it copies, for the tile the NEXT prefetch
         // fetches. They advance by the same number of pixels every iteration, so the two divisions by hw per
         // position and tile become one division per kernel (dq, dr) and an add with a wrap-around.
@@ -402,23 +411,25 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
             }
         };
         const int tile0 = (int)blockIdx.x * NWG + g;
-        PixPos own = pos_at((unsigned)tile0 * kTile + t), quad = pos_at((unsigned)tile0 * kTile + 4 * (t & 31));
+        PixPos own = pos_at((unsigned)tile0 * kTile + t), quad = pos_at((unsigned)tile0 * kTile + PXG * (t & (NGRP - 1)));
+        [[maybe_unused]] float gnext[4] = {0.f, 0.f, 0.f, 0.f};   // bf16 twin: the next tile's gradient words
         auto prefetch = [&](int tl) {
             const unsigned gp = own.g;
             const bool ok = tl < ntiles && gp < npx;
             [[maybe_unused]] const int b = ok ? own.b : 0;
             [[maybe_unused]] const int p = ok ? own.p : 0;
             {                                                     // 128-bit copies (host checks x_vec16), see chain_tc_fwd.cu
-                const int q = t & 31, cw = t >> 5;
+                constexpr int CWN = kTile / NGRP;                 // channels per pass of the warpgroup
+                const int q = t & (NGRP - 1), cw = t / NGRP;
                 const bool okv = tl < ntiles && quad.g < npx;
                 const int bn = okv ? quad.b : 0;
                 const int pn = okv ? quad.p : 0;
-                const float *xq = a.x + ((size_t)bn * K0 + cw) * a.hw + pn;
-                const uint32_t dst = smem_u32(xs_wg + cw * kTile + 4 * q);
+                const TIO *xq = xg + ((size_t)bn * K0 + cw) * a.hw + pn;
+                const uint32_t dst = smem_u32(xs_wg + cw * kTile + PXG * q);
 #pragma unroll
-                for (int i = 0; i < K0 / 4; ++i) cp_async16(dst + i * 4 * kTile * 4, xq + (size_t)i * 4 * a.hw, okv);
+                for (int i = 0; i < K0 / CWN; ++i) cp_async16(dst + i * CWN * kTile * (int)sizeof(TIO), xq + (size_t)i * CWN * a.hw, okv);
             }
-            if constexpr (GPRE) {
+            if constexpr (GPRE && !BF) {
                 const uint32_t gd = smem_u32(gs);
                 if constexpr (MODE == 0) {
                     cp_async4(gd, a.grad + (ok ? gp : 0), ok);
@@ -435,6 +446,30 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
                     cp_async8(gd, g0, ok);
                     cp_async8(gd + 8, g0 + Wd, ok);
                 }
+            }
+            if constexpr (GPRE && BF) {
+                // bf16 gradients are 2-byte elements, below cp.async's minimum: plain loads one tile ahead, parked in the
+                // pixel's gradient words (the loads are in flight while the current tile computes)
+                float g4[4] = {0.f, 0.f, 0.f, 0.f};
+                if (ok) {
+                    if constexpr (MODE == 0) {
+                        g4[0] = io_load<TIO>(gg_in + gp);
+                    } else if constexpr (MODE == 2 && R == 1) {
+                        g4[0] = io_load<TIO>(gg_in + (size_t)b * a.grad_bstride + p);
+                    } else if constexpr (MODE == 1) {
+                        const TIO *gq = gg_in + (size_t)b * 4 * a.hw + p;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) g4[j] = io_load<TIO>(gq + (size_t)j * a.hw);
+                    } else {
+                        const int i = p / a.w, j = p - i * a.w;
+                        const int Wd = a.w * 2;
+                        const TIO *g0 = gg_in + (size_t)b * a.grad_bstride + (size_t)i * 2 * (size_t)Wd + (size_t)j * 2;
+                        const uint32_t r0 = __ldg(reinterpret_cast<const uint32_t *>(g0)), r1 = __ldg(reinterpret_cast<const uint32_t *>(g0 + Wd));
+                        g4[0] = bf16_to_f32((unsigned short)(r0 & 0xffffu)); g4[1] = bf16_to_f32((unsigned short)(r0 >> 16));
+                        g4[2] = bf16_to_f32((unsigned short)(r1 & 0xffffu)); g4[3] = bf16_to_f32((unsigned short)(r1 >> 16));
+                    }
+                }
+                gnext[0] = g4[0]; gnext[1] = g4[1]; gnext[2] = g4[2]; gnext[3] = g4[3];
             }
             cp_async_commit();
         };
@@ -574,18 +609,29 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
                 uint32_t hi[16], lo[16];
 #pragma unroll
                 for (int j = 0; j < 16; j += 2) {
-                    const float v0 = xs[(c0 + j) * kTile], v1 = xs[(c0 + j + 1) * kTile];
+                    float v0, v1;
+                    if constexpr (BF) {                           // bf16 is exact in tf32: the remainder is zero
+                        v0 = bf16_to_f32(xs[(c0 + j) * kTile]);
+                        v1 = bf16_to_f32(xs[(c0 + j + 1) * kTile]);
+                        lo[j] = lo[j + 1] = 0u;
+                    } else {
+                        v0 = xs[(c0 + j) * kTile];
+                        v1 = xs[(c0 + j + 1) * kTile];
+                        tf32_lo2(v0, v1, lo[j], lo[j + 1]);
+                    }
                     hi[j] = __float_as_uint(v0);
                     hi[j + 1] = __float_as_uint(v1);
-                    tf32_lo2(v0, v1, lo[j], lo[j + 1]);
                 }
                 tmem_st<16>(xh + c0, hi);
                 tmem_st<16>(xl + c0, lo);
             }
             float gcur[4] = {0.f, 0.f, 0.f, 0.f};
-            if constexpr (GPRE) {
+            if constexpr (GPRE && !BF) {
                 const float4 g4 = *reinterpret_cast<const float4 *>(gs);
                 gcur[0] = g4.x; gcur[1] = g4.y; gcur[2] = g4.z; gcur[3] = g4.w;
+            }
+            if constexpr (GPRE && BF) {
+                gcur[0] = gnext[0]; gcur[1] = gnext[1]; gcur[2] = gnext[2]; gcur[3] = gnext[3];
             }
             wait_st();
             fence_before_sync();
@@ -730,7 +776,7 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
             };
             auto gradx_epilogue = [&]() {
                 done_wait();
-                float *gx = a.grad_x + (size_t)b * K0 * a.hw + p;
+                TIO *gx = reinterpret_cast<TIO *>(a.grad_x) + (size_t)b * K0 * a.hw + p;
 #pragma unroll
                 for (int n0 = 0; n0 < K0; n0 += 16) {
                     uint32_t r[16];
@@ -738,7 +784,7 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
                     wait_ld();
                     if (valid && a.grad_x != nullptr) {
 #pragma unroll
-                        for (int j = 0; j < 16; ++j) gx[(size_t)(n0 + j) * a.hw] = __uint_as_float(r[j]);
+                        for (int j = 0; j < 16; ++j) io_store(gx + (size_t)(n0 + j) * a.hw, __uint_as_float(r[j]));
                     }
                 }
             };
@@ -884,10 +930,10 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
 int launch_wreduce(const ChainParams &cp, const float *partials, int nparts, int total_w, cudaStream_t s);
 size_t tc_pack_bytes();
 
-template <class CFG, int MODE, int R, int NWG>
-static int launch_fused_cfg(const ChainParams &cp, const TcArgs &a, char *ws, int sms, cudaStream_t s)
+template <class CFG, int MODE, int R, int NWG, bool BF>
+static int launch_fused_cfg2(const ChainParams &cp, const TcArgs &a, char *ws, int sms, cudaStream_t s)
 {
-    using L = FusedLayout<CFG, MODE, R, NWG>;
+    using L = FusedLayout<CFG, MODE, R, NWG, BF>;
     float *partials = reinterpret_cast<float *>(ws + 2 * tc_pack_bytes());
     int total_w = 0;
     for (int l = 0; l < cp.n_layers; ++l) total_w += cp.dims[l] * cp.dims[l + 1];
@@ -905,7 +951,7 @@ static int launch_fused_cfg(const ChainParams &cp, const TcArgs &a, char *ws, in
     fa.total_w = total_w;
     static const int drain_env = getenv("BTS_WGRAD_DRAIN") ? atoi(getenv("BTS_WGRAD_DRAIN")) : 0;   // tuning hook
     fa.drain_every = drain_env > 0 ? drain_env : kWgradDrain;
-    auto kern = chain_bwd_fused_kernel<CFG, MODE, R, NWG>;
+    auto kern = chain_bwd_fused_kernel<CFG, MODE, R, NWG, BF>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::smem_bytes);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     const long long ntiles = (a.npx + kTile - 1) / kTile;
@@ -917,6 +963,12 @@ static int launch_fused_cfg(const ChainParams &cp, const TcArgs &a, char *ws, in
         if (int e2 = launch_wreduce(cp, partials, (int)grid, total_w, s)) return e2;
     }
     return BTS_OK;
+}
+
+template <class CFG, int MODE, int R, int NWG>
+static int launch_fused_cfg(const ChainParams &cp, const TcArgs &a, char *ws, int sms, cudaStream_t s)
+{
+    return a.bf16_io ? launch_fused_cfg2<CFG, MODE, R, NWG, true>(cp, a, ws, sms, s) : launch_fused_cfg2<CFG, MODE, R, NWG, false>(cp, a, ws, sms, s);
 }
 
 template <class CFG, int NWG>

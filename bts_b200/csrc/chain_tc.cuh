@@ -67,6 +67,33 @@ __device__ __forceinline__ float elu_fast(float t)
     return t > 0.f ? t : e - 1.f;
 }
 
+// ---- bf16 storage (the optional bf16 twin of the path: big tensors in bf16, arithmetic unchanged). A bf16 value is
+// the top 16 bits of the fp32 word, hence exactly representable in tf32: the 3xTF32 remainder of a bf16 input is zero.
+__device__ __forceinline__ float bf16_to_f32(unsigned short v) { return __uint_as_float((uint32_t)v << 16); }
+__device__ __forceinline__ unsigned short f32_to_bf16(float v)        // round to nearest even, NaN kept quiet
+{
+    uint32_t u = __float_as_uint(v);
+    if ((u & 0x7fffffffu) > 0x7f800000u) return (unsigned short)((u >> 16) | 0x40u);
+    u += 0x7fffu + ((u >> 16) & 1u);
+    return (unsigned short)(u >> 16);
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) { return (uint32_t)f32_to_bf16(lo) | ((uint32_t)f32_to_bf16(hi) << 16); }
+// element i of a tensor stored as T (float or bf16 = unsigned short)
+template <class T> __device__ __forceinline__ float io_load(const T *p);
+template <> __device__ __forceinline__ float io_load<float>(const float *p) { return __ldg(p); }
+template <> __device__ __forceinline__ float io_load<unsigned short>(const unsigned short *p) { return bf16_to_f32(__ldg(p)); }
+template <class T> __device__ __forceinline__ void io_store(T *p, float v);
+template <> __device__ __forceinline__ void io_store<float>(float *p, float v) { *p = v; }
+template <> __device__ __forceinline__ void io_store<unsigned short>(unsigned short *p, float v) { *p = f32_to_bf16(v); }
+// 4 / 2 consecutive elements (16- / 8-byte aligned for float, 8 / 4 for bf16)
+__device__ __forceinline__ void io_store4(float *p, float a, float b, float c, float d) { *reinterpret_cast<float4 *>(p) = make_float4(a, b, c, d); }
+__device__ __forceinline__ void io_store4(unsigned short *p, float a, float b, float c, float d)
+{
+    *reinterpret_cast<uint2 *>(p) = make_uint2(pack_bf16x2(a, b), pack_bf16x2(c, d));
+}
+__device__ __forceinline__ void io_store2(float *p, float a, float b) { *reinterpret_cast<float2 *>(p) = make_float2(a, b); }
+__device__ __forceinline__ void io_store2(unsigned short *p, float a, float b) { *reinterpret_cast<uint32_t *>(p) = pack_bf16x2(a, b); }
+
 // Parameters shared by the forward and backward tensor-core kernels.
 struct TcArgs {
     const float *x;          // [B][D0][hw]
@@ -78,13 +105,15 @@ struct TcArgs {
     float *grad_x;
     float *gw[BTS_MAX_LAYERS];
     int B, h, w, hw;
-    int x_vec16;             // hw % 4 == 0 and x 16-byte aligned: 128-bit cp.async of 4 pixels is legal
+    int x_vec16;             // hw % 4 == 0 (% 8 for bf16) and x 16-byte aligned: 128-bit cp.async of a pixel group is legal
+    int bf16_io;             // bf16 twin: x, out, depth, grad, grad_x point at bf16 tensors
     long long npx;           // B*hw
     float max_depth, eps;
     // activation stash (forward writes, backward reads; null = recompute): rows [channel][stash_npp] of
     // a_1 .. a_NW (= a16), a8 on a pixel axis padded per image to stash_hw_pad, and plane_eq [B][4][hw]
     float *stash_act;
     float *stash_pe;
+    float *stash_x;          // bf16 twin only: the features as fp32 rows [D0][stash_npp] (the TMA weight-gradient kernel's operand)
     long long stash_npp;
     int stash_hw_pad;
     // post-LPG glue (pytorch/bts.py:255-256, 269-270, 283) folded into the fused stage: the depth map is divided
@@ -211,7 +240,8 @@ __device__ __forceinline__ void tc_epilogue_to_a_spill(uint32_t lane_addr, float
 // ---- chunked variants: the A operand region is AW columns wide (hi at [0,AW), lo at [AW,2AW), D at 2AW),
 // so a layer with K > AW input channels runs as K/AW rounds of MMAs that accumulate into the same D.
 // With AW = 64 a 128-channel chain needs 256 TMEM columns per warpgroup and two warpgroups fit.
-template <class CFG, int L, int AW, int KOFF, int KC>
+// NOLO: the A operand has no remainder part (bf16 features): the lo(a) * hi(W) pass is skipped
+template <class CFG, int L, int AW, int KOFF, int KC, bool NOLO = false>
 __device__ __forceinline__ void tc_issue_chunk(uint32_t wg_base, const float *sw, uint64_t *bar)
 {
     constexpr int K = CFG::K(L), N = CFG::N(L);
@@ -220,12 +250,14 @@ __device__ __forceinline__ void tc_issue_chunk(uint32_t wg_base, const float *sw
     const uint32_t whi = smem_u32(sw + CFG::w_off(L));
     const uint32_t wlo = whi + N * K * 4;
     const uint32_t d = wg_base + 2 * AW;
+    if constexpr (!NOLO) {
 #pragma unroll
-    for (int k0 = 0; k0 < KC; k0 += 8)   // lo(a) * hi(W)
-        mma_tf32_ts(d, wg_base + AW + k0, smem_desc(whi + ((KOFF + k0) / 4) * LBO, LBO, SBO), idesc, (KOFF + k0) > 0);
+        for (int k0 = 0; k0 < KC; k0 += 8)   // lo(a) * hi(W)
+            mma_tf32_ts(d, wg_base + AW + k0, smem_desc(whi + ((KOFF + k0) / 4) * LBO, LBO, SBO), idesc, (KOFF + k0) > 0);
+    }
 #pragma unroll
     for (int k0 = 0; k0 < KC; k0 += 8)   // hi(a) * lo(W)
-        mma_tf32_ts(d, wg_base + k0, smem_desc(wlo + ((KOFF + k0) / 4) * LBO, LBO, SBO), idesc, 1);
+        mma_tf32_ts(d, wg_base + k0, smem_desc(wlo + ((KOFF + k0) / 4) * LBO, LBO, SBO), idesc, NOLO ? (KOFF + k0) > 0 : 1);
 #pragma unroll
     for (int k0 = 0; k0 < KC; k0 += 8)   // hi(a) * hi(W)
         mma_tf32_ts(d, wg_base + k0, smem_desc(whi + ((KOFF + k0) / 4) * LBO, LBO, SBO), idesc, 1);
@@ -234,7 +266,7 @@ __device__ __forceinline__ void tc_issue_chunk(uint32_t wg_base, const float *sw
 
 // SUBS: threads per pixel. With SUBS = 2 a tile group is 256 threads: warps w and w + 4 share TMEM lane quarter w and
 // split every epilogue's columns (sub = 0 / 1), which halves the SIMT latency of a tile and doubles the warps per SM.
-template <class CFG, int L, int AW, int KOFF, int KC, int SUBS = 1>
+template <class CFG, int L, int AW, int KOFF, int KC, int SUBS = 1, bool NOLO = false>
 __device__ __forceinline__ void tc_run_chunk(uint32_t wg_base, const float *sw, uint64_t *bar, uint32_t &phase,
                                              int wg, int t)
 {
@@ -244,7 +276,7 @@ __device__ __forceinline__ void tc_run_chunk(uint32_t wg_base, const float *sw, 
     if (t == 0) {                                                 // t: warp index inside the warpgroup, made warp-uniform once by the kernel
         if (elect_one()) {
             fence_after_sync();
-            tc_issue_chunk<CFG, L, AW, KOFF, KC>(wg_base, sw, bar);
+            tc_issue_chunk<CFG, L, AW, KOFF, KC, NOLO>(wg_base, sw, bar);
         }
         __syncwarp();
     }
@@ -328,10 +360,11 @@ __device__ __forceinline__ float lpg_depth_fast(float n4, float den, float eps)
 __device__ __forceinline__ int lpg_key(float amin, bool nan) { return nan ? (int)0xFFC00000 : __float_as_int(amin); }
 
 // SUBS = 2: sub-thread `sub` writes half of the block: the 16 pixels of half `sub` (R = 8), rows [sub R/2, (sub+1) R/2)
-template <int R, int SUBS = 1>
+template <int R, int SUBS = 1, class TO = float>
 __device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, float n3, float n4,
                                           unsigned gp, int b_own, int p_own, bool valid, int lane, int sub = 0)
 {
+    TO *const depth_base = reinterpret_cast<TO *>(a.depth);
     static_assert(SUBS == 1 || (R % 2) == 0, "two sub-threads split an even number of rows");
     // all index arithmetic is 32-bit: the C ABI rejects more than 2^31 - 1 low-res pixels
     float amin = __int_as_float(0x7f800000);
@@ -353,7 +386,7 @@ __device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, f
                 const int i = rem / a.w, j = rem - i * a.w;
                 const int q0 = (lane & 1) * 4;
                 const int Wd = a.w * 8;
-                float *out = a.depth + (size_t)b * a.depth_bstride + (size_t)i * 8 * (size_t)Wd + (size_t)j * 8 + q0;
+                TO *out = depth_base + (size_t)b * a.depth_bstride + (size_t)i * 8 * (size_t)Wd + (size_t)j * 8 + q0;
                 float *ds = a.ds_out ? a.ds_out + (size_t)b * a.ds_bstride + (size_t)(2 * i) * (2 * a.w) + 2 * j + (lane & 1) : nullptr;
                 float n1u[4];
 #pragma unroll
@@ -369,7 +402,7 @@ __device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, f
                         amin = fminf(amin, fabsf(den));
                         op[k] = lpg_depth_fast(m4, den, a.eps);
                     }
-                    *reinterpret_cast<float4 *>(out + (size_t)p * Wd) = o;
+                    io_store4(out + (size_t)p * Wd, o.x, o.y, o.z, o.w);
                     if ((p & 3) == 0 && ds != nullptr) ds[(size_t)(p >> 2) * (2 * a.w)] = op[0];   // rows 0, 4; cols 0, 4
                 }
             }
@@ -379,7 +412,7 @@ __device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, f
         const int b = b_own, rem = p_own;
         const int i = rem / a.w, j = rem - i * a.w;
         const int Wd = a.w * R;
-        float *out = a.depth + (size_t)b * a.depth_bstride + (size_t)i * R * (size_t)Wd + (size_t)j * R;
+        TO *out = depth_base + (size_t)b * a.depth_bstride + (size_t)i * R * (size_t)Wd + (size_t)j * R;
         float n1u[R];
 #pragma unroll
         for (int k = 0; k < R; ++k) n1u[k] = __fmul_rn(n1, lpg_offset(k, R));
@@ -394,18 +427,18 @@ __device__ __forceinline__ int lpg_expand(const TcArgs &a, float n1, float n2, f
                 amin = fminf(amin, fabsf(den));
                 o[k] = lpg_depth_fast(n4, den, a.eps);
             }
-            float *row = out + (size_t)p * Wd;
+            TO *row = out + (size_t)p * Wd;
             if constexpr (R == 4) {
                 if ((p & 1) == 0 && a.ds_out != nullptr) {        // rows 0, 2; cols 0, 2
                     float *ds = a.ds_out + (size_t)b * a.ds_bstride + (size_t)(2 * i + (p >> 1)) * (2 * a.w) + 2 * j;
                     ds[0] = o[0]; ds[1] = o[2];
                 }
             }
-            if constexpr (R == 4) *reinterpret_cast<float4 *>(row) = make_float4(o[0], o[1], o[2], o[3]);
-            else if constexpr (R == 2) *reinterpret_cast<float2 *>(row) = make_float2(o[0], o[1]);
+            if constexpr (R == 4) io_store4(row, o[0], o[1], o[2], o[3]);
+            else if constexpr (R == 2) io_store2(row, o[0], o[1]);
             else {
 #pragma unroll
-                for (int k = 0; k < R; ++k) row[k] = o[k];
+                for (int k = 0; k < R; ++k) io_store(row + k, o[k]);
             }
         }
     }

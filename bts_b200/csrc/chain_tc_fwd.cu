@@ -22,9 +22,13 @@ constexpr int kWideSubs = BTS_WIDE_SUBS;   // threads per pixel in the 128-chann
 // PREFETCH: the next tile's features travel global -> shared with cp.async while the current tile is
 // computed (needs D0*512 B of shared memory per warpgroup next to the weight images).
 // SUBS: threads per pixel (chain_tc.cuh): 2 for the 128-channel chains, whose tiles are few and long.
-template <class CFG, int R, bool FINAL, int NWG, bool PREFETCH, int AW, int SUBS>
+// BF: bf16 twin -- x, out and depth are bf16 tensors (TcArgs carries them as float pointers), arithmetic unchanged.
+template <class CFG, int R, bool FINAL, int NWG, bool PREFETCH, int AW, int SUBS, bool BF>
 __global__ void __launch_bounds__(NWG * SUBS * kTile, 1) chain_tc_fwd_kernel(TcArgs a)
 {
+    using TIO = std::conditional_t<BF, unsigned short, float>;
+    constexpr int PXG = BF ? 8 : 4;                               // pixels per 16-byte copy
+    constexpr int NGRP = kTile / PXG;                             // copy groups per tile row
     constexpr int GT = SUBS * kTile;                              // threads of one tile group
     constexpr int LAST = FINAL ? 1 : 3;
     constexpr int PACK = CFG::pack_floats(LAST);
@@ -55,8 +59,9 @@ __global__ void __launch_bounds__(NWG * SUBS * kTile, 1) chain_tc_fwd_kernel(TcA
     const unsigned npx = (unsigned)a.npx, hw = (unsigned)a.hw;
     const int ntiles = (int)((npx + kTile - 1) / kTile);
     const int stride = (int)gridDim.x * NWG;
-    float *xs_wg = xs_all + (size_t)wg * D0 * kTile;              // [channel][pixel] of the staged tile
-    float *xs = xs_wg + t;                                        // this thread's pixel column
+    TIO *xs_wg = reinterpret_cast<TIO *>(xs_all) + (size_t)wg * D0 * kTile;   // [channel][pixel] of the staged tile
+    TIO *xs = xs_wg + t;                                          // this thread's pixel column
+    const TIO *const xg = reinterpret_cast<const TIO *>(a.x);
     // 128-bit copies: 4 pixels never straddle two images because hw % 4 == 0 (the launcher picks the
     // non-prefetching kernel otherwise). Two mappings, chosen by measurement: WARP_PRIVATE (32-channel head) -- each
     // warp copies its own 32 pixels (lane l: pixels 4(l%8)..+3 of channels l/8, l/8+4, ...) and the staged tile
@@ -93,18 +98,21 @@ __global__ void __launch_bounds__(NWG * SUBS * kTile, 1) chain_tc_fwd_kernel(TcA
         }
     };
     const int tile0 = (int)blockIdx.x * NWG + wg;
-    const int pq = WARP_PRIVATE ? (((t >> 5) << 3) | (lane & 7)) : (t & 31);
-    PixPos own = pos_at((unsigned)tile0 * kTile + t), quad = pos_at((unsigned)tile0 * kTile + 4 * pq);
+    // copy group of this thread: WARP_PRIVATE -> one of the NGRP / 4 groups of its own warp's 32 pixels
+    const int pq = WARP_PRIVATE ? ((t >> 5) * (NGRP / 4) + (lane & (NGRP / 4 - 1))) : (tt & (NGRP - 1));
+    PixPos own = pos_at((unsigned)tile0 * kTile + t), quad = pos_at((unsigned)tile0 * kTile + PXG * pq);
     auto prefetch = [&](int tl) {                                 // fetches the tile `quad` points at
-        const int q = pq, cw = WARP_PRIVATE ? (lane >> 3) : (tt >> 5);
-        constexpr int CWN = 4 * SUBS;                             // channels copied per pass of the tile group
+        // channels copied per pass: a warp's 32 lanes cover NGRP / 4 groups x (128 / NGRP) channels when WARP_PRIVATE,
+        // else the tile group's GT threads cover NGRP groups x GT / NGRP channels
+        constexpr int CWN = WARP_PRIVATE ? 32 / (NGRP / 4) : GT / NGRP;
+        const int q = pq, cw = WARP_PRIVATE ? lane / (NGRP / 4) : tt / NGRP;
         const bool ok = tl < ntiles && quad.g < npx;
         const int bn = ok ? quad.b : 0;
         const int pn = ok ? quad.p : 0;
-        const float *xq = a.x + ((size_t)bn * D0 + cw) * a.hw + pn;
-        const uint32_t dst = smem_u32(xs_wg + cw * kTile + 4 * q);
+        const TIO *xq = xg + ((size_t)bn * D0 + cw) * a.hw + pn;
+        const uint32_t dst = smem_u32(xs_wg + cw * kTile + PXG * q);
 #pragma unroll
-        for (int i = 0; i < D0 / CWN; ++i) cp_async16(dst + i * CWN * kTile * 4, xq + (size_t)i * CWN * a.hw, ok);
+        for (int i = 0; i < D0 / CWN; ++i) cp_async16(dst + i * CWN * kTile * (int)sizeof(TIO), xq + (size_t)i * CWN * a.hw, ok);
         cp_async_commit();
     };
     if constexpr (PREFETCH) prefetch(tile0);                      // in flight while the weight images are packed
@@ -128,7 +136,7 @@ __global__ void __launch_bounds__(NWG * SUBS * kTile, 1) chain_tc_fwd_kernel(TcA
         const int p = valid ? own.p : 0;
         pos_advance(own);
         if constexpr (PREFETCH) pos_advance(quad);                // now the tile the next prefetch fetches
-        const float *xp = a.x + (size_t)b * D0 * a.hw + p;
+        const TIO *xp = xg + (size_t)b * D0 * a.hw + p;
         bool stash = false;
         float *act_gp = nullptr;
         if constexpr (SPILL) {
@@ -136,6 +144,11 @@ __global__ void __launch_bounds__(NWG * SUBS * kTile, 1) chain_tc_fwd_kernel(TcA
             act_gp = a.stash_act + (size_t)b * a.stash_hw_pad + p;
         }
         // channels [C0, C0+KC0) of the features -> (hi, lo) -> TMEM A operand
+        // bf16 twin, wide chains: the TMA weight-gradient kernel wants fp32 rows, so the features go to the stash too
+        [[maybe_unused]] float *xrow = nullptr;
+        if constexpr (BF && SPILL) {
+            if (stash && a.stash_x != nullptr) xrow = a.stash_x + (size_t)b * a.stash_hw_pad + p;
+        }
         auto load_x = [&](auto c0_tag) {
             constexpr int C0 = decltype(c0_tag)::value;
             constexpr int KS = KC0 / SUBS;                        // channels of this round per sub-thread
@@ -146,13 +159,26 @@ __global__ void __launch_bounds__(NWG * SUBS * kTile, 1) chain_tc_fwd_kernel(TcA
                     uint32_t hi[16], lo[16];
 #pragma unroll
                     for (int j = 0; j < 16; j += 2) {
-                        const float v0 = xs[(C0 + c0 + j) * kTile], v1 = xs[(C0 + c0 + j + 1) * kTile];
+                        float v0, v1;
+                        if constexpr (BF) {
+                            v0 = bf16_to_f32(xs[(C0 + c0 + j) * kTile]);
+                            v1 = bf16_to_f32(xs[(C0 + c0 + j + 1) * kTile]);
+                        } else {
+                            v0 = xs[(C0 + c0 + j) * kTile];
+                            v1 = xs[(C0 + c0 + j + 1) * kTile];
+                            tf32_lo2(v0, v1, lo[j], lo[j + 1]);
+                        }
                         hi[j] = __float_as_uint(v0);
                         hi[j + 1] = __float_as_uint(v1);
-                        tf32_lo2(v0, v1, lo[j], lo[j + 1]);
+                        if constexpr (BF && SPILL) {
+                            if (xrow != nullptr) {
+                                xrow[(size_t)(C0 + c0 + j) * a.stash_npp] = v0;
+                                xrow[(size_t)(C0 + c0 + j + 1) * a.stash_npp] = v1;
+                            }
+                        }
                     }
                     tmem_st<16>(lane_addr + c0, hi);
-                    tmem_st<16>(lane_addr + AW + c0, lo);
+                    if constexpr (!BF) tmem_st<16>(lane_addr + AW + c0, lo);
                 }
             } else {
                 // up to 64 independent coalesced loads in flight per thread (a whole K round of the 128-channel chains:
@@ -163,7 +189,7 @@ __global__ void __launch_bounds__(NWG * SUBS * kTile, 1) chain_tc_fwd_kernel(TcA
                 for (int c0 = cb; c0 < cb + KS; c0 += LB) {
                     uint32_t hi[LB];
 #pragma unroll
-                    for (int j = 0; j < LB; ++j) hi[j] = valid ? __float_as_uint(__ldg(xp + (size_t)(C0 + c0 + j) * a.hw)) : 0u;
+                    for (int j = 0; j < LB; ++j) hi[j] = valid ? __float_as_uint(io_load<TIO>(xp + (size_t)(C0 + c0 + j) * a.hw)) : 0u;
 #pragma unroll
                     for (int h = 0; h < LB; h += 32) {
                         uint32_t h32[32], lo[32];
@@ -171,10 +197,16 @@ __global__ void __launch_bounds__(NWG * SUBS * kTile, 1) chain_tc_fwd_kernel(TcA
                         for (int j = 0; j < 32; j += 2) {
                             h32[j] = hi[h + j];
                             h32[j + 1] = hi[h + j + 1];
-                            tf32_lo2(__uint_as_float(hi[h + j]), __uint_as_float(hi[h + j + 1]), lo[j], lo[j + 1]);
+                            if constexpr (!BF) tf32_lo2(__uint_as_float(hi[h + j]), __uint_as_float(hi[h + j + 1]), lo[j], lo[j + 1]);
+                            if constexpr (BF && SPILL) {
+                                if (xrow != nullptr) {
+                                    xrow[(size_t)(C0 + c0 + h + j) * a.stash_npp] = __uint_as_float(hi[h + j]);
+                                    xrow[(size_t)(C0 + c0 + h + j + 1) * a.stash_npp] = __uint_as_float(hi[h + j + 1]);
+                                }
+                            }
                         }
                         tmem_st<32>(lane_addr + c0 + h, h32);
-                        tmem_st<32>(lane_addr + AW + c0 + h, lo);
+                        if constexpr (!BF) tmem_st<32>(lane_addr + AW + c0 + h, lo);
                     }
                 }
             }
@@ -185,14 +217,14 @@ __global__ void __launch_bounds__(NWG * SUBS * kTile, 1) chain_tc_fwd_kernel(TcA
         }
         load_x(std::integral_constant<int, 0>{});
         if constexpr (D0 > KC0) {
-            tc_run_chunk<CFG, 0, AW, 0, KC0, SUBS>(wg_base, sw, bar, phase, wg, lt);
+            tc_run_chunk<CFG, 0, AW, 0, KC0, SUBS, BF>(wg_base, sw, bar, phase, wg, lt);
             load_x(std::integral_constant<int, KC0>{});
         }
         if constexpr (PREFETCH) {
             tile_sync();                                          // the staged tile has been read by everyone who shares it
             prefetch(tile + stride);
         }
-        tc_run_chunk<CFG, 0, AW, D0 - KC0, KC0, SUBS>(wg_base, sw, bar, phase, wg, lt);
+        tc_run_chunk<CFG, 0, AW, D0 - KC0, KC0, SUBS, BF>(wg_base, sw, bar, phase, wg, lt);
         // wide layers
         if constexpr (CFG::NW > 1) tc_layer_from_d<CFG, 1, AW, SPILL, SUBS>(wg_base, lane_addr, sw, bar, phase, wg, lt, act_gp, a.stash_npp, stash, sub);
         if constexpr (CFG::NW > 2) tc_layer_from_d<CFG, 2, AW, SPILL, SUBS>(wg_base, lane_addr, sw, bar, phase, wg, lt, act_gp, a.stash_npp, stash, sub);
@@ -219,12 +251,12 @@ __global__ void __launch_bounds__(NWG * SUBS * kTile, 1) chain_tc_fwd_kernel(TcA
             }
         }
         if constexpr (FINAL) {
-            if (valid && sub == 0) a.out[gp] = sigmoidf(z[0]);
+            if (valid && sub == 0) io_store(reinterpret_cast<TIO *>(a.out) + gp, sigmoidf(z[0]));
         } else {
             const PlaneFwd pl = plane_from_logits(z[0], z[1], z[2], a.max_depth);
             if (a.out != nullptr && valid && sub == 0) {
-                float *o = a.out + (size_t)b * 4 * a.hw + p;
-                o[0] = pl.n1; o[(size_t)a.hw] = pl.n2; o[(size_t)2 * a.hw] = pl.n3; o[(size_t)3 * a.hw] = pl.n4;
+                TIO *o = reinterpret_cast<TIO *>(a.out) + (size_t)b * 4 * a.hw + p;
+                io_store(o, pl.n1); io_store(o + (size_t)a.hw, pl.n2); io_store(o + (size_t)2 * a.hw, pl.n3); io_store(o + (size_t)3 * a.hw, pl.n4);
             }
             if constexpr (kStashCfg<CFG>) {
                 if (stash && a.stash_pe != nullptr && sub == SUBS - 1) {
@@ -232,7 +264,7 @@ __global__ void __launch_bounds__(NWG * SUBS * kTile, 1) chain_tc_fwd_kernel(TcA
                     o[0] = pl.n1; o[(size_t)a.hw] = pl.n2; o[(size_t)2 * a.hw] = pl.n3; o[(size_t)3 * a.hw] = pl.n4;
                 }
             }
-            if (a.depth != nullptr) key = min(key, lpg_expand<R, (R % 2 == 0 ? SUBS : 1)>(a, pl.n1, pl.n2, pl.n3, pl.n4, gp, b, p, valid && (R % 2 == 0 || sub == 0), lane, sub));
+            if (a.depth != nullptr) key = min(key, lpg_expand<R, (R % 2 == 0 ? SUBS : 1), TIO>(a, pl.n1, pl.n2, pl.n3, pl.n4, gp, b, p, valid && (R % 2 == 0 || sub == 0), lane, sub));
         }
     }
     if constexpr (!FINAL) {
@@ -247,16 +279,16 @@ __global__ void __launch_bounds__(NWG * SUBS * kTile, 1) chain_tc_fwd_kernel(TcA
     if (tid < 32) tmem_dealloc(tbase, 512);
 }
 
-template <class CFG, int R, bool FINAL, int NWG, int AW, int SUBS>
+template <class CFG, int R, bool FINAL, int NWG, int AW, int SUBS, bool BF>
 static int launch_one(const ChainParams &cp, const TcArgs &a, int sms, cudaStream_t s)
 {
     constexpr int LAST = FINAL ? 1 : 3;
     constexpr size_t base = sizeof(float) * CFG::pack_floats(LAST) + (8 * NWG + 16 + 15) / 16 * 16;
-    constexpr size_t xs_bytes = (size_t)NWG * CFG::dim(0) * kTile * sizeof(float);
+    constexpr size_t xs_bytes = (size_t)NWG * CFG::dim(0) * kTile * (BF ? 2 : 4);
     constexpr bool CAN_PREFETCH = base + xs_bytes <= 227 * 1024;
     const bool prefetch = CAN_PREFETCH && a.x_vec16;
     const size_t smem = base + (prefetch ? xs_bytes : 0);
-    auto kern = prefetch ? chain_tc_fwd_kernel<CFG, R, FINAL, NWG, CAN_PREFETCH, AW, SUBS> : chain_tc_fwd_kernel<CFG, R, FINAL, NWG, false, AW, SUBS>;
+    auto kern = prefetch ? chain_tc_fwd_kernel<CFG, R, FINAL, NWG, CAN_PREFETCH, AW, SUBS, BF> : chain_tc_fwd_kernel<CFG, R, FINAL, NWG, false, AW, SUBS, BF>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     const long long ntiles = (a.npx + kTile - 1) / kTile;
@@ -268,6 +300,8 @@ static int launch_one(const ChainParams &cp, const TcArgs &a, int sms, cudaStrea
     return check_launch("chain_tc_fwd");
 }
 
+// header bytes at the start of the workspace (nothing is packed in HBM any more: every CTA builds its operand images
+// in shared memory); a small aligned prefix so that the scratch rows start 256-byte aligned
 size_t tc_pack_bytes() { return 128; }
 
 bool tc_supported(const ChainParams &cp)
@@ -276,16 +310,21 @@ bool tc_supported(const ChainParams &cp)
            cfg_matches<Cfg64_32>(cp) || cfg_matches<Cfg32_32>(cp) || cfg_matches<Cfg32_16>(cp);
 }
 
+template <class CFG, int NWG, int AW, int SUBS, bool BF>
+static int dispatch_r2(const ChainParams &cp, const TcArgs &a, int r, int sms, cudaStream_t s)
+{
+    if (cp.is_final) return launch_one<CFG, 1, true, NWG, AW, SUBS, BF>(cp, a, sms, s);
+    switch (r) {
+    case 8: return launch_one<CFG, 8, false, NWG, AW, SUBS, BF>(cp, a, sms, s);
+    case 4: return launch_one<CFG, 4, false, NWG, AW, SUBS, BF>(cp, a, sms, s);
+    case 2: return launch_one<CFG, 2, false, NWG, AW, SUBS, BF>(cp, a, sms, s);
+    default: return launch_one<CFG, 1, false, NWG, AW, SUBS, BF>(cp, a, sms, s);   // r == 1, or plane_eq only
+    }
+}
 template <class CFG, int NWG, int AW = CFG::kmax(), int SUBS = 1>
 static int dispatch_r(const ChainParams &cp, const TcArgs &a, int r, int sms, cudaStream_t s)
 {
-    if (cp.is_final) return launch_one<CFG, 1, true, NWG, AW, SUBS>(cp, a, sms, s);
-    switch (r) {
-    case 8: return launch_one<CFG, 8, false, NWG, AW, SUBS>(cp, a, sms, s);
-    case 4: return launch_one<CFG, 4, false, NWG, AW, SUBS>(cp, a, sms, s);
-    case 2: return launch_one<CFG, 2, false, NWG, AW, SUBS>(cp, a, sms, s);
-    default: return launch_one<CFG, 1, false, NWG, AW, SUBS>(cp, a, sms, s);   // r == 1, or plane_eq only
-    }
+    return a.bf16_io ? dispatch_r2<CFG, NWG, AW, SUBS, true>(cp, a, r, sms, s) : dispatch_r2<CFG, NWG, AW, SUBS, false>(cp, a, r, sms, s);
 }
 
 // r = 0: no LPG (reduction only). Returns BTS_ERR_UNSUPPORTED when the chain is not covered.

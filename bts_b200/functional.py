@@ -275,6 +275,131 @@ class _ReducLPG(torch.autograd.Function):
         return (None, gx, None, None, None, None, None, None, *gw_out)
 
 
+# ------------------------------------------------------------------------------------------------
+# bf16 twin (include/bts_b200.h, ABI 4): big tensors in bf16, weights fp32 (bf16 weights are upcast: 41 552 values),
+# arithmetic as in the fp32 path. Where the library has no native bf16 kernel (the backward of the two 128-channel
+# chains, odd shapes) the wrappers below run the fp32 CUDA path on upcast tensors -- still this library, never PyTorch
+# or CPU arithmetic.
+# ------------------------------------------------------------------------------------------------
+def _require_cuda_bf16(t, name):
+    if not isinstance(t, torch.Tensor) or not t.is_cuda or t.dtype != torch.bfloat16:
+        raise RuntimeError("%s must be a CUDA torch.bfloat16 tensor in the bf16 path" % name)
+    return t.contiguous()
+
+
+def _weights_f32(weights):
+    return _weights2d([w if w.dtype == torch.float32 else w.float() for w in weights])
+
+
+def _workspace_bf16(dims, B, h, w, r, device):
+    with torch.cuda.device(device):
+        n = max(_cabi.lib().bts_workspace_bytes_bf16(_cabi.int_array(dims), len(dims) - 1, B, h, w, r), 256)
+    ws = torch.empty((n + 3) // 4, dtype=torch.float32, device=device)
+    return ws, ws.data_ptr(), n
+
+
+def bf16_native(dims, is_final, backward, h, w, x=None):
+    """Does libbts_b200 serve this chain natively in bf16 (forward, or forward + backward)?"""
+    ok = bool(_cabi.lib().bts_bf16_supported(_cabi.int_array(list(dims)), len(dims) - 1, int(bool(is_final)), int(bool(backward))))
+    if ok and backward:
+        ok = (h * w) % 8 == 0 and (x is None or x.data_ptr() % 16 == 0)
+    return ok
+
+
+class _LPGBF(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, plane_eq, upratio):
+        plane_eq = _require_cuda_bf16(plane_eq, "plane_eq")
+        B, _, h, w = plane_eq.shape
+        r = int(upratio)
+        depth = torch.empty((B, h * r, w * r), dtype=torch.bfloat16, device=plane_eq.device)
+        abs_min = torch.full((), float("inf"), dtype=torch.float32, device=plane_eq.device)
+        with torch.cuda.device(plane_eq.device):
+            _cabi.check(_cabi.lib().bts_lpg_fwd_bf16(plane_eq.data_ptr(), depth.data_ptr(), abs_min.data_ptr(), B, h, w, r, EPS,
+                                                     _stream()), "bts_lpg_fwd_bf16")
+        ctx.save_for_backward(plane_eq)
+        ctx.r = r
+        ctx.mark_non_differentiable(abs_min)
+        ctx.set_materialize_grads(False)
+        return depth, abs_min
+
+    @staticmethod
+    def backward(ctx, grad_depth, _g=None):
+        (plane_eq,) = ctx.saved_tensors
+        grad_depth = _require_cuda_bf16(grad_depth.to(torch.bfloat16), "grad_depth")
+        B, _, h, w = plane_eq.shape
+        gpe = torch.empty_like(plane_eq)
+        with torch.cuda.device(plane_eq.device):
+            _cabi.check(_cabi.lib().bts_lpg_bwd_bf16(grad_depth.data_ptr(), plane_eq.data_ptr(), gpe.data_ptr(), B, h, w, ctx.r,
+                                                     EPS, _stream()), "bts_lpg_bwd_bf16")
+        return gpe, None
+
+
+class _ReducBF(torch.autograd.Function):
+    """reduction_1x1 (+ optionally the fused LPG stage when upratio > 0) in bf16 storage."""
+
+    @staticmethod
+    def forward(ctx, x, max_depth, is_final, upratio, scaled, want_plane_eq, *weights):
+        x = _require_cuda_bf16(x, "net")
+        ws = _weights_f32(weights)
+        dims = _dims(x, ws)
+        B, _, h, w = x.shape
+        r = int(upratio)
+        wsb, wsp, wsn = _workspace_bf16(dims, B, h, w, r, x.device)
+        W = _cabi.ptr_array([t.data_ptr() for t in ws])
+        outs = []
+        with torch.cuda.device(x.device):
+            if r == 0:
+                out = torch.empty((B, 1 if is_final else 4, h, w), dtype=torch.bfloat16, device=x.device)
+                _cabi.check(_cabi.lib().bts_reduc_fwd_bf16(x.data_ptr(), W, _cabi.int_array(dims), len(ws), int(bool(is_final)),
+                                                           float(max_depth), B, h, w, out.data_ptr(), wsp, wsn, _stream()),
+                            "bts_reduc_fwd_bf16")
+                outs = [out]
+            else:
+                depth = torch.empty((B, 1, h * r, w * r) if scaled else (B, h * r, w * r), dtype=torch.bfloat16, device=x.device)
+                abs_min = torch.full((), float("inf"), dtype=torch.float32, device=x.device)
+                pe = torch.empty((B, 4, h, w), dtype=torch.bfloat16, device=x.device) if want_plane_eq else None
+                _cabi.check(_cabi.lib().bts_reduc_lpg_fwd_bf16(
+                    x.data_ptr(), W, _cabi.int_array(dims), len(ws), float(max_depth), B, h, w, r, EPS,
+                    float(max_depth) if scaled else 1.0, pe.data_ptr() if want_plane_eq else None, depth.data_ptr(),
+                    abs_min.data_ptr(), wsp, wsn, _stream()), "bts_reduc_lpg_fwd_bf16")
+                ctx.mark_non_differentiable(abs_min)
+                outs = [depth, abs_min]
+                if want_plane_eq:
+                    ctx.mark_non_differentiable(pe)
+                    outs.append(pe)
+        ctx.save_for_backward(x, *ws)
+        ctx.cfg = (float(max_depth), bool(is_final), r, bool(scaled), dims, [(tuple(t.shape), t.dtype) for t in weights])
+        ctx.set_materialize_grads(False)
+        return outs[0] if len(outs) == 1 else tuple(outs)
+
+    @staticmethod
+    def backward(ctx, grad_out, *_rest):
+        x, *ws = ctx.saved_tensors
+        max_depth, is_final, r, scaled, dims, wmeta = ctx.cfg
+        B, _, h, w = x.shape
+        grad_out = _require_cuda_bf16(grad_out.to(torch.bfloat16), "grad_out")
+        need_x = ctx.needs_input_grad[0]
+        need_w = any(ctx.needs_input_grad[6:])
+        gx = torch.empty_like(x) if need_x else None
+        gws = _zero_grads(ws) if need_w else None
+        wsb, wsp, wsn = _workspace_bf16(dims, B, h, w, r, x.device)
+        W = _cabi.ptr_array([t.data_ptr() for t in ws])
+        GW = _cabi.ptr_array([t.data_ptr() for t in gws]) if need_w else None
+        with torch.cuda.device(x.device):
+            if r == 0:
+                _cabi.check(_cabi.lib().bts_reduc_bwd_bf16(x.data_ptr(), W, _cabi.int_array(dims), len(ws), int(is_final), max_depth,
+                                                           B, h, w, grad_out.data_ptr(), gx.data_ptr() if need_x else None, GW,
+                                                           wsp, wsn, _stream()), "bts_reduc_bwd_bf16")
+            else:
+                _cabi.check(_cabi.lib().bts_reduc_lpg_bwd_bf16(grad_out.data_ptr(), max_depth if scaled else 1.0, x.data_ptr(), W,
+                                                               _cabi.int_array(dims), len(ws), max_depth, B, h, w, r, EPS,
+                                                               gx.data_ptr() if need_x else None, GW, wsp, wsn, _stream()),
+                            "bts_reduc_lpg_bwd_bf16")
+        gw_out = [g.view(sh).to(dt) for g, (sh, dt) in zip(gws, wmeta)] if need_w else [None] * len(ws)
+        return (gx, None, None, None, None, None, *gw_out)
+
+
 class _Silog(torch.autograd.Function):
     """silog_loss.forward (pytorch/bts.py:46-48) and its autograd backward, without the mask gather."""
 
@@ -363,13 +488,27 @@ def backproject(depth, fx=518.8579, fy=518.8579, cx=None, cy=None, edge_thresh=0
     return pts[0] if single else pts
 
 
+def _any_grad(x, weights):
+    return torch.is_grad_enabled() and (x.requires_grad or any(w.requires_grad for w in weights))
+
+
 def lpg(plane_eq, upratio):
     """-> (depth [B,h*r,w*r], abs_min 0-dim). Drop-in math of local_planar_guidance.forward."""
+    if isinstance(plane_eq, torch.Tensor) and plane_eq.dtype == torch.bfloat16:
+        if int(upratio) in (1, 2, 4, 8):
+            return _LPGBF.apply(plane_eq, upratio)
+        depth, abs_min = _LPG.apply(plane_eq.float(), upratio)
+        return depth.to(torch.bfloat16), abs_min
     return _LPG.apply(plane_eq, upratio)
 
 
 def reduc(x, weights, max_depth, is_final=False):
     """-> [B,4,h,w] plane parameters, or [B,1,h,w] sigmoid head. Drop-in math of reduction_1x1.forward."""
+    if isinstance(x, torch.Tensor) and x.dtype == torch.bfloat16:
+        dims = [x.shape[1]] + [w.shape[0] for w in weights]
+        if x.is_cuda and bf16_native(dims, is_final, _any_grad(x, weights), x.shape[2], x.shape[3], x):
+            return _ReducBF.apply(x, max_depth, is_final, 0, False, False, *weights)
+        return _Reduc.apply(x.float(), max_depth, is_final, *[w.float() for w in weights]).to(torch.bfloat16)
     return _Reduc.apply(x, max_depth, is_final, *weights)
 
 
@@ -377,6 +516,16 @@ def reduc_lpg(x, weights, max_depth, upratio, return_plane_eq=False, scaled=Fals
     """Fused stage -> (depth, abs_min[, depth_ds][, plane_eq]). scaled: depth is [B,1,H,W] / max_depth
     (bts.py:255); downsample: also its nearest down-sampling by upratio/2, [B,1,2h,2w] (bts.py:256); out: a
     caller-owned [B,1,H,W] view (channel slice of a concat buffer) that receives the scaled map in place."""
+    if isinstance(x, torch.Tensor) and x.dtype == torch.bfloat16:
+        if downsample or out is not None:
+            raise RuntimeError("the bf16 twin has no down-sampled map and no strided destination (fp32 path only)")
+        dims = [x.shape[1]] + [w.shape[0] for w in weights]
+        r = int(upratio)
+        grad = _any_grad(x, weights)
+        if x.is_cuda and r in (1, 2, 4, 8) and bf16_native(dims, False, grad, x.shape[2], x.shape[3], x) and (not grad or r <= 2):
+            return _ReducBF.apply(x, max_depth, False, r, scaled, return_plane_eq, *weights)
+        res = _ReducLPG.apply(None, x.float(), max_depth, upratio, return_plane_eq, scaled, False, None, *[w.float() for w in weights])
+        return tuple(t.to(torch.bfloat16) if i != 1 else t for i, t in enumerate(res))
     if out is None:
         return _ReducLPG.apply(None, x, max_depth, upratio, return_plane_eq, scaled, downsample, None, *weights)
     abs_min = torch.full((), float("inf"), dtype=torch.float32, device=x.device)

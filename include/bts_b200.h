@@ -38,7 +38,7 @@ extern "C" {
 #define BTS_API
 #endif
 
-#define BTS_ABI_VERSION 3
+#define BTS_ABI_VERSION 4
 #define BTS_MAX_LAYERS 8      /* reduction_1x1 builds at most log2(num_out) layers */
 #define BTS_MAX_CHANNELS 512  /* per layer */
 
@@ -195,6 +195,38 @@ BTS_API int bts_silog_fwd(const float *depth_est, const float *depth_gt, const u
                   float variance_focus, float *loss, void *ws, size_t ws_bytes, void *stream);
 BTS_API int bts_silog_bwd(const float *depth_est, const float *depth_gt, const unsigned char *mask, long long n,
                   float variance_focus, const float *grad_loss, const void *ws, float *grad_est, void *stream);
+
+/*
+ * bf16 twin of the path (ABI 4; BASELINE.json north_star: "1e-2 for an optional bf16 path", configs[4] "fp32 and bf16").
+ * Each entry point is the bf16-storage twin of the fp32 one of the same name (and cites the same reference lines:
+ * pytorch/bts.py:124-136 reduction_1x1.forward, :149-173 local_planar_guidance.forward, :249-254 the fused stage, and
+ * their autograd backward): x, out / plane_eq, depth and the gradients of those are bf16 tensors (`void *`, 2-byte
+ * elements, same NCHW shapes), weights and weight gradients stay fp32 (master weights), abs_min stays one fp32 word.
+ * Arithmetic is the fp32 path's (3xTF32 tensor-core layers, fp32 SIMT tail) with ONE rounding to bf16 at each store; a
+ * bf16 input is exact in tf32, so its remainder pass is skipped. Bytes per full-resolution pixel are half of the fp32
+ * figures of SURVEY.md 8(d). Served: forward of every tensor-core chain (bts_bf16_supported(dims, n, final, 0)); backward
+ * of the two chains that carry 81 % of the bytes -- head 32->16->8->1 and 64->32->16->8->3 (upratio 1 / 2) -- when
+ * h*w % 8 == 0 and x is 16-byte aligned (bts_bf16_supported(.., 1)). Anything else returns BTS_ERR_UNSUPPORTED and the
+ * caller converts to fp32 (bts_b200/functional.py does). depth_div: 1, or max_depth for depth / max_depth (bts.py:255).
+ * Workspace: bts_workspace_bytes_bf16(). No stash, no strided destinations, no down-sampled map in the bf16 twin.
+ */
+BTS_API int bts_bf16_supported(const int *dims, int n_layers, int is_final, int backward);
+BTS_API size_t bts_workspace_bytes_bf16(const int *dims, int n_layers, int B, int h, int w, int r);
+BTS_API int bts_lpg_fwd_bf16(const void *plane_eq, void *depth, float *abs_min, int B, int h, int w, int r, float eps,
+                             void *stream);
+BTS_API int bts_lpg_bwd_bf16(const void *grad_depth, const void *plane_eq, void *grad_plane_eq, int B, int h, int w, int r,
+                             float eps, void *stream);
+BTS_API int bts_reduc_fwd_bf16(const void *x, const float *const *W, const int *dims, int n_layers, int is_final,
+                               float max_depth, int B, int h, int w, void *out, void *ws, size_t ws_bytes, void *stream);
+BTS_API int bts_reduc_bwd_bf16(const void *x, const float *const *W, const int *dims, int n_layers, int is_final,
+                               float max_depth, int B, int h, int w, const void *grad_out, void *grad_x,
+                               float *const *grad_W, void *ws, size_t ws_bytes, void *stream);
+BTS_API int bts_reduc_lpg_fwd_bf16(const void *x, const float *const *W, const int *dims, int n_layers, float max_depth,
+                                   int B, int h, int w, int r, float eps, float depth_div, void *plane_eq_out, void *depth,
+                                   float *abs_min, void *ws, size_t ws_bytes, void *stream);
+BTS_API int bts_reduc_lpg_bwd_bf16(const void *grad_depth, float depth_div, const void *x, const float *const *W,
+                                   const int *dims, int n_layers, float max_depth, int B, int h, int w, int r, float eps,
+                                   void *grad_x, float *const *grad_W, void *ws, size_t ws_bytes, void *stream);
 
 /*
  * bts_silog_fwd without a workspace and without any allocation. NO COUNTERPART IN THE REFERENCE: added at the
