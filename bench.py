@@ -55,6 +55,8 @@ def parse_args():
     ap.add_argument("--kernel-only", action="store_true", help="only the timed device loop (for ncu)")
     ap.add_argument("--e2e-serial", action="store_true", help="end-to-end leg on one stream (no upload/download overlap)")
     ap.add_argument("--no-graph", action="store_true", help="launch every step eagerly instead of replaying a CUDA graph")
+    ap.add_argument("--dtype", default="f32", choices=["f32", "bf16"],
+                    help="f32 (the reference's arithmetic: the headline) or the bf16 twin (bf16 storage, same arithmetic)")
     ap.add_argument("--grad-allreduce", action="store_true",
                     help="N > 1: every step ends with an NCCL all-reduce(avg) of the path's weight gradients as one "
                          "bucket, as DDP does in training (BASELINE.json configs[3]; pytorch/bts_main.py:314)")
@@ -187,11 +189,12 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------------
-def build_stages(wl, device, seed):
+def build_stages(wl, device, seed, dtype="f32"):
     """Modules with the reference constructor signatures + synthetic features resident in HBM."""
     import torch
     import bts_b200
     torch.manual_seed(seed)
+    td = torch.bfloat16 if dtype == "bf16" else torch.float32
     H, W, B = wl["H"], wl["W"], wl["B"]
     stages = []
     for name, cin, nout, r, final in STAGES:
@@ -200,8 +203,8 @@ def build_stages(wl, device, seed):
             if isinstance(m, torch.nn.Conv2d):
                 torch.nn.init.xavier_uniform_(m.weight)
         lpg = None if final else bts_b200.local_planar_guidance(r)
-        x = torch.randn(B, cin, H // r, W // r, device=device, requires_grad=True)
-        g = torch.randn((B, 1, H, W) if final else (B, H, W), device=device)
+        x = torch.randn(B, cin, H // r, W // r, device=device).to(td).requires_grad_(True)
+        g = torch.randn((B, 1, H, W) if final else (B, H, W), device=device).to(td)
         stages.append(dict(name=name, r=r, final=final, red=red, lpg=lpg, x=x, g=g))
     return stages
 
@@ -329,14 +332,37 @@ def time_back_to_back(fn, iters):
     return e0.elapsed_time(e1) / iters
 
 
-def time_calls(stages, wl, device, iters=20):
+def stage_calls_api(st):
+    """(forward, forward + backward) closures through the module API -- the bf16 twin's per-call timing: its backward of the
+    128-channel chains runs the fp32 kernels on upcast tensors, and that conversion belongs in the figure."""
+    import torch
+
+    def f():
+        with torch.no_grad():
+            return stage_forward(st)
+
+    def fb():
+        st["x"].grad = None
+        for p in st["red"].parameters():
+            p.grad = None
+        stage_forward(st).backward(st["g"])
+    return f, fb
+
+
+def time_calls(stages, wl, device, iters=20, dtype="f32"):
     """Per-call device times of each stage's forward and backward C-ABI call."""
     res = {}
     px = wl["B"] * wl["H"] * wl["W"]
+    scale = 0.5 if dtype == "bf16" else 1.0                       # bf16 storage: half the algorithmic bytes
     for st in stages:
-        f, b = stage_calls(st, wl, device)
-        tf, tb = time_back_to_back(f, iters), time_back_to_back(b, iters)
-        fb, bb = ALGO_BYTES[st["name"]]
+        if dtype == "bf16":
+            f, fbk = stage_calls_api(st)
+            tf = time_back_to_back(f, iters)
+            tb = max(time_back_to_back(fbk, iters) - tf, 1e-6)
+        else:
+            f, b = stage_calls(st, wl, device)
+            tf, tb = time_back_to_back(f, iters), time_back_to_back(b, iters)
+        fb, bb = (scale * v for v in ALGO_BYTES[st["name"]])
         res[st["name"]] = dict(fwd_ms=tf, bwd_ms=tb, fwd_gbs=fb * px / tf / 1e6, bwd_gbs=bb * px / tb / 1e6)
     return res
 
@@ -391,7 +417,7 @@ def e2e_leg(stages, wl, steps, warmup, device, pipelined=True):
     host_in = []
     for st in stages:
         host_in.append((st["x"].detach().cpu().pin_memory(), st["g"].cpu().pin_memory()))
-    h2d = sum(hx.numel() * 4 + hg.numel() * 4 for hx, hg in host_in)
+    h2d = sum(hx.numel() * hx.element_size() + hg.numel() * hg.element_size() for hx, hg in host_in)
     nset = 2 if pipelined else 1
     dev_in = [[(torch.empty_like(st["x"]).requires_grad_(True), torch.empty_like(st["g"])) for st in stages]
               for _ in range(nset)]
@@ -438,7 +464,7 @@ def e2e_leg(stages, wl, steps, warmup, device, pipelined=True):
             ev_free[j] = ev_comp[-1]
         if host_out[j] is None:
             host_out[j] = [[torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in res] for res in results]
-            d2h[0] = sum(t.numel() * 4 for res in results for t in res)
+            d2h[0] = sum(t.numel() * t.element_size() for res in results for t in res)
         with torch.cuda.stream(s_out):
             for k, (res, hres) in enumerate(zip(results, host_out[j])):
                 s_out.wait_event(ev_comp[k])
@@ -539,9 +565,10 @@ def main():
         _DIST["allreduce"] = bool(args.grad_allreduce)
     lib = _cabi.lib()
 
-    stages = build_stages(wl, device, seed=rank)
+    stages = build_stages(wl, device, seed=rank, dtype=args.dtype)
+    bscale = 0.5 if args.dtype == "bf16" else 1.0
     px_per_rank = wl["B"] * wl["H"] * wl["W"]
-    in_bytes = sum(st["x"].numel() * 4 + st["g"].numel() * 4 for st in stages)
+    in_bytes = sum((st["x"].numel() + st["g"].numel()) * st["x"].element_size() for st in stages)
 
     for _ in range(max(3, args.warmup)):
         gpu_step(stages)
@@ -594,24 +621,24 @@ def main():
         return
 
     # per-call device times -> roofline of the dominant call (the one that moves the most bytes)
-    calls = time_calls(stages, wl, device)
+    calls = time_calls(stages, wl, device, dtype=args.dtype)
     peak, peak_src = hbm_peak()
     dom = max(((n, d, k) for n, d in calls.items() for k in ("fwd", "bwd")),
               key=lambda t: ALGO_BYTES[t[0]][0 if t[2] == "fwd" else 1])
     dn, dd, dk = dom
-    algo_b = ALGO_BYTES[dn][0 if dk == "fwd" else 1] * px_per_rank
+    algo_b = bscale * ALGO_BYTES[dn][0 if dk == "fwd" else 1] * px_per_rank
     achieved = dd[dk + "_gbs"]
-    step_bytes = sum(sum(ALGO_BYTES[n]) for n in calls) * px_per_rank
+    step_bytes = bscale * sum(sum(ALGO_BYTES[n]) for n in calls) * px_per_rank
     roofline = {"bound": "hbm", "kernel": "%s %s" % (dn, dk), "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": measured_traffic("%s %s" % (dn, dk)), "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": algo_b, "launch_ms": dd[dk + "_ms"],
                 "whole_step": {"algorithmic_bytes": step_bytes, "achieved": step_bytes / (ms_step * 1e-3) / 1e9,
                                "frac": step_bytes / (ms_step * 1e-3) / 1e9 / peak},
-                "per_call": calls, "standalone_lpg": time_standalone_lpg(wl, device)}
+                "per_call": calls, "standalone_lpg": time_standalone_lpg(wl, device) if args.dtype == "f32" else None}
     # SURVEY.md 8(d) reports 2 and 3 from the per-call device times: the three LPG stages, and all four
     for key, names in (("lpg3", [n for n in calls if "lpg" in n]), ("lpg3_head", list(calls))):
         ms = sum(calls[n]["fwd_ms"] + calls[n]["bwd_ms"] for n in names)
-        by = sum(sum(ALGO_BYTES[n]) for n in names) * px_per_rank
+        by = bscale * sum(sum(ALGO_BYTES[n]) for n in names) * px_per_rank
         roofline[key] = {"ms": ms, "mpixels_per_s": px_per_rank / ms / 1e3, "achieved": by / ms / 1e6, "frac": by / ms / 1e6 / peak}
 
     e2e = None
@@ -638,7 +665,7 @@ def main():
             "metric": "LPG decoder Mpixels/s fwd+bwd", "value": value, "unit": "Mpixels/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_step,
             "ms_per_step_median": ms_median, "ms_per_step_max": ms_worst, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
             "config": {"workload": wl["desc"], "per_gpu_batch": wl["B"], "H": wl["H"], "W": wl["W"],
                        "max_depth": wl["max_depth"], "stages": [s[0] for s in STAGES], "parallelism": "batch-sharded x%d" % world + (
                            " + NCCL all-reduce(avg) of the weight gradients every step" if _DIST.get("allreduce") else ""),

@@ -62,18 +62,21 @@ struct FusedArgs {
 };
 
 // D[128 x N](TMEM, col d) = A[128 x K](TMEM; hi at a_hi, lo at a_lo) * B[N x K]^T (smem image at w: hi | lo)
-template <int K, int N>
+// NOLO: the A operand has no remainder part (bf16 features are exact in tf32): two passes instead of three
+template <int K, int N, bool NOLO = false>
 __device__ __forceinline__ void issue_ts3(uint32_t d, uint32_t a_hi, uint32_t a_lo, const float *w)
 {
     constexpr uint32_t LBO = 128, SBO = (K / 4) * 128;
     constexpr uint32_t idesc = idesc_tf32(kTile, N, 0, 0);
     const uint32_t whi = smem_u32(w), wlo = whi + N * K * 4;
+    if constexpr (!NOLO) {
+#pragma unroll
+        for (int k0 = 0; k0 < K; k0 += 8)
+            mma_tf32_ts(d, a_lo + k0, smem_desc(whi + (k0 / 4) * LBO, LBO, SBO), idesc, k0 > 0);
+    }
 #pragma unroll
     for (int k0 = 0; k0 < K; k0 += 8)
-        mma_tf32_ts(d, a_lo + k0, smem_desc(whi + (k0 / 4) * LBO, LBO, SBO), idesc, k0 > 0);
-#pragma unroll
-    for (int k0 = 0; k0 < K; k0 += 8)
-        mma_tf32_ts(d, a_hi + k0, smem_desc(wlo + (k0 / 4) * LBO, LBO, SBO), idesc, 1);
+        mma_tf32_ts(d, a_hi + k0, smem_desc(wlo + (k0 / 4) * LBO, LBO, SBO), idesc, NOLO ? k0 > 0 : 1);
 #pragma unroll
     for (int k0 = 0; k0 < K; k0 += 8)
         mma_tf32_ts(d, a_hi + k0, smem_desc(whi + (k0 / 4) * LBO, LBO, SBO), idesc, 1);
@@ -245,7 +248,9 @@ __device__ __forceinline__ void stage_b(const StageCtx &s, int row, float v)
     *reinterpret_cast<float *>(p + kBLo) = tf32_lo(v);
 }
 // rows row0 .. row0+31 of the A image <- 32 TMEM columns of this thread's lane (raw fp32 words)
-template <int kALo>
+// LOMODE 0: remainder rows computed and stored; 1: skipped (bf16 features: they are zero and were cleared once);
+// 2: zeros stored (bf16 features in a buffer whose remainder rows another job overwrites)
+template <int kALo, int LOMODE = 0>
 __device__ __forceinline__ void stage_a_from_tmem32(const StageCtx &s, int row0, uint32_t taddr)
 {
 #pragma unroll
@@ -254,7 +259,21 @@ __device__ __forceinline__ void stage_a_from_tmem32(const StageCtx &s, int row0,
         tmem_ld<16>(taddr + c0, r);
         wait_ld();
 #pragma unroll
-        for (int j = 0; j < 16; j += 2) stage_a2<kALo>(s, row0 + c0 + j, __uint_as_float(r[j]), __uint_as_float(r[j + 1]));
+        for (int j = 0; j < 16; j += 2) {
+            if constexpr (LOMODE == 0) {
+                stage_a2<kALo>(s, row0 + c0 + j, __uint_as_float(r[j]), __uint_as_float(r[j + 1]));
+            } else {
+                const int row = row0 + c0 + j;
+                unsigned char *p0 = s.sub + row * 128 + s.coff[row & 7];
+                unsigned char *p1 = s.sub + (row + 1) * 128 + s.coff[(row + 1) & 7];
+                *reinterpret_cast<uint32_t *>(p0) = r[j];
+                *reinterpret_cast<uint32_t *>(p1) = r[j + 1];
+                if constexpr (LOMODE == 2) {
+                    *reinterpret_cast<uint32_t *>(p0 + kALo) = 0u;
+                    *reinterpret_cast<uint32_t *>(p1 + kALo) = 0u;
+                }
+            }
+        }
     }
 }
 
@@ -329,6 +348,10 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
     // run it AFTER their first tile's copies have taken off, so the DRAM round trip hides behind the packing.
     uint32_t tbase = 0;
     auto prologue = [&]() {
+        if constexpr (BF) {                                       // remainder rows of the bf16 features stay zero for the whole kernel
+            for (size_t i = (size_t)tid * 16; i < L::stage_bytes; i += (size_t)NT * 16)
+                *reinterpret_cast<uint4 *>(stage + i) = make_uint4(0u, 0u, 0u, 0u);
+        }
         tc_pack_to_smem<CFG>(a.W, sw, LAST, tid, NT);
         tc_pack_t_to_smem<CFG>(a.W, swt, tid, NT);
         fence_smem_to_async();
@@ -623,7 +646,7 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
                     hi[j + 1] = __float_as_uint(v1);
                 }
                 tmem_st<16>(xh + c0, hi);
-                tmem_st<16>(xl + c0, lo);
+                if constexpr (!BF) tmem_st<16>(xl + c0, lo);      // (bf16: layer 0 skips the remainder pass)
             }
             float gcur[4] = {0.f, 0.f, 0.f, 0.f};
             if constexpr (GPRE && !BF) {
@@ -641,7 +664,7 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
                 if (lead_wg) {                                    // F0
                     fence_after_sync();
                     if (elect_one()) {
-                        issue_ts3<CFG::K(0), CFG::N(0)>(ddu, wbu, xlu, sw + CFG::w_off(0));
+                        issue_ts3<CFG::K(0), CFG::N(0), BF>(ddu, wbu, xlu, sw + CFG::w_off(0));
                         mma_commit(done);
                     }
                     __syncwarp();
@@ -770,7 +793,7 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
                 for (int j = 0; j < kTailMid; j += 2) stage_b2<L::SUBB>(sc, 16 + j, d8[j], d8[j + 1]);
 #pragma unroll
                 for (int j = 0; j < LAST; ++j) stage_b<L::SUBB>(sc, 24 + j, dz[j]);
-                if constexpr (NW == 1) stage_a_from_tmem32<L::ALO>(sc, 0, xh);
+                if constexpr (NW == 1) stage_a_from_tmem32<L::ALO, (BF ? (L::PRIV ? 1 : 2) : 0)>(sc, 0, xh);
                 fence_smem_to_async();
                 handoff(bid + 3 + half, 64, lead_pair, stg, [&]() { issue_wt(tacc); });           // WT(half)
             };
@@ -835,8 +858,8 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
 #pragma unroll
                         for (int j = 0; j < 16; j += 2) stage_b2<L::SUBB>(sc, n0 + j, __uint_as_float(r[j]), __uint_as_float(r[j + 1]));
                     }
-                    stage_a_from_tmem32<L::ALO>(sc, 0, xh);
-                    stage_a_from_tmem32<L::ALO>(sc, 32, xh + 32);
+                    stage_a_from_tmem32<L::ALO, (BF ? 2 : 0)>(sc, 0, xh);
+                    stage_a_from_tmem32<L::ALO, (BF ? 2 : 0)>(sc, 32, xh + 32);
                     fence_smem_to_async();
                     handoff(bid + 3 + half, 64, lead_pair, stg, [&]() { issue_wt(tacc + 64); });    // WX(half)
                 };

@@ -70,14 +70,18 @@ __device__ __forceinline__ float elu_fast(float t)
 // ---- bf16 storage (the optional bf16 twin of the path: big tensors in bf16, arithmetic unchanged). A bf16 value is
 // the top 16 bits of the fp32 word, hence exactly representable in tf32: the 3xTF32 remainder of a bf16 input is zero.
 __device__ __forceinline__ float bf16_to_f32(unsigned short v) { return __uint_as_float((uint32_t)v << 16); }
-__device__ __forceinline__ unsigned short f32_to_bf16(float v)        // round to nearest even, NaN kept quiet
+__device__ __forceinline__ unsigned short f32_to_bf16(float v)        // round to nearest even (one hardware instruction)
 {
-    uint32_t u = __float_as_uint(v);
-    if ((u & 0x7fffffffu) > 0x7f800000u) return (unsigned short)((u >> 16) | 0x40u);
-    u += 0x7fffu + ((u >> 16) & 1u);
-    return (unsigned short)(u >> 16);
+    unsigned short r;
+    asm("cvt.rn.bf16.f32 %0, %1;" : "=h"(r) : "f"(v));
+    return r;
 }
-__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) { return (uint32_t)f32_to_bf16(lo) | ((uint32_t)f32_to_bf16(hi) << 16); }
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi)   // {hi : lo}, both rounded to nearest even
+{
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
 // element i of a tensor stored as T (float or bf16 = unsigned short)
 template <class T> __device__ __forceinline__ float io_load(const T *p);
 template <> __device__ __forceinline__ float io_load<float>(const float *p) { return __ldg(p); }
