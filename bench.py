@@ -60,6 +60,9 @@ def parse_args():
     ap.add_argument("--grad-allreduce", action="store_true",
                     help="N > 1: every step ends with an NCCL all-reduce(avg) of the path's weight gradients as one "
                          "bucket, as DDP does in training (BASELINE.json configs[3]; pytorch/bts_main.py:314)")
+    ap.add_argument("--allreduce-buckets", default="two", choices=["per-stage", "two", "one"],
+                    help="--grad-allreduce: one collective per stage as soon as its backward is enqueued; two (the three LPG "
+                         "stages under the head's kernels, then the head's 648 floats); or one at the end of the step")
     return ap.parse_args()
 
 
@@ -231,9 +234,24 @@ def _flat_grads(params):
 
 def gpu_step(stages):
     """fwd + bwd of the four stages through the public module API (autograd drives the backward)."""
-    outs, works = [], []
+    outs, works, pending = [], [], []
     allreduce = _DIST["on"] and _DIST.get("allreduce")
-    for st in stages:
+    policy = _DIST.get("buckets", "two")
+
+    def reduce_now(param_groups):
+        # what DDP's buckets do (pytorch/bts_main.py:314): weight gradients are averaged over the ranks on NCCL's own
+        # stream, under the kernels that follow. A group whose gradients share one buffer is reduced in place.
+        import torch
+        import torch.distributed as dist
+        flats = [(_flat_grads(ps), ps) for ps in param_groups]
+        if len(flats) == 1 and flats[0][0] is not None:
+            works.append((dist.all_reduce(flats[0][0], op=dist.ReduceOp.AVG, async_op=True), flats[0][0], None))
+            return
+        params = [p for ps in param_groups for p in ps]           # several stages (or a foreign layout): one copy each way
+        flat = torch.cat([p.grad.reshape(-1) for p in params])
+        works.append((dist.all_reduce(flat, op=dist.ReduceOp.AVG, async_op=True), flat, params))
+
+    for k, st in enumerate(stages):
         st["x"].grad = None
         for p in st["red"].parameters():
             p.grad = None
@@ -241,18 +259,11 @@ def gpu_step(stages):
         out.backward(st["g"])
         outs.append(out)
         if allreduce:
-            # what DDP's buckets do (pytorch/bts_main.py:314): a stage's weight gradients are averaged over the ranks as
-            # soon as its backward is enqueued -- on NCCL's own stream, under the next stage's kernels. Only the head's
-            # 648 floats are exposed at the end of the step.
-            import torch
-            import torch.distributed as dist
-            params = list(st["red"].parameters())
-            flat = _flat_grads(params)
-            if flat is None:                                       # foreign gradient layout: one copy each way
-                flat = torch.cat([p.grad.reshape(-1) for p in params])
-                works.append((dist.all_reduce(flat, op=dist.ReduceOp.AVG, async_op=True), flat, params))
-            else:
-                works.append((dist.all_reduce(flat, op=dist.ReduceOp.AVG, async_op=True), flat, None))
+            pending.append(list(st["red"].parameters()))
+            last = k + 1 == len(stages)
+            if policy == "per-stage" or last or (policy == "two" and k + 2 == len(stages)):
+                reduce_now(pending)
+                pending = []
     for work, flat, params in works:
         work.wait()                                               # the compute stream waits for the collective
         if params is not None:
@@ -563,6 +574,7 @@ def main():
         dist.init_process_group("nccl", device_id=device)
         _DIST["on"] = True
         _DIST["allreduce"] = bool(args.grad_allreduce)
+        _DIST["buckets"] = args.allreduce_buckets
     lib = _cabi.lib()
 
     stages = build_stages(wl, device, seed=rank, dtype=args.dtype)
@@ -668,7 +680,7 @@ def main():
             "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
             "config": {"workload": wl["desc"], "per_gpu_batch": wl["B"], "H": wl["H"], "W": wl["W"],
                        "max_depth": wl["max_depth"], "stages": [s[0] for s in STAGES], "parallelism": "batch-sharded x%d" % world + (
-                           " + NCCL all-reduce(avg) of the weight gradients every step" if _DIST.get("allreduce") else ""),
+                           " + NCCL all-reduce(avg) of the weight gradients every step (%s)" % _DIST.get("buckets") if _DIST.get("allreduce") else ""),
                        "l2": "inputs %.0f MB per step > 126 MB L2 (no flush needed)" % (in_bytes / 1e6),
                        "api": "bts_b200.reduction_1x1 / fused_stage via libbts_b200.so C ABI",
                        "launch": launch_mode},
