@@ -60,10 +60,11 @@ _SIGNATURES["bts_bf16_supported"] = (ctypes.c_int, [_P, _I, _I, _I])
 _SIGNATURES["bts_workspace_bytes_bf16"] = (ctypes.c_size_t, [_P, _I, _I, _I, _I, _I])
 _SIGNATURES["bts_lpg_fwd_bf16"] = (ctypes.c_int, [_P, _P, _P, _I, _I, _I, _I, _F, _P])
 _SIGNATURES["bts_lpg_bwd_bf16"] = (ctypes.c_int, [_P, _P, _P, _I, _I, _I, _I, _F, _P])
-_SIGNATURES["bts_reduc_fwd_bf16"] = (ctypes.c_int, [_P, _P, _P, _I, _I, _F, _I, _I, _I, _P, _P, _SZ, _P])
-_SIGNATURES["bts_reduc_bwd_bf16"] = (ctypes.c_int, [_P, _P, _P, _I, _I, _F, _I, _I, _I, _P, _P, _P, _P, _SZ, _P])
-_SIGNATURES["bts_reduc_lpg_fwd_bf16"] = (ctypes.c_int, [_P, _P, _P, _I, _F, _I, _I, _I, _I, _F, _F, _P, _P, _P, _P, _SZ, _P])
-_SIGNATURES["bts_reduc_lpg_bwd_bf16"] = (ctypes.c_int, [_P, _F, _P, _P, _P, _I, _F, _I, _I, _I, _I, _F, _P, _P, _P, _SZ, _P])
+_SIGNATURES["bts_stash_bytes_bf16"] = (ctypes.c_size_t, [_P, _I, _I, _I, _I])
+_SIGNATURES["bts_reduc_fwd_bf16"] = (ctypes.c_int, [_P, _P, _P, _I, _I, _F, _I, _I, _I, _P, _P, _SZ, _P, _SZ, _P])
+_SIGNATURES["bts_reduc_bwd_bf16"] = (ctypes.c_int, [_P, _P, _P, _I, _I, _F, _I, _I, _I, _P, _P, _P, _P, _SZ, _P, _SZ, _P])
+_SIGNATURES["bts_reduc_lpg_fwd_bf16"] = (ctypes.c_int, [_P, _P, _P, _I, _F, _I, _I, _I, _I, _F, _F, _P, _P, _P, _P, _SZ, _P, _SZ, _P])
+_SIGNATURES["bts_reduc_lpg_bwd_bf16"] = (ctypes.c_int, [_P, _F, _P, _P, _P, _I, _F, _I, _I, _I, _I, _F, _P, _P, _P, _SZ, _P, _SZ, _P])
 _SIGNATURES["bts_silog_fwd_static"] = (ctypes.c_int, [_P, _P, _P, _LL, _F, _P, _P, _P])
 _SIGNATURES["bts_eval_workspace_bytes"] = (ctypes.c_size_t, [_I, _I, _I])
 _SIGNATURES["bts_eval_metrics"] = (ctypes.c_int, [_P, _P, _I, _I, _I, _F, _F, _I, _I, _I, _I, _P, _P, _P, _SZ, _P])

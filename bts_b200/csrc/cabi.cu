@@ -57,6 +57,7 @@ size_t tc_bwd_workspace_bytes(const ChainParams &, int B, int hw, int sms);
 int launch_chain_tc_bwd_stash(const ChainParams &, const TcArgs &, int mode, int r, void *ws, int sms, cudaStream_t);
 bool tc_stash_supported(const ChainParams &, int hw, const void *x);
 size_t tc_stash_bytes(const ChainParams &, int B, int hw);
+size_t tc_stash_bytes_bf16(const ChainParams &, int B, int hw);
 int tc_stash_bind(const ChainParams &, TcArgs &, void *stash, bool clear, cudaStream_t);
 
 size_t silog_workspace_bytes(int sms);
@@ -473,12 +474,21 @@ static TcArgs make_tc_args_bf16(const void *x, int B, int h, int w, float max_de
     return a;
 }
 
-// bytes the bf16 entry points need: the one-pass backward only keeps per-CTA partial sums (deterministic route)
-static size_t bf16_ws_bytes(const ChainParams &cp)
+// bytes the bf16 entry points need: the one-pass backward only keeps per-CTA partial sums (deterministic route); the
+// stash backward of the wider chains needs the delta rows and partials of the fp32 path
+static size_t bf16_ws_bytes(const ChainParams &cp, int B, int hw)
 {
+    if (!fused_bwd_supported(cp)) return 2 * tc_pack_bytes() + tc_bwd_workspace_bytes(cp, B, hw, sm_count());
     size_t tw = 0;
     for (int l = 0; l < cp.n_layers; ++l) tw += (size_t)cp.dims[l] * cp.dims[l + 1];
     return 2 * tc_pack_bytes() + sizeof(float) * tw * (size_t)sm_count();
+}
+
+static bool fake_chain(ChainParams &cp, const int *dims, int n_layers, int is_final)
+{
+    static const float *fake[BTS_MAX_LAYERS];
+    for (int l = 0; l < BTS_MAX_LAYERS; ++l) fake[l] = reinterpret_cast<const float *>(16);
+    return dims && n_layers >= 1 && n_layers <= BTS_MAX_LAYERS && fill_chain(cp, fake, nullptr, dims, n_layers, is_final, 1.f) == BTS_OK;
 }
 
 size_t bts_workspace_bytes_bf16(const int *dims, int n_layers, int B, int h, int w, int r)
@@ -486,21 +496,36 @@ size_t bts_workspace_bytes_bf16(const int *dims, int n_layers, int B, int h, int
     (void)r;
     if (B <= 0 || h <= 0 || w <= 0) return 0;
     ChainParams cp;
-    const float *fake[BTS_MAX_LAYERS];
-    for (int l = 0; l < BTS_MAX_LAYERS; ++l) fake[l] = reinterpret_cast<const float *>(16);
     const int last = (dims && n_layers >= 1 && n_layers <= BTS_MAX_LAYERS) ? dims[n_layers] : 0;
-    if (!last || fill_chain(cp, fake, nullptr, dims, n_layers, last == 1, 1.f) != BTS_OK) return 0;
-    return bf16_ws_bytes(cp);
+    if (!last || !fake_chain(cp, dims, n_layers, last == 1)) return 0;
+    return bf16_ws_bytes(cp, B, h * w);
 }
 
+size_t bts_stash_bytes_bf16(const int *dims, int n_layers, int B, int h, int w)
+{
+    if (B <= 0 || h <= 0 || w <= 0) return 0;
+    ChainParams cp;
+    const int last = (dims && n_layers >= 1 && n_layers <= BTS_MAX_LAYERS) ? dims[n_layers] : 0;
+    if (!last || !fake_chain(cp, dims, n_layers, last == 1)) return 0;
+    if (!tc_stash_supported(cp, h * w, reinterpret_cast<const void *>(16))) return 0;
+    return tc_stash_bytes_bf16(cp, B, h * w);
+}
+
+// backward: 1 = one-pass kernel (no stash), 2 = stash route (hand the forward a bts_stash_bytes_bf16() buffer), 0 = none
 int bts_bf16_supported(const int *dims, int n_layers, int is_final, int backward)
 {
     ChainParams cp;
-    const float *fake[BTS_MAX_LAYERS];
-    for (int l = 0; l < BTS_MAX_LAYERS; ++l) fake[l] = reinterpret_cast<const float *>(16);
-    if (fill_chain(cp, fake, nullptr, dims, n_layers, is_final, 1.f)) return 0;
+    if (!fake_chain(cp, dims, n_layers, is_final)) return 0;
     if (!tc_supported(cp)) return 0;
-    return backward ? (fused_bwd_supported(cp) ? 1 : 0) : 1;
+    if (!backward) return 1;
+    if (fused_bwd_supported(cp)) return 1;
+    return tc_stash_supported(cp, 32, reinterpret_cast<const void *>(16)) ? 2 : 0;
+}
+
+static bool use_stash_bf16(const ChainParams &cp, const void *x, int B, int hw, const void *stash, size_t stash_bytes)
+{
+    if (stash == nullptr || !aligned16(stash)) return false;
+    return tc_stash_supported(cp, hw, x) && stash_bytes >= tc_stash_bytes_bf16(cp, B, hw);
 }
 
 int bts_lpg_fwd_bf16(const void *plane_eq, void *depth, float *abs_min, int B, int h, int w, int r, float eps, void *stream)
@@ -523,7 +548,7 @@ int bts_lpg_bwd_bf16(const void *grad_depth, const void *plane_eq, void *grad_pl
 }
 
 int bts_reduc_fwd_bf16(const void *x, const float *const *W, const int *dims, int n_layers, int is_final, float max_depth,
-                       int B, int h, int w, void *out, void *ws, size_t ws_bytes, void *stream)
+                       int B, int h, int w, void *out, void *ws, size_t ws_bytes, void *stash, size_t stash_bytes, void *stream)
 {
     ChainParams cp;
     if (int e = fill_chain(cp, W, nullptr, dims, n_layers, is_final, max_depth)) return e;
@@ -534,12 +559,14 @@ int bts_reduc_fwd_bf16(const void *x, const float *const *W, const int *dims, in
         return set_error(BTS_ERR_UNSUPPORTED, "the bf16 twin serves the chains of the tensor-core path (and needs a workspace)");
     TcArgs a = make_tc_args_bf16(x, B, h, w, max_depth, 0.f);
     a.out = static_cast<float *>(out);
+    if (use_stash_bf16(cp, x, B, h * w, stash, stash_bytes))
+        if (int e = tc_stash_bind(cp, a, stash, true, (cudaStream_t)stream)) return e;
     return launch_chain_tc_fwd(cp, a, 0, sm_count(), (cudaStream_t)stream);
 }
 
 int bts_reduc_bwd_bf16(const void *x, const float *const *W, const int *dims, int n_layers, int is_final, float max_depth,
                        int B, int h, int w, const void *grad_out, void *grad_x, float *const *grad_W, void *ws,
-                       size_t ws_bytes, void *stream)
+                       size_t ws_bytes, const void *stash, size_t stash_bytes, void *stream)
 {
     ChainParams cp;
     if (int e = fill_chain(cp, W, grad_W, dims, n_layers, is_final, max_depth)) return e;
@@ -547,16 +574,22 @@ int bts_reduc_bwd_bf16(const void *x, const float *const *W, const int *dims, in
     if ((long long)B * h * w == 0) return BTS_OK;
     if (!x || !grad_out) return set_error(BTS_ERR_BAD_ARG, "x / grad_out is NULL");
     TcArgs a = make_tc_args_bf16(x, B, h, w, max_depth, 0.f);
-    if (!use_tc(cp, ws, ws_bytes, nullptr) || ws_bytes < bf16_ws_bytes(cp) || !fused_bwd_supported(cp) || !a.x_vec16)
-        return set_error(BTS_ERR_UNSUPPORTED, "bf16 backward: chains 32->16->8 and 64->32->16->8 with h*w %% 8 == 0 and 16-byte aligned x");
     a.grad = static_cast<const float *>(grad_out);
     a.grad_x = static_cast<float *>(grad_x);
-    return launch_chain_bwd_fused(cp, a, is_final ? 0 : 1, 0, ws, sm_count(), (cudaStream_t)stream);
+    if (!use_tc(cp, ws, ws_bytes, nullptr) || ws_bytes < bf16_ws_bytes(cp, B, h * w))
+        return set_error(BTS_ERR_UNSUPPORTED, "bf16 backward: chain outside the tensor-core path, or workspace below bts_workspace_bytes_bf16()");
+    if (fused_bwd_supported(cp) && a.x_vec16)
+        return launch_chain_bwd_fused(cp, a, is_final ? 0 : 1, 0, ws, sm_count(), (cudaStream_t)stream);
+    if (use_stash_bf16(cp, x, B, h * w, stash, stash_bytes)) {
+        if (int e = tc_stash_bind(cp, a, const_cast<void *>(stash), false, (cudaStream_t)stream)) return e;
+        return launch_chain_tc_bwd_stash(cp, a, is_final ? 0 : 1, 0, ws, sm_count(), (cudaStream_t)stream);
+    }
+    return set_error(BTS_ERR_UNSUPPORTED, "bf16 backward needs h*w %% 8 == 0 and a 16-byte aligned x (one-pass chains) or the stash the forward filled");
 }
 
 int bts_reduc_lpg_fwd_bf16(const void *x, const float *const *W, const int *dims, int n_layers, float max_depth, int B, int h,
                            int w, int r, float eps, float depth_div, void *plane_eq_out, void *depth, float *abs_min,
-                           void *ws, size_t ws_bytes, void *stream)
+                           void *ws, size_t ws_bytes, void *stash, size_t stash_bytes, void *stream)
 {
     ChainParams cp;
     if (int e = fill_chain(cp, W, nullptr, dims, n_layers, 0, max_depth)) return e;
@@ -569,12 +602,14 @@ int bts_reduc_lpg_fwd_bf16(const void *x, const float *const *W, const int *dims
     TcArgs a = make_tc_args_bf16(x, B, h, w, max_depth, eps);
     a.out = static_cast<float *>(plane_eq_out); a.depth = static_cast<float *>(depth); a.abs_min = abs_min;
     a.depth_div = depth_div; a.depth_bstride = (long long)h * r * w * r;
+    if (use_stash_bf16(cp, x, B, h * w, stash, stash_bytes))
+        if (int e = tc_stash_bind(cp, a, stash, true, (cudaStream_t)stream)) return e;
     return launch_chain_tc_fwd(cp, a, r, sm_count(), (cudaStream_t)stream);
 }
 
 int bts_reduc_lpg_bwd_bf16(const void *grad_depth, float depth_div, const void *x, const float *const *W, const int *dims,
                            int n_layers, float max_depth, int B, int h, int w, int r, float eps, void *grad_x,
-                           float *const *grad_W, void *ws, size_t ws_bytes, void *stream)
+                           float *const *grad_W, void *ws, size_t ws_bytes, const void *stash, size_t stash_bytes, void *stream)
 {
     ChainParams cp;
     if (int e = fill_chain(cp, W, grad_W, dims, n_layers, 0, max_depth)) return e;
@@ -583,13 +618,18 @@ int bts_reduc_lpg_bwd_bf16(const void *grad_depth, float depth_div, const void *
     if ((long long)B * h * w == 0) return BTS_OK;
     if (!x || !grad_depth) return set_error(BTS_ERR_BAD_ARG, "x / grad_depth is NULL");
     TcArgs a = make_tc_args_bf16(x, B, h, w, max_depth, eps);
-    // the one-pass backward prefetches the r x r block of grad_depth per low-res pixel: upratio 1 and 2 only
-    if (!(r == 1 || r == 2) || !use_tc(cp, ws, ws_bytes, grad_depth) || ws_bytes < bf16_ws_bytes(cp) || !fused_bwd_supported(cp) ||
-        !a.x_vec16)
-        return set_error(BTS_ERR_UNSUPPORTED, "bf16 fused backward: chain 64->32->16->8->3 at upratio 1 or 2, h*w %% 8 == 0, aligned x");
     a.grad = static_cast<const float *>(grad_depth); a.grad_x = static_cast<float *>(grad_x);
     a.depth_div = depth_div; a.grad_bstride = (long long)h * r * w * r;
-    return launch_chain_bwd_fused(cp, a, 2, r, ws, sm_count(), (cudaStream_t)stream);
+    if (!(r == 1 || r == 2 || r == 4 || r == 8) || !use_tc(cp, ws, ws_bytes, grad_depth) || ws_bytes < bf16_ws_bytes(cp, B, h * w))
+        return set_error(BTS_ERR_UNSUPPORTED, "bf16 fused backward: tensor-core chains at upratio 1, 2, 4, 8 with a bts_workspace_bytes_bf16() workspace");
+    // the one-pass backward prefetches the r x r block of grad_depth per low-res pixel: upratio 1 and 2 only
+    if (fused_bwd_supported(cp) && a.x_vec16 && r <= 2)
+        return launch_chain_bwd_fused(cp, a, 2, r, ws, sm_count(), (cudaStream_t)stream);
+    if (use_stash_bf16(cp, x, B, h * w, stash, stash_bytes)) {
+        if (int e = tc_stash_bind(cp, a, const_cast<void *>(stash), false, (cudaStream_t)stream)) return e;
+        return launch_chain_tc_bwd_stash(cp, a, 2, r, ws, sm_count(), (cudaStream_t)stream);
+    }
+    return set_error(BTS_ERR_UNSUPPORTED, "bf16 fused backward needs the one-pass chain (upratio <= 2, h*w %% 8 == 0) or the stash the forward filled");
 }
 
 }  // extern "C"

@@ -270,14 +270,21 @@ __device__ __forceinline__ void dgrad_layer(const BwdArgs &ba, uint32_t wg_base,
     }
     if constexpr (L == 0) {
         float *gx = ba.a.grad_x + (size_t)b * NP * ba.a.hw + p;
+        unsigned short *gxh = reinterpret_cast<unsigned short *>(ba.a.grad_x) + (size_t)b * NP * ba.a.hw + p;   // bf16 twin
+        const bool bf = ba.a.bf16_io != 0;
 #pragma unroll 1
         for (int n0 = 0; n0 < NP; n0 += 16) {
             uint32_t r[16];
             tmem_ld<16>(lane_addr + 2 * AW + n0, r);
             wait_ld();
             if (valid) {
+                if (bf) {
 #pragma unroll
-                for (int j = 0; j < 16; ++j) gx[(size_t)(n0 + j) * ba.a.hw] = __uint_as_float(r[j]);
+                    for (int j = 0; j < 16; ++j) gxh[(size_t)(n0 + j) * ba.a.hw] = f32_to_bf16(__uint_as_float(r[j]));
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) gx[(size_t)(n0 + j) * ba.a.hw] = __uint_as_float(r[j]);
+                }
             }
         }
     } else {
@@ -725,7 +732,9 @@ size_t tc_bwd_workspace_bytes(const ChainParams &cp, int B, int hw, int sms)
 
 bool wgrad_tma_supported(const ChainParams &cp, int hw, const void *x);
 int launch_wgrad_tma(const ChainParams &cp, const float *x, const float *act, const float *del, float *partials,
-                     int B, int hw, int hw_pad, long long npp, int sms, cudaStream_t s);
+                     int B, int hw, int hw_pad, long long npp, int sms, cudaStream_t s, const float *x_rows = nullptr);
+int launch_lpg_bwd_bf16_to_f32(const void *, const float *, float *, int, int, int, int, float, float, cudaStream_t);
+int launch_cvt_bf16_to_f32(const void *, float *, long long, cudaStream_t);
 
 static int build_wgrad_plan(const ChainParams &cp, WPlan &pl, const float *x, float *act, float *del,
                             long long npx, long long npp, int hw)
@@ -873,6 +882,12 @@ size_t tc_stash_bytes(const ChainParams &cp, int B, int hw)
     const long long npp = pad128((long long)B * pad32(hw));
     return sizeof(float) * (stash_act_rows(cp) * (size_t)npp + (cp.is_final ? 0 : (size_t)4 * B * hw));
 }
+// bf16 twin: the stash also holds the features as fp32 rows [D0][npp] (the TMA weight-gradient kernel's operand)
+size_t tc_stash_bytes_bf16(const ChainParams &cp, int B, int hw)
+{
+    const long long npp = pad128((long long)B * pad32(hw));
+    return tc_stash_bytes(cp, B, hw) + sizeof(float) * (size_t)cp.dims[0] * (size_t)npp;
+}
 
 // point the TcArgs at the stash; with `clear`, zero the activation rows when the padded pixel axis has
 // columns no forward thread writes (the weight-gradient MMAs read whole rows)
@@ -882,9 +897,14 @@ int tc_stash_bind(const ChainParams &cp, TcArgs &a, void *stash, bool clear, cud
     a.stash_npp = pad128((long long)a.B * a.stash_hw_pad);
     a.stash_act = static_cast<float *>(stash);
     a.stash_pe = cp.is_final ? nullptr : a.stash_act + stash_act_rows(cp) * (size_t)a.stash_npp;
+    a.stash_x = a.bf16_io ? a.stash_act + stash_act_rows(cp) * (size_t)a.stash_npp + (cp.is_final ? 0 : (size_t)4 * a.B * a.hw) : nullptr;
     if (clear && a.stash_npp != a.npx) {
         cudaError_t e = cudaMemsetAsync(stash, 0, sizeof(float) * stash_act_rows(cp) * (size_t)a.stash_npp, s);
         if (e != cudaSuccess) return set_error((int)e, "cudaMemsetAsync(stash): %s", cudaGetErrorString(e));
+        if (a.stash_x != nullptr) {
+            e = cudaMemsetAsync(a.stash_x, 0, sizeof(float) * (size_t)cp.dims[0] * (size_t)a.stash_npp, s);
+            if (e != cudaSuccess) return set_error((int)e, "cudaMemsetAsync(stash x rows): %s", cudaGetErrorString(e));
+        }
     }
     return BTS_OK;
 }
@@ -907,10 +927,19 @@ static int launch_bwd_stash_cfg(const ChainParams &cp, const TcArgs &a, int r, c
         tc_set_weights(ba.a, cp);
         ba.act = a.stash_act; ba.del = del; ba.npx_pad = npp; ba.hw_pad = a.stash_hw_pad;
         ba.w4 = cp.W[CFG::NW]; ba.w5 = cp.W[CFG::NW + 1];
+        bool chained = TM == 1 && r > 0;     // the dgrad kernel follows a kernel of this call (programmatic dependent launch)
         if (TM == 1 && r > 0) {              // grad_depth -> gradient of the plane parameters [B][4][hw]
-            const LpgGlue gl{a.depth_div, a.grad_bstride, nullptr, a.grad_ds, a.grad_ds_bstride};
-            if (int e = launch_lpg_bwd_glue(a.grad, a.stash_pe, scratch, a.B, a.h, a.w, r, a.eps, gl, s)) return e;
+            if (a.bf16_io) {
+                if (int e = launch_lpg_bwd_bf16_to_f32(a.grad, a.stash_pe, scratch, a.B, a.h, a.w, r, a.eps, a.depth_div, s)) return e;
+            } else {
+                const LpgGlue gl{a.depth_div, a.grad_bstride, nullptr, a.grad_ds, a.grad_ds_bstride};
+                if (int e = launch_lpg_bwd_glue(a.grad, a.stash_pe, scratch, a.B, a.h, a.w, r, a.eps, gl, s)) return e;
+            }
             ba.a.grad = scratch;
+        } else if (a.bf16_io) {              // bf16 gradient of the head output / plane parameters -> fp32 scratch
+            if (int e = launch_cvt_bf16_to_f32(a.grad, scratch, (long long)(TM == 0 ? 1 : 4) * a.B * a.hw, s)) return e;
+            ba.a.grad = scratch;
+            chained = true;
         }
         const long long ntiles = npp / kTile;
         auto k2 = chain_tc_dgrad_kernel<CFG, NWG2, TM>;
@@ -919,11 +948,12 @@ static int launch_bwd_stash_cfg(const ChainParams &cp, const TcArgs &a, int r, c
         if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
         long long grid = (ntiles + NWG2 - 1) / NWG2;
         if (grid > sms) grid = sms;
-        if (TM == 1 && r > 0) launch_dependent(k2, dim3((unsigned)grid), dim3(NWG2 * kTile), smem, s, ba);
+        if (chained) launch_dependent(k2, dim3((unsigned)grid), dim3(NWG2 * kTile), smem, s, ba);
         else k2<<<(unsigned)grid, NWG2 * kTile, smem, s>>>(ba);
         if (int e2 = check_launch("chain_tc_dgrad")) return e2;
         if (cp.gW[0] != nullptr)
-            return launch_wgrad_tma(cp, a.x, a.stash_act, del, partials, a.B, a.hw, a.stash_hw_pad, npp, sms, s);
+            return launch_wgrad_tma(cp, a.x, a.stash_act, del, partials, a.B, a.hw, a.stash_hw_pad, npp, sms, s,
+                                    a.bf16_io ? a.stash_x : nullptr);
         return BTS_OK;
     }
 }

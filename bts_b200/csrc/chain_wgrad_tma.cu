@@ -324,8 +324,9 @@ bool wgrad_tma_supported(const ChainParams &cp, int hw, const void *x)
 
 // act = [ra][npp] rows a_1 .. a_{L-1}; del = [rd][npp] rows delta_1 .. delta_L (chain order); the pixel
 // axis is padded per image to hw_pad (a multiple of 32), npp = padded total (a multiple of 128).
+// x_rows (bf16 twin): the features as fp32 rows [dims[0]][npp] in the stash, read through a 2-D map like the other rows
 int launch_wgrad_tma(const ChainParams &cp, const float *x, const float *act, const float *del, float *partials,
-                     int B, int hw, int hw_pad, long long npp, int sms, cudaStream_t s)
+                     int B, int hw, int hw_pad, long long npp, int sms, cudaStream_t s, const float *x_rows)
 {
     const int L = cp.n_layers;
     WtPlan pl;
@@ -352,7 +353,11 @@ int launch_wgrad_tma(const ChainParams &cp, const float *x, const float *act, co
         if (pl.nmaps == kWtMaxMaps) return -1;
         const int i = pl.nmaps;
         int e;
-        if (src == 0) {
+        if (src == 0 && x_rows != nullptr) {
+            const cuuint64_t dims[2] = {(cuuint64_t)npp, (cuuint64_t)cp.dims[0]};
+            const cuuint64_t str[1] = {(cuuint64_t)npp * 4};
+            e = make_map(&maps.m[i], x_rows, 2, dims, str, rows);
+        } else if (src == 0) {
             const cuuint64_t dims[3] = {(cuuint64_t)hw, (cuuint64_t)cp.dims[0], (cuuint64_t)B};
             const cuuint64_t str[2] = {(cuuint64_t)hw * 4, (cuuint64_t)hw * 4 * cp.dims[0]};
             e = make_map(&maps.m[i], x, 3, dims, str, rows);
@@ -389,7 +394,7 @@ int launch_wgrad_tma(const ChainParams &cp, const float *x, const float *act, co
         if (l0 == 0) {
             const int m = get_map(0, cp.dims[0]);
             if (m < 0) return set_error(BTS_ERR_UNSUPPORTED, "tensor map for x");
-            job.ops[job.nops++] = WtOp{0, 0, (unsigned short)cp.dims[0], (unsigned char)m, 1};
+            job.ops[job.nops++] = WtOp{0, 0, (unsigned short)cp.dims[0], (unsigned char)m, (unsigned char)(x_rows == nullptr ? 1 : 0)};
             act_first = 1;
             act_dst = cp.dims[0];
         }

@@ -83,10 +83,13 @@ lpg_fwd_bf16_kernel(const unsigned short *__restrict__ plane_eq, unsigned short 
     block_absmin_commit(key, abs_min);
 }
 
-template <int R>
+// TP / TO: storage of plane_eq and of its gradient. (bf16, bf16) is the standalone twin; (float, float) serves the bf16
+// backward of the 128-channel chains, whose planes come from the fp32 stash and whose gradient feeds the fp32 dgrad
+// kernel. `scale` = 1 / max_depth when the forward wrote depth / max_depth (bts.py:255), else 1.
+template <int R, class TP, class TO>
 __global__ void __launch_bounds__(256)
-lpg_bwd_bf16_kernel(const unsigned short *__restrict__ grad_depth, const unsigned short *__restrict__ plane_eq,
-                    unsigned short *__restrict__ grad_plane_eq, int B, int h, int w, float eps)
+lpg_bwd_bf16_kernel(const unsigned short *__restrict__ grad_depth, const TP *__restrict__ plane_eq,
+                    TO *__restrict__ grad_plane_eq, int B, int h, int w, float eps, float scale)
 {
     const size_t hw = (size_t)h * w;
     const long long total = (long long)B * hw;
@@ -96,8 +99,8 @@ lpg_bwd_bf16_kernel(const unsigned short *__restrict__ grad_depth, const unsigne
     const int ij = (int)(t - (long long)b * hw);
     const int i = ij / w, j = ij - i * w;
     const size_t base = (size_t)b * 4 * hw + ij;
-    const float n1 = bf16_to_f32(__ldg(plane_eq + base)), n2 = bf16_to_f32(__ldg(plane_eq + base + hw));
-    const float n3 = bf16_to_f32(__ldg(plane_eq + base + 2 * hw)), n4 = bf16_to_f32(__ldg(plane_eq + base + 3 * hw));
+    const float n1 = io_load<TP>(plane_eq + base), n2 = io_load<TP>(plane_eq + base + hw);
+    const float n3 = io_load<TP>(plane_eq + base + 2 * hw), n4 = io_load<TP>(plane_eq + base + 3 * hw);
     const int Wd = w * R;
     const unsigned short *gp = grad_depth + (size_t)b * h * R * Wd + (size_t)i * R * Wd + (size_t)j * R;
     LpgAcc a{0.f, 0.f, 0.f, 0.f};
@@ -113,10 +116,10 @@ lpg_bwd_bf16_kernel(const unsigned short *__restrict__ grad_depth, const unsigne
             lpg_bwd_accum(a, g[k], __fmul_rn(n1, u), n2v, n3, u, v, eps);
         }
     }
-    grad_plane_eq[base] = f32_to_bf16(-n4 * a.tu);
-    grad_plane_eq[base + hw] = f32_to_bf16(-n4 * a.tv);
-    grad_plane_eq[base + 2 * hw] = f32_to_bf16(-n4 * a.t);
-    grad_plane_eq[base + 3 * hw] = f32_to_bf16(a.s4);
+    io_store(grad_plane_eq + base, -n4 * a.tu * scale);
+    io_store(grad_plane_eq + base + hw, -n4 * a.tv * scale);
+    io_store(grad_plane_eq + base + 2 * hw, -n4 * a.t * scale);
+    io_store(grad_plane_eq + base + 3 * hw, a.s4 * scale);
 }
 
 static bool row_aligned(const void *p, int w, int r)
@@ -152,13 +155,47 @@ int launch_lpg_bwd_bf16(const void *grad_depth, const void *plane_eq, void *grad
     const unsigned short *g = static_cast<const unsigned short *>(grad_depth), *pe = static_cast<const unsigned short *>(plane_eq);
     unsigned short *o = static_cast<unsigned short *>(grad_plane_eq);
     switch (r) {
-    case 8: lpg_bwd_bf16_kernel<8><<<grid, 256, 0, s>>>(g, pe, o, B, h, w, eps); break;
-    case 4: lpg_bwd_bf16_kernel<4><<<grid, 256, 0, s>>>(g, pe, o, B, h, w, eps); break;
-    case 2: lpg_bwd_bf16_kernel<2><<<grid, 256, 0, s>>>(g, pe, o, B, h, w, eps); break;
-    case 1: lpg_bwd_bf16_kernel<1><<<grid, 256, 0, s>>>(g, pe, o, B, h, w, eps); break;
+    case 8: lpg_bwd_bf16_kernel<8><<<grid, 256, 0, s>>>(g, pe, o, B, h, w, eps, 1.f); break;
+    case 4: lpg_bwd_bf16_kernel<4><<<grid, 256, 0, s>>>(g, pe, o, B, h, w, eps, 1.f); break;
+    case 2: lpg_bwd_bf16_kernel<2><<<grid, 256, 0, s>>>(g, pe, o, B, h, w, eps, 1.f); break;
+    case 1: lpg_bwd_bf16_kernel<1><<<grid, 256, 0, s>>>(g, pe, o, B, h, w, eps, 1.f); break;
     default: return set_error(BTS_ERR_UNSUPPORTED, "the bf16 twin serves upratio 1, 2, 4, 8 (got %d)", r);
     }
     return check_launch("bts_lpg_bwd_bf16");
+}
+
+// bf16 grad_depth, fp32 planes (the forward's stash) -> fp32 gradient of the plane parameters (the dgrad kernel's input)
+int launch_lpg_bwd_bf16_to_f32(const void *grad_depth, const float *plane_eq, float *grad_plane_eq, int B, int h, int w, int r,
+                               float eps, float depth_div, cudaStream_t s)
+{
+    if (!row_aligned(grad_depth, w, r))
+        return set_error(BTS_ERR_BAD_ARG, "bf16 grad_depth must be aligned to one block row (%d bytes)", 2 * r);
+    const long long total = (long long)B * h * w;
+    const unsigned grid = (unsigned)((total + 255) / 256);
+    const unsigned short *g = static_cast<const unsigned short *>(grad_depth);
+    const float sc = depth_div != 1.f ? 1.f / depth_div : 1.f;
+    switch (r) {
+    case 8: lpg_bwd_bf16_kernel<8><<<grid, 256, 0, s>>>(g, plane_eq, grad_plane_eq, B, h, w, eps, sc); break;
+    case 4: lpg_bwd_bf16_kernel<4><<<grid, 256, 0, s>>>(g, plane_eq, grad_plane_eq, B, h, w, eps, sc); break;
+    case 2: lpg_bwd_bf16_kernel<2><<<grid, 256, 0, s>>>(g, plane_eq, grad_plane_eq, B, h, w, eps, sc); break;
+    case 1: lpg_bwd_bf16_kernel<1><<<grid, 256, 0, s>>>(g, plane_eq, grad_plane_eq, B, h, w, eps, sc); break;
+    default: return set_error(BTS_ERR_UNSUPPORTED, "the bf16 twin serves upratio 1, 2, 4, 8 (got %d)", r);
+    }
+    return check_launch("bts_lpg_bwd_bf16_to_f32");
+}
+
+__global__ void __launch_bounds__(256) cvt_bf16_to_f32_kernel(const unsigned short *__restrict__ in, float *__restrict__ out, long long n)
+{
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        out[i] = bf16_to_f32(__ldg(in + i));
+}
+
+int launch_cvt_bf16_to_f32(const void *in, float *out, long long n, cudaStream_t s)
+{
+    long long grid = (n + 255) / 256;
+    if (grid > 148 * 16) grid = 148 * 16;
+    cvt_bf16_to_f32_kernel<<<(unsigned)(grid < 1 ? 1 : grid), 256, 0, s>>>(static_cast<const unsigned short *>(in), out, n);
+    return check_launch("cvt_bf16_to_f32");
 }
 
 }  // namespace bts

@@ -298,12 +298,27 @@ def _workspace_bf16(dims, B, h, w, r, device):
     return ws, ws.data_ptr(), n
 
 
-def bf16_native(dims, is_final, backward, h, w, x=None):
-    """Does libbts_b200 serve this chain natively in bf16 (forward, or forward + backward)?"""
-    ok = bool(_cabi.lib().bts_bf16_supported(_cabi.int_array(list(dims)), len(dims) - 1, int(bool(is_final)), int(bool(backward))))
-    if ok and backward:
-        ok = (h * w) % 8 == 0 and (x is None or x.data_ptr() % 16 == 0)
-    return ok
+def bf16_native(dims, is_final, backward, h, w, x=None, r=0):
+    """Does libbts_b200 serve this chain natively in bf16 (forward, or forward + backward)? Backward: the one-pass kernel
+    of the two narrow chains (upratio <= 2, h*w % 8 == 0, aligned x) or the stash route of the wider ones (h*w % 4 == 0)."""
+    mode = _cabi.lib().bts_bf16_supported(_cabi.int_array(list(dims)), len(dims) - 1, int(bool(is_final)), int(bool(backward)))
+    if not backward:
+        return mode == 1
+    aligned = x is None or x.data_ptr() % 16 == 0
+    if mode == 1:
+        return (h * w) % 8 == 0 and aligned and r <= 2
+    return mode == 2 and (h * w) % 4 == 0 and aligned
+
+
+def _stash_bf16(dims, B, h, w, device, wanted):
+    n = 0
+    if wanted and _STASH["on"]:
+        with torch.cuda.device(device):
+            n = _cabi.lib().bts_stash_bytes_bf16(_cabi.int_array(dims), len(dims) - 1, B, h, w)
+    if n == 0:
+        return None, None, 0
+    st = torch.empty((n + 3) // 4, dtype=torch.float32, device=device)
+    return st, st.data_ptr(), n
 
 
 class _LPGBF(torch.autograd.Function):
@@ -346,13 +361,14 @@ class _ReducBF(torch.autograd.Function):
         B, _, h, w = x.shape
         r = int(upratio)
         wsb, wsp, wsn = _workspace_bf16(dims, B, h, w, r, x.device)
+        st, stp, stn = _stash_bf16(dims, B, h, w, x.device, any(ctx.needs_input_grad))
         W = _cabi.ptr_array([t.data_ptr() for t in ws])
         outs = []
         with torch.cuda.device(x.device):
             if r == 0:
                 out = torch.empty((B, 1 if is_final else 4, h, w), dtype=torch.bfloat16, device=x.device)
                 _cabi.check(_cabi.lib().bts_reduc_fwd_bf16(x.data_ptr(), W, _cabi.int_array(dims), len(ws), int(bool(is_final)),
-                                                           float(max_depth), B, h, w, out.data_ptr(), wsp, wsn, _stream()),
+                                                           float(max_depth), B, h, w, out.data_ptr(), wsp, wsn, stp, stn, _stream()),
                             "bts_reduc_fwd_bf16")
                 outs = [out]
             else:
@@ -362,12 +378,13 @@ class _ReducBF(torch.autograd.Function):
                 _cabi.check(_cabi.lib().bts_reduc_lpg_fwd_bf16(
                     x.data_ptr(), W, _cabi.int_array(dims), len(ws), float(max_depth), B, h, w, r, EPS,
                     float(max_depth) if scaled else 1.0, pe.data_ptr() if want_plane_eq else None, depth.data_ptr(),
-                    abs_min.data_ptr(), wsp, wsn, _stream()), "bts_reduc_lpg_fwd_bf16")
+                    abs_min.data_ptr(), wsp, wsn, stp, stn, _stream()), "bts_reduc_lpg_fwd_bf16")
                 ctx.mark_non_differentiable(abs_min)
                 outs = [depth, abs_min]
                 if want_plane_eq:
                     ctx.mark_non_differentiable(pe)
                     outs.append(pe)
+        ctx.stash = st
         ctx.save_for_backward(x, *ws)
         ctx.cfg = (float(max_depth), bool(is_final), r, bool(scaled), dims, [(tuple(t.shape), t.dtype) for t in weights])
         ctx.set_materialize_grads(False)
@@ -386,15 +403,17 @@ class _ReducBF(torch.autograd.Function):
         wsb, wsp, wsn = _workspace_bf16(dims, B, h, w, r, x.device)
         W = _cabi.ptr_array([t.data_ptr() for t in ws])
         GW = _cabi.ptr_array([t.data_ptr() for t in gws]) if need_w else None
+        st = ctx.stash
+        stp, stn = (st.data_ptr(), st.numel() * 4) if st is not None else (None, 0)
         with torch.cuda.device(x.device):
             if r == 0:
                 _cabi.check(_cabi.lib().bts_reduc_bwd_bf16(x.data_ptr(), W, _cabi.int_array(dims), len(ws), int(is_final), max_depth,
                                                            B, h, w, grad_out.data_ptr(), gx.data_ptr() if need_x else None, GW,
-                                                           wsp, wsn, _stream()), "bts_reduc_bwd_bf16")
+                                                           wsp, wsn, stp, stn, _stream()), "bts_reduc_bwd_bf16")
             else:
                 _cabi.check(_cabi.lib().bts_reduc_lpg_bwd_bf16(grad_out.data_ptr(), max_depth if scaled else 1.0, x.data_ptr(), W,
                                                                _cabi.int_array(dims), len(ws), max_depth, B, h, w, r, EPS,
-                                                               gx.data_ptr() if need_x else None, GW, wsp, wsn, _stream()),
+                                                               gx.data_ptr() if need_x else None, GW, wsp, wsn, stp, stn, _stream()),
                             "bts_reduc_lpg_bwd_bf16")
         gw_out = [g.view(sh).to(dt) for g, (sh, dt) in zip(gws, wmeta)] if need_w else [None] * len(ws)
         return (gx, None, None, None, None, None, *gw_out)
@@ -522,7 +541,7 @@ def reduc_lpg(x, weights, max_depth, upratio, return_plane_eq=False, scaled=Fals
         dims = [x.shape[1]] + [w.shape[0] for w in weights]
         r = int(upratio)
         grad = _any_grad(x, weights)
-        if x.is_cuda and r in (1, 2, 4, 8) and bf16_native(dims, False, grad, x.shape[2], x.shape[3], x) and (not grad or r <= 2):
+        if x.is_cuda and r in (1, 2, 4, 8) and bf16_native(dims, False, grad, x.shape[2], x.shape[3], x, r):
             return _ReducBF.apply(x, max_depth, False, r, scaled, return_plane_eq, *weights)
         res = _ReducLPG.apply(None, x.float(), max_depth, upratio, return_plane_eq, scaled, False, None, *[w.float() for w in weights])
         return tuple(t.to(torch.bfloat16) if i != 1 else t for i, t in enumerate(res))

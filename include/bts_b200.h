@@ -204,29 +204,35 @@ BTS_API int bts_silog_bwd(const float *depth_est, const float *depth_gt, const u
  * elements, same NCHW shapes), weights and weight gradients stay fp32 (master weights), abs_min stays one fp32 word.
  * Arithmetic is the fp32 path's (3xTF32 tensor-core layers, fp32 SIMT tail) with ONE rounding to bf16 at each store; a
  * bf16 input is exact in tf32, so its remainder pass is skipped. Bytes per full-resolution pixel are half of the fp32
- * figures of SURVEY.md 8(d). Served: forward of every tensor-core chain (bts_bf16_supported(dims, n, final, 0)); backward
- * of the two chains that carry 81 % of the bytes -- head 32->16->8->1 and 64->32->16->8->3 (upratio 1 / 2) -- when
- * h*w % 8 == 0 and x is 16-byte aligned (bts_bf16_supported(.., 1)). Anything else returns BTS_ERR_UNSUPPORTED and the
- * caller converts to fp32 (bts_b200/functional.py does). depth_div: 1, or max_depth for depth / max_depth (bts.py:255).
- * Workspace: bts_workspace_bytes_bf16(). No stash, no strided destinations, no down-sampled map in the bf16 twin.
+ * figures of SURVEY.md 8(d). Served: forward of every tensor-core chain (bts_bf16_supported(dims, n, final, 0) == 1).
+ * Backward, bts_bf16_supported(.., 1): 1 = one-pass kernel, nothing saved -- head 32->16->8->1 and 64->32->16->8->3
+ * (upratio 1 / 2), when h*w % 8 == 0 and x is 16-byte aligned; 2 = stash route -- the wider chains: hand the forward a
+ * `stash` of bts_stash_bytes_bf16() bytes and the backward the same buffer (as the fp32 *_stash entry points; it also
+ * keeps an fp32 copy of the features for the TMA weight-gradient kernel); 0 = not served. Anything not served returns
+ * BTS_ERR_UNSUPPORTED and the caller converts to fp32 (bts_b200/functional.py does). depth_div: 1, or max_depth for
+ * depth / max_depth (bts.py:255). Workspace: bts_workspace_bytes_bf16(). No strided destinations and no down-sampled map.
  */
 BTS_API int bts_bf16_supported(const int *dims, int n_layers, int is_final, int backward);
 BTS_API size_t bts_workspace_bytes_bf16(const int *dims, int n_layers, int B, int h, int w, int r);
+BTS_API size_t bts_stash_bytes_bf16(const int *dims, int n_layers, int B, int h, int w);
 BTS_API int bts_lpg_fwd_bf16(const void *plane_eq, void *depth, float *abs_min, int B, int h, int w, int r, float eps,
                              void *stream);
 BTS_API int bts_lpg_bwd_bf16(const void *grad_depth, const void *plane_eq, void *grad_plane_eq, int B, int h, int w, int r,
                              float eps, void *stream);
 BTS_API int bts_reduc_fwd_bf16(const void *x, const float *const *W, const int *dims, int n_layers, int is_final,
-                               float max_depth, int B, int h, int w, void *out, void *ws, size_t ws_bytes, void *stream);
+                               float max_depth, int B, int h, int w, void *out, void *ws, size_t ws_bytes,
+                               void *stash, size_t stash_bytes, void *stream);
 BTS_API int bts_reduc_bwd_bf16(const void *x, const float *const *W, const int *dims, int n_layers, int is_final,
                                float max_depth, int B, int h, int w, const void *grad_out, void *grad_x,
-                               float *const *grad_W, void *ws, size_t ws_bytes, void *stream);
+                               float *const *grad_W, void *ws, size_t ws_bytes, const void *stash, size_t stash_bytes,
+                               void *stream);
 BTS_API int bts_reduc_lpg_fwd_bf16(const void *x, const float *const *W, const int *dims, int n_layers, float max_depth,
                                    int B, int h, int w, int r, float eps, float depth_div, void *plane_eq_out, void *depth,
-                                   float *abs_min, void *ws, size_t ws_bytes, void *stream);
+                                   float *abs_min, void *ws, size_t ws_bytes, void *stash, size_t stash_bytes, void *stream);
 BTS_API int bts_reduc_lpg_bwd_bf16(const void *grad_depth, float depth_div, const void *x, const float *const *W,
                                    const int *dims, int n_layers, float max_depth, int B, int h, int w, int r, float eps,
-                                   void *grad_x, float *const *grad_W, void *ws, size_t ws_bytes, void *stream);
+                                   void *grad_x, float *const *grad_W, void *ws, size_t ws_bytes, const void *stash,
+                                   size_t stash_bytes, void *stream);
 
 /*
  * bts_silog_fwd without a workspace and without any allocation. NO COUNTERPART IN THE REFERENCE: added at the

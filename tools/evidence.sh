@@ -3,7 +3,7 @@
 # one `ncu --set full` capture per stage kernel (digested on the box), batch sweep, eager-PyTorch baseline.
 # Everything lands in gpurun_out/ev/ (text only, a few hundred KB); copy what should be judged into profiles/.
 # Usage: tools/evidence.sh [round-tag]   e.g. tools/evidence.sh r01
-TAG=${1:-r01}
+TAG=${1:-r02}
 OUT=gpurun_out/ev; mkdir -p $OUT
 python -m pytest tests -m gpu -x -q 2>&1 | tail -3 > $OUT/${TAG}_pytest_gpu.log
 python bench.py > $OUT/${TAG}_bench.json 2> $OUT/bench.err
@@ -12,7 +12,8 @@ python bench.py --impl reference --steps 5 --warmup 3 > $OUT/${TAG}_bench_refere
 python tools/stage_times.py nyu_b8 > $OUT/${TAG}_stage_times_nyu_b8.txt 2>&1
 python tools/stage_times.py kitti_b16 > $OUT/${TAG}_stage_times_kitti_b16.txt 2>&1
 python tests/perf_eager_gpu_baseline.py nyu_b8 > $OUT/${TAG}_eager_gpu_baseline.json 2>> $OUT/bench.err
-[ -n "$SWEEP" ] && python tools/sweep.py 256 > $OUT/${TAG}_sweep_batch_1_256.md 2>> $OUT/bench.err
+[ -n "$SWEEP" ] && python tools/sweep.py > $OUT/${TAG}_sweep_batch_1_256_f32_bf16_n1.md 2>> $OUT/bench.err
+python bench.py --dtype bf16 --no-cpu-baseline > $OUT/${TAG}_bench_bf16.json 2>> $OUT/bench.err
 # launch list of the same command as the bench's timed loop (eager launches so that ncu sees every kernel)
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/${TAG}_launches.csv \
     python bench.py --steps 2 --warmup 3 --kernel-only --no-graph > $OUT/ncu_launches.log 2>&1
