@@ -149,8 +149,12 @@ __global__ void __launch_bounds__(NWG * SUBS * kTile, 1) chain_tc_fwd_kernel(TcA
         if constexpr (BF && SPILL) {
             if (stash && a.stash_x != nullptr) xrow = a.stash_x + (size_t)b * a.stash_hw_pad + p;
         }
-        auto load_x = [&](auto c0_tag) {
+        // XS: also write the features to the stash as fp32 rows (bf16 twin of a stashing chain, training only). A template
+        // flag chosen by ONE kernel-uniform branch per round: predicated-off stores in the inner loops cost 25 % of the
+        // inference forward.
+        auto load_x_impl = [&](auto c0_tag, auto xs_tag) {
             constexpr int C0 = decltype(c0_tag)::value;
+            constexpr bool XS = decltype(xs_tag)::value;
             constexpr int KS = KC0 / SUBS;                        // channels of this round per sub-thread
             const int cb = sub * KS;
             if constexpr (PREFETCH) {
@@ -170,8 +174,8 @@ __global__ void __launch_bounds__(NWG * SUBS * kTile, 1) chain_tc_fwd_kernel(TcA
                         }
                         hi[j] = __float_as_uint(v0);
                         hi[j + 1] = __float_as_uint(v1);
-                        if constexpr (BF && SPILL) {
-                            if (xrow != nullptr) {
+                        if constexpr (XS) {
+                            if (xrow != nullptr) {                // (per thread: pixels past the end have no row)
                                 xrow[(size_t)(C0 + c0 + j) * a.stash_npp] = v0;
                                 xrow[(size_t)(C0 + c0 + j + 1) * a.stash_npp] = v1;
                             }
@@ -198,7 +202,7 @@ __global__ void __launch_bounds__(NWG * SUBS * kTile, 1) chain_tc_fwd_kernel(TcA
                             h32[j] = hi[h + j];
                             h32[j + 1] = hi[h + j + 1];
                             if constexpr (!BF) tf32_lo2(__uint_as_float(hi[h + j]), __uint_as_float(hi[h + j + 1]), lo[j], lo[j + 1]);
-                            if constexpr (BF && SPILL) {
+                            if constexpr (XS) {
                                 if (xrow != nullptr) {
                                     xrow[(size_t)(C0 + c0 + h + j) * a.stash_npp] = __uint_as_float(hi[h + j]);
                                     xrow[(size_t)(C0 + c0 + h + j + 1) * a.stash_npp] = __uint_as_float(hi[h + j + 1]);
@@ -210,6 +214,16 @@ __global__ void __launch_bounds__(NWG * SUBS * kTile, 1) chain_tc_fwd_kernel(TcA
                     }
                 }
             }
+        };
+        auto load_x = [&](auto c0_tag) {
+            if constexpr (BF && SPILL) {
+                // KERNEL-uniform condition (the loads end in warp-collective tcgen05.st: no divergence around them)
+                if (a.stash_x != nullptr && a.stash_act != nullptr) {
+                    load_x_impl(c0_tag, std::true_type{});
+                    return;
+                }
+            }
+            load_x_impl(c0_tag, std::false_type{});
         };
         if constexpr (PREFETCH) {
             cp_async_wait_all();
