@@ -89,6 +89,8 @@ static bool use_tc(const ChainParams &cp, const void *ws, size_t ws_bytes, const
 {
     if (g_force_path == BTS_PATH_GENERIC) return false;
     if (!tc_supported(cp)) return false;
+    for (int l = 0; l < cp.n_layers; ++l)                         // the operand images are packed with 128-bit loads
+        if (!aligned16(cp.W[l])) return false;
     if (ws == nullptr || ws_bytes < tc_pack_bytes() || !aligned16(ws)) return false;
     return depth == nullptr || aligned16(depth);
 }

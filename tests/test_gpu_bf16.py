@@ -142,3 +142,32 @@ def test_bf16_strict_dropin_route():
     # two bf16 roundings of the plane (after the chain, after the glue) sit between the features and the depth
     a = depth.float().cpu().numpy().astype(np.float64)
     assert np.mean(np.abs(a - ref_out) > 2e-2 * np.abs(ref_out) + 1e-2) <= 1e-4
+
+
+@pytest.mark.parametrize("cfg", [(64, 32, 2, 2, 40, 48), (128, 64, 4, 2, 24, 32), (128, 128, 8, 2, 12, 20)], ids=str)
+def test_bf16_scaled_depth(cfg):
+    """fused_stage(..., scaled=True): depth.unsqueeze(1) / max_depth (bts.py:255) folded in, on the one-pass and the stash
+    backward of the bf16 twin"""
+    import bts_b200
+    cin, nout, r, B, h, w = cfg
+    md = 80.0
+    gen = torch.Generator().manual_seed(900 + cin + r)
+    ws = tp.xavier_weights(tp.chain_dims(cin, nout, False), False, gen)
+    xb = _bf(torch.randn(B, cin, h, w, generator=gen))
+    gb = _bf(torch.randn(B, 1, h * r, w * r, generator=gen))
+    wd = [t.double().requires_grad_(True) for t in ws]
+    xr = xb.double().requires_grad_(True)
+    ref = tp.stage_forward(xr, wd, md, r)[0].unsqueeze(1) / md
+    ref.backward(gb.double())
+    red = bts_b200.reduction_1x1(cin, nout, md).cuda()
+    with torch.no_grad():
+        for p, wt in zip(red.chain_weights(), ws):
+            p.copy_(wt.cuda())
+    xd = xb.cuda().requires_grad_(True)
+    out = bts_b200.fused_stage(red, bts_b200.local_planar_guidance(r), xd, scaled=True)
+    assert out.dtype == torch.bfloat16 and out.shape == (B, 1, h * r, w * r)
+    _close_depth(out, ref.detach().numpy(), 1.0, "scaled depth")
+    out.backward(gb.cuda())
+    _close(xd.grad, xr.grad.numpy(), "grad_x")
+    for i, (p, g) in enumerate(zip(red.chain_weights(), wd)):
+        _close(p.grad.view(p.shape[0], p.shape[1]), g.grad[:, :, 0, 0].numpy(), "grad_w%d" % i)

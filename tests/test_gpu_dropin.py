@@ -159,6 +159,39 @@ def test_graft_inside_the_decoder_call_sequence():
             assert l2_rel(a, b64) <= max(2e-5, 3 * l2_rel(b32, b64)), (kind, i)
 
 
+def test_weights_at_unaligned_offsets_take_the_generic_route():
+    """Weights that are views at odd offsets of a flat buffer (flattened parameters) are not 16-byte aligned: the
+    tensor-core kernels pack them with 128-bit loads, so the library must route such a call to the generic kernels."""
+    import bts_b200
+    torch.manual_seed(2)
+    red = bts_b200.reduction_1x1(64, 32, 10.0).cuda()
+    for p in red.parameters():
+        nn.init.xavier_uniform_(p)
+    x = torch.randn(2, 64, 12, 16, device="cuda")
+    g = torch.randn(2, 24, 32, device="cuda")
+    lpg = bts_b200.local_planar_guidance(2)
+    xa = x.clone().requires_grad_(True)
+    ref = bts_b200.fused_stage(red, lpg, xa)
+    ref.backward(g)
+    ref_gw = [p.grad.clone() for p in red.parameters()]
+    shifted = copy.deepcopy(red)
+    flat = torch.empty(sum(p.numel() + 8 for p in red.parameters()) + 8, device="cuda")
+    off = 1                                                       # every view starts 4 bytes past a 16-byte boundary + k
+    for p, q in zip(red.parameters(), shifted.parameters()):
+        view = flat[off:off + p.numel()].view_as(p)
+        view.copy_(p.detach())
+        q.data = view
+        off += p.numel() + (5 - p.numel() % 4)
+    assert any(q.data_ptr() % 16 for q in shifted.parameters())
+    xb = x.clone().requires_grad_(True)
+    out = bts_b200.fused_stage(shifted, lpg, xb)
+    out.backward(g)
+    assert torch.allclose(out, ref, rtol=2e-5, atol=1e-5)
+    assert max_rel_to_peak(xb.grad.cpu().numpy(), xa.grad.cpu().numpy()) <= 2e-5
+    for q, r in zip(shifted.parameters(), ref_gw):
+        assert max_rel_to_peak(q.grad.cpu().numpy(), r.cpu().numpy()) <= 2e-5
+
+
 def test_downsample_is_rejected_for_upratio_2():
     import bts_b200
     red = bts_b200.reduction_1x1(64, 32, 10.0).cuda()
