@@ -395,6 +395,9 @@ class _ReducBF(torch.autograd.Function):
         x, *ws = ctx.saved_tensors
         max_depth, is_final, r, scaled, dims, wmeta = ctx.cfg
         B, _, h, w = x.shape
+        if grad_out is None:                                       # the output was not used downstream
+            shape = (B, 1 if is_final else 4, h, w) if r == 0 else ((B, 1, h * r, w * r) if scaled else (B, h * r, w * r))
+            grad_out = torch.zeros(shape, dtype=torch.bfloat16, device=x.device)
         grad_out = _require_cuda_bf16(grad_out.to(torch.bfloat16), "grad_out")
         need_x = ctx.needs_input_grad[0]
         need_w = any(ctx.needs_input_grad[6:])
