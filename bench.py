@@ -55,6 +55,11 @@ def parse_args():
     ap.add_argument("--kernel-only", action="store_true", help="only the timed device loop (for ncu)")
     ap.add_argument("--e2e-serial", action="store_true", help="end-to-end leg on one stream (no upload/download overlap)")
     ap.add_argument("--no-graph", action="store_true", help="launch every step eagerly instead of replaying a CUDA graph")
+    ap.add_argument("--e2e-d2h", default="all", choices=["all", "results"],
+                    help="what the end-to-end leg reads back to the host every step: every output incl. grad_x (default, the "
+                         "conservative reading) or only what the reference brings to the host -- depth maps / head output "
+                         "(bts_test.py:134-138), weight gradients, abs_min (bts_main.py:484-486); grad_x stays on the GPU, "
+                         "where the encoder's backward consumes it")
     ap.add_argument("--dtype", default="f32", choices=["f32", "bf16"],
                     help="f32 (the reference's arithmetic: the headline) or the bf16 twin (bf16 storage, same arithmetic)")
     ap.add_argument("--grad-allreduce", action="store_true",
@@ -416,7 +421,7 @@ def measured_traffic(kernel):
         return None
 
 
-def e2e_leg(stages, wl, steps, warmup, device, pipelined=True):
+def e2e_leg(stages, wl, steps, warmup, device, pipelined=True, d2h="all"):
     """Same step through the public module API with HOST buffers: every step copies the features and
     upstream gradients from pinned host memory, and reads every result (depth maps / head output,
     grad_x, grad_W, abs_min) back to pinned host memory, inside the timed region.
@@ -462,7 +467,7 @@ def e2e_leg(stages, wl, steps, warmup, device, pipelined=True):
                 out = stage_forward(st)
                 out.backward(dg)
                 st["x"] = saved
-                res = [out.detach(), dx.grad] + [p.grad for p in st["red"].parameters()]
+                res = [out.detach()] + ([dx.grad] if d2h == "all" else []) + [p.grad for p in st["red"].parameters()]
                 if st["lpg"] is not None:
                     res.append(st["lpg"].abs_min)
                 if pipelined:
@@ -656,15 +661,17 @@ def main():
     e2e = None
     if not args.no_e2e:
         e_steps = max(2, min(args.steps, 10))
-        dt, h2d, d2h, _ = e2e_leg(stages, wl, e_steps, 2, device, pipelined=not args.e2e_serial)
+        dt, h2d, d2h, _ = e2e_leg(stages, wl, e_steps, 2, device, pipelined=not args.e2e_serial, d2h=args.e2e_d2h)
         dt = max_over_ranks(dt, device)
         e2e = {"value": world * px_per_rank * e_steps / dt / 1e6, "unit": "Mpixels/s",
                "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": e_steps,
                "ms_per_step": dt / e_steps * 1e3,
                "mode": "serial (one stream)" if args.e2e_serial else
                        "pipelined (upload / compute / download streams, double-buffered inputs and host outputs)",
-               "what": "module API with pinned HOST buffers: H2D of features + upstream grads, D2H of every "
-                       "output (depths, grad_x, grad_W, abs_min) inside the timed region"}
+               "what": "module API with pinned HOST buffers: H2D of features + upstream grads, D2H of " +
+                       ("every output (depths, grad_x, grad_W, abs_min)" if args.e2e_d2h == "all" else
+                        "the results the reference brings to the host (depths, grad_W, abs_min; grad_x stays on the GPU)") +
+                       " inside the timed region"}
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
