@@ -438,7 +438,7 @@ def e2e_leg(stages, wl, steps, warmup, device, pipelined=True, d2h="all"):
     dev_in = [[(torch.empty_like(st["x"]).requires_grad_(True), torch.empty_like(st["g"])) for st in stages]
               for _ in range(nset)]
     host_out = [None] * nset
-    d2h = [0]
+    d2h_bytes = [0]
     cur = torch.cuda.current_stream()
     s_in, s_comp, s_out = (torch.cuda.Stream(), torch.cuda.Stream(), torch.cuda.Stream()) if pipelined else (cur, cur, cur)
     ev_free = [None] * nset          # compute of the step that last used input set j has finished
@@ -480,7 +480,7 @@ def e2e_leg(stages, wl, steps, warmup, device, pipelined=True, d2h="all"):
             ev_free[j] = ev_comp[-1]
         if host_out[j] is None:
             host_out[j] = [[torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in res] for res in results]
-            d2h[0] = sum(t.numel() * t.element_size() for res in results for t in res)
+            d2h_bytes[0] = sum(t.numel() * t.element_size() for res in results for t in res)
         with torch.cuda.stream(s_out):
             for k, (res, hres) in enumerate(zip(results, host_out[j])):
                 s_out.wait_event(ev_comp[k])
@@ -496,7 +496,7 @@ def e2e_leg(stages, wl, steps, warmup, device, pipelined=True, d2h="all"):
         step(i)
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
-    return dt, h2d, d2h[0], host_out
+    return dt, h2d, d2h_bytes[0], host_out
 
 
 _DIST = {"on": False}
