@@ -971,7 +971,7 @@ __global__ void __launch_bounds__(fused_threads(NWG), 1) chain_bwd_fused_kernel(
 // ------------------------------------------------------------------------------------------------
 int launch_wreduce(const ChainParams &cp, const float *partials, int nparts, int total_w, cudaStream_t s);
 size_t tc_pack_bytes();
-bool head_bwd_mma_wanted(const ChainParams &cp, const TcArgs &a, int mode);        // chain_bwd_mma.cu
+bool head_bwd_mma_wanted(const ChainParams &cp, const TcArgs &a, int mode);        // chain_head_mma.cu
 int launch_head_bwd_mma(const ChainParams &cp, const TcArgs &a, int sms, cudaStream_t s);
 
 template <class CFG, int MODE, int R, int NWG, bool BF>
@@ -1035,7 +1035,7 @@ bool fused_bwd_supported(const ChainParams &cp) { return cfg_matches<Cfg32_16>(c
 int launch_chain_bwd_fused(const ChainParams &cp, const TcArgs &a, int mode, int r, void *ws, int sms, cudaStream_t s)
 {
     char *w = static_cast<char *>(ws);
-    // the sigmoid head in fp32: register-operand kernel on warp-level MMAs (chain_bwd_mma.cu; BTS_HEAD_MMA=0 disables)
+    // the sigmoid head in fp32: register-operand kernel on warp-level MMAs (chain_head_mma.cu; BTS_HEAD_MMA=0 disables)
     if (head_bwd_mma_wanted(cp, a, mode)) return launch_head_bwd_mma(cp, a, sms, s);
     if (cfg_matches<Cfg32_16>(cp)) {
         // two warpgroups with private staging buffers per warp pair (168 registers, no spills, no turn-taking between

@@ -1,8 +1,10 @@
-// chain_bwd_mma.cu -- ONE-PASS backward of the full-resolution head 32 -> 16 -> 8 -> 1 (+ sigmoid) on sm_100a,
-// operands in REGISTERS: warp-level tensor-core MMAs (mma.sync m16n8k8, 3xTF32) instead of tcgen05.
+// chain_head_mma.cu -- the full-resolution head 32 -> 16 -> 8 -> 1 (+ sigmoid) on sm_100a with its operands in
+// REGISTERS: warp-level tensor-core MMAs (mma.sync m16n8k8 tf32 + m16n8k16 bf16) instead of tcgen05. ONE-PASS backward
+// (head_bwd_mma_kernel) and forward (head_fwd_mma_kernel).
 //
-// Autograd backward of reduction_1x1(is_final=True) (pytorch/bts.py:108-110, 124-126, 136),
-// the dominant call of the path (260 B per full-resolution pixel: x and grad read once, grad_x written once).
+// reduction_1x1(is_final=True) and its autograd backward (pytorch/bts.py:108-110, 124-126, 136; SURVEY.md 8(a) rows
+// a3 / a8): the backward is the dominant call of the path (260 B per full-resolution pixel: x and grad read once, grad_x
+// written once), the forward the second largest (132 B per pixel).
 //
 // Why not tcgen05 here (chain_bwd_fused.cu is that kernel, and stays as the alternative route): the chain's matrices are
 // 32x16, 16x8 and 8x1. tcgen05 wants M >= 64 rows per operand and operands in shared memory / TMEM, so every pixel's
@@ -493,6 +495,122 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_bwd_mma_kernel(const __
     }
 }
 
+
+// ---- forward: out[px] = sigmoid(W2 . ELU(W1 ELU(W0 x))). The first half of the backward's iteration; memory-bound
+// (~40 MMAs and ~400 other instructions per 32 pixels), so all that matters is bytes in flight: 16 warps x one tile ahead.
+template <int WARPS, int NSTAGE, int MINB>
+__global__ void __launch_bounds__(WARPS * 32, MINB) head_fwd_mma_kernel(const __grid_constant__ MmaArgs ma)
+{
+    const TcArgs &a = ma.a;
+    extern __shared__ __align__(16) float smem[];
+    float4 *f0b = reinterpret_cast<float4 *>(smem);               // [4 k-steps][2 n-tiles][32 lanes]
+    float4 *f1b = f0b + 4 * 2 * 32;                               // [2][32]
+    float *tiles = reinterpret_cast<float *>(f1b + 2 * 32);       // [WARPS][NSTAGE][32 channels][kXS]
+
+    const int tid = threadIdx.x, lane = tid & 31, g = lane >> 2, t = lane & 3;
+    const int warp = uniform(tid >> 5);
+    const float *W0 = a.W[0], *W1 = a.W[1], *W2 = a.W[2];
+    const unsigned npx = (unsigned)a.npx, hw = (unsigned)a.hw;
+    const int ngroups = (int)((npx + kGP - 1) / kGP);
+    const int stride = (int)gridDim.x * WARPS;
+    const int first = (int)blockIdx.x * WARPS + warp;
+    float *mytiles = tiles + (size_t)warp * NSTAGE * kTileFloats;
+
+    const unsigned step = (unsigned)stride * kGP;
+    const unsigned dq = step / hw, dr = step - dq * hw;
+    unsigned q_gp = (unsigned)first * kGP + 4u * (lane & 7), q_b = q_gp / hw, q_p = q_gp - q_b * hw;
+    const size_t hw4 = (size_t)hw * 4;
+    auto prefetch = [&](int st) {
+        const bool ok = q_gp < npx;
+        const float *src = a.x + ((size_t)(ok ? q_b : 0u) * 32 + (lane >> 3)) * hw + (ok ? q_p : 0u);
+        const uint32_t dst = smem_u32(mytiles + st * kTileFloats + (lane >> 3) * kXS + 4 * (lane & 7));
+#pragma unroll
+        for (int i = 0; i < 8; ++i) cp_async16(dst + i * 4 * kXS * 4, src + i * hw4, ok);
+        cp_async_commit();
+        q_gp += step;
+        q_b += dq;
+        q_p += dr;
+        if (q_p >= hw) {
+            q_p -= hw;
+            ++q_b;
+        }
+    };
+#pragma unroll
+    for (int k = 0; k < NSTAGE - 1; ++k) prefetch(k);
+
+    for (int e = tid; e < 4 * 2 * 32; e += WARPS * 32) {
+        const int ln = e & 31, j = (e >> 5) & 1, s = e >> 6, gg = ln >> 2, tt = ln & 3;
+        f0b[e] = with_lo(__ldg(W0 + (8 * j + gg) * 32 + 8 * s + tt), __ldg(W0 + (8 * j + gg) * 32 + 8 * s + tt + 4));
+    }
+    for (int e = tid; e < 2 * 32; e += WARPS * 32) {
+        const int ln = e & 31, s = e >> 5, gg = ln >> 2, tt = ln & 3;
+        f1b[e] = with_lo(__ldg(W1 + gg * 16 + 8 * s + 2 * tt), __ldg(W1 + gg * 16 + 8 * s + 2 * tt + 1));
+    }
+    const float w2a = __ldg(W2 + 2 * t), w2b = __ldg(W2 + 2 * t + 1);
+    __syncthreads();
+
+    int slot = 0;
+#pragma unroll 1
+    for (int G = first; G < ngroups; G += stride) {
+        cp_async_wait<NSTAGE - 2>();
+        __syncwarp();
+        {
+            int pst = slot + NSTAGE - 1;
+            if (pst >= NSTAGE) pst -= NSTAGE;
+            prefetch(pst);
+        }
+        const float *xt = mytiles + slot * kTileFloats;
+        if (++slot == NSTAGE) slot = 0;
+
+        float a1[2][2][4];
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+            FragA fa[2];
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt) {
+                const float *q = xt + (8 * s + t) * kXS + 16 * mt + g;
+                make_a(q[0], q[8], q[4 * kXS], q[4 * kXS + 8], fa[mt]);
+            }
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const FragB fb = frag_b(f0b[(s * 2 + j) * 32 + lane]);
+#pragma unroll
+                for (int mt = 0; mt < 2; ++mt) {
+                    if (s == 0) mma2<true>(a1[mt][j], fa[mt], fb);
+                    else mma2(a1[mt][j], fa[mt], fb);
+                }
+            }
+        }
+        float a2[2][4];
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+            const FragB fb = frag_b(f1b[s * 32 + lane]);
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt) {
+                FragA fa;
+                make_a(elu_fast(a1[mt][s][0]), elu_fast(a1[mt][s][2]), elu_fast(a1[mt][s][1]), elu_fast(a1[mt][s][3]), fa);
+                if (s == 0) mma2<true>(a2[mt], fa, fb);
+                else mma2(a2[mt], fa, fb);
+            }
+        }
+        // z of pixels 8q + g (q = 2 mt + r), the same in the four t lanes; lane (g, t) stores pixel 8t + g: one 128-byte line per warp
+        float z[4];
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int r = 0; r < 2; ++r) {
+                float zp = fmaf(elu_fast(a2[mt][2 * r + 1]), w2b, elu_fast(a2[mt][2 * r]) * w2a);
+                zp += __shfl_xor_sync(0xffffffffu, zp, 1);
+                zp += __shfl_xor_sync(0xffffffffu, zp, 2);
+                z[2 * mt + r] = zp;
+            }
+        const float zm = t == 0 ? z[0] : (t == 1 ? z[1] : (t == 2 ? z[2] : z[3]));
+        const unsigned gp = (unsigned)G * kGP + 8u * t + g;
+        if (gp < npx) a.out[gp] = sigmoidf(zm);
+    }
+    cp_async_wait<0>();
+}
+
 template <int WARPS, int NSTAGE, int MINB>
 int launch_cfg(const MmaArgs &ma, int sms, cudaStream_t s)
 {
@@ -508,7 +626,46 @@ int launch_cfg(const MmaArgs &ma, int sms, cudaStream_t s)
     return check_launch("head_bwd_mma");
 }
 
+template <int WARPS, int NSTAGE, int MINB>
+int launch_fwd_cfg(const MmaArgs &ma, int sms, cudaStream_t s)
+{
+    constexpr size_t smem_bytes = sizeof(float4) * (4 * 2 * 32 + 2 * 32) + sizeof(float) * (size_t)WARPS * NSTAGE * kTileFloats;
+    auto kern = head_fwd_mma_kernel<WARPS, NSTAGE, MINB>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+    if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    const long long ngroups = (ma.a.npx + kGP - 1) / kGP;
+    long long grid = (ngroups + WARPS - 1) / WARPS;
+    if (grid > (long long)sms * MINB) grid = (long long)sms * MINB;
+    kern<<<(unsigned)grid, WARPS * 32, smem_bytes, s>>>(ma);
+    return check_launch("head_fwd_mma");
+}
+
 }  // namespace
+
+// The head's forward on warp-level MMAs: fp32 tensors, 128-bit-copyable features, no fused depth / stash.
+// BTS_HEAD_MMA=0 keeps the tcgen05 kernel (chain_tc_fwd.cu).
+bool head_fwd_mma_wanted(const ChainParams &cp, const TcArgs &a)
+{
+    static const int env = getenv("BTS_HEAD_MMA") ? atoi(getenv("BTS_HEAD_MMA")) : 1;
+    if (env == 0 || a.bf16_io || !a.x_vec16 || a.depth != nullptr || a.stash_act != nullptr || a.out == nullptr) return false;
+    return cfg_matches<Cfg32_16>(cp) && cp.is_final && cp.dims[3] == 1;
+}
+
+int launch_head_fwd_mma(const ChainParams &cp, const TcArgs &a, int sms, cudaStream_t s)
+{
+    MmaArgs ma;
+    ma.a = a;
+    tc_set_weights(ma.a, cp);
+    ma.atomic_w = 0;
+    static const int variant = getenv("BTS_HEAD_MMA") ? atoi(getenv("BTS_HEAD_MMA")) : 1;
+    switch (variant) {
+    case 1: return launch_fwd_cfg<4, 3, 3>(ma, sms, s);
+    case 3: return launch_fwd_cfg<4, 4, 3>(ma, sms, s);
+    case 4: return launch_fwd_cfg<8, 2, 2>(ma, sms, s);
+    case 5: return launch_fwd_cfg<4, 2, 6>(ma, sms, s);           // 24 warps per SM
+    default: return launch_fwd_cfg<4, 2, 4>(ma, sms, s);
+    }
+}
 
 // The head's backward on warp-level MMAs: fp32 tensors, 128-bit-copyable features, atomic weight-gradient accumulation.
 // BTS_HEAD_MMA=0 keeps the tcgen05 kernel (chain_bwd_fused.cu).
@@ -518,7 +675,7 @@ bool head_bwd_mma_wanted(const ChainParams &cp, const TcArgs &a, int mode)
     static const bool deterministic = getenv("BTS_DETERMINISTIC") != nullptr && atoi(getenv("BTS_DETERMINISTIC")) != 0;
     static const bool nwg_forced = getenv("BTS_HEAD_NWG") != nullptr;    // a tcgen05 variant was asked for by name
     if (env == 0 || deterministic || nwg_forced || mode != 0 || a.bf16_io || !a.x_vec16) return false;
-    if (!cfg_matches<Cfg32_16>(cp) || cp.dims[3] != 1) return false;
+    if (!cfg_matches<Cfg32_16>(cp) || !cp.is_final || cp.dims[3] != 1) return false;
     if (a.grad_x != nullptr && (reinterpret_cast<uintptr_t>(a.grad_x) & 7u) != 0) return false;
     return true;
 }
@@ -531,10 +688,12 @@ int launch_head_bwd_mma(const ChainParams &cp, const TcArgs &a, int sms, cudaStr
     for (int l = 0; l < BTS_MAX_LAYERS; ++l) ma.a.gw[l] = l < cp.n_layers ? cp.gW[l] : nullptr;
     ma.atomic_w = cp.gW[0] != nullptr ? 1 : 0;
     static const int variant = getenv("BTS_HEAD_MMA") ? atoi(getenv("BTS_HEAD_MMA")) : 1;
-    switch (variant) {
-    case 2: return launch_cfg<4, 2, 4>(ma, sms, s);               // 16 warps per SM, 128 registers, one tile ahead
+    switch (variant) {                                            // (tuning variants; the default is the measured best)
+    case 1: return launch_cfg<4, 3, 3>(ma, sms, s);               // 12 warps per SM, 168 registers, two tiles ahead
     case 3: return launch_cfg<4, 3, 2>(ma, sms, s);               // 8 warps per SM, 255 registers
-    default: return launch_cfg<4, 3, 3>(ma, sms, s);              // 12 warps per SM, 168 registers, two tiles ahead
+    case 4: return launch_cfg<8, 2, 2>(ma, sms, s);               // 16 warps per SM in two CTAs
+    case 5: return launch_cfg<16, 2, 1>(ma, sms, s);              // 16 warps per SM in one CTA
+    default: return launch_cfg<4, 2, 4>(ma, sms, s);              // 16 warps per SM, 128 registers, one tile ahead
     }
 }
 

@@ -342,8 +342,13 @@ static int dispatch_r(const ChainParams &cp, const TcArgs &a, int r, int sms, cu
 }
 
 // r = 0: no LPG (reduction only). Returns BTS_ERR_UNSUPPORTED when the chain is not covered.
+bool head_fwd_mma_wanted(const ChainParams &cp, const TcArgs &a);                   // chain_head_mma.cu
+int launch_head_fwd_mma(const ChainParams &cp, const TcArgs &a, int sms, cudaStream_t s);
+
 int launch_chain_tc_fwd(const ChainParams &cp, const TcArgs &a, int r, int sms, cudaStream_t s)
 {
+    // the sigmoid head in fp32: register-operand kernel on warp-level MMAs (chain_head_mma.cu; BTS_HEAD_MMA=0 disables)
+    if (r == 0 && head_fwd_mma_wanted(cp, a)) return launch_head_fwd_mma(cp, a, sms, s);
     if (cfg_matches<Cfg128_128>(cp)) return dispatch_r<Cfg128_128, 2, 64, kWideSubs>(cp, a, r, sms, s);
     if (cfg_matches<Cfg128_64>(cp)) return dispatch_r<Cfg128_64, 2, 64, kWideSubs>(cp, a, r, sms, s);
     if (cfg_matches<Cfg64_64>(cp)) return dispatch_r<Cfg64_64, 2>(cp, a, r, sms, s);

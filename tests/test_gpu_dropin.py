@@ -7,7 +7,7 @@
   and every gradient must agree.
 * re-entrancy (include/bts_b200.h: no global mutable state; nn.DataParallel = one Python thread per replica,
   pytorch/bts_test.py:91): two threads, two streams, concurrent fused_stage forward + backward == serial results.
-* environment routes of INTEGRATION.md (BTS_DETERMINISTIC=1, BTS_HEAD_NWG=3, BTS_PDL=0): read once per process, so each
+* environment routes of INTEGRATION.md (BTS_DETERMINISTIC=1, BTS_HEAD_NWG=3, BTS_PDL=0, BTS_HEAD_MMA=0/1/3): read once per process, so each
   runs in a subprocess against the C oracle.
 """
 import copy
@@ -279,7 +279,8 @@ assert worst <= 1e-5, worst
 """
 
 
-@pytest.mark.parametrize("env", [{"BTS_DETERMINISTIC": "1"}, {"BTS_HEAD_NWG": "3"}, {"BTS_PDL": "0"}], ids=lambda e: "-".join("%s=%s" % kv for kv in e.items()))
+@pytest.mark.parametrize("env", [{"BTS_DETERMINISTIC": "1"}, {"BTS_HEAD_NWG": "3"}, {"BTS_PDL": "0"}, {"BTS_HEAD_MMA": "0"},
+                                 {"BTS_HEAD_MMA": "1"}, {"BTS_HEAD_MMA": "3"}], ids=lambda e: "-".join("%s=%s" % kv for kv in e.items()))
 def test_environment_routes_vs_c_oracle(env):
     e = dict(os.environ)
     e.update(env)

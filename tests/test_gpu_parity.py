@@ -116,6 +116,12 @@ SEEDED = [  # (num_in, num_out, is_final, r, B, h, w, max_depth): sizes the C or
     (64, 64, False, 8, 1, 17, 9, 10.0),      # hw % 4 != 0: recompute backward + non-TMA weight-gradient kernel
     (48, 24, False, 4, 1, 9, 7, 10.0),       # widths no fast path covers: generic kernel
     (16, 16, True, 1, 3, 33, 31, 10.0),
+    # the head's register-operand backward (chain_bwd_mma.cu): 32-pixel groups that straddle images, a ragged last
+    # group, images smaller than a group (several wraps inside one group), a tensor smaller than a group
+    (32, 16, True, 1, 3, 6, 10, 10.0),
+    (32, 16, True, 1, 5, 7, 12, 80.0),
+    (32, 16, True, 1, 7, 3, 4, 10.0),
+    (32, 16, True, 1, 1, 2, 2, 10.0),
 ]
 
 
