@@ -76,10 +76,12 @@ __device__ __forceinline__ uint32_t bfpair(uint32_t lo, uint32_t hi)
 struct FragA {
     uint32_t h[4];                         // tf32 A fragment (row g | g+8, k = t | t+4) of the hi parts
     uint32_t s[4];                         // bf16 A fragment: {lo(k=t), lo(k=t+4)} rows g, g+8; {hi, hi} rows g, g+8
+    uint32_t l[4];                         // tf32 A fragment of the remainders (the exact three-instruction variant only)
 };
 struct FragB {
     uint32_t h0, h1;                       // tf32 B fragment (k = t | t+4, n = g) of the hi parts
     uint32_t s0, s1;                       // bf16 B fragment: {hi(k=t), hi(k=t+4)}, {lo, lo}
+    uint32_t l0, l1;                       // tf32 B fragment of the remainders (exact variant only)
 };
 __device__ __forceinline__ void split1(float v, uint32_t &h, uint32_t &l)
 {
@@ -89,38 +91,58 @@ __device__ __forceinline__ void split1(float v, uint32_t &h, uint32_t &l)
 // (v0 .. v3) in fragment order: (row g, k=t), (row g+8, k=t), (row g, k=t+4), (row g+8, k=t+4)
 __device__ __forceinline__ void make_a(float v0, float v1, float v2, float v3, FragA &f)
 {
-    uint32_t l[4];
-    split1(v0, f.h[0], l[0]);
-    split1(v1, f.h[1], l[1]);
-    split1(v2, f.h[2], l[2]);
-    split1(v3, f.h[3], l[3]);
-    f.s[0] = bfpair(l[0], l[2]);
-    f.s[1] = bfpair(l[1], l[3]);
+    split1(v0, f.h[0], f.l[0]);
+    split1(v1, f.h[1], f.l[1]);
+    split1(v2, f.h[2], f.l[2]);
+    split1(v3, f.h[3], f.l[3]);
+    f.s[0] = bfpair(f.l[0], f.l[2]);
+    f.s[1] = bfpair(f.l[1], f.l[3]);
     f.s[2] = bfpair(f.h[0], f.h[2]);
     f.s[3] = bfpair(f.h[1], f.h[3]);
 }
 __device__ __forceinline__ void make_b(float v0, float v1, FragB &f)
 {
-    uint32_t l0, l1;
-    split1(v0, f.h0, l0);
-    split1(v1, f.h1, l1);
+    split1(v0, f.h0, f.l0);
+    split1(v1, f.h1, f.l1);
     f.s0 = bfpair(f.h0, f.h1);
-    f.s1 = bfpair(l0, l1);
+    f.s1 = bfpair(f.l0, f.l1);
 }
 __device__ __forceinline__ FragB frag_b(const float4 &w)
 {
     FragB f;
     f.h0 = __float_as_uint(w.x); f.h1 = __float_as_uint(w.y); f.s0 = __float_as_uint(w.z); f.s1 = __float_as_uint(w.w);
+    f.l0 = f.l1 = 0u;
     return f;
 }
-// d (+)= a * b, small products first
+// exact variant: the table entry carries the remainder words instead of the bf16 pairs
+__device__ __forceinline__ FragB frag_b_exact(const float4 &w)
+{
+    FragB f;
+    f.h0 = __float_as_uint(w.x); f.h1 = __float_as_uint(w.y); f.l0 = __float_as_uint(w.z); f.l1 = __float_as_uint(w.w);
+    f.s0 = f.s1 = 0u;
+    return f;
+}
+__device__ __forceinline__ float4 with_lo_exact(float b0, float b1) { return make_float4(tf32_hi(b0), tf32_hi(b1), tf32_lo(b0), tf32_lo(b1)); }
+// d (+)= a * b in three tf32 instructions (plain 3xTF32: ~5e-7 of peak instead of ~3e-6), small products first
 template <bool ZERO = false>
-__device__ __forceinline__ void mma2(float (&d)[4], const FragA &a, const FragB &b)
+__device__ __forceinline__ void mma3_small(float (&d)[4], const FragA &a, const FragB &b)
+{
+    if constexpr (ZERO) {
+        d[0] = d[1] = d[2] = d[3] = 0.f;
+    }
+    hmma(d, a.l, b.h0, b.h1);
+    hmma(d, a.h, b.l0, b.l1);
+}
+// d (+)= a * b in two instructions, small products first. Callers issue the first halves of several independent
+// accumulators, then the second halves: back-to-back MMAs into one accumulator wait for each other (the asm statements
+// are volatile, the compiler keeps their order).
+template <bool ZERO = false>
+__device__ __forceinline__ void mma2_small(float (&d)[4], const FragA &a, const FragB &b)
 {
     if constexpr (ZERO) hmma_bf_z(d, a.s, b.s0, b.s1);
     else hmma_bf(d, a.s, b.s0, b.s1);
-    hmma(d, a.h, b.h0, b.h1);
 }
+__device__ __forceinline__ void mma2_main(float (&d)[4], const FragA &a, const FragB &b) { hmma(d, a.h, b.h0, b.h1); }
 // sigmoid with the hardware exponential and reciprocal (relative error ~2e-7; the backward is held to 1e-5)
 __device__ __forceinline__ float sigmoid_fast(float t)
 {
@@ -141,6 +163,19 @@ __device__ __forceinline__ void tr8x8(float e0, float e1, float &w0, float &w1)
     w0 = __uint_as_float(__byte_perm(tl, th, 0x5410));
     w1 = __uint_as_float(__byte_perm(tl, th, 0x7632));
 }
+__device__ __forceinline__ uint32_t movm(uint32_t v)                 // 8x8 transpose of 16-bit elements (a bf16 pair per thread)
+{
+    uint32_t r;
+    asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(r) : "r"(v));
+    return r;
+}
+__device__ __forceinline__ void tr8x8(uint32_t e0, uint32_t e1, uint32_t &w0, uint32_t &w1)
+{
+    float a, b;
+    tr8x8(__uint_as_float(e0), __uint_as_float(e1), a, b);
+    w0 = __float_as_uint(a);
+    w1 = __float_as_uint(b);
+}
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
@@ -150,6 +185,27 @@ __device__ __forceinline__ float4 with_lo(float b0, float b1)
     make_b(b0, b1, f);
     return make_float4(__uint_as_float(f.h0), __uint_as_float(f.h1), __uint_as_float(f.s0), __uint_as_float(f.s1));
 }
+
+template <bool EXACT, bool ZERO>
+__device__ __forceinline__ void mma_small(float (&d)[4], const FragA &a, const FragB &b)
+{
+    if constexpr (EXACT) mma3_small<ZERO>(d, a, b);
+    else mma2_small<ZERO>(d, a, b);
+}
+
+// Tuning / accuracy switches (A/B builds): the forward-chain products of the backward in plain 3xTF32.
+#ifndef BTS_MMA_EXACT_F
+#define BTS_MMA_EXACT_F 0
+#endif
+#if BTS_MMA_EXACT_F
+#define MMA_F_TABLE with_lo_exact
+#define MMA_F_FRAG frag_b_exact
+#define MMA_F_SMALL mma3_small
+#else
+#define MMA_F_TABLE with_lo
+#define MMA_F_FRAG frag_b
+#define MMA_F_SMALL mma2_small
+#endif
 
 template <int WARPS, int NSTAGE, int MINB>
 __global__ void __launch_bounds__(WARPS * 32, MINB) head_bwd_mma_kernel(const __grid_constant__ MmaArgs ma)
@@ -233,11 +289,11 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_bwd_mma_kernel(const __
     // ---- fragment tables (while the first tiles are in flight)
     for (int e = tid; e < 4 * 2 * 32; e += WARPS * 32) {
         const int ln = e & 31, j = (e >> 5) & 1, s = e >> 6, gg = ln >> 2, tt = ln & 3;
-        f0b[e] = with_lo(__ldg(W0 + (8 * j + gg) * 32 + 8 * s + tt), __ldg(W0 + (8 * j + gg) * 32 + 8 * s + tt + 4));
+        f0b[e] = MMA_F_TABLE(__ldg(W0 + (8 * j + gg) * 32 + 8 * s + tt), __ldg(W0 + (8 * j + gg) * 32 + 8 * s + tt + 4));
     }
     for (int e = tid; e < 2 * 32; e += WARPS * 32) {
         const int ln = e & 31, s = e >> 5, gg = ln >> 2, tt = ln & 3;
-        f1b[e] = with_lo(__ldg(W1 + gg * 16 + 8 * s + 2 * tt), __ldg(W1 + gg * 16 + 8 * s + 2 * tt + 1));
+        f1b[e] = MMA_F_TABLE(__ldg(W1 + gg * 16 + 8 * s + 2 * tt), __ldg(W1 + gg * 16 + 8 * s + 2 * tt + 1));
         b1b[e] = with_lo(__ldg(W1 + (2 * tt) * 16 + 8 * s + gg), __ldg(W1 + (2 * tt + 1) * 16 + 8 * s + gg));
     }
     for (int e = tid; e < 2 * 2 * 32; e += WARPS * 32) {
@@ -291,15 +347,20 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_bwd_mma_kernel(const __
                 const float *q = xt + (8 * s + t) * kXS + 16 * mt + g;
                 make_a(q[0], q[8], q[4 * kXS], q[4 * kXS + 8], fa[mt]);
             }
+            FragB fb[2];
 #pragma unroll
-            for (int j = 0; j < 2; ++j) {
-                const FragB fb = frag_b(f0b[(s * 2 + j) * 32 + lane]);
+            for (int j = 0; j < 2; ++j) fb[j] = MMA_F_FRAG(f0b[(s * 2 + j) * 32 + lane]);
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
 #pragma unroll
                 for (int mt = 0; mt < 2; ++mt) {
-                    if (s == 0) mma2<true>(a1[mt][j], fa[mt], fb);
-                    else mma2(a1[mt][j], fa[mt], fb);
+                    if (s == 0) MMA_F_SMALL<true>(a1[mt][j], fa[mt], fb[j]);
+                    else MMA_F_SMALL(a1[mt][j], fa[mt], fb[j]);
                 }
-            }
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+                for (int mt = 0; mt < 2; ++mt) mma2_main(a1[mt][j], fa[mt], fb[j]);
         }
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt)
@@ -310,16 +371,19 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_bwd_mma_kernel(const __
 
         // ---- layer 1: the accumulator fragment (px g / g+8, channels 8s + 2t, 2t+1) is the A fragment (k = t, t+4)
         float a2[2][4];
+        FragA fa1[2][2];                                          // a1 as A operand [k-step = its n-tile][m-tile]: kept for dW1
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
-            const FragB fb = frag_b(f1b[s * 32 + lane]);
+            const FragB fb = MMA_F_FRAG(f1b[s * 32 + lane]);
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt) make_a(a1[mt][s][0], a1[mt][s][2], a1[mt][s][1], a1[mt][s][3], fa1[s][mt]);
 #pragma unroll
             for (int mt = 0; mt < 2; ++mt) {
-                FragA fa;
-                make_a(a1[mt][s][0], a1[mt][s][2], a1[mt][s][1], a1[mt][s][3], fa);
-                if (s == 0) mma2<true>(a2[mt], fa, fb);
-                else mma2(a2[mt], fa, fb);
+                if (s == 0) MMA_F_SMALL<true>(a2[mt], fa1[s][mt], fb);
+                else MMA_F_SMALL(a2[mt], fa1[s][mt], fb);
             }
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt) mma2_main(a2[mt], fa1[s][mt], fb);
         }
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt)
@@ -343,35 +407,72 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_bwd_mma_kernel(const __
                 d2[mt][2 * r + 1] = mul_elu_grad(dz * w2b, a2[mt][2 * r + 1]);
             }
 
+        // The weight gradients need the pixel axis as K: operands [channel g][pixel 2t, 2t+1] = 8x8 transposes of what the
+        // chain's fragments hold as [pixel g][channel 2t, 2t+1]. Nothing is split twice: the fragments built for the chain
+        // products already carry the hi words and the bf16 pairs {ch 2t, ch 2t+1} of the hi parts and of the remainders;
+        // a pair register IS an 8x8 matrix of 16-bit elements, so ONE movmatrix yields the transposed pair {px 2t, px 2t+1},
+        // and the hi words take the 32-bit transpose (two movmatrix on the halves).
+        // (mt, r): the eight pixels of row half r of m-tile mt = one k-step.
+        float g0[4][4], g1[4];
+
         // ---- delta1 = (delta2 * W1) . ELU'(a1)    (px on M, K = 8: one k-step)
         float d1[2][2][4];
         {
-            FragA fa[2];
+            FragA fa2[2];
 #pragma unroll
-            for (int mt = 0; mt < 2; ++mt) make_a(d2[mt][0], d2[mt][2], d2[mt][1], d2[mt][3], fa[mt]);
+            for (int mt = 0; mt < 2; ++mt) make_a(d2[mt][0], d2[mt][2], d2[mt][1], d2[mt][3], fa2[mt]);
+            FragB fb[2];
+            float acc[2][2][4];
 #pragma unroll
-            for (int j = 0; j < 2; ++j) {
-                const FragB fb = frag_b(b1b[j * 32 + lane]);
+            for (int j = 0; j < 2; ++j) fb[j] = frag_b(b1b[j * 32 + lane]);
 #pragma unroll
-                for (int mt = 0; mt < 2; ++mt) {
-                    float acc[4];
-                    mma2<true>(acc, fa[mt], fb);
+            for (int j = 0; j < 2; ++j)
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) d1[mt][j][q] = mul_elu_grad(acc[q], a1[mt][j][q]);
-                }
-            }
-        }
-
-        // ---- grad_x^T[32 ch x 32 px] = W0^T[32 x 16] * delta1^T (px on N): delta1's accumulator fragment is the B fragment
-        if (a.grad_x != nullptr) {
-            FragB fd[2][2][2];                                    // delta1 as B operand: [m-tile][channel k-step][row half]
+                for (int mt = 0; mt < 2; ++mt) mma2_small<true>(acc[mt][j], fa2[mt], fb[j]);
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+                for (int mt = 0; mt < 2; ++mt) mma2_main(acc[mt][j], fa2[mt], fb[j]);
+            // ---- dW1[o][c] += delta2[px][o] * a1[px][c]: A = a1^T (m = c: rows g from n-tile 0, g+8 from n-tile 1), B = delta2^T
+            // (fragment order of make_a(c0, c2, c1, c3): h[r], h[2+r] = channels 2t, 2t+1 of row half r; s[r] / s[2+r] = the
+            // remainder / hi pair of row half r)
 #pragma unroll
             for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
-                for (int j = 0; j < 2; ++j) {
-                    make_b(d1[mt][j][0], d1[mt][j][1], fd[mt][j][0]);
-                    make_b(d1[mt][j][2], d1[mt][j][3], fd[mt][j][1]);
+                for (int r = 0; r < 2; ++r) {
+                    FragA fc;
+                    FragB fe;
+                    tr8x8(fa1[0][mt].h[r], fa1[0][mt].h[2 + r], fc.h[0], fc.h[2]);
+                    tr8x8(fa1[1][mt].h[r], fa1[1][mt].h[2 + r], fc.h[1], fc.h[3]);
+                    fc.s[0] = movm(fa1[0][mt].s[r]);
+                    fc.s[1] = movm(fa1[1][mt].s[r]);
+                    fc.s[2] = movm(fa1[0][mt].s[2 + r]);
+                    fc.s[3] = movm(fa1[1][mt].s[2 + r]);
+                    tr8x8(fa2[mt].h[r], fa2[mt].h[2 + r], fe.h0, fe.h1);
+                    fe.s0 = movm(fa2[mt].s[2 + r]);
+                    fe.s1 = movm(fa2[mt].s[r]);
+                    if (mt == 0 && r == 0) mma2_small<true>(g1, fc, fe);
+                    else mma2_small(g1, fc, fe);
+                    mma2_main(g1, fc, fe);
                 }
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+                for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) d1[mt][j][q] = mul_elu_grad(acc[mt][j][q], a1[mt][j][q]);
+        }
+
+        // ---- grad_x^T[32 ch x 32 px] = W0^T[32 x 16] * delta1^T (px on N): delta1's accumulator fragment is the B fragment
+        FragB fd[2][2][2];                                        // delta1 as B operand: [m-tile][channel k-step][row half]
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                make_b(d1[mt][j][0], d1[mt][j][1], fd[mt][j][0]);
+                make_b(d1[mt][j][2], d1[mt][j][3], fd[mt][j][1]);
+            }
+        if (a.grad_x != nullptr) {
             // whole group inside one image and inside the tensor: four row pointers, immediate offsets
             const bool fast = base.gp + kGP <= npx && base.p + kGP <= hw;
             float *row0 = a.grad_x + ((size_t)base.b * 32 + g) * hw + base.p + 2 * t;
@@ -385,14 +486,15 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_bwd_mma_kernel(const __
                     fw[s].s[0] = __float_as_uint(vs.x); fw[s].s[1] = __float_as_uint(vs.y); fw[s].s[2] = __float_as_uint(vs.z); fw[s].s[3] = __float_as_uint(vs.w);
                 }
                 float acc[4][4];
+                // n-tile n: 8 pixels = rows r = n % 2 of m-tile n / 2; four independent accumulators per pass
 #pragma unroll
-                for (int n = 0; n < 4; ++n) {                     // 8 pixels: rows r = n % 2 of m-tile n / 2
-                    const int mt = n >> 1, r = n & 1;
-                    hmma_bf_z(acc[n], fw[0].s, fd[mt][0][r].s0, fd[mt][0][r].s1);
-                    hmma_bf(acc[n], fw[1].s, fd[mt][1][r].s0, fd[mt][1][r].s1);
-                    hmma(acc[n], fw[0].h, fd[mt][0][r].h0, fd[mt][0][r].h1);
-                    hmma(acc[n], fw[1].h, fd[mt][1][r].h0, fd[mt][1][r].h1);
-                }
+                for (int n = 0; n < 4; ++n) hmma_bf_z(acc[n], fw[0].s, fd[n >> 1][0][n & 1].s0, fd[n >> 1][0][n & 1].s1);
+#pragma unroll
+                for (int n = 0; n < 4; ++n) hmma_bf(acc[n], fw[1].s, fd[n >> 1][1][n & 1].s0, fd[n >> 1][1][n & 1].s1);
+#pragma unroll
+                for (int n = 0; n < 4; ++n) hmma(acc[n], fw[0].h, fd[n >> 1][0][n & 1].h0, fd[n >> 1][0][n & 1].h1);
+#pragma unroll
+                for (int n = 0; n < 4; ++n) hmma(acc[n], fw[1].h, fd[n >> 1][1][n & 1].h0, fd[n >> 1][1][n & 1].h1);
                 if (fast) {
                     float *ra = row0 + (size_t)(16 * i) * hw, *rb = ra + (size_t)8 * hw;
 #pragma unroll
@@ -424,38 +526,32 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_bwd_mma_kernel(const __
             }
         }
 
-        // ---- weight gradients: the pixel axis is K. Operands [channel g][pixel 2t, 2t+1]: register transposes of the
-        // accumulator fragments; x comes from the tile. Eight pixels (rows r of m-tile mt) per k-step.
-        float g0[4][4], g1[4];
+        // ---- dW0[o][c] += delta1[px][o] * x[px][c]: A = delta1^T (m = o: rows g from n-tile 0, g+8 from n-tile 1) out of the
+        // fragments of the product above, B = x (n = c) from the tile, one 64-bit load per fragment
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
             for (int r = 0; r < 2; ++r) {
-                const bool z = mt == 0 && r == 0;
-                float t0a, t0b, t1a, t1b;
                 FragA fa;
-                // dW0[o][c] += delta1[px][o] * x[px][c]: A = delta1^T (m = o), B = x (n = c)
-                tr8x8(d1[mt][0][2 * r], d1[mt][0][2 * r + 1], t0a, t0b);
-                tr8x8(d1[mt][1][2 * r], d1[mt][1][2 * r + 1], t1a, t1b);
-                make_a(t0a, t1a, t0b, t1b, fa);
+                FragB fb[4];
+                tr8x8(fd[mt][0][r].h0, fd[mt][0][r].h1, fa.h[0], fa.h[2]);
+                tr8x8(fd[mt][1][r].h0, fd[mt][1][r].h1, fa.h[1], fa.h[3]);
+                fa.s[0] = movm(fd[mt][0][r].s1);
+                fa.s[1] = movm(fd[mt][1][r].s1);
+                fa.s[2] = movm(fd[mt][0][r].s0);
+                fa.s[3] = movm(fd[mt][1][r].s0);
 #pragma unroll
                 for (int n = 0; n < 4; ++n) {
                     const float2 xv = *reinterpret_cast<const float2 *>(xt + (8 * n + g) * kXS + 16 * mt + 8 * r + 2 * t);
-                    FragB fb;
-                    make_b(xv.x, xv.y, fb);
-                    if (z) mma2<true>(g0[n], fa, fb);
-                    else mma2(g0[n], fa, fb);
+                    make_b(xv.x, xv.y, fb[n]);
                 }
-                // dW1[o][c] += delta2[px][o] * a1[px][c]: A = a1^T (m = c), B = delta2 (n = o)
-                tr8x8(a1[mt][0][2 * r], a1[mt][0][2 * r + 1], t0a, t0b);
-                tr8x8(a1[mt][1][2 * r], a1[mt][1][2 * r + 1], t1a, t1b);
-                make_a(t0a, t1a, t0b, t1b, fa);
-                float e0, e1;
-                tr8x8(d2[mt][2 * r], d2[mt][2 * r + 1], e0, e1);
-                FragB fb;
-                make_b(e0, e1, fb);
-                if (z) mma2<true>(g1, fa, fb);
-                else mma2(g1, fa, fb);
+#pragma unroll
+                for (int n = 0; n < 4; ++n) {
+                    if (mt == 0 && r == 0) mma2_small<true>(g0[n], fa, fb[n]);
+                    else mma2_small(g0[n], fa, fb[n]);
+                }
+#pragma unroll
+                for (int n = 0; n < 4; ++n) mma2_main(g0[n], fa, fb[n]);
             }
 #pragma unroll
         for (int n = 0; n < 4; ++n)
@@ -497,8 +593,10 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_bwd_mma_kernel(const __
 
 
 // ---- forward: out[px] = sigmoid(W2 . ELU(W1 ELU(W0 x))). The first half of the backward's iteration; memory-bound
-// (~40 MMAs and ~400 other instructions per 32 pixels), so all that matters is bytes in flight: 16 warps x one tile ahead.
-template <int WARPS, int NSTAGE, int MINB>
+// (~40 MMAs and ~400 other instructions per 32 pixels), 16 warps x one tile ahead. EXACT: plain three-instruction 3xTF32
+// products (output within 8e-7 of the fp64 oracle's peak instead of 3.6e-6, 72 instead of 61 us at nyu_b8: the kernel is
+// latency-bound on its dependent MMA chain, not idle under the copies); BTS_HEAD_EXACT=1 selects it.
+template <int WARPS, int NSTAGE, int MINB, bool EXACT>
 __global__ void __launch_bounds__(WARPS * 32, MINB) head_fwd_mma_kernel(const __grid_constant__ MmaArgs ma)
 {
     const TcArgs &a = ma.a;
@@ -540,11 +638,11 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_fwd_mma_kernel(const __
 
     for (int e = tid; e < 4 * 2 * 32; e += WARPS * 32) {
         const int ln = e & 31, j = (e >> 5) & 1, s = e >> 6, gg = ln >> 2, tt = ln & 3;
-        f0b[e] = with_lo(__ldg(W0 + (8 * j + gg) * 32 + 8 * s + tt), __ldg(W0 + (8 * j + gg) * 32 + 8 * s + tt + 4));
+        f0b[e] = (EXACT ? with_lo_exact : with_lo)(__ldg(W0 + (8 * j + gg) * 32 + 8 * s + tt), __ldg(W0 + (8 * j + gg) * 32 + 8 * s + tt + 4));
     }
     for (int e = tid; e < 2 * 32; e += WARPS * 32) {
         const int ln = e & 31, s = e >> 5, gg = ln >> 2, tt = ln & 3;
-        f1b[e] = with_lo(__ldg(W1 + gg * 16 + 8 * s + 2 * tt), __ldg(W1 + gg * 16 + 8 * s + 2 * tt + 1));
+        f1b[e] = (EXACT ? with_lo_exact : with_lo)(__ldg(W1 + gg * 16 + 8 * s + 2 * tt), __ldg(W1 + gg * 16 + 8 * s + 2 * tt + 1));
     }
     const float w2a = __ldg(W2 + 2 * t), w2b = __ldg(W2 + 2 * t + 1);
     __syncthreads();
@@ -571,27 +669,36 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_fwd_mma_kernel(const __
                 const float *q = xt + (8 * s + t) * kXS + 16 * mt + g;
                 make_a(q[0], q[8], q[4 * kXS], q[4 * kXS + 8], fa[mt]);
             }
+            FragB fb[2];
 #pragma unroll
-            for (int j = 0; j < 2; ++j) {
-                const FragB fb = frag_b(f0b[(s * 2 + j) * 32 + lane]);
+            for (int j = 0; j < 2; ++j) fb[j] = EXACT ? frag_b_exact(f0b[(s * 2 + j) * 32 + lane]) : frag_b(f0b[(s * 2 + j) * 32 + lane]);
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
 #pragma unroll
                 for (int mt = 0; mt < 2; ++mt) {
-                    if (s == 0) mma2<true>(a1[mt][j], fa[mt], fb);
-                    else mma2(a1[mt][j], fa[mt], fb);
+                    if (s == 0) mma_small<EXACT, true>(a1[mt][j], fa[mt], fb[j]);
+                    else mma_small<EXACT, false>(a1[mt][j], fa[mt], fb[j]);
                 }
-            }
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+                for (int mt = 0; mt < 2; ++mt) mma2_main(a1[mt][j], fa[mt], fb[j]);
         }
         float a2[2][4];
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
-            const FragB fb = frag_b(f1b[s * 32 + lane]);
+            const FragB fb = EXACT ? frag_b_exact(f1b[s * 32 + lane]) : frag_b(f1b[s * 32 + lane]);
+            FragA fa[2];
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt)
+                make_a(elu_fast(a1[mt][s][0]), elu_fast(a1[mt][s][2]), elu_fast(a1[mt][s][1]), elu_fast(a1[mt][s][3]), fa[mt]);
 #pragma unroll
             for (int mt = 0; mt < 2; ++mt) {
-                FragA fa;
-                make_a(elu_fast(a1[mt][s][0]), elu_fast(a1[mt][s][2]), elu_fast(a1[mt][s][1]), elu_fast(a1[mt][s][3]), fa);
-                if (s == 0) mma2<true>(a2[mt], fa, fb);
-                else mma2(a2[mt], fa, fb);
+                if (s == 0) mma_small<EXACT, true>(a2[mt], fa[mt], fb);
+                else mma_small<EXACT, false>(a2[mt], fa[mt], fb);
             }
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt) mma2_main(a2[mt], fa[mt], fb);
         }
         // z of pixels 8q + g (q = 2 mt + r), the same in the four t lanes; lane (g, t) stores pixel 8t + g: one 128-byte line per warp
         float z[4];
@@ -626,11 +733,11 @@ int launch_cfg(const MmaArgs &ma, int sms, cudaStream_t s)
     return check_launch("head_bwd_mma");
 }
 
-template <int WARPS, int NSTAGE, int MINB>
+template <int WARPS, int NSTAGE, int MINB, bool EXACT = false>
 int launch_fwd_cfg(const MmaArgs &ma, int sms, cudaStream_t s)
 {
     constexpr size_t smem_bytes = sizeof(float4) * (4 * 2 * 32 + 2 * 32) + sizeof(float) * (size_t)WARPS * NSTAGE * kTileFloats;
-    auto kern = head_fwd_mma_kernel<WARPS, NSTAGE, MINB>;
+    auto kern = head_fwd_mma_kernel<WARPS, NSTAGE, MINB, EXACT>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     const long long ngroups = (ma.a.npx + kGP - 1) / kGP;
@@ -658,12 +765,14 @@ int launch_head_fwd_mma(const ChainParams &cp, const TcArgs &a, int sms, cudaStr
     tc_set_weights(ma.a, cp);
     ma.atomic_w = 0;
     static const int variant = getenv("BTS_HEAD_MMA") ? atoi(getenv("BTS_HEAD_MMA")) : 1;
+    static const bool exact = getenv("BTS_HEAD_EXACT") != nullptr && atoi(getenv("BTS_HEAD_EXACT")) != 0;
+    if (exact) return launch_fwd_cfg<8, 2, 2, true>(ma, sms, s);
     switch (variant) {
     case 1: return launch_fwd_cfg<4, 3, 3>(ma, sms, s);
     case 3: return launch_fwd_cfg<4, 4, 3>(ma, sms, s);
-    case 4: return launch_fwd_cfg<8, 2, 2>(ma, sms, s);
-    case 5: return launch_fwd_cfg<4, 2, 6>(ma, sms, s);           // 24 warps per SM
-    default: return launch_fwd_cfg<4, 2, 4>(ma, sms, s);
+    case 2: return launch_fwd_cfg<4, 2, 4>(ma, sms, s);
+    case 5: return launch_fwd_cfg<4, 2, 5>(ma, sms, s);           // 20 warps per SM
+    default: return launch_fwd_cfg<8, 2, 2>(ma, sms, s);          // 16 warps per SM in two CTAs (measured best)
     }
 }
 

@@ -280,7 +280,7 @@ assert worst <= 1e-5, worst
 
 
 @pytest.mark.parametrize("env", [{"BTS_DETERMINISTIC": "1"}, {"BTS_HEAD_NWG": "3"}, {"BTS_PDL": "0"}, {"BTS_HEAD_MMA": "0"},
-                                 {"BTS_HEAD_MMA": "1"}, {"BTS_HEAD_MMA": "3"}], ids=lambda e: "-".join("%s=%s" % kv for kv in e.items()))
+                                 {"BTS_HEAD_MMA": "1"}, {"BTS_HEAD_MMA": "3"}, {"BTS_HEAD_EXACT": "1"}], ids=lambda e: "-".join("%s=%s" % kv for kv in e.items()))
 def test_environment_routes_vs_c_oracle(env):
     e = dict(os.environ)
     e.update(env)
