@@ -764,7 +764,7 @@ int launch_head_fwd_mma(const ChainParams &cp, const TcArgs &a, int sms, cudaStr
     ma.a = a;
     tc_set_weights(ma.a, cp);
     ma.atomic_w = 0;
-    static const int variant = getenv("BTS_HEAD_MMA") ? atoi(getenv("BTS_HEAD_MMA")) : 1;
+    static const int variant = getenv("BTS_HEAD_MMA") ? atoi(getenv("BTS_HEAD_MMA")) : -1;   // unset: the default case
     static const bool exact = getenv("BTS_HEAD_EXACT") != nullptr && atoi(getenv("BTS_HEAD_EXACT")) != 0;
     if (exact) return launch_fwd_cfg<8, 2, 2, true>(ma, sms, s);
     switch (variant) {
@@ -796,7 +796,7 @@ int launch_head_bwd_mma(const ChainParams &cp, const TcArgs &a, int sms, cudaStr
     tc_set_weights(ma.a, cp);
     for (int l = 0; l < BTS_MAX_LAYERS; ++l) ma.a.gw[l] = l < cp.n_layers ? cp.gW[l] : nullptr;
     ma.atomic_w = cp.gW[0] != nullptr ? 1 : 0;
-    static const int variant = getenv("BTS_HEAD_MMA") ? atoi(getenv("BTS_HEAD_MMA")) : 1;
+    static const int variant = getenv("BTS_HEAD_MMA") ? atoi(getenv("BTS_HEAD_MMA")) : -1;   // unset: the default case
     switch (variant) {                                            // (tuning variants; the default is the measured best)
     case 1: return launch_cfg<4, 3, 3>(ma, sms, s);               // 12 warps per SM, 168 registers, two tiles ahead
     case 3: return launch_cfg<4, 3, 2>(ma, sms, s);               // 8 warps per SM, 255 registers

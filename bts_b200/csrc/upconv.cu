@@ -1,0 +1,307 @@
+// upconv.cu -- the decoder's `upconv` block (pytorch/bts.py:83-94), forward:
+//     y = ELU(conv3x3(interpolate(x, scale_factor=2, mode='nearest')), bias=False, padding=1)
+// with the up-sampled tensor never materialised and 2.25x fewer multiply-adds than the reference's sequence.
+//
+// Folding. Output pixel (2i+a, 2j+b) of phase (a, b) reads rows {2i+a-1, 2i+a, 2i+a+1} of the up-sampled image =
+// source rows {i-1, i, i} (a = 0) or {i, i, i+1} (a = 1), likewise for columns. So every phase is a 2x2 convolution of the
+// LOW-RES input with weights that are sums of the 3x3 taps:
+//     y[o][2i+a][2j+b] = sum_c sum_{dy,dx in {0,1}} Wf[a][b][dy][dx][o][c] * x[c][i-1+a+dy][j-1+b+dx]      (zero outside)
+//     Wf[a][.][dy] sums the tap rows  a=0: {0} | {1,2},   a=1: {0,1} | {2}        (same for b / dx and the tap columns)
+// 16 Cin multiply-adds per low-res pixel and output channel for the four phases, against 36 Cin.
+//
+// Kernel: implicit GEMM on warp-level tensor-core MMAs with fp32-accurate two-instruction products (chain_head_mma.cu:
+// hi*hi as tf32 m16n8k8, lo*hi + hi*lo as one bf16 m16n8k16). Out channels on M (folded weights from a shared-memory
+// chunk), low-res pixels on N (eight consecutive pixels of a row: a shifted window of the halo tile is just another
+// shared-memory offset for register fragments -- no descriptor alignment to respect), input channels x taps on K. A CTA
+// computes 32 out channels x (8 x 16 low-res pixels) x both column phases of row phase a = blockIdx.z; a thread ends up
+// with output columns 4k..4k+3 of a row: 128-bit stores. cp.async double buffering, 16 input channels per stage.
+#include <cstdlib>
+
+#include "chain_tc.cuh"
+
+namespace bts {
+namespace {
+
+constexpr int kUcTW = 16, kUcTH = 8;                 // low-res tile
+constexpr int kUcKC = 16;                            // input channels per stage
+constexpr int kUcXR = kUcTH + 1, kUcXC = kUcTW + 2;  // halo tile of one row phase: 9 x 18
+constexpr int kUcXS = 168;                           // floats per channel (162 -> 168 = 8 mod 32: conflict-free B fragments)
+constexpr int kUcWS = 20;                            // floats per out-channel row of a weight chunk (16 + 4: conflict-free A fragments)
+constexpr int kUcMO = 32;                            // out channels per CTA
+constexpr int kUcXFloats = kUcKC * kUcXS, kUcWFloats = 8 * kUcMO * kUcWS;
+constexpr int kUcStageFloats = kUcXFloats + kUcWFloats;
+
+__device__ __forceinline__ void hmma_t(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1)
+{
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void hmma_b(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1)
+{
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t bf2(uint32_t lo, uint32_t hi)
+{
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(__uint_as_float(hi)), "f"(__uint_as_float(lo)));
+    return r;
+}
+__device__ __forceinline__ void split(float v, uint32_t &h, uint32_t &l)
+{
+    h = __float_as_uint(v) & 0xFFFFE000u;
+    l = __float_as_uint(v - __uint_as_float(h));
+}
+// fragments of an fp32-accurate product (see chain_head_mma.cu): tf32 hi words + bf16 pairs {lo, lo} / {hi, hi}
+struct UFragA { uint32_t h[4], s[4], l[4]; };
+struct UFragB { uint32_t h0, h1, s0, s1, l0, l1; };
+#ifndef BTS_UC_EXACT
+#define BTS_UC_EXACT 0       // 1: plain 3xTF32 (three tf32 instructions per product)
+#endif
+// The tensor core's fp32 accumulator truncates what it adds (tests/cuda/probe_hmma.cu), a bias toward zero that grows with
+// the K steps an accumulator sees: measured against the fp64 oracle 1.1e-5 of peak at cin = 512 and 4.6e-5 at cin = 2208
+// (cuDNN's fp32 kernels show 3.8e-5 there). So the accumulators leave the tensor core every BTS_UC_DRAIN stages (32 steps)
+// and continue as fp32 master sums with round-to-nearest adds: 1.4e-6 at every cin, for 64 more registers (two CTAs per SM
+// instead of three: 5.3 instead of 4.95 ms for the five decoder upconvs at nyu_b8). 0 = no drains.
+#ifndef BTS_UC_DRAIN
+#define BTS_UC_DRAIN 2
+#endif
+__device__ __forceinline__ void make_a(float v0, float v1, float v2, float v3, UFragA &f)
+{
+    split(v0, f.h[0], f.l[0]);
+    split(v1, f.h[1], f.l[1]);
+    split(v2, f.h[2], f.l[2]);
+    split(v3, f.h[3], f.l[3]);
+    f.s[0] = bf2(f.l[0], f.l[2]);
+    f.s[1] = bf2(f.l[1], f.l[3]);
+    f.s[2] = bf2(f.h[0], f.h[2]);
+    f.s[3] = bf2(f.h[1], f.h[3]);
+}
+__device__ __forceinline__ void make_b(float v0, float v1, UFragB &f)
+{
+    split(v0, f.h0, f.l0);
+    split(v1, f.h1, f.l1);
+    f.s0 = bf2(f.h0, f.h1);
+    f.s1 = bf2(f.l0, f.l1);
+}
+
+struct UpconvArgs {
+    const float *x;          // [B][Cin][h][w]
+    const float *wf;         // folded weights [2 a][2 b][2 dy][2 dx][Cout][Cin]
+    float *y;                // [B][Cout][2h][2w]
+    int B, Cin, Cout, h, w, tiles_x, tiles_y;
+};
+
+// Wf[a][b][dy][dx][o][c] from W[o][c][3][3]
+__global__ void upconv_fold_kernel(const float *__restrict__ w, float *__restrict__ wf, int cout, int cin)
+{
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= cout * cin) return;
+    float t[3][3];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) t[k / 3][k % 3] = __ldg(w + (size_t)e * 9 + k);
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int b = 0; b < 2; ++b)
+#pragma unroll
+            for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+                for (int dx = 0; dx < 2; ++dx) {
+                    // tap rows of (a, dy): a=0: {0} | {1,2}; a=1: {0,1} | {2}
+                    const int y0 = a == 0 ? (dy == 0 ? 0 : 1) : (dy == 0 ? 0 : 2), y1 = a == 0 ? (dy == 0 ? 0 : 2) : (dy == 0 ? 1 : 2);
+                    const int x0 = b == 0 ? (dx == 0 ? 0 : 1) : (dx == 0 ? 0 : 2), x1 = b == 0 ? (dx == 0 ? 0 : 2) : (dx == 0 ? 1 : 2);
+                    float s = 0.f;
+                    for (int ky = y0; ky <= y1; ++ky)
+                        for (int kx = x0; kx <= x1; ++kx) s += t[ky][kx];
+                    wf[(size_t)(((a * 2 + b) * 2 + dy) * 2 + dx) * cout * cin + e] = s;
+                }
+}
+
+__global__ void __launch_bounds__(128, BTS_UC_DRAIN ? 2 : 3) upconv_fwd_kernel(const __grid_constant__ UpconvArgs ua)
+{
+    extern __shared__ __align__(16) float smem[];
+    const int tid = threadIdx.x, lane = tid & 31, g = lane >> 2, t = lane & 3;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    const int a = blockIdx.z, o0 = blockIdx.y * kUcMO;
+    int tile = blockIdx.x;
+    const int tx = tile % ua.tiles_x;
+    tile /= ua.tiles_x;
+    const int ty = tile % ua.tiles_y, b_img = tile / ua.tiles_y;
+    const int i0 = ty * kUcTH, j0 = tx * kUcTW;
+    const int h = ua.h, w = ua.w, Cin = ua.Cin, Cout = ua.Cout;
+    const float *xb = ua.x + (size_t)b_img * Cin * h * w;
+    const float *wfa = ua.wf + (size_t)a * 8 * Cout * Cin;           // the eight (b, dy, dx) matrices of this row phase
+
+    auto load_stage = [&](int kc, int buf) {
+        float *xs = smem + buf * kUcStageFloats, *ws = xs + kUcXFloats;
+        // halo tile: smem row r <-> source row i0 - 1 + a + r, smem column c <-> source column j0 - 1 + c
+        for (int idx = tid; idx < kUcKC * kUcXR * kUcXC; idx += 128) {
+            const int c = idx / (kUcXR * kUcXC), rem = idx - c * (kUcXR * kUcXC);
+            const int r = rem / kUcXC, col = rem - r * kUcXC;
+            const int sr = i0 - 1 + a + r, sc = j0 - 1 + col;
+            const bool ok = sr >= 0 && sr < h && sc >= 0 && sc < w;
+            const float *src = xb + ((size_t)(kc * kUcKC + c) * h + (ok ? sr : 0)) * w + (ok ? sc : 0);
+            cp_async4(smem_u32(xs + c * kUcXS + r * kUcXC + col), src, ok);
+        }
+        // weight chunk: [8 products][32 out channels][16 input channels], 16 bytes per copy
+        for (int idx = tid; idx < 8 * kUcMO * (kUcKC / 4); idx += 128) {
+            const int p = idx / (kUcMO * (kUcKC / 4)), rem = idx - p * (kUcMO * (kUcKC / 4));
+            const int o = rem / (kUcKC / 4), q = rem - o * (kUcKC / 4);
+            const float *src = wfa + ((size_t)p * Cout + o0 + o) * Cin + kc * kUcKC + 4 * q;
+            cp_async16(smem_u32(ws + (p * kUcMO + o) * kUcWS + 4 * q), src, true);
+        }
+        cp_async_commit();
+    };
+
+    float acc[2][4][2][4];                                           // [m-tile][n-tile][column phase b][fragment]
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int n = 0; n < 4; ++n)
+#pragma unroll
+            for (int b = 0; b < 2; ++b)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) acc[mt][n][b][q] = 0.f;
+#if BTS_UC_DRAIN
+    float master[2][4][2][4];
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int n = 0; n < 4; ++n)
+#pragma unroll
+            for (int b = 0; b < 2; ++b)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) master[mt][n][b][q] = 0.f;
+#endif
+
+    const int nk = Cin / kUcKC;
+    load_stage(0, 0);
+    for (int kc = 0; kc < nk; ++kc) {
+        const int buf = kc & 1;
+        if (kc + 1 < nk) {
+            load_stage(kc + 1, buf ^ 1);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        __syncthreads();
+        const float *xs = smem + buf * kUcStageFloats, *ws = xs + kUcXFloats;
+#pragma unroll
+        for (int ks = 0; ks < kUcKC / 8; ++ks) {
+#pragma unroll
+            for (int p = 0; p < 8; ++p) {                            // product p = (b, dy, dx)
+                const int b = p >> 2, dy = (p >> 1) & 1, dx = p & 1;
+                UFragA fa[2];
+#pragma unroll
+                for (int mt = 0; mt < 2; ++mt) {
+                    const float *q = ws + (p * kUcMO + 16 * mt + g) * kUcWS + 8 * ks + t;
+                    make_a(q[0], q[8 * kUcWS], q[4], q[8 * kUcWS + 4], fa[mt]);
+                }
+#pragma unroll
+                for (int n = 0; n < 4; ++n) {                        // n-tile: row 2 warp + n/2 of the tile, columns 8 (n%2) ..+7
+                    const float *q = xs + (8 * ks + t) * kUcXS + (2 * warp + (n >> 1) + dy) * kUcXC + 8 * (n & 1) + b + dx + g;
+                    UFragB fb;
+                    make_b(q[0], q[4 * kUcXS], fb);
+#if BTS_UC_EXACT
+#pragma unroll
+                    for (int mt = 0; mt < 2; ++mt) hmma_t(acc[mt][n][b], fa[mt].l, fb.h0, fb.h1);
+#pragma unroll
+                    for (int mt = 0; mt < 2; ++mt) hmma_t(acc[mt][n][b], fa[mt].h, fb.l0, fb.l1);
+#else
+#pragma unroll
+                    for (int mt = 0; mt < 2; ++mt) hmma_b(acc[mt][n][b], fa[mt].s, fb.s0, fb.s1);
+#endif
+#pragma unroll
+                    for (int mt = 0; mt < 2; ++mt) hmma_t(acc[mt][n][b], fa[mt].h, fb.h0, fb.h1);
+                }
+            }
+        }
+        __syncthreads();
+#if BTS_UC_DRAIN
+        if ((kc + 1) % BTS_UC_DRAIN == 0 || kc + 1 == nk) {
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                for (int n = 0; n < 4; ++n)
+#pragma unroll
+                    for (int b = 0; b < 2; ++b)
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            master[mt][n][b][q] += acc[mt][n][b][q];
+                            acc[mt][n][b][q] = 0.f;
+                        }
+        }
+#endif
+    }
+#if BTS_UC_DRAIN
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int n = 0; n < 4; ++n)
+#pragma unroll
+            for (int b = 0; b < 2; ++b)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) acc[mt][n][b][q] = master[mt][n][b][q];
+#endif
+
+    // ---- ELU + stores: thread holds (o = 16 mt + g | + 8) x (low-res columns 2t, 2t+1 of the n-tile) x (b = 0, 1)
+    //      = four consecutive output columns of output row 2 i + a
+    const int H2 = 2 * h, W2 = 2 * w;
+    const bool vec_ok = (W2 % 4) == 0 && (reinterpret_cast<uintptr_t>(ua.y) & 15u) == 0;
+#pragma unroll
+    for (int n = 0; n < 4; ++n) {
+        const int i = i0 + 2 * warp + (n >> 1), j = j0 + 8 * (n & 1) + 2 * t;
+        if (i >= h || j >= w) continue;
+        const bool two = j + 1 < w;
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int hf = 0; hf < 2; ++hf) {
+                const int o = o0 + 16 * mt + g + 8 * hf;
+                float *dst = ua.y + (((size_t)b_img * Cout + o) * H2 + 2 * i + a) * W2 + 2 * j;
+                const float v0 = elu(acc[mt][n][0][2 * hf]), v1 = elu(acc[mt][n][1][2 * hf]);
+                const float v2 = elu(acc[mt][n][0][2 * hf + 1]), v3 = elu(acc[mt][n][1][2 * hf + 1]);
+                if (two && vec_ok) {
+                    *reinterpret_cast<float4 *>(dst) = make_float4(v0, v1, v2, v3);
+                } else {
+                    dst[0] = v0;
+                    dst[1] = v1;
+                    if (two) {
+                        dst[2] = v2;
+                        dst[3] = v3;
+                    }
+                }
+            }
+    }
+}
+
+}  // namespace
+
+size_t upconv_workspace_bytes(int cin, int cout) { return (size_t)16 * cin * cout * sizeof(float); }
+
+bool upconv_supported(int cin, int cout) { return cin > 0 && cout > 0 && cin % kUcKC == 0 && cout % kUcMO == 0; }
+
+int launch_upconv_fwd(const float *x, const float *w, float *y, int B, int cin, int cout, int h, int wd, void *ws, cudaStream_t s)
+{
+    float *wf = static_cast<float *>(ws);
+    upconv_fold_kernel<<<(cin * cout + 255) / 256, 256, 0, s>>>(w, wf, cout, cin);
+    if (int e = check_launch("upconv_fold")) return e;
+    UpconvArgs ua;
+    ua.x = x; ua.wf = wf; ua.y = y;
+    ua.B = B; ua.Cin = cin; ua.Cout = cout; ua.h = h; ua.w = wd;
+    ua.tiles_x = (wd + kUcTW - 1) / kUcTW;
+    ua.tiles_y = (h + kUcTH - 1) / kUcTH;
+    const size_t smem_bytes = sizeof(float) * 2 * kUcStageFloats;
+    cudaError_t e = cudaFuncSetAttribute(upconv_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+    if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    const long long tiles = (long long)ua.tiles_x * ua.tiles_y * B;
+    if (tiles > 0x7fffffffLL) return set_error(BTS_ERR_BAD_ARG, "too many tiles");
+    dim3 grid((unsigned)tiles, (unsigned)(cout / kUcMO), 2);
+    upconv_fwd_kernel<<<grid, 128, smem_bytes, s>>>(ua);
+    return check_launch("upconv_fwd");
+}
+
+}  // namespace bts

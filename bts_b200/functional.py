@@ -510,6 +510,28 @@ def backproject(depth, fx=518.8579, fy=518.8579, cx=None, cy=None, edge_thresh=0
     return pts[0] if single else pts
 
 
+def upconv_forward(x, weight):
+    """upconv.forward (pytorch/bts.py:90-94): ELU(conv3x3(nearest x2 (x)), padding 1, no bias) without materialising the
+    up-sampled tensor. x [B,Cin,h,w], weight [Cout,Cin,3,3] -> [B,Cout,2h,2w]. FORWARD ONLY: no
+    autograd graph is recorded (raises when a gradient is required); Cin % 16 == 0 and Cout % 32 == 0."""
+    x = _require_cuda_f32(x, "x")
+    weight = _require_cuda_f32(weight, "weight")
+    if torch.is_grad_enabled() and (x.requires_grad or weight.requires_grad):
+        raise RuntimeError("bts_b200 upconv: the backward is not built; call under torch.no_grad() or keep the stock module for training")
+    if x.dim() != 4 or weight.dim() != 4 or tuple(weight.shape[2:]) != (3, 3) or weight.shape[1] != x.shape[1]:
+        raise RuntimeError("upconv: x [B,Cin,h,w] and weight [Cout,Cin,3,3] expected")
+    x, weight = x.contiguous(), weight.contiguous()
+    B, cin, h, w = x.shape
+    cout = weight.shape[0]
+    y = torch.empty((B, cout, 2 * h, 2 * w), dtype=torch.float32, device=x.device)
+    nws = _cabi.lib().bts_upconv_workspace_bytes(cin, cout)
+    ws = torch.empty(((nws + 15) // 16 * 4,), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        _cabi.check(_cabi.lib().bts_upconv_fwd(x.data_ptr(), weight.data_ptr(), B, cin, cout, h, w, y.data_ptr(), ws.data_ptr(),
+                                               ws.numel() * 4, _stream()), "bts_upconv_fwd")
+    return y
+
+
 def _any_grad(x, weights):
     return torch.is_grad_enabled() and (x.requires_grad or any(w.requires_grad for w in weights))
 

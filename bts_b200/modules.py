@@ -93,6 +93,30 @@ class silog_loss(nn.Module):
         return Fn.silog(depth_est, depth_gt, mask, self.variance_focus)
 
 
+class upconv(nn.Module):
+    """Mirror of the reference `upconv` (pytorch/bts.py:83-94): same constructor, attributes (`elu`, `conv`, `ratio`) and
+    state_dict key (`conv.weight`). Inference (no gradient required) runs the folded tensor-core kernel
+    (functional.upconv_forward); under autograd, or for shapes / ratios the kernel does not serve, the reference's own
+    operator sequence runs (the backward of this block is not built -- SURVEY.md 8(f)-3 is forward only)."""
+
+    def __init__(self, in_channels, out_channels, ratio=2):
+        super().__init__()
+        self.elu = nn.ELU()
+        self.conv = nn.Conv2d(in_channels=in_channels, out_channels=out_channels, bias=False, kernel_size=3, stride=1, padding=1)
+        self.ratio = ratio
+
+    def native(self, x):
+        need_grad = torch.is_grad_enabled() and (x.requires_grad or self.conv.weight.requires_grad)
+        return (not need_grad and self.ratio == 2 and x.is_cuda and x.dtype == torch.float32
+                and self.conv.in_channels % 16 == 0 and self.conv.out_channels % 32 == 0)
+
+    def forward(self, x):
+        if self.native(x):
+            return Fn.upconv_forward(x, self.conv.weight)
+        up_x = torch.nn.functional.interpolate(x, scale_factor=self.ratio, mode='nearest')
+        return self.elu(self.conv(up_x))
+
+
 def fused_stage(reduc, lpg, net, return_plane_eq=False, scaled=False, downsample=False, out=None):
     """reducNxN -> normalise/cat -> lpgNxN (pytorch/bts.py:249-254) as ONE fused call.
 

@@ -250,6 +250,21 @@ BTS_API int bts_silog_fwd_static(const float *depth_est, const float *depth_gt, 
                                  float variance_focus, float *loss, void *state_out, void *stream);
 
 /*
+ * upconv.forward                                         pytorch/bts.py:83-94 (callers :226, 231, 258, 272, 285)
+ * (SURVEY.md 8(f)-3), FORWARD:  y = ELU(conv3x3(interpolate(x, scale_factor=2, mode='nearest'), padding=1, bias=False)).
+ * x [B][cin][h][w], weight [cout][cin][3][3] (the module's `conv.weight`), y [B][cout][2h][2w], all fp32, contiguous.
+ * The up-sampled tensor is never materialised: the nearest x2 is folded into the weights (four phases, each a 2x2
+ * convolution of the low-resolution input with sums of the 3x3 taps: 16 cin multiply-adds per low-res pixel and output
+ * channel instead of 36 cin), run as an implicit GEMM on tensor cores with fp32-accurate products, ELU in the epilogue.
+ * `ws`: bts_upconv_workspace_bytes(cin, cout) bytes (the folded weights, rebuilt by every call), 16-byte aligned.
+ * Served: cin % 16 == 0 and cout % 32 == 0 (every upconv of the BTS decoders); BTS_ERR_UNSUPPORTED otherwise.
+ * The backward is not built: autograd callers keep the stock modules.
+ */
+BTS_API size_t bts_upconv_workspace_bytes(int cin, int cout);
+BTS_API int bts_upconv_fwd(const float *x, const float *weight, int B, int cin, int cout, int h, int w, float *y,
+                           void *ws, size_t ws_bytes, void *stream);
+
+/*
  * online_eval's per-sample metrics                       pytorch/bts_main.py:218-254, compute_errors :87-108
  * (SURVEY.md 8(f)-5). For each of the B images: clamp the prediction to [min_depth, max_depth] (inf -> max,
  * nan -> min, :233-236), mask = min_depth < gt < max_depth inside the crop rectangle [crop_top, crop_bottom) x

@@ -97,3 +97,45 @@ def silog_forward(depth_est, depth_gt, mask, variance_focus):
     """silog_loss.forward, pytorch/bts.py:46-48 (pinned by tests/golden/silog_*.npz)."""
     d = torch.log(depth_est[mask]) - torch.log(depth_gt[mask])
     return torch.sqrt((d ** 2).mean() - variance_focus * (d.mean() ** 2)) * 10.0
+
+
+# ---- upconv (pytorch/bts.py:83-94) and the fold the CUDA kernel uses (SURVEY.md 8(f)-3) -------------------------------
+def upconv_forward(x, weight):
+    """The reference's operator sequence: nearest x2 -> conv3x3 (padding 1, no bias) -> ELU   (bts.py:90-94)."""
+    import torch.nn.functional as F
+    return F.elu(F.conv2d(F.interpolate(x, scale_factor=2, mode="nearest"), weight, padding=1))
+
+
+def upconv_fold_weights(weight):
+    """[Cout,Cin,3,3] -> [2 a][2 b][2 dy][2 dx][Cout][Cin]: phase (a, b) of the output is a 2x2 convolution of the LOW-RES
+    input with sums of the 3x3 taps (rows of (a, dy): a=0: {0} | {1,2}; a=1: {0,1} | {2}; same for columns)."""
+    import torch
+    rows = {(0, 0): (0,), (0, 1): (1, 2), (1, 0): (0, 1), (1, 1): (2,)}
+    wf = torch.zeros((2, 2, 2, 2) + tuple(weight.shape[:2]), dtype=weight.dtype)
+    for a in range(2):
+        for b in range(2):
+            for dy in range(2):
+                for dx in range(2):
+                    for ky in rows[(a, dy)]:
+                        for kx in rows[(b, dx)]:
+                            wf[a, b, dy, dx] += weight[:, :, ky, kx]
+    return wf
+
+
+def upconv_forward_folded(x, weight):
+    """Restatement of the kernel's arithmetic: y[o][2i+a][2j+b] = sum_c sum_{dy,dx} Wf[a][b][dy][dx][o][c] x[c][i-1+a+dy][j-1+b+dx]."""
+    import torch
+    import torch.nn.functional as F
+    B, cin, h, w = x.shape
+    wf = upconv_fold_weights(weight)
+    xp = F.pad(x, (1, 1, 1, 1))
+    y = torch.zeros((B, weight.shape[0], 2 * h, 2 * w), dtype=x.dtype)
+    for a in range(2):
+        for b in range(2):
+            acc = 0
+            for dy in range(2):
+                for dx in range(2):
+                    win = xp[:, :, a + dy:a + dy + h, b + dx:b + dx + w]           # x[c][i-1+a+dy][j-1+b+dx]
+                    acc = acc + torch.einsum("oc,bcij->boij", wf[a, b, dy, dx], win)
+            y[:, :, a::2, b::2] = acc
+    return F.elu(y)

@@ -177,6 +177,27 @@ def main():
                                         ("silog_sparse", (2, 1, 40, 56), 0.05, 0.5, 33)):
         silog_case(ref, name, shape, frac, vf, seed)
 
+    # --- upconv: the imported reference class, pytorch/bts.py:83-94, forward; ragged tiles, odd
+    # widths, one tile smaller than the kernel's 8 x 16
+    for name, cin, cout, B, h, w, seed in (("upconv_64_32", 64, 32, 2, 11, 19, 41), ("upconv_128_64", 128, 64, 1, 8, 16, 42),
+                                           ("upconv_32_32_tiny", 32, 32, 2, 3, 5, 43), ("upconv_48_96_odd", 48, 96, 1, 9, 17, 44)):
+        upconv_case(ref, name, cin, cout, B, h, w, seed)
+
+
+def upconv_case(ref, name, cin, cout, B, h, w, seed):
+    torch.manual_seed(seed)
+    mod = ref.upconv(cin, cout)                                  # the reference module itself (default Conv2d init)
+    x = torch.randn(B, cin, h, w)
+    out = dict(x=x.numpy(), w=mod.conv.weight.detach().numpy())
+    for tag, dt in (("f32", torch.float32), ("f64", torch.float64)):
+        with torch.no_grad():
+            out[tag + "_y"] = mod.to(dt)(x.to(dt)).numpy()
+    meta = dict(kind="upconv", name=name, cin=cin, cout=cout, B=B, h=h, w=w, seed=seed, reference="pytorch/bts.py:83-94",
+                torch=torch.__version__)
+    out["meta"] = json.dumps(meta)
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
+    print(name, {k: v.shape for k, v in out.items() if k != "meta"})
+
 
 def silog_case(ref, name, shape, frac, vf, seed):
     gen = torch.Generator().manual_seed(seed)

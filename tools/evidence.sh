@@ -20,7 +20,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-fil
 # full captures, digested here; the reports themselves stay on the box
 for s in head 2x2 4x4 8x8; do
   for d in bwd fwd; do
-    if [ $d = bwd ]; then K='regex:chain_bwd_fused|chain_tc_dgrad'; else K='regex:chain_tc_fwd'; fi
+    if [ $d = bwd ]; then K='regex:chain_bwd_fused|chain_tc_dgrad|head_bwd_mma'; else K='regex:chain_tc_fwd|head_fwd_mma'; fi
     ncu --set full --clock-control none --import-source on -k "$K" --launch-skip 3 -c 1 -f -o /tmp/${d}_$s \
         python tools/stage_times.py nyu_b8 5 $s > $OUT/ncu_${d}_$s.log 2>&1
     python tools/ncu_summary.py /tmp/${d}_$s.ncu-rep "$s $d" > $OUT/${TAG}_ncu_${d}_$s.txt 2>&1

@@ -7,7 +7,7 @@ STAGES=${@:-head 2x2 4x4 8x8}
 OUT=gpurun_out; mkdir -p $OUT
 for s in $STAGES; do
   for d in bwd fwd; do
-    if [ $d = bwd ]; then K='regex:chain_bwd_fused|chain_tc_dgrad'; else K='regex:chain_tc_fwd'; fi
+    if [ $d = bwd ]; then K='regex:chain_bwd_fused|chain_tc_dgrad|head_bwd_mma'; else K='regex:chain_tc_fwd|head_fwd_mma'; fi
     ncu --set full --clock-control none --import-source on -k "$K" --launch-skip 3 -c 1 -f -o $OUT/${d}_$s \
         python tools/stage_times.py $WL 5 $s > $OUT/ncu_${d}_$s.log 2>&1
     python tools/ncu_summary.py $OUT/${d}_$s.ncu-rep > $OUT/sum_${d}_$s.txt 2>&1
