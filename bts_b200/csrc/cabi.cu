@@ -53,6 +53,10 @@ int launch_chain_bwd_fused(const ChainParams &, const TcArgs &, int mode, int r,
 size_t upconv_workspace_bytes(int cin, int cout);
 bool upconv_supported(int cin, int cout);
 int launch_upconv_fwd(const float *x, const float *w, float *y, int B, int cin, int cout, int h, int wd, void *ws, cudaStream_t s);
+bool upconv_bwd_supported(int cin, int cout);
+size_t upconv_bwd_workspace_bytes(int B, int cin, int cout, int h, int w);
+int launch_upconv_bwd(const float *x, const float *w, const float *y, const float *gy, float *gx, float *gw, int B, int cin, int cout,
+                      int h, int wd, void *ws, cudaStream_t s);
 bool fused_bwd_supported(const ChainParams &);
 bool tc_supported(const ChainParams &);
 size_t tc_pack_bytes();
@@ -487,6 +491,29 @@ int bts_upconv_fwd(const float *x, const float *weight, int B, int cin, int cout
         return set_error(BTS_ERR_BAD_ARG, "upconv: workspace of %zu bytes (16-byte aligned) required", upconv_workspace_bytes(cin, cout));
     if (!aligned16(x) || !aligned16(weight)) return set_error(BTS_ERR_BAD_ARG, "upconv: x / weight must be 16-byte aligned");
     return launch_upconv_fwd(x, weight, y, B, cin, cout, h, w, ws, (cudaStream_t)stream);
+}
+
+size_t bts_upconv_bwd_workspace_bytes(int B, int cin, int cout, int h, int w)
+{
+    if (B <= 0 || cin <= 0 || cout <= 0 || h <= 0 || w <= 0) return 0;
+    return upconv_bwd_workspace_bytes(B, cin, cout, h, w);
+}
+
+int bts_upconv_bwd(const float *x, const float *weight, const float *y, const float *grad_y, int B, int cin, int cout, int h, int w,
+                   float *grad_x, float *grad_weight, void *ws, size_t ws_bytes, void *stream)
+{
+    if (B < 0 || h < 0 || w < 0 || cin <= 0 || cout <= 0) return set_error(BTS_ERR_BAD_ARG, "bad size B=%d cin=%d cout=%d h=%d w=%d", B, cin, cout, h, w);
+    if (!upconv_bwd_supported(cin, cout)) return set_error(BTS_ERR_UNSUPPORTED, "upconv backward: cin %% 32 == 0 and cout %% 32 == 0 required (cin=%d cout=%d)", cin, cout);
+    if ((long long)B * h * w == 0) {
+        if (grad_weight != nullptr) cudaMemsetAsync(grad_weight, 0, sizeof(float) * (size_t)9 * cin * cout, (cudaStream_t)stream);
+        return BTS_OK;
+    }
+    if (!x || !weight || !y || !grad_y) return set_error(BTS_ERR_BAD_ARG, "x / weight / y / grad_y is NULL");
+    if ((long long)B * cout * 4 * h * w > (1ll << 40) || (long long)4 * h * w > (1ll << 31) - 1) return set_error(BTS_ERR_UNSUPPORTED, "upconv: tensor too large");
+    if (ws == nullptr || !aligned16(ws) || ws_bytes < upconv_bwd_workspace_bytes(B, cin, cout, h, w))
+        return set_error(BTS_ERR_BAD_ARG, "upconv backward: workspace of %zu bytes (16-byte aligned) required", upconv_bwd_workspace_bytes(B, cin, cout, h, w));
+    if (!aligned16(x) || !aligned16(weight)) return set_error(BTS_ERR_BAD_ARG, "upconv: x / weight must be 16-byte aligned");
+    return launch_upconv_bwd(x, weight, y, grad_y, grad_x, grad_weight, B, cin, cout, h, w, ws, (cudaStream_t)stream);
 }
 
 /* ------------------------------------------------------------------ bf16 twin (ABI 4) ------------------------------ */

@@ -278,6 +278,304 @@ __global__ void __launch_bounds__(128, BTS_UC_DRAIN ? 2 : 3) upconv_fwd_kernel(c
     }
 }
 
+
+// =====================================================================================================================
+// backward.  e = grad_y . ELU'(y)  (ELU'(t) through y = ELU(t): y > 0 ? 1 : y + 1), split into its four phase planes
+//     E[a][b][img][o][i][j] = e[img][o][2i+a][2j+b]          (low-resolution sized, so every plane is a dense image)
+//   grad_x[c][i][j]          = sum_{a,b,dy,dx} sum_o Wf[a][b][dy][dx][o][c] * E[a][b][o][i+1-a-dy][j+1-b-dx]     (zero outside)
+//   grad_Wf[a][b][dy][dx][o][c] = sum_{img,i,j} E[a][b][o][i][j] * x[c][i-1+a+dy][j-1+b+dx]
+//   grad_W[o][c][ky][kx]     = sum of the grad_Wf entries whose tap sets contain (ky, kx)
+// Both products are implicit GEMMs of the forward's kind: the input gradient has the phase planes as its four sources
+// (K = out channels x 16 products), the weight gradient has the pixel axis as K.
+// =====================================================================================================================
+__global__ void upconv_eplanes_kernel(const float *__restrict__ gy, const float *__restrict__ y, float *__restrict__ e,
+                                      long long nlow, int h, int w)
+{
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;   // (img * Cout + o, i, j)
+    if (idx >= nlow) return;
+    const int j = (int)(idx % w);
+    const long long r = idx / w;
+    const int i = (int)(r % h);
+    const long long plane = r / h;
+    const size_t src = ((size_t)plane * 2 * h + 2 * i) * (2 * (size_t)w) + 2 * j;
+    float g4[4], y4[4];
+    g4[0] = __ldg(gy + src); g4[1] = __ldg(gy + src + 1); g4[2] = __ldg(gy + src + 2 * w); g4[3] = __ldg(gy + src + 2 * w + 1);
+    y4[0] = __ldg(y + src); y4[1] = __ldg(y + src + 1); y4[2] = __ldg(y + src + 2 * w); y4[3] = __ldg(y + src + 2 * w + 1);
+#pragma unroll
+    for (int ab = 0; ab < 4; ++ab) e[(size_t)ab * nlow + idx] = g4[ab] * elu_grad_from_out(y4[ab]);
+}
+
+constexpr int kDgKC = 8;                              // out channels (K) per stage: one k-step
+constexpr int kDgWS = 40;                             // floats per out-channel row of a weight chunk (32 c + 8: conflict-free A)
+constexpr int kDgEFloats = 4 * kDgKC * kUcXS, kDgWFloats = 16 * kDgKC * kDgWS;
+constexpr int kDgStageFloats = kDgEFloats + kDgWFloats;
+
+struct UpconvBwdArgs {
+    const float *x;          // [B][Cin][h][w]
+    const float *wf;         // folded weights [16 p][Cout][Cin]
+    const float *e;          // phase planes [4][B][Cout][h][w]
+    float *gx;               // [B][Cin][h][w]
+    float *gwf;              // [16 p][Cout][Cin], zero-filled before the weight-gradient kernel
+    int B, Cin, Cout, h, w, tiles_x, tiles_y;
+    int tiles_per_cta;       // weight gradient: pixel tiles per CTA (split K)
+};
+
+// grad_x: CTA = 32 input channels (M) x 8x16 pixels (N); K = out channels, 8 per stage, x 16 (plane, tap) products
+__global__ void __launch_bounds__(128, 2) upconv_dgrad_kernel(const __grid_constant__ UpconvBwdArgs ua)
+{
+    extern __shared__ __align__(16) float smem[];
+    const int tid = threadIdx.x, lane = tid & 31, g = lane >> 2, t = lane & 3;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    const int c0 = blockIdx.y * 32;
+    int tile = blockIdx.x;
+    const int tx = tile % ua.tiles_x;
+    tile /= ua.tiles_x;
+    const int ty = tile % ua.tiles_y, b_img = tile / ua.tiles_y;
+    const int i0 = ty * kUcTH, j0 = tx * kUcTW;
+    const int h = ua.h, w = ua.w, Cin = ua.Cin, Cout = ua.Cout;
+    const size_t plane_sz = (size_t)ua.B * Cout * h * w;
+
+    auto load_stage = [&](int kc, int buf) {
+        float *es = smem + buf * kDgStageFloats, *ws = es + kDgEFloats;
+        // plane (a, b): smem row r <-> source row i0 - a + r, smem column c <-> source column j0 - b + c
+        for (int idx = tid; idx < 4 * kDgKC * kUcXR * kUcXC; idx += 128) {
+            const int po = idx / (kUcXR * kUcXC), rem = idx - po * (kUcXR * kUcXC);   // po = plane * 8 + o
+            const int r = rem / kUcXC, col = rem - r * kUcXC;
+            const int ab = po >> 3, o = po & 7;
+            const int sr = i0 - (ab >> 1) + r, sc = j0 - (ab & 1) + col;
+            const bool ok = sr >= 0 && sr < h && sc >= 0 && sc < w;
+            const float *src = ua.e + (size_t)ab * plane_sz + (((size_t)b_img * Cout + kc * kDgKC + o) * h + (ok ? sr : 0)) * w + (ok ? sc : 0);
+            cp_async4(smem_u32(es + po * kUcXS + r * kUcXC + col), src, ok);
+        }
+        // weights: [16 products][8 out channels][32 input channels]
+        for (int idx = tid; idx < 16 * kDgKC * 8; idx += 128) {
+            const int po = idx >> 3, q = idx & 7;                    // po = product * 8 + o
+            const int p = po >> 3, o = po & 7;
+            const float *src = ua.wf + ((size_t)p * Cout + kc * kDgKC + o) * Cin + c0 + 4 * q;
+            cp_async16(smem_u32(ws + po * kDgWS + 4 * q), src, true);
+        }
+        cp_async_commit();
+    };
+
+    float acc[2][4][4], master[2][4][4];
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int n = 0; n < 4; ++n)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) acc[mt][n][q] = master[mt][n][q] = 0.f;
+
+    const int nk = Cout / kDgKC;
+    load_stage(0, 0);
+    for (int kc = 0; kc < nk; ++kc) {
+        const int buf = kc & 1;
+        if (kc + 1 < nk) {
+            load_stage(kc + 1, buf ^ 1);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        __syncthreads();
+        const float *es = smem + buf * kDgStageFloats, *ws = es + kDgEFloats;
+#pragma unroll
+        for (int p = 0; p < 16; ++p) {                               // p = ((a*2 + b)*2 + dy)*2 + dx
+            const int ab = p >> 2, dy = (p >> 1) & 1, dx = p & 1;
+            UFragA fa[2];
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt) {                         // A[m = c][k = o] = Wf[p][o][c]
+                const float *q = ws + (p * kDgKC + t) * kDgWS + 16 * mt + g;
+                make_a(q[0], q[8], q[4 * kDgWS], q[4 * kDgWS + 8], fa[mt]);
+            }
+#pragma unroll
+            for (int n = 0; n < 4; ++n) {
+                const float *q = es + (ab * kDgKC + t) * kUcXS + (2 * warp + (n >> 1) + 1 - dy) * kUcXC + 8 * (n & 1) + 1 - dx + g;
+                UFragB fb;
+                make_b(q[0], q[4 * kUcXS], fb);
+#pragma unroll
+                for (int mt = 0; mt < 2; ++mt) hmma_b(acc[mt][n], fa[mt].s, fb.s0, fb.s1);
+#pragma unroll
+                for (int mt = 0; mt < 2; ++mt) hmma_t(acc[mt][n], fa[mt].h, fb.h0, fb.h1);
+            }
+        }
+        __syncthreads();
+        // 32 accumulate steps per stage: the sums leave the tensor core (truncating accumulator, see BTS_UC_DRAIN)
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int n = 0; n < 4; ++n)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    master[mt][n][q] += acc[mt][n][q];
+                    acc[mt][n][q] = 0.f;
+                }
+    }
+
+    const bool vec_ok = (w % 2) == 0 && (reinterpret_cast<uintptr_t>(ua.gx) & 7u) == 0;
+#pragma unroll
+    for (int n = 0; n < 4; ++n) {
+        const int i = i0 + 2 * warp + (n >> 1), j = j0 + 8 * (n & 1) + 2 * t;
+        if (i >= h || j >= w) continue;
+        const bool two = j + 1 < w;
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int hf = 0; hf < 2; ++hf) {
+                float *dst = ua.gx + (((size_t)b_img * Cin + c0 + 16 * mt + g + 8 * hf) * h + i) * w + j;
+                if (two && vec_ok) {
+                    *reinterpret_cast<float2 *>(dst) = make_float2(master[mt][n][2 * hf], master[mt][n][2 * hf + 1]);
+                } else {
+                    dst[0] = master[mt][n][2 * hf];
+                    if (two) dst[1] = master[mt][n][2 * hf + 1];
+                }
+            }
+    }
+}
+
+
+// grad_Wf: the pixel axis is K. CTA = one phase plane (a, b) [its four (dy, dx) products share the plane's tile and one halo
+// tile of x] x 16 out channels (M) x 32 input channels (N) x a run of 8x16 pixel tiles (split K; fp32 atomics at the end).
+// A warp takes two rows of every tile = four k-steps of eight pixels along a row.
+constexpr int kWgES = 132;                            // floats per out-channel row of the plane tile (128 px + 4: conflict-free A)
+constexpr int kWgXS = 164;                            // floats per input channel of the halo tile (162 + 2: conflict-free B)
+constexpr int kWgEFloats = 16 * kWgES, kWgXFloats = 32 * kWgXS;
+constexpr int kWgStageFloats = kWgEFloats + kWgXFloats;
+
+__global__ void __launch_bounds__(128, 2) upconv_wgrad_kernel(const __grid_constant__ UpconvBwdArgs ua)
+{
+    extern __shared__ __align__(16) float smem[];
+    const int tid = threadIdx.x, lane = tid & 31, g = lane >> 2, t = lane & 3;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    const int h = ua.h, w = ua.w, Cin = ua.Cin, Cout = ua.Cout;
+    const int nob = Cout / 16;
+    const int ab = blockIdx.y / nob, o0 = (blockIdx.y % nob) * 16, c0 = blockIdx.z * 32;
+    const int a = ab >> 1, b = ab & 1;
+    const int ntiles = ua.tiles_x * ua.tiles_y * ua.B;
+    const int tile_begin = blockIdx.x * ua.tiles_per_cta;
+    const int tile_end = min(ntiles, tile_begin + ua.tiles_per_cta);
+    const float *eplane = ua.e + (size_t)ab * ua.B * Cout * h * w;
+
+    auto load_stage = [&](int tile, int buf) {
+        float *es = smem + buf * kWgStageFloats, *xs = es + kWgEFloats;
+        const int tx = tile % ua.tiles_x;
+        const int rest = tile / ua.tiles_x;
+        const int ty = rest % ua.tiles_y, img = rest / ua.tiles_y;
+        const int i0 = ty * kUcTH, j0 = tx * kUcTW;
+        {   // plane tile [16 o][8 x 16 px]: thread = pixel
+            const int r = tid >> 4, col = tid & 15;
+            const int sr = i0 + r, sc = j0 + col;
+            const bool ok = sr < h && sc < w;
+            const float *src = eplane + (((size_t)img * Cout + o0) * h + (ok ? sr : 0)) * w + (ok ? sc : 0);
+            const uint32_t dst = smem_u32(es + tid);
+#pragma unroll
+            for (int o = 0; o < 16; ++o) cp_async4(dst + o * kWgES * 4, src + (size_t)o * h * w, ok);
+        }
+        // halo tile of x [32 c][9 x 18]: smem row r <-> source row i0 - 1 + a + r, column c <-> j0 - 1 + b + c
+        for (int pos = tid; pos < kUcXR * kUcXC; pos += 128) {
+            const int r = pos / kUcXC, col = pos - r * kUcXC;
+            const int sr = i0 - 1 + a + r, sc = j0 - 1 + b + col;
+            const bool ok = sr >= 0 && sr < h && sc >= 0 && sc < w;
+            const float *src = ua.x + (((size_t)img * Cin + c0) * h + (ok ? sr : 0)) * w + (ok ? sc : 0);
+            const uint32_t dst = smem_u32(xs + pos);
+#pragma unroll 8
+            for (int c = 0; c < 32; ++c) cp_async4(dst + c * kWgXS * 4, src + (size_t)c * h * w, ok);
+        }
+        cp_async_commit();
+    };
+
+    float acc[4][4][4], master[4][4][4];                             // [product (dy, dx)][n-tile (8 c)][fragment]
+#pragma unroll
+    for (int p = 0; p < 4; ++p)
+#pragma unroll
+        for (int n = 0; n < 4; ++n)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) acc[p][n][q] = master[p][n][q] = 0.f;
+
+    if (tile_begin < tile_end) load_stage(tile_begin, 0);
+    for (int tile = tile_begin; tile < tile_end; ++tile) {
+        const int buf = (tile - tile_begin) & 1;
+        if (tile + 1 < tile_end) {
+            load_stage(tile + 1, buf ^ 1);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        __syncthreads();
+        const float *es = smem + buf * kWgStageFloats, *xs = es + kWgEFloats;
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) {                             // eight pixels: row 2 warp + ks/2, columns 8 (ks%2) ..+7
+            const int rowl = 2 * warp + (ks >> 1), colb = 8 * (ks & 1);
+            UFragA fa;                                               // A[m = o][k = px] = E[o][px]
+            {
+                const float *q = es + g * kWgES + rowl * 16 + colb + t;
+                make_a(q[0], q[8 * kWgES], q[4], q[8 * kWgES + 4], fa);
+            }
+#pragma unroll
+            for (int p = 0; p < 4; ++p) {
+                const int dy = p >> 1, dx = p & 1;
+#pragma unroll
+                for (int n = 0; n < 4; ++n) {                        // B[k = px][n = c] = x[c][row + dy][col + dx]
+                    const float *q = xs + (8 * n + g) * kWgXS + (rowl + dy) * kUcXC + colb + dx + t;
+                    UFragB fb;
+                    make_b(q[0], q[4], fb);
+                    hmma_b(acc[p][n], fa.s, fb.s0, fb.s1);
+                    hmma_t(acc[p][n], fa.h, fb.h0, fb.h1);
+                }
+            }
+        }
+        __syncthreads();
+        if (((tile - tile_begin) & 3) == 3 || tile + 1 == tile_end) {   // 32 accumulate steps: drain (see BTS_UC_DRAIN)
+#pragma unroll
+            for (int p = 0; p < 4; ++p)
+#pragma unroll
+                for (int n = 0; n < 4; ++n)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        master[p][n][q] += acc[p][n][q];
+                        acc[p][n][q] = 0.f;
+                    }
+        }
+    }
+    // the four warps' sums -> shared memory -> one atomic per element and CTA
+    float *red = smem;                                               // [4 p][16 o][32 c]
+    for (int e = tid; e < 4 * 16 * 32; e += 128) red[e] = 0.f;
+    __syncthreads();
+#pragma unroll
+    for (int p = 0; p < 4; ++p)
+#pragma unroll
+        for (int n = 0; n < 4; ++n)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) atomicAdd(red + (p * 16 + g + 8 * (q >> 1)) * 32 + 8 * n + 2 * t + (q & 1), master[p][n][q]);
+    __syncthreads();
+    for (int e = tid; e < 4 * 16 * 32; e += 128) {
+        const int p = e >> 9, o = (e >> 5) & 15, c = e & 31;
+        atomicAdd(ua.gwf + ((size_t)(ab * 4 + p) * Cout + o0 + o) * Cin + c0 + c, red[e]);
+    }
+}
+
+// grad_W[o][c][ky][kx] = sum of the folded gradients whose tap sets contain (ky, kx)
+__global__ void upconv_unfold_kernel(const float *__restrict__ gwf, float *__restrict__ gw, int cout, int cin)
+{
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= cout * cin) return;
+    const size_t n = (size_t)cout * cin;
+    float f[2][2][2][2];
+#pragma unroll
+    for (int p = 0; p < 16; ++p) f[p >> 3][(p >> 2) & 1][(p >> 1) & 1][p & 1] = __ldg(gwf + p * n + e);
+    // tap k belongs to (phase, d): k=0: (0,0), (1,0);  k=1: (0,1), (1,0);  k=2: (0,1), (1,1)
+    const int ph[3][2] = {{0, 1}, {0, 1}, {0, 1}}, dd[3][2] = {{0, 0}, {1, 0}, {1, 1}};
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+        for (int kx = 0; kx < 3; ++kx) {
+            float s = 0.f;
+#pragma unroll
+            for (int u = 0; u < 2; ++u)
+#pragma unroll
+                for (int v = 0; v < 2; ++v) s += f[ph[ky][u]][ph[kx][v]][dd[ky][u]][dd[kx][v]];
+            gw[(size_t)e * 9 + ky * 3 + kx] = s;
+        }
+}
+
 }  // namespace
 
 size_t upconv_workspace_bytes(int cin, int cout) { return (size_t)16 * cin * cout * sizeof(float); }
@@ -302,6 +600,64 @@ int launch_upconv_fwd(const float *x, const float *w, float *y, int B, int cin, 
     dim3 grid((unsigned)tiles, (unsigned)(cout / kUcMO), 2);
     upconv_fwd_kernel<<<grid, 128, smem_bytes, s>>>(ua);
     return check_launch("upconv_fwd");
+}
+
+}  // namespace bts
+
+namespace bts {
+
+bool upconv_bwd_supported(int cin, int cout) { return cin > 0 && cout > 0 && cin % 32 == 0 && cout % 32 == 0; }
+
+size_t upconv_bwd_workspace_bytes(int B, int cin, int cout, int h, int w)
+{
+    return sizeof(float) * ((size_t)32 * cin * cout + (size_t)4 * B * cout * h * w);
+}
+
+// ws = [folded weights 16 Cout Cin | folded weight gradients 16 Cout Cin | phase planes 4 B Cout h w]
+int launch_upconv_bwd(const float *x, const float *w, const float *y, const float *gy, float *gx, float *gw, int B, int cin, int cout,
+                      int h, int wd, void *ws, cudaStream_t s)
+{
+    float *wf = static_cast<float *>(ws), *gwf = wf + (size_t)16 * cin * cout, *e = gwf + (size_t)16 * cin * cout;
+    const long long nlow = (long long)B * cout * h * wd;
+    upconv_eplanes_kernel<<<(unsigned)((nlow + 255) / 256), 256, 0, s>>>(gy, y, e, nlow, h, wd);
+    if (int er = check_launch("upconv_eplanes")) return er;
+    UpconvBwdArgs ua;
+    ua.x = x; ua.wf = wf; ua.e = e; ua.gx = gx; ua.gwf = gwf;
+    ua.B = B; ua.Cin = cin; ua.Cout = cout; ua.h = h; ua.w = wd;
+    ua.tiles_x = (wd + kUcTW - 1) / kUcTW;
+    ua.tiles_y = (h + kUcTH - 1) / kUcTH;
+    ua.tiles_per_cta = 1;
+    const long long tiles = (long long)ua.tiles_x * ua.tiles_y * B;
+    if (tiles > 0x7fffffffLL) return set_error(BTS_ERR_BAD_ARG, "too many tiles");
+    if (gx != nullptr) {
+        upconv_fold_kernel<<<(cin * cout + 255) / 256, 256, 0, s>>>(w, wf, cout, cin);
+        if (int er = check_launch("upconv_fold")) return er;
+        const size_t smem_bytes = sizeof(float) * 2 * kDgStageFloats;
+        cudaError_t ce = cudaFuncSetAttribute(upconv_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+        if (ce != cudaSuccess) return set_error((int)ce, "cudaFuncSetAttribute: %s", cudaGetErrorString(ce));
+        upconv_dgrad_kernel<<<dim3((unsigned)tiles, (unsigned)(cin / 32), 1), 128, smem_bytes, s>>>(ua);
+        if (int er = check_launch("upconv_dgrad")) return er;
+    }
+    if (gw != nullptr) {
+        cudaError_t ce = cudaMemsetAsync(gwf, 0, sizeof(float) * (size_t)16 * cin * cout, s);
+        if (ce != cudaSuccess) return set_error((int)ce, "cudaMemsetAsync: %s", cudaGetErrorString(ce));
+        // split K so that the grid has a few CTAs per SM slot
+        const long long blocks = (long long)4 * (cout / 16) * (cin / 32);
+        long long ksplit = (8 * 148 * 2 + blocks - 1) / blocks;
+        if (ksplit < 1) ksplit = 1;
+        if (ksplit > tiles) ksplit = tiles;
+        ua.tiles_per_cta = (int)((tiles + ksplit - 1) / ksplit);
+        const unsigned gx_ = (unsigned)((tiles + ua.tiles_per_cta - 1) / ua.tiles_per_cta);
+        if (4 * (cout / 16) > 65535 || cin / 32 > 65535) return set_error(BTS_ERR_UNSUPPORTED, "upconv: too many channels");
+        const size_t smem_bytes = sizeof(float) * 2 * kWgStageFloats;
+        ce = cudaFuncSetAttribute(upconv_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+        if (ce != cudaSuccess) return set_error((int)ce, "cudaFuncSetAttribute: %s", cudaGetErrorString(ce));
+        upconv_wgrad_kernel<<<dim3(gx_, (unsigned)(4 * (cout / 16)), (unsigned)(cin / 32)), 128, smem_bytes, s>>>(ua);
+        if (int er = check_launch("upconv_wgrad")) return er;
+        upconv_unfold_kernel<<<(cin * cout + 255) / 256, 256, 0, s>>>(gwf, gw, cout, cin);
+        if (int er = check_launch("upconv_unfold")) return er;
+    }
+    return BTS_OK;
 }
 
 }  // namespace bts

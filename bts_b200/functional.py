@@ -510,17 +510,7 @@ def backproject(depth, fx=518.8579, fy=518.8579, cx=None, cy=None, edge_thresh=0
     return pts[0] if single else pts
 
 
-def upconv_forward(x, weight):
-    """upconv.forward (pytorch/bts.py:90-94): ELU(conv3x3(nearest x2 (x)), padding 1, no bias) without materialising the
-    up-sampled tensor. x [B,Cin,h,w], weight [Cout,Cin,3,3] -> [B,Cout,2h,2w]. FORWARD ONLY: no
-    autograd graph is recorded (raises when a gradient is required); Cin % 16 == 0 and Cout % 32 == 0."""
-    x = _require_cuda_f32(x, "x")
-    weight = _require_cuda_f32(weight, "weight")
-    if torch.is_grad_enabled() and (x.requires_grad or weight.requires_grad):
-        raise RuntimeError("bts_b200 upconv: the backward is not built; call under torch.no_grad() or keep the stock module for training")
-    if x.dim() != 4 or weight.dim() != 4 or tuple(weight.shape[2:]) != (3, 3) or weight.shape[1] != x.shape[1]:
-        raise RuntimeError("upconv: x [B,Cin,h,w] and weight [Cout,Cin,3,3] expected")
-    x, weight = x.contiguous(), weight.contiguous()
+def _upconv_fwd_raw(x, weight):
     B, cin, h, w = x.shape
     cout = weight.shape[0]
     y = torch.empty((B, cout, 2 * h, 2 * w), dtype=torch.float32, device=x.device)
@@ -530,6 +520,55 @@ def upconv_forward(x, weight):
         _cabi.check(_cabi.lib().bts_upconv_fwd(x.data_ptr(), weight.data_ptr(), B, cin, cout, h, w, y.data_ptr(), ws.data_ptr(),
                                                ws.numel() * 4, _stream()), "bts_upconv_fwd")
     return y
+
+
+class _Upconv(torch.autograd.Function):
+    """upconv.forward (pytorch/bts.py:90-94) and its autograd backward (bts_upconv_fwd / bts_upconv_bwd)."""
+
+    @staticmethod
+    def forward(ctx, x, weight):
+        y = _upconv_fwd_raw(x, weight)
+        ctx.save_for_backward(x, weight, y)
+        return y
+
+    @staticmethod
+    def backward(ctx, grad_y):
+        x, weight, y = ctx.saved_tensors
+        grad_y = _require_cuda_f32(grad_y, "grad_y").contiguous()
+        B, cin, h, w = x.shape
+        cout = weight.shape[0]
+        gx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
+        gw = torch.empty_like(weight) if ctx.needs_input_grad[1] else None
+        nws = _cabi.lib().bts_upconv_bwd_workspace_bytes(B, cin, cout, h, w)
+        ws = torch.empty(((nws + 15) // 16 * 4,), dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            _cabi.check(_cabi.lib().bts_upconv_bwd(x.data_ptr(), weight.data_ptr(), y.data_ptr(), grad_y.data_ptr(), B, cin, cout, h, w,
+                                                   gx.data_ptr() if gx is not None else None, gw.data_ptr() if gw is not None else None,
+                                                   ws.data_ptr(), ws.numel() * 4, _stream()), "bts_upconv_bwd")
+        return gx, gw
+
+
+def upconv_supported(cin, cout, need_grad):
+    """Channel counts the upconv kernels serve (every upconv of the BTS decoders qualifies)."""
+    return cin % (32 if need_grad else 16) == 0 and cout % 32 == 0
+
+
+def upconv_forward(x, weight):
+    """upconv.forward (pytorch/bts.py:90-94): ELU(conv3x3(nearest x2 (x)), padding 1, no bias) without materialising the
+    up-sampled tensor. x [B,Cin,h,w], weight [Cout,Cin,3,3] -> [B,Cout,2h,2w]; differentiable in x and
+    weight. Cin % 16 == 0 and Cout % 32 == 0 (Cin % 32 == 0 when a gradient is required); raises otherwise."""
+    x = _require_cuda_f32(x, "x")
+    weight = _require_cuda_f32(weight, "weight")
+    if x.dim() != 4 or weight.dim() != 4 or tuple(weight.shape[2:]) != (3, 3) or weight.shape[1] != x.shape[1]:
+        raise RuntimeError("upconv: x [B,Cin,h,w] and weight [Cout,Cin,3,3] expected")
+    need_grad = torch.is_grad_enabled() and (x.requires_grad or weight.requires_grad)
+    if not upconv_supported(x.shape[1], weight.shape[0], need_grad):
+        raise RuntimeError("bts_b200 upconv: Cin %% %d == 0 and Cout %% 32 == 0 required (Cin=%d, Cout=%d)" % (
+            32 if need_grad else 16, x.shape[1], weight.shape[0]))
+    x, weight = x.contiguous(), weight.contiguous()
+    if need_grad:
+        return _Upconv.apply(x, weight)
+    return _upconv_fwd_raw(x, weight)
 
 
 def _any_grad(x, weights):

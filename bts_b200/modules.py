@@ -95,9 +95,10 @@ class silog_loss(nn.Module):
 
 class upconv(nn.Module):
     """Mirror of the reference `upconv` (pytorch/bts.py:83-94): same constructor, attributes (`elu`, `conv`, `ratio`) and
-    state_dict key (`conv.weight`). Inference (no gradient required) runs the folded tensor-core kernel
-    (functional.upconv_forward); under autograd, or for shapes / ratios the kernel does not serve, the reference's own
-    operator sequence runs (the backward of this block is not built -- SURVEY.md 8(f)-3 is forward only)."""
+    state_dict key (`conv.weight`). Forward and backward run the folded tensor-core kernels (functional.upconv_forward).
+    What the kernels do not serve -- ratio != 2, channel counts that are not multiples of 32 (16 for the input channels
+    when no gradient is required), non-CUDA / non-fp32 tensors -- runs the reference's own operator sequence;
+    `native(x)` tells which."""
 
     def __init__(self, in_channels, out_channels, ratio=2):
         super().__init__()
@@ -107,8 +108,8 @@ class upconv(nn.Module):
 
     def native(self, x):
         need_grad = torch.is_grad_enabled() and (x.requires_grad or self.conv.weight.requires_grad)
-        return (not need_grad and self.ratio == 2 and x.is_cuda and x.dtype == torch.float32
-                and self.conv.in_channels % 16 == 0 and self.conv.out_channels % 32 == 0)
+        return (self.ratio == 2 and x.is_cuda and x.dtype == torch.float32 and x.dim() == 4
+                and Fn.upconv_supported(self.conv.in_channels, self.conv.out_channels, need_grad))
 
     def forward(self, x):
         if self.native(x):

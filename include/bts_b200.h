@@ -258,11 +258,20 @@ BTS_API int bts_silog_fwd_static(const float *depth_est, const float *depth_gt, 
  * channel instead of 36 cin), run as an implicit GEMM on tensor cores with fp32-accurate products, ELU in the epilogue.
  * `ws`: bts_upconv_workspace_bytes(cin, cout) bytes (the folded weights, rebuilt by every call), 16-byte aligned.
  * Served: cin % 16 == 0 and cout % 32 == 0 (every upconv of the BTS decoders); BTS_ERR_UNSUPPORTED otherwise.
- * The backward is not built: autograd callers keep the stock modules.
+ *
+ * bts_upconv_bwd: its autograd backward. y = the forward's output (ELU' is taken through it: y > 0 ? 1 : y + 1),
+ * grad_y like y; grad_x [B][cin][h][w] and grad_weight [cout][cin][3][3] are WRITTEN (either may be NULL = not wanted).
+ * e = grad_y . ELU'(y) is split into its four phase planes, grad_x gathers them through the folded weights, the folded
+ * weight gradient has the pixel axis as K (split over CTAs, fp32 atomics) and is un-folded into the 3x3 taps.
+ * `ws`: bts_upconv_bwd_workspace_bytes() bytes (folded weights, folded weight gradients, phase planes), 16-byte aligned.
+ * Served: cin % 32 == 0 and cout % 32 == 0.
  */
 BTS_API size_t bts_upconv_workspace_bytes(int cin, int cout);
 BTS_API int bts_upconv_fwd(const float *x, const float *weight, int B, int cin, int cout, int h, int w, float *y,
                            void *ws, size_t ws_bytes, void *stream);
+BTS_API size_t bts_upconv_bwd_workspace_bytes(int B, int cin, int cout, int h, int w);
+BTS_API int bts_upconv_bwd(const float *x, const float *weight, const float *y, const float *grad_y, int B, int cin, int cout,
+                           int h, int w, float *grad_x, float *grad_weight, void *ws, size_t ws_bytes, void *stream);
 
 /*
  * online_eval's per-sample metrics                       pytorch/bts_main.py:218-254, compute_errors :87-108

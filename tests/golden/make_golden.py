@@ -188,10 +188,17 @@ def upconv_case(ref, name, cin, cout, B, h, w, seed):
     torch.manual_seed(seed)
     mod = ref.upconv(cin, cout)                                  # the reference module itself (default Conv2d init)
     x = torch.randn(B, cin, h, w)
-    out = dict(x=x.numpy(), w=mod.conv.weight.detach().numpy())
+    gy = torch.randn(B, cout, 2 * h, 2 * w)
+    out = dict(x=x.numpy(), w=mod.conv.weight.detach().numpy(), grad_y=gy.numpy())
     for tag, dt in (("f32", torch.float32), ("f64", torch.float64)):
-        with torch.no_grad():
-            out[tag + "_y"] = mod.to(dt)(x.to(dt)).numpy()
+        m = mod.to(dt)
+        m.zero_grad()
+        xd = x.detach().clone().to(dt).requires_grad_(True)
+        y = m(xd)
+        y.backward(gy.to(dt))
+        out[tag + "_y"] = y.detach().numpy()
+        out[tag + "_grad_x"] = xd.grad.numpy()
+        out[tag + "_grad_w"] = m.conv.weight.grad.numpy().copy()
     meta = dict(kind="upconv", name=name, cin=cin, cout=cout, B=B, h=h, w=w, seed=seed, reference="pytorch/bts.py:83-94",
                 torch=torch.__version__)
     out["meta"] = json.dumps(meta)

@@ -20,6 +20,20 @@ def test_upconv_oracle_vs_golden(g):
     assert max_rel_to_peak(tp.upconv_forward_folded(x, w).numpy(), g["f64_y"]) <= 2e-6
 
 
+def _oracle_grads(x, w, gy, dtype):
+    xd = x.detach().clone().to(dtype).requires_grad_(True)
+    wd = w.detach().clone().to(dtype).requires_grad_(True)
+    y = tp.upconv_forward(xd, wd)
+    y.backward(gy.to(dtype))
+    return y.detach(), xd.grad, wd.grad
+
+
+@pytest.mark.parametrize("g", CASES, ids=lambda g: g.name)
+def test_upconv_oracle_backward_vs_golden(g):
+    y, gx, gw = _oracle_grads(torch.from_numpy(g["x"]), torch.from_numpy(g["w"]), torch.from_numpy(g["grad_y"]), torch.float64)
+    assert max_rel_to_peak(gx.numpy(), g["f64_grad_x"]) <= 1e-12 and max_rel_to_peak(gw.numpy(), g["f64_grad_w"]) <= 1e-12
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("g", CASES, ids=lambda g: g.name)
 def test_upconv_kernel_vs_golden(g):
@@ -29,41 +43,69 @@ def test_upconv_kernel_vs_golden(g):
     with torch.no_grad():
         mod.conv.weight.copy_(torch.from_numpy(g["w"]).cuda())
         x = torch.from_numpy(g["x"]).cuda()
-        if m["cin"] % 16 == 0 and m["cout"] % 32 == 0:
-            assert mod.native(x)
+        assert mod.native(x)
         y = mod(x)
     torch.cuda.synchronize()
     assert tuple(y.shape) == g["f64_y"].shape
     assert max_rel_to_peak(y.cpu().numpy(), g["f64_y"]) <= 1e-5
     assert np.allclose(y.cpu().numpy(), g["f64_y"], rtol=1e-4, atol=1e-5 * np.abs(g["f64_y"]).max())
+    # backward (served for cin % 32 == 0; otherwise the module runs the reference's operator sequence, also checked)
+    xg = torch.from_numpy(g["x"]).cuda().requires_grad_(True)
+    assert mod.native(xg) == (m["cin"] % 32 == 0)
+    tf32 = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False              # (the stock sequence is 3e-4 off with PyTorch's TF32 default)
+    try:
+        yg = mod(xg)
+        yg.backward(torch.from_numpy(g["grad_y"]).cuda())
+        torch.cuda.synchronize()
+    finally:
+        torch.backends.cudnn.allow_tf32 = tf32
+    assert max_rel_to_peak(yg.detach().cpu().numpy(), g["f64_y"]) <= 1e-5
+    assert max_rel_to_peak(xg.grad.cpu().numpy(), g["f64_grad_x"]) <= 1e-5
+    assert max_rel_to_peak(mod.conv.weight.grad.cpu().numpy(), g["f64_grad_w"]) <= 1e-5
 
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("cin,cout,B,h,w", [(64, 32, 2, 60, 80), (128, 64, 1, 30, 40), (512, 256, 1, 15, 20), (2208, 512, 1, 7, 10)], ids=str)
 def test_upconv_kernel_vs_oracle_decoder_shapes(cin, cout, B, h, w):
-    """The decoder's own channel counts (bts.py:226-285, bts_size 512 on densenet161) against the fp64 oracle on the host."""
+    """The decoder's own channel counts (bts.py:226-285, bts_size 512 on densenet161), forward and backward, against the
+    fp64 oracle (autograd of the reference's operator sequence) on the host."""
     from bts_b200 import functional as Fn
     gen = torch.Generator().manual_seed(7 + cin)
     x = torch.randn(B, cin, h, w, generator=gen)
     wt = torch.randn(cout, cin, 3, 3, generator=gen) * (2.0 / (9 * cin)) ** 0.5
-    ref = tp.upconv_forward(x.double(), wt.double()).numpy()
+    gy = torch.randn(B, cout, 2 * h, 2 * w, generator=gen)
+    ref_y, ref_gx, ref_gw = _oracle_grads(x, wt, gy, torch.float64)
+    xd, wd = x.cuda().requires_grad_(True), wt.cuda().requires_grad_(True)
+    y = Fn.upconv_forward(xd, wd)
+    y.backward(gy.cuda())
+    torch.cuda.synchronize()
+    assert max_rel_to_peak(y.detach().cpu().numpy(), ref_y.numpy()) <= 1e-5
+    assert max_rel_to_peak(xd.grad.cpu().numpy(), ref_gx.numpy()) <= 1e-5
+    assert max_rel_to_peak(wd.grad.cpu().numpy(), ref_gw.numpy()) <= 1e-5
     with torch.no_grad():
-        y = Fn.upconv_forward(x.cuda(), wt.cuda())
-    assert max_rel_to_peak(y.cpu().numpy(), ref) <= 1e-5
+        assert torch.equal(Fn.upconv_forward(x.cuda(), wt.cuda()), y.detach())
 
 
 @pytest.mark.gpu
 def test_upconv_module_contract():
     import bts_b200
+    from bts_b200 import functional as Fn
     mod = bts_b200.upconv(64, 32)
     assert list(mod.state_dict().keys()) == ["conv.weight"] and mod.ratio == 2 and isinstance(mod.elu, torch.nn.ELU)
     mod = mod.cuda()
     x = torch.randn(1, 64, 6, 10, device="cuda", requires_grad=True)
-    y = mod(x)                                     # a gradient is required: the reference's operator sequence (backward not built)
-    y.sum().backward()
-    assert x.grad is not None and not mod.native(x)
-    from bts_b200 import functional as Fn
-    with pytest.raises(RuntimeError):
-        Fn.upconv_forward(x, mod.conv.weight)
+    assert mod.native(x)
+    mod(x).sum().backward()
+    assert x.grad is not None and mod.conv.weight.grad is not None
+    only_x = torch.randn(1, 64, 6, 10, device="cuda", requires_grad=True)       # frozen weights: grad_x only
+    w_frozen = mod.conv.weight.detach()
+    Fn.upconv_forward(only_x, w_frozen).sum().backward()
+    ref_in = only_x.detach().double().cpu().requires_grad_(True)
+    ref_gx = torch.autograd.grad(tp.upconv_forward(ref_in, w_frozen.double().cpu()).sum(), ref_in)[0]
+    assert max_rel_to_peak(only_x.grad.cpu().numpy(), ref_gx.numpy()) <= 1e-5
+    odd = bts_b200.upconv(24, 32).cuda()                                         # not served: the reference's sequence
+    xo = torch.randn(1, 24, 4, 4, device="cuda")
+    assert not odd.native(xo) and odd(xo).shape == (1, 32, 8, 8)
     with torch.no_grad(), pytest.raises(RuntimeError):
-        Fn.upconv_forward(torch.randn(1, 24, 4, 4, device="cuda"), torch.randn(32, 24, 3, 3, device="cuda"))
+        Fn.upconv_forward(xo, odd.conv.weight)
