@@ -26,9 +26,9 @@ constexpr int kUcTW = 16, kUcTH = 8;                 // low-res tile
 constexpr int kUcKC = 16;                            // input channels per stage
 constexpr int kUcXR = kUcTH + 1, kUcXC = kUcTW + 2;  // halo tile of one row phase: 9 x 18
 constexpr int kUcXS = 168;                           // floats per channel (162 -> 168 = 8 mod 32: conflict-free B fragments)
-constexpr int kUcWS = 20;                            // floats per out-channel row of a weight chunk (16 + 4: conflict-free A fragments)
 constexpr int kUcMO = 32;                            // out channels per CTA
-constexpr int kUcXFloats = kUcKC * kUcXS, kUcWFloats = 8 * kUcMO * kUcWS;
+constexpr int kUcFrag = 256;                         // words of one A fragment in lane order: 32 lanes x {4 hi words, 4 bf16 pairs}
+constexpr int kUcXFloats = kUcKC * kUcXS, kUcWFloats = (kUcKC / 8) * 8 * 2 * kUcFrag;   // [k-step][product][m-tile] fragments
 constexpr int kUcStageFloats = kUcXFloats + kUcWFloats;
 
 __device__ __forceinline__ void hmma_t(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1)
@@ -89,7 +89,7 @@ __device__ __forceinline__ void make_b(float v0, float v1, UFragB &f)
 
 struct UpconvArgs {
     const float *x;          // [B][Cin][h][w]
-    const float *wf;         // folded weights [2 a][2 b][2 dy][2 dx][Cout][Cin]
+    const uint4 *wfrag;      // folded weights as A fragments (upconv_fold_frag_kernel)
     float *y;                // [B][Cout][2h][2w]
     int B, Cin, Cout, h, w, tiles_x, tiles_y;
 };
@@ -120,6 +120,39 @@ __global__ void upconv_fold_kernel(const float *__restrict__ w, float *__restric
                 }
 }
 
+// The forward's A operand, ready to use: the folded weights split (hi words, bf16 pairs of the remainders and of the hi
+// parts) and laid out as the MMA fragments the lanes load, [a][out-channel block of 32][k-step of 8 c][product (b,dy,dx)]
+// [m-tile][lane][8 words] -- a stage's chunk is one contiguous 128-bit-copyable run, a fragment two 128-bit loads, and no
+// warp splits a weight again (the four warps of a CTA used to split the same fragments four times).
+__global__ void upconv_fold_frag_kernel(const float *__restrict__ w, uint4 *__restrict__ wfrag, int cout, int cin)
+{
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long total = (long long)2 * (cout / 32) * (cin / 8) * 8 * 2 * 32;
+    if (idx >= total) return;
+    const int lane = (int)(idx & 31), mt = (int)((idx >> 5) & 1), p = (int)((idx >> 6) & 7);
+    long long r = idx >> 9;
+    const int ks = (int)(r % (cin / 8));
+    r /= (cin / 8);
+    const int ob = (int)(r % (cout / 32)), a = (int)(r / (cout / 32));
+    const int b = p >> 2, dy = (p >> 1) & 1, dx = p & 1, g = lane >> 2, t = lane & 3;
+    const int y0 = a == 0 ? (dy == 0 ? 0 : 1) : (dy == 0 ? 0 : 2), y1 = a == 0 ? (dy == 0 ? 0 : 2) : (dy == 0 ? 1 : 2);
+    const int x0 = b == 0 ? (dx == 0 ? 0 : 1) : (dx == 0 ? 0 : 2), x1 = b == 0 ? (dx == 0 ? 0 : 2) : (dx == 0 ? 1 : 2);
+    float v[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {                                    // (row g, k t), (row g+8, k t), (row g, k t+4), (row g+8, k t+4)
+        const int o = 32 * ob + 16 * mt + g + 8 * (q & 1), c = 8 * ks + t + 4 * (q >> 1);
+        const float *src = w + ((size_t)o * cin + c) * 9;
+        float sum = 0.f;
+        for (int ky = y0; ky <= y1; ++ky)
+            for (int kx = x0; kx <= x1; ++kx) sum += __ldg(src + ky * 3 + kx);
+        v[q] = sum;
+    }
+    UFragA f;
+    make_a(v[0], v[1], v[2], v[3], f);
+    wfrag[2 * idx] = make_uint4(f.h[0], f.h[1], f.h[2], f.h[3]);
+    wfrag[2 * idx + 1] = make_uint4(f.s[0], f.s[1], f.s[2], f.s[3]);
+}
+
 __global__ void __launch_bounds__(128, BTS_UC_DRAIN ? 2 : 3) upconv_fwd_kernel(const __grid_constant__ UpconvArgs ua)
 {
     extern __shared__ __align__(16) float smem[];
@@ -133,7 +166,8 @@ __global__ void __launch_bounds__(128, BTS_UC_DRAIN ? 2 : 3) upconv_fwd_kernel(c
     const int i0 = ty * kUcTH, j0 = tx * kUcTW;
     const int h = ua.h, w = ua.w, Cin = ua.Cin, Cout = ua.Cout;
     const float *xb = ua.x + (size_t)b_img * Cin * h * w;
-    const float *wfa = ua.wf + (size_t)a * 8 * Cout * Cin;           // the eight (b, dy, dx) matrices of this row phase
+    // fragments of row phase a, out-channel block blockIdx.y: [k-step][8 products][2 m-tiles][32 lanes][8 words]
+    const uint4 *wchunk = ua.wfrag + ((size_t)a * (Cout / kUcMO) + blockIdx.y) * (size_t)(Cin / 8) * (8 * 2 * kUcFrag / 4);
 
     auto load_stage = [&](int kc, int buf) {
         float *xs = smem + buf * kUcStageFloats, *ws = xs + kUcXFloats;
@@ -146,12 +180,10 @@ __global__ void __launch_bounds__(128, BTS_UC_DRAIN ? 2 : 3) upconv_fwd_kernel(c
             const float *src = xb + ((size_t)(kc * kUcKC + c) * h + (ok ? sr : 0)) * w + (ok ? sc : 0);
             cp_async4(smem_u32(xs + c * kUcXS + r * kUcXC + col), src, ok);
         }
-        // weight chunk: [8 products][32 out channels][16 input channels], 16 bytes per copy
-        for (int idx = tid; idx < 8 * kUcMO * (kUcKC / 4); idx += 128) {
-            const int p = idx / (kUcMO * (kUcKC / 4)), rem = idx - p * (kUcMO * (kUcKC / 4));
-            const int o = rem / (kUcKC / 4), q = rem - o * (kUcKC / 4);
-            const float *src = wfa + ((size_t)p * Cout + o0 + o) * Cin + kc * kUcKC + 4 * q;
-            cp_async16(smem_u32(ws + (p * kUcMO + o) * kUcWS + 4 * q), src, true);
+        // weight chunk: the stage's 2 k-steps x 8 products x 2 m-tiles of ready fragments, one contiguous run
+        {
+            const uint4 *src = wchunk + (size_t)kc * (kUcWFloats / 4);
+            for (int idx = tid; idx < kUcWFloats / 4; idx += 128) cp_async16(smem_u32(ws + 4 * idx), src + idx, true);
         }
         cp_async_commit();
     };
@@ -191,33 +223,41 @@ __global__ void __launch_bounds__(128, BTS_UC_DRAIN ? 2 : 3) upconv_fwd_kernel(c
         const float *xs = smem + buf * kUcStageFloats, *ws = xs + kUcXFloats;
 #pragma unroll
         for (int ks = 0; ks < kUcKC / 8; ++ks) {
+            // six distinct windows of the halo tile: tap row dy x column shift sh = b + dx; each feeds the products (b, dx)
+            // with b + dx = sh (one, two, one of them)
 #pragma unroll
-            for (int p = 0; p < 8; ++p) {                            // product p = (b, dy, dx)
-                const int b = p >> 2, dy = (p >> 1) & 1, dx = p & 1;
-                UFragA fa[2];
+            for (int dy = 0; dy < 2; ++dy)
 #pragma unroll
-                for (int mt = 0; mt < 2; ++mt) {
-                    const float *q = ws + (p * kUcMO + 16 * mt + g) * kUcWS + 8 * ks + t;
-                    make_a(q[0], q[8 * kUcWS], q[4], q[8 * kUcWS + 4], fa[mt]);
+                for (int sh = 0; sh < 3; ++sh) {
+                    UFragB fb[4];
+#pragma unroll
+                    for (int n = 0; n < 4; ++n) {                    // n-tile: row 2 warp + n/2 of the tile, columns 8 (n%2) ..+7
+                        const float *q = xs + (8 * ks + t) * kUcXS + (2 * warp + (n >> 1) + dy) * kUcXC + 8 * (n & 1) + sh + g;
+                        make_b(q[0], q[4 * kUcXS], fb[n]);
+                    }
+#pragma unroll
+                    for (int b = 0; b < 2; ++b) {
+                        const int dx = sh - b;
+                        if (dx < 0 || dx > 1) continue;
+                        const int p = b * 4 + dy * 2 + dx;
+                        UFragA fa[2];
+#pragma unroll
+                        for (int mt = 0; mt < 2; ++mt) {
+                            const uint4 *q = reinterpret_cast<const uint4 *>(ws + ((ks * 8 + p) * 2 + mt) * kUcFrag) + 2 * lane;
+                            const uint4 vh = q[0], vs = q[1];
+                            fa[mt].h[0] = vh.x; fa[mt].h[1] = vh.y; fa[mt].h[2] = vh.z; fa[mt].h[3] = vh.w;
+                            fa[mt].s[0] = vs.x; fa[mt].s[1] = vs.y; fa[mt].s[2] = vs.z; fa[mt].s[3] = vs.w;
+                        }
+#pragma unroll
+                        for (int n = 0; n < 4; ++n)
+#pragma unroll
+                            for (int mt = 0; mt < 2; ++mt) hmma_b(acc[mt][n][b], fa[mt].s, fb[n].s0, fb[n].s1);
+#pragma unroll
+                        for (int n = 0; n < 4; ++n)
+#pragma unroll
+                            for (int mt = 0; mt < 2; ++mt) hmma_t(acc[mt][n][b], fa[mt].h, fb[n].h0, fb[n].h1);
+                    }
                 }
-#pragma unroll
-                for (int n = 0; n < 4; ++n) {                        // n-tile: row 2 warp + n/2 of the tile, columns 8 (n%2) ..+7
-                    const float *q = xs + (8 * ks + t) * kUcXS + (2 * warp + (n >> 1) + dy) * kUcXC + 8 * (n & 1) + b + dx + g;
-                    UFragB fb;
-                    make_b(q[0], q[4 * kUcXS], fb);
-#if BTS_UC_EXACT
-#pragma unroll
-                    for (int mt = 0; mt < 2; ++mt) hmma_t(acc[mt][n][b], fa[mt].l, fb.h0, fb.h1);
-#pragma unroll
-                    for (int mt = 0; mt < 2; ++mt) hmma_t(acc[mt][n][b], fa[mt].h, fb.l0, fb.l1);
-#else
-#pragma unroll
-                    for (int mt = 0; mt < 2; ++mt) hmma_b(acc[mt][n][b], fa[mt].s, fb.s0, fb.s1);
-#endif
-#pragma unroll
-                    for (int mt = 0; mt < 2; ++mt) hmma_t(acc[mt][n][b], fa[mt].h, fb.h0, fb.h1);
-                }
-            }
         }
         __syncthreads();
 #if BTS_UC_DRAIN
@@ -578,17 +618,18 @@ __global__ void upconv_unfold_kernel(const float *__restrict__ gwf, float *__res
 
 }  // namespace
 
-size_t upconv_workspace_bytes(int cin, int cout) { return (size_t)16 * cin * cout * sizeof(float); }
+size_t upconv_workspace_bytes(int cin, int cout) { return (size_t)16 * cin * cout * 2 * sizeof(float); }   // hi word + bf16 halves per weight
 
 bool upconv_supported(int cin, int cout) { return cin > 0 && cout > 0 && cin % kUcKC == 0 && cout % kUcMO == 0; }
 
 int launch_upconv_fwd(const float *x, const float *w, float *y, int B, int cin, int cout, int h, int wd, void *ws, cudaStream_t s)
 {
-    float *wf = static_cast<float *>(ws);
-    upconv_fold_kernel<<<(cin * cout + 255) / 256, 256, 0, s>>>(w, wf, cout, cin);
-    if (int e = check_launch("upconv_fold")) return e;
+    uint4 *wfrag = static_cast<uint4 *>(ws);
+    const long long nfrag = (long long)2 * (cout / 32) * (cin / 8) * 8 * 2 * 32;
+    upconv_fold_frag_kernel<<<(unsigned)((nfrag + 255) / 256), 256, 0, s>>>(w, wfrag, cout, cin);
+    if (int e = check_launch("upconv_fold_frag")) return e;
     UpconvArgs ua;
-    ua.x = x; ua.wf = wf; ua.y = y;
+    ua.x = x; ua.wfrag = wfrag; ua.y = y;
     ua.B = B; ua.Cin = cin; ua.Cout = cout; ua.h = h; ua.w = wd;
     ua.tiles_x = (wd + kUcTW - 1) / kUcTW;
     ua.tiles_y = (h + kUcTH - 1) / kUcTH;

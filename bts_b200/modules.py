@@ -141,12 +141,21 @@ def fused_stage(reduc, lpg, net, return_plane_eq=False, scaled=False, downsample
 _STAGES = (("reduc8x8", "lpg8x8"), ("reduc4x4", "lpg4x4"), ("reduc2x2", "lpg2x2"))
 
 
-def graft(model):
+def graft(model, upconvs=False):
     """Replace every reference reduction_1x1 / local_planar_guidance inside `model` (a reference `bts`
     decoder, BtsModel, or anything containing them) by the B200 modules, keeping the weights.
-    Matching is by class NAME so the reference module need not be importable here."""
+    Matching is by class NAME so the reference module need not be importable here.
+    upconvs=True also swaps the reference's `upconv` blocks (bts.py:83-94) for the folded kernels: fp32-accurate
+    (1.5e-6 of the fp64 oracle) and 1.6x the reference's sequence on cuDNN in fp32, but slower than cuDNN with PyTorch's
+    TF32 default (which is 3e-4 off) -- hence opt-in."""
     for name, child in list(model.named_children()):
         cls = type(child).__name__
+        if upconvs and cls == "upconv" and not isinstance(child, upconv):
+            new = upconv(child.conv.in_channels, child.conv.out_channels, child.ratio)
+            new.load_state_dict(child.state_dict())
+            new.to(child.conv.weight.device)
+            setattr(model, name, new)
+            continue
         if cls == "reduction_1x1" and not isinstance(child, reduction_1x1):
             convs = [m for m in child.modules() if isinstance(m, nn.Conv2d)]
             new = reduction_1x1(convs[0].in_channels, convs[0].out_channels if len(convs) > 1 else 4,
@@ -157,5 +166,5 @@ def graft(model):
         elif cls == "local_planar_guidance" and not isinstance(child, local_planar_guidance):
             setattr(model, name, local_planar_guidance(int(child.upratio)))
         else:
-            graft(child)
+            graft(child, upconvs)
     return model

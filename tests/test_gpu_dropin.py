@@ -65,10 +65,10 @@ class local_planar_guidance(nn.Module):      # noqa: N801 (pytorch/bts.py:138)
 class upconv(nn.Module):                     # noqa: N801 (pytorch/bts.py:83-94)
     def __init__(self, cin, cout):
         super().__init__()
-        self.conv, self.elu = nn.Conv2d(cin, cout, 3, 1, 1, bias=False), nn.ELU()
+        self.conv, self.elu, self.ratio = nn.Conv2d(cin, cout, 3, 1, 1, bias=False), nn.ELU(), 2
 
     def forward(self, x):
-        return self.elu(self.conv(F.interpolate(x, scale_factor=2, mode="nearest")))
+        return self.elu(self.conv(F.interpolate(x, scale_factor=self.ratio, mode="nearest")))
 
 
 class DecoderTail(nn.Module):
@@ -120,7 +120,8 @@ def _run(model, inputs, gouts, dtype):
     return [o.detach().double().cpu().numpy() for o in outs], [g.double().cpu().numpy() for g in grads]
 
 
-def test_graft_inside_the_decoder_call_sequence():
+@pytest.mark.parametrize("upconvs", [False, True], ids=["lpg-path", "lpg-path+upconvs"])
+def test_graft_inside_the_decoder_call_sequence(upconvs):
     import bts_b200
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
@@ -138,8 +139,10 @@ def test_graft_inside_the_decoder_call_sequence():
 
     ref64 = _run(copy.deepcopy(model), inputs, gouts, torch.float64)
     ref32 = _run(copy.deepcopy(model), inputs, gouts, torch.float32)
-    grafted = bts_b200.graft(copy.deepcopy(model))
+    grafted = bts_b200.graft(copy.deepcopy(model), upconvs=upconvs)
     assert list(grafted.state_dict().keys()) == keys_before
+    for name in ("upconv3", "upconv2", "upconv1"):                 # (opt-in: SURVEY.md 8(f)-3)
+        assert isinstance(getattr(grafted, name), bts_b200.upconv) == upconvs
     for name in ("reduc8x8", "reduc4x4", "reduc2x2", "reduc1x1"):
         assert isinstance(getattr(grafted, name), bts_b200.reduction_1x1)
         for a, b in zip(getattr(grafted, name).parameters(), getattr(model, name).parameters()):
