@@ -23,6 +23,7 @@
 // adds truncated addends (like tcgen05), so weight-gradient sums leave the tensor core after every 32 pixels (12 steps)
 // and continue in fp32 registers with round-to-nearest adds.
 #include <cstdlib>
+#include <type_traits>
 
 #include "chain_tc.cuh"
 
@@ -186,6 +187,40 @@ __device__ __forceinline__ float4 with_lo(float b0, float b1)
     return make_float4(__uint_as_float(f.h0), __uint_as_float(f.h1), __uint_as_float(f.s0), __uint_as_float(f.s1));
 }
 
+// ---- tile / tensor access for fp32 and for the bf16 twin (BF: x, grad, grad_x, out are bf16 tensors; a tile row is 32
+// two-byte pixels at a stride of kXS elements, both fragment patterns stay bank-conflict-free). A bf16 value is exact in
+// tf32: its remainder is zero (the remainder halves of the bf16 operands are zero registers) and its bf16 pair is a
+// byte permute of the raw halves.
+template <bool BF>
+__device__ __forceinline__ void x_frag_a(const void *tile, int ch, int px, FragA &f)   // rows px, px+8; k = ch, ch+4
+{
+    if constexpr (!BF) {
+        const float *q = static_cast<const float *>(tile) + ch * kXS + px;
+        make_a(q[0], q[8], q[4 * kXS], q[4 * kXS + 8], f);
+    } else {
+        const unsigned short *q = static_cast<const unsigned short *>(tile) + ch * kXS + px;
+        f.h[0] = (uint32_t)q[0] << 16; f.h[1] = (uint32_t)q[8] << 16; f.h[2] = (uint32_t)q[4 * kXS] << 16; f.h[3] = (uint32_t)q[4 * kXS + 8] << 16;
+        f.l[0] = f.l[1] = f.l[2] = f.l[3] = 0u;
+        f.s[0] = f.s[1] = 0u;
+        f.s[2] = __byte_perm(f.h[0], f.h[2], 0x7632);
+        f.s[3] = __byte_perm(f.h[1], f.h[3], 0x7632);
+    }
+}
+template <bool BF>
+__device__ __forceinline__ void x_frag_b(const void *tile, int ch, int px, FragB &f)   // k = px, px+1 (a pair); n = ch
+{
+    if constexpr (!BF) {
+        const float2 xv = *reinterpret_cast<const float2 *>(static_cast<const float *>(tile) + ch * kXS + px);
+        make_b(xv.x, xv.y, f);
+    } else {
+        const uint32_t w = *reinterpret_cast<const uint32_t *>(static_cast<const unsigned short *>(tile) + ch * kXS + px);
+        f.h0 = w << 16; f.h1 = w & 0xFFFF0000u;
+        f.l0 = f.l1 = 0u;
+        f.s0 = w;
+        f.s1 = 0u;
+    }
+}
+
 template <bool EXACT, bool ZERO>
 __device__ __forceinline__ void mma_small(float (&d)[4], const FragA &a, const FragB &b)
 {
@@ -207,7 +242,7 @@ __device__ __forceinline__ void mma_small(float (&d)[4], const FragA &a, const F
 #define MMA_F_SMALL mma2_small
 #endif
 
-template <int WARPS, int NSTAGE, int MINB>
+template <int WARPS, int NSTAGE, int MINB, bool BF>
 __global__ void __launch_bounds__(WARPS * 32, MINB) head_bwd_mma_kernel(const __grid_constant__ MmaArgs ma)
 {
     const TcArgs &a = ma.a;
@@ -251,32 +286,37 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_bwd_mma_kernel(const __
             ++s.b;
         }
     };
-    // the tile of the group at `q` (this lane's pixel quad) -> ring slot st: pixels 4(lane % 8).. of channels lane/8 + 4i
-    const size_t hw4 = (size_t)hw * 4;
+    // the tile of the group at `q` (this lane's pixel group) -> ring slot st. fp32: pixels 4 (lane % 8).. of channels
+    // lane / 8 + 4 i; bf16: pixels 8 (lane % 4).. of channels lane / 4 + 8 i (16 bytes per copy either way)
+    using TIO = std::conditional_t<BF, unsigned short, float>;
+    constexpr int PXG = BF ? 8 : 4, NCP = BF ? 4 : 8, LPR = 32 / PXG;      // pixels per copy, copies per lane, lanes per row
+    const TIO *const xin = reinterpret_cast<const TIO *>(a.x);
+    const size_t hwrow = (size_t)hw * (32 / NCP);                          // elements between this lane's successive rows
     auto prefetch = [&](const Pos &q, int st) {
         const bool ok = q.gp < npx;
-        const float *src = a.x + ((size_t)(ok ? q.b : 0u) * 32 + (lane >> 3)) * hw + (ok ? q.p : 0u);
-        const uint32_t dst = smem_u32(mytiles + st * kTileFloats + (lane >> 3) * kXS + 4 * (lane & 7));
+        const TIO *src = xin + ((size_t)(ok ? q.b : 0u) * 32 + (lane / LPR)) * hw + (ok ? q.p : 0u);
+        const uint32_t dst = smem_u32(reinterpret_cast<TIO *>(mytiles + st * kTileFloats) + (lane / LPR) * kXS + PXG * (lane % LPR));
 #pragma unroll
-        for (int i = 0; i < 8; ++i) cp_async16(dst + i * 4 * kXS * 4, src + i * hw4, ok);
+        for (int i = 0; i < NCP; ++i) cp_async16(dst + i * (32 / NCP) * kXS * (int)sizeof(TIO), src + i * hwrow, ok);
         cp_async_commit();
     };
     // upstream gradient of pixels 8q + g of the group that starts at gp0 (0 beyond the end: such pixels add nothing anywhere)
+    const TIO *const gin = reinterpret_cast<const TIO *>(a.grad);
     auto load_grad = [&](unsigned gp0, float (&gv)[4]) {
         if (gp0 + kGP <= npx) {
-            const float *gsrc = a.grad + gp0 + g;
+            const TIO *gsrc = gin + gp0 + g;
 #pragma unroll
-            for (int q = 0; q < 4; ++q) gv[q] = __ldg(gsrc + 8 * q);
+            for (int q = 0; q < 4; ++q) gv[q] = io_load<TIO>(gsrc + 8 * q);
         } else {
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 const unsigned gp = gp0 + 8u * q + g;
-                gv[q] = (gp0 < npx && gp < npx) ? __ldg(a.grad + gp) : 0.f;
+                gv[q] = (gp0 < npx && gp < npx) ? io_load<TIO>(gin + gp) : 0.f;
             }
         }
     };
 
-    Pos quad = pos_at((unsigned)first * kGP + 4u * (lane & 7));  // this lane's quad of the next group to fetch
+    Pos quad = pos_at((unsigned)first * kGP + (unsigned)(PXG * (lane % LPR)));  // this lane's quad of the next group to fetch
     Pos base = pos_at((unsigned)first * kGP);                     // first pixel of the current group
 #pragma unroll
     for (int k = 0; k < NSTAGE - 1; ++k) {
@@ -334,7 +374,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_bwd_mma_kernel(const __
 #pragma unroll
         for (int q = 0; q < 4; ++q) gc[q] = gn[q];
         load_grad(base.gp + step, gn);
-        const float *xt = mytiles + slot * kTileFloats;
+        const void *xt = mytiles + slot * kTileFloats;
         if (++slot == NSTAGE) slot = 0;
 
         // ---- layer 0 (px on M): pre1[16 px x 16] per m-tile = x[16 px x 32] * W0^T; a1 = ELU
@@ -343,10 +383,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_bwd_mma_kernel(const __
         for (int s = 0; s < 4; ++s) {
             FragA fa[2];
 #pragma unroll
-            for (int mt = 0; mt < 2; ++mt) {
-                const float *q = xt + (8 * s + t) * kXS + 16 * mt + g;
-                make_a(q[0], q[8], q[4 * kXS], q[4 * kXS + 8], fa[mt]);
-            }
+            for (int mt = 0; mt < 2; ++mt) x_frag_a<BF>(xt, 8 * s + t, 16 * mt + g, fa[mt]);
             FragB fb[2];
 #pragma unroll
             for (int j = 0; j < 2; ++j) fb[j] = MMA_F_FRAG(f0b[(s * 2 + j) * 32 + lane]);
@@ -475,7 +512,8 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_bwd_mma_kernel(const __
         if (a.grad_x != nullptr) {
             // whole group inside one image and inside the tensor: four row pointers, immediate offsets
             const bool fast = base.gp + kGP <= npx && base.p + kGP <= hw;
-            float *row0 = a.grad_x + ((size_t)base.b * 32 + g) * hw + base.p + 2 * t;
+            TIO *const gxo = reinterpret_cast<TIO *>(a.grad_x);
+            TIO *row0 = gxo + ((size_t)base.b * 32 + g) * hw + base.p + 2 * t;
 #pragma unroll
             for (int i = 0; i < 2; ++i) {
                 FragA fw[2];
@@ -496,11 +534,11 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_bwd_mma_kernel(const __
 #pragma unroll
                 for (int n = 0; n < 4; ++n) hmma(acc[n], fw[1].h, fd[n >> 1][1][n & 1].h0, fd[n >> 1][1][n & 1].h1);
                 if (fast) {
-                    float *ra = row0 + (size_t)(16 * i) * hw, *rb = ra + (size_t)8 * hw;
+                    TIO *ra = row0 + (size_t)(16 * i) * hw, *rb = ra + (size_t)8 * hw;
 #pragma unroll
                     for (int n = 0; n < 4; ++n) {
-                        *reinterpret_cast<float2 *>(ra + 8 * n) = make_float2(acc[n][0], acc[n][1]);
-                        *reinterpret_cast<float2 *>(rb + 8 * n) = make_float2(acc[n][2], acc[n][3]);
+                        io_store2(ra + 8 * n, acc[n][0], acc[n][1]);
+                        io_store2(rb + 8 * n, acc[n][2], acc[n][3]);
                     }
                 } else {
 #pragma unroll 1
@@ -512,14 +550,14 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_bwd_mma_kernel(const __
                                 b += p / hw;
                                 p %= hw;
                             }
-                            float *dst = a.grad_x + ((size_t)b * 32 + 16 * i + g) * hw + p;
+                            TIO *dst = gxo + ((size_t)b * 32 + 16 * i + g) * hw + p;
                             // (acc[n] with a run-time n: select instead of indexing, the array stays in registers)
                             float v0 = acc[0][0], v1 = acc[0][1], v2 = acc[0][2], v3 = acc[0][3];
 #pragma unroll
                             for (int m = 1; m < 4; ++m)
                                 if (n == m) { v0 = acc[m][0]; v1 = acc[m][1]; v2 = acc[m][2]; v3 = acc[m][3]; }
-                            *reinterpret_cast<float2 *>(dst) = make_float2(v0, v1);
-                            *reinterpret_cast<float2 *>(dst + (size_t)8 * hw) = make_float2(v2, v3);
+                            io_store2(dst, v0, v1);
+                            io_store2(dst + (size_t)8 * hw, v2, v3);
                         }
                     }
                 }
@@ -541,10 +579,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_bwd_mma_kernel(const __
                 fa.s[2] = movm(fd[mt][0][r].s0);
                 fa.s[3] = movm(fd[mt][1][r].s0);
 #pragma unroll
-                for (int n = 0; n < 4; ++n) {
-                    const float2 xv = *reinterpret_cast<const float2 *>(xt + (8 * n + g) * kXS + 16 * mt + 8 * r + 2 * t);
-                    make_b(xv.x, xv.y, fb[n]);
-                }
+                for (int n = 0; n < 4; ++n) x_frag_b<BF>(xt, 8 * n + g, 16 * mt + 8 * r + 2 * t, fb[n]);
 #pragma unroll
                 for (int n = 0; n < 4; ++n) {
                     if (mt == 0 && r == 0) mma2_small<true>(g0[n], fa, fb[n]);
@@ -596,7 +631,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_bwd_mma_kernel(const __
 // (~40 MMAs and ~400 other instructions per 32 pixels), 16 warps x one tile ahead. EXACT: plain three-instruction 3xTF32
 // products (output within 8e-7 of the fp64 oracle's peak instead of 3.6e-6, 72 instead of 61 us at nyu_b8: the kernel is
 // latency-bound on its dependent MMA chain, not idle under the copies); BTS_HEAD_EXACT=1 selects it.
-template <int WARPS, int NSTAGE, int MINB, bool EXACT>
+template <int WARPS, int NSTAGE, int MINB, bool EXACT, bool BF>
 __global__ void __launch_bounds__(WARPS * 32, MINB) head_fwd_mma_kernel(const __grid_constant__ MmaArgs ma)
 {
     const TcArgs &a = ma.a;
@@ -616,14 +651,17 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_fwd_mma_kernel(const __
 
     const unsigned step = (unsigned)stride * kGP;
     const unsigned dq = step / hw, dr = step - dq * hw;
-    unsigned q_gp = (unsigned)first * kGP + 4u * (lane & 7), q_b = q_gp / hw, q_p = q_gp - q_b * hw;
-    const size_t hw4 = (size_t)hw * 4;
+    using TIO = std::conditional_t<BF, unsigned short, float>;
+    constexpr int PXG = BF ? 8 : 4, NCP = BF ? 4 : 8, LPR = 32 / PXG;      // pixels per copy, copies per lane, lanes per row
+    unsigned q_gp = (unsigned)first * kGP + (unsigned)(PXG * (lane % LPR)), q_b = q_gp / hw, q_p = q_gp - q_b * hw;
+    const TIO *const xin = reinterpret_cast<const TIO *>(a.x);
+    const size_t hwrow = (size_t)hw * (32 / NCP);
     auto prefetch = [&](int st) {
         const bool ok = q_gp < npx;
-        const float *src = a.x + ((size_t)(ok ? q_b : 0u) * 32 + (lane >> 3)) * hw + (ok ? q_p : 0u);
-        const uint32_t dst = smem_u32(mytiles + st * kTileFloats + (lane >> 3) * kXS + 4 * (lane & 7));
+        const TIO *src = xin + ((size_t)(ok ? q_b : 0u) * 32 + (lane / LPR)) * hw + (ok ? q_p : 0u);
+        const uint32_t dst = smem_u32(reinterpret_cast<TIO *>(mytiles + st * kTileFloats) + (lane / LPR) * kXS + PXG * (lane % LPR));
 #pragma unroll
-        for (int i = 0; i < 8; ++i) cp_async16(dst + i * 4 * kXS * 4, src + i * hw4, ok);
+        for (int i = 0; i < NCP; ++i) cp_async16(dst + i * (32 / NCP) * kXS * (int)sizeof(TIO), src + i * hwrow, ok);
         cp_async_commit();
         q_gp += step;
         q_b += dq;
@@ -657,7 +695,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_fwd_mma_kernel(const __
             if (pst >= NSTAGE) pst -= NSTAGE;
             prefetch(pst);
         }
-        const float *xt = mytiles + slot * kTileFloats;
+        const void *xt = mytiles + slot * kTileFloats;
         if (++slot == NSTAGE) slot = 0;
 
         float a1[2][2][4];
@@ -665,10 +703,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_fwd_mma_kernel(const __
         for (int s = 0; s < 4; ++s) {
             FragA fa[2];
 #pragma unroll
-            for (int mt = 0; mt < 2; ++mt) {
-                const float *q = xt + (8 * s + t) * kXS + 16 * mt + g;
-                make_a(q[0], q[8], q[4 * kXS], q[4 * kXS + 8], fa[mt]);
-            }
+            for (int mt = 0; mt < 2; ++mt) x_frag_a<BF>(xt, 8 * s + t, 16 * mt + g, fa[mt]);
             FragB fb[2];
 #pragma unroll
             for (int j = 0; j < 2; ++j) fb[j] = EXACT ? frag_b_exact(f0b[(s * 2 + j) * 32 + lane]) : frag_b(f0b[(s * 2 + j) * 32 + lane]);
@@ -713,17 +748,17 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) head_fwd_mma_kernel(const __
             }
         const float zm = t == 0 ? z[0] : (t == 1 ? z[1] : (t == 2 ? z[2] : z[3]));
         const unsigned gp = (unsigned)G * kGP + 8u * t + g;
-        if (gp < npx) a.out[gp] = sigmoidf(zm);
+        if (gp < npx) io_store(reinterpret_cast<TIO *>(a.out) + gp, sigmoidf(zm));
     }
     cp_async_wait<0>();
 }
 
-template <int WARPS, int NSTAGE, int MINB>
-int launch_cfg(const MmaArgs &ma, int sms, cudaStream_t s)
+template <int WARPS, int NSTAGE, int MINB, bool BF>
+int launch_cfg2(const MmaArgs &ma, int sms, cudaStream_t s)
 {
     constexpr size_t smem_bytes = sizeof(float4) * (4 * 2 * 32 + 2 * 32 + 2 * 32 + 2 * 2 * 32 * 2) + sizeof(float) * kSumFloats +
                                   sizeof(float) * (size_t)WARPS * NSTAGE * kTileFloats;
-    auto kern = head_bwd_mma_kernel<WARPS, NSTAGE, MINB>;
+    auto kern = head_bwd_mma_kernel<WARPS, NSTAGE, MINB, BF>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     const long long ngroups = (ma.a.npx + kGP - 1) / kGP;
@@ -732,12 +767,17 @@ int launch_cfg(const MmaArgs &ma, int sms, cudaStream_t s)
     kern<<<(unsigned)grid, WARPS * 32, smem_bytes, s>>>(ma);
     return check_launch("head_bwd_mma");
 }
+template <int WARPS, int NSTAGE, int MINB>
+int launch_cfg(const MmaArgs &ma, int sms, cudaStream_t s)
+{
+    return ma.a.bf16_io ? launch_cfg2<WARPS, NSTAGE, MINB, true>(ma, sms, s) : launch_cfg2<WARPS, NSTAGE, MINB, false>(ma, sms, s);
+}
 
-template <int WARPS, int NSTAGE, int MINB, bool EXACT = false>
-int launch_fwd_cfg(const MmaArgs &ma, int sms, cudaStream_t s)
+template <int WARPS, int NSTAGE, int MINB, bool EXACT, bool BF>
+int launch_fwd_cfg2(const MmaArgs &ma, int sms, cudaStream_t s)
 {
     constexpr size_t smem_bytes = sizeof(float4) * (4 * 2 * 32 + 2 * 32) + sizeof(float) * (size_t)WARPS * NSTAGE * kTileFloats;
-    auto kern = head_fwd_mma_kernel<WARPS, NSTAGE, MINB, EXACT>;
+    auto kern = head_fwd_mma_kernel<WARPS, NSTAGE, MINB, EXACT, BF>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     const long long ngroups = (ma.a.npx + kGP - 1) / kGP;
@@ -745,6 +785,11 @@ int launch_fwd_cfg(const MmaArgs &ma, int sms, cudaStream_t s)
     if (grid > (long long)sms * MINB) grid = (long long)sms * MINB;
     kern<<<(unsigned)grid, WARPS * 32, smem_bytes, s>>>(ma);
     return check_launch("head_fwd_mma");
+}
+template <int WARPS, int NSTAGE, int MINB, bool EXACT = false>
+int launch_fwd_cfg(const MmaArgs &ma, int sms, cudaStream_t s)
+{
+    return ma.a.bf16_io ? launch_fwd_cfg2<WARPS, NSTAGE, MINB, EXACT, true>(ma, sms, s) : launch_fwd_cfg2<WARPS, NSTAGE, MINB, EXACT, false>(ma, sms, s);
 }
 
 }  // namespace
@@ -754,7 +799,7 @@ int launch_fwd_cfg(const MmaArgs &ma, int sms, cudaStream_t s)
 bool head_fwd_mma_wanted(const ChainParams &cp, const TcArgs &a)
 {
     static const int env = getenv("BTS_HEAD_MMA") ? atoi(getenv("BTS_HEAD_MMA")) : 1;
-    if (env == 0 || a.bf16_io || !a.x_vec16 || a.depth != nullptr || a.stash_act != nullptr || a.out == nullptr) return false;
+    if (env == 0 || !a.x_vec16 || a.depth != nullptr || a.stash_act != nullptr || a.out == nullptr) return false;
     return cfg_matches<Cfg32_16>(cp) && cp.is_final && cp.dims[3] == 1;
 }
 
@@ -783,9 +828,9 @@ bool head_bwd_mma_wanted(const ChainParams &cp, const TcArgs &a, int mode)
     static const int env = getenv("BTS_HEAD_MMA") ? atoi(getenv("BTS_HEAD_MMA")) : 1;
     static const bool deterministic = getenv("BTS_DETERMINISTIC") != nullptr && atoi(getenv("BTS_DETERMINISTIC")) != 0;
     static const bool nwg_forced = getenv("BTS_HEAD_NWG") != nullptr;    // a tcgen05 variant was asked for by name
-    if (env == 0 || deterministic || nwg_forced || mode != 0 || a.bf16_io || !a.x_vec16) return false;
+    if (env == 0 || deterministic || nwg_forced || mode != 0 || !a.x_vec16) return false;
     if (!cfg_matches<Cfg32_16>(cp) || !cp.is_final || cp.dims[3] != 1) return false;
-    if (a.grad_x != nullptr && (reinterpret_cast<uintptr_t>(a.grad_x) & 7u) != 0) return false;
+    if (a.grad_x != nullptr && (reinterpret_cast<uintptr_t>(a.grad_x) & (a.bf16_io ? 3u : 7u)) != 0) return false;
     return true;
 }
 
