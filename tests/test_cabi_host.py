@@ -47,6 +47,16 @@ def test_argument_validation_needs_no_gpu():
     d3 = _cabi.int_array([32, 16, 8, 3])
     assert lib.bts_reduc_lpg_bwd(16, 16, w, d3, 3, 10.0, 1, 2, 2, 2, 1e-3, None, None, None, 0, None) in (-3, 0)
     assert lib.bts_workspace_bytes(d3, 3, 0, 4, 4, 2) == 0
+    # upconv: channel counts the kernels do not serve, missing workspace, empty input
+    assert lib.bts_upconv_fwd(16, 16, 1, 24, 32, 4, 4, 16, 16, 1 << 20, None) == -2
+    assert b"cin" in lib.bts_last_error()
+    assert lib.bts_upconv_fwd(16, 16, 1, 32, 32, 4, 4, 16, None, 0, None) == -1
+    assert lib.bts_upconv_fwd(None, 16, 1, 32, 32, 4, 4, 16, 16, 1 << 20, None) == -1
+    assert lib.bts_upconv_fwd(None, None, 0, 32, 32, 4, 4, None, None, 0, None) == 0
+    assert lib.bts_upconv_workspace_bytes(64, 32) == 16 * 64 * 32 * 8 and lib.bts_upconv_workspace_bytes(0, 32) == 0
+    assert lib.bts_upconv_bwd(16, 16, 16, 16, 1, 48, 32, 4, 4, 16, 16, 16, 1 << 20, None) == -2   # backward: cin % 32
+    assert lib.bts_upconv_bwd(16, 16, 16, 16, 1, 32, 32, 4, 4, 16, 16, 16, 64, None) == -1       # workspace too small
+    assert lib.bts_upconv_bwd_workspace_bytes(2, 64, 32, 4, 6) == 4 * (32 * 64 * 32 + 4 * 2 * 32 * 4 * 6)
 
 
 @pytest.mark.parametrize("cfg", [(128, 128, False), (128, 64, False), (64, 32, False), (32, 16, True),

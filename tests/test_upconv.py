@@ -88,6 +88,25 @@ def test_upconv_kernel_vs_oracle_decoder_shapes(cin, cout, B, h, w):
 
 
 @pytest.mark.gpu
+def test_upconv_full_size_configs1():
+    """upconv2 of the decoder at BASELINE.json configs[1] (NYU 480x640, batch 8): [8,128,120,160] -> [8,64,240,320], forward
+    and backward against the fp64 oracle on the host (5 G multiply-adds per pass)."""
+    from bts_b200 import functional as Fn
+    gen = torch.Generator().manual_seed(11)
+    x = torch.randn(8, 128, 120, 160, generator=gen)
+    wt = torch.randn(64, 128, 3, 3, generator=gen) * (2.0 / (9 * 128)) ** 0.5
+    gy = torch.randn(8, 64, 240, 320, generator=gen)
+    ref_y, ref_gx, ref_gw = _oracle_grads(x, wt, gy, torch.float64)
+    xd, wd = x.cuda().requires_grad_(True), wt.cuda().requires_grad_(True)
+    y = Fn.upconv_forward(xd, wd)
+    y.backward(gy.cuda())
+    torch.cuda.synchronize()
+    assert max_rel_to_peak(y.detach().cpu().numpy(), ref_y.numpy()) <= 1e-5
+    assert max_rel_to_peak(xd.grad.cpu().numpy(), ref_gx.numpy()) <= 1e-5
+    assert max_rel_to_peak(wd.grad.cpu().numpy(), ref_gw.numpy()) <= 1e-5
+
+
+@pytest.mark.gpu
 def test_upconv_module_contract():
     import bts_b200
     from bts_b200 import functional as Fn
