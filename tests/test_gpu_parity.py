@@ -122,6 +122,7 @@ SEEDED = [  # (num_in, num_out, is_final, r, B, h, w, max_depth): sizes the C or
     (32, 16, True, 1, 5, 7, 12, 80.0),
     (32, 16, True, 1, 7, 3, 4, 10.0),
     (32, 16, True, 1, 1, 2, 2, 10.0),
+    (32, 16, True, 1, 2, 9, 7, 10.0),        # hw % 4 != 0: no 16-byte copies, the tcgen05 / generic head kernels
 ]
 
 
