@@ -8,7 +8,7 @@ Constructor and forward signatures, attribute names (`reduc`, `sigmoid`, `max_de
 `reduc.plane_params.weight`, `reduc.final.0.weight`) are the reference's (pytorch/bts.py:97-147,
 SURVEY.md 3.5), so `weights_init_xavier` (bts.py:34-38), checkpoints (bts_main.py:368,725-728), the
 optimizer grouping (bts_main.py:354-355) and DDP hooks keep working. The arithmetic runs in
-libbts_b200.so (hand-written sm_100a CUDA); there is no PyTorch or CPU fallback.
+libbts_b200.so (hand-written sm_100a CUDA); there is no PyTorch or CPU fallback for these two modules.
 
 `fused_stage(reduc, lpg, net)` evaluates reducNxN -> normalise/cat -> lpgNxN (bts.py:249-254) in one
 pass; `graft(decoder)` swaps the modules inside an existing reference `bts` decoder / BtsModel.
