@@ -197,8 +197,9 @@ def upconv_case(ref, name, cin, cout, B, h, w, seed):
         y = m(xd)
         y.backward(gy.to(dt))
         out[tag + "_y"] = y.detach().numpy()
-        out[tag + "_grad_x"] = xd.grad.numpy()
-        out[tag + "_grad_w"] = m.conv.weight.grad.numpy().copy()
+        if tag == "f64":                                         # the arbiter's gradients (the fp32 ones are not used by any test)
+            out[tag + "_grad_x"] = xd.grad.numpy()
+            out[tag + "_grad_w"] = m.conv.weight.grad.numpy().copy()
     meta = dict(kind="upconv", name=name, cin=cin, cout=cout, B=B, h=h, w=w, seed=seed, reference="pytorch/bts.py:83-94",
                 torch=torch.__version__)
     out["meta"] = json.dumps(meta)
