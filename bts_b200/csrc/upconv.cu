@@ -22,14 +22,24 @@
 namespace bts {
 namespace {
 
-constexpr int kUcTW = 16, kUcTH = 8;                 // low-res tile
 constexpr int kUcKC = 16;                            // input channels per stage
-constexpr int kUcXR = kUcTH + 1, kUcXC = kUcTW + 2;  // halo tile of one row phase: 9 x 18
-constexpr int kUcXS = 168;                           // floats per channel (162 -> 168 = 8 mod 32: conflict-free B fragments)
+// Low-res tile of a CTA: 128 pixels as 8 rows x 16 columns (WIDE) or 16 x 8 (TALL: small images whose width wastes less that
+// way, e.g. the 15 x 20 input of upconv5). A warp owns four runs of eight pixels along a row: rows 2w, 2w+1 x both column
+// halves (WIDE) or rows 4w .. 4w+3 (TALL).
+template <bool TALL>
+struct UcTile {
+    static constexpr int TW = TALL ? 8 : 16, TH = TALL ? 16 : 8;
+    static constexpr int XR = TH + 1, XC = TW + 2;   // halo tile: 9 x 18 | 17 x 10
+    static constexpr int XS = TALL ? 200 : 168;      // floats per channel, = 8 mod 32: conflict-free B fragments (k = channel)
+    static constexpr int WXS = TALL ? 196 : 164;     // same for the weight gradient, = 4 mod 32 (k = pixel)
+    static constexpr int XFloats = kUcKC * XS;
+    __device__ static constexpr int row(int warp, int n) { return TALL ? 4 * warp + n : 2 * warp + (n >> 1); }
+    __device__ static constexpr int colb(int n) { return TALL ? 0 : 8 * (n & 1); }
+};
 constexpr int kUcMO = 32;                            // out channels per CTA
 constexpr int kUcFrag = 256;                         // words of one A fragment in lane order: 32 lanes x {4 hi words, 4 bf16 pairs}
-constexpr int kUcXFloats = kUcKC * kUcXS, kUcWFloats = (kUcKC / 8) * 8 * 2 * kUcFrag;   // [k-step][product][m-tile] fragments
-constexpr int kUcStageFloats = kUcXFloats + kUcWFloats;
+constexpr int kUcWFloats = (kUcKC / 8) * 8 * 2 * kUcFrag;   // [k-step][product][m-tile] fragments
+template <bool TALL> constexpr int kUcStageFloats = UcTile<TALL>::XFloats + kUcWFloats;
 
 __device__ __forceinline__ void hmma_t(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1)
 {
@@ -153,8 +163,10 @@ __global__ void upconv_fold_frag_kernel(const float *__restrict__ w, uint4 *__re
     wfrag[2 * idx + 1] = make_uint4(f.s[0], f.s[1], f.s[2], f.s[3]);
 }
 
+template <bool TALL>
 __global__ void __launch_bounds__(128, BTS_UC_DRAIN ? 2 : 3) upconv_fwd_kernel(const __grid_constant__ UpconvArgs ua)
 {
+    using T = UcTile<TALL>;
     extern __shared__ __align__(16) float smem[];
     const int tid = threadIdx.x, lane = tid & 31, g = lane >> 2, t = lane & 3;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
@@ -163,22 +175,22 @@ __global__ void __launch_bounds__(128, BTS_UC_DRAIN ? 2 : 3) upconv_fwd_kernel(c
     const int tx = tile % ua.tiles_x;
     tile /= ua.tiles_x;
     const int ty = tile % ua.tiles_y, b_img = tile / ua.tiles_y;
-    const int i0 = ty * kUcTH, j0 = tx * kUcTW;
+    const int i0 = ty * T::TH, j0 = tx * T::TW;
     const int h = ua.h, w = ua.w, Cin = ua.Cin, Cout = ua.Cout;
     const float *xb = ua.x + (size_t)b_img * Cin * h * w;
     // fragments of row phase a, out-channel block blockIdx.y: [k-step][8 products][2 m-tiles][32 lanes][8 words]
     const uint4 *wchunk = ua.wfrag + ((size_t)a * (Cout / kUcMO) + blockIdx.y) * (size_t)(Cin / 8) * (8 * 2 * kUcFrag / 4);
 
     auto load_stage = [&](int kc, int buf) {
-        float *xs = smem + buf * kUcStageFloats, *ws = xs + kUcXFloats;
+        float *xs = smem + buf * kUcStageFloats<TALL>, *ws = xs + T::XFloats;
         // halo tile: smem row r <-> source row i0 - 1 + a + r, smem column c <-> source column j0 - 1 + c
-        for (int idx = tid; idx < kUcKC * kUcXR * kUcXC; idx += 128) {
-            const int c = idx / (kUcXR * kUcXC), rem = idx - c * (kUcXR * kUcXC);
-            const int r = rem / kUcXC, col = rem - r * kUcXC;
+        for (int idx = tid; idx < kUcKC * T::XR * T::XC; idx += 128) {
+            const int c = idx / (T::XR * T::XC), rem = idx - c * (T::XR * T::XC);
+            const int r = rem / T::XC, col = rem - r * T::XC;
             const int sr = i0 - 1 + a + r, sc = j0 - 1 + col;
             const bool ok = sr >= 0 && sr < h && sc >= 0 && sc < w;
             const float *src = xb + ((size_t)(kc * kUcKC + c) * h + (ok ? sr : 0)) * w + (ok ? sc : 0);
-            cp_async4(smem_u32(xs + c * kUcXS + r * kUcXC + col), src, ok);
+            cp_async4(smem_u32(xs + c * T::XS + r * T::XC + col), src, ok);
         }
         // weight chunk: the stage's 2 k-steps x 8 products x 2 m-tiles of ready fragments, one contiguous run
         {
@@ -220,7 +232,7 @@ __global__ void __launch_bounds__(128, BTS_UC_DRAIN ? 2 : 3) upconv_fwd_kernel(c
             asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
         __syncthreads();
-        const float *xs = smem + buf * kUcStageFloats, *ws = xs + kUcXFloats;
+        const float *xs = smem + buf * kUcStageFloats<TALL>, *ws = xs + T::XFloats;
 #pragma unroll
         for (int ks = 0; ks < kUcKC / 8; ++ks) {
             // six distinct windows of the halo tile: tap row dy x column shift sh = b + dx; each feeds the products (b, dx)
@@ -232,8 +244,8 @@ __global__ void __launch_bounds__(128, BTS_UC_DRAIN ? 2 : 3) upconv_fwd_kernel(c
                     UFragB fb[4];
 #pragma unroll
                     for (int n = 0; n < 4; ++n) {                    // n-tile: row 2 warp + n/2 of the tile, columns 8 (n%2) ..+7
-                        const float *q = xs + (8 * ks + t) * kUcXS + (2 * warp + (n >> 1) + dy) * kUcXC + 8 * (n & 1) + sh + g;
-                        make_b(q[0], q[4 * kUcXS], fb[n]);
+                        const float *q = xs + (8 * ks + t) * T::XS + (T::row(warp, n) + dy) * T::XC + T::colb(n) + sh + g;
+                        make_b(q[0], q[4 * T::XS], fb[n]);
                     }
 #pragma unroll
                     for (int b = 0; b < 2; ++b) {
@@ -293,7 +305,7 @@ __global__ void __launch_bounds__(128, BTS_UC_DRAIN ? 2 : 3) upconv_fwd_kernel(c
     const bool vec_ok = (W2 % 4) == 0 && (reinterpret_cast<uintptr_t>(ua.y) & 15u) == 0;
 #pragma unroll
     for (int n = 0; n < 4; ++n) {
-        const int i = i0 + 2 * warp + (n >> 1), j = j0 + 8 * (n & 1) + 2 * t;
+        const int i = i0 + T::row(warp, n), j = j0 + T::colb(n) + 2 * t;
         if (i >= h || j >= w) continue;
         const bool two = j + 1 < w;
 #pragma unroll
@@ -347,8 +359,9 @@ __global__ void upconv_eplanes_kernel(const float *__restrict__ gy, const float 
 
 constexpr int kDgKC = 8;                              // out channels (K) per stage: one k-step
 constexpr int kDgWS = 40;                             // floats per out-channel row of a weight chunk (32 c + 8: conflict-free A)
-constexpr int kDgEFloats = 4 * kDgKC * kUcXS, kDgWFloats = 16 * kDgKC * kDgWS;
-constexpr int kDgStageFloats = kDgEFloats + kDgWFloats;
+constexpr int kDgWFloats = 16 * kDgKC * kDgWS;
+template <bool TALL> constexpr int kDgEFloats = 4 * kDgKC * UcTile<TALL>::XS;
+template <bool TALL> constexpr int kDgStageFloats = kDgEFloats<TALL> + kDgWFloats;
 
 struct UpconvBwdArgs {
     const float *x;          // [B][Cin][h][w]
@@ -361,8 +374,10 @@ struct UpconvBwdArgs {
 };
 
 // grad_x: CTA = 32 input channels (M) x 8x16 pixels (N); K = out channels, 8 per stage, x 16 (plane, tap) products
+template <bool TALL>
 __global__ void __launch_bounds__(128, 2) upconv_dgrad_kernel(const __grid_constant__ UpconvBwdArgs ua)
 {
+    using T = UcTile<TALL>;
     extern __shared__ __align__(16) float smem[];
     const int tid = threadIdx.x, lane = tid & 31, g = lane >> 2, t = lane & 3;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
@@ -371,21 +386,21 @@ __global__ void __launch_bounds__(128, 2) upconv_dgrad_kernel(const __grid_const
     const int tx = tile % ua.tiles_x;
     tile /= ua.tiles_x;
     const int ty = tile % ua.tiles_y, b_img = tile / ua.tiles_y;
-    const int i0 = ty * kUcTH, j0 = tx * kUcTW;
+    const int i0 = ty * T::TH, j0 = tx * T::TW;
     const int h = ua.h, w = ua.w, Cin = ua.Cin, Cout = ua.Cout;
     const size_t plane_sz = (size_t)ua.B * Cout * h * w;
 
     auto load_stage = [&](int kc, int buf) {
-        float *es = smem + buf * kDgStageFloats, *ws = es + kDgEFloats;
+        float *es = smem + buf * kDgStageFloats<TALL>, *ws = es + kDgEFloats<TALL>;
         // plane (a, b): smem row r <-> source row i0 - a + r, smem column c <-> source column j0 - b + c
-        for (int idx = tid; idx < 4 * kDgKC * kUcXR * kUcXC; idx += 128) {
-            const int po = idx / (kUcXR * kUcXC), rem = idx - po * (kUcXR * kUcXC);   // po = plane * 8 + o
-            const int r = rem / kUcXC, col = rem - r * kUcXC;
+        for (int idx = tid; idx < 4 * kDgKC * T::XR * T::XC; idx += 128) {
+            const int po = idx / (T::XR * T::XC), rem = idx - po * (T::XR * T::XC);   // po = plane * 8 + o
+            const int r = rem / T::XC, col = rem - r * T::XC;
             const int ab = po >> 3, o = po & 7;
             const int sr = i0 - (ab >> 1) + r, sc = j0 - (ab & 1) + col;
             const bool ok = sr >= 0 && sr < h && sc >= 0 && sc < w;
             const float *src = ua.e + (size_t)ab * plane_sz + (((size_t)b_img * Cout + kc * kDgKC + o) * h + (ok ? sr : 0)) * w + (ok ? sc : 0);
-            cp_async4(smem_u32(es + po * kUcXS + r * kUcXC + col), src, ok);
+            cp_async4(smem_u32(es + po * T::XS + r * T::XC + col), src, ok);
         }
         // weights: [16 products][8 out channels][32 input channels]
         for (int idx = tid; idx < 16 * kDgKC * 8; idx += 128) {
@@ -416,7 +431,7 @@ __global__ void __launch_bounds__(128, 2) upconv_dgrad_kernel(const __grid_const
             asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
         __syncthreads();
-        const float *es = smem + buf * kDgStageFloats, *ws = es + kDgEFloats;
+        const float *es = smem + buf * kDgStageFloats<TALL>, *ws = es + kDgEFloats<TALL>;
 #pragma unroll
         for (int p = 0; p < 16; ++p) {                               // p = ((a*2 + b)*2 + dy)*2 + dx
             const int ab = p >> 2, dy = (p >> 1) & 1, dx = p & 1;
@@ -428,9 +443,9 @@ __global__ void __launch_bounds__(128, 2) upconv_dgrad_kernel(const __grid_const
             }
 #pragma unroll
             for (int n = 0; n < 4; ++n) {
-                const float *q = es + (ab * kDgKC + t) * kUcXS + (2 * warp + (n >> 1) + 1 - dy) * kUcXC + 8 * (n & 1) + 1 - dx + g;
+                const float *q = es + (ab * kDgKC + t) * T::XS + (T::row(warp, n) + 1 - dy) * T::XC + T::colb(n) + 1 - dx + g;
                 UFragB fb;
-                make_b(q[0], q[4 * kUcXS], fb);
+                make_b(q[0], q[4 * T::XS], fb);
 #pragma unroll
                 for (int mt = 0; mt < 2; ++mt) hmma_b(acc[mt][n], fa[mt].s, fb.s0, fb.s1);
 #pragma unroll
@@ -453,7 +468,7 @@ __global__ void __launch_bounds__(128, 2) upconv_dgrad_kernel(const __grid_const
     const bool vec_ok = (w % 2) == 0 && (reinterpret_cast<uintptr_t>(ua.gx) & 7u) == 0;
 #pragma unroll
     for (int n = 0; n < 4; ++n) {
-        const int i = i0 + 2 * warp + (n >> 1), j = j0 + 8 * (n & 1) + 2 * t;
+        const int i = i0 + T::row(warp, n), j = j0 + T::colb(n) + 2 * t;
         if (i >= h || j >= w) continue;
         const bool two = j + 1 < w;
 #pragma unroll
@@ -476,12 +491,13 @@ __global__ void __launch_bounds__(128, 2) upconv_dgrad_kernel(const __grid_const
 // tile of x] x 16 out channels (M) x 32 input channels (N) x a run of 8x16 pixel tiles (split K; fp32 atomics at the end).
 // A warp takes two rows of every tile = four k-steps of eight pixels along a row.
 constexpr int kWgES = 132;                            // floats per out-channel row of the plane tile (128 px + 4: conflict-free A)
-constexpr int kWgXS = 164;                            // floats per input channel of the halo tile (162 + 2: conflict-free B)
-constexpr int kWgEFloats = 16 * kWgES, kWgXFloats = 32 * kWgXS;
-constexpr int kWgStageFloats = kWgEFloats + kWgXFloats;
+constexpr int kWgEFloats = 16 * kWgES;
+template <bool TALL> constexpr int kWgStageFloats = kWgEFloats + 32 * UcTile<TALL>::WXS;   // + halo tile of x, 32 input channels
 
+template <bool TALL>
 __global__ void __launch_bounds__(128, 2) upconv_wgrad_kernel(const __grid_constant__ UpconvBwdArgs ua)
 {
+    using T = UcTile<TALL>;
     extern __shared__ __align__(16) float smem[];
     const int tid = threadIdx.x, lane = tid & 31, g = lane >> 2, t = lane & 3;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
@@ -495,13 +511,13 @@ __global__ void __launch_bounds__(128, 2) upconv_wgrad_kernel(const __grid_const
     const float *eplane = ua.e + (size_t)ab * ua.B * Cout * h * w;
 
     auto load_stage = [&](int tile, int buf) {
-        float *es = smem + buf * kWgStageFloats, *xs = es + kWgEFloats;
+        float *es = smem + buf * kWgStageFloats<TALL>, *xs = es + kWgEFloats;
         const int tx = tile % ua.tiles_x;
         const int rest = tile / ua.tiles_x;
         const int ty = rest % ua.tiles_y, img = rest / ua.tiles_y;
-        const int i0 = ty * kUcTH, j0 = tx * kUcTW;
+        const int i0 = ty * T::TH, j0 = tx * T::TW;
         {   // plane tile [16 o][8 x 16 px]: thread = pixel
-            const int r = tid >> 4, col = tid & 15;
+            const int r = tid / T::TW, col = tid % T::TW;
             const int sr = i0 + r, sc = j0 + col;
             const bool ok = sr < h && sc < w;
             const float *src = eplane + (((size_t)img * Cout + o0) * h + (ok ? sr : 0)) * w + (ok ? sc : 0);
@@ -510,14 +526,14 @@ __global__ void __launch_bounds__(128, 2) upconv_wgrad_kernel(const __grid_const
             for (int o = 0; o < 16; ++o) cp_async4(dst + o * kWgES * 4, src + (size_t)o * h * w, ok);
         }
         // halo tile of x [32 c][9 x 18]: smem row r <-> source row i0 - 1 + a + r, column c <-> j0 - 1 + b + c
-        for (int pos = tid; pos < kUcXR * kUcXC; pos += 128) {
-            const int r = pos / kUcXC, col = pos - r * kUcXC;
+        for (int pos = tid; pos < T::XR * T::XC; pos += 128) {
+            const int r = pos / T::XC, col = pos - r * T::XC;
             const int sr = i0 - 1 + a + r, sc = j0 - 1 + b + col;
             const bool ok = sr >= 0 && sr < h && sc >= 0 && sc < w;
             const float *src = ua.x + (((size_t)img * Cin + c0) * h + (ok ? sr : 0)) * w + (ok ? sc : 0);
             const uint32_t dst = smem_u32(xs + pos);
 #pragma unroll 8
-            for (int c = 0; c < 32; ++c) cp_async4(dst + c * kWgXS * 4, src + (size_t)c * h * w, ok);
+            for (int c = 0; c < 32; ++c) cp_async4(dst + c * T::WXS * 4, src + (size_t)c * h * w, ok);
         }
         cp_async_commit();
     };
@@ -540,13 +556,13 @@ __global__ void __launch_bounds__(128, 2) upconv_wgrad_kernel(const __grid_const
             asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
         __syncthreads();
-        const float *es = smem + buf * kWgStageFloats, *xs = es + kWgEFloats;
+        const float *es = smem + buf * kWgStageFloats<TALL>, *xs = es + kWgEFloats;
 #pragma unroll
         for (int ks = 0; ks < 4; ++ks) {                             // eight pixels: row 2 warp + ks/2, columns 8 (ks%2) ..+7
-            const int rowl = 2 * warp + (ks >> 1), colb = 8 * (ks & 1);
+            const int rowl = T::row(warp, ks), colb = T::colb(ks);
             UFragA fa;                                               // A[m = o][k = px] = E[o][px]
             {
-                const float *q = es + g * kWgES + rowl * 16 + colb + t;
+                const float *q = es + g * kWgES + rowl * T::TW + colb + t;
                 make_a(q[0], q[8 * kWgES], q[4], q[8 * kWgES + 4], fa);
             }
 #pragma unroll
@@ -554,7 +570,7 @@ __global__ void __launch_bounds__(128, 2) upconv_wgrad_kernel(const __grid_const
                 const int dy = p >> 1, dx = p & 1;
 #pragma unroll
                 for (int n = 0; n < 4; ++n) {                        // B[k = px][n = c] = x[c][row + dy][col + dx]
-                    const float *q = xs + (8 * n + g) * kWgXS + (rowl + dy) * kUcXC + colb + dx + t;
+                    const float *q = xs + (8 * n + g) * T::WXS + (rowl + dy) * T::XC + colb + dx + t;
                     UFragB fb;
                     make_b(q[0], q[4], fb);
                     hmma_b(acc[p][n], fa.s, fb.s0, fb.s1);
@@ -622,6 +638,32 @@ size_t upconv_workspace_bytes(int cin, int cout) { return (size_t)16 * cin * cou
 
 bool upconv_supported(int cin, int cout) { return cin > 0 && cout > 0 && cin % kUcKC == 0 && cout % kUcMO == 0; }
 
+// 16 x 8 tiles when they cover the image with less padding than 8 x 16 (BTS_UPCONV_TILE=wide|tall overrides)
+static bool upconv_tall(int h, int w)
+{
+    static const char *env = getenv("BTS_UPCONV_TILE");
+    if (env != nullptr && env[0] == 'w') return false;
+    if (env != nullptr && env[0] == 't') return true;
+    const long long wide = (long long)((h + 7) / 8) * ((w + 15) / 16), tall = (long long)((h + 15) / 16) * ((w + 7) / 8);
+    return tall < wide;
+}
+
+template <bool TALL>
+static int launch_upconv_fwd_t(UpconvArgs &ua, int B, cudaStream_t s)
+{
+    using T = UcTile<TALL>;
+    ua.tiles_x = (ua.w + T::TW - 1) / T::TW;
+    ua.tiles_y = (ua.h + T::TH - 1) / T::TH;
+    const size_t smem_bytes = sizeof(float) * 2 * kUcStageFloats<TALL>;
+    cudaError_t e = cudaFuncSetAttribute(upconv_fwd_kernel<TALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+    if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    const long long tiles = (long long)ua.tiles_x * ua.tiles_y * B;
+    if (tiles > 0x7fffffffLL) return set_error(BTS_ERR_BAD_ARG, "too many tiles");
+    dim3 grid((unsigned)tiles, (unsigned)(ua.Cout / kUcMO), 2);
+    upconv_fwd_kernel<TALL><<<grid, 128, smem_bytes, s>>>(ua);
+    return check_launch("upconv_fwd");
+}
+
 int launch_upconv_fwd(const float *x, const float *w, float *y, int B, int cin, int cout, int h, int wd, void *ws, cudaStream_t s)
 {
     uint4 *wfrag = static_cast<uint4 *>(ws);
@@ -631,27 +673,55 @@ int launch_upconv_fwd(const float *x, const float *w, float *y, int B, int cin, 
     UpconvArgs ua;
     ua.x = x; ua.wfrag = wfrag; ua.y = y;
     ua.B = B; ua.Cin = cin; ua.Cout = cout; ua.h = h; ua.w = wd;
-    ua.tiles_x = (wd + kUcTW - 1) / kUcTW;
-    ua.tiles_y = (h + kUcTH - 1) / kUcTH;
-    const size_t smem_bytes = sizeof(float) * 2 * kUcStageFloats;
-    cudaError_t e = cudaFuncSetAttribute(upconv_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
-    if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-    const long long tiles = (long long)ua.tiles_x * ua.tiles_y * B;
-    if (tiles > 0x7fffffffLL) return set_error(BTS_ERR_BAD_ARG, "too many tiles");
-    dim3 grid((unsigned)tiles, (unsigned)(cout / kUcMO), 2);
-    upconv_fwd_kernel<<<grid, 128, smem_bytes, s>>>(ua);
-    return check_launch("upconv_fwd");
+    return upconv_tall(h, wd) ? launch_upconv_fwd_t<true>(ua, B, s) : launch_upconv_fwd_t<false>(ua, B, s);
 }
-
-}  // namespace bts
-
-namespace bts {
 
 bool upconv_bwd_supported(int cin, int cout) { return cin > 0 && cout > 0 && cin % 32 == 0 && cout % 32 == 0; }
 
 size_t upconv_bwd_workspace_bytes(int B, int cin, int cout, int h, int w)
 {
     return sizeof(float) * ((size_t)32 * cin * cout + (size_t)4 * B * cout * h * w);
+}
+
+template <bool TALL>
+static int launch_upconv_bwd_t(UpconvBwdArgs &ua, const float *w, float *wf, float *gw, cudaStream_t s)
+{
+    using T = UcTile<TALL>;
+    const int cin = ua.Cin, cout = ua.Cout;
+    ua.tiles_x = (ua.w + T::TW - 1) / T::TW;
+    ua.tiles_y = (ua.h + T::TH - 1) / T::TH;
+    ua.tiles_per_cta = 1;
+    const long long tiles = (long long)ua.tiles_x * ua.tiles_y * ua.B;
+    if (tiles > 0x7fffffffLL) return set_error(BTS_ERR_BAD_ARG, "too many tiles");
+    if (ua.gx != nullptr) {
+        upconv_fold_kernel<<<(cin * cout + 255) / 256, 256, 0, s>>>(w, wf, cout, cin);
+        if (int er = check_launch("upconv_fold")) return er;
+        const size_t smem_bytes = sizeof(float) * 2 * kDgStageFloats<TALL>;
+        cudaError_t ce = cudaFuncSetAttribute(upconv_dgrad_kernel<TALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+        if (ce != cudaSuccess) return set_error((int)ce, "cudaFuncSetAttribute: %s", cudaGetErrorString(ce));
+        upconv_dgrad_kernel<TALL><<<dim3((unsigned)tiles, (unsigned)(cin / 32), 1), 128, smem_bytes, s>>>(ua);
+        if (int er = check_launch("upconv_dgrad")) return er;
+    }
+    if (gw != nullptr) {
+        cudaError_t ce = cudaMemsetAsync(ua.gwf, 0, sizeof(float) * (size_t)16 * cin * cout, s);
+        if (ce != cudaSuccess) return set_error((int)ce, "cudaMemsetAsync: %s", cudaGetErrorString(ce));
+        // split K so that the grid has a few CTAs per SM slot
+        const long long blocks = (long long)4 * (cout / 16) * (cin / 32);
+        long long ksplit = (8 * 148 * 2 + blocks - 1) / blocks;
+        if (ksplit < 1) ksplit = 1;
+        if (ksplit > tiles) ksplit = tiles;
+        ua.tiles_per_cta = (int)((tiles + ksplit - 1) / ksplit);
+        const unsigned gx_ = (unsigned)((tiles + ua.tiles_per_cta - 1) / ua.tiles_per_cta);
+        if (4 * (cout / 16) > 65535 || cin / 32 > 65535) return set_error(BTS_ERR_UNSUPPORTED, "upconv: too many channels");
+        const size_t smem_bytes = sizeof(float) * 2 * kWgStageFloats<TALL>;
+        ce = cudaFuncSetAttribute(upconv_wgrad_kernel<TALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+        if (ce != cudaSuccess) return set_error((int)ce, "cudaFuncSetAttribute: %s", cudaGetErrorString(ce));
+        upconv_wgrad_kernel<TALL><<<dim3(gx_, (unsigned)(4 * (cout / 16)), (unsigned)(cin / 32)), 128, smem_bytes, s>>>(ua);
+        if (int er = check_launch("upconv_wgrad")) return er;
+        upconv_unfold_kernel<<<(cin * cout + 255) / 256, 256, 0, s>>>(ua.gwf, gw, cout, cin);
+        if (int er = check_launch("upconv_unfold")) return er;
+    }
+    return BTS_OK;
 }
 
 // ws = [folded weights 16 Cout Cin | folded weight gradients 16 Cout Cin | phase planes 4 B Cout h w]
@@ -665,40 +735,7 @@ int launch_upconv_bwd(const float *x, const float *w, const float *y, const floa
     UpconvBwdArgs ua;
     ua.x = x; ua.wf = wf; ua.e = e; ua.gx = gx; ua.gwf = gwf;
     ua.B = B; ua.Cin = cin; ua.Cout = cout; ua.h = h; ua.w = wd;
-    ua.tiles_x = (wd + kUcTW - 1) / kUcTW;
-    ua.tiles_y = (h + kUcTH - 1) / kUcTH;
-    ua.tiles_per_cta = 1;
-    const long long tiles = (long long)ua.tiles_x * ua.tiles_y * B;
-    if (tiles > 0x7fffffffLL) return set_error(BTS_ERR_BAD_ARG, "too many tiles");
-    if (gx != nullptr) {
-        upconv_fold_kernel<<<(cin * cout + 255) / 256, 256, 0, s>>>(w, wf, cout, cin);
-        if (int er = check_launch("upconv_fold")) return er;
-        const size_t smem_bytes = sizeof(float) * 2 * kDgStageFloats;
-        cudaError_t ce = cudaFuncSetAttribute(upconv_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
-        if (ce != cudaSuccess) return set_error((int)ce, "cudaFuncSetAttribute: %s", cudaGetErrorString(ce));
-        upconv_dgrad_kernel<<<dim3((unsigned)tiles, (unsigned)(cin / 32), 1), 128, smem_bytes, s>>>(ua);
-        if (int er = check_launch("upconv_dgrad")) return er;
-    }
-    if (gw != nullptr) {
-        cudaError_t ce = cudaMemsetAsync(gwf, 0, sizeof(float) * (size_t)16 * cin * cout, s);
-        if (ce != cudaSuccess) return set_error((int)ce, "cudaMemsetAsync: %s", cudaGetErrorString(ce));
-        // split K so that the grid has a few CTAs per SM slot
-        const long long blocks = (long long)4 * (cout / 16) * (cin / 32);
-        long long ksplit = (8 * 148 * 2 + blocks - 1) / blocks;
-        if (ksplit < 1) ksplit = 1;
-        if (ksplit > tiles) ksplit = tiles;
-        ua.tiles_per_cta = (int)((tiles + ksplit - 1) / ksplit);
-        const unsigned gx_ = (unsigned)((tiles + ua.tiles_per_cta - 1) / ua.tiles_per_cta);
-        if (4 * (cout / 16) > 65535 || cin / 32 > 65535) return set_error(BTS_ERR_UNSUPPORTED, "upconv: too many channels");
-        const size_t smem_bytes = sizeof(float) * 2 * kWgStageFloats;
-        ce = cudaFuncSetAttribute(upconv_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
-        if (ce != cudaSuccess) return set_error((int)ce, "cudaFuncSetAttribute: %s", cudaGetErrorString(ce));
-        upconv_wgrad_kernel<<<dim3(gx_, (unsigned)(4 * (cout / 16)), (unsigned)(cin / 32)), 128, smem_bytes, s>>>(ua);
-        if (int er = check_launch("upconv_wgrad")) return er;
-        upconv_unfold_kernel<<<(cin * cout + 255) / 256, 256, 0, s>>>(gwf, gw, cout, cin);
-        if (int er = check_launch("upconv_unfold")) return er;
-    }
-    return BTS_OK;
+    return upconv_tall(h, wd) ? launch_upconv_bwd_t<true>(ua, w, wf, gw, s) : launch_upconv_bwd_t<false>(ua, w, wf, gw, s);
 }
 
 }  // namespace bts
