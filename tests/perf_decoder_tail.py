@@ -21,6 +21,23 @@ import bts_b200  # noqa: E402
 from test_gpu_dropin import DecoderTail  # noqa: E402
 
 
+class FusedDecoderTail(DecoderTail):
+    """The same decoder with INTEGRATION.md section 3's edit: each `reduc -> normalize/cat -> lpg -> / max_depth
+    [-> interpolate]` group is one bts_b200.fused_stage call."""
+
+    def forward(self, daspp_feat, skip1, skip0, focal):
+        F = torch.nn.functional
+        d8, d8_ds = bts_b200.fused_stage(self.reduc8x8, self.lpg8x8, daspp_feat, scaled=True, downsample=True)
+        iconv3 = self.conv3(torch.cat([self.bn3(self.upconv3(daspp_feat)), skip1, d8_ds], 1))
+        d4, d4_ds = bts_b200.fused_stage(self.reduc4x4, self.lpg4x4, iconv3, scaled=True, downsample=True)
+        iconv2 = self.conv2(torch.cat([self.bn2(self.upconv2(iconv3)), skip0, d4_ds], 1))
+        d2 = bts_b200.fused_stage(self.reduc2x2, self.lpg2x2, iconv2, scaled=True)
+        upconv1 = self.upconv1(iconv2)
+        reduc1x1 = self.reduc1x1(upconv1)
+        iconv1 = self.conv1(torch.cat([upconv1, reduc1x1, d2, d4, d8], 1))
+        return d8, d4, d2, reduc1x1, self.max_depth * self.get_depth(iconv1)
+
+
 def timed(model, inputs, gouts, iters):
     def step():
         model.zero_grad(set_to_none=True)
@@ -61,12 +78,16 @@ def main():
         res["stock_" + tag] = timed(copy.deepcopy(model), inputs, gouts, iters)
         res["graft_lpg_path_" + tag] = timed(bts_b200.graft(copy.deepcopy(model)), inputs, gouts, iters)
         res["graft_lpg_path_and_upconvs_" + tag] = timed(bts_b200.graft(copy.deepcopy(model), upconvs=True), inputs, gouts, iters)
+        fused = bts_b200.graft(copy.deepcopy(model))
+        fused.__class__ = FusedDecoderTail
+        res["graft_fused_stages_" + tag] = timed(fused, inputs, gouts, iters)
     px = B * H * W
     print(json.dumps({"what": "decoder from daspp_feat on (bts.py:249-293), forward + backward, ms per step (median of %d)" % iters,
                       "workload": wl["desc"], "device": torch.cuda.get_device_name(0), "ms": res,
                       "mpixels_per_s": {k: px / v / 1e3 for k, v in res.items()},
                       "note": "tf32_off = the reference's fp32 arithmetic for the stock cuDNN layers; tf32_on = PyTorch's default. "
-                              "graft_lpg_path: reduction_1x1 + local_planar_guidance swapped (strict drop-in, bts.forward untouched)."}))
+                              "graft_lpg_path: reduction_1x1 + local_planar_guidance swapped (strict drop-in, bts.forward untouched); "
+                              "graft_fused_stages: plus the three fused_stage edits of INTEGRATION.md section 3."}))
 
 
 if __name__ == "__main__":
