@@ -38,8 +38,6 @@ struct UcTile {
 };
 constexpr int kUcMO = 32;                            // out channels per CTA
 constexpr int kUcFrag = 256;                         // words of one A fragment in lane order: 32 lanes x {4 hi words, 4 bf16 pairs}
-constexpr int kUcWFloats = (kUcKC / 8) * 8 * 2 * kUcFrag;   // [k-step][product][m-tile] fragments
-template <bool TALL> constexpr int kUcStageFloats = UcTile<TALL>::XFloats + kUcWFloats;
 
 __device__ __forceinline__ void hmma_t(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1)
 {
@@ -163,14 +161,16 @@ __global__ void upconv_fold_frag_kernel(const float *__restrict__ w, uint4 *__re
     wfrag[2 * idx + 1] = make_uint4(f.s[0], f.s[1], f.s[2], f.s[3]);
 }
 
-template <bool TALL>
-__global__ void __launch_bounds__(128, BTS_UC_DRAIN ? 2 : 3) upconv_fwd_kernel(const __grid_constant__ UpconvArgs ua)
+// MT: m-tiles (16 out channels each) per CTA; 2 by default (see launch_upconv_fwd for the measured alternative).
+template <bool TALL, int MT>
+__global__ void __launch_bounds__(128, MT == 1 ? 4 : 2) upconv_fwd_kernel(const __grid_constant__ UpconvArgs ua)
 {
     using T = UcTile<TALL>;
+    constexpr int WFloats = (kUcKC / 8) * 8 * MT * kUcFrag, StageFloats = T::XFloats + WFloats;
     extern __shared__ __align__(16) float smem[];
     const int tid = threadIdx.x, lane = tid & 31, g = lane >> 2, t = lane & 3;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
-    const int a = blockIdx.z, o0 = blockIdx.y * kUcMO;
+    const int a = blockIdx.z, oblk = blockIdx.y / (2 / MT), msel = blockIdx.y % (2 / MT), o0 = oblk * kUcMO + 16 * msel;
     int tile = blockIdx.x;
     const int tx = tile % ua.tiles_x;
     tile /= ua.tiles_x;
@@ -179,10 +179,10 @@ __global__ void __launch_bounds__(128, BTS_UC_DRAIN ? 2 : 3) upconv_fwd_kernel(c
     const int h = ua.h, w = ua.w, Cin = ua.Cin, Cout = ua.Cout;
     const float *xb = ua.x + (size_t)b_img * Cin * h * w;
     // fragments of row phase a, out-channel block blockIdx.y: [k-step][8 products][2 m-tiles][32 lanes][8 words]
-    const uint4 *wchunk = ua.wfrag + ((size_t)a * (Cout / kUcMO) + blockIdx.y) * (size_t)(Cin / 8) * (8 * 2 * kUcFrag / 4);
+    const uint4 *wchunk = ua.wfrag + ((size_t)a * (Cout / kUcMO) + oblk) * (size_t)(Cin / 8) * (8 * 2 * kUcFrag / 4);
 
     auto load_stage = [&](int kc, int buf) {
-        float *xs = smem + buf * kUcStageFloats<TALL>, *ws = xs + T::XFloats;
+        float *xs = smem + buf * StageFloats, *ws = xs + T::XFloats;
         // halo tile: smem row r <-> source row i0 - 1 + a + r, smem column c <-> source column j0 - 1 + c
         for (int idx = tid; idx < kUcKC * T::XR * T::XC; idx += 128) {
             const int c = idx / (T::XR * T::XC), rem = idx - c * (T::XR * T::XC);
@@ -192,17 +192,21 @@ __global__ void __launch_bounds__(128, BTS_UC_DRAIN ? 2 : 3) upconv_fwd_kernel(c
             const float *src = xb + ((size_t)(kc * kUcKC + c) * h + (ok ? sr : 0)) * w + (ok ? sc : 0);
             cp_async4(smem_u32(xs + c * T::XS + r * T::XC + col), src, ok);
         }
-        // weight chunk: the stage's 2 k-steps x 8 products x 2 m-tiles of ready fragments, one contiguous run
+        // weight chunk: the stage's 2 k-steps x 8 products x MT m-tiles of ready fragments (1 KB each; global order
+        // [k-step][product][2 m-tiles])
         {
-            const uint4 *src = wchunk + (size_t)kc * (kUcWFloats / 4);
-            for (int idx = tid; idx < kUcWFloats / 4; idx += 128) cp_async16(smem_u32(ws + 4 * idx), src + idx, true);
+            const uint4 *src = wchunk + (size_t)kc * ((kUcKC / 8) * 8 * 2 * kUcFrag / 4);
+            for (int idx = tid; idx < WFloats / 4; idx += 128) {
+                const int fr = idx / (MT * 64), j = idx - fr * (MT * 64);             // fr = k-step * 8 + product
+                cp_async16(smem_u32(ws + 4 * idx), src + (size_t)(fr * 2 + (MT == 1 ? msel : 0)) * 64 + j, true);
+            }
         }
         cp_async_commit();
     };
 
-    float acc[2][4][2][4];                                           // [m-tile][n-tile][column phase b][fragment]
+    float acc[MT][4][2][4];                                           // [m-tile][n-tile][column phase b][fragment]
 #pragma unroll
-    for (int mt = 0; mt < 2; ++mt)
+    for (int mt = 0; mt < MT; ++mt)
 #pragma unroll
         for (int n = 0; n < 4; ++n)
 #pragma unroll
@@ -210,9 +214,9 @@ __global__ void __launch_bounds__(128, BTS_UC_DRAIN ? 2 : 3) upconv_fwd_kernel(c
 #pragma unroll
                 for (int q = 0; q < 4; ++q) acc[mt][n][b][q] = 0.f;
 #if BTS_UC_DRAIN
-    float master[2][4][2][4];
+    float master[MT][4][2][4];
 #pragma unroll
-    for (int mt = 0; mt < 2; ++mt)
+    for (int mt = 0; mt < MT; ++mt)
 #pragma unroll
         for (int n = 0; n < 4; ++n)
 #pragma unroll
@@ -232,7 +236,7 @@ __global__ void __launch_bounds__(128, BTS_UC_DRAIN ? 2 : 3) upconv_fwd_kernel(c
             asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
         __syncthreads();
-        const float *xs = smem + buf * kUcStageFloats<TALL>, *ws = xs + T::XFloats;
+        const float *xs = smem + buf * StageFloats, *ws = xs + T::XFloats;
 #pragma unroll
         for (int ks = 0; ks < kUcKC / 8; ++ks) {
             // six distinct windows of the halo tile: tap row dy x column shift sh = b + dx; each feeds the products (b, dx)
@@ -252,10 +256,10 @@ __global__ void __launch_bounds__(128, BTS_UC_DRAIN ? 2 : 3) upconv_fwd_kernel(c
                         const int dx = sh - b;
                         if (dx < 0 || dx > 1) continue;
                         const int p = b * 4 + dy * 2 + dx;
-                        UFragA fa[2];
+                        UFragA fa[MT];
 #pragma unroll
-                        for (int mt = 0; mt < 2; ++mt) {
-                            const uint4 *q = reinterpret_cast<const uint4 *>(ws + ((ks * 8 + p) * 2 + mt) * kUcFrag) + 2 * lane;
+                        for (int mt = 0; mt < MT; ++mt) {
+                            const uint4 *q = reinterpret_cast<const uint4 *>(ws + ((ks * 8 + p) * MT + mt) * kUcFrag) + 2 * lane;
                             const uint4 vh = q[0], vs = q[1];
                             fa[mt].h[0] = vh.x; fa[mt].h[1] = vh.y; fa[mt].h[2] = vh.z; fa[mt].h[3] = vh.w;
                             fa[mt].s[0] = vs.x; fa[mt].s[1] = vs.y; fa[mt].s[2] = vs.z; fa[mt].s[3] = vs.w;
@@ -263,11 +267,11 @@ __global__ void __launch_bounds__(128, BTS_UC_DRAIN ? 2 : 3) upconv_fwd_kernel(c
 #pragma unroll
                         for (int n = 0; n < 4; ++n)
 #pragma unroll
-                            for (int mt = 0; mt < 2; ++mt) hmma_b(acc[mt][n][b], fa[mt].s, fb[n].s0, fb[n].s1);
+                            for (int mt = 0; mt < MT; ++mt) hmma_b(acc[mt][n][b], fa[mt].s, fb[n].s0, fb[n].s1);
 #pragma unroll
                         for (int n = 0; n < 4; ++n)
 #pragma unroll
-                            for (int mt = 0; mt < 2; ++mt) hmma_t(acc[mt][n][b], fa[mt].h, fb[n].h0, fb[n].h1);
+                            for (int mt = 0; mt < MT; ++mt) hmma_t(acc[mt][n][b], fa[mt].h, fb[n].h0, fb[n].h1);
                     }
                 }
         }
@@ -275,7 +279,7 @@ __global__ void __launch_bounds__(128, BTS_UC_DRAIN ? 2 : 3) upconv_fwd_kernel(c
 #if BTS_UC_DRAIN
         if ((kc + 1) % BTS_UC_DRAIN == 0 || kc + 1 == nk) {
 #pragma unroll
-            for (int mt = 0; mt < 2; ++mt)
+            for (int mt = 0; mt < MT; ++mt)
 #pragma unroll
                 for (int n = 0; n < 4; ++n)
 #pragma unroll
@@ -290,7 +294,7 @@ __global__ void __launch_bounds__(128, BTS_UC_DRAIN ? 2 : 3) upconv_fwd_kernel(c
     }
 #if BTS_UC_DRAIN
 #pragma unroll
-    for (int mt = 0; mt < 2; ++mt)
+    for (int mt = 0; mt < MT; ++mt)
 #pragma unroll
         for (int n = 0; n < 4; ++n)
 #pragma unroll
@@ -309,7 +313,7 @@ __global__ void __launch_bounds__(128, BTS_UC_DRAIN ? 2 : 3) upconv_fwd_kernel(c
         if (i >= h || j >= w) continue;
         const bool two = j + 1 < w;
 #pragma unroll
-        for (int mt = 0; mt < 2; ++mt)
+        for (int mt = 0; mt < MT; ++mt)
 #pragma unroll
             for (int hf = 0; hf < 2; ++hf) {
                 const int o = o0 + 16 * mt + g + 8 * hf;
@@ -648,19 +652,19 @@ static bool upconv_tall(int h, int w)
     return tall < wide;
 }
 
-template <bool TALL>
+template <bool TALL, int MT>
 static int launch_upconv_fwd_t(UpconvArgs &ua, int B, cudaStream_t s)
 {
     using T = UcTile<TALL>;
     ua.tiles_x = (ua.w + T::TW - 1) / T::TW;
     ua.tiles_y = (ua.h + T::TH - 1) / T::TH;
-    const size_t smem_bytes = sizeof(float) * 2 * kUcStageFloats<TALL>;
-    cudaError_t e = cudaFuncSetAttribute(upconv_fwd_kernel<TALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+    const size_t smem_bytes = sizeof(float) * 2 * (T::XFloats + (kUcKC / 8) * 8 * MT * kUcFrag);
+    cudaError_t e = cudaFuncSetAttribute(upconv_fwd_kernel<TALL, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     const long long tiles = (long long)ua.tiles_x * ua.tiles_y * B;
     if (tiles > 0x7fffffffLL) return set_error(BTS_ERR_BAD_ARG, "too many tiles");
-    dim3 grid((unsigned)tiles, (unsigned)(ua.Cout / kUcMO), 2);
-    upconv_fwd_kernel<TALL><<<grid, 128, smem_bytes, s>>>(ua);
+    dim3 grid((unsigned)tiles, (unsigned)(ua.Cout / kUcMO * (2 / MT)), 2);
+    upconv_fwd_kernel<TALL, MT><<<grid, 128, smem_bytes, s>>>(ua);
     return check_launch("upconv_fwd");
 }
 
@@ -673,7 +677,11 @@ int launch_upconv_fwd(const float *x, const float *w, float *y, int B, int cin, 
     UpconvArgs ua;
     ua.x = x; ua.wfrag = wfrag; ua.y = y;
     ua.B = B; ua.Cin = cin; ua.Cout = cout; ua.h = h; ua.w = wd;
-    return upconv_tall(h, wd) ? launch_upconv_fwd_t<true>(ua, B, s) : launch_upconv_fwd_t<false>(ua, B, s);
+    // 32 out channels per CTA. BTS_UPCONV_MT=1 (tuning): 16 per CTA = half the accumulators, 16 instead of 8 warps per SM --
+    // measured SLOWER (5.6 vs 4.5 ms for the five decoder upconvs at nyu_b8): every B fragment then serves half as many MMAs
+    static const int mt_env = getenv("BTS_UPCONV_MT") ? atoi(getenv("BTS_UPCONV_MT")) : 2;
+    if (mt_env == 1) return upconv_tall(h, wd) ? launch_upconv_fwd_t<true, 1>(ua, B, s) : launch_upconv_fwd_t<false, 1>(ua, B, s);
+    return upconv_tall(h, wd) ? launch_upconv_fwd_t<true, 2>(ua, B, s) : launch_upconv_fwd_t<false, 2>(ua, B, s);
 }
 
 bool upconv_bwd_supported(int cin, int cout) { return cin > 0 && cout > 0 && cin % 32 == 0 && cout % 32 == 0; }

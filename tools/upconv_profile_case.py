@@ -1,0 +1,10 @@
+import sys, torch
+sys.path.insert(0, "/root/repo")
+from bts_b200 import functional as Fn
+x = torch.randn(8, 128, 120, 160, device="cuda", requires_grad=True)
+wt = (torch.randn(64, 128, 3, 3, device="cuda") * 0.03).requires_grad_(True)
+gy = torch.randn(8, 64, 240, 320, device="cuda")
+for _ in range(3):
+    x.grad = wt.grad = None
+    Fn.upconv_forward(x, wt).backward(gy)
+torch.cuda.synchronize()
