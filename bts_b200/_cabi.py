@@ -69,7 +69,7 @@ _SIGNATURES["bts_silog_fwd_static"] = (ctypes.c_int, [_P, _P, _P, _LL, _F, _P, _
 _SIGNATURES["bts_eval_workspace_bytes"] = (ctypes.c_size_t, [_I, _I, _I])
 _SIGNATURES["bts_eval_metrics"] = (ctypes.c_int, [_P, _P, _I, _I, _I, _F, _F, _I, _I, _I, _I, _P, _P, _P, _SZ, _P])
 _SIGNATURES["bts_backproject"] = (ctypes.c_int, [_P, _P, _I, _I, _I, _F, _F, _F, _F, _F, _F, _P])
-_SIGNATURES["bts_upconv_workspace_bytes"] = (ctypes.c_size_t, [_I, _I])
+_SIGNATURES["bts_upconv_workspace_bytes"] = (ctypes.c_size_t, [_I, _I, _I, _I, _I])
 _SIGNATURES["bts_upconv_fwd"] = (ctypes.c_int, [_P, _P, _I, _I, _I, _I, _I, _P, _P, _SZ, _P])
 _SIGNATURES["bts_upconv_bwd_workspace_bytes"] = (ctypes.c_size_t, [_I, _I, _I, _I, _I])
 _SIGNATURES["bts_upconv_bwd"] = (ctypes.c_int, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _SZ, _P])

@@ -50,7 +50,7 @@ int launch_chain_generic_bwd(const ChainParams &, const float *, const float *, 
 int launch_chain_tc_fwd(const ChainParams &, const TcArgs &, int r, int sms, cudaStream_t);
 int launch_chain_tc_bwd(const ChainParams &, const TcArgs &, int mode, int r, void *ws, int sms, cudaStream_t);
 int launch_chain_bwd_fused(const ChainParams &, const TcArgs &, int mode, int r, void *ws, int sms, cudaStream_t);
-size_t upconv_workspace_bytes(int cin, int cout);
+size_t upconv_workspace_bytes(int B, int cin, int cout, int h, int w);
 bool upconv_supported(int cin, int cout);
 int launch_upconv_fwd(const float *x, const float *w, float *y, int B, int cin, int cout, int h, int wd, void *ws, cudaStream_t s);
 bool upconv_bwd_supported(int cin, int cout);
@@ -473,10 +473,10 @@ int bts_backproject(const float *depth, float *points, int B, int H, int W, floa
     return launch_backproject(depth, points, B, H, W, fx, fy, cx, cy, edge_thresh, hidden, (cudaStream_t)stream);
 }
 
-size_t bts_upconv_workspace_bytes(int cin, int cout)
+size_t bts_upconv_workspace_bytes(int B, int cin, int cout, int h, int w)
 {
-    if (cin <= 0 || cout <= 0) return 0;
-    return upconv_workspace_bytes(cin, cout);
+    if (B < 0 || cin <= 0 || cout <= 0 || h < 0 || w < 0) return 0;
+    return upconv_workspace_bytes(B, cin, cout, h, w);
 }
 
 int bts_upconv_fwd(const float *x, const float *weight, int B, int cin, int cout, int h, int w, float *y, void *ws,
@@ -487,8 +487,8 @@ int bts_upconv_fwd(const float *x, const float *weight, int B, int cin, int cout
     if (!x || !weight || !y) return set_error(BTS_ERR_BAD_ARG, "x / weight / y is NULL");
     if (!upconv_supported(cin, cout)) return set_error(BTS_ERR_UNSUPPORTED, "upconv: cin %% 16 == 0 and cout %% 32 == 0 required (cin=%d cout=%d)", cin, cout);
     if ((long long)B * cout * 4 * h * w > (1ll << 40) || (long long)4 * h * w > (1ll << 31) - 1) return set_error(BTS_ERR_UNSUPPORTED, "upconv: tensor too large");
-    if (ws == nullptr || !aligned16(ws) || ws_bytes < upconv_workspace_bytes(cin, cout))
-        return set_error(BTS_ERR_BAD_ARG, "upconv: workspace of %zu bytes (16-byte aligned) required", upconv_workspace_bytes(cin, cout));
+    if (ws == nullptr || !aligned16(ws) || ws_bytes < upconv_workspace_bytes(B, cin, cout, h, w))
+        return set_error(BTS_ERR_BAD_ARG, "upconv: workspace of %zu bytes (16-byte aligned) required", upconv_workspace_bytes(B, cin, cout, h, w));
     if (!aligned16(x) || !aligned16(weight)) return set_error(BTS_ERR_BAD_ARG, "upconv: x / weight must be 16-byte aligned");
     return launch_upconv_fwd(x, weight, y, B, cin, cout, h, w, ws, (cudaStream_t)stream);
 }

@@ -32,7 +32,6 @@ struct UcTile {
     static constexpr int XR = TH + 1, XC = TW + 2;   // halo tile: 9 x 18 | 17 x 10
     static constexpr int XS = TALL ? 200 : 168;      // floats per channel, = 8 mod 32: conflict-free B fragments (k = channel)
     static constexpr int WXS = TALL ? 196 : 164;     // same for the weight gradient, = 4 mod 32 (k = pixel)
-    static constexpr int XFloats = kUcKC * XS;
     __device__ static constexpr int row(int warp, int n) { return TALL ? 4 * warp + n : 2 * warp + (n >> 1); }
     __device__ static constexpr int colb(int n) { return TALL ? 0 : 8 * (n & 1); }
 };
@@ -98,6 +97,7 @@ __device__ __forceinline__ void make_b(float v0, float v1, UFragB &f)
 struct UpconvArgs {
     const float *x;          // [B][Cin][h][w]
     const uint4 *wfrag;      // folded weights as A fragments (upconv_fold_frag_kernel)
+    const uint4 *xsplit;     // x as B fragments (upconv_split_kernel)
     float *y;                // [B][Cout][2h][2w]
     int B, Cin, Cout, h, w, tiles_x, tiles_y;
 };
@@ -161,12 +161,36 @@ __global__ void upconv_fold_frag_kernel(const float *__restrict__ w, uint4 *__re
     wfrag[2 * idx + 1] = make_uint4(f.s[0], f.s[1], f.s[2], f.s[3]);
 }
 
+// The forward's B operand, ready to use. A B fragment pairs channels (c, c+4) of ONE pixel, so the split does not depend on
+// the tap window: xs[img][c / 8][t = c % 4][pixel] = {hi(c), hi(c+4), bf16 pair of the hi parts, bf16 pair of the remainders}
+// (16 bytes = one fragment of lane (g, t) once the pixel is chosen). One elementwise pass (x read once, 2x its bytes
+// written) replaces two loads and six ALU instructions per fragment in every warp, window and out-channel block that uses it
+// -- the kernel was issue-bound on exactly that.
+__global__ void upconv_split_kernel(const float *__restrict__ x, uint4 *__restrict__ xs, long long n, int hw, int cin)
+{
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;   // ((img * cin/8 + oct) * 4 + t) * hw + px
+    if (idx >= n) return;
+    const int px = (int)(idx % hw);
+    const long long r = idx / hw;
+    const int t = (int)(r & 3);
+    const long long io = r >> 2;                                     // img * (cin / 8) + oct
+    const long long img = io / (cin / 8);
+    const int oct = (int)(io - img * (cin / 8));
+    const float *src = x + ((size_t)img * cin + 8 * oct + t) * hw + px;
+    UFragB f;
+    make_b(__ldg(src), __ldg(src + (size_t)4 * hw), f);
+    xs[idx] = make_uint4(f.h0, f.h1, f.s0, f.s1);
+}
+
 // MT: m-tiles (16 out channels each) per CTA; 2 by default (see launch_upconv_fwd for the measured alternative).
 template <bool TALL, int MT>
 __global__ void __launch_bounds__(128, MT == 1 ? 4 : 2) upconv_fwd_kernel(const __grid_constant__ UpconvArgs ua)
 {
     using T = UcTile<TALL>;
-    constexpr int WFloats = (kUcKC / 8) * 8 * MT * kUcFrag, StageFloats = T::XFloats + WFloats;
+    constexpr int NPX = T::XR * T::XC;                               // halo pixels; a plane (k-step, t) is NPX 16-byte fragments
+    constexpr int XFloats = (kUcKC / 8) * 4 * NPX * 4;               // (NPX * 4 words = 8 mod 32: the eight lanes of a 128-bit load phase hit eight bank groups)
+    constexpr int WFloats = (kUcKC / 8) * 8 * MT * kUcFrag, StageFloats = XFloats + WFloats;
+    static_assert((NPX * 4) % 32 == 8, "conflict-free fragment loads");
     extern __shared__ __align__(16) float smem[];
     const int tid = threadIdx.x, lane = tid & 31, g = lane >> 2, t = lane & 3;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
@@ -177,20 +201,20 @@ __global__ void __launch_bounds__(128, MT == 1 ? 4 : 2) upconv_fwd_kernel(const 
     const int ty = tile % ua.tiles_y, b_img = tile / ua.tiles_y;
     const int i0 = ty * T::TH, j0 = tx * T::TW;
     const int h = ua.h, w = ua.w, Cin = ua.Cin, Cout = ua.Cout;
-    const float *xb = ua.x + (size_t)b_img * Cin * h * w;
+    const uint4 *xb = ua.xsplit + (size_t)b_img * (Cin / 8) * 4 * h * w;
     // fragments of row phase a, out-channel block blockIdx.y: [k-step][8 products][2 m-tiles][32 lanes][8 words]
     const uint4 *wchunk = ua.wfrag + ((size_t)a * (Cout / kUcMO) + oblk) * (size_t)(Cin / 8) * (8 * 2 * kUcFrag / 4);
 
     auto load_stage = [&](int kc, int buf) {
-        float *xs = smem + buf * StageFloats, *ws = xs + T::XFloats;
-        // halo tile: smem row r <-> source row i0 - 1 + a + r, smem column c <-> source column j0 - 1 + c
-        for (int idx = tid; idx < kUcKC * T::XR * T::XC; idx += 128) {
-            const int c = idx / (T::XR * T::XC), rem = idx - c * (T::XR * T::XC);
+        float *xs = smem + buf * StageFloats, *ws = xs + XFloats;
+        // halo tile of ready B fragments, planes [k-step][t]: smem row r <-> source row i0 - 1 + a + r, column c <-> j0 - 1 + c
+        for (int idx = tid; idx < (kUcKC / 8) * 4 * NPX; idx += 128) {
+            const int pl = idx / NPX, rem = idx - pl * NPX;
             const int r = rem / T::XC, col = rem - r * T::XC;
             const int sr = i0 - 1 + a + r, sc = j0 - 1 + col;
             const bool ok = sr >= 0 && sr < h && sc >= 0 && sc < w;
-            const float *src = xb + ((size_t)(kc * kUcKC + c) * h + (ok ? sr : 0)) * w + (ok ? sc : 0);
-            cp_async4(smem_u32(xs + c * T::XS + r * T::XC + col), src, ok);
+            const uint4 *src = xb + ((size_t)(kc * (kUcKC / 8) * 4 + pl) * h + (ok ? sr : 0)) * w + (ok ? sc : 0);
+            cp_async16(smem_u32(xs + 4 * idx), src, ok);
         }
         // weight chunk: the stage's 2 k-steps x 8 products x MT m-tiles of ready fragments (1 KB each; global order
         // [k-step][product][2 m-tiles])
@@ -236,7 +260,7 @@ __global__ void __launch_bounds__(128, MT == 1 ? 4 : 2) upconv_fwd_kernel(const 
             asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
         __syncthreads();
-        const float *xs = smem + buf * StageFloats, *ws = xs + T::XFloats;
+        const float *xs = smem + buf * StageFloats, *ws = xs + XFloats;
 #pragma unroll
         for (int ks = 0; ks < kUcKC / 8; ++ks) {
             // six distinct windows of the halo tile: tap row dy x column shift sh = b + dx; each feeds the products (b, dx)
@@ -247,9 +271,9 @@ __global__ void __launch_bounds__(128, MT == 1 ? 4 : 2) upconv_fwd_kernel(const 
                 for (int sh = 0; sh < 3; ++sh) {
                     UFragB fb[4];
 #pragma unroll
-                    for (int n = 0; n < 4; ++n) {                    // n-tile: row 2 warp + n/2 of the tile, columns 8 (n%2) ..+7
-                        const float *q = xs + (8 * ks + t) * T::XS + (T::row(warp, n) + dy) * T::XC + T::colb(n) + sh + g;
-                        make_b(q[0], q[4 * T::XS], fb[n]);
+                    for (int n = 0; n < 4; ++n) {                    // n-tile: eight pixels of tile row T::row(warp, n); lane (g, t) takes pixel g's fragment t
+                        const uint4 v = reinterpret_cast<const uint4 *>(xs)[(ks * 4 + t) * NPX + (T::row(warp, n) + dy) * T::XC + T::colb(n) + sh + g];
+                        fb[n].h0 = v.x; fb[n].h1 = v.y; fb[n].s0 = v.z; fb[n].s1 = v.w;
                     }
 #pragma unroll
                     for (int b = 0; b < 2; ++b) {
@@ -638,7 +662,11 @@ __global__ void upconv_unfold_kernel(const float *__restrict__ gwf, float *__res
 
 }  // namespace
 
-size_t upconv_workspace_bytes(int cin, int cout) { return (size_t)16 * cin * cout * 2 * sizeof(float); }   // hi word + bf16 halves per weight
+// folded weights as A fragments (hi word + bf16 halves per weight) + x as B fragments (same, per element)
+size_t upconv_workspace_bytes(int B, int cin, int cout, int h, int w)
+{
+    return ((size_t)16 * cin * cout + (size_t)B * cin * h * w) * 2 * sizeof(float);
+}
 
 bool upconv_supported(int cin, int cout) { return cin > 0 && cout > 0 && cin % kUcKC == 0 && cout % kUcMO == 0; }
 
@@ -658,7 +686,7 @@ static int launch_upconv_fwd_t(UpconvArgs &ua, int B, cudaStream_t s)
     using T = UcTile<TALL>;
     ua.tiles_x = (ua.w + T::TW - 1) / T::TW;
     ua.tiles_y = (ua.h + T::TH - 1) / T::TH;
-    const size_t smem_bytes = sizeof(float) * 2 * (T::XFloats + (kUcKC / 8) * 8 * MT * kUcFrag);
+    const size_t smem_bytes = sizeof(float) * 2 * ((kUcKC / 8) * 4 * T::XR * T::XC * 4 + (kUcKC / 8) * 8 * MT * kUcFrag);
     cudaError_t e = cudaFuncSetAttribute(upconv_fwd_kernel<TALL, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
     if (e != cudaSuccess) return set_error((int)e, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     const long long tiles = (long long)ua.tiles_x * ua.tiles_y * B;
@@ -674,8 +702,12 @@ int launch_upconv_fwd(const float *x, const float *w, float *y, int B, int cin, 
     const long long nfrag = (long long)2 * (cout / 32) * (cin / 8) * 8 * 2 * 32;
     upconv_fold_frag_kernel<<<(unsigned)((nfrag + 255) / 256), 256, 0, s>>>(w, wfrag, cout, cin);
     if (int e = check_launch("upconv_fold_frag")) return e;
+    uint4 *xsplit = wfrag + (size_t)16 * cin * cout / 2;              // (16 cin cout weights x 8 bytes)
+    const long long nsplit = (long long)B * (cin / 2) * h * wd;
+    upconv_split_kernel<<<(unsigned)((nsplit + 255) / 256), 256, 0, s>>>(x, xsplit, nsplit, h * wd, cin);
+    if (int e = check_launch("upconv_split")) return e;
     UpconvArgs ua;
-    ua.x = x; ua.wfrag = wfrag; ua.y = y;
+    ua.x = x; ua.wfrag = wfrag; ua.xsplit = xsplit; ua.y = y;
     ua.B = B; ua.Cin = cin; ua.Cout = cout; ua.h = h; ua.w = wd;
     // 32 out channels per CTA. BTS_UPCONV_MT=1 (tuning): 16 per CTA = half the accumulators, 16 instead of 8 warps per SM --
     // measured SLOWER (5.6 vs 4.5 ms for the five decoder upconvs at nyu_b8): every B fragment then serves half as many MMAs

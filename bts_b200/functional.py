@@ -514,7 +514,7 @@ def _upconv_fwd_raw(x, weight):
     B, cin, h, w = x.shape
     cout = weight.shape[0]
     y = torch.empty((B, cout, 2 * h, 2 * w), dtype=torch.float32, device=x.device)
-    nws = _cabi.lib().bts_upconv_workspace_bytes(cin, cout)
+    nws = _cabi.lib().bts_upconv_workspace_bytes(B, cin, cout, h, w)
     ws = torch.empty(((nws + 15) // 16 * 4,), dtype=torch.float32, device=x.device)
     with torch.cuda.device(x.device):
         _cabi.check(_cabi.lib().bts_upconv_fwd(x.data_ptr(), weight.data_ptr(), B, cin, cout, h, w, y.data_ptr(), ws.data_ptr(),

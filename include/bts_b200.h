@@ -256,7 +256,8 @@ BTS_API int bts_silog_fwd_static(const float *depth_est, const float *depth_gt, 
  * The up-sampled tensor is never materialised: the nearest x2 is folded into the weights (four phases, each a 2x2
  * convolution of the low-resolution input with sums of the 3x3 taps: 16 cin multiply-adds per low-res pixel and output
  * channel instead of 36 cin), run as an implicit GEMM on tensor cores with fp32-accurate products, ELU in the epilogue.
- * `ws`: bts_upconv_workspace_bytes(cin, cout) bytes (the folded weights, rebuilt by every call), 16-byte aligned.
+ * `ws`: bts_upconv_workspace_bytes() bytes (the folded weights and the input, both pre-split into ready MMA fragments by
+ * two small kernels of the same call), 16-byte aligned.
  * Served: cin % 16 == 0 and cout % 32 == 0 (every upconv of the BTS decoders); BTS_ERR_UNSUPPORTED otherwise.
  *
  * bts_upconv_bwd: its autograd backward. y = the forward's output (ELU' is taken through it: y > 0 ? 1 : y + 1),
@@ -266,7 +267,7 @@ BTS_API int bts_silog_fwd_static(const float *depth_est, const float *depth_gt, 
  * `ws`: bts_upconv_bwd_workspace_bytes() bytes (folded weights, folded weight gradients, phase planes), 16-byte aligned.
  * Served: cin % 32 == 0 and cout % 32 == 0.
  */
-BTS_API size_t bts_upconv_workspace_bytes(int cin, int cout);
+BTS_API size_t bts_upconv_workspace_bytes(int B, int cin, int cout, int h, int w);
 BTS_API int bts_upconv_fwd(const float *x, const float *weight, int B, int cin, int cout, int h, int w, float *y,
                            void *ws, size_t ws_bytes, void *stream);
 BTS_API size_t bts_upconv_bwd_workspace_bytes(int B, int cin, int cout, int h, int w);
