@@ -1,3 +1,5 @@
+"""Forward error of the upconv kernel against the fp64 oracle at three decoder widths (and of the CPU fp32 / cuDNN fp32
+sequences, for scale): the figure behind the drained accumulators of upconv.cu."""
 import sys, torch
 sys.path.insert(0, "/root/repo")
 from bts_b200 import functional as Fn

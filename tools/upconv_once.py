@@ -1,3 +1,5 @@
+"""One forward + backward of each of the five decoder upconvs at nyu_b8 (the command `ncu --metrics gpu__time_duration.sum
+-k regex:upconv` is run on for a per-kernel breakdown)."""
 import sys, torch
 sys.path.insert(0, "/root/repo")
 from bts_b200 import functional as Fn

@@ -1,3 +1,5 @@
+"""upconv2 of the decoder at nyu_b8 ([8,128,120,160] -> [8,64,240,320]), forward + backward, three times: the case
+`ncu --set full -k regex:upconv_fwd_kernel|upconv_dgrad|upconv_wgrad --launch-skip 3 -c 3` profiles."""
 import sys, torch
 sys.path.insert(0, "/root/repo")
 from bts_b200 import functional as Fn
