@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Error of every output of the four stages against the fp64 oracle at a bench workload's FULL shapes
 (max|a-b| / max|b|; the bar is 1e-5). The tuning companion of tests/test_gpu_baseline_shapes.py: prints the margins.
-Usage: parity_report.py [workload] [stage-substring]"""
+Usage: tests/perf_parity_report.py [workload] [stage-substring]   (test infrastructure: uses oracle/; not collected by pytest)"""
 import os
 import sys
 

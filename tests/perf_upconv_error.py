@@ -1,7 +1,8 @@
 """Forward error of the upconv kernel against the fp64 oracle at three decoder widths (and of the CPU fp32 / cuDNN fp32
 sequences, for scale): the figure behind the drained accumulators of upconv.cu."""
 import sys, torch
-sys.path.insert(0, "/root/repo")
+import os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from bts_b200 import functional as Fn
 from oracle import torch_port as tp
 for cin, cout, B, h, w in ((64, 32, 1, 24, 32), (512, 256, 1, 15, 20), (2208, 512, 1, 7, 10)):
