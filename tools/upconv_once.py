@@ -1,7 +1,8 @@
 """One forward + backward of each of the five decoder upconvs at nyu_b8 (the command `ncu --metrics gpu__time_duration.sum
 -k regex:upconv` is run on for a per-kernel breakdown)."""
 import sys, torch
-sys.path.insert(0, "/root/repo")
+import os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from bts_b200 import functional as Fn
 B, H, W = 8, 480, 640
 for name, cin, cout, div in (("upconv5", 2208, 512, 32), ("upconv4", 512, 256, 16), ("upconv3", 256, 128, 8), ("upconv2", 128, 64, 4), ("upconv1", 64, 32, 2)):
