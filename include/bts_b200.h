@@ -138,6 +138,11 @@ BTS_API int bts_reduc_lpg_bwd(const float *grad_depth, const float *x, const flo
  * recompute. bts_stash_bytes() == 0 means the chain is always recomputed (narrow chains, whose
  * one-pass backward is cheaper than the extra traffic; chains outside the tensor-core path).
  * stash == NULL / too small / misaligned (16 B) -> exactly the behaviour of the plain entry points.
+ * CONTRACT: the stash carries no validity tag (the backward cannot see, without a host synchronisation, whether the
+ * forward filled it). The forward fills it only when it takes the tensor-core route: weights and `depth` 16-byte
+ * aligned, a workspace of bts_workspace_bytes() bytes, the route not forced elsewhere (bts_force_path). Hand the backward
+ * a stash only from a forward call made under those conditions with the same workspace size (bts_b200/functional.py
+ * allocates all of them itself and does); otherwise pass stash = NULL and the backward recomputes.
  */
 BTS_API size_t bts_stash_bytes(const int *dims, int n_layers, int B, int h, int w);
 
