@@ -139,3 +139,19 @@ def upconv_forward_folded(x, weight):
                     acc = acc + torch.einsum("oc,bcij->boij", wf[a, b, dy, dx], win)
             y[:, :, a::2, b::2] = acc
     return F.elu(y)
+
+
+def upconv_unfold_grads(gwf):
+    """Adjoint of upconv_fold_weights: [2][2][2][2][Cout][Cin] -> [Cout,Cin,3,3]; tap (ky, kx) collects the folded entries whose
+    tap sets contain it (what upconv_unfold_kernel computes from the folded weight gradient)."""
+    import torch
+    rows = {(0, 0): (0,), (0, 1): (1, 2), (1, 0): (0, 1), (1, 1): (2,)}
+    gw = torch.zeros(tuple(gwf.shape[4:]) + (3, 3), dtype=gwf.dtype)
+    for a in range(2):
+        for b in range(2):
+            for dy in range(2):
+                for dx in range(2):
+                    for ky in rows[(a, dy)]:
+                        for kx in rows[(b, dx)]:
+                            gw[:, :, ky, kx] += gwf[a, b, dy, dx]
+    return gw

@@ -20,6 +20,19 @@ def test_upconv_oracle_vs_golden(g):
     assert max_rel_to_peak(tp.upconv_forward_folded(x, w).numpy(), g["f64_y"]) <= 2e-6
 
 
+def test_upconv_fold_and_unfold_are_adjoint():
+    """<fold(W), G> == <W, unfold(G)> and autograd through the folded restatement gives unfold(grad of the folded weights):
+    pins the un-fold step of the weight-gradient kernel to the oracle."""
+    gen = torch.Generator().manual_seed(5)
+    w = torch.randn(6, 5, 3, 3, generator=gen, dtype=torch.float64)
+    g = torch.randn(2, 2, 2, 2, 6, 5, generator=gen, dtype=torch.float64)
+    assert abs(float((tp.upconv_fold_weights(w) * g).sum() - (w * tp.upconv_unfold_grads(g)).sum())) < 1e-10
+    wl = w.clone().requires_grad_(True)
+    wf = tp.upconv_fold_weights(wl)
+    (wf * g).sum().backward()
+    assert torch.allclose(wl.grad, tp.upconv_unfold_grads(g), atol=1e-12)
+
+
 def _oracle_grads(x, w, gy, dtype):
     xd = x.detach().clone().to(dtype).requires_grad_(True)
     wd = w.detach().clone().to(dtype).requires_grad_(True)
