@@ -102,32 +102,6 @@ struct UpconvArgs {
     int B, Cin, Cout, h, w, tiles_x, tiles_y;
 };
 
-// Wf[a][b][dy][dx][o][c] from W[o][c][3][3]
-__global__ void upconv_fold_kernel(const float *__restrict__ w, float *__restrict__ wf, int cout, int cin)
-{
-    const int e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= cout * cin) return;
-    float t[3][3];
-#pragma unroll
-    for (int k = 0; k < 9; ++k) t[k / 3][k % 3] = __ldg(w + (size_t)e * 9 + k);
-#pragma unroll
-    for (int a = 0; a < 2; ++a)
-#pragma unroll
-        for (int b = 0; b < 2; ++b)
-#pragma unroll
-            for (int dy = 0; dy < 2; ++dy)
-#pragma unroll
-                for (int dx = 0; dx < 2; ++dx) {
-                    // tap rows of (a, dy): a=0: {0} | {1,2}; a=1: {0,1} | {2}
-                    const int y0 = a == 0 ? (dy == 0 ? 0 : 1) : (dy == 0 ? 0 : 2), y1 = a == 0 ? (dy == 0 ? 0 : 2) : (dy == 0 ? 1 : 2);
-                    const int x0 = b == 0 ? (dx == 0 ? 0 : 1) : (dx == 0 ? 0 : 2), x1 = b == 0 ? (dx == 0 ? 0 : 2) : (dx == 0 ? 1 : 2);
-                    float s = 0.f;
-                    for (int ky = y0; ky <= y1; ++ky)
-                        for (int kx = x0; kx <= x1; ++kx) s += t[ky][kx];
-                    wf[(size_t)(((a * 2 + b) * 2 + dy) * 2 + dx) * cout * cin + e] = s;
-                }
-}
-
 // The forward's A operand, ready to use: the folded weights split (hi words, bf16 pairs of the remainders and of the hi
 // parts) and laid out as the MMA fragments the lanes load, [a][out-channel block of 32][k-step of 8 c][product (b,dy,dx)]
 // [m-tile][lane][8 words] -- a stage's chunk is one contiguous 128-bit-copyable run, a fragment two 128-bit loads, and no
@@ -385,15 +359,43 @@ __global__ void upconv_eplanes_kernel(const float *__restrict__ gy, const float 
     for (int ab = 0; ab < 4; ++ab) e[(size_t)ab * nlow + idx] = g4[ab] * elu_grad_from_out(y4[ab]);
 }
 
+// The input gradient's A operand (A[m = c][k = o] = Wf[p][o][c]) as ready fragments, like the forward's:
+// [input-channel block of 32][k-step of 8 out channels][16 products][2 m-tiles][lane][8 words].
+__global__ void upconv_fold_frag_t_kernel(const float *__restrict__ w, uint4 *__restrict__ wfrag, int cout, int cin)
+{
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long total = (long long)(cin / 32) * (cout / 8) * 16 * 2 * 32;
+    if (idx >= total) return;
+    const int lane = (int)(idx & 31), mt = (int)((idx >> 5) & 1), p = (int)((idx >> 6) & 15);
+    const long long r = idx >> 10;
+    const int ks = (int)(r % (cout / 8)), cb = (int)(r / (cout / 8));
+    const int a = p >> 3, b = (p >> 2) & 1, dy = (p >> 1) & 1, dx = p & 1, g = lane >> 2, t = lane & 3;
+    const int y0 = a == 0 ? (dy == 0 ? 0 : 1) : (dy == 0 ? 0 : 2), y1 = a == 0 ? (dy == 0 ? 0 : 2) : (dy == 0 ? 1 : 2);
+    const int x0 = b == 0 ? (dx == 0 ? 0 : 1) : (dx == 0 ? 0 : 2), x1 = b == 0 ? (dx == 0 ? 0 : 2) : (dx == 0 ? 1 : 2);
+    float v[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {                                    // (row g, k t), (row g+8, k t), (row g, k t+4), (row g+8, k t+4)
+        const int c = 32 * cb + 16 * mt + g + 8 * (q & 1), o = 8 * ks + t + 4 * (q >> 1);
+        const float *src = w + ((size_t)o * cin + c) * 9;
+        float sum = 0.f;
+        for (int ky = y0; ky <= y1; ++ky)
+            for (int kx = x0; kx <= x1; ++kx) sum += __ldg(src + ky * 3 + kx);
+        v[q] = sum;
+    }
+    UFragA f;
+    make_a(v[0], v[1], v[2], v[3], f);
+    wfrag[2 * idx] = make_uint4(f.h[0], f.h[1], f.h[2], f.h[3]);
+    wfrag[2 * idx + 1] = make_uint4(f.s[0], f.s[1], f.s[2], f.s[3]);
+}
+
 constexpr int kDgKC = 8;                              // out channels (K) per stage: one k-step
-constexpr int kDgWS = 40;                             // floats per out-channel row of a weight chunk (32 c + 8: conflict-free A)
-constexpr int kDgWFloats = 16 * kDgKC * kDgWS;
-template <bool TALL> constexpr int kDgEFloats = 4 * kDgKC * UcTile<TALL>::XS;
-template <bool TALL> constexpr int kDgStageFloats = kDgEFloats<TALL> + kDgWFloats;
+constexpr int kDgWFloats = 16 * 2 * kUcFrag;             // the stage's 16 products x 2 m-tiles of ready A fragments
+constexpr int kDgEFloats = 4 * kDgKC * 168;
+constexpr int kDgStageFloats = kDgEFloats + kDgWFloats;
 
 struct UpconvBwdArgs {
     const float *x;          // [B][Cin][h][w]
-    const float *wf;         // folded weights [16 p][Cout][Cin]
+    const uint4 *wfrag_t;    // folded weights as the input gradient's A fragments (upconv_fold_frag_t_kernel)
     const float *e;          // phase planes [4][B][Cout][h][w]
     float *gx;               // [B][Cin][h][w]
     float *gwf;              // [16 p][Cout][Cin], zero-filled before the weight-gradient kernel
@@ -406,6 +408,9 @@ template <bool TALL>
 __global__ void __launch_bounds__(128, 2) upconv_dgrad_kernel(const __grid_constant__ UpconvBwdArgs ua)
 {
     using T = UcTile<TALL>;
+    // halo of a plane: TH + 1 rows x TW + 1 columns (153 pixels either way), channel stride 168 = 8 mod 32
+    constexpr int DXR = T::TH + 1, DXC = T::TW + 1, DXS = 168;
+    static_assert(DXR * DXC <= DXS, "halo fits its stride");
     extern __shared__ __align__(16) float smem[];
     const int tid = threadIdx.x, lane = tid & 31, g = lane >> 2, t = lane & 3;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
@@ -419,23 +424,21 @@ __global__ void __launch_bounds__(128, 2) upconv_dgrad_kernel(const __grid_const
     const size_t plane_sz = (size_t)ua.B * Cout * h * w;
 
     auto load_stage = [&](int kc, int buf) {
-        float *es = smem + buf * kDgStageFloats<TALL>, *ws = es + kDgEFloats<TALL>;
+        float *es = smem + buf * kDgStageFloats, *ws = es + kDgEFloats;
         // plane (a, b): smem row r <-> source row i0 - a + r, smem column c <-> source column j0 - b + c
-        for (int idx = tid; idx < 4 * kDgKC * T::XR * T::XC; idx += 128) {
-            const int po = idx / (T::XR * T::XC), rem = idx - po * (T::XR * T::XC);   // po = plane * 8 + o
-            const int r = rem / T::XC, col = rem - r * T::XC;
+        for (int idx = tid; idx < 4 * kDgKC * DXR * DXC; idx += 128) {
+            const int po = idx / (DXR * DXC), rem = idx - po * (DXR * DXC);   // po = plane * 8 + o
+            const int r = rem / DXC, col = rem - r * DXC;
             const int ab = po >> 3, o = po & 7;
             const int sr = i0 - (ab >> 1) + r, sc = j0 - (ab & 1) + col;
             const bool ok = sr >= 0 && sr < h && sc >= 0 && sc < w;
             const float *src = ua.e + (size_t)ab * plane_sz + (((size_t)b_img * Cout + kc * kDgKC + o) * h + (ok ? sr : 0)) * w + (ok ? sc : 0);
-            cp_async4(smem_u32(es + po * T::XS + r * T::XC + col), src, ok);
+            cp_async4(smem_u32(es + po * DXS + r * DXC + col), src, ok);
         }
-        // weights: [16 products][8 out channels][32 input channels]
-        for (int idx = tid; idx < 16 * kDgKC * 8; idx += 128) {
-            const int po = idx >> 3, q = idx & 7;                    // po = product * 8 + o
-            const int p = po >> 3, o = po & 7;
-            const float *src = ua.wf + ((size_t)p * Cout + kc * kDgKC + o) * Cin + c0 + 4 * q;
-            cp_async16(smem_u32(ws + po * kDgWS + 4 * q), src, true);
+        // weights: the stage's 16 products x 2 m-tiles of ready fragments, one contiguous run
+        {
+            const uint4 *src = ua.wfrag_t + ((size_t)blockIdx.y * (Cout / kDgKC) + kc) * (kDgWFloats / 4);
+            for (int idx = tid; idx < kDgWFloats / 4; idx += 128) cp_async16(smem_u32(ws + 4 * idx), src + idx, true);
         }
         cp_async_commit();
     };
@@ -459,21 +462,23 @@ __global__ void __launch_bounds__(128, 2) upconv_dgrad_kernel(const __grid_const
             asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
         __syncthreads();
-        const float *es = smem + buf * kDgStageFloats<TALL>, *ws = es + kDgEFloats<TALL>;
+        const float *es = smem + buf * kDgStageFloats, *ws = es + kDgEFloats;
 #pragma unroll
         for (int p = 0; p < 16; ++p) {                               // p = ((a*2 + b)*2 + dy)*2 + dx
             const int ab = p >> 2, dy = (p >> 1) & 1, dx = p & 1;
             UFragA fa[2];
 #pragma unroll
-            for (int mt = 0; mt < 2; ++mt) {                         // A[m = c][k = o] = Wf[p][o][c]
-                const float *q = ws + (p * kDgKC + t) * kDgWS + 16 * mt + g;
-                make_a(q[0], q[8], q[4 * kDgWS], q[4 * kDgWS + 8], fa[mt]);
+            for (int mt = 0; mt < 2; ++mt) {                         // A[m = c][k = o] = Wf[p][o][c], pre-split
+                const uint4 *q = reinterpret_cast<const uint4 *>(ws + (p * 2 + mt) * kUcFrag) + 2 * lane;
+                const uint4 vh = q[0], vs = q[1];
+                fa[mt].h[0] = vh.x; fa[mt].h[1] = vh.y; fa[mt].h[2] = vh.z; fa[mt].h[3] = vh.w;
+                fa[mt].s[0] = vs.x; fa[mt].s[1] = vs.y; fa[mt].s[2] = vs.z; fa[mt].s[3] = vs.w;
             }
 #pragma unroll
             for (int n = 0; n < 4; ++n) {
-                const float *q = es + (ab * kDgKC + t) * T::XS + (T::row(warp, n) + 1 - dy) * T::XC + T::colb(n) + 1 - dx + g;
+                const float *q = es + (ab * kDgKC + t) * DXS + (T::row(warp, n) + 1 - dy) * DXC + T::colb(n) + 1 - dx + g;
                 UFragB fb;
-                make_b(q[0], q[4 * T::XS], fb);
+                make_b(q[0], q[4 * DXS], fb);
 #pragma unroll
                 for (int mt = 0; mt < 2; ++mt) hmma_b(acc[mt][n], fa[mt].s, fb.s0, fb.s1);
 #pragma unroll
@@ -720,11 +725,11 @@ bool upconv_bwd_supported(int cin, int cout) { return cin > 0 && cout > 0 && cin
 
 size_t upconv_bwd_workspace_bytes(int B, int cin, int cout, int h, int w)
 {
-    return sizeof(float) * ((size_t)32 * cin * cout + (size_t)4 * B * cout * h * w);
+    return sizeof(float) * ((size_t)48 * cin * cout + (size_t)4 * B * cout * h * w);
 }
 
 template <bool TALL>
-static int launch_upconv_bwd_t(UpconvBwdArgs &ua, const float *w, float *wf, float *gw, cudaStream_t s)
+static int launch_upconv_bwd_t(UpconvBwdArgs &ua, const float *w, uint4 *wfrag_t, float *gw, cudaStream_t s)
 {
     using T = UcTile<TALL>;
     const int cin = ua.Cin, cout = ua.Cout;
@@ -734,9 +739,10 @@ static int launch_upconv_bwd_t(UpconvBwdArgs &ua, const float *w, float *wf, flo
     const long long tiles = (long long)ua.tiles_x * ua.tiles_y * ua.B;
     if (tiles > 0x7fffffffLL) return set_error(BTS_ERR_BAD_ARG, "too many tiles");
     if (ua.gx != nullptr) {
-        upconv_fold_kernel<<<(cin * cout + 255) / 256, 256, 0, s>>>(w, wf, cout, cin);
-        if (int er = check_launch("upconv_fold")) return er;
-        const size_t smem_bytes = sizeof(float) * 2 * kDgStageFloats<TALL>;
+        const long long nfrag = (long long)(cin / 32) * (cout / 8) * 16 * 2 * 32;
+        upconv_fold_frag_t_kernel<<<(unsigned)((nfrag + 255) / 256), 256, 0, s>>>(w, wfrag_t, cout, cin);
+        if (int er = check_launch("upconv_fold_frag_t")) return er;
+        const size_t smem_bytes = sizeof(float) * 2 * kDgStageFloats;
         cudaError_t ce = cudaFuncSetAttribute(upconv_dgrad_kernel<TALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
         if (ce != cudaSuccess) return set_error((int)ce, "cudaFuncSetAttribute: %s", cudaGetErrorString(ce));
         upconv_dgrad_kernel<TALL><<<dim3((unsigned)tiles, (unsigned)(cin / 32), 1), 128, smem_bytes, s>>>(ua);
@@ -764,18 +770,19 @@ static int launch_upconv_bwd_t(UpconvBwdArgs &ua, const float *w, float *wf, flo
     return BTS_OK;
 }
 
-// ws = [folded weights 16 Cout Cin | folded weight gradients 16 Cout Cin | phase planes 4 B Cout h w]
+// ws = [folded weights as fragments, 16 Cout Cin x 8 bytes | folded weight gradients 16 Cout Cin | phase planes 4 B Cout h w]
 int launch_upconv_bwd(const float *x, const float *w, const float *y, const float *gy, float *gx, float *gw, int B, int cin, int cout,
                       int h, int wd, void *ws, cudaStream_t s)
 {
-    float *wf = static_cast<float *>(ws), *gwf = wf + (size_t)16 * cin * cout, *e = gwf + (size_t)16 * cin * cout;
+    uint4 *wfrag_t = static_cast<uint4 *>(ws);
+    float *gwf = static_cast<float *>(ws) + (size_t)32 * cin * cout, *e = gwf + (size_t)16 * cin * cout;
     const long long nlow = (long long)B * cout * h * wd;
     upconv_eplanes_kernel<<<(unsigned)((nlow + 255) / 256), 256, 0, s>>>(gy, y, e, nlow, h, wd);
     if (int er = check_launch("upconv_eplanes")) return er;
     UpconvBwdArgs ua;
-    ua.x = x; ua.wf = wf; ua.e = e; ua.gx = gx; ua.gwf = gwf;
+    ua.x = x; ua.wfrag_t = wfrag_t; ua.e = e; ua.gx = gx; ua.gwf = gwf;
     ua.B = B; ua.Cin = cin; ua.Cout = cout; ua.h = h; ua.w = wd;
-    return upconv_tall(h, wd) ? launch_upconv_bwd_t<true>(ua, w, wf, gw, s) : launch_upconv_bwd_t<false>(ua, w, wf, gw, s);
+    return upconv_tall(h, wd) ? launch_upconv_bwd_t<true>(ua, w, wfrag_t, gw, s) : launch_upconv_bwd_t<false>(ua, w, wfrag_t, gw, s);
 }
 
 }  // namespace bts

@@ -56,7 +56,7 @@ def test_argument_validation_needs_no_gpu():
     assert lib.bts_upconv_workspace_bytes(2, 64, 32, 4, 6) == (16 * 64 * 32 + 2 * 64 * 4 * 6) * 8 and lib.bts_upconv_workspace_bytes(1, 0, 32, 4, 4) == 0
     assert lib.bts_upconv_bwd(16, 16, 16, 16, 1, 48, 32, 4, 4, 16, 16, 16, 1 << 20, None) == -2   # backward: cin % 32
     assert lib.bts_upconv_bwd(16, 16, 16, 16, 1, 32, 32, 4, 4, 16, 16, 16, 64, None) == -1       # workspace too small
-    assert lib.bts_upconv_bwd_workspace_bytes(2, 64, 32, 4, 6) == 4 * (32 * 64 * 32 + 4 * 2 * 32 * 4 * 6)
+    assert lib.bts_upconv_bwd_workspace_bytes(2, 64, 32, 4, 6) == 4 * (48 * 64 * 32 + 4 * 2 * 32 * 4 * 6)
 
 
 @pytest.mark.parametrize("cfg", [(128, 128, False), (128, 64, False), (64, 32, False), (32, 16, True),
