@@ -275,7 +275,7 @@ __global__ void __launch_bounds__(128, MT == 1 ? 4 : 2) upconv_fwd_kernel(const 
         }
         __syncthreads();
 #if BTS_UC_DRAIN
-        if ((kc + 1) % BTS_UC_DRAIN == 0 || kc + 1 == nk) {
+        if ((kc + 1) % (BTS_UC_DRAIN * 16 / kUcKC) == 0 || kc + 1 == nk) {   // every BTS_UC_DRAIN x 16 input channels
 #pragma unroll
             for (int mt = 0; mt < MT; ++mt)
 #pragma unroll
